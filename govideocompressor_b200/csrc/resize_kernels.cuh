@@ -1,0 +1,258 @@
+// resize_kernels.cuh -- K1: swscale-equivalent separable resize of 8-bit 4:2:0 frames (sm_100a).
+//
+// Replaces libswscale as reached from client.go:115 (`ffmpeg ... -s WxH`).  Arithmetic contract
+// (bit-exact with swscale's C path: hScale8To15_c + yuv2planeX_8_c):
+//     t[r][x] = min( (sum_j src[r][hpos[x]+j] * hc[x][j]) >> 7, 32767 )
+//     d[y][x] = clip_u8( ((64<<12) + sum_j t[vpos[y]+j][x] * vc[y][j]) >> 19 )
+//
+// Two device paths:
+//   * fused (resize_fused_kernel): one CTA = one 128 x TH output tile of one plane of one frame.
+//     phase 0  source tile -> shared memory (128-bit coalesced loads when the plane is 16 B aligned)
+//     phase 1  horizontal pass, lanes <-> source rows, x marches warp-uniformly so taps/positions are
+//              uniform loads; pixels are consumed as packed words through dp2a (2 taps / instruction)
+//     phase 2  vertical pass from the int32 intermediate tile in shared memory, 4 pixels per lane,
+//              32-bit stores.  No intermediate ever touches HBM: traffic = source + destination.
+//   * two-pass (resize_hpass_kernel / resize_vpass_kernel): any tap count / ratio, int16 intermediate
+//     plane in device scratch.  Used when a plan does not meet the fused kernel's limits.
+//
+// The phase functions are plain C++ over (tid, shared buffers) so tests can run them on the host
+// (tests/emu/emu_resize.cpp, compiled with GVC_EMU) to check indexing before a GPU is involved.
+#pragma once
+#include <stdint.h>
+
+#if defined(GVC_EMU)
+#define GVC_HD inline
+struct gvc_int4 { int x, y, z, w; };
+struct gvc_uint4 { unsigned x, y, z, w; };
+#else
+#define GVC_HD __device__ __forceinline__
+typedef int4  gvc_int4;
+typedef uint4 gvc_uint4;
+#endif
+
+#include "resize_types.h"
+
+namespace gvc {
+
+// ---------------------------------------------------------------- small intrinsics ------------
+GVC_HD int dp2a_lo_su(int coef_pair, unsigned pix, int acc) {   // acc + c.lo*pix.b0 + c.hi*pix.b1
+#if defined(GVC_EMU)
+    return acc + (int)(short)(coef_pair & 0xffff) * (int)(pix & 0xff) + (int)(short)(coef_pair >> 16) * (int)((pix >> 8) & 0xff);
+#else
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(coef_pair), "r"(pix), "r"(acc));
+    return d;
+#endif
+}
+GVC_HD int dp2a_hi_su(int coef_pair, unsigned pix, int acc) {   // acc + c.lo*pix.b2 + c.hi*pix.b3
+#if defined(GVC_EMU)
+    return acc + (int)(short)(coef_pair & 0xffff) * (int)((pix >> 16) & 0xff) + (int)(short)(coef_pair >> 16) * (int)(pix >> 24);
+#else
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(coef_pair), "r"(pix), "r"(acc));
+    return d;
+#endif
+}
+GVC_HD unsigned funnel_r(unsigned lo, unsigned hi, int sh) {    // bytes of hi:lo shifted right by sh (0..24) bits
+#if defined(GVC_EMU)
+    return sh ? (lo >> sh) | (hi << (32 - sh)) : lo;
+#else
+    return __funnelshift_r(lo, hi, sh);
+#endif
+}
+GVC_HD int clip_u8(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }
+GVC_HD int imin(int a, int b) { return a < b ? a : b; }
+GVC_HD int imax(int a, int b) { return a > b ? a : b; }
+
+struct TileGeom {
+    int x0, ncols;   // first output column, number of output columns (<= kTileW)
+    int y0, nrows;   // first output row, number of output rows (<= th)
+    int r0, rows;    // first source row, number of source rows needed (<= kTileRows)
+    int qa0;         // first source word (4 bytes) of the shared tile, multiple of 4 (16 B chunk aligned)
+    int nchunks;     // 16-byte chunks per row that must be loaded
+};
+
+GVC_HD TileGeom tile_geom(const PlaneClassDev &pc, int tx, int ty) {
+    TileGeom g;
+    g.x0    = tx * kTileW;
+    g.ncols = imin(kTileW, pc.dw - g.x0);
+    g.y0    = ty * pc.th;
+    g.nrows = imin(pc.th, pc.dh - g.y0);
+    const int vrow = 4 * pc.vq;
+    g.r0    = pc.vtab[(long long)g.y0 * vrow];
+    g.rows  = pc.vtab[(long long)(g.y0 + g.nrows - 1) * vrow] + pc.vtaps - g.r0;
+    g.qa0   = pc.htab[(long long)g.x0 * kHEntry] & ~3;
+    const int qlast = pc.htab[(long long)(g.x0 + g.ncols - 1) * kHEntry] + pc.hgroups;  // last word touched
+    g.nchunks = ((qlast - g.qa0) >> 2) + 1;
+    return g;
+}
+
+// ---------------------------------------------------------------- phase 0: source tile -> smem --
+// S layout: kTileRows rows x s_chunks chunks of 16 bytes; bytes outside the plane are zero.
+GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, const uint8_t *src,
+                          const TileGeom &g, gvc_uint4 *S) {
+    const int  chunks  = pc.s_chunks;
+    const int  total   = kTileRows * chunks;
+    const bool aligned = pj.spix == 1 && ((((unsigned long long)src) | (unsigned)pj.sstride) & 15) == 0;
+    for (int i = tid; i < total; i += kThreads) {
+        const int r = i / chunks, c = i - r * chunks;
+        const int row = g.r0 + r;
+        const int col = (g.qa0 << 2) + (c << 4);       // first source sample of this chunk
+        gvc_uint4 v;
+        v.x = v.y = v.z = v.w = 0u;
+        if (r < g.rows && row < pc.sh && c < g.nchunks + 1 && col < pc.sw) {
+            const uint8_t *p = src + (long long)row * pj.sstride;
+            if (aligned && col + 16 <= pc.sw) {
+                v = *reinterpret_cast<const gvc_uint4 *>(p + col);
+            } else {
+                unsigned w[4] = {0u, 0u, 0u, 0u};
+                for (int b = 0; b < 16; ++b) {
+                    const int cc = col + b;
+                    if (cc < pc.sw) w[b >> 2] |= (unsigned)p[(long long)cc * pj.spix] << ((b & 3) * 8);
+                }
+                v.x = w[0]; v.y = w[1]; v.z = w[2]; v.w = w[3];
+            }
+        }
+        S[i] = v;
+    }
+}
+
+// ---------------------------------------------------------------- phase 1: horizontal ----------
+// T layout: [quad (4 output columns)][kTPad source rows][4] int32.
+template <int NG>
+GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, const gvc_uint4 *S, gvc_int4 *T) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const int chunks = pc.s_chunks;
+    const gvc_int4 *htab = reinterpret_cast<const gvc_int4 *>(pc.htab);
+    gvc_uint4 c0[kRowGroups], c1[kRowGroups];
+    int       kcur = -2;
+    constexpr int kQuadsPerWarp = kTileW / 4 / kWarps;  // 4
+#pragma unroll 1
+    for (int qi = 0; qi < kQuadsPerWarp; ++qi) {
+        const int xq = (warp * kQuadsPerWarp + qi) * 4;   // tile-relative first column of the quad
+        if (xq >= g.ncols) break;                         // warp-uniform
+        int acc[kRowGroups][4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int      x  = imin(g.x0 + xq + k, pc.dw - 1);
+            const gvc_int4 e0 = htab[(long long)x * 2], e1 = htab[(long long)x * 2 + 1];
+            const int      qrel = e0.x - g.qa0;
+            const int      kc = qrel >> 2, o = qrel & 3, r8 = e0.y;
+            if (kc != kcur) {                              // warp-uniform: slide the two-chunk window
+#pragma unroll
+                for (int rg = 0; rg < kRowGroups; ++rg) {
+                    const gvc_uint4 *row = S + (rg * 32 + lane) * chunks;
+                    c0[rg] = (kc == kcur + 1) ? c1[rg] : row[kc];
+                    c1[rg] = row[kc + 1];
+                }
+                kcur = kc;
+            }
+#pragma unroll
+            for (int rg = 0; rg < kRowGroups; ++rg) {
+                unsigned w0, w1, w2, w3;
+                switch (o) {                               // warp-uniform
+                    case 0:  w0 = c0[rg].x; w1 = c0[rg].y; w2 = c0[rg].z; w3 = c0[rg].w; break;
+                    case 1:  w0 = c0[rg].y; w1 = c0[rg].z; w2 = c0[rg].w; w3 = c1[rg].x; break;
+                    case 2:  w0 = c0[rg].z; w1 = c0[rg].w; w2 = c1[rg].x; w3 = c1[rg].y; break;
+                    default: w0 = c0[rg].w; w1 = c1[rg].x; w2 = c1[rg].y; w3 = c1[rg].z; break;
+                }
+                const unsigned u0 = funnel_r(w0, w1, r8);
+                int a = dp2a_lo_su(e0.z, u0, 0);
+                a     = dp2a_hi_su(e0.w, u0, a);
+                if (NG >= 2) {
+                    const unsigned u1 = funnel_r(w1, w2, r8);
+                    a = dp2a_lo_su(e1.x, u1, a);
+                    a = dp2a_hi_su(e1.y, u1, a);
+                }
+                if (NG >= 3) {
+                    const unsigned u2 = funnel_r(w2, w3, r8);
+                    a = dp2a_lo_su(e1.z, u2, a);
+                    a = dp2a_hi_su(e1.w, u2, a);
+                }
+                acc[rg][k] = imin(a >> 7, 32767);
+            }
+        }
+#pragma unroll
+        for (int rg = 0; rg < kRowGroups; ++rg) {
+            gvc_int4 v;
+            v.x = acc[rg][0]; v.y = acc[rg][1]; v.z = acc[rg][2]; v.w = acc[rg][3];
+            T[((xq >> 2) * kTPad) + rg * 32 + lane] = v;
+        }
+    }
+}
+
+// ---------------------------------------------------------------- phase 2: vertical ------------
+template <int VQ>
+GVC_HD void resize_phase2(int tid, const PlaneClassDev &pc, const PlaneJob &pj, uint8_t *dst,
+                          const TileGeom &g, const gvc_int4 *T) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const gvc_int4 *vtab = reinterpret_cast<const gvc_int4 *>(pc.vtab);
+    const int  xl      = lane * 4;                   // tile-relative column of this lane's 4 pixels
+    const bool active  = xl < g.ncols;
+    const bool store32 = pj.dpix == 1 && ((((unsigned long long)dst) | (unsigned)pj.dstride) & 3) == 0;
+#pragma unroll 1
+    for (int y = g.y0 + warp; y < g.y0 + g.nrows; y += kWarps) {
+        int cf[4 * VQ];
+#pragma unroll
+        for (int i = 0; i < VQ; ++i) {
+            const gvc_int4 e = vtab[(long long)y * VQ + i];
+            cf[4 * i] = e.x; cf[4 * i + 1] = e.y; cf[4 * i + 2] = e.z; cf[4 * i + 3] = e.w;
+        }
+        if (!active) continue;
+        const gvc_int4 *col = T + lane * kTPad + (cf[0] - g.r0);
+        int a0 = 64 << 12, a1 = 64 << 12, a2 = 64 << 12, a3 = 64 << 12;
+#pragma unroll
+        for (int j = 0; j < 4 * VQ - 1; ++j) {
+            if (j < pc.vtaps) {                      // uniform
+                const gvc_int4 t = col[j];
+                const int      c = cf[j + 1];
+                a0 += t.x * c; a1 += t.y * c; a2 += t.z * c; a3 += t.w * c;
+            }
+        }
+        const int b0 = clip_u8(a0 >> 19), b1 = clip_u8(a1 >> 19), b2 = clip_u8(a2 >> 19), b3 = clip_u8(a3 >> 19);
+        uint8_t  *p  = dst + (long long)y * pj.dstride + (long long)(g.x0 + xl) * pj.dpix;
+        if (store32 && xl + 4 <= g.ncols) {
+            *reinterpret_cast<unsigned *>(p) = (unsigned)b0 | ((unsigned)b1 << 8) | ((unsigned)b2 << 16) | ((unsigned)b3 << 24);
+        } else {
+            const int n = g.ncols - xl;
+            p[0] = (uint8_t)b0;
+            if (n > 1) p[pj.dpix] = (uint8_t)b1;
+            if (n > 2) p[2 * pj.dpix] = (uint8_t)b2;
+            if (n > 3) p[3 * pj.dpix] = (uint8_t)b3;
+        }
+    }
+}
+
+// Which plane job / tile does a frame-local tile id belong to?
+GVC_HD int find_job(const ResizeParams &P, int tile) {
+    int j = 0;
+#pragma unroll
+    for (int i = 1; i < 3; ++i)
+        if (i < P.njobs && tile >= P.job[i].tile_base) j = i;
+    return j;
+}
+
+// ---------------------------------------------------------------- two-pass generic path --------
+GVC_HD int generic_h_sample(const GenericClassDev &pc, const uint8_t *row, int spix, int x) {
+    const int16_t *c  = pc.hc + (long long)x * pc.htaps;
+    const int      sp = pc.hp[x];
+    int            a  = 0;
+    for (int j = 0; j < pc.htaps; ++j) {
+        const int col = sp + j;
+        if (col < pc.sw) a += (int)row[(long long)col * spix] * c[j];
+    }
+    return imin(a >> 7, 32767);
+}
+
+GVC_HD int generic_v_sample(const GenericClassDev &pc, const int16_t *tmp, int y, int x) {
+    const int16_t *c  = pc.vc + (long long)y * pc.vtaps;
+    const int      sp = pc.vp[y];
+    int            a  = 64 << 12;
+    for (int j = 0; j < pc.vtaps; ++j) {
+        const int r = sp + j;
+        if (r < pc.sh) a += (int)tmp[(long long)r * pc.dw + x] * c[j];
+    }
+    return clip_u8(a >> 19);
+}
+
+}  // namespace gvc

@@ -1,0 +1,49 @@
+// resize_types.h -- plain structs shared by the resize kernels (device), the plan builder (host C++)
+// and the host emulation harness used by the CPU tests.
+#pragma once
+#include <stdint.h>
+
+namespace gvc {
+
+constexpr int kTileW      = 128;  // output columns per tile (32 lanes x 4 pixels)
+constexpr int kThreads    = 256;
+constexpr int kWarps      = kThreads / 32;
+constexpr int kRowGroups  = 2;    // source rows per tile <= 64 (lanes <-> rows, 2 groups)
+constexpr int kTileRows   = kRowGroups * 32;
+constexpr int kTPad       = kTileRows + 1;  // odd row pitch of the intermediate tile (bank spread)
+constexpr int kHEntry     = 8;    // int32 words per horizontal table entry: q, r8, 6 packed tap pairs
+constexpr int kMaxHGroups = 3;    // <= 12 horizontal taps in the fused kernel
+
+struct PlaneClassDev {            // geometry + tables shared by all planes of one class (luma / chroma)
+    int sw, sh, dw, dh;
+    int hgroups;                  // 4-tap groups actually used (1..3)
+    int vtaps;                    // vertical taps
+    int vq;                       // int4 per vertical table row (row = vpos, taps..., zero padded)
+    int th;                       // output rows per tile
+    int tiles_x, tiles_y;
+    int s_chunks;                 // odd; 16-byte chunks per source-tile row in shared memory
+    const int32_t *htab;          // [dw][kHEntry]
+    const int32_t *vtab;          // [dh][4*vq]
+};
+
+struct PlaneJob {
+    const uint8_t *src; int sstride; int spix; unsigned long long sframe;
+    uint8_t       *dst; int dstride; int dpix; unsigned long long dframe;
+    int cls;                      // index into ResizeParams::cls
+    int tile_base;                // first tile id of this plane within a frame
+};
+
+struct ResizeParams {
+    PlaneClassDev cls[2];
+    PlaneJob      job[3];
+    int           njobs;
+    int           tiles_per_frame;
+};
+
+struct GenericClassDev {
+    int sw, sh, dw, dh, htaps, vtaps;
+    const int16_t *hc; const int32_t *hp;   // [dw][htaps], [dw]
+    const int16_t *vc; const int32_t *vp;   // [dh][vtaps], [dh]
+};
+
+}  // namespace gvc

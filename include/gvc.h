@@ -1,0 +1,101 @@
+/*
+ * gvc.h -- C ABI of libgvc.so, the B200 (sm_100a) implementation of goVideoCompressor's
+ * per-segment compress path.
+ *
+ * What it replaces.  The reference worker transcodes one segment by spawning an external
+ * process: client.go:101-130 `convert(path, args)` builds `ffmpeg -i <id>.mp4 <args...> c<id>.mp4`
+ * (client.go:103-112), runs it (client.go:115-118) and writes its stderr to c<id>.mp4.log
+ * (client.go:120-123).  There is no FFI in the reference; this header is the boundary a cgo
+ * build of client.go binds instead of exec.Command (see INTEGRATION.md for the stub).
+ *
+ * Conventions: every function returns GVC_OK (0) or a negative gvc_status; nothing throws or
+ * aborts; no torch / C++ types cross the boundary; pointers are plain host or device addresses
+ * as each function states; `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ * There is NO CPU fallback: without a usable CUDA device every compute entry point fails with
+ * GVC_ERR_NO_DEVICE / GVC_ERR_CUDA.
+ */
+#ifndef GVC_H
+#define GVC_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum gvc_status {
+    GVC_OK              = 0,
+    GVC_ERR_INVALID_ARG = -1,
+    GVC_ERR_NO_DEVICE   = -2,
+    GVC_ERR_CUDA        = -3,
+    GVC_ERR_NOMEM       = -4,
+    GVC_ERR_UNSUPPORTED = -5, /* e.g. -vcodec other than libx264: no fallback (north_star) */
+    GVC_ERR_IO          = -6,
+    GVC_ERR_NOT_INIT    = -7,
+    GVC_ERR_TOO_LARGE   = -8
+} gvc_status;
+
+/* pixel layouts (values follow libavutil's AV_PIX_FMT_* so ffmpeg-side code can pass them through) */
+#define GVC_PIX_YUV420P 0  /* three planes Y, U, V           (AV_PIX_FMT_YUV420P) */
+#define GVC_PIX_NV12    23 /* Y plane + interleaved UV plane (AV_PIX_FMT_NV12)    */
+
+/* scaler kernels (values follow libswscale's SWS_* flags; ffmpeg's default for -s / -vf scale is bicubic) */
+#define GVC_SCALE_BILINEAR 2
+#define GVC_SCALE_BICUBIC  4
+
+/* ---------------------------------------------------------------- library life cycle ---------- */
+
+/* Replaces: process start-up of the spawned ffmpeg (client.go:115).  Selects the CUDA device for
+ * this worker process (one worker per GPU).  device_ordinal < 0 reads env GVC_DEVICE
+ * (default 0) -- env vars are the worker's configuration mechanism (client.go:22-36). */
+int gvc_init(int device_ordinal);
+void gvc_shutdown(void);
+
+const char *gvc_strerror(int status);
+/* Detail text of the most recent failure on the calling thread ("" if none). */
+const char *gvc_last_error(void);
+/* Frees buffers handed out by this library (the log returned by gvc_transcode_*). */
+void gvc_free(void *p);
+/* "gvc-b200 <version> sm_100a" */
+const char *gvc_version(void);
+
+/* ---------------------------------------------------------------- resize (K1) ----------------- */
+/* Replaces: libswscale as reached by `-s WxH` / `-vf scale=W:H` in the args string that
+ * server.go:179 sends and client.go:105-115 splices into the ffmpeg command line.  Results are
+ * bit-identical to sws_scale() of FFmpeg's C path (flags algo|SWS_BITEXACT|SWS_ACCURATE_RND).   */
+
+typedef struct gvc_resize_plan gvc_resize_plan;
+
+/* Builds the polyphase filter banks (libswscale utils.c initFilter semantics) and uploads the
+ * device tables.  pix_fmt: GVC_PIX_*; algo: GVC_SCALE_*.  Needs gvc_init(). */
+int  gvc_resize_plan_create(gvc_resize_plan **plan, int src_w, int src_h, int dst_w, int dst_h,
+                            int pix_fmt, int algo);
+void gvc_resize_plan_destroy(gvc_resize_plan *plan);
+
+/* A batch of n_frames equally laid out frames.  plane[k] points at frame 0's plane k; frame f's
+ * plane k starts at plane[k] + f*frame_stride[k]; rows are stride[k] bytes apart.  YUV420P uses
+ * k = 0..2, NV12 k = 0..1 (entry 2 ignored). */
+typedef struct gvc_frames {
+    uint8_t *plane[3];
+    int      stride[3];
+    size_t   frame_stride[3];
+} gvc_frames;
+
+/* src/dst are DEVICE pointers.  Asynchronous on `stream`. */
+int gvc_resize_frames_device(const gvc_resize_plan *plan, const gvc_frames *src, const gvc_frames *dst,
+                             int n_frames, void *stream);
+/* src/dst are HOST pointers (pinned or pageable): copies in, runs the kernels, copies out,
+ * returns when dst is complete.  Staging buffers are cached inside the plan. */
+int gvc_resize_frames_host(gvc_resize_plan *plan, const gvc_frames *src, const gvc_frames *dst, int n_frames);
+
+/* Introspection for tests / bench: which kernel path the plan uses (1 = fused smem-tiled kernel,
+ * 0 = two-pass kernel with an int16 intermediate plane in device scratch) and tap counts. */
+int gvc_resize_plan_info(const gvc_resize_plan *plan, int *fused, int *h_taps_luma, int *v_taps_luma);
+/* Forces the two-pass path (tests exercise both). */
+int gvc_resize_plan_force_two_pass(gvc_resize_plan *plan, int on);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GVC_H */

@@ -1,0 +1,61 @@
+"""Loader for tests/emu/libgvc_emu.so: the CUDA resize phases compiled for the host (test harness only)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+EDIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "emu")
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is None:
+        subprocess.check_call(["make", "-s", "-C", EDIR])
+        _lib = ctypes.CDLL(os.path.join(EDIR, "libgvc_emu.so"))
+    return _lib
+
+
+def out_planes(dw, dh, fmt, pad=0):
+    cdw, cdh = (dw + 1) // 2, (dh + 1) // 2
+    if fmt == "yuv420p":
+        return [np.zeros((dh, dw + pad), np.uint8), np.zeros((cdh, cdw + pad), np.uint8), np.zeros((cdh, cdw + pad), np.uint8)]
+    return [np.zeros((dh, dw + pad), np.uint8), np.zeros((cdh, 2 * cdw + pad), np.uint8)]
+
+
+def resize(planes, sw, sh, dw, dh, fmt="yuv420p", algo=4, mode=0, pad=0):
+    """mode 0: fused-kernel phases, 1: two-pass kernels.  Returns (rc, planes) with rc 1 = fused not eligible."""
+    lib = load()
+    outs = out_planes(dw, dh, fmt, pad)
+    n = len(planes)
+    P3, I3, Z3 = ctypes.c_void_p * 3, ctypes.c_int * 3, ctypes.c_size_t * 3
+    sp = P3(*([p.ctypes.data for p in planes] + [None] * (3 - n)))
+    ss = I3(*([p.strides[0] for p in planes] + [0] * (3 - n)))
+    dp = P3(*([p.ctypes.data for p in outs] + [None] * (3 - n)))
+    ds = I3(*([p.strides[0] for p in outs] + [0] * (3 - n)))
+    z = Z3(0, 0, 0)
+    rc = lib.emu_resize(sp, ss, z, dp, ds, z, 1, sw, sh, dw, dh, 0 if fmt == "yuv420p" else 23, algo, mode)
+    if pad:
+        widths = [dw, (dw + 1) // 2, (dw + 1) // 2] if fmt == "yuv420p" else [dw, 2 * ((dw + 1) // 2)]
+        for o, w in zip(outs, widths):
+            assert not o[:, w:].any(), "kernel wrote into row padding"
+        outs = [o[:, :w] for o, w in zip(outs, widths)]
+    return rc, outs
+
+
+def filter_bank(src_len, dst_len, algo, one):
+    lib = load()
+    coef = np.zeros((dst_len, 64), np.int16)
+    pos = np.zeros(dst_len, np.int32)
+    taps = lib.emu_filter_bank(src_len, dst_len, algo, one, coef.ctypes.data_as(ctypes.c_void_p),
+                               pos.ctypes.data_as(ctypes.c_void_p), 64)
+    assert taps > 0
+    return coef.reshape(-1)[: dst_len * taps].reshape(dst_len, taps).copy(), pos
+
+
+def plan_info(sw, sh, dw, dh, algo):
+    out = (ctypes.c_int * 8)()
+    assert load().emu_plan_info(sw, sh, dw, dh, algo, out) == 0
+    return dict(fused=bool(out[0]), ng=out[1], vq=out[2], th_luma=out[3], th_chroma=out[4], smem=out[5],
+                h_taps=out[6], v_taps=out[7])

@@ -75,3 +75,36 @@ def scale(planes, sw, sh, dw, dh, fmt=AV_PIX_FMT_YUV420P, algo=SWS_BICUBIC, extr
     if r != dh:
         raise RuntimeError(f"sws_scale returned {r}, expected {dh}")
     return outs
+
+
+class Scaler:
+    """A reusable context (what a long-running ffmpeg holds): create once, scale many frames."""
+
+    def __init__(self, sw, sh, dw, dh, fmt=AV_PIX_FMT_YUV420P, algo=SWS_BICUBIC, extra=SWS_BITEXACT | SWS_ACCURATE_RND):
+        self.lib = load()
+        self.sw, self.sh, self.dw, self.dh, self.fmt = sw, sh, dw, dh, fmt
+        self.ctx = self.lib.sws_getContext(sw, sh, fmt, dw, dh, fmt, algo | extra, None, None, None)
+        if not self.ctx:
+            raise RuntimeError("sws_getContext failed")
+        cdw, cdh = (dw + 1) // 2, (dh + 1) // 2
+        if fmt == AV_PIX_FMT_YUV420P:
+            self.outs = [np.zeros((dh, dw), np.uint8), np.zeros((cdh, cdw), np.uint8), np.zeros((cdh, cdw), np.uint8)]
+        else:
+            self.outs = [np.zeros((dh, dw), np.uint8), np.zeros((cdh, 2 * cdw), np.uint8)]
+        n = len(self.outs)
+        self.dp = (ctypes.c_void_p * 4)(*[p.ctypes.data for p in self.outs] + [None] * (4 - n))
+        self.ds = (ctypes.c_int * 4)(*[p.strides[0] for p in self.outs] + [0] * (4 - n))
+
+    def __call__(self, planes):
+        n = len(planes)
+        sp = (ctypes.c_void_p * 4)(*[p.ctypes.data for p in planes] + [None] * (4 - n))
+        ss = (ctypes.c_int * 4)(*[p.strides[0] for p in planes] + [0] * (4 - n))
+        r = self.lib.sws_scale(self.ctx, sp, ss, 0, self.sh, self.dp, self.ds)
+        if r != self.dh:
+            raise RuntimeError("sws_scale failed")
+        return self.outs
+
+    def __del__(self):
+        if getattr(self, "ctx", None):
+            self.lib.sws_freeContext(self.ctx)
+            self.ctx = None
