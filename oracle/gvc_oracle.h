@@ -64,6 +64,37 @@ int gvc_oracle_sws_yuv420p(const uint8_t *const src[3], const int sstride[3], in
 int gvc_oracle_sws_nv12(const uint8_t *const src[2], const int sstride[2], int sw, int sh,
                         uint8_t *const dst[2], const int dstride[2], int dw, int dh, int algo);
 
+#include <stddef.h>
+
+/* ---------------------------------------------------------------- x264-semantics routines (h264_core.c) --- */
+void gvc_oracle_quant4_tables(int qp, int intra, uint16_t mf[16], uint16_t bias[16]);
+void gvc_oracle_quant8_tables(int qp, int intra, uint16_t mf[64], uint16_t bias[64]);
+int  gvc_oracle_dequant4_scale(int qp, int idx);
+int  gvc_oracle_dequant8_scale(int qp, int idx);
+int  gvc_oracle_chroma_qp(int qp);
+void gvc_oracle_sub4x4_dct(int16_t c[16], const uint8_t *src, int sstride, const uint8_t *pred, int pstride);
+void gvc_oracle_sub8x8_dct8(int16_t c[64], const uint8_t *src, int sstride, const uint8_t *pred, int pstride);
+void gvc_oracle_dct4x4dc(int16_t d[16]);
+void gvc_oracle_idct4x4dc(int16_t d[16]);
+void gvc_oracle_dct2x2dc(int16_t d[4]);
+int  gvc_oracle_quant(int16_t *c, int n, const uint16_t *mf, const uint16_t *bias);
+int  gvc_oracle_quant_dc(int16_t *c, int n, int mf, int bias);
+void gvc_oracle_dequant4(int16_t c[16], int qp);
+void gvc_oracle_dequant8(int16_t c[64], int qp);
+void gvc_oracle_dequant4_dc(int16_t c[16], int qp);
+void gvc_oracle_dequant2x2_dc(int16_t c[4], int qp);
+void gvc_oracle_add4x4_idct(uint8_t *dst, int dstride, const uint8_t *pred, int pstride, const int16_t c[16]);
+void gvc_oracle_add8x8_idct8(uint8_t *dst, int dstride, const uint8_t *pred, int pstride, const int16_t c[64]);
+int  gvc_oracle_sad(const uint8_t *a, int as, const uint8_t *b, int bs, int w, int h);
+int  gvc_oracle_satd(const uint8_t *a, int as, const uint8_t *b, int bs, int w, int h);
+void gvc_oracle_hpel_filter(uint8_t *dh, uint8_t *dv, uint8_t *dc, const uint8_t *src, int stride, int w, int h, int pad);
+void gvc_oracle_lowres(const uint8_t *src, int sstride, uint8_t *d0, uint8_t *dh, uint8_t *dv, uint8_t *dc, int dstride,
+                       int lw, int lh);
+void gvc_oracle_mc_luma(uint8_t *dst, int dstride, const uint8_t *const planes[4], int stride, int bx, int by,
+                        int mvx, int mvy, int w, int h);
+void gvc_oracle_mc_chroma(uint8_t *dst, int dstride, const uint8_t *src, int stride, int bx, int by, int mvx, int mvy,
+                          int w, int h);
+
 #ifdef __cplusplus
 }
 #endif
