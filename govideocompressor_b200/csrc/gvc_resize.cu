@@ -5,6 +5,7 @@
 // arithmetic contract and the kernel design.
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -391,3 +392,104 @@ int gvc_resize_frames_host(gvc_resize_plan *p, const gvc_frames *src, const gvc_
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ allocation-free variant ----
+// gvc_resize_frames_device_static(): the two-pass resize with its int16 intermediate plane held in a
+// fixed array that is part of the library image instead of a buffer obtained from cudaMalloc.
+//
+// Who this is for.  gvc_resize_frames_device() may call cudaMalloc the first time a plan takes the
+// two-pass path (or when a bigger batch arrives).  Two kinds of callers cannot live with that:
+//   * a worker in its steady state, with copy streams of the previous and next segment in flight:
+//     cudaMalloc/cudaFree synchronise the whole device, so a lazy allocation stalls every stream;
+//   * a deployment where the GPU's memory is budgeted up front (several workers per GPU under a
+//     memory cap, or frame pools sized to fill HBM): a late allocation can fail after the job was
+//     accepted, and the reference dispatcher never re-queues a failed piece (server.go:276-283).
+// Such callers create their plans and buffers during start-up and then use this entry point, which
+// performs no allocation of any kind: no cudaMalloc/cudaFree, no allocating library call.
+//
+// The price is a fixed ceiling.  The array below occupies kStaticScratchBytes of device memory on
+// every GPU that loads libgvc.so, from load until the process exits, whether or not this entry
+// point is ever called.  A frame needs 2 * (src_h * dst_w + 2 * ceil(src_h/2) * ceil(dst_w/2))
+// bytes of it (4.1 MB for 1080p->720p, 12.4 MB for 2160p->1080p); frames are processed in groups
+// that fit, and a plan whose single frame does not fit is rejected with GVC_ERR_TOO_LARGE.
+namespace {
+
+constexpr size_t kStaticScratchBytes = size_t(16) << 20;   // 16 MiB, the stated maximum
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// In host code `g_static_scratch` is only a handle for the symbol, not an address the GPU can use.
+// The device address is looked up once per device (with that device current) and remembered here.
+constexpr int kMaxDevices = 64;
+int16_t   *g_static_scratch_addr[kMaxDevices] = {};
+std::mutex g_static_scratch_mutex;
+
+int static_scratch_address(int16_t **out) {
+    const int dev = gvc::current_device();
+    if (dev < 0 || dev >= kMaxDevices) { set_error("device ordinal %d outside the supported range 0..%d", dev, kMaxDevices - 1); return GVC_ERR_INVALID_ARG; }
+    std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+    if (!g_static_scratch_addr[dev]) {
+        void *p = nullptr;
+        GVC_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));   // enter() made `dev` current
+        g_static_scratch_addr[dev] = static_cast<int16_t *>(p);
+    }
+    *out = g_static_scratch_addr[dev];
+    return GVC_OK;
+}
+
+}  // namespace
+
+extern "C" int gvc_resize_frames_device_static(const gvc_resize_plan *p, const gvc_frames *src, const gvc_frames *dst,
+                                               int n_frames, void *stream) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!p) { set_error("plan is NULL"); return GVC_ERR_INVALID_ARG; }
+    if (n_frames < 0) { set_error("n_frames < 0"); return GVC_ERR_INVALID_ARG; }
+    if ((rc = check_frames(p, src, p->t.sw, p->t.sh, "src"))) return rc;
+    if ((rc = check_frames(p, dst, p->t.dw, p->t.dh, "dst"))) return rc;
+
+    const bool nv12 = p->fmt == GVC_PIX_NV12;
+    GenericParams G;
+    memset(&G, 0, sizeof(G));
+    G.cls[0] = p->t.gcls[0]; G.cls[1] = p->t.gcls[1]; G.njobs = 3;
+    unsigned long long elems = 0;   // int16 elements of intermediate per frame
+    for (int k = 0; k < 3; ++k) {
+        GenericJob &j = G.job[k];
+        const int sk = nv12 && k == 2 ? 1 : k;
+        j.src = src->plane[sk] + (nv12 && k == 2 ? 1 : 0);
+        j.dst = dst->plane[sk] + (nv12 && k == 2 ? 1 : 0);
+        j.sstride = src->stride[sk]; j.dstride = dst->stride[sk];
+        j.sframe = src->frame_stride[sk]; j.dframe = dst->frame_stride[sk];
+        j.spix = j.dpix = nv12 && k > 0 ? 2 : 1;
+        j.cls = k == 0 ? 0 : 1;
+        j.scratch_off = elems;
+        elems += (unsigned long long)G.cls[j.cls].sh * G.cls[j.cls].dw;
+    }
+    G.scratch_per_frame = elems;
+    const size_t capacity = kStaticScratchBytes / sizeof(int16_t);
+    if (elems > capacity) {
+        set_error("one %dx%d -> %dx%d frame needs %llu bytes of intermediate; the built-in scratch of "
+                  "gvc_resize_frames_device_static holds %zu bytes (use gvc_resize_frames_device instead)",
+                  p->t.sw, p->t.sh, p->t.dw, p->t.dh, elems * 2ull, kStaticScratchBytes);
+        return GVC_ERR_TOO_LARGE;
+    }
+    if (n_frames == 0) return GVC_OK;
+    int16_t *scratch = nullptr;
+    if ((rc = static_scratch_address(&scratch))) return rc;
+
+    // Nothing in the scratch has to start at zero: the horizontal pass writes every element the
+    // vertical pass reads (all src_h x dst_w samples of each plane), so whatever an earlier call left
+    // behind is overwritten before it can be observed.
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int group = (int)std::min<unsigned long long>({(unsigned long long)n_frames, capacity / elems, 65535ull / 3});
+    for (int f0 = 0; f0 < n_frames; f0 += group) {
+        const int nf = std::min(group, n_frames - f0);
+        GenericParams Q = G;
+        for (int k = 0; k < 3; ++k) { Q.job[k].src += (size_t)f0 * Q.job[k].sframe; Q.job[k].dst += (size_t)f0 * Q.job[k].dframe; }
+        const int mdw = G.cls[0].dw, msh = G.cls[0].sh, mdh = G.cls[0].dh;
+        resize_hpass_kernel<<<dim3((mdw + 255) / 256, msh, nf * 3), 256, 0, st>>>(Q, scratch);
+        GVC_CUDA(cudaGetLastError());
+        resize_vpass_kernel<<<dim3((mdw + 255) / 256, mdh, nf * 3), 256, 0, st>>>(Q, scratch);
+        GVC_CUDA(cudaGetLastError());
+    }
+    return GVC_OK;
+}

@@ -42,6 +42,7 @@ def load_library():
     lib.gvc_resize_plan_destroy.argtypes = [c_void_p]
     lib.gvc_resize_plan_destroy.restype = None
     lib.gvc_resize_frames_device.argtypes = [c_void_p, ctypes.POINTER(Frames), ctypes.POINTER(Frames), c_int, c_void_p]
+    lib.gvc_resize_frames_device_static.argtypes = [c_void_p, ctypes.POINTER(Frames), ctypes.POINTER(Frames), c_int, c_void_p]
     lib.gvc_resize_frames_host.argtypes = [c_void_p, ctypes.POINTER(Frames), ctypes.POINTER(Frames), c_int]
     lib.gvc_resize_plan_info.argtypes = [c_void_p] + [ctypes.POINTER(c_int)] * 3
     lib.gvc_resize_plan_force_two_pass.argtypes = [c_void_p, c_int]

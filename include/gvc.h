@@ -89,6 +89,24 @@ int gvc_resize_frames_device(const gvc_resize_plan *plan, const gvc_frames *src,
  * returns when dst is complete.  Staging buffers are cached inside the plan. */
 int gvc_resize_frames_host(gvc_resize_plan *plan, const gvc_frames *src, const gvc_frames *dst, int n_frames);
 
+/* No counterpart in the reference: an extra entry point for callers that must not allocate.
+ * Same result as gvc_resize_frames_device() (src/dst are DEVICE pointers, asynchronous on `stream`), but
+ * it always runs the two-pass kernels and keeps their int16 intermediate plane in a fixed 16 MiB array
+ * built into the library, so it never calls cudaMalloc/cudaFree or any other allocating routine.  Meant
+ * for a worker in its steady state (cudaMalloc would synchronise the device and stall the copy streams of
+ * neighbouring segments) and for GPUs whose memory is fully budgeted at start-up (a late allocation could
+ * fail after the job was accepted; server.go:276-283 never re-queues a failed piece).
+ *   - Limit: one frame needs 2*(src_h*dst_w + 2*ceil(src_h/2)*ceil(dst_w/2)) bytes of the array (4.1 MB for
+ *     1080p->720p, 12.4 MB for 2160p->1080p); larger plans return GVC_ERR_TOO_LARGE.  The 16 MiB are held on
+ *     every GPU that loads libgvc.so until the process exits.
+ *   - The first call on a device looks up the array's device address (one cudaGetSymbolAddress); make that
+ *     first call before starting any stream capture.
+ *   - All calls share the one array: calls whose kernels can overlap on the GPU (different streams, or
+ *     several host threads) race on it.  Serialise them on one stream.  Nothing in the array needs clearing
+ *     between calls; every element read has been written earlier in the same call. */
+int gvc_resize_frames_device_static(const gvc_resize_plan *plan, const gvc_frames *src, const gvc_frames *dst,
+                                    int n_frames, void *stream);
+
 /* Introspection for tests / bench: which kernel path the plan uses (1 = fused smem-tiled kernel,
  * 0 = two-pass kernel with an int16 intermediate plane in device scratch) and tap counts. */
 int gvc_resize_plan_info(const gvc_resize_plan *plan, int *fused, int *h_taps_luma, int *v_taps_luma);
