@@ -130,37 +130,34 @@ void gvc_oracle_sub8x8_dct8(int16_t c[64], const uint8_t *src, int sstride, cons
     for (int i = 0; i < 64; i++) c[i] = (int16_t)d[i];
 }
 
-/* x264 dct4x4dc: 4x4 Hadamard of the luma DCs of an Intra16x16 MB, (x+1)>>1 on the second pass */
-void gvc_oracle_dct4x4dc(int16_t d[16])
+/* 4x4 Hadamard butterflies on rows then columns: out = H * in * H^T, H rows (1,1,1,1),(1,1,-1,-1),(1,-1,-1,1),(1,-1,1,-1) */
+static void hadamard4x4(const int16_t d[16], int o[16])
 {
     int t[16];
     for (int i = 0; i < 4; i++) {
         const int s01 = d[i * 4 + 0] + d[i * 4 + 1], d01 = d[i * 4 + 0] - d[i * 4 + 1];
         const int s23 = d[i * 4 + 2] + d[i * 4 + 3], d23 = d[i * 4 + 2] - d[i * 4 + 3];
-        t[0 * 4 + i] = s01 + s23; t[1 * 4 + i] = s01 - s23; t[2 * 4 + i] = d01 - d23; t[3 * 4 + i] = d01 + d23;
+        t[i * 4 + 0] = s01 + s23; t[i * 4 + 1] = s01 - s23; t[i * 4 + 2] = d01 - d23; t[i * 4 + 3] = d01 + d23;
     }
-    for (int i = 0; i < 4; i++) {
-        const int s01 = t[i * 4 + 0] + t[i * 4 + 1], d01 = t[i * 4 + 0] - t[i * 4 + 1];
-        const int s23 = t[i * 4 + 2] + t[i * 4 + 3], d23 = t[i * 4 + 2] - t[i * 4 + 3];
-        d[i * 4 + 0] = (int16_t)((s01 + s23 + 1) >> 1); d[i * 4 + 1] = (int16_t)((s01 - s23 + 1) >> 1);
-        d[i * 4 + 2] = (int16_t)((d01 - d23 + 1) >> 1); d[i * 4 + 3] = (int16_t)((d01 + d23 + 1) >> 1);
+    for (int j = 0; j < 4; j++) {
+        const int s01 = t[0 + j] + t[4 + j], d01 = t[0 + j] - t[4 + j];
+        const int s23 = t[8 + j] + t[12 + j], d23 = t[8 + j] - t[12 + j];
+        o[0 + j] = s01 + s23; o[4 + j] = s01 - s23; o[8 + j] = d01 - d23; o[12 + j] = d01 + d23;
     }
+}
+/* x264 dct4x4dc: 4x4 Hadamard of the luma DCs of an Intra16x16 MB, (x+1)>>1 on the result */
+void gvc_oracle_dct4x4dc(int16_t d[16])
+{
+    int o[16];
+    hadamard4x4(d, o);
+    for (int i = 0; i < 16; i++) d[i] = (int16_t)((o[i] + 1) >> 1);
 }
 /* x264 idct4x4dc: same butterflies, no rounding (H.264 8.5.10) */
 void gvc_oracle_idct4x4dc(int16_t d[16])
 {
-    int t[16];
-    for (int i = 0; i < 4; i++) {
-        const int s01 = d[i * 4 + 0] + d[i * 4 + 1], d01 = d[i * 4 + 0] - d[i * 4 + 1];
-        const int s23 = d[i * 4 + 2] + d[i * 4 + 3], d23 = d[i * 4 + 2] - d[i * 4 + 3];
-        t[0 * 4 + i] = s01 + s23; t[1 * 4 + i] = s01 - s23; t[2 * 4 + i] = d01 - d23; t[3 * 4 + i] = d01 + d23;
-    }
-    for (int i = 0; i < 4; i++) {
-        const int s01 = t[i * 4 + 0] + t[i * 4 + 1], d01 = t[i * 4 + 0] - t[i * 4 + 1];
-        const int s23 = t[i * 4 + 2] + t[i * 4 + 3], d23 = t[i * 4 + 2] - t[i * 4 + 3];
-        d[i * 4 + 0] = (int16_t)(s01 + s23); d[i * 4 + 1] = (int16_t)(s01 - s23);
-        d[i * 4 + 2] = (int16_t)(d01 - d23); d[i * 4 + 3] = (int16_t)(d01 + d23);
-    }
+    int o[16];
+    hadamard4x4(d, o);
+    for (int i = 0; i < 16; i++) d[i] = (int16_t)o[i];
 }
 /* x264 dct2x2dc / idct2x2 (self-inverse up to scale): d = [[a,b],[c,e]] raster */
 void gvc_oracle_dct2x2dc(int16_t d[4])
