@@ -1,0 +1,22 @@
+// dev_common.h -- definitions shared by all kernel headers.  With GVC_EMU defined the same headers compile as
+// plain C++ so the CPU tests can execute kernel bodies thread by thread (tests/emu, a test harness only).
+#pragma once
+#include <stdint.h>
+
+#if defined(GVC_EMU)
+#define GVC_HD inline
+struct gvc_int4 { int x, y, z, w; };
+struct gvc_uint4 { unsigned x, y, z, w; };
+#else
+#define GVC_HD __device__ __forceinline__
+typedef int4  gvc_int4;
+typedef uint4 gvc_uint4;
+#endif
+
+namespace gvc {
+GVC_HD int clip_u8(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }
+GVC_HD int imin(int a, int b) { return a < b ? a : b; }
+GVC_HD int imax(int a, int b) { return a > b ? a : b; }
+GVC_HD int iclamp(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+GVC_HD int iabs(int v) { return v < 0 ? -v : v; }
+}  // namespace gvc

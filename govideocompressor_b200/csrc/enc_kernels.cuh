@@ -1,0 +1,498 @@
+// enc_kernels.cuh -- encoder-side kernels K2..K6 (sm_100a): border extension, half-sample planes, lowres,
+// hierarchical motion search, motion compensation, 4x4 transform / quant / dequant / reconstruction.
+//
+// These stand where the reference runs libx264 inside the spawned ffmpeg (client.go:115, args
+// `-vcodec libx264` from server.go:69-70).  Arithmetic follows ITU-T H.264 and x264's routines
+// (common/mc.c hpel_filter, frame_init_lowres_core, mc_luma/mc_chroma; common/pixel.c sad/satd;
+// common/dct.c sub4x4_dct/add4x4_idct/dct2x2dc; common/quant.c quant/dequant); the search strategy is
+// specified by oracle/h264_mb.c (every macroblock independent: exhaustive lowres window, fixed
+// full-resolution candidate list, half- then quarter-sample SATD refinement, 16x16 vs 8x8 decision).
+//
+// Bodies are written per (block, thread/lane) with explicit phases so the CPU tests can execute them
+// serially (GVC_EMU, tests/emu); warp-level exchange goes through a small shared-memory record.
+#pragma once
+#include "dev_common.h"
+#include "enc_types.h"
+
+namespace gvc {
+
+// ------------------------------------------------------------------ byte-granular word loads ----
+GVC_HD unsigned ld_u32_any(const uint8_t *p) {   // 4 bytes at any address (reads up to 7 bytes past p's word)
+#if defined(GVC_EMU)
+    return (unsigned)p[0] | ((unsigned)p[1] << 8) | ((unsigned)p[2] << 16) | ((unsigned)p[3] << 24);
+#else
+    const unsigned long long a = (unsigned long long)p;
+    const unsigned *w = reinterpret_cast<const unsigned *>(a & ~3ull);
+    return __funnelshift_r(w[0], w[1], (unsigned)(a & 3) * 8);
+#endif
+}
+GVC_HD void ld_u64_any(const uint8_t *p, unsigned &lo, unsigned &hi) {   // 8 bytes at any address
+#if defined(GVC_EMU)
+    lo = ld_u32_any(p); hi = ld_u32_any(p + 4);
+#else
+    const unsigned long long a = (unsigned long long)p;
+    const unsigned *w = reinterpret_cast<const unsigned *>(a & ~3ull);
+    const unsigned  s = (unsigned)(a & 3) * 8, w0 = w[0], w1 = w[1], w2 = w[2];
+    lo = __funnelshift_r(w0, w1, s); hi = __funnelshift_r(w1, w2, s);
+#endif
+}
+GVC_HD unsigned sad_u8x4(unsigned a, unsigned b, unsigned acc) {   // acc + sum |a.b[i] - b.b[i]|
+#if defined(GVC_EMU)
+    for (int i = 0; i < 4; ++i) { const int d = (int)((a >> (8 * i)) & 255) - (int)((b >> (8 * i)) & 255); acc += d < 0 ? -d : d; }
+    return acc;
+#else
+    return __vsadu4(a, b) + acc;   // VABSDIFF4.U8.ACC
+#endif
+}
+
+// ------------------------------------------------------------------ se(v) bit count ------------
+GVC_HD int se_bits(int v) {
+    const unsigned code = (v > 0 ? 2u * (unsigned)v - 1u : 2u * (unsigned)(-v)) + 1u;
+#if defined(GVC_EMU)
+    int n = 0;
+    for (unsigned c = code; c > 1; c >>= 1) ++n;
+#else
+    const int n = 31 - __clz(code);
+#endif
+    return 2 * n + 1;
+}
+GVC_HD int mv_bits(int mx, int my, int px, int py) { return se_bits(mx - px) + se_bits(my - py); }
+GVC_HD int median3(int a, int b, int c) { return imax(imin(a, b), imin(imax(a, b), c)); }
+
+// ------------------------------------------------------------------ border extension -----------
+GVC_HD void extend_border_px(uint8_t *p, int stride, int w, int h, int x, int y) {
+    if (x >= 0 && x < w && y >= 0 && y < h) return;
+    p[(long long)y * stride + x] = p[(long long)iclamp(y, 0, h - 1) * stride + iclamp(x, 0, w - 1)];
+}
+
+// ------------------------------------------------------------------ K3 lowres ------------------
+// x264 frame_init_lowres_core on the border-extended frame; source coordinates clamp to [lo, hi].
+GVC_HD int avg4(int a, int b, int c, int d) { return (((a + b + 1) >> 1) + ((c + d + 1) >> 1) + 1) >> 1; }
+GVC_HD void lowres_px(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, uint8_t *dh,
+                      uint8_t *dv, uint8_t *dc, int dstride, int lx, int ly) {
+    int v[3][3];
+    for (int j = 0; j < 3; ++j)
+        for (int i = 0; i < 3; ++i)
+            v[j][i] = src[(long long)iclamp(2 * ly + j, y_lo, y_hi) * sstride + iclamp(2 * lx + i, x_lo, x_hi)];
+    const long long o = (long long)ly * dstride + lx;
+    d0[o] = (uint8_t)avg4(v[0][0], v[1][0], v[0][1], v[1][1]);
+    if (dh) dh[o] = (uint8_t)avg4(v[0][1], v[1][1], v[0][2], v[1][2]);
+    if (dv) dv[o] = (uint8_t)avg4(v[1][0], v[2][0], v[1][1], v[2][1]);
+    if (dc) dc[o] = (uint8_t)avg4(v[1][1], v[2][1], v[1][2], v[2][2]);
+}
+
+// ------------------------------------------------------------------ K2 half-sample planes -------
+constexpr int kHpTileW = 64, kHpTileH = 32, kHpThreads = 256, kHpPitch = 72;
+struct HpelSmem {
+    uint8_t src[kHpTileH + 5][kHpPitch];   // tile rows y0-2 .. y0+TH+2, cols x0-2 .. x0+TW+2
+    int16_t v[kHpTileH][kHpPitch];         // unrounded vertical 6-tap sums, cols x0-2 .. x0+TW+2
+};
+GVC_HD int tap6(int a, int b, int c, int d, int e, int f) { return a + f - 5 * (b + e) + 20 * (c + d); }
+
+struct HpelArgs {
+    const uint8_t *src; uint8_t *dh, *dv, *dc;   // all at sample (0,0), same stride
+    int stride, x_lo, x_hi, y_lo, y_hi;          // region to fill = readable region: [x_lo,x_hi) x [y_lo,y_hi)
+};
+GVC_HD void hpel_phase_a(int tid, const HpelArgs &a, int x0, int y0, HpelSmem &sm) {
+    for (int i = tid; i < (kHpTileH + 5) * (kHpTileW + 5); i += kHpThreads) {
+        const int r = i / (kHpTileW + 5), c = i - r * (kHpTileW + 5);
+        sm.src[r][c] = a.src[(long long)iclamp(y0 - 2 + r, a.y_lo, a.y_hi - 1) * a.stride + iclamp(x0 - 2 + c, a.x_lo, a.x_hi - 1)];
+    }
+}
+GVC_HD void hpel_phase_b(int tid, const HpelArgs &a, int x0, int y0, HpelSmem &sm) {
+    for (int i = tid; i < kHpTileH * (kHpTileW + 5); i += kHpThreads) {
+        const int r = i / (kHpTileW + 5), c = i - r * (kHpTileW + 5);
+        const int v = tap6(sm.src[r][c], sm.src[r + 1][c], sm.src[r + 2][c], sm.src[r + 3][c], sm.src[r + 4][c], sm.src[r + 5][c]);
+        sm.v[r][c] = (int16_t)v;
+        const int x = x0 + c - 2, y = y0 + r;
+        if (c >= 2 && c < kHpTileW + 2 && x < a.x_hi && y < a.y_hi) a.dv[(long long)y * a.stride + x] = (uint8_t)clip_u8((v + 16) >> 5);
+    }
+}
+GVC_HD void hpel_phase_c(int tid, const HpelArgs &a, int x0, int y0, HpelSmem &sm) {
+    for (int i = tid; i < kHpTileH * kHpTileW; i += kHpThreads) {
+        const int r = i / kHpTileW, c = i - r * kHpTileW;
+        const int x = x0 + c, y = y0 + r;
+        if (x >= a.x_hi || y >= a.y_hi) continue;
+        const uint8_t *s = &sm.src[r + 2][c];
+        const int16_t *v = &sm.v[r][c];
+        a.dh[(long long)y * a.stride + x] = (uint8_t)clip_u8((tap6(s[0], s[1], s[2], s[3], s[4], s[5]) + 16) >> 5);
+        a.dc[(long long)y * a.stride + x] = (uint8_t)clip_u8((tap6(v[0], v[1], v[2], v[3], v[4], v[5]) + 512) >> 10);
+    }
+}
+
+// ------------------------------------------------------------------ K5 motion compensation -----
+// H.264 8.4.2.2.1 quarter-sample rule / x264 mc_luma: which two planes are averaged for fraction q = fy*4+fx
+// (2 bits per entry: 0 full, 1 H, 2 V, 3 C).
+constexpr unsigned kQpelRef0 = 0u | (1u << 2) | (1u << 4) | (1u << 6) | (0u << 8) | (1u << 10) | (1u << 12) | (1u << 14) |
+                               (2u << 16) | (3u << 18) | (3u << 20) | (3u << 22) | (0u << 24) | (1u << 26) | (1u << 28) | (1u << 30);
+constexpr unsigned kQpelRef1 = 0u | (0u << 2) | (1u << 4) | (0u << 6) | (2u << 8) | (2u << 10) | (3u << 12) | (2u << 14) |
+                               (2u << 16) | (2u << 18) | (3u << 20) | (2u << 22) | (2u << 24) | (2u << 26) | (3u << 28) | (2u << 30);
+
+struct LumaSrc { const uint8_t *s1, *s2; };   // s2 == nullptr: plain copy
+GVC_HD LumaSrc mc_luma_src(const RefPlanes &r, int stride, int x, int y, int mvx, int mvy) {
+    const int fx = mvx & 3, fy = mvy & 3, q = fy * 4 + fx;
+    const uint8_t *pl[4] = {r.y, r.hh, r.hv, r.hc};
+    const long long off = (long long)(y + (mvy >> 2)) * stride + x + (mvx >> 2);
+    LumaSrc o;
+    o.s1 = pl[(kQpelRef0 >> (2 * q)) & 3] + off + (fy == 3 ? stride : 0);
+    o.s2 = (q & 5) ? pl[(kQpelRef1 >> (2 * q)) & 3] + off + (fx == 3 ? 1 : 0) : nullptr;
+    return o;
+}
+// 4x4 luma prediction block at (x,y) with vector (mvx,mvy); out[16] raster
+GVC_HD void mc_luma_4x4(const RefPlanes &r, int stride, int x, int y, int mvx, int mvy, int out[16]) {
+    const LumaSrc s = mc_luma_src(r, stride, x, y, mvx, mvy);
+    for (int j = 0; j < 4; ++j) {
+        const unsigned a = ld_u32_any(s.s1 + (long long)j * stride);
+        if (s.s2) {
+            const unsigned b = ld_u32_any(s.s2 + (long long)j * stride);
+            for (int i = 0; i < 4; ++i) out[j * 4 + i] = (int)(((a >> (8 * i)) & 255) + ((b >> (8 * i)) & 255) + 1) >> 1;
+        } else {
+            for (int i = 0; i < 4; ++i) out[j * 4 + i] = (int)((a >> (8 * i)) & 255);
+        }
+    }
+}
+// 4x4 chroma prediction block at chroma position (x,y), luma vector (mvx,mvy) in quarter luma samples
+GVC_HD void mc_chroma_4x4(const uint8_t *src, int stride, int x, int y, int mvx, int mvy, int out[16]) {
+    const int dx = mvx & 7, dy = mvy & 7;
+    const int cA = (8 - dx) * (8 - dy), cB = dx * (8 - dy), cC = (8 - dx) * dy, cD = dx * dy;
+    const uint8_t *s = src + (long long)(y + (mvy >> 3)) * stride + x + (mvx >> 3);
+    for (int j = 0; j < 4; ++j, s += stride)
+        for (int i = 0; i < 4; ++i) out[j * 4 + i] = (cA * s[i] + cB * s[i + 1] + cC * s[stride + i] + cD * s[stride + i + 1] + 32) >> 6;
+}
+
+// ------------------------------------------------------------------ 4x4 transforms --------------
+GVC_HD void dct4x4(int d[16]) {   // x264 sub4x4_dct butterflies, rows then columns, in place
+    for (int y = 0; y < 4; ++y) {
+        const int s03 = d[y * 4] + d[y * 4 + 3], s12 = d[y * 4 + 1] + d[y * 4 + 2];
+        const int d03 = d[y * 4] - d[y * 4 + 3], d12 = d[y * 4 + 1] - d[y * 4 + 2];
+        d[y * 4] = s03 + s12; d[y * 4 + 1] = 2 * d03 + d12; d[y * 4 + 2] = s03 - s12; d[y * 4 + 3] = d03 - 2 * d12;
+    }
+    for (int x = 0; x < 4; ++x) {
+        const int s03 = d[x] + d[12 + x], s12 = d[4 + x] + d[8 + x];
+        const int d03 = d[x] - d[12 + x], d12 = d[4 + x] - d[8 + x];
+        d[x] = s03 + s12; d[4 + x] = 2 * d03 + d12; d[8 + x] = s03 - s12; d[12 + x] = d03 - 2 * d12;
+    }
+}
+GVC_HD void idct4x4(int c[16]) {  // H.264 8.5.12.2, result includes the (x+32)>>6
+    for (int y = 0; y < 4; ++y) {
+        const int s02 = c[y * 4] + c[y * 4 + 2], d02 = c[y * 4] - c[y * 4 + 2];
+        const int s13 = c[y * 4 + 1] + (c[y * 4 + 3] >> 1), d13 = (c[y * 4 + 1] >> 1) - c[y * 4 + 3];
+        c[y * 4] = s02 + s13; c[y * 4 + 1] = d02 + d13; c[y * 4 + 2] = d02 - d13; c[y * 4 + 3] = s02 - s13;
+    }
+    for (int x = 0; x < 4; ++x) {
+        const int s02 = c[x] + c[8 + x], d02 = c[x] - c[8 + x];
+        const int s13 = c[4 + x] + (c[12 + x] >> 1), d13 = (c[4 + x] >> 1) - c[12 + x];
+        c[x] = (s02 + s13 + 32) >> 6; c[4 + x] = (d02 + d13 + 32) >> 6; c[8 + x] = (d02 - d13 + 32) >> 6; c[12 + x] = (s02 - s13 + 32) >> 6;
+    }
+}
+GVC_HD int quant_one(int c, int mf, int bias) {   // x264 QUANT_ONE
+    return c > 0 ? (int)(((unsigned)(bias + c) * (unsigned)mf) >> 16) : -(int)(((unsigned)(bias - c) * (unsigned)mf) >> 16);
+}
+GVC_HD int dequant_one(int c, int scale, int qp) {   // H.264 8.5.12.1 / x264 dequant_4x4; wraps to int16 like the oracle
+    const int qbits = qp / 6 - 4;
+    const int v = qbits >= 0 ? (c * scale) * (1 << qbits) : (c * scale + (1 << (-qbits - 1))) >> (-qbits);
+    return (int)(int16_t)v;
+}
+GVC_HD int coef_class(int i) { return ((i >> 2) & 1) + (i & 1); }
+GVC_HD int zigzag4(int i) {   // raster index of the i-th coefficient in frame zig-zag order
+    // 0,1,4,8,5,2,3,6,9,12,13,10,7,11,14,15 packed 4 bits each, LSB first
+    const unsigned long long z = 0xFEB7ADC963258410ull;
+    return (int)((z >> (4 * i)) & 15);
+}
+
+// SATD contribution of one 4x4 block: sum |H D H| (always even; callers halve per x264's 8x4 pairing)
+GVC_HD int hadamard4_abs(const int d[16]) {
+    int t[16], s = 0;
+    for (int y = 0; y < 4; ++y) {
+        const int s01 = d[y * 4] + d[y * 4 + 1], d01 = d[y * 4] - d[y * 4 + 1];
+        const int s23 = d[y * 4 + 2] + d[y * 4 + 3], d23 = d[y * 4 + 2] - d[y * 4 + 3];
+        t[y * 4] = s01 + s23; t[y * 4 + 1] = s01 - s23; t[y * 4 + 2] = d01 + d23; t[y * 4 + 3] = d01 - d23;
+    }
+    for (int x = 0; x < 4; ++x) {
+        const int s01 = t[x] + t[4 + x], d01 = t[x] - t[4 + x];
+        const int s23 = t[8 + x] + t[12 + x], d23 = t[8 + x] - t[12 + x];
+        s += iabs(s01 + s23) + iabs(s01 - s23) + iabs(d01 + d23) + iabs(d01 - d23);
+    }
+    return s;
+}
+
+// ------------------------------------------------------------------ K4a lowres search ----------
+// One warp per macroblock.  lanes stride over the (2r+1)^2 candidates; key = cost<<11 | index.
+struct MeLowArgs {
+    const uint8_t *cur, *ref;   // lowres planes at (0,0)
+    int stride, mbw, mbh, r, lambda;
+    int16_t *out_mv;            // (dx,dy) per MB
+};
+GVC_HD void me_lowres_lane(int lane, const MeLowArgs &a, int mx, int my, unsigned *keys /* [32] per warp */) {
+    const int n = 2 * a.r + 1;
+    unsigned  c[8][2];
+    const uint8_t *cp = a.cur + (long long)(8 * my) * a.stride + 8 * mx;   // 8-byte aligned (pitch, origin multiples of 8)
+    for (int j = 0; j < 8; ++j) ld_u64_any(cp + (long long)j * a.stride, c[j][0], c[j][1]);
+    unsigned best = 0xffffffffu;
+    for (int idx = lane; idx < n * n; idx += 32) {
+        const int dy = idx / n - a.r, dx = idx - (idx / n) * n - a.r;
+        const uint8_t *p = a.ref + (long long)(8 * my + dy) * a.stride + 8 * mx + dx;
+        unsigned sad = 0;
+        for (int j = 0; j < 8; ++j) {
+            unsigned lo, hi;
+            ld_u64_any(p + (long long)j * a.stride, lo, hi);
+            sad = sad_u8x4(c[j][0], lo, sad);
+            sad = sad_u8x4(c[j][1], hi, sad);
+        }
+        const unsigned cost = sad + (unsigned)(a.lambda * (se_bits(4 * dx) + se_bits(4 * dy)));
+        const unsigned key  = (cost << 11) | (unsigned)idx;
+        best = key < best ? key : best;
+    }
+    keys[lane] = best;
+}
+GVC_HD void me_lowres_pick(int lane, const MeLowArgs &a, int mx, int my, const unsigned *keys) {
+    if (lane != 0) return;
+    unsigned best = keys[0];
+    for (int i = 1; i < 32; ++i) best = keys[i] < best ? keys[i] : best;
+    const int n = 2 * a.r + 1, idx = (int)(best & 2047);
+    a.out_mv[2 * (my * a.mbw + mx)]     = (int16_t)(idx - (idx / n) * n - a.r);
+    a.out_mv[2 * (my * a.mbw + mx) + 1] = (int16_t)(idx / n - a.r);
+}
+
+// ------------------------------------------------------------------ K4b refinement -------------
+struct MeRefArgs {
+    const uint8_t *cur;          // source luma (0,0)
+    RefPlanes      ref;
+    int            stride, w16, h16, mbw, mbh, lambda;
+    const int16_t *lowres_mv;
+    MbMotion      *out;
+};
+struct MeRefSmem {               // per warp
+    unsigned key[5][32];
+    int      part[32];
+    int      center[5][2], best_mv[5][2], best_cost[5];
+};
+GVC_HD void sq8(int i, int &dx, int &dy) {   // (0,-1),(0,1),(-1,0),(1,0),(-1,-1),(-1,1),(1,-1),(1,1)
+    dx = i < 2 ? 0 : ((i == 2 || i == 4 || i == 5) ? -1 : 1);
+    dy = i == 0 ? -1 : i == 1 ? 1 : (i < 4 ? 0 : ((i & 1) ? 1 : -1));
+}
+GVC_HD void me_mvp(const MeRefArgs &a, int mx, int my, int &px, int &py) {
+    int v[3][2];
+    int nx[3] = {mx - 1, mx, mx + 1}, ny[3] = {my, my - 1, my - 1};
+    if (!(nx[2] < a.mbw && ny[2] >= 0)) { nx[2] = mx - 1; ny[2] = my - 1; }
+    for (int k = 0; k < 3; ++k) {
+        const bool ok = nx[k] >= 0 && nx[k] < a.mbw && ny[k] >= 0 && ny[k] < a.mbh;
+        v[k][0] = ok ? 8 * a.lowres_mv[2 * (ny[k] * a.mbw + nx[k])] : 0;
+        v[k][1] = ok ? 8 * a.lowres_mv[2 * (ny[k] * a.mbw + nx[k]) + 1] : 0;
+    }
+    px = median3(v[0][0], v[1][0], v[2][0]);
+    py = median3(v[0][1], v[1][1], v[2][1]);
+}
+// integer candidates: lane i < 27 evaluates candidate i (four 8x8 SADs)
+GVC_HD void me_ref_int(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
+    for (int k = 0; k < 5; ++k) sm.key[k][lane] = 0xffffffffu;
+    if (lane >= 27) return;
+    int px, py;
+    me_mvp(a, mx, my, px, py);
+    const int x0 = 16 * mx, y0 = 16 * my;
+    int cx, cy;
+    if (lane < 25) {
+        cx = 2 * a.lowres_mv[2 * (my * a.mbw + mx)] + (lane % 5) - 2;
+        cy = 2 * a.lowres_mv[2 * (my * a.mbw + mx) + 1] + (lane / 5) - 2;
+    } else if (lane == 25) {
+        cx = (px + 2) >> 2; cy = (py + 2) >> 2;
+    } else {
+        cx = 0; cy = 0;
+    }
+    cx = iclamp(cx, -x0 - (kEncPad - 8), a.w16 - x0 - 16 + (kEncPad - 8));
+    cy = iclamp(cy, -y0 - (kEncPad - 8), a.h16 - y0 - 16 + (kEncPad - 8));
+    const uint8_t *c = a.cur + (long long)y0 * a.stride + x0;
+    const uint8_t *p = a.ref.y + (long long)(y0 + cy) * a.stride + x0 + cx;
+    unsigned s[4] = {0, 0, 0, 0};
+    for (int j = 0; j < 16; ++j) {
+        unsigned c0, c1, c2, c3, r0, r1, r2, r3;
+        ld_u64_any(c + (long long)j * a.stride, c0, c1);
+        ld_u64_any(c + (long long)j * a.stride + 8, c2, c3);
+        ld_u64_any(p + (long long)j * a.stride, r0, r1);
+        ld_u64_any(p + (long long)j * a.stride + 8, r2, r3);
+        const int k = (j >> 3) * 2;
+        s[k]     = sad_u8x4(c1, r1, sad_u8x4(c0, r0, s[k]));
+        s[k + 1] = sad_u8x4(c3, r3, sad_u8x4(c2, r2, s[k + 1]));
+    }
+    const unsigned bits = (unsigned)(a.lambda * mv_bits(4 * cx, 4 * cy, px, py));
+    sm.key[0][lane] = ((s[0] + s[1] + s[2] + s[3] + bits) << 5) | (unsigned)lane;
+    for (int k = 0; k < 4; ++k) sm.key[1 + k][lane] = ((s[k] + bits) << 5) | (unsigned)lane;
+    // candidate coordinates are recomputed by the picker from the winning lane id
+}
+GVC_HD void me_ref_pick(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
+    if (lane >= 5) return;
+    unsigned best = sm.key[lane][0];
+    for (int i = 1; i < 27; ++i) best = sm.key[lane][i] < best ? sm.key[lane][i] : best;
+    const int i = (int)(best & 31);
+    int px, py;
+    me_mvp(a, mx, my, px, py);
+    const int x0 = 16 * mx, y0 = 16 * my;
+    int cx, cy;
+    if (i < 25) {
+        cx = 2 * a.lowres_mv[2 * (my * a.mbw + mx)] + (i % 5) - 2;
+        cy = 2 * a.lowres_mv[2 * (my * a.mbw + mx) + 1] + (i / 5) - 2;
+    } else if (i == 25) {
+        cx = (px + 2) >> 2; cy = (py + 2) >> 2;
+    } else {
+        cx = 0; cy = 0;
+    }
+    cx = iclamp(cx, -x0 - (kEncPad - 8), a.w16 - x0 - 16 + (kEncPad - 8));
+    cy = iclamp(cy, -y0 - (kEncPad - 8), a.h16 - y0 - 16 + (kEncPad - 8));
+    sm.center[lane][0] = sm.best_mv[lane][0] = 4 * cx;
+    sm.center[lane][1] = sm.best_mv[lane][1] = 4 * cy;
+    sm.best_cost[lane] = 0x7fffffff;
+}
+// lane -> (partition P, 4x4 block offset inside the MB): lanes 0..15 the 16x16 partition, 16..31 the four 8x8s
+GVC_HD void me_lane_block(int lane, int &P, int &ox, int &oy) {
+    if (lane < 16) { P = 0; ox = 4 * (lane & 3); oy = 4 * (lane >> 2); }
+    else { const int l = lane - 16, k = l >> 2, j = l & 3; P = 1 + k; ox = 8 * (k & 1) + 4 * (j & 1); oy = 8 * (k >> 1) + 4 * (j >> 1); }
+}
+// sub-pel candidate ci (-1 = the centre itself) at `step`: each lane's 4x4 Hadamard sum -> sm.part
+GVC_HD void me_ref_satd(int lane, const MeRefArgs &a, int mx, int my, int ci, int step, MeRefSmem &sm) {
+    int P, ox, oy, dx = 0, dy = 0;
+    me_lane_block(lane, P, ox, oy);
+    if (ci >= 0) sq8(ci, dx, dy);
+    const int mvx = sm.center[P][0] + dx * step, mvy = sm.center[P][1] + dy * step;
+    const int x = 16 * mx + ox, y = 16 * my + oy;
+    int pred[16], d[16];
+    mc_luma_4x4(a.ref, a.stride, x, y, mvx, mvy, pred);
+    for (int j = 0; j < 4; ++j) {
+        const unsigned c = ld_u32_any(a.cur + (long long)(y + j) * a.stride + x);
+        for (int i = 0; i < 4; ++i) d[j * 4 + i] = (int)((c >> (8 * i)) & 255) - pred[j * 4 + i];
+    }
+    sm.part[lane] = hadamard4_abs(d) >> 1;
+}
+GVC_HD void me_ref_update(int lane, const MeRefArgs &a, int mx, int my, int ci, int step, MeRefSmem &sm) {
+    const bool leader = lane == 0 || (lane >= 16 && ((lane - 16) & 3) == 0);
+    if (!leader) return;
+    int P, ox, oy, dx = 0, dy = 0;
+    me_lane_block(lane, P, ox, oy);
+    if (ci >= 0) sq8(ci, dx, dy);
+    const int mvx = sm.center[P][0] + dx * step, mvy = sm.center[P][1] + dy * step;
+    int px, py;
+    me_mvp(a, mx, my, px, py);
+    int total = 0;
+    const int n = P == 0 ? 16 : 4;
+    for (int i = 0; i < n; ++i) total += sm.part[lane + i];
+    const int cost = total + a.lambda * mv_bits(mvx, mvy, px, py);
+    if (cost < sm.best_cost[P]) { sm.best_cost[P] = cost; sm.best_mv[P][0] = mvx; sm.best_mv[P][1] = mvy; }
+    if (ci == 7) { sm.center[P][0] = sm.best_mv[P][0]; sm.center[P][1] = sm.best_mv[P][1]; }
+}
+GVC_HD void me_ref_out(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
+    if (lane != 0) return;
+    const int j16 = sm.best_cost[0];
+    const int j8  = sm.best_cost[1] + sm.best_cost[2] + sm.best_cost[3] + sm.best_cost[4] + 8 * a.lambda;
+    MbMotion m;
+    m.mode = j8 < j16 ? 1 : 0;
+    m.cost = j8 < j16 ? j8 : j16;
+    for (int k = 0; k < 4; ++k) {
+        m.mv[k][0] = (int16_t)(m.mode ? sm.best_mv[1 + k][0] : sm.best_mv[0][0]);
+        m.mv[k][1] = (int16_t)(m.mode ? sm.best_mv[1 + k][1] : sm.best_mv[0][1]);
+    }
+    m.pad[0] = m.pad[1] = m.pad[2] = 0;
+    a.out[my * a.mbw + mx] = m;
+}
+
+// ------------------------------------------------------------------ K5+K6 inter MB encode -------
+// coef layout per MB (int16[26][16]): blocks 0..15 luma 4x4 (raster block order, zig-zag coefficient order),
+// 16..19 Cb AC, 20..23 Cr AC (entry 0 = 0), 24: chroma DC levels Cb[0..3] Cr[4..7], 25: luma DC (Intra16x16 only).
+// nzmask: bit b = block b has a nonzero level; bits 24 / 25 = Cb / Cr DC.
+struct EncMbArgs {
+    const uint8_t *cur_y, *cur_u, *cur_v;   // source planes (0,0)
+    RefPlanes      ref;
+    uint8_t       *rec_y, *rec_u, *rec_v;   // reconstruction planes (0,0)
+    int            sy, sc, mbw, mbh;
+    QuantParams    q;
+    const MbMotion *motion;
+    int16_t       *coefs;
+    uint32_t      *nzmask;
+};
+struct EncMbSmem {               // per warp
+    int16_t  cblk[8][16];        // chroma blocks after the forward transform
+    uint8_t  cpred[8][16];
+    int      flags[32];
+};
+GVC_HD void enc_mb_p1(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
+    sm.flags[lane] = 0;
+    if (lane >= 24) return;
+    const MbMotion &mo = a.motion[my * a.mbw + mx];
+    int16_t *co = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs + lane * 16;
+    int pred[16], d[16];
+    if (lane < 16) {
+        const int bx = 4 * (lane & 3), by = 4 * (lane >> 2), k = (by >> 3) * 2 + (bx >> 3);
+        const int x = 16 * mx + bx, y = 16 * my + by;
+        mc_luma_4x4(a.ref, a.sy, x, y, mo.mv[k][0], mo.mv[k][1], pred);
+        for (int j = 0; j < 4; ++j) {
+            const unsigned c = ld_u32_any(a.cur_y + (long long)(y + j) * a.sy + x);
+            for (int i = 0; i < 4; ++i) d[j * 4 + i] = (int)((c >> (8 * i)) & 255) - pred[j * 4 + i];
+        }
+        dct4x4(d);
+        int nz = 0;
+        for (int i = 0; i < 16; ++i) {
+            const int cls = coef_class(i);
+            d[i] = quant_one(d[i], a.q.mf_y[cls], a.q.bias_y[cls]);
+            nz |= d[i];
+        }
+        for (int i = 0; i < 16; ++i) co[i] = (int16_t)d[zigzag4(i)];
+        sm.flags[lane] = nz != 0;
+        for (int i = 0; i < 16; ++i) d[i] = dequant_one(d[i], a.q.dq_y[coef_class(i)], a.q.qp);
+        idct4x4(d);
+        for (int j = 0; j < 4; ++j)
+            for (int i = 0; i < 4; ++i) a.rec_y[(long long)(y + j) * a.sy + x + i] = (uint8_t)clip_u8(pred[j * 4 + i] + d[j * 4 + i]);
+    } else {
+        const int l = lane - 16, p = l >> 2, b = l & 3;
+        const int bx = 4 * (b & 1), by = 4 * (b >> 1), k = b;   // chroma block b lies under luma partition b
+        const int x = 8 * mx + bx, y = 8 * my + by;
+        const uint8_t *src = p ? a.cur_v : a.cur_u;
+        mc_chroma_4x4(p ? a.ref.v : a.ref.u, a.sc, x, y, mo.mv[k][0], mo.mv[k][1], pred);
+        for (int j = 0; j < 4; ++j)
+            for (int i = 0; i < 4; ++i) d[j * 4 + i] = (int)src[(long long)(y + j) * a.sc + x + i] - pred[j * 4 + i];
+        dct4x4(d);
+        for (int i = 0; i < 16; ++i) { sm.cblk[l][i] = (int16_t)d[i]; sm.cpred[l][i] = (uint8_t)pred[i]; }
+    }
+}
+GVC_HD void enc_mb_p2(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
+    if (lane < 16 || lane >= 24) return;
+    const int l = lane - 16, p = l >> 2, b = l & 3;
+    int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
+    // 2x2 DC transform of this plane's four DCs (every lane of the plane does it; lane b keeps element b)
+    const int d0 = sm.cblk[4 * p][0], d1 = sm.cblk[4 * p + 1][0], d2 = sm.cblk[4 * p + 2][0], d3 = sm.cblk[4 * p + 3][0];
+    int dc[4] = {d0 + d1 + d2 + d3, d0 - d1 + d2 - d3, d0 + d1 - d2 - d3, d0 - d1 - d2 + d3};
+    int nzdc = 0;
+    for (int i = 0; i < 4; ++i) { dc[i] = quant_one(dc[i], a.q.mf_c[0] >> 1, a.q.bias_c[0] << 1); nzdc |= dc[i]; }
+    if (b == 0) {
+        for (int i = 0; i < 4; ++i) mbco[24 * 16 + 4 * p + i] = (int16_t)dc[i];
+        sm.flags[24 + p] = nzdc != 0;
+    }
+    const int f[4] = {dc[0] + dc[1] + dc[2] + dc[3], dc[0] - dc[1] + dc[2] - dc[3], dc[0] + dc[1] - dc[2] - dc[3], dc[0] - dc[1] - dc[2] + dc[3]};
+    const int mydc = (int)(int16_t)((f[b] * (a.q.dq_c[0] << (a.q.qpc / 6))) >> 5);
+    int d[16], nz = 0;
+    for (int i = 0; i < 16; ++i) d[i] = sm.cblk[l][i];
+    d[0] = 0;
+    for (int i = 0; i < 16; ++i) {
+        const int cls = coef_class(i);
+        d[i] = quant_one(d[i], a.q.mf_c[cls], a.q.bias_c[cls]);
+        nz |= d[i];
+    }
+    int16_t *co = mbco + lane * 16;
+    for (int i = 0; i < 16; ++i) co[i] = (int16_t)d[zigzag4(i)];
+    sm.flags[lane] = nz != 0;
+    for (int i = 0; i < 16; ++i) d[i] = dequant_one(d[i], a.q.dq_c[coef_class(i)], a.q.qpc);
+    d[0] = mydc;
+    idct4x4(d);
+    uint8_t *rec = p ? a.rec_v : a.rec_u;
+    const int x = 8 * mx + 4 * (b & 1), y = 8 * my + 4 * (b >> 1);
+    for (int j = 0; j < 4; ++j)
+        for (int i = 0; i < 4; ++i) rec[(long long)(y + j) * a.sc + x + i] = (uint8_t)clip_u8(sm.cpred[l][j * 4 + i] + d[j * 4 + i]);
+}
+GVC_HD void enc_mb_p3(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
+    if (lane != 0) return;
+    uint32_t m = 0;
+    for (int i = 0; i < 26; ++i) m |= (uint32_t)(sm.flags[i] != 0) << i;
+    a.nzmask[my * a.mbw + mx] = m;
+    int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
+    for (int i = 8; i < 16; ++i) mbco[24 * 16 + i] = 0;
+    for (int i = 0; i < 16; ++i) mbco[25 * 16 + i] = 0;
+}
+
+}  // namespace gvc

@@ -1,0 +1,204 @@
+// gvc_enc.cu -- launchers and C ABI of the encoder-side kernels (include/gvc.h "encoder stages").
+// Kernel bodies: enc_kernels.cuh.  These entry points take DEVICE pointers and are asynchronous on `stream`.
+#include <cstring>
+
+#include "enc_host.h"
+#include "enc_kernels.cuh"
+#include "gvc_common.h"
+
+namespace gvc {
+
+__global__ void __launch_bounds__(256) extend_border_kernel(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi) {
+    const int x = x_lo + blockIdx.x * 256 + threadIdx.x, y = y_lo + blockIdx.y;
+    if (x < x_hi && y < y_hi) extend_border_px(p, stride, w, h, x, y);
+}
+
+__global__ void __launch_bounds__(256) lowres_kernel(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi,
+                                                     uint8_t *d0, uint8_t *dh, uint8_t *dv, uint8_t *dc, int dstride,
+                                                     int lx_lo, int lx_hi, int ly_lo, int ly_hi) {
+    const int lx = lx_lo + blockIdx.x * 256 + threadIdx.x, ly = ly_lo + blockIdx.y;
+    if (lx < lx_hi && ly < ly_hi) lowres_px(src, sstride, x_lo, x_hi, y_lo, y_hi, d0, dh, dv, dc, dstride, lx, ly);
+}
+
+__global__ void __launch_bounds__(kHpThreads) hpel_kernel(const __grid_constant__ HpelArgs a) {
+    __shared__ HpelSmem sm;
+    const int x0 = a.x_lo + blockIdx.x * kHpTileW, y0 = a.y_lo + blockIdx.y * kHpTileH;
+    hpel_phase_a(threadIdx.x, a, x0, y0, sm);
+    __syncthreads();
+    hpel_phase_b(threadIdx.x, a, x0, y0, sm);
+    __syncthreads();
+    hpel_phase_c(threadIdx.x, a, x0, y0, sm);
+}
+
+constexpr int kMbWarps = 4;   // macroblocks (warps) per CTA in the per-MB kernels
+
+__global__ void __launch_bounds__(32 * kMbWarps) me_lowres_kernel(const __grid_constant__ MeLowArgs a) {
+    __shared__ unsigned keys[kMbWarps][32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int mb = blockIdx.x * kMbWarps + warp;
+    if (mb >= a.mbw * a.mbh) return;
+    const int my = mb / a.mbw, mx = mb - my * a.mbw;
+    me_lowres_lane(lane, a, mx, my, keys[warp]);
+    __syncwarp();
+    me_lowres_pick(lane, a, mx, my, keys[warp]);
+}
+
+__global__ void __launch_bounds__(32 * kMbWarps) me_refine_kernel(const __grid_constant__ MeRefArgs a) {
+    __shared__ MeRefSmem sms[kMbWarps];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int mb = blockIdx.x * kMbWarps + warp;
+    if (mb >= a.mbw * a.mbh) return;
+    const int my = mb / a.mbw, mx = mb - my * a.mbw;
+    MeRefSmem &sm = sms[warp];
+    me_ref_int(lane, a, mx, my, sm);
+    __syncwarp();
+    me_ref_pick(lane, a, mx, my, sm);
+    __syncwarp();
+    for (int step = 2; step >= 1; --step)
+        for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
+            me_ref_satd(lane, a, mx, my, ci, step, sm);
+            __syncwarp();
+            me_ref_update(lane, a, mx, my, ci, step, sm);
+            __syncwarp();
+        }
+    me_ref_out(lane, a, mx, my, sm);
+}
+
+__global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __grid_constant__ EncMbArgs a) {
+    __shared__ EncMbSmem sms[kMbWarps];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int mb = blockIdx.x * kMbWarps + warp;
+    if (mb >= a.mbw * a.mbh) return;
+    const int my = mb / a.mbw, mx = mb - my * a.mbw;
+    EncMbSmem &sm = sms[warp];
+    enc_mb_p1(lane, a, mx, my, sm);
+    __syncwarp();
+    enc_mb_p2(lane, a, mx, my, sm);
+    __syncwarp();
+    enc_mb_p3(lane, a, mx, my, sm);
+}
+
+// ---- launchers shared with the segment encoder -------------------------------------------------
+int launch_extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi, cudaStream_t st) {
+    if (x_hi <= x_lo || y_hi <= y_lo) return GVC_OK;
+    extend_border_kernel<<<dim3((x_hi - x_lo + 255) / 256, y_hi - y_lo), 256, 0, st>>>(p, stride, w, h, x_lo, x_hi, y_lo, y_hi);
+    GVC_CUDA(cudaGetLastError());
+    return GVC_OK;
+}
+int launch_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, uint8_t *dh, uint8_t *dv,
+                  uint8_t *dc, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi, cudaStream_t st) {
+    if (lx_hi <= lx_lo || ly_hi <= ly_lo) return GVC_OK;
+    lowres_kernel<<<dim3((lx_hi - lx_lo + 255) / 256, ly_hi - ly_lo), 256, 0, st>>>(src, sstride, x_lo, x_hi, y_lo, y_hi, d0, dh, dv, dc,
+                                                                                    dstride, lx_lo, lx_hi, ly_lo, ly_hi);
+    GVC_CUDA(cudaGetLastError());
+    return GVC_OK;
+}
+int launch_hpel(const HpelArgs &a, cudaStream_t st) {
+    if (a.x_hi <= a.x_lo || a.y_hi <= a.y_lo) return GVC_OK;
+    hpel_kernel<<<dim3((a.x_hi - a.x_lo + kHpTileW - 1) / kHpTileW, (a.y_hi - a.y_lo + kHpTileH - 1) / kHpTileH), kHpThreads, 0, st>>>(a);
+    GVC_CUDA(cudaGetLastError());
+    return GVC_OK;
+}
+int launch_me_lowres(const MeLowArgs &a, cudaStream_t st) {
+    me_lowres_kernel<<<(a.mbw * a.mbh + kMbWarps - 1) / kMbWarps, 32 * kMbWarps, 0, st>>>(a);
+    GVC_CUDA(cudaGetLastError());
+    return GVC_OK;
+}
+int launch_me_refine(const MeRefArgs &a, cudaStream_t st) {
+    me_refine_kernel<<<(a.mbw * a.mbh + kMbWarps - 1) / kMbWarps, 32 * kMbWarps, 0, st>>>(a);
+    GVC_CUDA(cudaGetLastError());
+    return GVC_OK;
+}
+int launch_encode_inter(const EncMbArgs &a, cudaStream_t st) {
+    encode_inter_kernel<<<(a.mbw * a.mbh + kMbWarps - 1) / kMbWarps, 32 * kMbWarps, 0, st>>>(a);
+    GVC_CUDA(cudaGetLastError());
+    return GVC_OK;
+}
+
+}  // namespace gvc
+
+using namespace gvc;
+
+static_assert(sizeof(gvc_mb_motion) == sizeof(MbMotion), "public and internal motion records must match");
+
+extern "C" {
+
+int gvc_extend_border(uint8_t *plane, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi, void *stream) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!plane || w < 1 || h < 1 || stride < 1) { set_error("gvc_extend_border: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    return launch_extend_border(plane, stride, w, h, x_lo, x_hi, y_lo, y_hi, static_cast<cudaStream_t>(stream));
+}
+
+int gvc_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, uint8_t *dh, uint8_t *dv,
+               uint8_t *dc, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi, void *stream) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!src || !d0) { set_error("gvc_lowres: null plane"); return GVC_ERR_INVALID_ARG; }
+    return launch_lowres(src, sstride, x_lo, x_hi - 1, y_lo, y_hi - 1, d0, dh, dv, dc, dstride, lx_lo, lx_hi, ly_lo, ly_hi,
+                         static_cast<cudaStream_t>(stream));
+}
+
+int gvc_hpel_filter(const uint8_t *src, uint8_t *dh, uint8_t *dv, uint8_t *dc, int stride, int x_lo, int x_hi, int y_lo, int y_hi,
+                    void *stream) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!src || !dh || !dv || !dc) { set_error("gvc_hpel_filter: null plane"); return GVC_ERR_INVALID_ARG; }
+    HpelArgs a;
+    a.src = src; a.dh = dh; a.dv = dv; a.dc = dc; a.stride = stride;
+    a.x_lo = x_lo; a.x_hi = x_hi; a.y_lo = y_lo; a.y_hi = y_hi;
+    return launch_hpel(a, static_cast<cudaStream_t>(stream));
+}
+
+int gvc_me_lowres(const uint8_t *cur_low, const uint8_t *ref_low, int stride, int mbw, int mbh, int range, int lambda,
+                  int16_t *out_mv, void *stream) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!cur_low || !ref_low || !out_mv || mbw < 1 || mbh < 1) { set_error("gvc_me_lowres: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    if (range < 0 || range > 22) { set_error("gvc_me_lowres: lowres range %d outside 0..22", range); return GVC_ERR_INVALID_ARG; }
+    MeLowArgs a;
+    a.cur = cur_low; a.ref = ref_low; a.stride = stride; a.mbw = mbw; a.mbh = mbh; a.r = range; a.lambda = lambda; a.out_mv = out_mv;
+    return launch_me_lowres(a, static_cast<cudaStream_t>(stream));
+}
+
+static RefPlanes to_ref(const gvc_ref_planes *r) {
+    RefPlanes o;
+    o.y = r->y; o.hh = r->h; o.hv = r->v; o.hc = r->c; o.u = r->cb; o.v = r->cr; o.low = r->low;
+    return o;
+}
+
+int gvc_me_refine(const uint8_t *cur_y, const gvc_ref_planes *ref, int stride, int w16, int h16, const int16_t *lowres_mv,
+                  int lambda, gvc_mb_motion *out, void *stream) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!cur_y || !ref || !ref->y || !ref->h || !ref->v || !ref->c || !lowres_mv || !out || (w16 & 15) || (h16 & 15) || w16 < 16 || h16 < 16) {
+        set_error("gvc_me_refine: bad arguments");
+        return GVC_ERR_INVALID_ARG;
+    }
+    MeRefArgs a;
+    a.cur = cur_y; a.ref = to_ref(ref); a.stride = stride; a.w16 = w16; a.h16 = h16; a.mbw = w16 / 16; a.mbh = h16 / 16;
+    a.lambda = lambda; a.lowres_mv = lowres_mv; a.out = reinterpret_cast<MbMotion *>(out);
+    return launch_me_refine(a, static_cast<cudaStream_t>(stream));
+}
+
+int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *cur_v, const gvc_ref_planes *ref, uint8_t *rec_y,
+                     uint8_t *rec_u, uint8_t *rec_v, int sy, int sc, int w16, int h16, const gvc_mb_motion *motion, int qp,
+                     int16_t *coefs, uint32_t *nzmask, void *stream) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!cur_y || !cur_u || !cur_v || !ref || !rec_y || !rec_u || !rec_v || !motion || !coefs || !nzmask || (w16 & 15) || (h16 & 15)) {
+        set_error("gvc_encode_inter: bad arguments");
+        return GVC_ERR_INVALID_ARG;
+    }
+    if (qp < 0 || qp > 51) { set_error("gvc_encode_inter: qp %d outside 0..51", qp); return GVC_ERR_INVALID_ARG; }
+    EncMbArgs a;
+    a.cur_y = cur_y; a.cur_u = cur_u; a.cur_v = cur_v; a.ref = to_ref(ref);
+    a.rec_y = rec_y; a.rec_u = rec_u; a.rec_v = rec_v; a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
+    fill_quant_params(a.q, qp, false);
+    a.motion = reinterpret_cast<const MbMotion *>(motion); a.coefs = coefs; a.nzmask = nzmask;
+    return launch_encode_inter(a, static_cast<cudaStream_t>(stream));
+}
+
+int gvc_lambda_for_qp(int qp) { return lambda_for_qp(qp); }
+
+}  // extern "C"

@@ -20,16 +20,7 @@
 #pragma once
 #include <stdint.h>
 
-#if defined(GVC_EMU)
-#define GVC_HD inline
-struct gvc_int4 { int x, y, z, w; };
-struct gvc_uint4 { unsigned x, y, z, w; };
-#else
-#define GVC_HD __device__ __forceinline__
-typedef int4  gvc_int4;
-typedef uint4 gvc_uint4;
-#endif
-
+#include "dev_common.h"
 #include "resize_types.h"
 
 namespace gvc {
@@ -60,9 +51,6 @@ GVC_HD unsigned funnel_r(unsigned lo, unsigned hi, int sh) {    // bytes of hi:l
     return __funnelshift_r(lo, hi, sh);
 #endif
 }
-GVC_HD int clip_u8(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }
-GVC_HD int imin(int a, int b) { return a < b ? a : b; }
-GVC_HD int imax(int a, int b) { return a > b ? a : b; }
 
 struct TileGeom {
     int x0, ncols;   // first output column, number of output columns (<= kTileW)

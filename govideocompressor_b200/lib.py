@@ -46,6 +46,14 @@ def load_library():
     lib.gvc_resize_frames_host.argtypes = [c_void_p, ctypes.POINTER(Frames), ctypes.POINTER(Frames), c_int]
     lib.gvc_resize_plan_info.argtypes = [c_void_p] + [ctypes.POINTER(c_int)] * 3
     lib.gvc_resize_plan_force_two_pass.argtypes = [c_void_p, c_int]
+    vp = c_void_p
+    lib.gvc_extend_border.argtypes = [vp] + [c_int] * 7 + [vp]
+    lib.gvc_lowres.argtypes = [vp] + [c_int] * 5 + [vp] * 4 + [c_int] * 5 + [vp]
+    lib.gvc_hpel_filter.argtypes = [vp] * 4 + [c_int] * 5 + [vp]
+    lib.gvc_me_lowres.argtypes = [vp, vp] + [c_int] * 5 + [vp, vp]
+    lib.gvc_me_refine.argtypes = [vp, vp] + [c_int] * 3 + [vp, c_int, vp, vp]
+    lib.gvc_encode_inter.argtypes = [vp] * 7 + [c_int] * 4 + [vp, c_int, vp, vp, vp]
+    lib.gvc_lambda_for_qp.argtypes = [c_int]
     _LIB = lib
     return lib
 

@@ -113,6 +113,50 @@ int gvc_resize_plan_info(const gvc_resize_plan *plan, int *fused, int *h_taps_lu
 /* Forces the two-pass path (tests exercise both). */
 int gvc_resize_plan_force_two_pass(gvc_resize_plan *plan, int on);
 
+/* ---------------------------------------------------------------- encoder stages (K2..K6) ----- */
+/* Replace: the per-frame work libx264 does inside the spawned ffmpeg (`-vcodec libx264`, server.go:69-70 ->
+ * client.go:115).  All pointers are DEVICE pointers addressing sample (0,0) of planes that carry padding
+ * (see DESIGN.md "Data layout"); calls are asynchronous on `stream`.  Arithmetic: ITU-T H.264 8.4.2.2 / 8.5
+ * in x264's decomposition; results are bit-identical to oracle/h264_core.c + oracle/h264_mb.c. */
+
+typedef struct gvc_ref_planes {     /* one reference frame */
+    const uint8_t *y, *h, *v, *c;   /* luma: full sample, and half-sample planes H (x+1/2), V (y+1/2), C (both) */
+    const uint8_t *cb, *cr;         /* chroma */
+    const uint8_t *low;             /* half-resolution luma */
+} gvc_ref_planes;
+
+typedef struct gvc_mb_motion {      /* per macroblock result of the motion search */
+    int16_t mv[4][2];               /* quarter-sample vectors of the four 8x8 partitions (equal for 16x16) */
+    int32_t cost;
+    uint8_t mode;                   /* 0 = P_L0_16x16, 1 = P_8x8 with four 8x8 partitions */
+    uint8_t pad[3];
+} gvc_mb_motion;
+
+#define GVC_MB_COEFS (26 * 16)      /* int16 per macroblock written by gvc_encode_inter (layout: DESIGN.md) */
+
+/* x264 plane_expand_border: replicate the w x h picture into [x_lo,x_hi) x [y_lo,y_hi) around it. */
+int gvc_extend_border(uint8_t *plane, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi, void *stream);
+/* x264 frame_init_lowres_core (K3): lowres samples [lx_lo,lx_hi) x [ly_lo,ly_hi); source readable in
+ * [x_lo,x_hi) x [y_lo,y_hi) (reads clamp to it).  dh/dv/dc may be NULL. */
+int gvc_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, uint8_t *dh,
+               uint8_t *dv, uint8_t *dc, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi, void *stream);
+/* x264 hpel_filter (K2): H, V, C planes over [x_lo,x_hi) x [y_lo,y_hi), which is also the readable region of src. */
+int gvc_hpel_filter(const uint8_t *src, uint8_t *dh, uint8_t *dv, uint8_t *dc, int stride, int x_lo, int x_hi, int y_lo,
+                    int y_hi, void *stream);
+/* K4a: exhaustive lowres search, one 8x8 lowres block per macroblock, window +-range (<= 22); out_mv: (dx,dy) per MB. */
+int gvc_me_lowres(const uint8_t *cur_low, const uint8_t *ref_low, int stride, int mbw, int mbh, int range, int lambda,
+                  int16_t *out_mv, void *stream);
+/* K4b: full-resolution SAD candidates, half/quarter-sample SATD refinement, 16x16 vs 8x8 decision. */
+int gvc_me_refine(const uint8_t *cur_y, const gvc_ref_planes *ref, int stride, int w16, int h16, const int16_t *lowres_mv,
+                  int lambda, gvc_mb_motion *out, void *stream);
+/* K5+K6: motion compensation (x264 mc_luma / mc_chroma), 4x4 transform, quant, dequant, reconstruction of an
+ * all-inter frame.  coefs: GVC_MB_COEFS int16 per MB; nzmask: one uint32 per MB. */
+int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *cur_v, const gvc_ref_planes *ref,
+                     uint8_t *rec_y, uint8_t *rec_u, uint8_t *rec_v, int sy, int sc, int w16, int h16,
+                     const gvc_mb_motion *motion, int qp, int16_t *coefs, uint32_t *nzmask, void *stream);
+/* x264_lambda_tab[qp] */
+int gvc_lambda_for_qp(int qp);
+
 #ifdef __cplusplus
 }
 #endif

@@ -95,6 +95,18 @@ void gvc_oracle_mc_luma(uint8_t *dst, int dstride, const uint8_t *const planes[4
 void gvc_oracle_mc_chroma(uint8_t *dst, int dstride, const uint8_t *src, int stride, int bx, int by, int mvx, int mvy,
                           int w, int h);
 
+/* ---------------------------------------------------------------- frame-level composition (h264_mb.c) ------ */
+int  gvc_oracle_lambda(int qp);
+int  gvc_oracle_se_bits(int v);
+void gvc_oracle_me_lowres(const uint8_t *cur, const uint8_t *ref, int stride, int mbw, int mbh, int r, int lambda,
+                          int16_t *out_mv, int32_t *out_cost);
+void gvc_oracle_me_refine(const uint8_t *cur, const uint8_t *const planes[4], int stride, int w16, int h16, int pad,
+                          const int16_t *lowres_mv, int lambda, int32_t *out);
+void gvc_oracle_encode_inter_frame(const uint8_t *const cur[3], const uint8_t *const ref_luma[4],
+                                   const uint8_t *const ref_chroma[2], uint8_t *const recon[3], int sy, int sc,
+                                   int w16, int h16, const int32_t *motion, int qp, int16_t *coefs, uint32_t *nzmask);
+void gvc_oracle_extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,110 @@
+// emu_enc.cpp -- TEST HARNESS: executes the encoder kernels' bodies (enc_kernels.cuh built with GVC_EMU) lane by
+// lane / thread by thread on the host, phase by phase, so the CPU suite can compare their logic with the oracle.
+// Not part of libgvc.so.
+#define GVC_EMU 1
+#include <cstring>
+#include <vector>
+
+#include "../../govideocompressor_b200/csrc/enc_host.h"
+#include "../../govideocompressor_b200/csrc/enc_kernels.cuh"
+
+using namespace gvc;
+
+extern "C" {
+
+void emu_extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi) {
+    for (int y = y_lo; y < y_hi; ++y)
+        for (int x = x_lo; x < x_hi; ++x) extend_border_px(p, stride, w, h, x, y);
+}
+
+void emu_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, uint8_t *dh, uint8_t *dv,
+                uint8_t *dc, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi) {
+    for (int ly = ly_lo; ly < ly_hi; ++ly)
+        for (int lx = lx_lo; lx < lx_hi; ++lx) lowres_px(src, sstride, x_lo, x_hi - 1, y_lo, y_hi - 1, d0, dh, dv, dc, dstride, lx, ly);
+}
+
+void emu_hpel(const uint8_t *src, uint8_t *dh, uint8_t *dv, uint8_t *dc, int stride, int x_lo, int x_hi, int y_lo, int y_hi) {
+    HpelArgs a;
+    a.src = src; a.dh = dh; a.dv = dv; a.dc = dc; a.stride = stride; a.x_lo = x_lo; a.x_hi = x_hi; a.y_lo = y_lo; a.y_hi = y_hi;
+    for (int y0 = y_lo; y0 < y_hi; y0 += kHpTileH)
+        for (int x0 = x_lo; x0 < x_hi; x0 += kHpTileW) {
+            HpelSmem sm;
+            memset(&sm, 0xAB, sizeof(sm));
+            for (int t = 0; t < kHpThreads; ++t) hpel_phase_a(t, a, x0, y0, sm);
+            for (int t = 0; t < kHpThreads; ++t) hpel_phase_b(t, a, x0, y0, sm);
+            for (int t = 0; t < kHpThreads; ++t) hpel_phase_c(t, a, x0, y0, sm);
+        }
+}
+
+void emu_me_lowres(const uint8_t *cur, const uint8_t *ref, int stride, int mbw, int mbh, int r, int lambda, int16_t *out_mv) {
+    MeLowArgs a;
+    a.cur = cur; a.ref = ref; a.stride = stride; a.mbw = mbw; a.mbh = mbh; a.r = r; a.lambda = lambda; a.out_mv = out_mv;
+    for (int my = 0; my < mbh; ++my)
+        for (int mx = 0; mx < mbw; ++mx) {
+            unsigned keys[32];
+            for (int l = 0; l < 32; ++l) me_lowres_lane(l, a, mx, my, keys);
+            for (int l = 0; l < 32; ++l) me_lowres_pick(l, a, mx, my, keys);
+        }
+}
+
+static RefPlanes mkref(const uint8_t *const p[7]) {
+    RefPlanes r;
+    r.y = p[0]; r.hh = p[1]; r.hv = p[2]; r.hc = p[3]; r.u = p[4]; r.v = p[5]; r.low = p[6];
+    return r;
+}
+
+// out: MbMotion records (24 bytes each)
+void emu_me_refine(const uint8_t *cur, const uint8_t *const ref[7], int stride, int w16, int h16, const int16_t *lowres_mv,
+                   int lambda, void *out) {
+    MeRefArgs a;
+    a.cur = cur; a.ref = mkref(ref); a.stride = stride; a.w16 = w16; a.h16 = h16; a.mbw = w16 / 16; a.mbh = h16 / 16;
+    a.lambda = lambda; a.lowres_mv = lowres_mv; a.out = static_cast<MbMotion *>(out);
+    for (int my = 0; my < a.mbh; ++my)
+        for (int mx = 0; mx < a.mbw; ++mx) {
+            MeRefSmem sm;
+            memset(&sm, 0xAB, sizeof(sm));
+            for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) me_ref_pick(l, a, mx, my, sm);
+            for (int step = 2; step >= 1; --step)
+                for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
+                    for (int l = 0; l < 32; ++l) me_ref_satd(l, a, mx, my, ci, step, sm);
+                    for (int l = 0; l < 32; ++l) me_ref_update(l, a, mx, my, ci, step, sm);
+                }
+            for (int l = 0; l < 32; ++l) me_ref_out(l, a, mx, my, sm);
+        }
+}
+
+void emu_encode_inter(const uint8_t *const cur[3], const uint8_t *const ref[7], uint8_t *const rec[3], int sy, int sc, int w16,
+                      int h16, const void *motion, int qp, int16_t *coefs, uint32_t *nzmask) {
+    EncMbArgs a;
+    a.cur_y = cur[0]; a.cur_u = cur[1]; a.cur_v = cur[2]; a.ref = mkref(ref);
+    a.rec_y = rec[0]; a.rec_u = rec[1]; a.rec_v = rec[2]; a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
+    fill_quant_params(a.q, qp, false);
+    a.motion = static_cast<const MbMotion *>(motion); a.coefs = coefs; a.nzmask = nzmask;
+    for (int my = 0; my < a.mbh; ++my)
+        for (int mx = 0; mx < a.mbw; ++mx) {
+            EncMbSmem sm;
+            memset(&sm, 0xAB, sizeof(sm));
+            for (int l = 0; l < 32; ++l) enc_mb_p1(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) enc_mb_p2(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) enc_mb_p3(l, a, mx, my, sm);
+        }
+}
+
+// quantiser constants as the product computes them: out[0..2]=mf_y, [3..5]=bias_y, [6..8]=dq_y, [9..11]=mf_c, [12..14]=bias_c,
+// [15..17]=dq_c, [18]=qpc, [19]=lambda
+void emu_quant_params(int qp, int intra, int out[20]) {
+    QuantParams q;
+    fill_quant_params(q, qp, intra != 0);
+    for (int i = 0; i < 3; ++i) {
+        out[i] = q.mf_y[i]; out[3 + i] = q.bias_y[i]; out[6 + i] = q.dq_y[i];
+        out[9 + i] = q.mf_c[i]; out[12 + i] = q.bias_c[i]; out[15 + i] = q.dq_c[i];
+    }
+    out[18] = q.qpc; out[19] = q.lambda;
+}
+
+void emu_geom(int w, int h, int out[9]) {
+    const EncGeom g = make_geom(w, h);
+    out[0] = g.w16; out[1] = g.h16; out[2] = g.mbw; out[3] = g.mbh; out[4] = g.sy; out[5] = g.sc; out[6] = g.sl; out[7] = kEncPad; out[8] = kMbCoefs;
+}
+}

@@ -1,0 +1,118 @@
+"""CPU: the encoder kernels' bodies executed on the host (tests/emu) against the oracle -- border extension,
+lowres, half-sample planes, lowres search, refinement + partition decision, inter MB encode/reconstruct."""
+import ctypes
+
+import numpy as np
+import pytest
+
+import emu_lib
+import enc_util as E
+import oracle_lib
+
+BACKEND = "emu"
+
+
+def _vp(x):
+    return ctypes.c_void_p(x)
+
+
+@pytest.fixture(scope="module")
+def pair():
+    g = E.geom(96, 64)
+    ref_yuv, cur_yuv = E.make_pair(g["w16"], g["h16"], seed=3)
+    return g, E.Frame(g, ref_yuv), E.Frame(g, cur_yuv, with_hpel=False)
+
+
+def test_quant_params_equal_oracle_tables():
+    out = (ctypes.c_int * 20)()
+    for qp in range(52):
+        for intra in (0, 1):
+            emu_lib.load().emu_quant_params(qp, intra, out)
+            mf, bias = oracle_lib.quant4_tables(qp, intra)
+            qpc = oracle_lib.load().gvc_oracle_chroma_qp(qp)
+            mfc, biasc = oracle_lib.quant4_tables(qpc, intra)
+            for cls, idx in ((0, 0), (1, 1), (2, 5)):
+                assert out[cls] == mf[idx] and out[3 + cls] == bias[idx]
+                assert out[9 + cls] == mfc[idx] and out[12 + cls] == biasc[idx]
+                assert out[6 + cls] == oracle_lib.load().gvc_oracle_dequant4_scale(qp, idx)
+                assert out[15 + cls] == oracle_lib.load().gvc_oracle_dequant4_scale(qpc, idx)
+            assert out[18] == qpc and out[19] == oracle_lib.load().gvc_oracle_lambda(qp)
+
+
+def test_border_extension(pair):
+    g, ref, cur = pair
+    w, h = 90, 60                      # picture smaller than the coded size: right/bottom strips get filled too
+    pl = E.luma_plane(g, 0xEE)
+    img = np.random.Generator(np.random.PCG64(5)).integers(0, 256, (h, w), dtype=np.uint8)
+    pl.arr[E.PAD:E.PAD + h, E.PAD:E.PAD + w] = img
+    want = np.pad(img, ((E.PAD, E.PAD + g["h16"] - h), (E.PAD, E.PAD + g["w16"] - w)), mode="edge")
+    emu_lib.load().emu_extend_border(_vp(pl.ptr()), g["sy"], w, h, -E.PAD, g["w16"] + E.PAD, -E.PAD, g["h16"] + E.PAD)
+    np.testing.assert_array_equal(pl.full(), want)
+
+
+def test_lowres_all_phases(pair):
+    g, ref, cur = pair
+    want = E.oracle_lowres_full(ref.Y.full())
+    outs = [E.low_plane(g, 0xEE) for _ in range(4)]
+    lp = E.PAD // 2
+    emu_lib.load().emu_lowres(_vp(ref.Y.ptr()), g["sy"], -E.PAD, g["w16"] + E.PAD, -E.PAD, g["h16"] + E.PAD,
+                              *[_vp(o.ptr()) for o in outs], g["sl"], -lp, g["w16"] // 2 + lp, -lp, g["h16"] // 2 + lp)
+    for o, wnt in zip(outs, want):
+        np.testing.assert_array_equal(o.full(), wnt)
+
+
+def test_hpel_planes(pair):
+    g, ref, cur = pair
+    outs = [E.luma_plane(g, 0xEE) for _ in range(3)]
+    emu_lib.load().emu_hpel(_vp(ref.Y.ptr()), *[_vp(o.ptr()) for o in outs], g["sy"], -E.PAD, g["w16"] + E.PAD, -E.PAD, g["h16"] + E.PAD)
+    for o, wnt in zip(outs, (ref.H, ref.Vp, ref.C)):
+        np.testing.assert_array_equal(o.full(), wnt.full())
+
+
+@pytest.mark.parametrize("r,qp", [(8, 23), (16, 36), (3, 0)])
+def test_me_lowres(pair, r, qp):
+    g, ref, cur = pair
+    lam = oracle_lib.load().gvc_oracle_lambda(qp)
+    a = E.me_lowres("oracle", cur, ref, r, lam)
+    b = E.me_lowres(BACKEND, cur, ref, r, lam)
+    np.testing.assert_array_equal(a, b)
+    if r >= 8:   # planted motion: top-left quadrant moved by (3,-2) full samples => lowres (1 or 2, -1)
+        assert abs(int(a[0, 0, 0]) * 2 - 3) <= 1 and abs(int(a[0, 0, 1]) * 2 + 2) <= 1
+
+
+@pytest.mark.parametrize("qp", [12, 23, 40])
+def test_me_refine_and_encode_inter(pair, qp):
+    g, ref, cur = pair
+    lam = oracle_lib.load().gvc_oracle_lambda(qp)
+    low = E.me_lowres("oracle", cur, ref, 8, lam)
+    mo = E.me_refine("oracle", cur, ref, low, lam)
+    mb = E.me_refine(BACKEND, cur, ref, low, lam)
+    np.testing.assert_array_equal(mo["mv"], mb["mv"])
+    np.testing.assert_array_equal(mo["cost"], mb["cost"])
+    np.testing.assert_array_equal(mo["mode"], mb["mode"])
+    # known answer: MB (0,0) follows the planted (3,-2) full-sample shift = (12,-8) quarter samples
+    assert tuple(mo["mv"][0, 0]) == (12, -8)
+    co, nzo, reco = E.encode_inter("oracle", cur, ref, mo, qp)
+    cb, nzb, recb = E.encode_inter(BACKEND, cur, ref, mo, qp)
+    np.testing.assert_array_equal(co, cb)
+    np.testing.assert_array_equal(nzo, nzb)
+    for x, y in zip(reco, recb):
+        np.testing.assert_array_equal(x, y)
+    # reconstruction quality sanity: PSNR of recon vs source rises as qp falls
+    err = np.mean((reco[0].astype(float) - cur.Y.inner()) ** 2)
+    assert err < {12: 3.0, 23: 12.0, 40: 120.0}[qp]
+
+
+def test_encode_inter_with_8x8_partitions_and_odd_vectors(pair):
+    g, ref, cur = pair
+    n = g["mbw"] * g["mbh"]
+    rng = np.random.Generator(np.random.PCG64(9))
+    mo = np.zeros(n, E.MOTION_DT)
+    mo["mv"] = rng.integers(-37, 38, (n, 4, 2))          # every fractional phase, different per partition
+    mo["mode"] = 1
+    co, nzo, reco = E.encode_inter("oracle", cur, ref, mo, 26)
+    cb, nzb, recb = E.encode_inter(BACKEND, cur, ref, mo, 26)
+    np.testing.assert_array_equal(co, cb)
+    np.testing.assert_array_equal(nzo, nzb)
+    for x, y in zip(reco, recb):
+        np.testing.assert_array_equal(x, y)

@@ -1,0 +1,111 @@
+"""GPU parity (-m gpu): encoder-side kernels of libgvc.so through the C ABI against the oracle, at a small size
+and at the BASELINE size (1280x720 coded frames = 3,600 macroblocks)."""
+import ctypes
+
+import numpy as np
+import pytest
+
+import enc_util as E
+import oracle_lib
+
+pytestmark = pytest.mark.gpu
+
+
+def _vp(x):
+    return ctypes.c_void_p(x)
+
+
+@pytest.fixture(scope="module", params=[(96, 64, 3), (1280, 720, 11), (200, 120, 5)], ids=["96x64", "720p", "200x120"])
+def pair(request):
+    w, h, seed = request.param
+    g = E.geom(w, h)
+    ref_yuv, cur_yuv = E.make_pair(g["w16"], g["h16"], seed=seed)
+    return g, E.Frame(g, ref_yuv), E.Frame(g, cur_yuv, with_hpel=False)
+
+
+@pytest.fixture(scope="module")
+def dev():
+    from gpu_enc import Dev
+    return Dev()
+
+
+def _down(devplane, plane):
+    out = type(plane)(plane.w, plane.h, plane.pad, plane.stride)
+    out.arr[...] = devplane.t.cpu().numpy().reshape(plane.arr.shape)
+    return out
+
+
+def test_border_lowres_hpel(pair, dev):
+    import torch
+    g, ref, cur = pair
+    # border: start from a plane whose padding is junk
+    w, h = g["w16"] - 6, g["h16"] - 4
+    pl = E.luma_plane(g, 0xEE)
+    pl.arr[E.PAD:E.PAD + h, E.PAD:E.PAD + w] = ref.Y.inner()[:h, :w]
+    want = np.pad(ref.Y.inner()[:h, :w], ((E.PAD, E.PAD + g["h16"] - h), (E.PAD, E.PAD + g["w16"] - w)), mode="edge")
+    d = dev.up(pl)
+    dev.check(dev.lib.gvc_extend_border(_vp(d.ptr), g["sy"], w, h, -E.PAD, g["w16"] + E.PAD, -E.PAD, g["h16"] + E.PAD, None))
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(_down(d, pl).full(), want)
+    # lowres, all four phases, over the padded lowres area
+    dy = dev.up(ref.Y)
+    outs = [E.low_plane(g, 0xEE) for _ in range(4)]
+    douts = [dev.up(o) for o in outs]
+    lp = E.PAD // 2
+    dev.check(dev.lib.gvc_lowres(_vp(dy.ptr), g["sy"], -E.PAD, g["w16"] + E.PAD, -E.PAD, g["h16"] + E.PAD, *[_vp(o.ptr) for o in douts],
+                                 g["sl"], -lp, g["w16"] // 2 + lp, -lp, g["h16"] // 2 + lp, None))
+    torch.cuda.synchronize()
+    for dd, o, wnt in zip(douts, outs, E.oracle_lowres_full(ref.Y.full())):
+        np.testing.assert_array_equal(_down(dd, o).full(), wnt)
+    # half-sample planes over the whole padded area
+    outs = [E.luma_plane(g, 0xEE) for _ in range(3)]
+    douts = [dev.up(o) for o in outs]
+    dev.check(dev.lib.gvc_hpel_filter(_vp(dy.ptr), *[_vp(o.ptr) for o in douts], g["sy"], -E.PAD, g["w16"] + E.PAD, -E.PAD, g["h16"] + E.PAD, None))
+    torch.cuda.synchronize()
+    for dd, o, wnt in zip(douts, outs, (ref.H, ref.Vp, ref.C)):
+        np.testing.assert_array_equal(_down(dd, o).full(), wnt.full())
+
+
+@pytest.mark.parametrize("r,qp", [(8, 23), (16, 36)])
+def test_me_lowres(pair, r, qp):
+    g, ref, cur = pair
+    lam = oracle_lib.load().gvc_oracle_lambda(qp)
+    np.testing.assert_array_equal(E.me_lowres("oracle", cur, ref, r, lam), E.me_lowres("gpu", cur, ref, r, lam))
+
+
+@pytest.mark.parametrize("qp", [12, 23, 40])
+def test_me_refine_and_encode_inter(pair, qp):
+    g, ref, cur = pair
+    lam = oracle_lib.load().gvc_oracle_lambda(qp)
+    low = E.me_lowres("gpu", cur, ref, 8, lam)
+    mo = E.me_refine("oracle", cur, ref, low, lam)
+    mg = E.me_refine("gpu", cur, ref, low, lam)
+    for f in ("mv", "cost", "mode"):
+        np.testing.assert_array_equal(mo[f], mg[f])
+    assert tuple(mo["mv"][0, 0]) == (12, -8)          # planted shift of the top-left quadrant
+    co, nzo, reco = E.encode_inter("oracle", cur, ref, mo, qp)
+    cg, nzg, recg = E.encode_inter("gpu", cur, ref, mg, qp)
+    np.testing.assert_array_equal(co, cg)
+    np.testing.assert_array_equal(nzo, nzg)
+    for x, y in zip(reco, recg):
+        np.testing.assert_array_equal(x, y)
+
+
+def test_encode_inter_all_fractional_phases(pair):
+    g, ref, cur = pair
+    n = g["mbw"] * g["mbh"]
+    rng = np.random.Generator(np.random.PCG64(9))
+    mo = np.zeros(n, E.MOTION_DT)
+    mo["mv"] = rng.integers(-37, 38, (n, 4, 2))
+    mo["mode"] = 1
+    co, nzo, reco = E.encode_inter("oracle", cur, ref, mo, 26)
+    cg, nzg, recg = E.encode_inter("gpu", cur, ref, mo, 26)
+    np.testing.assert_array_equal(co, cg)
+    np.testing.assert_array_equal(nzo, nzg)
+    for x, y in zip(reco, recg):
+        np.testing.assert_array_equal(x, y)
+
+
+def test_bad_arguments(dev):
+    assert dev.lib.gvc_me_lowres(None, None, 64, 4, 4, 8, 4, None, None) == -1
+    assert dev.lib.gvc_encode_inter(None, None, None, None, None, None, None, 0, 0, 16, 16, None, 23, None, None, None) == -1
