@@ -45,6 +45,15 @@ GVC_HD unsigned sad_u8x4(unsigned a, unsigned b, unsigned acc) {   // acc + sum 
 #endif
 }
 
+// byte that another CTA of the same launch may have written: must not be served from this SM's L1
+GVC_HD int ld_u8_cg(const uint8_t *p) {
+#if defined(GVC_EMU)
+    return *p;
+#else
+    return (int)__ldcg(p);
+#endif
+}
+
 // ------------------------------------------------------------------ se(v) bit count ------------
 GVC_HD int se_bits(int v) {
     const unsigned code = (v > 0 ? 2u * (unsigned)v - 1u : 2u * (unsigned)(-v)) + 1u;
@@ -451,39 +460,43 @@ GVC_HD void enc_mb_p1(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &s
         for (int i = 0; i < 16; ++i) { sm.cblk[l][i] = (int16_t)d[i]; sm.cpred[l][i] = (uint8_t)pred[i]; }
     }
 }
-GVC_HD void enc_mb_p2(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
-    if (lane < 16 || lane >= 24) return;
+// Second half of the chroma path, shared by the inter and intra kernels: 2x2 DC transform of the plane's four DCs
+// (every lane of the plane recomputes it and keeps element b), DC + AC quantisation, levels out, reconstruction.
+GVC_HD void chroma_finish(int lane, const QuantParams &q, int16_t *mbco, uint8_t *rec_u, uint8_t *rec_v, int sc, int mx, int my,
+                          const int16_t cblk[8][16], const uint8_t cpred[8][16], int *flags) {
     const int l = lane - 16, p = l >> 2, b = l & 3;
-    int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
-    // 2x2 DC transform of this plane's four DCs (every lane of the plane does it; lane b keeps element b)
-    const int d0 = sm.cblk[4 * p][0], d1 = sm.cblk[4 * p + 1][0], d2 = sm.cblk[4 * p + 2][0], d3 = sm.cblk[4 * p + 3][0];
+    const int d0 = cblk[4 * p][0], d1 = cblk[4 * p + 1][0], d2 = cblk[4 * p + 2][0], d3 = cblk[4 * p + 3][0];
     int dc[4] = {d0 + d1 + d2 + d3, d0 - d1 + d2 - d3, d0 + d1 - d2 - d3, d0 - d1 - d2 + d3};
     int nzdc = 0;
-    for (int i = 0; i < 4; ++i) { dc[i] = quant_one(dc[i], a.q.mf_c[0] >> 1, a.q.bias_c[0] << 1); nzdc |= dc[i]; }
+    for (int i = 0; i < 4; ++i) { dc[i] = quant_one(dc[i], q.mf_c[0] >> 1, q.bias_c[0] << 1); nzdc |= dc[i]; }
     if (b == 0) {
         for (int i = 0; i < 4; ++i) mbco[24 * 16 + 4 * p + i] = (int16_t)dc[i];
-        sm.flags[24 + p] = nzdc != 0;
+        flags[24 + p] = nzdc != 0;
     }
     const int f[4] = {dc[0] + dc[1] + dc[2] + dc[3], dc[0] - dc[1] + dc[2] - dc[3], dc[0] + dc[1] - dc[2] - dc[3], dc[0] - dc[1] - dc[2] + dc[3]};
-    const int mydc = (int)(int16_t)((f[b] * (a.q.dq_c[0] << (a.q.qpc / 6))) >> 5);
+    const int mydc = (int)(int16_t)((f[b] * (q.dq_c[0] << (q.qpc / 6))) >> 5);
     int d[16], nz = 0;
-    for (int i = 0; i < 16; ++i) d[i] = sm.cblk[l][i];
+    for (int i = 0; i < 16; ++i) d[i] = cblk[l][i];
     d[0] = 0;
     for (int i = 0; i < 16; ++i) {
         const int cls = coef_class(i);
-        d[i] = quant_one(d[i], a.q.mf_c[cls], a.q.bias_c[cls]);
+        d[i] = quant_one(d[i], q.mf_c[cls], q.bias_c[cls]);
         nz |= d[i];
     }
     int16_t *co = mbco + lane * 16;
     for (int i = 0; i < 16; ++i) co[i] = (int16_t)d[zigzag4(i)];
-    sm.flags[lane] = nz != 0;
-    for (int i = 0; i < 16; ++i) d[i] = dequant_one(d[i], a.q.dq_c[coef_class(i)], a.q.qpc);
+    flags[lane] = nz != 0;
+    for (int i = 0; i < 16; ++i) d[i] = dequant_one(d[i], q.dq_c[coef_class(i)], q.qpc);
     d[0] = mydc;
     idct4x4(d);
-    uint8_t *rec = p ? a.rec_v : a.rec_u;
+    uint8_t *rec = p ? rec_v : rec_u;
     const int x = 8 * mx + 4 * (b & 1), y = 8 * my + 4 * (b >> 1);
     for (int j = 0; j < 4; ++j)
-        for (int i = 0; i < 4; ++i) rec[(long long)(y + j) * a.sc + x + i] = (uint8_t)clip_u8(sm.cpred[l][j * 4 + i] + d[j * 4 + i]);
+        for (int i = 0; i < 4; ++i) rec[(long long)(y + j) * sc + x + i] = (uint8_t)clip_u8(cpred[l][j * 4 + i] + d[j * 4 + i]);
+}
+GVC_HD void enc_mb_p2(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
+    if (lane < 16 || lane >= 24) return;
+    chroma_finish(lane, a.q, a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs, a.rec_u, a.rec_v, a.sc, mx, my, sm.cblk, sm.cpred, sm.flags);
 }
 GVC_HD void enc_mb_p3(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
     if (lane != 0) return;
@@ -493,6 +506,174 @@ GVC_HD void enc_mb_p3(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &s
     int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
     for (int i = 8; i < 16; ++i) mbco[24 * 16 + i] = 0;
     for (int i = 0; i < 16; ++i) mbco[25 * 16 + i] = 0;
+}
+
+// ------------------------------------------------------------------ K7 all-Intra16x16 frame (IDR) -
+// Specification: oracle/h264_mb.c gvc_oracle_encode_intra_frame (H.264 8.3.3, 8.3.4, 8.5.2, 8.5.10).  One warp
+// per macroblock ROW walks its row left to right; a row may start macroblock mx once the row above has
+// finished macroblock mx (vertical / DC prediction read its bottom samples).  Progress counters live in global
+// memory (one int per row, zeroed before the launch); all rows are co-resident (<= 148 CTAs of one warp).
+struct IntraArgs {
+    const uint8_t *cur_y, *cur_u, *cur_v;
+    uint8_t       *rec_y, *rec_u, *rec_v;
+    int            sy, sc, mbw, mbh;
+    QuantParams    q;          // intra dead zone
+    int16_t       *coefs;
+    uint32_t      *nzmask;
+    uint8_t       *modes;
+    int           *progress;   // [mbh]
+};
+struct IntraSmem {
+    int      top[16], left[16];       // reconstructed neighbours of the luma MB
+    int      ctop[2][8], cleft[2][8];
+    int      sadp[3][16];
+    int16_t  lblk[16][16];            // dequantised luma AC (entry 0 unused)
+    int16_t  ldc[16];
+    int16_t  cblk[8][16];
+    uint8_t  cpred[8][16];
+    int      flags[32];
+};
+// phase 0: fetch neighbours
+GVC_HD void intra_p0(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+    const bool has_top = my > 0, has_left = mx > 0;
+    sm.flags[lane] = 0;
+    if (lane < 16) {
+        sm.top[lane]  = has_top ? ld_u8_cg(a.rec_y + (long long)(16 * my - 1) * a.sy + 16 * mx + lane) : 0;
+        sm.left[lane] = has_left ? ld_u8_cg(a.rec_y + (long long)(16 * my + lane) * a.sy + 16 * mx - 1) : 0;
+    } else {
+        const int l = lane - 16, p = l >> 3, i = l & 7;
+        const uint8_t *r = p ? a.rec_v : a.rec_u;
+        sm.ctop[p][i]  = has_top ? ld_u8_cg(r + (long long)(8 * my - 1) * a.sc + 8 * mx + i) : 0;
+        sm.cleft[p][i] = has_left ? ld_u8_cg(r + (long long)(8 * my + i) * a.sc + 8 * mx - 1) : 0;
+    }
+}
+GVC_HD int intra_dc_value(const IntraSmem &sm, bool has_top, bool has_left) {
+    int sum = 0;
+    for (int i = 0; i < 16; ++i) sum += (has_top ? sm.top[i] : 0) + (has_left ? sm.left[i] : 0);
+    return has_top && has_left ? (sum + 16) >> 5 : (has_top || has_left) ? (sum + 8) >> 4 : 128;
+}
+GVC_HD int intra_pred_px(const IntraSmem &sm, int mode, int dcv, int x, int y) { return mode == 0 ? sm.top[x] : mode == 1 ? sm.left[y] : dcv; }
+// phase 1: per-block SAD of the three candidate modes
+GVC_HD void intra_p1(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+    if (lane >= 16) return;
+    const bool has_top = my > 0, has_left = mx > 0;
+    const int  dcv = intra_dc_value(sm, has_top, has_left);
+    const int  bx = 4 * (lane & 3), by = 4 * (lane >> 2);
+    int s[3] = {0, 0, 0};
+    for (int j = 0; j < 4; ++j) {
+        const unsigned c = ld_u32_any(a.cur_y + (long long)(16 * my + by + j) * a.sy + 16 * mx + bx);
+        for (int i = 0; i < 4; ++i) {
+            const int v = (int)((c >> (8 * i)) & 255);
+            for (int m = 0; m < 3; ++m) s[m] += iabs(v - intra_pred_px(sm, m, dcv, bx + i, by + j));
+        }
+    }
+    for (int m = 0; m < 3; ++m) sm.sadp[m][lane] = s[m];
+}
+GVC_HD int intra_pick_mode(const IntraSmem &sm, bool has_top, bool has_left) {
+    int best = -1, mode = 2;
+    for (int m = 0; m < 3; ++m) {
+        if ((m == 0 && !has_top) || (m == 1 && !has_left)) continue;
+        int s = 0;
+        for (int i = 0; i < 16; ++i) s += sm.sadp[m][i];
+        if (best < 0 || s < best) { best = s; mode = m; }
+    }
+    return mode;
+}
+// phase 2: luma forward transform + AC quant; chroma prediction + forward transform
+GVC_HD void intra_p2(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+    if (lane >= 24) return;
+    const bool has_top = my > 0, has_left = mx > 0;
+    int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
+    int d[16];
+    if (lane < 16) {
+        const int mode = intra_pick_mode(sm, has_top, has_left), dcv = intra_dc_value(sm, has_top, has_left);
+        const int bx = 4 * (lane & 3), by = 4 * (lane >> 2);
+        for (int j = 0; j < 4; ++j) {
+            const unsigned c = ld_u32_any(a.cur_y + (long long)(16 * my + by + j) * a.sy + 16 * mx + bx);
+            for (int i = 0; i < 4; ++i) d[j * 4 + i] = (int)((c >> (8 * i)) & 255) - intra_pred_px(sm, mode, dcv, bx + i, by + j);
+        }
+        dct4x4(d);
+        sm.ldc[lane] = (int16_t)d[0];
+        d[0] = 0;
+        int nz = 0;
+        for (int i = 0; i < 16; ++i) {
+            const int cls = coef_class(i);
+            d[i] = quant_one(d[i], a.q.mf_y[cls], a.q.bias_y[cls]);
+            nz |= d[i];
+        }
+        for (int i = 0; i < 16; ++i) mbco[lane * 16 + i] = (int16_t)d[zigzag4(i)];
+        sm.flags[lane] = nz != 0;
+        for (int i = 0; i < 16; ++i) sm.lblk[lane][i] = (int16_t)dequant_one(d[i], a.q.dq_y[coef_class(i)], a.q.qp);
+        if (lane == 0) a.modes[my * a.mbw + mx] = (uint8_t)mode;
+    } else {
+        const int l = lane - 16, p = l >> 2, b = l & 3, bx = b & 1, by = b >> 1;
+        int st[2] = {0, 0}, sl[2] = {0, 0};
+        for (int i = 0; i < 8; ++i) { st[i >> 2] += sm.ctop[p][i]; sl[i >> 2] += sm.cleft[p][i]; }
+        int v;
+        if (bx == by)     v = has_top && has_left ? (st[bx] + sl[by] + 4) >> 3 : has_top ? (st[bx] + 2) >> 2 : has_left ? (sl[by] + 2) >> 2 : 128;
+        else if (bx == 1) v = has_top ? (st[1] + 2) >> 2 : has_left ? (sl[0] + 2) >> 2 : 128;
+        else              v = has_left ? (sl[1] + 2) >> 2 : has_top ? (st[0] + 2) >> 2 : 128;
+        const uint8_t *src = p ? a.cur_v : a.cur_u;
+        const int x = 8 * mx + 4 * bx, y = 8 * my + 4 * by;
+        for (int j = 0; j < 4; ++j)
+            for (int i = 0; i < 4; ++i) d[j * 4 + i] = (int)src[(long long)(y + j) * a.sc + x + i] - v;
+        dct4x4(d);
+        for (int i = 0; i < 16; ++i) { sm.cblk[l][i] = (int16_t)d[i]; sm.cpred[l][i] = (uint8_t)v; }
+    }
+}
+// phase 3: luma DC path + reconstruction; chroma finish
+GVC_HD void intra_p3(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+    if (lane >= 24) return;
+    int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
+    if (lane >= 16) { chroma_finish(lane, a.q, mbco, a.rec_u, a.rec_v, a.sc, mx, my, sm.cblk, sm.cpred, sm.flags); return; }
+    const bool has_top = my > 0, has_left = mx > 0;
+    // 4x4 Hadamard of the 16 DCs (every luma lane recomputes it and keeps its own element)
+    int t[16], o[16];
+    for (int i = 0; i < 4; ++i) {
+        const int s01 = sm.ldc[i * 4] + sm.ldc[i * 4 + 1], d01 = sm.ldc[i * 4] - sm.ldc[i * 4 + 1];
+        const int s23 = sm.ldc[i * 4 + 2] + sm.ldc[i * 4 + 3], d23 = sm.ldc[i * 4 + 2] - sm.ldc[i * 4 + 3];
+        t[i * 4] = s01 + s23; t[i * 4 + 1] = s01 - s23; t[i * 4 + 2] = d01 - d23; t[i * 4 + 3] = d01 + d23;
+    }
+    int nzdc = 0;
+    for (int j = 0; j < 4; ++j) {
+        const int s01 = t[j] + t[4 + j], d01 = t[j] - t[4 + j], s23 = t[8 + j] + t[12 + j], d23 = t[8 + j] - t[12 + j];
+        o[j] = (s01 + s23 + 1) >> 1; o[4 + j] = (s01 - s23 + 1) >> 1; o[8 + j] = (d01 - d23 + 1) >> 1; o[12 + j] = (d01 + d23 + 1) >> 1;
+    }
+    for (int i = 0; i < 16; ++i) { o[i] = quant_one((int)(int16_t)o[i], a.q.mf_y[0] >> 1, a.q.bias_y[0] << 1); nzdc |= o[i]; }
+    if (lane == 0) {
+        for (int i = 0; i < 16; ++i) mbco[25 * 16 + i] = (int16_t)o[zigzag4(i)];
+        sm.flags[26] = nzdc != 0;
+    }
+    for (int i = 0; i < 4; ++i) {
+        const int s01 = o[i * 4] + o[i * 4 + 1], d01 = o[i * 4] - o[i * 4 + 1], s23 = o[i * 4 + 2] + o[i * 4 + 3], d23 = o[i * 4 + 2] - o[i * 4 + 3];
+        t[i * 4] = s01 + s23; t[i * 4 + 1] = s01 - s23; t[i * 4 + 2] = d01 - d23; t[i * 4 + 3] = d01 + d23;
+    }
+    const int j = lane & 3, r = lane >> 2;   // element (r, j) of the inverse transform = column butterfly of column j
+    int mine;
+    {
+        const int s01 = t[j] + t[4 + j], d01 = t[j] - t[4 + j], s23 = t[8 + j] + t[12 + j], d23 = t[8 + j] - t[12 + j];
+        mine = r == 0 ? s01 + s23 : r == 1 ? s01 - s23 : r == 2 ? d01 - d23 : d01 + d23;
+    }
+    mine = (int)(int16_t)mine;
+    const int qbits = a.q.qp / 6 - 6;
+    const int dcq = (int)(int16_t)(qbits >= 0 ? mine * (a.q.dq_y[0] << qbits) : (mine * a.q.dq_y[0] + (1 << (-qbits - 1))) >> (-qbits));
+    int d[16];
+    for (int i = 0; i < 16; ++i) d[i] = sm.lblk[lane][i];
+    d[0] = dcq;
+    idct4x4(d);
+    const int mode = intra_pick_mode(sm, has_top, has_left), dcv = intra_dc_value(sm, has_top, has_left);
+    const int bx = 4 * (lane & 3), by = 4 * (lane >> 2);
+    for (int jj = 0; jj < 4; ++jj)
+        for (int i = 0; i < 4; ++i)
+            a.rec_y[(long long)(16 * my + by + jj) * a.sy + 16 * mx + bx + i] = (uint8_t)clip_u8(intra_pred_px(sm, mode, dcv, bx + i, by + jj) + d[jj * 4 + i]);
+}
+GVC_HD void intra_p4(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+    if (lane != 0) return;
+    uint32_t m = 0;
+    for (int i = 0; i < 27; ++i) m |= (uint32_t)(sm.flags[i] != 0) << i;
+    a.nzmask[my * a.mbw + mx] = m;
+    int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
+    for (int i = 8; i < 16; ++i) mbco[24 * 16 + i] = 0;
 }
 
 }  // namespace gvc

@@ -78,6 +78,33 @@ __global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __gri
     enc_mb_p3(lane, a, mx, my, sm);
 }
 
+// One warp per macroblock row; rows advance as a wavefront (see enc_kernels.cuh K7).
+__global__ void __launch_bounds__(32) intra_frame_kernel(const __grid_constant__ IntraArgs a) {
+    __shared__ IntraSmem sm;
+    const int my = blockIdx.x, lane = threadIdx.x;
+    volatile int *prog = a.progress;
+    for (int mx = 0; mx < a.mbw; ++mx) {
+        if (my > 0) {
+            if (lane == 0)
+                while (prog[my - 1] < mx + 1) { }
+            __syncwarp();
+            __threadfence();
+        }
+        intra_p0(lane, a, mx, my, sm);
+        __syncwarp();
+        intra_p1(lane, a, mx, my, sm);
+        __syncwarp();
+        intra_p2(lane, a, mx, my, sm);
+        __syncwarp();
+        intra_p3(lane, a, mx, my, sm);
+        __syncwarp();
+        intra_p4(lane, a, mx, my, sm);
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) prog[my] = mx + 1;
+    }
+}
+
 // ---- launchers shared with the segment encoder -------------------------------------------------
 int launch_extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi, cudaStream_t st) {
     if (x_hi <= x_lo || y_hi <= y_lo) return GVC_OK;
@@ -111,6 +138,13 @@ int launch_me_refine(const MeRefArgs &a, cudaStream_t st) {
 }
 int launch_encode_inter(const EncMbArgs &a, cudaStream_t st) {
     encode_inter_kernel<<<(a.mbw * a.mbh + kMbWarps - 1) / kMbWarps, 32 * kMbWarps, 0, st>>>(a);
+    GVC_CUDA(cudaGetLastError());
+    return GVC_OK;
+}
+
+int launch_encode_intra(const IntraArgs &a, cudaStream_t st) {
+    GVC_CUDA(cudaMemsetAsync(a.progress, 0, sizeof(int) * a.mbh, st));
+    intra_frame_kernel<<<a.mbh, 32, 0, st>>>(a);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
@@ -197,6 +231,26 @@ int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
     fill_quant_params(a.q, qp, false);
     a.motion = reinterpret_cast<const MbMotion *>(motion); a.coefs = coefs; a.nzmask = nzmask;
     return launch_encode_inter(a, static_cast<cudaStream_t>(stream));
+}
+
+int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *cur_v, uint8_t *rec_y, uint8_t *rec_u, uint8_t *rec_v,
+                     int sy, int sc, int w16, int h16, int qp, int16_t *coefs, uint32_t *nzmask, uint8_t *modes, int *row_progress,
+                     void *stream) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!cur_y || !cur_u || !cur_v || !rec_y || !rec_u || !rec_v || !coefs || !nzmask || !modes || !row_progress || (w16 & 15) || (h16 & 15) ||
+        w16 < 16 || h16 < 16) {
+        set_error("gvc_encode_intra: bad arguments");
+        return GVC_ERR_INVALID_ARG;
+    }
+    if (qp < 0 || qp > 51) { set_error("gvc_encode_intra: qp %d outside 0..51", qp); return GVC_ERR_INVALID_ARG; }
+    if (h16 / 16 > 1024) { set_error("gvc_encode_intra: more than 1024 macroblock rows"); return GVC_ERR_TOO_LARGE; }
+    IntraArgs a;
+    a.cur_y = cur_y; a.cur_u = cur_u; a.cur_v = cur_v; a.rec_y = rec_y; a.rec_u = rec_u; a.rec_v = rec_v;
+    a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
+    fill_quant_params(a.q, qp, true);
+    a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.progress = row_progress;
+    return launch_encode_intra(a, static_cast<cudaStream_t>(stream));
 }
 
 int gvc_lambda_for_qp(int qp) { return lambda_for_qp(qp); }

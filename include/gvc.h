@@ -154,6 +154,13 @@ int gvc_me_refine(const uint8_t *cur_y, const gvc_ref_planes *ref, int stride, i
 int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *cur_v, const gvc_ref_planes *ref,
                      uint8_t *rec_y, uint8_t *rec_u, uint8_t *rec_v, int sy, int sc, int w16, int h16,
                      const gvc_mb_motion *motion, int qp, int16_t *coefs, uint32_t *nzmask, void *stream);
+/* K7: an all-Intra16x16 frame (the IDR that opens every segment): prediction from reconstructed neighbours
+ * (H.264 8.3.3 vertical / horizontal / DC by SAD, chroma DC), transform with the luma DC Hadamard path, quant,
+ * reconstruction.  Macroblock rows run as a wavefront inside one launch; row_progress is device scratch of
+ * h16/16 ints (cleared by the call).  modes: chosen Intra16x16 prediction mode per MB. */
+int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *cur_v, uint8_t *rec_y, uint8_t *rec_u,
+                     uint8_t *rec_v, int sy, int sc, int w16, int h16, int qp, int16_t *coefs, uint32_t *nzmask,
+                     uint8_t *modes, int *row_progress, void *stream);
 /* x264_lambda_tab[qp] */
 int gvc_lambda_for_qp(int qp);
 

@@ -105,6 +105,8 @@ void gvc_oracle_me_refine(const uint8_t *cur, const uint8_t *const planes[4], in
 void gvc_oracle_encode_inter_frame(const uint8_t *const cur[3], const uint8_t *const ref_luma[4],
                                    const uint8_t *const ref_chroma[2], uint8_t *const recon[3], int sy, int sc,
                                    int w16, int h16, const int32_t *motion, int qp, int16_t *coefs, uint32_t *nzmask);
+void gvc_oracle_encode_intra_frame(const uint8_t *const cur[3], uint8_t *const recon[3], int sy, int sc, int w16, int h16,
+                                   int qp, int16_t *coefs, uint32_t *nzmask, uint8_t *modes);
 void gvc_oracle_extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi);
 
 #ifdef __cplusplus

@@ -227,3 +227,124 @@ void gvc_oracle_extend_border(uint8_t *p, int stride, int w, int h, int x_lo, in
             p[(ptrdiff_t)y * stride + x] = p[(ptrdiff_t)cy * stride + cx];
         }
 }
+
+/* ---- K7: all-Intra16x16 frame (IDR) ----------------------------------------------------------------
+ * Every macroblock is Intra16x16 with the cheapest (SAD against the source) of the available modes
+ * vertical (0, needs the MB above), horizontal (1, needs the MB to the left), DC (2); candidates are tried in
+ * that order and a later one must be strictly cheaper.  Chroma always uses DC prediction (mode 0).
+ * H.264 8.3.3 (Intra_16x16 prediction), 8.3.4 (chroma DC rules per 4x4 block), 8.5.2 / 8.5.10 (DC path);
+ * x264 mb_encode_i16x16 for the order of operations.  Neighbours are RECONSTRUCTED samples.
+ * coef layout as for inter MBs; luma blocks carry AC only (entry 0 = 0), block 25 holds the 16 luma DC levels
+ * (zig-zag), nzmask bit 26 = luma DC nonzero.  modes[mb] = chosen luma mode. */
+static void chroma_dc_pred(const uint8_t *rec, int sc, int x0, int y0, int has_top, int has_left, uint8_t pred[64])
+{
+    int st[2] = {0, 0}, sl[2] = {0, 0};
+    for (int i = 0; i < 8; i++) {
+        if (has_top) st[i >> 2] += rec[(ptrdiff_t)(y0 - 1) * sc + x0 + i];
+        if (has_left) sl[i >> 2] += rec[(ptrdiff_t)(y0 + i) * sc + x0 - 1];
+    }
+    for (int b = 0; b < 4; b++) {
+        const int bx = b & 1, by = b >> 1;
+        int v;
+        if (bx == by) { /* (0,0) and (4,4): both neighbours when present */
+            if (has_top && has_left) v = (st[bx] + sl[by] + 4) >> 3;
+            else if (has_top) v = (st[bx] + 2) >> 2;
+            else if (has_left) v = (sl[by] + 2) >> 2;
+            else v = 128;
+        } else if (bx == 1) { /* (4,0): top preferred */
+            if (has_top) v = (st[1] + 2) >> 2;
+            else if (has_left) v = (sl[0] + 2) >> 2;
+            else v = 128;
+        } else { /* (0,4): left preferred */
+            if (has_left) v = (sl[1] + 2) >> 2;
+            else if (has_top) v = (st[0] + 2) >> 2;
+            else v = 128;
+        }
+        for (int j = 0; j < 4; j++)
+            for (int i = 0; i < 4; i++) pred[(4 * by + j) * 8 + 4 * bx + i] = (uint8_t)v;
+    }
+}
+
+void gvc_oracle_encode_intra_frame(const uint8_t *const cur[3], uint8_t *const recon[3], int sy, int sc, int w16, int h16,
+                                   int qp, int16_t *coefs, uint32_t *nzmask, uint8_t *modes)
+{
+    const int mbw = w16 / 16, mbh = h16 / 16, qpc = gvc_oracle_chroma_qp(qp);
+    uint16_t mfy[16], by_[16], mfc[16], bc[16];
+    gvc_oracle_quant4_tables(qp, 1, mfy, by_);
+    gvc_oracle_quant4_tables(qpc, 1, mfc, bc);
+    for (int my = 0; my < mbh; my++)
+        for (int mx = 0; mx < mbw; mx++) {
+            const int has_top = my > 0, has_left = mx > 0, x0 = 16 * mx, y0 = 16 * my;
+            int16_t *co = coefs + (size_t)(my * mbw + mx) * 26 * 16;
+            uint32_t nz = 0;
+            uint8_t  pred[3][256], py[256], pc[64];
+            const uint8_t *src = cur[0] + (ptrdiff_t)y0 * sy + x0;
+            uint8_t       *rec = recon[0] + (ptrdiff_t)y0 * sy + x0;
+            memset(co, 0, sizeof(int16_t) * 26 * 16);
+            int sum = 0, n = 0;
+            for (int i = 0; i < 16; i++) {
+                if (has_top) { sum += rec[-sy + i]; n++; }
+                if (has_left) { sum += rec[(ptrdiff_t)i * sy - 1]; n++; }
+            }
+            const int dcv = n == 32 ? (sum + 16) >> 5 : n == 16 ? (sum + 8) >> 4 : 128;
+            for (int y = 0; y < 16; y++)
+                for (int x = 0; x < 16; x++) {
+                    pred[0][y * 16 + x] = has_top ? rec[-sy + x] : 0;
+                    pred[1][y * 16 + x] = has_left ? rec[(ptrdiff_t)y * sy - 1] : 0;
+                    pred[2][y * 16 + x] = (uint8_t)dcv;
+                }
+            int best = -1, mode = 2;
+            for (int m = 0; m < 3; m++) {
+                if ((m == 0 && !has_top) || (m == 1 && !has_left)) continue;
+                const int s = gvc_oracle_sad(src, sy, pred[m], 16, 16, 16);
+                if (best < 0 || s < best) { best = s; mode = m; }
+            }
+            memcpy(py, pred[mode], 256);
+            modes[my * mbw + mx] = (uint8_t)mode;
+            int16_t c[16][16], dc[16];
+            for (int b = 0; b < 16; b++) {
+                const int bx = 4 * (b & 3), by = 4 * (b >> 2);
+                gvc_oracle_sub4x4_dct(c[b], src + (ptrdiff_t)by * sy + bx, sy, py + by * 16 + bx, 16);
+                dc[b] = c[b][0];
+                c[b][0] = 0;
+                if (gvc_oracle_quant(c[b], 16, mfy, by_)) nz |= 1u << b;
+                for (int i = 0; i < 16; i++) co[b * 16 + i] = c[b][k_zigzag4[i]];
+                gvc_oracle_dequant4(c[b], qp);
+            }
+            gvc_oracle_dct4x4dc(dc);
+            if (gvc_oracle_quant_dc(dc, 16, mfy[0] >> 1, by_[0] << 1)) nz |= 1u << 26;
+            for (int i = 0; i < 16; i++) co[25 * 16 + i] = dc[k_zigzag4[i]];
+            gvc_oracle_idct4x4dc(dc);
+            gvc_oracle_dequant4_dc(dc, qp);
+            for (int b = 0; b < 16; b++) {
+                const int bx = 4 * (b & 3), by = 4 * (b >> 2);
+                c[b][0] = dc[b];
+                gvc_oracle_add4x4_idct(rec + (ptrdiff_t)by * sy + bx, sy, py + by * 16 + bx, 16, c[b]);
+            }
+            for (int p = 0; p < 2; p++) {
+                int16_t cc[4][16], cdc[4];
+                uint8_t *crec = recon[1 + p];
+                chroma_dc_pred(crec, sc, 8 * mx, 8 * my, has_top, has_left, pc);
+                for (int b = 0; b < 4; b++) {
+                    const int bx = 4 * (b & 1), by = 4 * (b >> 1);
+                    gvc_oracle_sub4x4_dct(cc[b], cur[1 + p] + (ptrdiff_t)(8 * my + by) * sc + 8 * mx + bx, sc, pc + by * 8 + bx, 8);
+                    cdc[b] = cc[b][0];
+                    cc[b][0] = 0;
+                }
+                gvc_oracle_dct2x2dc(cdc);
+                if (gvc_oracle_quant_dc(cdc, 4, mfc[0] >> 1, bc[0] << 1)) nz |= 1u << (24 + p);
+                for (int i = 0; i < 4; i++) co[24 * 16 + 4 * p + i] = cdc[i];
+                gvc_oracle_dct2x2dc(cdc);
+                gvc_oracle_dequant2x2_dc(cdc, qpc);
+                for (int b = 0; b < 4; b++) {
+                    const int bx = 4 * (b & 1), by = 4 * (b >> 1);
+                    if (gvc_oracle_quant(cc[b], 16, mfc, bc)) nz |= 1u << (16 + 4 * p + b);
+                    for (int i = 0; i < 16; i++) co[(16 + 4 * p + b) * 16 + i] = cc[b][k_zigzag4[i]];
+                    gvc_oracle_dequant4(cc[b], qpc);
+                    cc[b][0] = cdc[b];
+                    gvc_oracle_add4x4_idct(crec + (ptrdiff_t)(8 * my + by) * sc + 8 * mx + bx, sc, pc + by * 8 + bx, 8, cc[b]);
+                }
+            }
+            nzmask[my * mbw + mx] = nz;
+        }
+}

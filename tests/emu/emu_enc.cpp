@@ -91,6 +91,25 @@ void emu_encode_inter(const uint8_t *const cur[3], const uint8_t *const ref[7], 
         }
 }
 
+void emu_encode_intra(const uint8_t *const cur[3], uint8_t *const rec[3], int sy, int sc, int w16, int h16, int qp, int16_t *coefs,
+                      uint32_t *nzmask, uint8_t *modes) {
+    IntraArgs a;
+    a.cur_y = cur[0]; a.cur_u = cur[1]; a.cur_v = cur[2]; a.rec_y = rec[0]; a.rec_u = rec[1]; a.rec_v = rec[2];
+    a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
+    fill_quant_params(a.q, qp, true);
+    a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.progress = nullptr;
+    for (int my = 0; my < a.mbh; ++my)          // rows in order: every wavefront dependency is already satisfied
+        for (int mx = 0; mx < a.mbw; ++mx) {
+            IntraSmem sm;
+            memset(&sm, 0xAB, sizeof(sm));
+            for (int l = 0; l < 32; ++l) intra_p0(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p1(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p2(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p3(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p4(l, a, mx, my, sm);
+        }
+}
+
 // quantiser constants as the product computes them: out[0..2]=mf_y, [3..5]=bias_y, [6..8]=dq_y, [9..11]=mf_c, [12..14]=bias_c,
 // [15..17]=dq_c, [18]=qpc, [19]=lambda
 void emu_quant_params(int qp, int intra, int out[20]) {

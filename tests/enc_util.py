@@ -231,3 +231,40 @@ def encode_inter(backend, cur, ref, motion, qp):
         for r, dev in zip(rec, (ry, ru, rv)):
             r.arr[...] = dev.t.cpu().numpy().reshape(r.arr.shape)
     return coefs, nz, [r.inner().copy() for r in rec]
+
+
+def encode_intra(backend, cur, qp):
+    """Returns (coefs[n,26,16], nzmask[n], modes[n], recon Y/U/V inner arrays)."""
+    g = cur.g
+    n = g["mbw"] * g["mbh"]
+    coefs = np.zeros((n, 26, 16), np.int16)
+    nz = np.zeros(n, np.uint32)
+    modes = np.zeros(n, np.uint8)
+    rec = [luma_plane(g, 0x11), chroma_plane(g, 0x11), chroma_plane(g, 0x11)]
+    P3 = ctypes.c_void_p * 3
+    if backend == "oracle":
+        oracle_lib.load().gvc_oracle_encode_intra_frame(P3(cur.Y.ptr(), cur.U.ptr(), cur.V.ptr()), P3(*[r.ptr() for r in rec]), g["sy"], g["sc"],
+                                                        g["w16"], g["h16"], qp, _vp(coefs.ctypes.data), _vp(nz.ctypes.data), _vp(modes.ctypes.data))
+    elif backend == "emu":
+        emu_lib.load().emu_encode_intra(P3(cur.Y.ptr(), cur.U.ptr(), cur.V.ptr()), P3(*[r.ptr() for r in rec]), g["sy"], g["sc"],
+                                        g["w16"], g["h16"], qp, _vp(coefs.ctypes.data), _vp(nz.ctypes.data), _vp(modes.ctypes.data))
+    else:
+        import torch
+        from gpu_enc import Dev
+        d = Dev()
+        cy, cu, cv = d.up(cur.Y), d.up(cur.U), d.up(cur.V)
+        ry, ru, rv = d.up(rec[0]), d.up(rec[1]), d.up(rec[2])
+        dco = torch.zeros(coefs.size, dtype=torch.int16, device="cuda")
+        dnz = torch.zeros(n, dtype=torch.int32, device="cuda")
+        dmo = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        prog = torch.full((g["mbh"],), 77, dtype=torch.int32, device="cuda")
+        d.check(d.lib.gvc_encode_intra(_vp(cy.ptr), _vp(cu.ptr), _vp(cv.ptr), _vp(ry.ptr), _vp(ru.ptr), _vp(rv.ptr), g["sy"], g["sc"],
+                                       g["w16"], g["h16"], qp, _vp(dco.data_ptr()), _vp(dnz.data_ptr()), _vp(dmo.data_ptr()),
+                                       _vp(prog.data_ptr()), None))
+        torch.cuda.synchronize()
+        coefs = dco.cpu().numpy().reshape(coefs.shape)
+        nz = dnz.cpu().numpy().view(np.uint32)
+        modes = dmo.cpu().numpy()
+        for r, dev in zip(rec, (ry, ru, rv)):
+            r.arr[...] = dev.t.cpu().numpy().reshape(r.arr.shape)
+    return coefs, nz, modes, [r.inner().copy() for r in rec]

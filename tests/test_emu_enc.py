@@ -116,3 +116,18 @@ def test_encode_inter_with_8x8_partitions_and_odd_vectors(pair):
     np.testing.assert_array_equal(nzo, nzb)
     for x, y in zip(reco, recb):
         np.testing.assert_array_equal(x, y)
+
+
+@pytest.mark.parametrize("qp", [10, 23, 38])
+def test_encode_intra_frame(pair, qp):
+    g, ref, cur = pair
+    co, nzo, mo, reco = E.encode_intra("oracle", cur, qp)
+    cb, nzb, mb, recb = E.encode_intra(BACKEND, cur, qp)
+    np.testing.assert_array_equal(mo, mb)
+    np.testing.assert_array_equal(co, cb)
+    np.testing.assert_array_equal(nzo, nzb)
+    for x, y in zip(reco, recb):
+        np.testing.assert_array_equal(x, y)
+    assert mo[0] == 2 and set(mo[1:g["mbw"]]) <= {1, 2}          # first MB: DC only; first row: no vertical
+    err = np.mean((reco[0].astype(float) - cur.Y.inner()) ** 2)
+    assert err < {10: 2.5, 23: 14.0, 38: 140.0}[qp]

@@ -109,3 +109,15 @@ def test_encode_inter_all_fractional_phases(pair):
 def test_bad_arguments(dev):
     assert dev.lib.gvc_me_lowres(None, None, 64, 4, 4, 8, 4, None, None) == -1
     assert dev.lib.gvc_encode_inter(None, None, None, None, None, None, None, 0, 0, 16, 16, None, 23, None, None, None) == -1
+
+
+@pytest.mark.parametrize("qp", [10, 23, 38])
+def test_encode_intra_frame(pair, qp):
+    g, ref, cur = pair
+    co, nzo, mo, reco = E.encode_intra("oracle", cur, qp)
+    cg, nzg, mg, recg = E.encode_intra("gpu", cur, qp)
+    np.testing.assert_array_equal(mo, mg)
+    np.testing.assert_array_equal(co, cg)
+    np.testing.assert_array_equal(nzo, nzg)
+    for x, y in zip(reco, recg):
+        np.testing.assert_array_equal(x, y)
