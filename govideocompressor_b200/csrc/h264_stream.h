@@ -1,0 +1,64 @@
+// h264_stream.h -- host-side H.264 bitstream writer (product code, C++): SPS / PPS / slice headers and CAVLC
+// slice data from the per-macroblock records the GPU kernels produce.
+//
+// north_star keeps entropy coding and muxing on the host; in the reference they happen inside the spawned
+// ffmpeg (libx264 CAVLC/CABAC + libavformat, client.go:115).  Syntax follows ITU-T H.264 clauses 7.3 (syntax),
+// 8.4.1.3 (motion vector prediction), 9.1 (Exp-Golomb), 9.2 (CAVLC).  Stream shape: Constrained Baseline,
+// one slice per picture, IDR + P pictures with one reference, Intra16x16 / P_L0_16x16 / P_8x8 / P_Skip,
+// 4x4 transform, in-loop deblocking disabled in the slice header (so the kernels' reconstruction is exactly what
+// a decoder produces).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+
+#include "enc_types.h"
+
+namespace gvc {
+
+class BitWriter {
+public:
+    void put(uint32_t value, int bits);          // MSB first, bits <= 32
+    void ue(uint32_t v);
+    void se(int32_t v);
+    void rbsp_trailing();                        // stop bit + zero alignment
+    size_t bit_count() const { return buf_.size() * 8 + n_; }
+    const std::vector<uint8_t> &bytes() const { return buf_; }   // valid after rbsp_trailing()
+private:
+    std::vector<uint8_t> buf_;
+    uint64_t acc_ = 0;
+    int      n_   = 0;
+};
+
+struct StreamParams {
+    int w = 0, h = 0;            // display size
+    int w16 = 0, h16 = 0;        // coded size
+    int fps_num = 30, fps_den = 1;
+    int level_idc = 31;
+};
+
+int  pick_level(int mbw, int mbh, int fps_num, int fps_den);
+void write_sps(BitWriter &bw, const StreamParams &p);
+void write_pps(BitWriter &bw);
+
+// Wraps an RBSP into a NAL unit (header byte + emulation prevention).  annexb: prefix 00 00 00 01, else a
+// 4-byte big-endian length (the MP4 sample format).
+void append_nal(std::vector<uint8_t> &out, int nal_ref_idc, int nal_unit_type, const std::vector<uint8_t> &rbsp, bool annexb);
+
+// Everything the slice writer needs about one coded picture (host copies of the kernels' outputs).
+struct PictureData {
+    int             mbw = 0, mbh = 0;
+    bool            idr = false;
+    int             frame_num = 0, idr_pic_id = 0, qp = 26;
+    const int16_t  *coefs = nullptr;    // kMbCoefs per MB (layout: enc_kernels.cuh)
+    const uint32_t *nzmask = nullptr;   // per MB
+    const MbMotion *motion = nullptr;   // P pictures
+    const uint8_t  *modes = nullptr;    // IDR pictures: Intra16x16 prediction mode
+};
+
+struct SliceStats { int skipped = 0, p16 = 0, p8 = 0, intra = 0; size_t bits = 0; };
+
+// Writes slice_layer_without_partitioning_rbsp() for the whole picture.
+void write_slice(BitWriter &bw, const PictureData &pic, SliceStats *stats);
+
+}  // namespace gvc

@@ -1,0 +1,265 @@
+// segment_encoder.h -- the per-segment encode loop (product code): orchestrates kernels K2..K7 over one closed-GOP
+// segment and turns their per-macroblock records into an H.264 elementary stream.
+//
+// This is what the reference obtains from `ffmpeg -i <id>.mp4 -vcodec libx264 ... c<id>.mp4` for one piece
+// (client.go:101-130): one IDR followed by P pictures, no state shared with other segments (server.go:176-190 hands
+// whole pieces to workers), so segments are independent units of work per GPU.
+//
+// The loop is a template over `Ops`, the set of stage launchers.  libgvc.so instantiates it with CUDA launchers
+// (gvc_segment.cu); the CPU test-suite instantiates it with the host emulation of the same kernel bodies
+// (tests/emu) to check the orchestration and the bitstream against a real decoder without a GPU.
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/gvc.h"
+#include "enc_host.h"
+#include "enc_kernels.cuh"
+#include "h264_stream.h"
+
+namespace gvc {
+
+struct SegmentConfig {
+    int  w = 0, h = 0;                  // picture size being encoded (after any resize)
+    int  fps_num = 30, fps_den = 1;
+    int  qp_i = 20, qp_p = 23;
+    int  merange = 16;                  // full-resolution search range; the lowres window is merange/2
+    bool keep_recon = false;            // keep every reconstructed picture (tests compare them with a decoder)
+};
+
+struct PlaneSizes { size_t y, c, l; int oy, oc, ol; };   // bytes per plane and offset of sample (0,0)
+
+inline PlaneSizes plane_sizes(const EncGeom &g) {
+    PlaneSizes s;
+    s.y = size_t(g.sy) * (g.h16 + 2 * kEncPad + 2);
+    s.c = size_t(g.sc) * (g.h16 / 2 + kEncPad + 2);
+    s.l = size_t(g.sl) * (g.h16 / 2 + kEncPad + 2);
+    s.oy = kEncPad * g.sy + kEncPad;
+    s.oc = (kEncPad / 2) * g.sc + kEncPad / 2;
+    s.ol = (kEncPad / 2) * g.sl + kEncPad / 2;
+    return s;
+}
+
+struct SegmentOutput {
+    std::vector<uint8_t>  sps_nal, pps_nal;       // NAL units without start code / length prefix
+    std::vector<uint8_t>  payload;                // length-prefixed NAL units, access unit after access unit
+    std::vector<size_t>   au_offset, au_size;     // one access unit per picture
+    std::vector<SliceStats> stats;
+    std::vector<uint8_t>  recon;                  // keep_recon: w16*h16*3/2 bytes per picture (Y, U, V tight)
+};
+
+// Ops concept (all calls asynchronous and in order; sync() waits for everything issued so far):
+//   void *alloc(size_t bytes);  void release(void *p);
+//   int extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi);
+//   int lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi);
+//   int hpel(const HpelArgs &a);  int me_lowres(const MeLowArgs &a);  int me_refine(const MeRefArgs &a);
+//   int encode_inter(const EncMbArgs &a);  int encode_intra(const IntraArgs &a);
+//   int download(void *host_dst, const void *dev_src, size_t bytes);
+//   int copy_plane(uint8_t *host_or_dev_dst, int dpitch, const uint8_t *dev_src, int spitch, int w, int h);   // device -> recon store
+//   int sync();
+template <class Ops>
+class SegmentEncoder {
+public:
+    SegmentEncoder(Ops &ops, const SegmentConfig &cfg) : ops_(ops), cfg_(cfg), g_(make_geom(cfg.w, cfg.h)), ps_(plane_sizes(g_)) {}
+    ~SegmentEncoder() { free_all(); }
+
+    const EncGeom &geom() const { return g_; }
+    const PlaneSizes &planes() const { return ps_; }
+
+    // Source pictures in the padded layout (interiors filled, borders not yet extended): device arrays holding
+    // n planes each, ps_.y / ps_.c bytes apart.  The resize stage writes straight into these.
+    struct CurFrames { uint8_t *y, *u, *v; };
+    int reserve(int n_frames) {
+        if (n_frames <= cap_) return 0;
+        free_all();
+        const size_t nmb = size_t(g_.mbw) * g_.mbh;
+        cur_.y = static_cast<uint8_t *>(ops_.alloc(ps_.y * n_frames));
+        cur_.u = static_cast<uint8_t *>(ops_.alloc(ps_.c * n_frames));
+        cur_.v = static_cast<uint8_t *>(ops_.alloc(ps_.c * n_frames));
+        cur_low_ = static_cast<uint8_t *>(ops_.alloc(ps_.l * n_frames));
+        for (int i = 0; i < 2; ++i) {
+            for (int k = 0; k < 4; ++k) rec_y_[i][k] = static_cast<uint8_t *>(ops_.alloc(ps_.y));
+            rec_u_[i] = static_cast<uint8_t *>(ops_.alloc(ps_.c));
+            rec_v_[i] = static_cast<uint8_t *>(ops_.alloc(ps_.c));
+            rec_low_[i] = static_cast<uint8_t *>(ops_.alloc(ps_.l));
+        }
+        d_coefs_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * kMbCoefs * nmb * n_frames));
+        d_nz_     = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb * n_frames));
+        d_motion_ = static_cast<MbMotion *>(ops_.alloc(sizeof(MbMotion) * nmb * n_frames));
+        d_modes_  = static_cast<uint8_t *>(ops_.alloc(nmb));
+        d_lowmv_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * 2 * nmb));
+        d_prog_   = static_cast<int *>(ops_.alloc(sizeof(int) * g_.mbh));
+        bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_coefs_ && d_nz_ && d_motion_ && d_modes_ && d_lowmv_ && d_prog_;
+        for (int i = 0; i < 2; ++i) {
+            for (int k = 0; k < 4; ++k) ok = ok && rec_y_[i][k];
+            ok = ok && rec_u_[i] && rec_v_[i] && rec_low_[i];
+        }
+        if (!ok) { free_all(); return GVC_ERR_NOMEM; }
+        cap_ = n_frames;
+        return 0;
+    }
+    CurFrames cur_frames() const { return cur_; }
+
+    // Issues every kernel of the segment (pictures 0..n-1 of cur_frames()).  Nothing is waited for.
+    int encode_device(int n) {
+        int rc;
+        const int P = kEncPad, Pc = kEncPad / 2;
+        const int lw = g_.w16 / 2, lh = g_.h16 / 2;
+        n_ = n;
+        for (int f = 0; f < n; ++f) {      // source pictures: extend the picture edges into the padding, build lowres
+            uint8_t *y = cur_.y + ps_.y * f + ps_.oy, *u = cur_.u + ps_.c * f + ps_.oc, *v = cur_.v + ps_.c * f + ps_.oc;
+            if ((rc = ops_.extend_border(y, g_.sy, cfg_.w, cfg_.h, -P, g_.w16 + P, -P, g_.h16 + P))) return rc;
+            if ((rc = ops_.extend_border(u, g_.sc, (cfg_.w + 1) / 2, (cfg_.h + 1) / 2, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
+            if ((rc = ops_.extend_border(v, g_.sc, (cfg_.w + 1) / 2, (cfg_.h + 1) / 2, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
+            if ((rc = ops_.lowres(y, g_.sy, -P, g_.w16 + P, -P, g_.h16 + P, cur_low_ + ps_.l * f + ps_.ol, g_.sl, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
+        }
+        const size_t nmb = size_t(g_.mbw) * g_.mbh;
+        if (cfg_.keep_recon) recon_store_.assign(size_t(g_.w16) * g_.h16 * 3 / 2 * n, 0);
+        for (int f = 0; f < n; ++f) {
+            const int r = f & 1, p = r ^ 1;
+            uint8_t *cy = cur_.y + ps_.y * f + ps_.oy, *cu = cur_.u + ps_.c * f + ps_.oc, *cv = cur_.v + ps_.c * f + ps_.oc;
+            uint8_t *ry = rec_y_[r][0] + ps_.oy, *ru = rec_u_[r] + ps_.oc, *rv = rec_v_[r] + ps_.oc;
+            if (f == 0) {
+                IntraArgs a;
+                a.cur_y = cy; a.cur_u = cu; a.cur_v = cv; a.rec_y = ry; a.rec_u = ru; a.rec_v = rv;
+                a.sy = g_.sy; a.sc = g_.sc; a.mbw = g_.mbw; a.mbh = g_.mbh;
+                fill_quant_params(a.q, cfg_.qp_i, true);
+                a.coefs = d_coefs_; a.nzmask = d_nz_; a.modes = d_modes_; a.progress = d_prog_;
+                if ((rc = ops_.encode_intra(a))) return rc;
+            } else {
+                RefPlanes ref;
+                ref.y = rec_y_[p][0] + ps_.oy; ref.hh = rec_y_[p][1] + ps_.oy; ref.hv = rec_y_[p][2] + ps_.oy; ref.hc = rec_y_[p][3] + ps_.oy;
+                ref.u = rec_u_[p] + ps_.oc; ref.v = rec_v_[p] + ps_.oc; ref.low = rec_low_[p] + ps_.ol;
+                QuantParams q;
+                fill_quant_params(q, cfg_.qp_p, false);
+                MeLowArgs ml;
+                ml.cur = cur_low_ + ps_.l * f + ps_.ol; ml.ref = ref.low; ml.stride = g_.sl; ml.mbw = g_.mbw; ml.mbh = g_.mbh;
+                ml.r = cfg_.merange / 2; ml.lambda = q.lambda; ml.out_mv = d_lowmv_;
+                if ((rc = ops_.me_lowres(ml))) return rc;
+                MeRefArgs mr;
+                mr.cur = cy; mr.ref = ref; mr.stride = g_.sy; mr.w16 = g_.w16; mr.h16 = g_.h16; mr.mbw = g_.mbw; mr.mbh = g_.mbh;
+                mr.lambda = q.lambda; mr.lowres_mv = d_lowmv_; mr.out = d_motion_ + nmb * f;
+                if ((rc = ops_.me_refine(mr))) return rc;
+                EncMbArgs e;
+                e.cur_y = cy; e.cur_u = cu; e.cur_v = cv; e.ref = ref; e.rec_y = ry; e.rec_u = ru; e.rec_v = rv;
+                e.sy = g_.sy; e.sc = g_.sc; e.mbw = g_.mbw; e.mbh = g_.mbh; e.q = q;
+                e.motion = d_motion_ + nmb * f; e.coefs = d_coefs_ + size_t(kMbCoefs) * nmb * f; e.nzmask = d_nz_ + nmb * f;
+                if ((rc = ops_.encode_inter(e))) return rc;
+            }
+            if (cfg_.keep_recon) {
+                uint8_t *dst = recon_store_.data() + size_t(g_.w16) * g_.h16 * 3 / 2 * f;
+                if ((rc = ops_.copy_plane(dst, g_.w16, ry, g_.sy, g_.w16, g_.h16))) return rc;
+                if ((rc = ops_.copy_plane(dst + size_t(g_.w16) * g_.h16, lw, ru, g_.sc, lw, lh))) return rc;
+                if ((rc = ops_.copy_plane(dst + size_t(g_.w16) * g_.h16 * 5 / 4, lw, rv, g_.sc, lw, lh))) return rc;
+            }
+            if (f + 1 < n) {                // the reconstruction becomes the next picture's reference
+                if ((rc = ops_.extend_border(ry, g_.sy, g_.w16, g_.h16, -P, g_.w16 + P, -P, g_.h16 + P))) return rc;
+                if ((rc = ops_.extend_border(ru, g_.sc, lw, lh, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
+                if ((rc = ops_.extend_border(rv, g_.sc, lw, lh, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
+                HpelArgs ha;
+                ha.src = ry; ha.dh = rec_y_[r][1] + ps_.oy; ha.dv = rec_y_[r][2] + ps_.oy; ha.dc = rec_y_[r][3] + ps_.oy;
+                ha.stride = g_.sy; ha.x_lo = -P; ha.x_hi = g_.w16 + P; ha.y_lo = -P; ha.y_hi = g_.h16 + P;
+                if ((rc = ops_.hpel(ha))) return rc;
+                if ((rc = ops_.lowres(ry, g_.sy, -P, g_.w16 + P, -P, g_.h16 + P, rec_low_[r] + ps_.ol, g_.sl, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
+            }
+        }
+        return 0;
+    }
+
+    // Copies the per-macroblock records to the host, waits, and writes the elementary stream.
+    int finish(SegmentOutput &out) {
+        const size_t nmb = size_t(g_.mbw) * g_.mbh;
+        int rc;
+        h_coefs_.resize(size_t(kMbCoefs) * nmb * n_);
+        h_nz_.resize(nmb * n_);
+        h_motion_.resize(nmb * n_);
+        h_modes_.resize(nmb);
+        if ((rc = ops_.download(h_coefs_.data(), d_coefs_, sizeof(int16_t) * h_coefs_.size()))) return rc;
+        if ((rc = ops_.download(h_nz_.data(), d_nz_, sizeof(uint32_t) * h_nz_.size()))) return rc;
+        if ((rc = ops_.download(h_motion_.data(), d_motion_, sizeof(MbMotion) * h_motion_.size()))) return rc;
+        if ((rc = ops_.download(h_modes_.data(), d_modes_, nmb))) return rc;
+        if ((rc = ops_.sync())) return rc;
+        write_stream(out);
+        if (cfg_.keep_recon) out.recon.swap(recon_store_);
+        return 0;
+    }
+
+    void write_stream(SegmentOutput &out) {
+        const size_t nmb = size_t(g_.mbw) * g_.mbh;
+        StreamParams sp;
+        sp.w = cfg_.w; sp.h = cfg_.h; sp.w16 = g_.w16; sp.h16 = g_.h16; sp.fps_num = cfg_.fps_num; sp.fps_den = cfg_.fps_den;
+        sp.level_idc = pick_level(g_.mbw, g_.mbh, cfg_.fps_num, cfg_.fps_den);
+        {
+            BitWriter s, p;
+            write_sps(s, sp);
+            write_pps(p);
+            std::vector<uint8_t> tmp;
+            append_nal(tmp, 3, 7, s.bytes(), false);
+            out.sps_nal.assign(tmp.begin() + 4, tmp.end());
+            tmp.clear();
+            append_nal(tmp, 3, 8, p.bytes(), false);
+            out.pps_nal.assign(tmp.begin() + 4, tmp.end());
+        }
+        out.payload.clear(); out.au_offset.clear(); out.au_size.clear(); out.stats.clear();
+        for (int f = 0; f < n_; ++f) {
+            PictureData pic;
+            pic.mbw = g_.mbw; pic.mbh = g_.mbh; pic.idr = f == 0; pic.frame_num = f; pic.idr_pic_id = 0;
+            pic.qp = f == 0 ? cfg_.qp_i : cfg_.qp_p;
+            pic.coefs = h_coefs_.data() + size_t(kMbCoefs) * nmb * f;
+            pic.nzmask = h_nz_.data() + nmb * f;
+            pic.motion = h_motion_.data() + nmb * f;
+            pic.modes = h_modes_.data();
+            BitWriter  bw;
+            SliceStats st;
+            write_slice(bw, pic, &st);
+            const size_t at = out.payload.size();
+            if (f == 0) {   // parameter sets travel in-band with the IDR too (Annex B extraction stays decodable)
+                BitWriter s, p;
+                write_sps(s, sp);
+                write_pps(p);
+                append_nal(out.payload, 3, 7, s.bytes(), false);
+                append_nal(out.payload, 3, 8, p.bytes(), false);
+            }
+            append_nal(out.payload, f == 0 ? 3 : 2, f == 0 ? 5 : 1, bw.bytes(), false);
+            out.au_offset.push_back(at);
+            out.au_size.push_back(out.payload.size() - at);
+            out.stats.push_back(st);
+        }
+    }
+
+private:
+    void free_all() {
+        auto rel = [&](auto *&p) { if (p) ops_.release(p); p = nullptr; };
+        rel(cur_.y); rel(cur_.u); rel(cur_.v); rel(cur_low_);
+        for (int i = 0; i < 2; ++i) {
+            for (int k = 0; k < 4; ++k) rel(rec_y_[i][k]);
+            rel(rec_u_[i]); rel(rec_v_[i]); rel(rec_low_[i]);
+        }
+        rel(d_coefs_); rel(d_nz_); rel(d_motion_); rel(d_modes_); rel(d_lowmv_); rel(d_prog_);
+        cap_ = 0;
+    }
+
+    Ops          &ops_;
+    SegmentConfig cfg_;
+    EncGeom       g_;
+    PlaneSizes    ps_;
+    int           cap_ = 0, n_ = 0;
+    CurFrames     cur_{nullptr, nullptr, nullptr};
+    uint8_t      *cur_low_ = nullptr;
+    uint8_t      *rec_y_[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
+    uint8_t      *rec_u_[2] = {nullptr, nullptr}, *rec_v_[2] = {nullptr, nullptr}, *rec_low_[2] = {nullptr, nullptr};
+    int16_t      *d_coefs_ = nullptr;
+    uint32_t     *d_nz_ = nullptr;
+    MbMotion     *d_motion_ = nullptr;
+    uint8_t      *d_modes_ = nullptr;
+    int16_t      *d_lowmv_ = nullptr;
+    int          *d_prog_ = nullptr;
+    std::vector<int16_t>  h_coefs_;
+    std::vector<uint32_t> h_nz_;
+    std::vector<MbMotion> h_motion_;
+    std::vector<uint8_t>  h_modes_, recon_store_;
+};
+
+}  // namespace gvc

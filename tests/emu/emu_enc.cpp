@@ -10,6 +10,52 @@
 
 using namespace gvc;
 
+void emu_run_me_lowres(const MeLowArgs &a) {
+    for (int my = 0; my < a.mbh; ++my)
+        for (int mx = 0; mx < a.mbw; ++mx) {
+            unsigned keys[32];
+            for (int l = 0; l < 32; ++l) me_lowres_lane(l, a, mx, my, keys);
+            for (int l = 0; l < 32; ++l) me_lowres_pick(l, a, mx, my, keys);
+        }
+}
+void emu_run_me_refine(const MeRefArgs &a) {
+    for (int my = 0; my < a.mbh; ++my)
+        for (int mx = 0; mx < a.mbw; ++mx) {
+            MeRefSmem sm;
+            memset(&sm, 0xAB, sizeof(sm));
+            for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) me_ref_pick(l, a, mx, my, sm);
+            for (int step = 2; step >= 1; --step)
+                for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
+                    for (int l = 0; l < 32; ++l) me_ref_satd(l, a, mx, my, ci, step, sm);
+                    for (int l = 0; l < 32; ++l) me_ref_update(l, a, mx, my, ci, step, sm);
+                }
+            for (int l = 0; l < 32; ++l) me_ref_out(l, a, mx, my, sm);
+        }
+}
+void emu_run_encode_inter(const EncMbArgs &a) {
+    for (int my = 0; my < a.mbh; ++my)
+        for (int mx = 0; mx < a.mbw; ++mx) {
+            EncMbSmem sm;
+            memset(&sm, 0xAB, sizeof(sm));
+            for (int l = 0; l < 32; ++l) enc_mb_p1(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) enc_mb_p2(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) enc_mb_p3(l, a, mx, my, sm);
+        }
+}
+void emu_run_encode_intra(const IntraArgs &a) {
+    for (int my = 0; my < a.mbh; ++my)          // rows in order: every wavefront dependency is already satisfied
+        for (int mx = 0; mx < a.mbw; ++mx) {
+            IntraSmem sm;
+            memset(&sm, 0xAB, sizeof(sm));
+            for (int l = 0; l < 32; ++l) intra_p0(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p1(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p2(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p3(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p4(l, a, mx, my, sm);
+        }
+}
+
 extern "C" {
 
 void emu_extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi) {
@@ -39,12 +85,7 @@ void emu_hpel(const uint8_t *src, uint8_t *dh, uint8_t *dv, uint8_t *dc, int str
 void emu_me_lowres(const uint8_t *cur, const uint8_t *ref, int stride, int mbw, int mbh, int r, int lambda, int16_t *out_mv) {
     MeLowArgs a;
     a.cur = cur; a.ref = ref; a.stride = stride; a.mbw = mbw; a.mbh = mbh; a.r = r; a.lambda = lambda; a.out_mv = out_mv;
-    for (int my = 0; my < mbh; ++my)
-        for (int mx = 0; mx < mbw; ++mx) {
-            unsigned keys[32];
-            for (int l = 0; l < 32; ++l) me_lowres_lane(l, a, mx, my, keys);
-            for (int l = 0; l < 32; ++l) me_lowres_pick(l, a, mx, my, keys);
-        }
+    emu_run_me_lowres(a);
 }
 
 static RefPlanes mkref(const uint8_t *const p[7]) {
@@ -59,19 +100,7 @@ void emu_me_refine(const uint8_t *cur, const uint8_t *const ref[7], int stride, 
     MeRefArgs a;
     a.cur = cur; a.ref = mkref(ref); a.stride = stride; a.w16 = w16; a.h16 = h16; a.mbw = w16 / 16; a.mbh = h16 / 16;
     a.lambda = lambda; a.lowres_mv = lowres_mv; a.out = static_cast<MbMotion *>(out);
-    for (int my = 0; my < a.mbh; ++my)
-        for (int mx = 0; mx < a.mbw; ++mx) {
-            MeRefSmem sm;
-            memset(&sm, 0xAB, sizeof(sm));
-            for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) me_ref_pick(l, a, mx, my, sm);
-            for (int step = 2; step >= 1; --step)
-                for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
-                    for (int l = 0; l < 32; ++l) me_ref_satd(l, a, mx, my, ci, step, sm);
-                    for (int l = 0; l < 32; ++l) me_ref_update(l, a, mx, my, ci, step, sm);
-                }
-            for (int l = 0; l < 32; ++l) me_ref_out(l, a, mx, my, sm);
-        }
+    emu_run_me_refine(a);
 }
 
 void emu_encode_inter(const uint8_t *const cur[3], const uint8_t *const ref[7], uint8_t *const rec[3], int sy, int sc, int w16,
@@ -81,14 +110,7 @@ void emu_encode_inter(const uint8_t *const cur[3], const uint8_t *const ref[7], 
     a.rec_y = rec[0]; a.rec_u = rec[1]; a.rec_v = rec[2]; a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, false);
     a.motion = static_cast<const MbMotion *>(motion); a.coefs = coefs; a.nzmask = nzmask;
-    for (int my = 0; my < a.mbh; ++my)
-        for (int mx = 0; mx < a.mbw; ++mx) {
-            EncMbSmem sm;
-            memset(&sm, 0xAB, sizeof(sm));
-            for (int l = 0; l < 32; ++l) enc_mb_p1(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) enc_mb_p2(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) enc_mb_p3(l, a, mx, my, sm);
-        }
+    emu_run_encode_inter(a);
 }
 
 void emu_encode_intra(const uint8_t *const cur[3], uint8_t *const rec[3], int sy, int sc, int w16, int h16, int qp, int16_t *coefs,
@@ -98,16 +120,7 @@ void emu_encode_intra(const uint8_t *const cur[3], uint8_t *const rec[3], int sy
     a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, true);
     a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.progress = nullptr;
-    for (int my = 0; my < a.mbh; ++my)          // rows in order: every wavefront dependency is already satisfied
-        for (int mx = 0; mx < a.mbw; ++mx) {
-            IntraSmem sm;
-            memset(&sm, 0xAB, sizeof(sm));
-            for (int l = 0; l < 32; ++l) intra_p0(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) intra_p1(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) intra_p2(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) intra_p3(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) intra_p4(l, a, mx, my, sm);
-        }
+    emu_run_encode_intra(a);
 }
 
 // quantiser constants as the product computes them: out[0..2]=mf_y, [3..5]=bias_y, [6..8]=dq_y, [9..11]=mf_c, [12..14]=bias_c,

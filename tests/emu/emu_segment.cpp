@@ -1,0 +1,102 @@
+// emu_segment.cpp -- TEST HARNESS: the product's SegmentEncoder (segment_encoder.h) instantiated over the host
+// emulation of the kernel bodies, so the CPU suite can check the orchestration, the bitstream writer and the MP4
+// muxer against a real H.264 decoder without a GPU.  Not part of libgvc.so.
+#define GVC_EMU 1
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "../../govideocompressor_b200/csrc/mp4_mux.h"
+#include "../../govideocompressor_b200/csrc/segment_encoder.h"
+
+using namespace gvc;
+
+extern "C" {
+void emu_extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi);
+void emu_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, uint8_t *dh, uint8_t *dv,
+                uint8_t *dc, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi);
+void emu_hpel(const uint8_t *src, uint8_t *dh, uint8_t *dv, uint8_t *dc, int stride, int x_lo, int x_hi, int y_lo, int y_hi);
+}
+void emu_run_me_lowres(const MeLowArgs &a);
+void emu_run_me_refine(const MeRefArgs &a);
+void emu_run_encode_inter(const EncMbArgs &a);
+void emu_run_encode_intra(const IntraArgs &a);
+
+namespace {
+struct EmuOps {
+    void *alloc(size_t n) { return calloc(1, n + 64); }
+    void  release(void *p) { free(p); }
+    int extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi) { emu_extend_border(p, stride, w, h, x_lo, x_hi, y_lo, y_hi); return 0; }
+    int lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi) {
+        emu_lowres(src, sstride, x_lo, x_hi, y_lo, y_hi, d0, nullptr, nullptr, nullptr, dstride, lx_lo, lx_hi, ly_lo, ly_hi);
+        return 0;
+    }
+    int hpel(const HpelArgs &a) { emu_hpel(a.src, a.dh, a.dv, a.dc, a.stride, a.x_lo, a.x_hi, a.y_lo, a.y_hi); return 0; }
+    int me_lowres(const MeLowArgs &a) { emu_run_me_lowres(a); return 0; }
+    int me_refine(const MeRefArgs &a) { emu_run_me_refine(a); return 0; }
+    int encode_inter(const EncMbArgs &a) { emu_run_encode_inter(a); return 0; }
+    int encode_intra(const IntraArgs &a) { emu_run_encode_intra(a); return 0; }
+    int download(void *dst, const void *src, size_t n) { memcpy(dst, src, n); return 0; }
+    int copy_plane(uint8_t *dst, int dpitch, const uint8_t *src, int spitch, int w, int h) {
+        for (int y = 0; y < h; ++y) memcpy(dst + size_t(y) * dpitch, src + size_t(y) * spitch, w);
+        return 0;
+    }
+    int sync() { return 0; }
+};
+}  // namespace
+
+extern "C" {
+
+// frames: n pictures, I420 tight (w*h*3/2 each).  Writes an MP4 to mp4_path (if not NULL), the Annex B stream to
+// annexb (caller buffer of annexb_cap bytes; *annexb_len receives the size), the encoder's reconstruction to recon
+// (n * w16*h16*3/2 bytes, or NULL) and per-picture stats (4 ints each: skipped, p16, p8, bytes).  Returns 0 or <0.
+int emu_encode_segment(const uint8_t *frames, int n, int w, int h, int fps, int qp_i, int qp_p, int merange, const char *mp4_path,
+                       uint8_t *annexb, size_t annexb_cap, size_t *annexb_len, uint8_t *recon, int *stats) {
+    EmuOps        ops;
+    SegmentConfig cfg;
+    cfg.w = w; cfg.h = h; cfg.fps_num = fps; cfg.fps_den = 1; cfg.qp_i = qp_i; cfg.qp_p = qp_p; cfg.merange = merange;
+    cfg.keep_recon = recon != nullptr;
+    SegmentEncoder<EmuOps> enc(ops, cfg);
+    if (enc.reserve(n)) return -4;
+    const EncGeom   &g  = enc.geom();
+    const PlaneSizes ps = enc.planes();
+    auto cur = enc.cur_frames();
+    const int cw = (w + 1) / 2, ch = (h + 1) / 2;
+    for (int f = 0; f < n; ++f) {
+        const uint8_t *src = frames + size_t(w) * h * 3 / 2 * f;   // tests use even sizes
+        for (int y = 0; y < h; ++y) memcpy(cur.y + ps.y * f + ps.oy + size_t(y) * g.sy, src + size_t(y) * w, w);
+        for (int y = 0; y < ch; ++y) {
+            memcpy(cur.u + ps.c * f + ps.oc + size_t(y) * g.sc, src + size_t(w) * h + size_t(y) * cw, cw);
+            memcpy(cur.v + ps.c * f + ps.oc + size_t(y) * g.sc, src + size_t(w) * h + size_t(cw) * ch + size_t(y) * cw, cw);
+        }
+    }
+    int rc = enc.encode_device(n);
+    if (rc) return rc;
+    SegmentOutput out;
+    if ((rc = enc.finish(out))) return rc;
+    if (recon) memcpy(recon, out.recon.data(), out.recon.size());
+    if (stats)
+        for (int f = 0; f < n; ++f) {
+            stats[4 * f] = out.stats[f].skipped; stats[4 * f + 1] = out.stats[f].p16; stats[4 * f + 2] = out.stats[f].p8;
+            stats[4 * f + 3] = int(out.au_size[f]);
+        }
+    if (annexb_len) {   // length-prefixed -> start codes
+        size_t o = 0, i = 0;
+        while (i + 4 <= out.payload.size()) {
+            const size_t len = (size_t(out.payload[i]) << 24) | (size_t(out.payload[i + 1]) << 16) | (size_t(out.payload[i + 2]) << 8) | out.payload[i + 3];
+            if (o + 4 + len > annexb_cap) return -8;
+            annexb[o] = 0; annexb[o + 1] = 0; annexb[o + 2] = 0; annexb[o + 3] = 1;
+            memcpy(annexb + o + 4, out.payload.data() + i + 4, len);
+            o += 4 + len; i += 4 + len;
+        }
+        *annexb_len = o;
+    }
+    if (mp4_path) {
+        std::vector<Mp4Sample> samples;
+        for (int f = 0; f < n; ++f) samples.push_back(Mp4Sample{out.au_offset[f], out.au_size[f], f == 0});
+        std::string err;
+        if (!write_mp4(mp4_path, w, h, fps, 1, out.sps_nal, out.pps_nal, out.payload, samples, err)) return -6;
+    }
+    return 0;
+}
+}

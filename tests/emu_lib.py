@@ -59,3 +59,22 @@ def plan_info(sw, sh, dw, dh, algo):
     assert load().emu_plan_info(sw, sh, dw, dh, algo, out) == 0
     return dict(fused=bool(out[0]), ng=out[1], vq=out[2], th_luma=out[3], th_chroma=out[4], smem=out[5],
                 h_taps=out[6], v_taps=out[7])
+
+
+def encode_segment(frames, w, h, fps=30, qp_i=20, qp_p=23, merange=16, mp4_path=None):
+    """frames: (n, w*h*3/2) uint8 I420.  Runs the product's SegmentEncoder over the emulated kernels.
+    Returns dict(annexb=bytes, recon=(n, w16*h16*3/2) uint8, stats=(n,4) int32 [skipped, p16, p8, au_bytes])."""
+    lib = load()
+    n = frames.shape[0]
+    w16, h16 = (w + 15) // 16 * 16, (h + 15) // 16 * 16
+    frames = np.ascontiguousarray(frames, np.uint8)
+    annexb = np.zeros(max(1 << 20, frames.size * 2), np.uint8)
+    alen = ctypes.c_size_t(0)
+    recon = np.zeros((n, w16 * h16 * 3 // 2), np.uint8)
+    stats = np.zeros((n, 4), np.int32)
+    lib.emu_encode_segment.argtypes = [ctypes.c_void_p] + [ctypes.c_int] * 7 + [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_size_t,
+                                                                                 ctypes.POINTER(ctypes.c_size_t), ctypes.c_void_p, ctypes.c_void_p]
+    rc = lib.emu_encode_segment(frames.ctypes.data, n, w, h, fps, qp_i, qp_p, merange, mp4_path.encode() if mp4_path else None,
+                                annexb.ctypes.data, annexb.size, ctypes.byref(alen), recon.ctypes.data, stats.ctypes.data)
+    assert rc == 0, f"emu_encode_segment failed: {rc}"
+    return dict(annexb=annexb[: alen.value].tobytes(), recon=recon, stats=stats, w16=w16, h16=h16)
