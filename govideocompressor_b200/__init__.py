@@ -7,3 +7,4 @@ fallback: importing works anywhere, but every compute call needs the built libra
 """
 from .lib import GvcError, load_library, library_path, init, version  # noqa: F401
 from .resize import ResizePlan, BICUBIC, BILINEAR, YUV420P, NV12  # noqa: F401
+from .encoder import Encoder, transcode_file, convert  # noqa: F401

@@ -4,6 +4,7 @@
 
 #include "enc_host.h"
 #include "enc_kernels.cuh"
+#include "enc_launch.h"
 #include "gvc_common.h"
 
 namespace gvc {

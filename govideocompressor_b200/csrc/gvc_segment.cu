@@ -1,0 +1,337 @@
+// gvc_segment.cu -- the segment encoder behind the C ABI: gvc_encoder_* and gvc_transcode_file.
+//
+// gvc_transcode_file is the drop-in for the reference's `exec.Command("ffmpeg", "-i", path, args..., "c"+path)`
+// (client.go:103-118): it reads the segment, runs resize (K1) and the encoder kernels (K2..K7) on the GPU, writes the
+// H.264 stream and the MP4 container on the host, and returns the text the reference stores as c<id>.mp4.log
+// (client.go:120-123).  On any failure it leaves NO output file, because the reference detects failure only by the
+// missing file (client.go:163-167).
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <thread>
+
+#include "enc_launch.h"
+#include "ff_args.h"
+#include "gvc_common.h"
+#include "mp4_mux.h"
+#include "segment_encoder.h"
+
+using namespace gvc;
+
+namespace {
+
+struct CudaOps {
+    cudaStream_t st = nullptr;
+    void *alloc(size_t n) { void *p = nullptr; return cudaMalloc(&p, n + 64) == cudaSuccess ? p : nullptr; }
+    void  release(void *p) { cudaFree(p); }
+    int extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi) { return launch_extend_border(p, stride, w, h, x_lo, x_hi, y_lo, y_hi, st); }
+    int lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi) {
+        return launch_lowres(src, sstride, x_lo, x_hi - 1, y_lo, y_hi - 1, d0, nullptr, nullptr, nullptr, dstride, lx_lo, lx_hi, ly_lo, ly_hi, st);
+    }
+    int hpel(const HpelArgs &a) { return launch_hpel(a, st); }
+    int me_lowres(const MeLowArgs &a) { return launch_me_lowres(a, st); }
+    int me_refine(const MeRefArgs &a) { return launch_me_refine(a, st); }
+    int encode_inter(const EncMbArgs &a) { return launch_encode_inter(a, st); }
+    int encode_intra(const IntraArgs &a) { return launch_encode_intra(a, st); }
+    int download(void *dst, const void *src, size_t n) { GVC_CUDA(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, st)); return 0; }
+    int copy_plane(uint8_t *dst, int dpitch, const uint8_t *src, int spitch, int w, int h) {
+        GVC_CUDA(cudaMemcpy2DAsync(dst, dpitch, src, spitch, w, h, cudaMemcpyDeviceToHost, st));
+        return 0;
+    }
+    int sync() { GVC_CUDA(cudaStreamSynchronize(st)); return 0; }
+};
+
+}  // namespace
+
+struct gvc_encoder {
+    gvc_encoder_config cfg;
+    CudaOps            ops;
+    SegmentEncoder<CudaOps> *seg = nullptr;
+    gvc_resize_plan   *plan = nullptr;
+    uint8_t           *d_src = nullptr;     // staging for host-supplied source pictures
+    size_t             d_src_cap = 0;
+    SegmentOutput      out;
+    int                n_last = 0;
+    bool               pending = false;
+    double             ms_kernels = 0, ms_entropy = 0;
+};
+
+namespace {
+
+size_t i420_bytes(int w, int h) { return size_t(w) * h + 2 * size_t((w + 1) / 2) * ((h + 1) / 2); }
+
+// issue resize (source I420 on the device -> padded current pictures) and every encoder kernel
+int issue_segment(gvc_encoder *e, const uint8_t *d_frames, int n) {
+    int rc = e->seg->reserve(n);
+    if (rc) { set_error("out of device memory reserving %d pictures", n); return rc; }
+    const EncGeom   &g  = e->seg->geom();
+    const PlaneSizes ps = e->seg->planes();
+    auto cur = e->seg->cur_frames();
+    const int sw = e->cfg.src_w, sh = e->cfg.src_h, scw = (sw + 1) / 2, sch = (sh + 1) / 2;
+    gvc_frames src, dst;
+    src.plane[0] = const_cast<uint8_t *>(d_frames);
+    src.plane[1] = src.plane[0] + size_t(sw) * sh;
+    src.plane[2] = src.plane[1] + size_t(scw) * sch;
+    src.stride[0] = sw; src.stride[1] = src.stride[2] = scw;
+    src.frame_stride[0] = src.frame_stride[1] = src.frame_stride[2] = i420_bytes(sw, sh);
+    dst.plane[0] = cur.y + ps.oy; dst.plane[1] = cur.u + ps.oc; dst.plane[2] = cur.v + ps.oc;
+    dst.stride[0] = g.sy; dst.stride[1] = dst.stride[2] = g.sc;
+    dst.frame_stride[0] = ps.y; dst.frame_stride[1] = dst.frame_stride[2] = ps.c;
+    if ((rc = gvc_resize_frames_device(e->plan, &src, &dst, n, e->ops.st))) return rc;
+    if ((rc = e->seg->encode_device(n))) return rc;
+    e->n_last = n;
+    e->pending = true;
+    return GVC_OK;
+}
+
+uint8_t *to_stream(const SegmentOutput &o, int annexb, size_t *len) {
+    uint8_t *buf = static_cast<uint8_t *>(malloc(o.payload.size() + 16));
+    if (!buf) return nullptr;
+    memcpy(buf, o.payload.data(), o.payload.size());
+    if (annexb) {   // 4-byte lengths -> 00 00 00 01 start codes, in place
+        size_t i = 0;
+        while (i + 4 <= o.payload.size()) {
+            const size_t n = (size_t(buf[i]) << 24) | (size_t(buf[i + 1]) << 16) | (size_t(buf[i + 2]) << 8) | buf[i + 3];
+            buf[i] = 0; buf[i + 1] = 0; buf[i + 2] = 0; buf[i + 3] = 1;
+            i += 4 + n;
+        }
+    }
+    *len = o.payload.size();
+    return buf;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg) {
+    if (!enc || !cfg) { set_error("gvc_encoder_create: NULL argument"); return GVC_ERR_INVALID_ARG; }
+    *enc = nullptr;
+    int rc = enter();
+    if (rc) return rc;
+    gvc_encoder_config c = *cfg;
+    if (c.dst_w <= 0) c.dst_w = c.src_w;
+    if (c.dst_h <= 0) c.dst_h = c.src_h;
+    if (c.fps_num <= 0) { c.fps_num = 30; c.fps_den = 1; }
+    if (c.fps_den <= 0) c.fps_den = 1;
+    if (c.merange <= 0) c.merange = 16;
+    if (c.scale_algo == 0) c.scale_algo = GVC_SCALE_BICUBIC;
+    if (c.src_w < 16 || c.src_h < 16 || c.dst_w < 16 || c.dst_h < 16 || c.src_w > 8192 || c.src_h > 8192 || c.dst_w > 8192 || c.dst_h > 8192) {
+        set_error("picture size %dx%d -> %dx%d outside 16..8192", c.src_w, c.src_h, c.dst_w, c.dst_h);
+        return GVC_ERR_INVALID_ARG;
+    }
+    if ((c.src_w | c.src_h | c.dst_w | c.dst_h) & 1) { set_error("odd picture sizes are not supported by the 4:2:0 encoder"); return GVC_ERR_UNSUPPORTED; }
+    if (c.crf < 0 || c.crf > 51) { set_error("crf %d outside 0..51", c.crf); return GVC_ERR_INVALID_ARG; }
+    if (c.merange < 4 || c.merange > 44) { set_error("merange %d outside 4..44", c.merange); return GVC_ERR_INVALID_ARG; }
+    gvc_encoder *e = new (std::nothrow) gvc_encoder;
+    if (!e) return GVC_ERR_NOMEM;
+    e->cfg = c;
+    if (cudaStreamCreateWithFlags(&e->ops.st, cudaStreamNonBlocking) != cudaSuccess) { delete e; set_error("cudaStreamCreate failed"); return GVC_ERR_CUDA; }
+    if ((rc = gvc_resize_plan_create(&e->plan, c.src_w, c.src_h, c.dst_w, c.dst_h, GVC_PIX_YUV420P, c.scale_algo))) { gvc_encoder_destroy(e); return rc; }
+    SegmentConfig sc;
+    sc.w = c.dst_w; sc.h = c.dst_h; sc.fps_num = c.fps_num; sc.fps_den = c.fps_den;
+    sc.qp_p = c.crf; sc.qp_i = c.crf >= 3 ? c.crf - 3 : 0;     // x264's default ip_factor 1.4 is about 3 QP
+    sc.merange = c.merange; sc.keep_recon = c.keep_recon != 0;
+    sc.host_threads = c.host_threads > 0 ? c.host_threads : int(std::max(1u, std::thread::hardware_concurrency()));
+    e->seg = new (std::nothrow) SegmentEncoder<CudaOps>(e->ops, sc);
+    if (!e->seg) { gvc_encoder_destroy(e); return GVC_ERR_NOMEM; }
+    *enc = e;
+    return GVC_OK;
+}
+
+void gvc_encoder_destroy(gvc_encoder *e) {
+    if (!e) return;
+    if (gvc::initialised()) cudaSetDevice(gvc::current_device());
+    if (e->ops.st) cudaStreamSynchronize(e->ops.st);
+    delete e->seg;
+    if (e->plan) gvc_resize_plan_destroy(e->plan);
+    if (e->d_src) cudaFree(e->d_src);
+    if (e->ops.st) cudaStreamDestroy(e->ops.st);
+    delete e;
+}
+
+int gvc_encoder_encode_device(gvc_encoder *e, const uint8_t *d_frames_i420, int n_frames) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!e || !d_frames_i420 || n_frames < 1) { set_error("gvc_encoder_encode_device: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    return issue_segment(e, d_frames_i420, n_frames);
+}
+
+int gvc_encoder_sync(gvc_encoder *e) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!e) { set_error("encoder is NULL"); return GVC_ERR_INVALID_ARG; }
+    GVC_CUDA(cudaStreamSynchronize(e->ops.st));
+    return GVC_OK;
+}
+
+void *gvc_encoder_stream(gvc_encoder *e) { return e ? static_cast<void *>(e->ops.st) : nullptr; }
+
+int gvc_encoder_finish(gvc_encoder *e, int annexb, uint8_t **out, size_t *out_len) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!e || !e->pending) { set_error("gvc_encoder_finish: no segment in flight"); return GVC_ERR_INVALID_ARG; }
+    const auto t0 = std::chrono::steady_clock::now();
+    if ((rc = e->seg->finish(e->out))) return rc;
+    e->ms_entropy = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    e->pending = false;
+    if (out && out_len) {
+        *out = to_stream(e->out, annexb, out_len);
+        if (!*out) return GVC_ERR_NOMEM;
+    }
+    return GVC_OK;
+}
+
+int gvc_encoder_encode_host(gvc_encoder *e, const uint8_t *frames_i420, int n_frames, int annexb, uint8_t **out, size_t *out_len) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!e || !frames_i420 || n_frames < 1) { set_error("gvc_encoder_encode_host: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    const size_t bytes = i420_bytes(e->cfg.src_w, e->cfg.src_h) * n_frames;
+    if (e->d_src_cap < bytes) {
+        if (e->d_src) cudaFree(e->d_src);
+        e->d_src = nullptr; e->d_src_cap = 0;
+        GVC_CUDA(cudaMalloc((void **)&e->d_src, bytes + 64));
+        e->d_src_cap = bytes;
+    }
+    GVC_CUDA(cudaMemcpyAsync(e->d_src, frames_i420, bytes, cudaMemcpyHostToDevice, e->ops.st));
+    if ((rc = issue_segment(e, e->d_src, n_frames))) return rc;
+    return gvc_encoder_finish(e, annexb, out, out_len);
+}
+
+int gvc_encoder_recon(gvc_encoder *e, uint8_t *dst, size_t cap) {
+    if (!e || !dst) { set_error("gvc_encoder_recon: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    if (e->out.recon.empty()) { set_error("the encoder was created without keep_recon"); return GVC_ERR_INVALID_ARG; }
+    if (cap < e->out.recon.size()) { set_error("recon buffer too small: need %zu bytes", e->out.recon.size()); return GVC_ERR_TOO_LARGE; }
+    memcpy(dst, e->out.recon.data(), e->out.recon.size());
+    return GVC_OK;
+}
+
+int gvc_encoder_stats(gvc_encoder *e, int *stats4_per_picture, int n_pictures) {
+    if (!e || !stats4_per_picture) { set_error("gvc_encoder_stats: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    for (int f = 0; f < n_pictures && f < (int)e->out.stats.size(); ++f) {
+        stats4_per_picture[4 * f] = e->out.stats[f].skipped; stats4_per_picture[4 * f + 1] = e->out.stats[f].p16;
+        stats4_per_picture[4 * f + 2] = e->out.stats[f].p8; stats4_per_picture[4 * f + 3] = int(e->out.au_size[f]);
+    }
+    return GVC_OK;
+}
+
+int gvc_encoder_write_mp4(gvc_encoder *e, const char *path) {
+    if (!e || !path || e->out.au_size.empty()) { set_error("gvc_encoder_write_mp4: nothing encoded"); return GVC_ERR_INVALID_ARG; }
+    std::vector<Mp4Sample> samples;
+    for (size_t f = 0; f < e->out.au_size.size(); ++f) samples.push_back(Mp4Sample{e->out.au_offset[f], e->out.au_size[f], f == 0});
+    std::string err, tmp = std::string(path) + ".gvc.tmp";
+    if (!write_mp4(tmp, e->cfg.dst_w, e->cfg.dst_h, e->cfg.fps_num, e->cfg.fps_den, e->out.sps_nal, e->out.pps_nal, e->out.payload, samples, err)) {
+        set_error("%s", err.c_str());
+        return GVC_ERR_IO;
+    }
+    if (rename(tmp.c_str(), path) != 0) { remove(tmp.c_str()); set_error("cannot rename %s to %s", tmp.c_str(), path); return GVC_ERR_IO; }
+    return GVC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- transcode
+static bool read_y4m_header(FILE *f, int &w, int &h, int &fn, int &fd, std::string &err) {
+    char line[256];
+    if (!fgets(line, sizeof(line), f) || strncmp(line, "YUV4MPEG2", 9) != 0) { err = "not a YUV4MPEG2 stream"; return false; }
+    w = h = 0; fn = 30; fd = 1;
+    bool c420 = true;
+    for (char *t = strtok(line + 9, " \n"); t; t = strtok(nullptr, " \n")) {
+        if (t[0] == 'W') w = atoi(t + 1);
+        else if (t[0] == 'H') h = atoi(t + 1);
+        else if (t[0] == 'F') { if (sscanf(t + 1, "%d:%d", &fn, &fd) != 2) { fn = 30; fd = 1; } }
+        else if (t[0] == 'C') c420 = strncmp(t + 1, "420", 3) == 0 && strstr(t, "p1") == nullptr;
+        else if (t[0] == 'I' && t[1] != 'p' && t[1] != '?') { err = "interlaced input is not supported"; return false; }
+    }
+    if (!c420) { err = "only 8-bit 4:2:0 input is supported"; return false; }
+    if (w < 16 || h < 16) { err = "bad picture size in the Y4M header"; return false; }
+    return true;
+}
+
+int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char *out_path, char **log_out, size_t *log_len) {
+    std::string log;
+    auto finish = [&](int rc) {
+        if (rc) log += std::string("gvc: error: ") + gvc_last_error() + "\n";
+        if (log_out && log_len) {
+            *log_out = static_cast<char *>(malloc(log.size() + 1));
+            if (*log_out) { memcpy(*log_out, log.c_str(), log.size() + 1); *log_len = log.size(); }
+        }
+        return rc;
+    };
+    if (log_out) *log_out = nullptr;
+    if (log_len) *log_len = 0;
+    if (!in_path || !ffmpeg_args || !out_path) { set_error("gvc_transcode_file: NULL argument"); return finish(GVC_ERR_INVALID_ARG); }
+    int rc = enter();
+    if (rc) return finish(rc);
+    log += std::string(gvc_version()) + "\n";
+    TranscodeOptions opt;
+    std::string      err;
+    if ((rc = parse_ffmpeg_args(ffmpeg_args, opt, err))) { set_error("%s", err.c_str()); return finish(rc); }
+    FILE *f = fopen(in_path, "rb");
+    if (!f) { set_error("%s: No such file or directory", in_path); return finish(GVC_ERR_IO); }
+    int w, h, fn, fd;
+    if (!read_y4m_header(f, w, h, fn, fd, err)) {
+        fclose(f);
+        set_error("%s: %s (this build reads YUV4MPEG2 segments; H.264-in-MP4 input needs a host demuxer/decoder)", in_path, err.c_str());
+        return finish(GVC_ERR_UNSUPPORTED);
+    }
+    if (opt.fps_num > 0) { fn = opt.fps_num; fd = opt.fps_den; }
+    gvc_encoder_config c;
+    memset(&c, 0, sizeof(c));
+    c.src_w = w; c.src_h = h; c.dst_w = opt.dst_w ? opt.dst_w : w; c.dst_h = opt.dst_h ? opt.dst_h : h;
+    c.fps_num = fn; c.fps_den = fd; c.crf = opt.crf; c.merange = opt.merange; c.scale_algo = opt.scale_algo;
+    gvc_encoder *e = nullptr;
+    if ((rc = gvc_encoder_create(&e, &c))) { fclose(f); return finish(rc); }
+    char buf[512];
+    snprintf(buf, sizeof(buf), "Input #0, yuv4mpegpipe, from '%s': %dx%d, %d/%d fps\nOutput #0, mp4, to '%s': h264 (gvc sm_100a), yuv420p, %dx%d, crf %d\n",
+             in_path, w, h, fn, fd, out_path, c.dst_w, c.dst_h, c.crf);
+    log += buf;
+
+    const size_t fb = i420_bytes(w, h);
+    const int    gop = std::max(1, std::min(opt.gop, 250));
+    uint8_t     *host = nullptr;
+    if (cudaHostAlloc((void **)&host, fb * gop, cudaHostAllocDefault) != cudaSuccess) { fclose(f); gvc_encoder_destroy(e); set_error("cannot allocate pinned staging"); return finish(GVC_ERR_NOMEM); }
+    std::vector<uint8_t>   payload;
+    std::vector<Mp4Sample> samples;
+    std::vector<uint8_t>   sps, pps;
+    int       total = 0;
+    long      n_skip = 0, n_p16 = 0, n_p8 = 0, n_intra = 0;
+    const auto t0 = std::chrono::steady_clock::now();
+    bool eof = false;
+    while (!eof && rc == 0) {
+        int n = 0;
+        while (n < gop) {
+            char fl[128];
+            if (!fgets(fl, sizeof(fl), f)) { eof = true; break; }
+            if (strncmp(fl, "FRAME", 5) != 0) { set_error("%s: damaged Y4M frame header", in_path); rc = GVC_ERR_IO; break; }
+            if (fread(host + fb * n, 1, fb, f) != fb) { set_error("%s: truncated frame %d", in_path, total + n); rc = GVC_ERR_IO; break; }
+            ++n;
+        }
+        if (rc || n == 0) break;
+        if ((rc = gvc_encoder_encode_host(e, host, n, 0, nullptr, nullptr))) break;
+        if (sps.empty()) { sps = e->out.sps_nal; pps = e->out.pps_nal; }
+        for (int i = 0; i < n; ++i) {
+            samples.push_back(Mp4Sample{payload.size() + e->out.au_offset[i], e->out.au_size[i], i == 0});
+            n_skip += e->out.stats[i].skipped; n_p16 += e->out.stats[i].p16; n_p8 += e->out.stats[i].p8; n_intra += e->out.stats[i].intra;
+        }
+        payload.insert(payload.end(), e->out.payload.begin(), e->out.payload.end());
+        total += n;
+    }
+    fclose(f);
+    cudaFreeHost(host);
+    gvc_encoder_destroy(e);
+    if (rc == 0 && total == 0) { set_error("%s: no frames", in_path); rc = GVC_ERR_IO; }
+    if (rc) return finish(rc);
+    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::string tmp = std::string(out_path) + ".gvc.tmp";
+    if (!write_mp4(tmp, c.dst_w, c.dst_h, fn, fd, sps, pps, payload, samples, err)) { set_error("%s", err.c_str()); return finish(GVC_ERR_IO); }
+    if (rename(tmp.c_str(), out_path) != 0) { remove(tmp.c_str()); set_error("cannot rename %s to %s", tmp.c_str(), out_path); return finish(GVC_ERR_IO); }
+    const double dur = double(total) * fd / fn, kbps = dur > 0 ? payload.size() * 8.0 / 1000.0 / dur : 0;
+    snprintf(buf, sizeof(buf), "frame=%5d fps=%.0f size=%8zukB time=%.2fs bitrate=%.1fkbits/s\n[gvc] mb I:%ld P16:%ld P8:%ld skip:%ld\n",
+             total, secs > 0 ? total / secs : 0.0, payload.size() / 1024, dur, kbps, n_intra, n_p16, n_p8, n_skip);
+    log += buf;
+    return finish(GVC_OK);
+}
+
+}  // extern "C"

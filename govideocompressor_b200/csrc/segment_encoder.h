@@ -11,7 +11,9 @@
 #pragma once
 #include <cstdint>
 #include <cstring>
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/gvc.h"
@@ -27,6 +29,7 @@ struct SegmentConfig {
     int  qp_i = 20, qp_p = 23;
     int  merange = 16;                  // full-resolution search range; the lowres window is merange/2
     bool keep_recon = false;            // keep every reconstructed picture (tests compare them with a decoder)
+    int  host_threads = 1;              // worker threads for entropy coding (pictures are independent)
 };
 
 struct PlaneSizes { size_t y, c, l; int oy, oc, ol; };   // bytes per plane and offset of sample (0,0)
@@ -203,30 +206,43 @@ public:
             out.pps_nal.assign(tmp.begin() + 4, tmp.end());
         }
         out.payload.clear(); out.au_offset.clear(); out.au_size.clear(); out.stats.clear();
-        for (int f = 0; f < n_; ++f) {
+        // pictures are independent for entropy coding: one worker thread per stripe of pictures
+        std::vector<std::vector<uint8_t>> au(n_);
+        out.stats.assign(n_, SliceStats());
+        auto code_picture = [&](int f) {
             PictureData pic;
-            pic.mbw = g_.mbw; pic.mbh = g_.mbh; pic.idr = f == 0; pic.frame_num = f; pic.idr_pic_id = 0;
+            pic.mbw = g_.mbw; pic.mbh = g_.mbh; pic.idr = f == 0; pic.frame_num = f; pic.idr_pic_id = idr_pic_id_;
             pic.qp = f == 0 ? cfg_.qp_i : cfg_.qp_p;
             pic.coefs = h_coefs_.data() + size_t(kMbCoefs) * nmb * f;
             pic.nzmask = h_nz_.data() + nmb * f;
             pic.motion = h_motion_.data() + nmb * f;
             pic.modes = h_modes_.data();
-            BitWriter  bw;
-            SliceStats st;
-            write_slice(bw, pic, &st);
-            const size_t at = out.payload.size();
+            BitWriter bw;
+            write_slice(bw, pic, &out.stats[f]);
             if (f == 0) {   // parameter sets travel in-band with the IDR too (Annex B extraction stays decodable)
                 BitWriter s, p;
                 write_sps(s, sp);
                 write_pps(p);
-                append_nal(out.payload, 3, 7, s.bytes(), false);
-                append_nal(out.payload, 3, 8, p.bytes(), false);
+                append_nal(au[f], 3, 7, s.bytes(), false);
+                append_nal(au[f], 3, 8, p.bytes(), false);
             }
-            append_nal(out.payload, f == 0 ? 3 : 2, f == 0 ? 5 : 1, bw.bytes(), false);
-            out.au_offset.push_back(at);
-            out.au_size.push_back(out.payload.size() - at);
-            out.stats.push_back(st);
+            append_nal(au[f], f == 0 ? 3 : 2, f == 0 ? 5 : 1, bw.bytes(), false);
+        };
+        const int workers = std::max(1, std::min(n_, std::min(cfg_.host_threads, 64)));
+        if (workers == 1) {
+            for (int f = 0; f < n_; ++f) code_picture(f);
+        } else {
+            std::vector<std::thread> pool;
+            for (int t = 0; t < workers; ++t)
+                pool.emplace_back([&, t] { for (int f = t; f < n_; f += workers) code_picture(f); });
+            for (std::thread &th : pool) th.join();
         }
+        for (int f = 0; f < n_; ++f) {
+            out.au_offset.push_back(out.payload.size());
+            out.au_size.push_back(au[f].size());
+            out.payload.insert(out.payload.end(), au[f].begin(), au[f].end());
+        }
+        idr_pic_id_ = (idr_pic_id_ + 1) & 0xffff;
     }
 
 private:
@@ -245,7 +261,7 @@ private:
     SegmentConfig cfg_;
     EncGeom       g_;
     PlaneSizes    ps_;
-    int           cap_ = 0, n_ = 0;
+    int           cap_ = 0, n_ = 0, idr_pic_id_ = 0;
     CurFrames     cur_{nullptr, nullptr, nullptr};
     uint8_t      *cur_low_ = nullptr;
     uint8_t      *rec_y_[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};

@@ -164,6 +164,48 @@ int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
 /* x264_lambda_tab[qp] */
 int gvc_lambda_for_qp(int qp);
 
+/* ---------------------------------------------------------------- segment encoder ------------- */
+/* Replaces: what one spawned `ffmpeg -i <id>.mp4 <args> c<id>.mp4` does for one piece (client.go:101-130):
+ * resize, H.264 encode (IDR + P pictures, closed GOP per call), container.  Kernels run on the library's own
+ * stream for the encoder; entropy coding (CAVLC) and muxing run on host threads (north_star keeps them on the host). */
+typedef struct gvc_encoder gvc_encoder;
+
+typedef struct gvc_encoder_config {
+    int src_w, src_h;          /* incoming pictures: 8-bit I420, planes tight */
+    int dst_w, dst_h;          /* encoded size; 0 = same as source (`-s WxH` / `-vf scale=`) */
+    int fps_num, fps_den;      /* 0 = 30/1 */
+    int crf;                   /* `-crf`, 0..51; P pictures use QP = crf, the IDR QP = crf - 3 */
+    int merange;               /* `-me_range`, 0 = 16 */
+    int scale_algo;            /* GVC_SCALE_*, 0 = bicubic */
+    int keep_recon;            /* keep the reconstruction of every picture (tests compare it with a decoder) */
+    int host_threads;          /* entropy-coding threads, 0 = all host cores */
+} gvc_encoder_config;
+
+int  gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg);
+void gvc_encoder_destroy(gvc_encoder *enc);
+/* One segment from HOST memory: n_frames I420 pictures.  Copies in, runs every kernel, copies the per-macroblock
+ * records back, entropy-codes them.  If out != NULL it receives a malloc'ed stream (gvc_free): Annex B when annexb != 0,
+ * else 4-byte length-prefixed NAL units (the MP4 sample format). */
+int gvc_encoder_encode_host(gvc_encoder *enc, const uint8_t *frames_i420, int n_frames, int annexb, uint8_t **out, size_t *out_len);
+/* Same, pictures already in DEVICE memory; only issues the kernels (asynchronous on gvc_encoder_stream()). */
+int gvc_encoder_encode_device(gvc_encoder *enc, const uint8_t *d_frames_i420, int n_frames);
+int gvc_encoder_sync(gvc_encoder *enc);
+void *gvc_encoder_stream(gvc_encoder *enc);      /* the cudaStream_t the encoder launches on */
+/* Completes a segment started with gvc_encoder_encode_device: D2H of the records + entropy coding. */
+int gvc_encoder_finish(gvc_encoder *enc, int annexb, uint8_t **out, size_t *out_len);
+/* keep_recon: the coded-size (multiples of 16) I420 reconstruction of every picture of the last segment. */
+int gvc_encoder_recon(gvc_encoder *enc, uint8_t *dst, size_t cap);
+/* per picture: skipped MBs, P16x16 MBs, P8x8 MBs, bytes */
+int gvc_encoder_stats(gvc_encoder *enc, int *stats4_per_picture, int n_pictures);
+/* Muxes the last segment into an MP4 file (temp name + rename). */
+int gvc_encoder_write_mp4(gvc_encoder *enc, const char *path);
+
+/* THE drop-in for client.go:115 `exec.Command("ffmpeg", "-i", in_path, args..., out_path)`: ffmpeg_args is the
+ * third field of the job string (server.go:179) verbatim.  On success out_path exists; on ANY failure it does not
+ * (the reference detects failure by the missing file, client.go:163-167).  *log_out (gvc_free) is the text the
+ * reference writes to c<id>.mp4.log (client.go:120-123).  Input container in this build: YUV4MPEG2. */
+int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char *out_path, char **log_out, size_t *log_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,122 @@
+"""GPU (-m gpu): the segment encoder of libgvc.so through the C ABI.
+ * its stream is byte-identical to the one the same encode loop produces over the emulated kernels on the CPU;
+ * FFmpeg's h264 decoder reproduces the GPU reconstruction bit for bit (tier 3) at small and BASELINE sizes, with resize;
+ * gvc_transcode_file / convert() keep the reference's conventions (output + log on success, NO output file on failure)."""
+import os
+
+import numpy as np
+import pytest
+
+import emu_lib
+import seq_util as S
+
+pytestmark = pytest.mark.gpu
+h264_decode = pytest.importorskip("h264_decode")
+
+
+@pytest.fixture(scope="module")
+def gvc():
+    import govideocompressor_b200 as g
+    g.init(0)
+    return g
+
+
+def check_decode(gvc_enc, annexb, recon, w, h, n):
+    dec = h264_decode.decode(annexb)
+    assert len(dec) == n
+    for f, (Y, U, V) in enumerate(dec):
+        ry, ru, rv = S.split_i420(recon[f], gvc_enc.w16, gvc_enc.h16)
+        np.testing.assert_array_equal(Y, ry[:h, :w], err_msg=f"luma drift at picture {f}")
+        np.testing.assert_array_equal(U, ru[: h // 2, : w // 2])
+        np.testing.assert_array_equal(V, rv[: h // 2, : w // 2])
+    return dec
+
+
+@pytest.mark.parametrize("w,h,n,crf,kw", [(96, 64, 5, 23, {}), (150, 100, 6, 26, dict(static_left=True, noise=1)),
+                                           (128, 96, 5, 28, dict(fast=True, noise=2)), (64, 48, 3, 4, dict(noise=40))])
+def test_stream_identical_to_cpu_emulation_and_decodable(gvc, w, h, n, crf, kw):
+    frames = S.moving_sequence(w, h, n, seed=w + n, **kw)
+    merange = 32 if kw.get("fast") else 16
+    enc = gvc.Encoder(w, h, crf=crf, merange=merange, keep_recon=True, host_threads=3)
+    stream = enc.encode_host(frames, annexb=True)
+    ref = emu_lib.encode_segment(frames, w, h, qp_i=max(crf - 3, 0), qp_p=crf, merange=merange)
+    assert stream == ref["annexb"], "GPU stream differs from the CPU emulation of the same kernels"
+    np.testing.assert_array_equal(enc.recon(), ref["recon"])
+    np.testing.assert_array_equal(enc.stats(), ref["stats"])
+    check_decode(enc, stream, enc.recon(), w, h, n)
+    enc.close()
+
+
+def test_baseline_size_with_resize_decodes_to_the_reconstruction(gvc):
+    """cfg2 shape: 1920x1080 source pictures resized to 1280x720 and encoded; 8 pictures of a segment."""
+    sw, sh, w, h, n = 1920, 1080, 1280, 720, 8
+    frames = S.moving_sequence(sw, sh, n, seed=2, noise=2)
+    enc = gvc.Encoder(sw, sh, w, h, crf=23, keep_recon=True)
+    stream = enc.encode_host(frames, annexb=True)
+    recon = enc.recon()
+    dec = check_decode(enc, stream, recon, w, h, n)
+    # quality sanity against the resized source (computed by the resize kernel that is itself pinned to libswscale)
+    plan = gvc.ResizePlan(sw, sh, w, h)
+    for f in (0, n - 1):
+        ref = plan.resize_host(list(S.split_i420(frames[f], sw, sh)))
+        assert S.psnr(dec[f][0], ref[0]) > 36.0
+    st = enc.stats()
+    assert st[0, 3] > st[1:, 3].mean()                       # the IDR is the largest picture
+    # a second segment on the same encoder object: state does not leak between segments
+    stream2 = enc.encode_host(frames[:3], annexb=True)
+    check_decode(enc, stream2, enc.recon(), w, h, 3)
+    assert stream2[:2000] == stream[:2000]                   # same IDR bytes: segments are independent
+    enc.close()
+
+
+def test_1080p_coded_height_1088_and_4k(gvc):
+    for (w, h, n) in ((1920, 1080, 3), (3840, 2160, 2)):
+        frames = S.moving_sequence(w, h, n, seed=5, noise=1)
+        enc = gvc.Encoder(w, h, crf=30, keep_recon=True)
+        stream = enc.encode_host(frames, annexb=True)
+        check_decode(enc, stream, enc.recon(), w, h, n)
+        enc.close()
+
+
+def write_y4m(path, frames, w, h, fps=30):
+    with open(path, "wb") as f:
+        f.write(b"YUV4MPEG2 W%d H%d F%d:1 Ip A1:1 C420jpeg\n" % (w, h, fps))
+        for fr in frames:
+            f.write(b"FRAME\n")
+            f.write(fr.tobytes())
+
+
+def test_transcode_file_and_convert_conventions(gvc, tmp_path):
+    cv2 = pytest.importorskip("cv2")
+    w, h, n = 320, 180, 12
+    frames = S.moving_sequence(w, h, n, seed=8)
+    src = os.path.join(tmp_path, "7.y4m")
+    write_y4m(src, frames, w, h, fps=25)
+    out = os.path.join(tmp_path, "c7.mp4")
+    rc, log = gvc.transcode_file(src, "-threads 4 -vcodec libx264 -crf 24 -s 160x90", out)      # server.go:69-70 shorthand + options
+    assert rc == 0 and os.path.exists(out) and not os.path.exists(out + ".gvc.tmp")
+    assert "frame=" in log and "160x90" in log
+    cap = cv2.VideoCapture(out)
+    assert cap.isOpened() and int(cap.get(cv2.CAP_PROP_FRAME_COUNT)) == n
+    assert int(cap.get(cv2.CAP_PROP_FRAME_WIDTH)) == 160 and int(cap.get(cv2.CAP_PROP_FRAME_HEIGHT)) == 90
+    assert abs(cap.get(cv2.CAP_PROP_FPS) - 25.0) < 1e-3
+    k = 0
+    while cap.read()[0]:
+        k += 1
+    assert k == n                                              # tier 3: the container decodes cleanly
+    # failures leave no output file (client.go:163-167 detects failure by the missing file) but do return a log
+    for bad_args in ("-threads 4 -vcodec libx265 -crf 26", "-vcodec libx264 -bogus 1", "-s 160x90"):
+        out2 = os.path.join(tmp_path, "c8.mp4")
+        rc, log = gvc.transcode_file(src, bad_args, out2)
+        assert rc != 0 and not os.path.exists(out2) and "error" in log
+    rc, log = gvc.transcode_file(os.path.join(tmp_path, "missing.y4m"), "-vcodec libx264", out + "x")
+    assert rc == -6 and not os.path.exists(out + "x")
+    # convert(): the reference's own entry point and side effects
+    cwd = os.getcwd()
+    os.chdir(tmp_path)
+    try:
+        assert gvc.convert("7.y4m", "-threads 4 -vcodec libx264") == 0
+        assert os.path.exists("c7.y4m") and os.path.getsize("c7.y4m.log") > 0
+        assert gvc.convert("7.y4m", "-threads 4 -vcodec libx265 -crf 26") == 0      # returns 0 even on failure, like the reference
+    finally:
+        os.chdir(cwd)
