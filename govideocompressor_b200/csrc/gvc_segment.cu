@@ -12,6 +12,7 @@
 #include <new>
 #include <string>
 #include <thread>
+#include <vector>
 
 #include "enc_launch.h"
 #include "ff_args.h"
@@ -23,19 +24,55 @@ using namespace gvc;
 
 namespace {
 
+// Optional per-stage timing with CUDA events on the launching stream (bench.py's roofline figures).
+enum Stage { kStResize = 0, kStBorder, kStLowres, kStHpel, kStMeLowres, kStMeRefine, kStEncInter, kStEncIntra, kStCount };
+struct StageTimer {
+    bool on = false;
+    struct Rec { int stage; cudaEvent_t a, b; };
+    std::vector<cudaEvent_t> pool;
+    size_t                   used = 0;
+    std::vector<Rec>         recs;
+    double ms[kStCount] = {};
+    int    launches[kStCount] = {};
+    cudaEvent_t get() {
+        if (used == pool.size()) { cudaEvent_t e; cudaEventCreate(&e); pool.push_back(e); }
+        return pool[used++];
+    }
+    void begin(int stage, cudaStream_t st) {
+        if (!on) return;
+        Rec r{stage, get(), get()};
+        cudaEventRecord(r.a, st);
+        recs.push_back(r);
+    }
+    void end(cudaStream_t st) { if (on) cudaEventRecord(recs.back().b, st); }
+    void reset() { recs.clear(); used = 0; for (int i = 0; i < kStCount; ++i) { ms[i] = 0; launches[i] = 0; } }
+    void collect() {      // the stream must have been synchronised
+        for (const Rec &r : recs) {
+            float t = 0;
+            if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) { ms[r.stage] += t; ++launches[r.stage]; }
+        }
+        recs.clear(); used = 0;
+    }
+    ~StageTimer() { for (cudaEvent_t e : pool) cudaEventDestroy(e); }
+};
+
 struct CudaOps {
     cudaStream_t st = nullptr;
+    StageTimer   tm;
+    template <class F> int timed(int stage, F f) { tm.begin(stage, st); const int rc = f(); tm.end(st); return rc; }
     void *alloc(size_t n) { void *p = nullptr; return cudaMalloc(&p, n + 64) == cudaSuccess ? p : nullptr; }
     void  release(void *p) { cudaFree(p); }
-    int extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi) { return launch_extend_border(p, stride, w, h, x_lo, x_hi, y_lo, y_hi, st); }
-    int lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi) {
-        return launch_lowres(src, sstride, x_lo, x_hi - 1, y_lo, y_hi - 1, d0, nullptr, nullptr, nullptr, dstride, lx_lo, lx_hi, ly_lo, ly_hi, st);
+    int extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi) {
+        return timed(kStBorder, [&] { return launch_extend_border(p, stride, w, h, x_lo, x_hi, y_lo, y_hi, st); });
     }
-    int hpel(const HpelArgs &a) { return launch_hpel(a, st); }
-    int me_lowres(const MeLowArgs &a) { return launch_me_lowres(a, st); }
-    int me_refine(const MeRefArgs &a) { return launch_me_refine(a, st); }
-    int encode_inter(const EncMbArgs &a) { return launch_encode_inter(a, st); }
-    int encode_intra(const IntraArgs &a) { return launch_encode_intra(a, st); }
+    int lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi) {
+        return timed(kStLowres, [&] { return launch_lowres(src, sstride, x_lo, x_hi - 1, y_lo, y_hi - 1, d0, nullptr, nullptr, nullptr, dstride, lx_lo, lx_hi, ly_lo, ly_hi, st); });
+    }
+    int hpel(const HpelArgs &a) { return timed(kStHpel, [&] { return launch_hpel(a, st); }); }
+    int me_lowres(const MeLowArgs &a) { return timed(kStMeLowres, [&] { return launch_me_lowres(a, st); }); }
+    int me_refine(const MeRefArgs &a) { return timed(kStMeRefine, [&] { return launch_me_refine(a, st); }); }
+    int encode_inter(const EncMbArgs &a) { return timed(kStEncInter, [&] { return launch_encode_inter(a, st); }); }
+    int encode_intra(const IntraArgs &a) { return timed(kStEncIntra, [&] { return launch_encode_intra(a, st); }); }
     int download(void *dst, const void *src, size_t n) { GVC_CUDA(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, st)); return 0; }
     int copy_plane(uint8_t *dst, int dpitch, const uint8_t *src, int spitch, int w, int h) {
         GVC_CUDA(cudaMemcpy2DAsync(dst, dpitch, src, spitch, w, h, cudaMemcpyDeviceToHost, st));
@@ -80,7 +117,7 @@ int issue_segment(gvc_encoder *e, const uint8_t *d_frames, int n) {
     dst.plane[0] = cur.y + ps.oy; dst.plane[1] = cur.u + ps.oc; dst.plane[2] = cur.v + ps.oc;
     dst.stride[0] = g.sy; dst.stride[1] = dst.stride[2] = g.sc;
     dst.frame_stride[0] = ps.y; dst.frame_stride[1] = dst.frame_stride[2] = ps.c;
-    if ((rc = gvc_resize_frames_device(e->plan, &src, &dst, n, e->ops.st))) return rc;
+    if ((rc = e->ops.timed(kStResize, [&] { return gvc_resize_frames_device(e->plan, &src, &dst, n, e->ops.st); }))) return rc;
     if ((rc = e->seg->encode_device(n))) return rc;
     e->n_last = n;
     e->pending = true;
@@ -165,6 +202,23 @@ int gvc_encoder_sync(gvc_encoder *e) {
     if (rc) return rc;
     if (!e) { set_error("encoder is NULL"); return GVC_ERR_INVALID_ARG; }
     GVC_CUDA(cudaStreamSynchronize(e->ops.st));
+    return GVC_OK;
+}
+
+int gvc_encoder_set_timing(gvc_encoder *e, int on) {
+    if (!e) { set_error("encoder is NULL"); return GVC_ERR_INVALID_ARG; }
+    e->ops.tm.on = on != 0;
+    e->ops.tm.reset();
+    return GVC_OK;
+}
+
+int gvc_encoder_stage_times(gvc_encoder *e, double *ms8, int *launches8) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!e || !ms8 || !launches8) { set_error("gvc_encoder_stage_times: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    GVC_CUDA(cudaStreamSynchronize(e->ops.st));
+    e->ops.tm.collect();
+    for (int i = 0; i < kStCount; ++i) { ms8[i] = e->ops.tm.ms[i]; launches8[i] = e->ops.tm.launches[i]; }
     return GVC_OK;
 }
 

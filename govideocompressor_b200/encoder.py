@@ -34,6 +34,8 @@ def _bind(lib):
     lib.gvc_encoder_recon.argtypes = [vp, vp, ctypes.c_size_t]
     lib.gvc_encoder_stats.argtypes = [vp, vp, ci]
     lib.gvc_encoder_write_mp4.argtypes = [vp, ctypes.c_char_p]
+    lib.gvc_encoder_set_timing.argtypes = [vp, ci]
+    lib.gvc_encoder_stage_times.argtypes = [vp, vp, vp]
     lib.gvc_transcode_file.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
     lib._enc_bound = True
 
@@ -108,6 +110,16 @@ class Encoder:
         st = np.zeros((self.n_last, 4), np.int32)
         _lib.check(self._lib.gvc_encoder_stats(self._h, ctypes.c_void_p(st.ctypes.data), self.n_last), "gvc_encoder_stats")
         return st
+
+    STAGES = ("resize", "border", "lowres", "hpel", "me_lowres", "me_refine", "encode_inter", "encode_intra")
+
+    def set_timing(self, on=True):
+        _lib.check(self._lib.gvc_encoder_set_timing(self._h, int(on)), "gvc_encoder_set_timing")
+
+    def stage_times(self):
+        ms, n = (ctypes.c_double * 8)(), (ctypes.c_int * 8)()
+        _lib.check(self._lib.gvc_encoder_stage_times(self._h, ms, n), "gvc_encoder_stage_times")
+        return {s: (ms[i], n[i]) for i, s in enumerate(self.STAGES)}
 
     def write_mp4(self, path):
         _lib.check(self._lib.gvc_encoder_write_mp4(self._h, os.fsencode(path)), "gvc_encoder_write_mp4")
