@@ -1,10 +1,11 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the segment compress hot path (BASELINE.json: 1080p->720p H.264 frames/sec).
 
-A "step" is one pass of the hot path over one segment of the cfg2 workload (10 s 1080p30 clip split into 8 segments
-=> 38 pictures of 1920x1080 I420): resize to 1280x720 (bicubic), then the H.264 encode kernels (IDR + 37 P pictures:
-lowres, motion search, motion compensation + transform/quant/reconstruction, border extension, half-sample planes).
-One process per GPU; with N GPUs every rank encodes its own segment (segments share nothing: weak scaling, no
+A "step" is one pass of the hot path over the cfg2 workload on one GPU: the 10 s 1080p30 clip split into 8 segments of 38
+pictures (1920x1080 I420), all 8 in flight on the GPU at once (one encoder object and CUDA stream per segment, the way 8
+reference workers would share a box): resize to 1280x720 (bicubic), then the H.264 encode kernels (IDR + 37 P pictures
+per segment: lowres, motion search, motion compensation + transform/quant/reconstruction, border extension, half-sample
+planes).  One process per GPU; with N GPUs every rank encodes its own clip (segments share nothing: weak scaling, no
 collective on the data path).
 
   value   pictures/s over all ranks, source pictures resident in HBM, every GPU stage, CUDA events on the encoder's stream
@@ -29,14 +30,15 @@ sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 
 SW, SH, DW, DH = 1920, 1080, 1280, 720
 SEG_FRAMES = 38                      # ceil(300 pictures / 8 segments)
+NSEG = 8                             # segments of the clip, all in flight on one GPU
 CRF = 23
-NBUF = 3                             # rotate source segments (3 x 118 MB) so no step finds its input in the 126 MB L2
 NMB = (DW // 16) * (DH // 16)
 METRIC = "1080p->720p H.264 frames/sec"
-CONFIG = {"workload": "cfg2: 10 s 1080p30 synthetic clip in 8 segments, one 38-picture segment per GPU per step, "
-                      "1920x1080 -> 1280x720 bicubic + H.264 (IDR+P, crf 23, me_range 16)",
-          "segment_frames": SEG_FRAMES, "crf": CRF, "l2": "source segments rotate over %d buffers (354 MB > L2)" % NBUF,
-          "parallelism": "segment-per-GPU, no collective"}
+CONFIG = {"workload": "cfg2: 10 s 1080p30 synthetic clip in 8 segments of 38 pictures, the whole clip per GPU per step (8 segments "
+                      "in flight), 1920x1080 -> 1280x720 bicubic + H.264 (IDR+P, crf 23, me_range 16)",
+          "segment_frames": SEG_FRAMES, "segments_per_step": NSEG, "crf": CRF,
+          "l2": "inputs larger than L2: 8 source segments = 945 MB per step, each read once",
+          "parallelism": "clip-per-GPU (8 independent segments each), no collective"}
 # ALGORITHMIC bytes per launch (SURVEY.md 8(d) formulas at the coded size 1280x720; DESIGN.md "Measurement")
 WH = DW * DH
 ALGO_BYTES = {"resize": int(1.5 * (SW * SH + WH)) * SEG_FRAMES,     # one launch covers the segment
@@ -160,6 +162,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gvc", choices=["gvc", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch kernels one by one instead of replaying CUDA graphs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -187,58 +190,72 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     gvc.init(local)
-    enc = gvc.Encoder(SW, SH, DW, DH, fps=(30, 1), crf=CRF, merange=16)
-    fb = enc.frame_bytes()
+    cores = os.cpu_count() or 1
+    encs = [gvc.Encoder(SW, SH, DW, DH, fps=(30, 1), crf=CRF, merange=16, host_threads=max(1, cores // NSEG),
+                        disable_graph=args.no_graph) for _ in range(NSEG)]
+    fb = encs[0].frame_bytes()
 
     seg0 = synth_segment(rank)
-    host_src = [torch.from_numpy(seg0 if b == 0 else np.roll(seg0, 7 * b, axis=0)).pin_memory() for b in range(NBUF)]
+    host_src = [torch.from_numpy(seg0 if b == 0 else np.roll(seg0, 5 * b, axis=0)).pin_memory() for b in range(NSEG)]
     dev_src = [h.cuda() for h in host_src]
-    ext = torch.cuda.ExternalStream(enc.stream_handle())
+    from concurrent.futures import ThreadPoolExecutor
+    pool = ThreadPoolExecutor(NSEG)                  # one issuing thread per segment (ctypes releases the GIL)
 
     def barrier():
         torch.cuda.synchronize()
-        enc.sync()
+        for e in encs:
+            e.sync()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident timing: every GPU stage of the path -----------------------------------
+    def step_device():
+        list(pool.map(lambda k: encs[k].encode_device(dev_src[k].data_ptr(), SEG_FRAMES), range(NSEG)))
+
+    def step_host():
+        list(pool.map(lambda k: encs[k].encode_host_discard(host_src[k].data_ptr(), SEG_FRAMES), range(NSEG)))
+
+    # ---- device-resident timing: every GPU stage of the path, 8 segments in flight ---------------
     for i in range(args.warmup):
-        enc.encode_device(dev_src[i % NBUF].data_ptr(), SEG_FRAMES)
-    enc.sync()
-    enc.set_timing(True)
+        step_device()
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(ext)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(NSEG)]
+    exts = [torch.cuda.ExternalStream(e.stream_handle()) for e in encs]
+    t0 = time.perf_counter()
+    for k in range(NSEG):
+        ev[k][0].record(exts[k])
     for i in range(args.steps):
-        enc.encode_device(dev_src[i % NBUF].data_ptr(), SEG_FRAMES)
-    e1.record(ext)
+        step_device()
+    for k in range(NSEG):
+        ev[k][1].record(exts[k])
     barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop()
-    ms_total = e0.elapsed_time(e1)
+    # device time of the step = the slowest stream's span (all streams start together); wall clock is reported beside it
+    ms_total = max(ev[k][0].elapsed_time(ev[k][1]) for k in range(NSEG))
+    from govideocompressor_b200 import farm
+    ms_total = farm.max_over_ranks(ms_total, "cuda")
+    value = world * NSEG * SEG_FRAMES * args.steps / (ms_total * 1e-3)
+
+    # ---- stage pass: one segment alone on the GPU, per-kernel CUDA events (roofline figures) -------
+    enc = encs[0]
+    enc.set_timing(True)
+    for i in range(args.steps):
+        enc.encode_device(dev_src[i % NSEG].data_ptr(), SEG_FRAMES)
     stages = enc.stage_times()
     enc.set_timing(False)
-    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
-    value = world * SEG_FRAMES * args.steps / (ms_total * 1e-3)
 
-    # ---- end to end through the C ABI: host pictures in, H.264 stream out ------------------------
-    for i in range(2):
-        enc.encode_host_discard(host_src[i % NBUF].data_ptr(), SEG_FRAMES)
+    # ---- end to end through the C ABI: host pictures in, H.264 streams out, 8 segments in flight ---
+    step_host()
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        enc.encode_host_discard(host_src[i % NBUF].data_ptr(), SEG_FRAMES)
+        step_host()
     e2e_s = time.perf_counter() - t0
-    stream_bytes = int(enc.stats()[:, 3].sum())                  # the step's result as read on the host
-    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e = world * SEG_FRAMES * args.steps / float(t.item())
+    stream_bytes = int(sum(e.stats()[:, 3].sum() for e in encs))   # the step's result as read on the host
+    e2e = world * NSEG * SEG_FRAMES * args.steps / farm.max_over_ranks(e2e_s, "cuda")
 
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -253,15 +270,15 @@ def main():
                 continue
             avg = ms / n
             b = ALGO_BYTES.get(name)
-            table[name] = {"launches_per_step": n / args.steps, "ms_per_step": ms / args.steps, "avg_launch_ms": avg,
+            table[name] = {"launches_per_segment": n / args.steps, "ms_per_segment": ms / args.steps, "avg_launch_ms": avg,
                            "share_of_kernel_time": None, "algorithmic_bytes_per_launch": b,
                            "achieved_gbs": (b / (avg * 1e-3) / 1e9) if b else None}
-        ktotal = sum(s["ms_per_step"] for s in table.values())
+        ktotal = sum(s["ms_per_segment"] for s in table.values())
         for s in table.values():
-            s["share_of_kernel_time"] = s["ms_per_step"] / ktotal
+            s["share_of_kernel_time"] = s["ms_per_segment"] / ktotal
             if s["achieved_gbs"] is not None:
                 s["frac_of_peak"] = s["achieved_gbs"] / peak
-        dom = max(table, key=lambda k: table[k]["ms_per_step"])
+        dom = max(table, key=lambda k: table[k]["ms_per_segment"])
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
@@ -270,20 +287,23 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": CONFIG,
-                "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": SEG_FRAMES * fb,
-                        "d2h_bytes_per_step": SEG_FRAMES * NMB * (26 * 16 * 2 + 4 + 24) + NMB,
-                        "stream_bytes_per_step": stream_bytes, "host_threads": os.cpu_count()},
-                "gpu_launches": launches, "clocks": clocks,
+                "wall_ms_per_step": wall_ms / args.steps,
+                "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": NSEG * SEG_FRAMES * fb,
+                        "d2h_bytes_per_step": NSEG * (SEG_FRAMES * NMB * (26 * 16 * 2 + 4 + 24) + NMB),
+                        "stream_bytes_per_step": stream_bytes, "host_threads": cores},
+                "gpu_launches": launches * NSEG, "clocks": clocks,
                 "roofline": {"kernel": dom, "bound": "hbm", "achieved": d["achieved_gbs"], "peak": peak, "unit": "GB/s",
                              "frac": (d["achieved_gbs"] / peak) if d["achieved_gbs"] else None, "traffic": traffic,
                              "peak_source": peak_src, "algorithmic_bytes_per_launch": d["algorithmic_bytes_per_launch"],
                              "launch_ms_avg": d["avg_launch_ms"], "share_of_step": d["share_of_kernel_time"],
-                             "note": "dominant kernel of the step by accumulated CUDA-event time; all stages in 'stages'"},
+                             "note": "dominant kernel by accumulated CUDA-event time in the stage pass (one segment alone on the GPU, "
+                                     "individual launches); the timed region replays the same kernels from CUDA graphs, 8 streams"},
                 "stages": table}
         if cpu:
             line["cpu_baseline"] = cpu
         print(json.dumps(line))
-    enc.close()
+    for e in encs:
+        e.close()
     if world > 1:
         dist.destroy_process_group()
 

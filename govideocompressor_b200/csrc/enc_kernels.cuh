@@ -74,6 +74,20 @@ GVC_HD void extend_border_px(uint8_t *p, int stride, int w, int h, int x, int y)
     p[(long long)y * stride + x] = p[(long long)iclamp(y, 0, h - 1) * stride + iclamp(x, 0, w - 1)];
 }
 
+// Y, U and V planes of n equally laid out pictures in one launch (blockIdx.z = picture*3 + plane)
+struct BorderBatchArgs {
+    uint8_t *p[3];
+    int stride[3], w[3], h[3], x_lo[3], x_hi[3], y_lo[3], y_hi[3];
+    unsigned long long frame_stride[3];
+    int n_frames;
+};
+struct LowresBatchArgs {
+    const uint8_t *src; uint8_t *dst;
+    int sstride, dstride, x_lo, x_hi, y_lo, y_hi, lx_lo, lx_hi, ly_lo, ly_hi;   // x_hi / y_hi inclusive maxima of readable source coordinates
+    unsigned long long sframe, dframe;
+    int n_frames;
+};
+
 // ------------------------------------------------------------------ K3 lowres ------------------
 // x264 frame_init_lowres_core on the border-extended frame; source coordinates clamp to [lo, hi].
 GVC_HD int avg4(int a, int b, int c, int d) { return (((a + b + 1) >> 1) + ((c + d + 1) >> 1) + 1) >> 1; }

@@ -21,6 +21,19 @@ __global__ void __launch_bounds__(256) lowres_kernel(const uint8_t *src, int sst
     if (lx < lx_hi && ly < ly_hi) lowres_px(src, sstride, x_lo, x_hi, y_lo, y_hi, d0, dh, dv, dc, dstride, lx, ly);
 }
 
+__global__ void __launch_bounds__(256) extend_border_batch_kernel(const __grid_constant__ BorderBatchArgs a) {
+    const int f = blockIdx.z / 3, k = blockIdx.z - 3 * f;
+    const int x = a.x_lo[k] + blockIdx.x * 256 + threadIdx.x, y = a.y_lo[k] + blockIdx.y;
+    if (x < a.x_hi[k] && y < a.y_hi[k]) extend_border_px(a.p[k] + (size_t)f * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], x, y);
+}
+
+__global__ void __launch_bounds__(256) lowres_batch_kernel(const __grid_constant__ LowresBatchArgs a) {
+    const int lx = a.lx_lo + blockIdx.x * 256 + threadIdx.x, ly = a.ly_lo + blockIdx.y;
+    if (lx < a.lx_hi && ly < a.ly_hi)
+        lowres_px(a.src + (size_t)blockIdx.z * a.sframe, a.sstride, a.x_lo, a.x_hi, a.y_lo, a.y_hi, a.dst + (size_t)blockIdx.z * a.dframe,
+                  nullptr, nullptr, nullptr, a.dstride, lx, ly);
+}
+
 __global__ void __launch_bounds__(kHpThreads) hpel_kernel(const __grid_constant__ HpelArgs a) {
     __shared__ HpelSmem sm;
     const int x0 = a.x_lo + blockIdx.x * kHpTileW, y0 = a.y_lo + blockIdx.y * kHpTileH;
@@ -119,6 +132,28 @@ int launch_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo,
     lowres_kernel<<<dim3((lx_hi - lx_lo + 255) / 256, ly_hi - ly_lo), 256, 0, st>>>(src, sstride, x_lo, x_hi, y_lo, y_hi, d0, dh, dv, dc,
                                                                                     dstride, lx_lo, lx_hi, ly_lo, ly_hi);
     GVC_CUDA(cudaGetLastError());
+    return GVC_OK;
+}
+int launch_extend_border_batch(const BorderBatchArgs &a, cudaStream_t st) {
+    if (a.n_frames < 1) return GVC_OK;
+    for (int f0 = 0; f0 < a.n_frames; f0 += 16384) {     // gridDim.z <= 65535
+        BorderBatchArgs b = a;
+        b.n_frames = a.n_frames - f0 < 16384 ? a.n_frames - f0 : 16384;
+        for (int k = 0; k < 3; ++k) b.p[k] = a.p[k] + (size_t)f0 * a.frame_stride[k];
+        extend_border_batch_kernel<<<dim3((a.x_hi[0] - a.x_lo[0] + 255) / 256, a.y_hi[0] - a.y_lo[0], b.n_frames * 3), 256, 0, st>>>(b);
+        GVC_CUDA(cudaGetLastError());
+    }
+    return GVC_OK;
+}
+int launch_lowres_batch(const LowresBatchArgs &a, cudaStream_t st) {
+    if (a.n_frames < 1 || a.lx_hi <= a.lx_lo || a.ly_hi <= a.ly_lo) return GVC_OK;
+    for (int f0 = 0; f0 < a.n_frames; f0 += 32768) {
+        LowresBatchArgs b = a;
+        b.n_frames = a.n_frames - f0 < 32768 ? a.n_frames - f0 : 32768;
+        b.src = a.src + (size_t)f0 * a.sframe; b.dst = a.dst + (size_t)f0 * a.dframe;
+        lowres_batch_kernel<<<dim3((a.lx_hi - a.lx_lo + 255) / 256, a.ly_hi - a.ly_lo, b.n_frames), 256, 0, st>>>(b);
+        GVC_CUDA(cudaGetLastError());
+    }
     return GVC_OK;
 }
 int launch_hpel(const HpelArgs &a, cudaStream_t st) {

@@ -62,12 +62,11 @@ struct CudaOps {
     template <class F> int timed(int stage, F f) { tm.begin(stage, st); const int rc = f(); tm.end(st); return rc; }
     void *alloc(size_t n) { void *p = nullptr; return cudaMalloc(&p, n + 64) == cudaSuccess ? p : nullptr; }
     void  release(void *p) { cudaFree(p); }
-    int extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi) {
-        return timed(kStBorder, [&] { return launch_extend_border(p, stride, w, h, x_lo, x_hi, y_lo, y_hi, st); });
-    }
-    int lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi) {
-        return timed(kStLowres, [&] { return launch_lowres(src, sstride, x_lo, x_hi - 1, y_lo, y_hi - 1, d0, nullptr, nullptr, nullptr, dstride, lx_lo, lx_hi, ly_lo, ly_hi, st); });
-    }
+    void *alloc_host(size_t n) { void *p = nullptr; return cudaHostAlloc(&p, n + 64, cudaHostAllocDefault) == cudaSuccess ? p : nullptr; }
+    void  release_host(void *p) { cudaFreeHost(p); }
+    int upload(void *dst, const void *src, size_t n) { GVC_CUDA(cudaMemcpy(dst, src, n, cudaMemcpyHostToDevice)); return 0; }
+    int extend_border3(const BorderBatchArgs &a) { return timed(kStBorder, [&] { return launch_extend_border_batch(a, st); }); }
+    int lowres_batch(const LowresBatchArgs &a) { return timed(kStLowres, [&] { return launch_lowres_batch(a, st); }); }
     int hpel(const HpelArgs &a) { return timed(kStHpel, [&] { return launch_hpel(a, st); }); }
     int me_lowres(const MeLowArgs &a) { return timed(kStMeLowres, [&] { return launch_me_lowres(a, st); }); }
     int me_refine(const MeRefArgs &a) { return timed(kStMeRefine, [&] { return launch_me_refine(a, st); }); }
@@ -94,6 +93,10 @@ struct gvc_encoder {
     int                n_last = 0;
     bool               pending = false;
     double             ms_kernels = 0, ms_entropy = 0;
+    // the per-picture kernel chain of a segment (everything after the resize) captured once and replayed
+    cudaGraph_t        graph = nullptr;
+    cudaGraphExec_t    graph_exec = nullptr;
+    int                graph_n = 0;
 };
 
 namespace {
@@ -118,7 +121,26 @@ int issue_segment(gvc_encoder *e, const uint8_t *d_frames, int n) {
     dst.stride[0] = g.sy; dst.stride[1] = dst.stride[2] = g.sc;
     dst.frame_stride[0] = ps.y; dst.frame_stride[1] = dst.frame_stride[2] = ps.c;
     if ((rc = e->ops.timed(kStResize, [&] { return gvc_resize_frames_device(e->plan, &src, &dst, n, e->ops.st); }))) return rc;
-    if ((rc = e->seg->encode_device(n))) return rc;
+    e->seg->begin_segment(n);
+    const bool use_graph = !e->cfg.disable_graph && !e->cfg.keep_recon && !e->ops.tm.on;
+    if (!use_graph) {
+        if ((rc = e->seg->encode_device(n))) return rc;
+    } else {
+        if (!e->graph_exec || e->graph_n != n) {       // ~12 launches per picture: capture once per segment length
+            if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+            if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
+            GVC_CUDA(cudaStreamBeginCapture(e->ops.st, cudaStreamCaptureModeThreadLocal));
+            rc = e->seg->encode_device(n);
+            cudaError_t ce = cudaStreamEndCapture(e->ops.st, &e->graph);
+            if (rc) return rc;
+            if (ce != cudaSuccess) { set_error("stream capture failed: %s", cudaGetErrorString(ce)); return GVC_ERR_CUDA; }
+            GVC_CUDA(cudaGraphInstantiate(&e->graph_exec, e->graph, 0));
+            e->graph_n = n;
+        } else {
+            e->seg->set_frame_count(n);
+        }
+        GVC_CUDA(cudaGraphLaunch(e->graph_exec, e->ops.st));
+    }
     e->n_last = n;
     e->pending = true;
     return GVC_OK;
@@ -183,6 +205,8 @@ void gvc_encoder_destroy(gvc_encoder *e) {
     if (!e) return;
     if (gvc::initialised()) cudaSetDevice(gvc::current_device());
     if (e->ops.st) cudaStreamSynchronize(e->ops.st);
+    if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
+    if (e->graph) cudaGraphDestroy(e->graph);
     delete e->seg;
     if (e->plan) gvc_resize_plan_destroy(e->plan);
     if (e->d_src) cudaFree(e->d_src);

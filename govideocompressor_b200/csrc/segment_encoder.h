@@ -54,9 +54,9 @@ struct SegmentOutput {
 };
 
 // Ops concept (all calls asynchronous and in order; sync() waits for everything issued so far):
-//   void *alloc(size_t bytes);  void release(void *p);
-//   int extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi);
-//   int lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi);
+//   void *alloc(size_t bytes);  void release(void *p);   void *alloc_host(size_t bytes);  void release_host(void *p);   // pinned
+//   int upload(void *dev_dst, const void *host_src, size_t bytes);
+//   int extend_border3(const BorderBatchArgs &a);   int lowres_batch(const LowresBatchArgs &a);
 //   int hpel(const HpelArgs &a);  int me_lowres(const MeLowArgs &a);  int me_refine(const MeRefArgs &a);
 //   int encode_inter(const EncMbArgs &a);  int encode_intra(const IntraArgs &a);
 //   int download(void *host_dst, const void *dev_src, size_t bytes);
@@ -94,29 +94,46 @@ public:
         d_modes_  = static_cast<uint8_t *>(ops_.alloc(nmb));
         d_lowmv_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * 2 * nmb));
         d_prog_   = static_cast<int *>(ops_.alloc(sizeof(int) * g_.mbh));
-        bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_coefs_ && d_nz_ && d_motion_ && d_modes_ && d_lowmv_ && d_prog_;
+        d_one_    = static_cast<int *>(ops_.alloc(sizeof(int)));
+        h_coefs_  = static_cast<int16_t *>(ops_.alloc_host(sizeof(int16_t) * kMbCoefs * nmb * n_frames));
+        h_nz_     = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * nmb * n_frames));
+        h_motion_ = static_cast<MbMotion *>(ops_.alloc_host(sizeof(MbMotion) * nmb * n_frames));
+        h_modes_  = static_cast<uint8_t *>(ops_.alloc_host(nmb));
+        h_done_   = static_cast<int *>(ops_.alloc_host(sizeof(int) * n_frames));
+        bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_coefs_ && d_nz_ && d_motion_ && d_modes_ && d_lowmv_ && d_prog_ && d_one_ &&
+                  h_coefs_ && h_nz_ && h_motion_ && h_modes_ && h_done_;
         for (int i = 0; i < 2; ++i) {
             for (int k = 0; k < 4; ++k) ok = ok && rec_y_[i][k];
             ok = ok && rec_u_[i] && rec_v_[i] && rec_low_[i];
         }
         if (!ok) { free_all(); return GVC_ERR_NOMEM; }
+        const int one = 1;
+        if (ops_.upload(d_one_, &one, sizeof(int))) { free_all(); return GVC_ERR_CUDA; }
         cap_ = n_frames;
         return 0;
     }
     CurFrames cur_frames() const { return cur_; }
+    void set_frame_count(int n) { n_ = n; }   // when the kernels of an n-picture segment are replayed from a captured graph
 
-    // Issues every kernel of the segment (pictures 0..n-1 of cur_frames()).  Nothing is waited for.
+    // Host-side reset of the per-picture arrival flags; call before issuing (or replaying) a segment's kernels.
+    void begin_segment(int n) {
+        for (int f = 0; f < n; ++f) __atomic_store_n(&h_done_[f], 0, __ATOMIC_RELEASE);
+    }
+
+    // Issues every kernel of the segment (pictures 0..n-1 of cur_frames()) and, behind each picture's encode kernel, the
+    // copies of its macroblock records to pinned host memory plus an arrival flag.  Nothing is waited for.
     int encode_device(int n) {
         int rc;
-        const int P = kEncPad, Pc = kEncPad / 2;
+        const int P = kEncPad;
         const int lw = g_.w16 / 2, lh = g_.h16 / 2;
         n_ = n;
-        for (int f = 0; f < n; ++f) {      // source pictures: extend the picture edges into the padding, build lowres
-            uint8_t *y = cur_.y + ps_.y * f + ps_.oy, *u = cur_.u + ps_.c * f + ps_.oc, *v = cur_.v + ps_.c * f + ps_.oc;
-            if ((rc = ops_.extend_border(y, g_.sy, cfg_.w, cfg_.h, -P, g_.w16 + P, -P, g_.h16 + P))) return rc;
-            if ((rc = ops_.extend_border(u, g_.sc, (cfg_.w + 1) / 2, (cfg_.h + 1) / 2, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
-            if ((rc = ops_.extend_border(v, g_.sc, (cfg_.w + 1) / 2, (cfg_.h + 1) / 2, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
-            if ((rc = ops_.lowres(y, g_.sy, -P, g_.w16 + P, -P, g_.h16 + P, cur_low_ + ps_.l * f + ps_.ol, g_.sl, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
+        {   // source pictures: extend the picture edges into the padding and build lowres, one launch each for the segment
+            BorderBatchArgs b = border_args(cur_.y + ps_.oy, cur_.u + ps_.oc, cur_.v + ps_.oc, cfg_.w, cfg_.h);
+            b.frame_stride[0] = ps_.y; b.frame_stride[1] = b.frame_stride[2] = ps_.c; b.n_frames = n;
+            if ((rc = ops_.extend_border3(b))) return rc;
+            LowresBatchArgs l = lowres_args(cur_.y + ps_.oy, cur_low_ + ps_.ol);
+            l.sframe = ps_.y; l.dframe = ps_.l; l.n_frames = n;
+            if ((rc = ops_.lowres_batch(l))) return rc;
         }
         const size_t nmb = size_t(g_.mbw) * g_.mbh;
         if (cfg_.keep_recon) recon_store_.assign(size_t(g_.w16) * g_.h16 * 3 / 2 * n, 0);
@@ -151,6 +168,14 @@ public:
                 e.motion = d_motion_ + nmb * f; e.coefs = d_coefs_ + size_t(kMbCoefs) * nmb * f; e.nzmask = d_nz_ + nmb * f;
                 if ((rc = ops_.encode_inter(e))) return rc;
             }
+            {   // records of this picture -> pinned host memory, then its arrival flag (copies complete in issue order)
+                const size_t co = size_t(kMbCoefs) * nmb * f;
+                if ((rc = ops_.download(h_coefs_ + co, d_coefs_ + co, sizeof(int16_t) * kMbCoefs * nmb))) return rc;
+                if ((rc = ops_.download(h_nz_ + nmb * f, d_nz_ + nmb * f, sizeof(uint32_t) * nmb))) return rc;
+                if (f == 0) { if ((rc = ops_.download(h_modes_, d_modes_, nmb))) return rc; }
+                else if ((rc = ops_.download(h_motion_ + nmb * f, d_motion_ + nmb * f, sizeof(MbMotion) * nmb))) return rc;
+                if ((rc = ops_.download(h_done_ + f, d_one_, sizeof(int)))) return rc;
+            }
             if (cfg_.keep_recon) {
                 uint8_t *dst = recon_store_.data() + size_t(g_.w16) * g_.h16 * 3 / 2 * f;
                 if ((rc = ops_.copy_plane(dst, g_.w16, ry, g_.sy, g_.w16, g_.h16))) return rc;
@@ -158,33 +183,24 @@ public:
                 if ((rc = ops_.copy_plane(dst + size_t(g_.w16) * g_.h16 * 5 / 4, lw, rv, g_.sc, lw, lh))) return rc;
             }
             if (f + 1 < n) {                // the reconstruction becomes the next picture's reference
-                if ((rc = ops_.extend_border(ry, g_.sy, g_.w16, g_.h16, -P, g_.w16 + P, -P, g_.h16 + P))) return rc;
-                if ((rc = ops_.extend_border(ru, g_.sc, lw, lh, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
-                if ((rc = ops_.extend_border(rv, g_.sc, lw, lh, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
+                BorderBatchArgs b = border_args(ry, ru, rv, g_.w16, g_.h16);
+                if ((rc = ops_.extend_border3(b))) return rc;
                 HpelArgs ha;
                 ha.src = ry; ha.dh = rec_y_[r][1] + ps_.oy; ha.dv = rec_y_[r][2] + ps_.oy; ha.dc = rec_y_[r][3] + ps_.oy;
                 ha.stride = g_.sy; ha.x_lo = -P; ha.x_hi = g_.w16 + P; ha.y_lo = -P; ha.y_hi = g_.h16 + P;
                 if ((rc = ops_.hpel(ha))) return rc;
-                if ((rc = ops_.lowres(ry, g_.sy, -P, g_.w16 + P, -P, g_.h16 + P, rec_low_[r] + ps_.ol, g_.sl, -Pc, lw + Pc, -Pc, lh + Pc))) return rc;
+                if ((rc = ops_.lowres_batch(lowres_args(ry, rec_low_[r] + ps_.ol)))) return rc;
             }
         }
         return 0;
     }
 
-    // Copies the per-macroblock records to the host, waits, and writes the elementary stream.
+    // Entropy-codes the pictures as their records arrive (worker threads wait on the arrival flags while the GPU is still
+    // working on later pictures), then waits for the stream.
     int finish(SegmentOutput &out) {
-        const size_t nmb = size_t(g_.mbw) * g_.mbh;
-        int rc;
-        h_coefs_.resize(size_t(kMbCoefs) * nmb * n_);
-        h_nz_.resize(nmb * n_);
-        h_motion_.resize(nmb * n_);
-        h_modes_.resize(nmb);
-        if ((rc = ops_.download(h_coefs_.data(), d_coefs_, sizeof(int16_t) * h_coefs_.size()))) return rc;
-        if ((rc = ops_.download(h_nz_.data(), d_nz_, sizeof(uint32_t) * h_nz_.size()))) return rc;
-        if ((rc = ops_.download(h_motion_.data(), d_motion_, sizeof(MbMotion) * h_motion_.size()))) return rc;
-        if ((rc = ops_.download(h_modes_.data(), d_modes_, nmb))) return rc;
-        if ((rc = ops_.sync())) return rc;
         write_stream(out);
+        const int rc = ops_.sync();
+        if (rc) return rc;
         if (cfg_.keep_recon) out.recon.swap(recon_store_);
         return 0;
     }
@@ -210,13 +226,14 @@ public:
         std::vector<std::vector<uint8_t>> au(n_);
         out.stats.assign(n_, SliceStats());
         auto code_picture = [&](int f) {
+            while (__atomic_load_n(&h_done_[f], __ATOMIC_ACQUIRE) == 0) std::this_thread::yield();
             PictureData pic;
             pic.mbw = g_.mbw; pic.mbh = g_.mbh; pic.idr = f == 0; pic.frame_num = f; pic.idr_pic_id = idr_pic_id_;
             pic.qp = f == 0 ? cfg_.qp_i : cfg_.qp_p;
-            pic.coefs = h_coefs_.data() + size_t(kMbCoefs) * nmb * f;
-            pic.nzmask = h_nz_.data() + nmb * f;
-            pic.motion = h_motion_.data() + nmb * f;
-            pic.modes = h_modes_.data();
+            pic.coefs = h_coefs_ + size_t(kMbCoefs) * nmb * f;
+            pic.nzmask = h_nz_ + nmb * f;
+            pic.motion = h_motion_ + nmb * f;
+            pic.modes = h_modes_;
             BitWriter bw;
             write_slice(bw, pic, &out.stats[f]);
             if (f == 0) {   // parameter sets travel in-band with the IDR too (Annex B extraction stays decodable)
@@ -246,6 +263,28 @@ public:
     }
 
 private:
+    // Y/U/V planes at sample (0,0) of one picture whose valid area is w x h luma samples
+    BorderBatchArgs border_args(uint8_t *y, uint8_t *u, uint8_t *v, int w, int h) const {
+        const int P = kEncPad, Pc = kEncPad / 2, lw = g_.w16 / 2, lh = g_.h16 / 2;
+        BorderBatchArgs b;
+        b.p[0] = y; b.p[1] = u; b.p[2] = v;
+        b.stride[0] = g_.sy; b.stride[1] = b.stride[2] = g_.sc;
+        b.w[0] = w; b.h[0] = h; b.w[1] = b.w[2] = (w + 1) / 2; b.h[1] = b.h[2] = (h + 1) / 2;
+        b.x_lo[0] = -P; b.x_hi[0] = g_.w16 + P; b.y_lo[0] = -P; b.y_hi[0] = g_.h16 + P;
+        for (int k = 1; k < 3; ++k) { b.x_lo[k] = -Pc; b.x_hi[k] = lw + Pc; b.y_lo[k] = -Pc; b.y_hi[k] = lh + Pc; }
+        b.frame_stride[0] = b.frame_stride[1] = b.frame_stride[2] = 0;
+        b.n_frames = 1;
+        return b;
+    }
+    LowresBatchArgs lowres_args(const uint8_t *y, uint8_t *low) const {
+        const int P = kEncPad, Pc = kEncPad / 2, lw = g_.w16 / 2, lh = g_.h16 / 2;
+        LowresBatchArgs l;
+        l.src = y; l.dst = low; l.sstride = g_.sy; l.dstride = g_.sl;
+        l.x_lo = -P; l.x_hi = g_.w16 + P - 1; l.y_lo = -P; l.y_hi = g_.h16 + P - 1;
+        l.lx_lo = -Pc; l.lx_hi = lw + Pc; l.ly_lo = -Pc; l.ly_hi = lh + Pc;
+        l.sframe = l.dframe = 0; l.n_frames = 1;
+        return l;
+    }
     void free_all() {
         auto rel = [&](auto *&p) { if (p) ops_.release(p); p = nullptr; };
         rel(cur_.y); rel(cur_.u); rel(cur_.v); rel(cur_low_);
@@ -253,7 +292,9 @@ private:
             for (int k = 0; k < 4; ++k) rel(rec_y_[i][k]);
             rel(rec_u_[i]); rel(rec_v_[i]); rel(rec_low_[i]);
         }
-        rel(d_coefs_); rel(d_nz_); rel(d_motion_); rel(d_modes_); rel(d_lowmv_); rel(d_prog_);
+        rel(d_coefs_); rel(d_nz_); rel(d_motion_); rel(d_modes_); rel(d_lowmv_); rel(d_prog_); rel(d_one_);
+        auto relh = [&](auto *&p) { if (p) ops_.release_host(p); p = nullptr; };
+        relh(h_coefs_); relh(h_nz_); relh(h_motion_); relh(h_modes_); relh(h_done_);
         cap_ = 0;
     }
 
@@ -272,10 +313,13 @@ private:
     uint8_t      *d_modes_ = nullptr;
     int16_t      *d_lowmv_ = nullptr;
     int          *d_prog_ = nullptr;
-    std::vector<int16_t>  h_coefs_;
-    std::vector<uint32_t> h_nz_;
-    std::vector<MbMotion> h_motion_;
-    std::vector<uint8_t>  h_modes_, recon_store_;
+    int          *d_one_ = nullptr;
+    int16_t      *h_coefs_ = nullptr;     // pinned host copies of the kernels' records
+    uint32_t     *h_nz_ = nullptr;
+    MbMotion     *h_motion_ = nullptr;
+    uint8_t      *h_modes_ = nullptr;
+    int          *h_done_ = nullptr;      // per picture: set to 1 by the last copy of that picture
+    std::vector<uint8_t> recon_store_;
 };
 
 }  // namespace gvc

@@ -15,7 +15,7 @@ from . import lib as _lib
 class EncoderConfig(ctypes.Structure):
     """struct gvc_encoder_config"""
     _fields_ = [(n, ctypes.c_int) for n in ("src_w", "src_h", "dst_w", "dst_h", "fps_num", "fps_den", "crf", "merange",
-                                            "scale_algo", "keep_recon", "host_threads")]
+                                            "scale_algo", "keep_recon", "host_threads", "disable_graph")]
 
 
 def _bind(lib):
@@ -41,10 +41,11 @@ def _bind(lib):
 
 
 class Encoder:
-    def __init__(self, src_w, src_h, dst_w=0, dst_h=0, fps=(30, 1), crf=23, merange=16, scale_algo=4, keep_recon=False, host_threads=0):
+    def __init__(self, src_w, src_h, dst_w=0, dst_h=0, fps=(30, 1), crf=23, merange=16, scale_algo=4, keep_recon=False, host_threads=0,
+                 disable_graph=False):
         self._lib = _lib.load_library()
         _bind(self._lib)
-        self.cfg = EncoderConfig(src_w, src_h, dst_w, dst_h, fps[0], fps[1], crf, merange, scale_algo, int(keep_recon), host_threads)
+        self.cfg = EncoderConfig(src_w, src_h, dst_w, dst_h, fps[0], fps[1], crf, merange, scale_algo, int(keep_recon), host_threads, int(disable_graph))
         self.src_w, self.src_h = src_w, src_h
         self.dst_w, self.dst_h = dst_w or src_w, dst_h or src_h
         self.w16, self.h16 = (self.dst_w + 15) // 16 * 16, (self.dst_h + 15) // 16 * 16

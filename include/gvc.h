@@ -179,6 +179,7 @@ typedef struct gvc_encoder_config {
     int scale_algo;            /* GVC_SCALE_*, 0 = bicubic */
     int keep_recon;            /* keep the reconstruction of every picture (tests compare it with a decoder) */
     int host_threads;          /* entropy-coding threads, 0 = all host cores */
+    int disable_graph;         /* 1 = launch every kernel individually instead of replaying a captured CUDA graph */
 } gvc_encoder_config;
 
 int  gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg);

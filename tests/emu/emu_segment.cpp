@@ -26,9 +26,19 @@ namespace {
 struct EmuOps {
     void *alloc(size_t n) { return calloc(1, n + 64); }
     void  release(void *p) { free(p); }
-    int extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi) { emu_extend_border(p, stride, w, h, x_lo, x_hi, y_lo, y_hi); return 0; }
-    int lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, int y_hi, uint8_t *d0, int dstride, int lx_lo, int lx_hi, int ly_lo, int ly_hi) {
-        emu_lowres(src, sstride, x_lo, x_hi, y_lo, y_hi, d0, nullptr, nullptr, nullptr, dstride, lx_lo, lx_hi, ly_lo, ly_hi);
+    void *alloc_host(size_t n) { return calloc(1, n + 64); }
+    void  release_host(void *p) { free(p); }
+    int upload(void *dst, const void *src, size_t n) { memcpy(dst, src, n); return 0; }
+    int extend_border3(const BorderBatchArgs &a) {
+        for (int f = 0; f < a.n_frames; ++f)
+            for (int k = 0; k < 3; ++k)
+                emu_extend_border(a.p[k] + size_t(f) * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], a.x_lo[k], a.x_hi[k], a.y_lo[k], a.y_hi[k]);
+        return 0;
+    }
+    int lowres_batch(const LowresBatchArgs &a) {
+        for (int f = 0; f < a.n_frames; ++f)
+            emu_lowres(a.src + size_t(f) * a.sframe, a.sstride, a.x_lo, a.x_hi + 1, a.y_lo, a.y_hi + 1, a.dst + size_t(f) * a.dframe, nullptr, nullptr,
+                       nullptr, a.dstride, a.lx_lo, a.lx_hi, a.ly_lo, a.ly_hi);
         return 0;
     }
     int hpel(const HpelArgs &a) { emu_hpel(a.src, a.dh, a.dv, a.dc, a.stride, a.x_lo, a.x_hi, a.y_lo, a.y_hi); return 0; }
@@ -70,6 +80,7 @@ int emu_encode_segment(const uint8_t *frames, int n, int w, int h, int fps, int 
             memcpy(cur.v + ps.c * f + ps.oc + size_t(y) * g.sc, src + size_t(w) * h + size_t(cw) * ch + size_t(y) * cw, cw);
         }
     }
+    enc.begin_segment(n);
     int rc = enc.encode_device(n);
     if (rc) return rc;
     SegmentOutput out;
