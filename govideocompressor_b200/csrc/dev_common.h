@@ -5,10 +5,12 @@
 
 #if defined(GVC_EMU)
 #define GVC_HD inline
+#define GVC_HDH inline
 struct gvc_int4 { int x, y, z, w; };
 struct gvc_uint4 { unsigned x, y, z, w; };
 #else
 #define GVC_HD __device__ __forceinline__
+#define GVC_HDH __host__ __device__ __forceinline__   // also callable from host launch code
 typedef int4  gvc_int4;
 typedef uint4 gvc_uint4;
 #endif

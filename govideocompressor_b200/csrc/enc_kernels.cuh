@@ -81,6 +81,32 @@ struct BorderBatchArgs {
     unsigned long long frame_stride[3];
     int n_frames;
 };
+// Work decomposition of the batched border kernel: piece `id` (256 samples) of plane k.  Pieces enumerate first the rows
+// that lie completely outside the picture (full padded width each), then, for the picture rows, the strips left and right
+// of the picture: nothing covers the picture interior.  Returns false when the (id, tid) pair maps to no sample.
+GVC_HDH int border_pieces(const BorderBatchArgs &a, int k) {
+    const int full_w = a.x_hi[k] - a.x_lo[k], strip_w = full_w - a.w[k];
+    return ((a.y_hi[k] - a.y_lo[k]) - a.h[k]) * ((full_w + 255) >> 8) + a.h[k] * ((strip_w + 255) >> 8);
+}
+GVC_HD bool border_piece_xy(const BorderBatchArgs &a, int k, int id, int tid, int &x, int &y) {
+    const int full_w = a.x_hi[k] - a.x_lo[k], strip_w = full_w - a.w[k];
+    const int segs_a = (full_w + 255) >> 8, segs_b = (strip_w + 255) >> 8;
+    const int rows_out = (a.y_hi[k] - a.y_lo[k]) - a.h[k], n_a = rows_out * segs_a;
+    if (id < n_a) {
+        const int r = id / segs_a, t = (id - r * segs_a) * 256 + tid;
+        y = r < -a.y_lo[k] ? a.y_lo[k] + r : a.h[k] + (r + a.y_lo[k]);
+        x = a.x_lo[k] + t;
+    } else {
+        id -= n_a;
+        if (segs_b == 0) return false;
+        y = id / segs_b;
+        if (y >= a.h[k]) return false;
+        const int t = (id - y * segs_b) * 256 + tid;
+        x = t < -a.x_lo[k] ? a.x_lo[k] + t : a.w[k] + (t + a.x_lo[k]);
+    }
+    return x < a.x_hi[k] && y < a.y_hi[k];
+}
+
 struct LowresBatchArgs {
     const uint8_t *src; uint8_t *dst;
     int sstride, dstride, x_lo, x_hi, y_lo, y_hi, lx_lo, lx_hi, ly_lo, ly_hi;   // x_hi / y_hi inclusive maxima of readable source coordinates

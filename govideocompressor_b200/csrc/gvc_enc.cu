@@ -22,9 +22,10 @@ __global__ void __launch_bounds__(256) lowres_kernel(const uint8_t *src, int sst
 }
 
 __global__ void __launch_bounds__(256) extend_border_batch_kernel(const __grid_constant__ BorderBatchArgs a) {
-    const int f = blockIdx.z / 3, k = blockIdx.z - 3 * f;
-    const int x = a.x_lo[k] + blockIdx.x * 256 + threadIdx.x, y = a.y_lo[k] + blockIdx.y;
-    if (x < a.x_hi[k] && y < a.y_hi[k]) extend_border_px(a.p[k] + (size_t)f * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], x, y);
+    const int f = blockIdx.y / 3, k = blockIdx.y - 3 * f;
+    int x, y;
+    if (border_piece_xy(a, k, blockIdx.x, threadIdx.x, x, y))
+        extend_border_px(a.p[k] + (size_t)f * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], x, y);
 }
 
 __global__ void __launch_bounds__(256) lowres_batch_kernel(const __grid_constant__ LowresBatchArgs a) {
@@ -136,11 +137,13 @@ int launch_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo,
 }
 int launch_extend_border_batch(const BorderBatchArgs &a, cudaStream_t st) {
     if (a.n_frames < 1) return GVC_OK;
-    for (int f0 = 0; f0 < a.n_frames; f0 += 16384) {     // gridDim.z <= 65535
+    int pieces = 1;                                   // the largest plane decides the grid; smaller planes' extra blocks exit
+    for (int k = 0; k < 3; ++k) pieces = border_pieces(a, k) > pieces ? border_pieces(a, k) : pieces;
+    for (int f0 = 0; f0 < a.n_frames; f0 += 16384) {     // gridDim.y <= 65535
         BorderBatchArgs b = a;
         b.n_frames = a.n_frames - f0 < 16384 ? a.n_frames - f0 : 16384;
         for (int k = 0; k < 3; ++k) b.p[k] = a.p[k] + (size_t)f0 * a.frame_stride[k];
-        extend_border_batch_kernel<<<dim3((a.x_hi[0] - a.x_lo[0] + 255) / 256, a.y_hi[0] - a.y_lo[0], b.n_frames * 3), 256, 0, st>>>(b);
+        extend_border_batch_kernel<<<dim3(pieces, b.n_frames * 3), 256, 0, st>>>(b);
         GVC_CUDA(cudaGetLastError());
     }
     return GVC_OK;

@@ -11,28 +11,11 @@
 namespace gvc {
 
 // ------------------------------------------------------------------------------- bit writer ----
-void BitWriter::put(uint32_t value, int bits) {
-    if (bits <= 0) return;
-    if (bits < 32) value &= (1u << bits) - 1u;
-    acc_ = (acc_ << bits) | value;
-    n_ += bits;
-    while (n_ >= 8) {
-        buf_.push_back(uint8_t(acc_ >> (n_ - 8)));
-        n_ -= 8;
-    }
-    acc_ &= (uint64_t(1) << n_) - 1;
-}
-void BitWriter::ue(uint32_t v) {
-    const uint64_t code = uint64_t(v) + 1;
-    int len = 0;
-    while ((code >> len) > 1) ++len;          // len = floor(log2(code))
-    put(0, len);
-    put(uint32_t(code), len + 1);
-}
-void BitWriter::se(int32_t v) { ue(v > 0 ? uint32_t(2 * v - 1) : uint32_t(-2 * int64_t(v))); }
 void BitWriter::rbsp_trailing() {
     put(1, 1);
-    if (n_) put(0, 8 - n_);
+    if (n_ & 7) put(0, 8 - (n_ & 7));
+    out_.assign(buf_.begin(), buf_.begin() + len_);
+    for (int k = n_ - 8; k >= 0; k -= 8) out_.push_back(uint8_t(acc_ >> k));
 }
 
 void append_nal(std::vector<uint8_t> &out, int nal_ref_idc, int nal_unit_type, const std::vector<uint8_t> &rbsp, bool annexb) {
@@ -321,25 +304,42 @@ void set_mv(PicState &s, int bx, int by, int w, int h, Mv v) {
         }
 }
 
+inline void write_empty_block(BitWriter &bw, int nC) {     // coeff_token with TotalCoeff = 0
+    if (nC == -1) { bw.put(kChromaDcTokenBits[0], kChromaDcTokenLen[0]); return; }
+    const int tab = nC < 2 ? 0 : nC < 4 ? 1 : nC < 8 ? 2 : 3;
+    bw.put(kCoeffTokenBits[tab][0], kCoeffTokenLen[tab][0]);
+}
+
 // residual( ) of one macroblock; updates the nnz maps.  i16: Intra16x16 (DC block + 15-coefficient AC blocks).
-void write_mb_residual(BitWriter &bw, PicState &s, const int16_t *co, int mx, int my, int cbp, bool i16) {
-    if (i16) write_residual(bw, co + 25 * 16, 16, luma_nc(s, 4 * mx, 4 * my));
+// nz is the kernels' per-block "has a nonzero level" mask: empty blocks are coded without touching their coefficients.
+void write_mb_residual(BitWriter &bw, PicState &s, const int16_t *co, int mx, int my, int cbp, bool i16, uint32_t nz) {
+    if (i16) {
+        if (nz & (1u << 26)) write_residual(bw, co + 25 * 16, 16, luma_nc(s, 4 * mx, 4 * my));
+        else write_empty_block(bw, luma_nc(s, 4 * mx, 4 * my));
+    }
     for (int blk = 0; blk < 16; ++blk) {
         const int r = kBlkToRaster[blk], bx = 4 * mx + (r & 3), by = 4 * my + (r >> 2);
         int       total = 0;
         if (cbp & (1 << (blk >> 2))) {
-            if (i16) total = write_residual(bw, co + r * 16 + 1, 15, luma_nc(s, bx, by));
-            else     total = write_residual(bw, co + r * 16, 16, luma_nc(s, bx, by));
+            if (!(nz & (1u << r))) write_empty_block(bw, luma_nc(s, bx, by));
+            else if (i16) total = write_residual(bw, co + r * 16 + 1, 15, luma_nc(s, bx, by));
+            else          total = write_residual(bw, co + r * 16, 16, luma_nc(s, bx, by));
         }
         s.nnz_y[by * s.w4 + bx] = uint8_t(total);
     }
     if (cbp & 0x30)
-        for (int p = 0; p < 2; ++p) write_residual(bw, co + 24 * 16 + 4 * p, 4, -1);
+        for (int p = 0; p < 2; ++p) {
+            if (nz & (1u << (24 + p))) write_residual(bw, co + 24 * 16 + 4 * p, 4, -1);
+            else write_empty_block(bw, -1);
+        }
     for (int p = 0; p < 2; ++p)
         for (int b = 0; b < 4; ++b) {
             const int bx = 2 * mx + (b & 1), by = 2 * my + (b >> 1);
             int       total = 0;
-            if (cbp & 0x20) total = write_residual(bw, co + (16 + 4 * p + b) * 16 + 1, 15, chroma_nc(s, p, bx, by));
+            if (cbp & 0x20) {
+                if (nz & (1u << (16 + 4 * p + b))) total = write_residual(bw, co + (16 + 4 * p + b) * 16 + 1, 15, chroma_nc(s, p, bx, by));
+                else write_empty_block(bw, chroma_nc(s, p, bx, by));
+            }
             s.nnz_c[p][by * 2 * s.mbw + bx] = uint8_t(total);
         }
 }
@@ -405,7 +405,7 @@ void write_slice(BitWriter &bw, const PictureData &pic, SliceStats *stats) {
                 bw.ue(uint32_t(1 + pic.modes[mb] + 4 * (cbp >> 4) + ((cbp & 15) ? 12 : 0)));   // mb_type I_16x16_<mode>_<cbpc>_<cbpl>
                 bw.ue(0);                  // intra_chroma_pred_mode: DC
                 bw.se(0);                  // mb_qp_delta
-                write_mb_residual(bw, s, co, mx, my, cbp, true);
+                write_mb_residual(bw, s, co, mx, my, cbp, true, nz);
                 ++st.intra;
                 continue;
             }
@@ -450,7 +450,7 @@ void write_slice(BitWriter &bw, const PictureData &pic, SliceStats *stats) {
             bw.ue(kCbpCode.inter[cbp]);    // coded_block_pattern me(v)
             if (cbp) {
                 bw.se(0);                  // mb_qp_delta
-                write_mb_residual(bw, s, co, mx, my, cbp, false);
+                write_mb_residual(bw, s, co, mx, my, cbp, false, nz);
             } else {
                 clear_mb_nnz(s, mx, my);
             }

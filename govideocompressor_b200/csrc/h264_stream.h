@@ -18,14 +18,33 @@ namespace gvc {
 
 class BitWriter {
 public:
-    void put(uint32_t value, int bits);          // MSB first, bits <= 32
-    void ue(uint32_t v);
-    void se(int32_t v);
-    void rbsp_trailing();                        // stop bit + zero alignment
-    size_t bit_count() const { return buf_.size() * 8 + n_; }
-    const std::vector<uint8_t> &bytes() const { return buf_; }   // valid after rbsp_trailing()
+    BitWriter() { buf_.resize(4096); }
+    void put(uint32_t value, int bits) {         // MSB first, 0 <= bits <= 32
+        if (bits < 32) value &= (1u << bits) - 1u;
+        acc_ = (acc_ << bits) | value;
+        n_ += bits;
+        if (n_ >= 32) {
+            if (len_ + 4 > buf_.size()) buf_.resize(buf_.size() * 2);
+            const uint32_t w = uint32_t(acc_ >> (n_ - 32));
+            uint8_t *p = buf_.data() + len_;
+            p[0] = uint8_t(w >> 24); p[1] = uint8_t(w >> 16); p[2] = uint8_t(w >> 8); p[3] = uint8_t(w);
+            len_ += 4;
+            n_ -= 32;
+        }
+    }
+    void ue(uint32_t v) {
+        const uint64_t code = uint64_t(v) + 1;
+        const int len = 63 - __builtin_clzll(code);     // floor(log2(code))
+        put(0, len);
+        put(uint32_t(code), len + 1);
+    }
+    void se(int32_t v) { ue(v > 0 ? uint32_t(2 * v - 1) : uint32_t(-2 * int64_t(v))); }
+    void rbsp_trailing();                        // stop bit + zero alignment; finalises bytes()
+    size_t bit_count() const { return len_ * 8 + n_; }
+    const std::vector<uint8_t> &bytes() const { return out_; }   // valid after rbsp_trailing()
 private:
-    std::vector<uint8_t> buf_;
+    std::vector<uint8_t> buf_, out_;
+    size_t   len_ = 0;
     uint64_t acc_ = 0;
     int      n_   = 0;
 };

@@ -29,10 +29,14 @@ struct EmuOps {
     void *alloc_host(size_t n) { return calloc(1, n + 64); }
     void  release_host(void *p) { free(p); }
     int upload(void *dst, const void *src, size_t n) { memcpy(dst, src, n); return 0; }
-    int extend_border3(const BorderBatchArgs &a) {
+    int extend_border3(const BorderBatchArgs &a) {      // same (piece, thread) decomposition as the CUDA kernel
         for (int f = 0; f < a.n_frames; ++f)
             for (int k = 0; k < 3; ++k)
-                emu_extend_border(a.p[k] + size_t(f) * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], a.x_lo[k], a.x_hi[k], a.y_lo[k], a.y_hi[k]);
+                for (int id = 0; id < border_pieces(a, k) + 3; ++id)
+                    for (int tid = 0; tid < 256; ++tid) {
+                        int x, y;
+                        if (border_piece_xy(a, k, id, tid, x, y)) extend_border_px(a.p[k] + size_t(f) * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], x, y);
+                    }
         return 0;
     }
     int lowres_batch(const LowresBatchArgs &a) {
