@@ -34,7 +34,7 @@ NSEG = 8                             # segments of the clip, all in flight on on
 CRF = 23
 NMB = (DW // 16) * (DH // 16)
 METRIC = "1080p->720p H.264 frames/sec"
-CONFIG = {"workload": "cfg2: 10 s 1080p30 synthetic clip in 8 segments of 38 pictures, the whole clip per GPU per step (8 segments "
+CONFIG = {"workload": "cfg2: 10 s 1080p30 synthetic testsrc-style clip (SURVEY.md 8d) in 8 segments of 38 pictures, the whole clip per GPU per step (8 segments "
                       "in flight), 1920x1080 -> 1280x720 bicubic + H.264 (IDR+P, crf 23, me_range 16)",
           "segment_frames": SEG_FRAMES, "segments_per_step": NSEG, "crf": CRF,
           "l2": "inputs larger than L2: 8 source segments = 945 MB per step, each read once",
@@ -46,9 +46,14 @@ ALGO_BYTES = {"resize": int(1.5 * (SW * SH + WH)) * SEG_FRAMES,     # one launch
               "encode_inter": int(7.5 * WH), "encode_intra": 6 * WH, "border": None}
 
 
-def synth_segment(seed):
-    import seq_util
-    return seq_util.moving_sequence(SW, SH, SEG_FRAMES, seed=seed, noise=2)
+def synth_segment(seed, n=SEG_FRAMES):
+    """SURVEY.md 8(d) synthetic testsrc-style clip (colour bars, translating gradient, orbiting box, LCG-noise patch), I420."""
+    import numpy as np
+    from util_inputs import make_frame
+    seg = np.empty((n, SW * SH * 3 // 2), np.uint8)
+    for f in range(n):
+        seg[f] = np.concatenate([p.reshape(-1) for p in make_frame(SW, SH, "yuv420p", "testsrc", seed, t=f)])
+    return seg
 
 
 class ClockSampler:
@@ -105,8 +110,7 @@ def _cpu_worker(args):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
     import oracle_segment
-    import seq_util
-    frames = seq_util.moving_sequence(SW, SH, n, seed=seed, noise=2)
+    frames = synth_segment(seed, n)
     try:
         import sws_ref
         sws_ref.load()

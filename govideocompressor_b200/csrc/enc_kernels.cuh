@@ -23,7 +23,7 @@ GVC_HD unsigned ld_u32_any(const uint8_t *p) {   // 4 bytes at any address (read
 #else
     const unsigned long long a = (unsigned long long)p;
     const unsigned *w = reinterpret_cast<const unsigned *>(a & ~3ull);
-    return __funnelshift_r(w[0], w[1], (unsigned)(a & 3) * 8);
+    return __funnelshift_r(__ldg(w), __ldg(w + 1), (unsigned)(a & 3) * 8);   // read-only planes: ld.global.nc
 #endif
 }
 GVC_HD void ld_u64_any(const uint8_t *p, unsigned &lo, unsigned &hi) {   // 8 bytes at any address
@@ -32,7 +32,7 @@ GVC_HD void ld_u64_any(const uint8_t *p, unsigned &lo, unsigned &hi) {   // 8 by
 #else
     const unsigned long long a = (unsigned long long)p;
     const unsigned *w = reinterpret_cast<const unsigned *>(a & ~3ull);
-    const unsigned  s = (unsigned)(a & 3) * 8, w0 = w[0], w1 = w[1], w2 = w[2];
+    const unsigned  s = (unsigned)(a & 3) * 8, w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
     lo = __funnelshift_r(w0, w1, s); hi = __funnelshift_r(w1, w2, s);
 #endif
 }
@@ -51,6 +51,23 @@ GVC_HD int ld_u8_cg(const uint8_t *p) {
     return *p;
 #else
     return (int)__ldcg(p);
+#endif
+}
+
+GVC_HD unsigned avg_u8x4(unsigned a, unsigned b) {   // per byte (a + b + 1) >> 1
+#if defined(GVC_EMU)
+    unsigned r = 0;
+    for (int i = 0; i < 4; ++i) r |= ((((a >> (8 * i)) & 255) + ((b >> (8 * i)) & 255) + 1) >> 1) << (8 * i);
+    return r;
+#else
+    return __vavgu4(a, b);
+#endif
+}
+GVC_HD int byte_of(unsigned w, int i) {
+#if defined(GVC_EMU)
+    return (int)((w >> (8 * i)) & 255);
+#else
+    return (int)__byte_perm(w, 0, 0x4440 + i);
 #endif
 }
 
@@ -396,34 +413,53 @@ GVC_HD void me_lane_block(int lane, int &P, int &ox, int &oy) {
     if (lane < 16) { P = 0; ox = 4 * (lane & 3); oy = 4 * (lane >> 2); }
     else { const int l = lane - 16, k = l >> 2, j = l & 3; P = 1 + k; ox = 8 * (k & 1) + 4 * (j & 1); oy = 8 * (k >> 1) + 4 * (j >> 1); }
 }
-// sub-pel candidate ci (-1 = the centre itself) at `step`: each lane's 4x4 Hadamard sum -> sm.part
-GVC_HD void me_ref_satd(int lane, const MeRefArgs &a, int mx, int my, int ci, int step, MeRefSmem &sm) {
-    int P, ox, oy, dx = 0, dy = 0;
-    me_lane_block(lane, P, ox, oy);
-    if (ci >= 0) sq8(ci, dx, dy);
-    const int mvx = sm.center[P][0] + dx * step, mvy = sm.center[P][1] + dy * step;
-    const int x = 16 * mx + ox, y = 16 * my + oy;
-    int pred[16], d[16];
-    mc_luma_4x4(a.ref, a.stride, x, y, mvx, mvy, pred);
+// Per-lane state that stays in registers across the 17 sub-pel candidates: the lane's 4x4 source block, its offset in
+// the planes and the predictor (the emulation harness keeps one record per lane).
+struct MeLane {
+    int       P, ox, oy, px, py;
+    long long base;      // (16*my + oy) * stride + 16*mx + ox
+    int       cur[16];
+};
+GVC_HD void me_lane_init(int lane, const MeRefArgs &a, int mx, int my, MeLane &L) {
+    me_lane_block(lane, L.P, L.ox, L.oy);
+    me_mvp(a, mx, my, L.px, L.py);
+    L.base = (long long)(16 * my + L.oy) * a.stride + 16 * mx + L.ox;
+    const uint8_t *c = a.cur + L.base;
     for (int j = 0; j < 4; ++j) {
-        const unsigned c = ld_u32_any(a.cur + (long long)(y + j) * a.stride + x);
-        for (int i = 0; i < 4; ++i) d[j * 4 + i] = (int)((c >> (8 * i)) & 255) - pred[j * 4 + i];
+        const unsigned w = ld_u32_any(c + (long long)j * a.stride);
+        for (int i = 0; i < 4; ++i) L.cur[j * 4 + i] = byte_of(w, i);
+    }
+}
+// sub-pel candidate ci (-1 = the centre itself) at `step`: each lane's 4x4 Hadamard sum -> sm.part
+GVC_HD void me_ref_satd(int lane, const MeRefArgs &a, const MeLane &L, int ci, int step, MeRefSmem &sm) {
+    int dx = 0, dy = 0;
+    if (ci >= 0) sq8(ci, dx, dy);
+    const int mvx = sm.center[L.P][0] + dx * step, mvy = sm.center[L.P][1] + dy * step;
+    const int fx = mvx & 3, fy = mvy & 3, q = fy * 4 + fx;
+    const long long off = L.base + (long long)(mvy >> 2) * a.stride + (mvx >> 2);
+    const int s0 = (int)((kQpelRef0 >> (2 * q)) & 3), s1 = (int)((kQpelRef1 >> (2 * q)) & 3);
+    const uint8_t *p1 = (s0 == 0 ? a.ref.y : s0 == 1 ? a.ref.hh : s0 == 2 ? a.ref.hv : a.ref.hc) + off + (fy == 3 ? a.stride : 0);
+    const uint8_t *p2 = (s1 == 0 ? a.ref.y : s1 == 1 ? a.ref.hh : s1 == 2 ? a.ref.hv : a.ref.hc) + off + (fx == 3 ? 1 : 0);
+    const bool two = (q & 5) != 0;
+    int d[16];
+    for (int j = 0; j < 4; ++j) {
+        unsigned w = ld_u32_any(p1);
+        p1 += a.stride;
+        if (two) { w = avg_u8x4(w, ld_u32_any(p2)); p2 += a.stride; }
+        for (int i = 0; i < 4; ++i) d[j * 4 + i] = L.cur[j * 4 + i] - byte_of(w, i);
     }
     sm.part[lane] = hadamard4_abs(d) >> 1;
 }
-GVC_HD void me_ref_update(int lane, const MeRefArgs &a, int mx, int my, int ci, int step, MeRefSmem &sm) {
+GVC_HD void me_ref_update(int lane, const MeRefArgs &a, const MeLane &L, int ci, int step, MeRefSmem &sm) {
     const bool leader = lane == 0 || (lane >= 16 && ((lane - 16) & 3) == 0);
     if (!leader) return;
-    int P, ox, oy, dx = 0, dy = 0;
-    me_lane_block(lane, P, ox, oy);
+    int dx = 0, dy = 0;
     if (ci >= 0) sq8(ci, dx, dy);
-    const int mvx = sm.center[P][0] + dx * step, mvy = sm.center[P][1] + dy * step;
-    int px, py;
-    me_mvp(a, mx, my, px, py);
+    const int P = L.P, mvx = sm.center[P][0] + dx * step, mvy = sm.center[P][1] + dy * step;
     int total = 0;
     const int n = P == 0 ? 16 : 4;
     for (int i = 0; i < n; ++i) total += sm.part[lane + i];
-    const int cost = total + a.lambda * mv_bits(mvx, mvy, px, py);
+    const int cost = total + a.lambda * mv_bits(mvx, mvy, L.px, L.py);
     if (cost < sm.best_cost[P]) { sm.best_cost[P] = cost; sm.best_mv[P][0] = mvx; sm.best_mv[P][1] = mvy; }
     if (ci == 7) { sm.center[P][0] = sm.best_mv[P][0]; sm.center[P][1] = sm.best_mv[P][1]; }
 }

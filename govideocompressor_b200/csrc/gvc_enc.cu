@@ -68,12 +68,14 @@ __global__ void __launch_bounds__(32 * kMbWarps) me_refine_kernel(const __grid_c
     me_ref_int(lane, a, mx, my, sm);
     __syncwarp();
     me_ref_pick(lane, a, mx, my, sm);
+    MeLane L;
+    me_lane_init(lane, a, mx, my, L);
     __syncwarp();
     for (int step = 2; step >= 1; --step)
         for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
-            me_ref_satd(lane, a, mx, my, ci, step, sm);
+            me_ref_satd(lane, a, L, ci, step, sm);
             __syncwarp();
-            me_ref_update(lane, a, mx, my, ci, step, sm);
+            me_ref_update(lane, a, L, ci, step, sm);
             __syncwarp();
         }
     me_ref_out(lane, a, mx, my, sm);

@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <new>
 #include <string>
 #include <thread>
@@ -17,6 +18,7 @@
 #include "enc_launch.h"
 #include "ff_args.h"
 #include "gvc_common.h"
+#include "media_input.h"
 #include "mp4_mux.h"
 #include "segment_encoder.h"
 
@@ -310,23 +312,6 @@ int gvc_encoder_write_mp4(gvc_encoder *e, const char *path) {
 }
 
 // ---------------------------------------------------------------------------------------------- transcode
-static bool read_y4m_header(FILE *f, int &w, int &h, int &fn, int &fd, std::string &err) {
-    char line[256];
-    if (!fgets(line, sizeof(line), f) || strncmp(line, "YUV4MPEG2", 9) != 0) { err = "not a YUV4MPEG2 stream"; return false; }
-    w = h = 0; fn = 30; fd = 1;
-    bool c420 = true;
-    for (char *t = strtok(line + 9, " \n"); t; t = strtok(nullptr, " \n")) {
-        if (t[0] == 'W') w = atoi(t + 1);
-        else if (t[0] == 'H') h = atoi(t + 1);
-        else if (t[0] == 'F') { if (sscanf(t + 1, "%d:%d", &fn, &fd) != 2) { fn = 30; fd = 1; } }
-        else if (t[0] == 'C') c420 = strncmp(t + 1, "420", 3) == 0 && strstr(t, "p1") == nullptr;
-        else if (t[0] == 'I' && t[1] != 'p' && t[1] != '?') { err = "interlaced input is not supported"; return false; }
-    }
-    if (!c420) { err = "only 8-bit 4:2:0 input is supported"; return false; }
-    if (w < 16 || h < 16) { err = "bad picture size in the Y4M header"; return false; }
-    return true;
-}
-
 int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char *out_path, char **log_out, size_t *log_len) {
     std::string log;
     auto finish = [&](int rc) {
@@ -346,30 +331,26 @@ int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char 
     TranscodeOptions opt;
     std::string      err;
     if ((rc = parse_ffmpeg_args(ffmpeg_args, opt, err))) { set_error("%s", err.c_str()); return finish(rc); }
-    FILE *f = fopen(in_path, "rb");
-    if (!f) { set_error("%s: No such file or directory", in_path); return finish(GVC_ERR_IO); }
-    int w, h, fn, fd;
-    if (!read_y4m_header(f, w, h, fn, fd, err)) {
-        fclose(f);
-        set_error("%s: %s (this build reads YUV4MPEG2 segments; H.264-in-MP4 input needs a host demuxer/decoder)", in_path, err.c_str());
-        return finish(GVC_ERR_UNSUPPORTED);
-    }
+    std::unique_ptr<FrameSource> srcf = open_frame_source(in_path, err);
+    if (!srcf) { set_error("%s: %s", in_path, err.c_str()); return finish(err == "No such file or directory" ? GVC_ERR_IO : GVC_ERR_UNSUPPORTED); }
+    int w = srcf->w, h = srcf->h, fn = srcf->fps_num, fd = srcf->fps_den;
+    if ((w | h) & 1) { set_error("%s: odd picture size %dx%d is not supported", in_path, w, h); return finish(GVC_ERR_UNSUPPORTED); }
     if (opt.fps_num > 0) { fn = opt.fps_num; fd = opt.fps_den; }
     gvc_encoder_config c;
     memset(&c, 0, sizeof(c));
     c.src_w = w; c.src_h = h; c.dst_w = opt.dst_w ? opt.dst_w : w; c.dst_h = opt.dst_h ? opt.dst_h : h;
     c.fps_num = fn; c.fps_den = fd; c.crf = opt.crf; c.merange = opt.merange; c.scale_algo = opt.scale_algo;
     gvc_encoder *e = nullptr;
-    if ((rc = gvc_encoder_create(&e, &c))) { fclose(f); return finish(rc); }
+    if ((rc = gvc_encoder_create(&e, &c))) return finish(rc);
     char buf[512];
-    snprintf(buf, sizeof(buf), "Input #0, yuv4mpegpipe, from '%s': %dx%d, %d/%d fps\nOutput #0, mp4, to '%s': h264 (gvc sm_100a), yuv420p, %dx%d, crf %d\n",
-             in_path, w, h, fn, fd, out_path, c.dst_w, c.dst_h, c.crf);
+    snprintf(buf, sizeof(buf), "Input #0, %s, from '%s': %dx%d, %d/%d fps\nOutput #0, mp4, to '%s': h264 (gvc sm_100a), yuv420p, %dx%d, crf %d\n",
+             srcf->format_name.c_str(), in_path, w, h, fn, fd, out_path, c.dst_w, c.dst_h, c.crf);
     log += buf;
 
     const size_t fb = i420_bytes(w, h);
     const int    gop = std::max(1, std::min(opt.gop, 250));
     uint8_t     *host = nullptr;
-    if (cudaHostAlloc((void **)&host, fb * gop, cudaHostAllocDefault) != cudaSuccess) { fclose(f); gvc_encoder_destroy(e); set_error("cannot allocate pinned staging"); return finish(GVC_ERR_NOMEM); }
+    if (cudaHostAlloc((void **)&host, fb * gop, cudaHostAllocDefault) != cudaSuccess) { gvc_encoder_destroy(e); set_error("cannot allocate pinned staging"); return finish(GVC_ERR_NOMEM); }
     std::vector<uint8_t>   payload;
     std::vector<Mp4Sample> samples;
     std::vector<uint8_t>   sps, pps;
@@ -378,14 +359,9 @@ int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char 
     const auto t0 = std::chrono::steady_clock::now();
     bool eof = false;
     while (!eof && rc == 0) {
-        int n = 0;
-        while (n < gop) {
-            char fl[128];
-            if (!fgets(fl, sizeof(fl), f)) { eof = true; break; }
-            if (strncmp(fl, "FRAME", 5) != 0) { set_error("%s: damaged Y4M frame header", in_path); rc = GVC_ERR_IO; break; }
-            if (fread(host + fb * n, 1, fb, f) != fb) { set_error("%s: truncated frame %d", in_path, total + n); rc = GVC_ERR_IO; break; }
-            ++n;
-        }
+        const int n = srcf->read(host, gop, err);
+        if (n < 0) { set_error("%s: %s (picture %d)", in_path, err.c_str(), total); rc = GVC_ERR_IO; }
+        if (n < gop) eof = true;
         if (rc || n == 0) break;
         if ((rc = gvc_encoder_encode_host(e, host, n, 0, nullptr, nullptr))) break;
         if (sps.empty()) { sps = e->out.sps_nal; pps = e->out.pps_nal; }
@@ -396,7 +372,6 @@ int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char 
         payload.insert(payload.end(), e->out.payload.begin(), e->out.payload.end());
         total += n;
     }
-    fclose(f);
     cudaFreeHost(host);
     gvc_encoder_destroy(e);
     if (rc == 0 && total == 0) { set_error("%s: no frames", in_path); rc = GVC_ERR_IO; }

@@ -126,8 +126,24 @@ class Encoder:
         _lib.check(self._lib.gvc_encoder_write_mp4(self._h, os.fsencode(path)), "gvc_encoder_write_mp4")
 
 
+def _find_ffmpeg_libs():
+    """MP4/H.264 input is demuxed and decoded on the host by FFmpeg's own libraries, which libgvc loads with dlopen from
+    GVC_FFMPEG_LIBDIR.  When the variable is unset, point it at the build bundled in this image's opencv wheel."""
+    if "GVC_FFMPEG_LIBDIR" in os.environ:
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("cv2")
+        d = os.path.join(os.path.dirname(os.path.dirname(spec.origin)), "opencv_python_headless.libs")
+        if os.path.isdir(d):
+            os.environ["GVC_FFMPEG_LIBDIR"] = d
+    except Exception:
+        pass
+
+
 def transcode_file(in_path, args, out_path):
     """gvc_transcode_file: returns (status, log_text)."""
+    _find_ffmpeg_libs()
     lib = _lib.load_library()
     _bind(lib)
     log, n = ctypes.c_void_p(), ctypes.c_size_t()

@@ -25,10 +25,12 @@ void emu_run_me_refine(const MeRefArgs &a) {
             memset(&sm, 0xAB, sizeof(sm));
             for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) me_ref_pick(l, a, mx, my, sm);
+            MeLane L[32];
+            for (int l = 0; l < 32; ++l) me_lane_init(l, a, mx, my, L[l]);
             for (int step = 2; step >= 1; --step)
                 for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
-                    for (int l = 0; l < 32; ++l) me_ref_satd(l, a, mx, my, ci, step, sm);
-                    for (int l = 0; l < 32; ++l) me_ref_update(l, a, mx, my, ci, step, sm);
+                    for (int l = 0; l < 32; ++l) me_ref_satd(l, a, L[l], ci, step, sm);
+                    for (int l = 0; l < 32; ++l) me_ref_update(l, a, L[l], ci, step, sm);
                 }
             for (int l = 0; l < 32; ++l) me_ref_out(l, a, mx, my, sm);
         }

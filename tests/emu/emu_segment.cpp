@@ -115,3 +115,24 @@ int emu_encode_segment(const uint8_t *frames, int n, int w, int h, int fps, int 
     return 0;
 }
 }
+
+// ---- media input (product code media_input.cpp) exercised on the host -------------------------------------
+#include "../../govideocompressor_b200/csrc/media_input.h"
+extern "C" int emu_read_media(const char *path, uint8_t *dst, size_t cap, int *info /* w, h, fps_num, fps_den, frames */, char *err, int err_cap) {
+    std::string e;
+    auto src = open_frame_source(path, e);
+    if (!src) { snprintf(err, err_cap, "%s", e.c_str()); return -1; }
+    info[0] = src->w; info[1] = src->h; info[2] = src->fps_num; info[3] = src->fps_den;
+    const size_t fb = size_t(src->w) * src->h + 2 * size_t((src->w + 1) / 2) * ((src->h + 1) / 2);
+    int total = 0;
+    for (;;) {
+        const int room = int((cap - fb * total) / fb);
+        if (room <= 0) break;
+        const int n = src->read(dst + fb * total, room < 7 ? room : 7, e);     // odd chunk size: reads span calls
+        if (n < 0) { snprintf(err, err_cap, "%s", e.c_str()); return -2; }
+        if (n == 0) break;
+        total += n;
+    }
+    info[4] = total;
+    return 0;
+}

@@ -78,3 +78,30 @@ def encode_segment(frames, w, h, fps=30, qp_i=20, qp_p=23, merange=16, mp4_path=
                                 annexb.ctypes.data, annexb.size, ctypes.byref(alen), recon.ctypes.data, stats.ctypes.data)
     assert rc == 0, f"emu_encode_segment failed: {rc}"
     return dict(annexb=annexb[: alen.value].tobytes(), recon=recon, stats=stats, w16=w16, h16=h16)
+
+
+def ffmpeg_libdir():
+    """Directory of the FFmpeg shared libraries bundled in the opencv wheel (for GVC_FFMPEG_LIBDIR), or None."""
+    try:
+        import cv2
+        d = os.path.join(os.path.dirname(os.path.dirname(cv2.__file__)), "opencv_python_headless.libs")
+        return d if os.path.isdir(d) else None
+    except Exception:
+        return None
+
+
+def read_media(path, max_frames=64, max_w=1920, max_h=1088):
+    """Product FrameSource (Y4M or libavformat/libavcodec via dlopen) run on the host.  Returns (info dict, frames)."""
+    d = ffmpeg_libdir()
+    if d and "GVC_FFMPEG_LIBDIR" not in os.environ:
+        os.environ["GVC_FFMPEG_LIBDIR"] = d
+    lib = load()
+    buf = np.zeros(max_frames * max_w * max_h * 3 // 2, np.uint8)
+    info = (ctypes.c_int * 5)()
+    err = ctypes.create_string_buffer(256)
+    rc = lib.emu_read_media(os.fsencode(path), ctypes.c_void_p(buf.ctypes.data), ctypes.c_size_t(buf.size), info, err, 256)
+    if rc != 0:
+        raise RuntimeError(err.value.decode())
+    w, h, n = info[0], info[1], info[4]
+    fb = w * h * 3 // 2
+    return dict(w=w, h=h, fps=(info[2], info[3]), frames=n), buf[: n * fb].reshape(n, fb).copy()
