@@ -213,15 +213,17 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step_device():
-        list(pool.map(lambda k: encs[k].encode_device(dev_src[k].data_ptr(), SEG_FRAMES), range(NSEG)))
+    # each segment slot is driven by its own host thread, like 8 worker processes sharing the box: a slot starts its next
+    # segment as soon as its previous one is issued / finished, so copies, kernels and host entropy coding of different
+    # segments overlap (no barrier between steps)
+    def run_device(steps):
+        list(pool.map(lambda k: [encs[k].encode_device(dev_src[k].data_ptr(), SEG_FRAMES) for _ in range(steps)], range(NSEG)))
 
-    def step_host():
-        list(pool.map(lambda k: encs[k].encode_host_discard(host_src[k].data_ptr(), SEG_FRAMES), range(NSEG)))
+    def run_host(steps):
+        list(pool.map(lambda k: [encs[k].encode_host_discard(host_src[k].data_ptr(), SEG_FRAMES) for _ in range(steps)], range(NSEG)))
 
     # ---- device-resident timing: every GPU stage of the path, 8 segments in flight ---------------
-    for i in range(args.warmup):
-        step_device()
+    run_device(args.warmup)
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
@@ -230,8 +232,7 @@ def main():
     t0 = time.perf_counter()
     for k in range(NSEG):
         ev[k][0].record(exts[k])
-    for i in range(args.steps):
-        step_device()
+    run_device(args.steps)
     for k in range(NSEG):
         ev[k][1].record(exts[k])
     barrier()
@@ -252,11 +253,10 @@ def main():
     enc.set_timing(False)
 
     # ---- end to end through the C ABI: host pictures in, H.264 streams out, 8 segments in flight ---
-    step_host()
+    run_host(1)
     barrier()
     t0 = time.perf_counter()
-    for i in range(args.steps):
-        step_host()
+    run_host(args.steps)
     e2e_s = time.perf_counter() - t0
     stream_bytes = int(sum(e.stats()[:, 3].sum() for e in encs))   # the step's result as read on the host
     e2e = world * NSEG * SEG_FRAMES * args.steps / farm.max_over_ranks(e2e_s, "cuda")

@@ -17,7 +17,7 @@
 namespace gvc {
 
 // ------------------------------------------------------------------------------- kernels ------
-template <int NG, int VQ>
+template <int NG, int VT>
 __global__ void __launch_bounds__(kThreads) resize_fused_kernel(const __grid_constant__ ResizeParams P, int s_chunks_max) {
     extern __shared__ uint4 smem[];
     const int            tile = blockIdx.x;
@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(kThreads) resize_fused_kernel(const __grid_con
     __syncthreads();
     resize_phase1<NG>(threadIdx.x, pc, g, S, T);
     __syncthreads();
-    resize_phase2<VQ>(threadIdx.x, pc, pj, dst, g, T);
+    resize_phase2<VT>(threadIdx.x, pc, pj, dst, g, T);
 }
 
 struct GenericJob {
@@ -127,20 +127,19 @@ int upload_tables(gvc_resize_plan *p) {
 }
 
 typedef void (*fused_fn)(const ResizeParams, int);
+template <int NG, int VT>
+struct PickVt {
+    static fused_fn get(int vt) { return vt >= VT ? static_cast<fused_fn>(resize_fused_kernel<NG, VT>) : PickVt<NG, VT - 1>::get(vt); }
+};
 template <int NG>
-fused_fn pick_vq(int vq) {
-    switch (vq) {
-        case 1: return resize_fused_kernel<NG, 1>;
-        case 2: return resize_fused_kernel<NG, 2>;
-        case 3: return resize_fused_kernel<NG, 3>;
-        default: return resize_fused_kernel<NG, 4>;
-    }
-}
-fused_fn pick_fused(int ng, int vq) {
+struct PickVt<NG, 1> {
+    static fused_fn get(int) { return resize_fused_kernel<NG, 1>; }
+};
+fused_fn pick_fused(int ng, int vt) {
     switch (ng) {
-        case 1: return pick_vq<1>(vq);
-        case 2: return pick_vq<2>(vq);
-        default: return pick_vq<3>(vq);
+        case 1: return PickVt<1, kMaxVTaps>::get(vt);
+        case 2: return PickVt<2, kMaxVTaps>::get(vt);
+        default: return PickVt<3, kMaxVTaps>::get(vt);
     }
 }
 
@@ -179,7 +178,7 @@ int launch_device(const gvc_resize_plan *p, const gvc_frames *src, const gvc_fra
         const int lt = p->t.cls[0].tiles_x * p->t.cls[0].tiles_y, ct = p->t.cls[1].tiles_x * p->t.cls[1].tiles_y;
         P.job[0].tile_base = 0; P.job[1].tile_base = lt; P.job[2].tile_base = lt + ct;
         P.tiles_per_frame = lt + 2 * ct;
-        fused_fn fn = pick_fused(p->t.ng, p->t.vq);
+        fused_fn fn = pick_fused(p->t.ng, p->t.vt);
         GVC_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->t.smem_bytes));
         for (int f0 = 0; f0 < n_frames; f0 += 32768) {
             const int nf = std::min(32768, n_frames - f0);

@@ -83,7 +83,12 @@ GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
     const int  total   = kTileRows * chunks;
     const bool aligned = pj.spix == 1 && ((((unsigned long long)src) | (unsigned)pj.sstride) & 15) == 0;
     for (int i = tid; i < total; i += kThreads) {
-        const int r = i / chunks, c = i - r * chunks;
+#if defined(GVC_EMU)
+        const int r = (int)(((unsigned long long)(unsigned)i * (unsigned)pc.s_chunks_magic) >> 32);
+#else
+        const int r = (int)__umulhi((unsigned)i, (unsigned)pc.s_chunks_magic);   // i / chunks without a divide
+#endif
+        const int c = i - r * chunks;
         const int row = g.r0 + r;
         const int col = (g.qa0 << 2) + (c << 4);       // first source sample of this chunk
         gvc_uint4 v;
@@ -109,97 +114,121 @@ GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
 // T layout: [quad (4 output columns)][kTPad source rows][4] int32.
 template <int NG>
 GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, const gvc_uint4 *S, gvc_int4 *T) {
-    const int warp = tid >> 5, lane = tid & 31;
+#if defined(GVC_EMU)
+    const int warp = tid >> 5;
+#else
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // broadcast: lets the compiler treat x / table entries as warp-uniform
+#endif
+    const int lane = tid & 31;
     const int chunks = pc.s_chunks;
     const gvc_int4 *htab = reinterpret_cast<const gvc_int4 *>(pc.htab);
     gvc_uint4 c0[kRowGroups], c1[kRowGroups];
     int       kcur = -2;
-    constexpr int kQuadsPerWarp = kTileW / 4 / kWarps;  // 4
-#pragma unroll 1
-    for (int qi = 0; qi < kQuadsPerWarp; ++qi) {
-        const int xq = (warp * kQuadsPerWarp + qi) * 4;   // tile-relative first column of the quad
-        if (xq >= g.ncols) break;                         // warp-uniform
-        int acc[kRowGroups][4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int      x  = imin(g.x0 + xq + k, pc.dw - 1);
-            const gvc_int4 e0 = htab[(long long)x * 2], e1 = htab[(long long)x * 2 + 1];
-            const int      qrel = e0.x - g.qa0;
-            const int      kc = qrel >> 2, o = qrel & 3, r8 = e0.y;
-            if (kc != kcur) {                              // warp-uniform: slide the two-chunk window
-#pragma unroll
-                for (int rg = 0; rg < kRowGroups; ++rg) {
-                    const gvc_uint4 *row = S + (rg * 32 + lane) * chunks;
-                    c0[rg] = (kc == kcur + 1) ? c1[rg] : row[kc];
-                    c1[rg] = row[kc + 1];
-                }
-                kcur = kc;
-            }
+    constexpr int kColsPerWarp = kTileW / kWarps;       // 16 output columns = 4 quads per warp
+    const int xw = warp * kColsPerWarp;                 // tile-relative first column of this warp
+    if (xw >= g.ncols) return;                          // warp-uniform
+    auto entry = [&](int xi, gvc_int4 &e0, gvc_int4 &e1) {
+        const int x = imin(g.x0 + xw + xi, pc.dw - 1);
+#if defined(GVC_EMU)
+        e0 = htab[(long long)x * 2]; e1 = htab[(long long)x * 2 + 1];
+#else
+        e0 = __ldg(htab + (long long)x * 2); e1 = __ldg(htab + (long long)x * 2 + 1);
+#endif
+    };
+    gvc_int4 n0, n1;
+    entry(0, n0, n1);
+    int acc[kRowGroups][4];
+#pragma unroll 4
+    for (int xi = 0; xi < kColsPerWarp; ++xi) {
+        const gvc_int4 e0 = n0, e1 = n1;
+        if (xi + 1 < kColsPerWarp) entry(xi + 1, n0, n1);   // table entry of the next column: off the critical path
+        const int qrel = e0.x - g.qa0;
+        const int kc = qrel >> 2, o = qrel & 3, r8 = e0.y;
+        if (kc != kcur) {                                  // warp-uniform: slide the two-chunk window
 #pragma unroll
             for (int rg = 0; rg < kRowGroups; ++rg) {
-                unsigned w0, w1, w2, w3;
-                switch (o) {                               // warp-uniform
-                    case 0:  w0 = c0[rg].x; w1 = c0[rg].y; w2 = c0[rg].z; w3 = c0[rg].w; break;
-                    case 1:  w0 = c0[rg].y; w1 = c0[rg].z; w2 = c0[rg].w; w3 = c1[rg].x; break;
-                    case 2:  w0 = c0[rg].z; w1 = c0[rg].w; w2 = c1[rg].x; w3 = c1[rg].y; break;
-                    default: w0 = c0[rg].w; w1 = c1[rg].x; w2 = c1[rg].y; w3 = c1[rg].z; break;
-                }
-                const unsigned u0 = funnel_r(w0, w1, r8);
-                int a = dp2a_lo_su(e0.z, u0, 0);
-                a     = dp2a_hi_su(e0.w, u0, a);
-                if (NG >= 2) {
-                    const unsigned u1 = funnel_r(w1, w2, r8);
-                    a = dp2a_lo_su(e1.x, u1, a);
-                    a = dp2a_hi_su(e1.y, u1, a);
-                }
-                if (NG >= 3) {
-                    const unsigned u2 = funnel_r(w2, w3, r8);
-                    a = dp2a_lo_su(e1.z, u2, a);
-                    a = dp2a_hi_su(e1.w, u2, a);
-                }
-                acc[rg][k] = imin(a >> 7, 32767);
+                const gvc_uint4 *row = S + (rg * 32 + lane) * chunks;
+                c0[rg] = (kc == kcur + 1) ? c1[rg] : row[kc];
+                c1[rg] = row[kc + 1];
             }
+            kcur = kc;
         }
 #pragma unroll
         for (int rg = 0; rg < kRowGroups; ++rg) {
-            gvc_int4 v;
-            v.x = acc[rg][0]; v.y = acc[rg][1]; v.z = acc[rg][2]; v.w = acc[rg][3];
-            T[((xq >> 2) * kTPad) + rg * 32 + lane] = v;
+            unsigned w0, w1, w2, w3;
+            switch (o) {                                   // warp-uniform
+                case 0:  w0 = c0[rg].x; w1 = c0[rg].y; w2 = c0[rg].z; w3 = c0[rg].w; break;
+                case 1:  w0 = c0[rg].y; w1 = c0[rg].z; w2 = c0[rg].w; w3 = c1[rg].x; break;
+                case 2:  w0 = c0[rg].z; w1 = c0[rg].w; w2 = c1[rg].x; w3 = c1[rg].y; break;
+                default: w0 = c0[rg].w; w1 = c1[rg].x; w2 = c1[rg].y; w3 = c1[rg].z; break;
+            }
+            const unsigned u0 = funnel_r(w0, w1, r8);
+            int a = dp2a_lo_su(e0.z, u0, 0);
+            a     = dp2a_hi_su(e0.w, u0, a);
+            if (NG >= 2) {
+                const unsigned u1 = funnel_r(w1, w2, r8);
+                a = dp2a_lo_su(e1.x, u1, a);
+                a = dp2a_hi_su(e1.y, u1, a);
+            }
+            if (NG >= 3) {
+                const unsigned u2 = funnel_r(w2, w3, r8);
+                a = dp2a_lo_su(e1.z, u2, a);
+                a = dp2a_hi_su(e1.w, u2, a);
+            }
+            acc[rg][xi & 3] = imin(a >> 7, 32767);
+        }
+        if ((xi & 3) == 3) {
+#pragma unroll
+            for (int rg = 0; rg < kRowGroups; ++rg) {
+                gvc_int4 v;
+                v.x = acc[rg][0]; v.y = acc[rg][1]; v.z = acc[rg][2]; v.w = acc[rg][3];
+                T[(((xw + xi) >> 2) * kTPad) + rg * 32 + lane] = v;
+            }
         }
     }
 }
 
 // ---------------------------------------------------------------- phase 2: vertical ------------
-template <int VQ>
+// VT = vertical taps of the plan (the larger of the luma / chroma banks; the other bank is zero padded).
+template <int VT>
 GVC_HD void resize_phase2(int tid, const PlaneClassDev &pc, const PlaneJob &pj, uint8_t *dst,
                           const TileGeom &g, const gvc_int4 *T) {
-    const int warp = tid >> 5, lane = tid & 31;
+    constexpr int VQ = (VT + 1 + 3) / 4;             // int4 per vertical table row (vpos + taps)
+#if defined(GVC_EMU)
+    const int warp = tid >> 5;
+#else
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+#endif
+    const int lane = tid & 31;
     const gvc_int4 *vtab = reinterpret_cast<const gvc_int4 *>(pc.vtab);
     const int  xl      = lane * 4;                   // tile-relative column of this lane's 4 pixels
-    const bool active  = xl < g.ncols;
-    const bool store32 = pj.dpix == 1 && ((((unsigned long long)dst) | (unsigned)pj.dstride) & 3) == 0;
+    if (xl >= g.ncols) return;
+    const bool store32 = pj.dpix == 1 && ((((unsigned long long)dst) | (unsigned)pj.dstride) & 3) == 0 && xl + 4 <= g.ncols;
+    const gvc_int4 *colbase = T + lane * kTPad - g.r0;
+    uint8_t *prow = dst + (long long)(g.x0 + xl) * pj.dpix;
 #pragma unroll 1
     for (int y = g.y0 + warp; y < g.y0 + g.nrows; y += kWarps) {
         int cf[4 * VQ];
 #pragma unroll
         for (int i = 0; i < VQ; ++i) {
+#if defined(GVC_EMU)
             const gvc_int4 e = vtab[(long long)y * VQ + i];
+#else
+            const gvc_int4 e = __ldg(vtab + (long long)y * VQ + i);
+#endif
             cf[4 * i] = e.x; cf[4 * i + 1] = e.y; cf[4 * i + 2] = e.z; cf[4 * i + 3] = e.w;
         }
-        if (!active) continue;
-        const gvc_int4 *col = T + lane * kTPad + (cf[0] - g.r0);
+        const gvc_int4 *col = colbase + cf[0];
         int a0 = 64 << 12, a1 = 64 << 12, a2 = 64 << 12, a3 = 64 << 12;
 #pragma unroll
-        for (int j = 0; j < 4 * VQ - 1; ++j) {
-            if (j < pc.vtaps) {                      // uniform
-                const gvc_int4 t = col[j];
-                const int      c = cf[j + 1];
-                a0 += t.x * c; a1 += t.y * c; a2 += t.z * c; a3 += t.w * c;
-            }
+        for (int j = 0; j < VT; ++j) {
+            const gvc_int4 t = col[j];
+            const int      c = cf[j + 1];
+            a0 += t.x * c; a1 += t.y * c; a2 += t.z * c; a3 += t.w * c;
         }
         const int b0 = clip_u8(a0 >> 19), b1 = clip_u8(a1 >> 19), b2 = clip_u8(a2 >> 19), b3 = clip_u8(a3 >> 19);
-        uint8_t  *p  = dst + (long long)y * pj.dstride + (long long)(g.x0 + xl) * pj.dpix;
-        if (store32 && xl + 4 <= g.ncols) {
+        uint8_t  *p  = prow + (long long)y * pj.dstride;
+        if (store32) {
             *reinterpret_cast<unsigned *>(p) = (unsigned)b0 | ((unsigned)b1 << 8) | ((unsigned)b2 << 16) | ((unsigned)b3 << 24);
         } else {
             const int n = g.ncols - xl;

@@ -53,10 +53,12 @@ bool build_resize_tables(ResizeTables &t, int sw, int sh, int dw, int dh, int al
         th[c] = pick_tile_height(t.vb[c], t.gcls[c].dh);
         ok = ok && th[c] >= std::min(8, t.gcls[c].dh);
     }
-    ok = ok && ng <= kMaxHGroups && vq <= 4;
+    int vt = std::max(t.vb[0].taps, t.vb[1].taps);
+    ok = ok && ng <= kMaxHGroups && vt <= kMaxVTaps;
+    vq = (vt + 1 + 3) / 4;
     t.fused_ok = ok;
     if (!ok) return true;
-    t.ng = ng; t.vq = vq;
+    t.ng = ng; t.vq = vq; t.vt = vt;
     int s_chunks_max = 1;
     for (int c = 0; c < 2; ++c) {
         PlaneClassDev    &d  = t.cls[c];
@@ -90,10 +92,12 @@ bool build_resize_tables(ResizeTables &t, int sw, int sh, int dw, int dh, int al
             chunks = std::max(chunks, ((ql - qa0) >> 2) + 1 + 1);
         }
         d.s_chunks   = chunks | 1;   // odd pitch: lanes <-> rows reads hit distinct banks
+        d.s_chunks_magic = int(unsigned((0x100000000ull + d.s_chunks - 1) / d.s_chunks));
+        d.vt = vt;
         s_chunks_max = std::max(s_chunks_max, d.s_chunks);
     }
     t.s_chunks_max = s_chunks_max;
-    t.smem_bytes   = size_t(kTileRows) * s_chunks_max * 16 + size_t(kTileW / 4) * kTPad * 16;
+    t.smem_bytes   = size_t(kTileRows) * s_chunks_max * 16 + (size_t(kTileW / 4) * kTPad + kTSlack) * 16;
     if (t.smem_bytes > 200 * 1024) t.fused_ok = false;
     return true;
 }

@@ -13,6 +13,8 @@ constexpr int kTileRows   = kRowGroups * 32;
 constexpr int kTPad       = kTileRows + 1;  // odd row pitch of the intermediate tile (bank spread)
 constexpr int kHEntry     = 8;    // int32 words per horizontal table entry: q, r8, 6 packed tap pairs
 constexpr int kMaxHGroups = 3;    // <= 12 horizontal taps in the fused kernel
+constexpr int kMaxVTaps   = 15;   // vertical taps in the fused kernel
+constexpr int kTSlack     = 16;   // int4 of slack behind the intermediate tile (zero-padded taps may read past a tile's rows)
 
 struct PlaneClassDev {            // geometry + tables shared by all planes of one class (luma / chroma)
     int sw, sh, dw, dh;
@@ -22,6 +24,8 @@ struct PlaneClassDev {            // geometry + tables shared by all planes of o
     int th;                       // output rows per tile
     int tiles_x, tiles_y;
     int s_chunks;                 // odd; 16-byte chunks per source-tile row in shared memory
+    int s_chunks_magic;           // ceil(2^32 / s_chunks): i / s_chunks == umulhi(i, magic) for the small i used
+    int vt;                       // vertical taps the kernel is instantiated for (>= vtaps, table zero padded)
     const int32_t *htab;          // [dw][kHEntry]
     const int32_t *vtab;          // [dh][4*vq]
 };

@@ -12,7 +12,7 @@ using namespace gvc;
 
 namespace {
 
-template <int NG, int VQ>
+template <int NG, int VT>
 void run_tile(const ResizeParams &P, int tile, int frame, int s_chunks_max) {
     const int            j  = find_job(P, tile);
     const PlaneJob      &pj = P.job[j];
@@ -21,27 +21,26 @@ void run_tile(const ResizeParams &P, int tile, int frame, int s_chunks_max) {
     const int            ty = t / pc.tiles_x, tx = t - ty * pc.tiles_x;
     const TileGeom       g  = tile_geom(pc, tx, ty);
     std::vector<gvc_uint4> S(size_t(kTileRows) * s_chunks_max);
-    std::vector<gvc_int4>  T(size_t(kTileW / 4) * kTPad);
+    std::vector<gvc_int4>  T(size_t(kTileW / 4) * kTPad + kTSlack);
     memset(S.data(), 0xAB, S.size() * sizeof(gvc_uint4));   // poison: stale smem must never matter
     memset(T.data(), 0xCD, T.size() * sizeof(gvc_int4));
     const uint8_t *src = pj.src + size_t(frame) * pj.sframe;
     uint8_t       *dst = pj.dst + size_t(frame) * pj.dframe;
     for (int tid = 0; tid < kThreads; ++tid) resize_phase0(tid, pc, pj, src, g, S.data());
     for (int tid = 0; tid < kThreads; ++tid) resize_phase1<NG>(tid, pc, g, S.data(), T.data());
-    for (int tid = 0; tid < kThreads; ++tid) resize_phase2<VQ>(tid, pc, pj, dst, g, T.data());
+    for (int tid = 0; tid < kThreads; ++tid) resize_phase2<VT>(tid, pc, pj, dst, g, T.data());
 }
 
 typedef void (*tile_fn)(const ResizeParams &, int, int, int);
+template <int NG, int VT>
+struct PickVt {
+    static tile_fn get(int vt) { return vt >= VT ? static_cast<tile_fn>(run_tile<NG, VT>) : PickVt<NG, VT - 1>::get(vt); }
+};
 template <int NG>
-tile_fn pick_vq(int vq) {
-    switch (vq) {
-        case 1: return run_tile<NG, 1>;
-        case 2: return run_tile<NG, 2>;
-        case 3: return run_tile<NG, 3>;
-        default: return run_tile<NG, 4>;
-    }
-}
-tile_fn pick(int ng, int vq) { return ng == 1 ? pick_vq<1>(vq) : ng == 2 ? pick_vq<2>(vq) : pick_vq<3>(vq); }
+struct PickVt<NG, 1> {
+    static tile_fn get(int) { return run_tile<NG, 1>; }
+};
+tile_fn pick(int ng, int vt) { return ng == 1 ? PickVt<1, kMaxVTaps>::get(vt) : ng == 2 ? PickVt<2, kMaxVTaps>::get(vt) : PickVt<3, kMaxVTaps>::get(vt); }
 
 }  // namespace
 
@@ -78,7 +77,7 @@ int emu_resize(const uint8_t *const sp[3], const int sstride[3], const size_t sf
             j.tile_base = k == 0 ? 0 : k == 1 ? lt : lt + ct;
         }
         P.tiles_per_frame = lt + 2 * ct;
-        tile_fn fn = pick(t.ng, t.vq);
+        tile_fn fn = pick(t.ng, t.vt);
         for (int f = 0; f < n_frames; ++f)
             for (int tile = 0; tile < P.tiles_per_frame; ++tile) fn(P, tile, f, t.s_chunks_max);
         return 0;
