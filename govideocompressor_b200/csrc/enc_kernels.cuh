@@ -584,6 +584,39 @@ GVC_HD void enc_mb_p3(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &s
     for (int i = 0; i < 16; ++i) mbco[25 * 16 + i] = 0;
 }
 
+// ------------------------------------------------------------------ record compaction ------------
+// Most 4x4 blocks quantise to nothing; the host entropy coder only needs the ones that did not.  Per macroblock the
+// blocks with a nonzero level are packed back to back (32 bytes each, ascending block number, block 24 = both chroma
+// DC sets, block 25 = luma DC) straight into host memory that is mapped into the device address space, so the copy back
+// shrinks from 832 bytes per macroblock to what the picture actually holds.
+GVC_HDH unsigned compact_mask(unsigned nz) {     // nzmask -> one bit per 16-coefficient block of the record (26 blocks)
+    return (nz & 0x00ffffffu) | ((nz & 0x03000000u) ? (1u << 24) : 0u) | (((nz >> 26) & 1u) << 25);
+}
+GVC_HDH int popcount32(unsigned v) {
+#if defined(__CUDA_ARCH__)
+    return __popc(v);
+#else
+    return __builtin_popcount(v);
+#endif
+}
+struct CompactArgs {
+    const uint32_t *nzmask;      // per MB
+    const int16_t  *coefs;       // kMbCoefs per MB
+    const uint32_t *offsets;     // per MB: number of blocks packed before it (exclusive prefix sum of popcount(compact_mask))
+    int16_t        *out;         // host-mapped destination
+    int             nmb;
+};
+GVC_HD void compact_mb_lane(int lane, const CompactArgs &a, int mb) {
+    if (lane >= 26) return;
+    const unsigned cm = compact_mask(a.nzmask[mb]);
+    if (!((cm >> lane) & 1u)) return;
+    const int rank = popcount32(cm & ((1u << lane) - 1u));
+    const gvc_int4 *src = reinterpret_cast<const gvc_int4 *>(a.coefs + (long long)mb * kMbCoefs + lane * 16);
+    gvc_int4       *dst = reinterpret_cast<gvc_int4 *>(a.out + ((long long)a.offsets[mb] + rank) * 16);
+    dst[0] = src[0];
+    dst[1] = src[1];
+}
+
 // ------------------------------------------------------------------ K7 all-Intra16x16 frame (IDR) -
 // Specification: oracle/h264_mb.c gvc_oracle_encode_intra_frame (H.264 8.3.3, 8.3.4, 8.5.2, 8.5.10).  One warp
 // per macroblock ROW walks its row left to right; a row may start macroblock mx once the row above has

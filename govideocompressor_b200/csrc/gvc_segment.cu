@@ -27,7 +27,7 @@ using namespace gvc;
 namespace {
 
 // Optional per-stage timing with CUDA events on the launching stream (bench.py's roofline figures).
-enum Stage { kStResize = 0, kStBorder, kStLowres, kStHpel, kStMeLowres, kStMeRefine, kStEncInter, kStEncIntra, kStCount };
+enum Stage { kStResize = 0, kStBorder, kStLowres, kStHpel, kStMeLowres, kStMeRefine, kStEncInter, kStEncIntra, kStCompact, kStCount };
 struct StageTimer {
     bool on = false;
     struct Rec { int stage; cudaEvent_t a, b; };
@@ -64,7 +64,9 @@ struct CudaOps {
     template <class F> int timed(int stage, F f) { tm.begin(stage, st); const int rc = f(); tm.end(st); return rc; }
     void *alloc(size_t n) { void *p = nullptr; return cudaMalloc(&p, n + 64) == cudaSuccess ? p : nullptr; }
     void  release(void *p) { cudaFree(p); }
-    void *alloc_host(size_t n) { void *p = nullptr; return cudaHostAlloc(&p, n + 64, cudaHostAllocDefault) == cudaSuccess ? p : nullptr; }
+    void *alloc_host(size_t n) { void *p = nullptr; return cudaHostAlloc(&p, n + 64, cudaHostAllocMapped) == cudaSuccess ? p : nullptr; }
+    void *device_alias(void *h) { void *d = nullptr; return cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess ? d : nullptr; }
+    int compact(const CompactArgs &a, uint32_t *offsets) { return timed(kStCompact, [&] { return launch_compact(a, offsets, st); }); }
     void  release_host(void *p) { cudaFreeHost(p); }
     int upload(void *dst, const void *src, size_t n) { GVC_CUDA(cudaMemcpy(dst, src, n, cudaMemcpyHostToDevice)); return 0; }
     int extend_border3(const BorderBatchArgs &a) { return timed(kStBorder, [&] { return launch_extend_border_batch(a, st); }); }
@@ -238,13 +240,13 @@ int gvc_encoder_set_timing(gvc_encoder *e, int on) {
     return GVC_OK;
 }
 
-int gvc_encoder_stage_times(gvc_encoder *e, double *ms8, int *launches8) {
+int gvc_encoder_stage_times(gvc_encoder *e, double *ms8, int *launches8) {   // GVC_STAGES entries each
     int rc = enter();
     if (rc) return rc;
     if (!e || !ms8 || !launches8) { set_error("gvc_encoder_stage_times: bad arguments"); return GVC_ERR_INVALID_ARG; }
     GVC_CUDA(cudaStreamSynchronize(e->ops.st));
     e->ops.tm.collect();
-    for (int i = 0; i < kStCount; ++i) { ms8[i] = e->ops.tm.ms[i]; launches8[i] = e->ops.tm.launches[i]; }
+    for (int i = 0; i < kStCount; ++i) { ms8[i] = e->ops.tm.ms[i]; launches8[i] = e->ops.tm.launches[i]; }   // 9 entries
     return GVC_OK;
 }
 

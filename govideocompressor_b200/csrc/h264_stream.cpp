@@ -312,9 +312,12 @@ inline void write_empty_block(BitWriter &bw, int nC) {     // coeff_token with T
 
 // residual( ) of one macroblock; updates the nnz maps.  i16: Intra16x16 (DC block + 15-coefficient AC blocks).
 // nz is the kernels' per-block "has a nonzero level" mask: empty blocks are coded without touching their coefficients.
-void write_mb_residual(BitWriter &bw, PicState &s, const int16_t *co, int mx, int my, int cbp, bool i16, uint32_t nz) {
+void write_mb_residual(BitWriter &bw, PicState &s, const int16_t *mbco, bool compact, int mx, int my, int cbp, bool i16, uint32_t nz) {
+    // block b of this macroblock's record: fixed slot in the full layout, rank among the present blocks when packed
+    const unsigned cm = (nz & 0x00ffffffu) | ((nz & 0x03000000u) ? (1u << 24) : 0u) | (((nz >> 26) & 1u) << 25);
+    auto block_at = [&](int b) { return compact ? mbco + 16 * __builtin_popcount(cm & ((1u << b) - 1u)) : mbco + 16 * b; };
     if (i16) {
-        if (nz & (1u << 26)) write_residual(bw, co + 25 * 16, 16, luma_nc(s, 4 * mx, 4 * my));
+        if (nz & (1u << 26)) write_residual(bw, block_at(25), 16, luma_nc(s, 4 * mx, 4 * my));
         else write_empty_block(bw, luma_nc(s, 4 * mx, 4 * my));
     }
     for (int blk = 0; blk < 16; ++blk) {
@@ -322,14 +325,14 @@ void write_mb_residual(BitWriter &bw, PicState &s, const int16_t *co, int mx, in
         int       total = 0;
         if (cbp & (1 << (blk >> 2))) {
             if (!(nz & (1u << r))) write_empty_block(bw, luma_nc(s, bx, by));
-            else if (i16) total = write_residual(bw, co + r * 16 + 1, 15, luma_nc(s, bx, by));
-            else          total = write_residual(bw, co + r * 16, 16, luma_nc(s, bx, by));
+            else if (i16) total = write_residual(bw, block_at(r) + 1, 15, luma_nc(s, bx, by));
+            else          total = write_residual(bw, block_at(r), 16, luma_nc(s, bx, by));
         }
         s.nnz_y[by * s.w4 + bx] = uint8_t(total);
     }
     if (cbp & 0x30)
         for (int p = 0; p < 2; ++p) {
-            if (nz & (1u << (24 + p))) write_residual(bw, co + 24 * 16 + 4 * p, 4, -1);
+            if (nz & (1u << (24 + p))) write_residual(bw, block_at(24) + 4 * p, 4, -1);
             else write_empty_block(bw, -1);
         }
     for (int p = 0; p < 2; ++p)
@@ -337,7 +340,7 @@ void write_mb_residual(BitWriter &bw, PicState &s, const int16_t *co, int mx, in
             const int bx = 2 * mx + (b & 1), by = 2 * my + (b >> 1);
             int       total = 0;
             if (cbp & 0x20) {
-                if (nz & (1u << (16 + 4 * p + b))) total = write_residual(bw, co + (16 + 4 * p + b) * 16 + 1, 15, chroma_nc(s, p, bx, by));
+                if (nz & (1u << (16 + 4 * p + b))) total = write_residual(bw, block_at(16 + 4 * p + b) + 1, 15, chroma_nc(s, p, bx, by));
                 else write_empty_block(bw, chroma_nc(s, p, bx, by));
             }
             s.nnz_c[p][by * 2 * s.mbw + bx] = uint8_t(total);
@@ -395,17 +398,20 @@ void write_slice(BitWriter &bw, const PictureData &pic, SliceStats *stats) {
 
     // slice_data()
     int skip_run = 0;
+    const int16_t *packed = pic.coefs;      // compact layout: advances by the number of present blocks of each macroblock
     for (int my = 0; my < pic.mbh; ++my)
         for (int mx = 0; mx < pic.mbw; ++mx) {
             const int       mb = my * pic.mbw + mx;
-            const int16_t  *co = pic.coefs + size_t(mb) * kMbCoefs;
             const uint32_t  nz = pic.nzmask[mb];
+            const int16_t  *co = pic.compact ? packed : pic.coefs + size_t(mb) * kMbCoefs;
+            if (pic.compact)
+                packed += 16 * __builtin_popcount((nz & 0x00ffffffu) | ((nz & 0x03000000u) ? (1u << 24) : 0u) | (((nz >> 26) & 1u) << 25));
             if (pic.idr) {
                 const int cbp = mb_cbp(nz, true);
                 bw.ue(uint32_t(1 + pic.modes[mb] + 4 * (cbp >> 4) + ((cbp & 15) ? 12 : 0)));   // mb_type I_16x16_<mode>_<cbpc>_<cbpl>
                 bw.ue(0);                  // intra_chroma_pred_mode: DC
                 bw.se(0);                  // mb_qp_delta
-                write_mb_residual(bw, s, co, mx, my, cbp, true, nz);
+                write_mb_residual(bw, s, co, pic.compact, mx, my, cbp, true, nz);
                 ++st.intra;
                 continue;
             }
@@ -450,7 +456,7 @@ void write_slice(BitWriter &bw, const PictureData &pic, SliceStats *stats) {
             bw.ue(kCbpCode.inter[cbp]);    // coded_block_pattern me(v)
             if (cbp) {
                 bw.se(0);                  // mb_qp_delta
-                write_mb_residual(bw, s, co, mx, my, cbp, false, nz);
+                write_mb_residual(bw, s, co, pic.compact, mx, my, cbp, false, nz);
             } else {
                 clear_mb_nnz(s, mx, my);
             }

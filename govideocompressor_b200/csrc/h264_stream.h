@@ -69,7 +69,9 @@ struct PictureData {
     int             mbw = 0, mbh = 0;
     bool            idr = false;
     int             frame_num = 0, idr_pic_id = 0, qp = 26;
-    const int16_t  *coefs = nullptr;    // kMbCoefs per MB (layout: enc_kernels.cuh)
+    const int16_t  *coefs = nullptr;    // kMbCoefs per MB (layout: enc_kernels.cuh), or, with compact = true, only the blocks
+                                        // whose compact_mask bit is set, 16 coefficients each, packed MB after MB
+    bool            compact = false;
     const uint32_t *nzmask = nullptr;   // per MB
     const MbMotion *motion = nullptr;   // P pictures
     const uint8_t  *modes = nullptr;    // IDR pictures: Intra16x16 prediction mode
