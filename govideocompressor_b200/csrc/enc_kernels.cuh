@@ -478,6 +478,53 @@ GVC_HD void me_ref_out(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &
     a.out[my * a.mbw + mx] = m;
 }
 
+// ------------------------------------------------------------------ record compaction ------------
+// Most 4x4 blocks quantise to nothing; the host entropy coder only needs the ones that did not.  Per macroblock the
+// blocks with a nonzero level are packed back to back (32 bytes each, ascending block number, block 24 = both chroma
+// DC sets, block 25 = luma DC) straight into host memory that is mapped into the device address space, so the copy back
+// shrinks from 832 bytes per macroblock to what the picture actually holds.
+GVC_HDH unsigned compact_mask(unsigned nz) {     // nzmask -> one bit per 16-coefficient block of the record (26 blocks)
+    return (nz & 0x00ffffffu) | ((nz & 0x03000000u) ? (1u << 24) : 0u) | (((nz >> 26) & 1u) << 25);
+}
+GVC_HDH int popcount32(unsigned v) {
+#if defined(__CUDA_ARCH__)
+    return __popc(v);
+#else
+    return __builtin_popcount(v);
+#endif
+}
+// Destination of the packed blocks of one picture (all three members null = packing off, e.g. in kernel-level tests).
+struct PackOut {
+    int16_t  *blocks;     // host-mapped: 16 coefficients per present block
+    uint32_t *offsets;    // per MB: index (in blocks) of its first packed block
+    unsigned *counter;    // blocks handed out so far in this picture (zeroed before the launch)
+};
+// lane 0 reserves room for the macroblock's present blocks (order between macroblocks is whatever the hardware
+// schedules; the offset table makes it irrelevant), every lane then copies its block if present.
+GVC_HD void pack_reserve(int lane, const PackOut &po, int mb, uint32_t nz, int *flags) {
+    if (lane != 0 || !po.blocks) return;
+    const unsigned cm = compact_mask(nz);
+#if defined(GVC_EMU)
+    const unsigned base = *po.counter;
+    *po.counter += (unsigned)popcount32(cm);
+#else
+    const unsigned base = atomicAdd(po.counter, (unsigned)popcount32(cm));
+#endif
+    po.offsets[mb] = base;
+    flags[30] = (int)cm;
+    flags[31] = (int)base;
+}
+GVC_HD void pack_copy(int lane, const PackOut &po, const int16_t *mbco, const int *flags) {
+    if (lane >= 26 || !po.blocks) return;
+    const unsigned cm = (unsigned)flags[30];
+    if (!((cm >> lane) & 1u)) return;
+    const int rank = popcount32(cm & ((1u << lane) - 1u));
+    const gvc_int4 *src = reinterpret_cast<const gvc_int4 *>(mbco + lane * 16);
+    gvc_int4       *dst = reinterpret_cast<gvc_int4 *>(po.blocks + ((long long)(unsigned)flags[31] + rank) * 16);
+    dst[0] = src[0];
+    dst[1] = src[1];
+}
+
 // ------------------------------------------------------------------ K5+K6 inter MB encode -------
 // coef layout per MB (int16[26][16]): blocks 0..15 luma 4x4 (raster block order, zig-zag coefficient order),
 // 16..19 Cb AC, 20..23 Cr AC (entry 0 = 0), 24: chroma DC levels Cb[0..3] Cr[4..7], 25: luma DC (Intra16x16 only).
@@ -491,6 +538,7 @@ struct EncMbArgs {
     const MbMotion *motion;
     int16_t       *coefs;
     uint32_t      *nzmask;
+    PackOut        pack;
 };
 struct EncMbSmem {               // per warp
     int16_t  cblk[8][16];        // chroma blocks after the forward transform
@@ -582,39 +630,10 @@ GVC_HD void enc_mb_p3(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &s
     int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
     for (int i = 8; i < 16; ++i) mbco[24 * 16 + i] = 0;
     for (int i = 0; i < 16; ++i) mbco[25 * 16 + i] = 0;
+    pack_reserve(lane, a.pack, my * a.mbw + mx, m, sm.flags);
 }
-
-// ------------------------------------------------------------------ record compaction ------------
-// Most 4x4 blocks quantise to nothing; the host entropy coder only needs the ones that did not.  Per macroblock the
-// blocks with a nonzero level are packed back to back (32 bytes each, ascending block number, block 24 = both chroma
-// DC sets, block 25 = luma DC) straight into host memory that is mapped into the device address space, so the copy back
-// shrinks from 832 bytes per macroblock to what the picture actually holds.
-GVC_HDH unsigned compact_mask(unsigned nz) {     // nzmask -> one bit per 16-coefficient block of the record (26 blocks)
-    return (nz & 0x00ffffffu) | ((nz & 0x03000000u) ? (1u << 24) : 0u) | (((nz >> 26) & 1u) << 25);
-}
-GVC_HDH int popcount32(unsigned v) {
-#if defined(__CUDA_ARCH__)
-    return __popc(v);
-#else
-    return __builtin_popcount(v);
-#endif
-}
-struct CompactArgs {
-    const uint32_t *nzmask;      // per MB
-    const int16_t  *coefs;       // kMbCoefs per MB
-    const uint32_t *offsets;     // per MB: number of blocks packed before it (exclusive prefix sum of popcount(compact_mask))
-    int16_t        *out;         // host-mapped destination
-    int             nmb;
-};
-GVC_HD void compact_mb_lane(int lane, const CompactArgs &a, int mb) {
-    if (lane >= 26) return;
-    const unsigned cm = compact_mask(a.nzmask[mb]);
-    if (!((cm >> lane) & 1u)) return;
-    const int rank = popcount32(cm & ((1u << lane) - 1u));
-    const gvc_int4 *src = reinterpret_cast<const gvc_int4 *>(a.coefs + (long long)mb * kMbCoefs + lane * 16);
-    gvc_int4       *dst = reinterpret_cast<gvc_int4 *>(a.out + ((long long)a.offsets[mb] + rank) * 16);
-    dst[0] = src[0];
-    dst[1] = src[1];
+GVC_HD void enc_mb_p4(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
+    pack_copy(lane, a.pack, a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs, sm.flags);
 }
 
 // ------------------------------------------------------------------ K7 all-Intra16x16 frame (IDR) -
@@ -631,6 +650,7 @@ struct IntraArgs {
     uint32_t      *nzmask;
     uint8_t       *modes;
     int           *progress;   // [mbh]
+    PackOut        pack;
 };
 struct IntraSmem {
     int      top[16], left[16];       // reconstructed neighbours of the luma MB
@@ -783,6 +803,10 @@ GVC_HD void intra_p4(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm
     a.nzmask[my * a.mbw + mx] = m;
     int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
     for (int i = 8; i < 16; ++i) mbco[24 * 16 + i] = 0;
+    pack_reserve(lane, a.pack, my * a.mbw + mx, m, sm.flags);
+}
+GVC_HD void intra_p5(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+    pack_copy(lane, a.pack, a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs, sm.flags);
 }
 
 }  // namespace gvc

@@ -15,5 +15,4 @@ int launch_me_lowres(const MeLowArgs &a, cudaStream_t st);
 int launch_me_refine(const MeRefArgs &a, cudaStream_t st);
 int launch_encode_inter(const EncMbArgs &a, cudaStream_t st);
 int launch_encode_intra(const IntraArgs &a, cudaStream_t st);
-int launch_compact(const CompactArgs &a, uint32_t *offsets_scratch, cudaStream_t st);
 }  // namespace gvc

@@ -93,40 +93,8 @@ __global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __gri
     enc_mb_p2(lane, a, mx, my, sm);
     __syncwarp();
     enc_mb_p3(lane, a, mx, my, sm);
-}
-
-// Exclusive prefix sum of the per-macroblock block counts (one CTA; nmb <= 1024 * 64).
-__global__ void __launch_bounds__(1024) compact_scan_kernel(const uint32_t *nzmask, uint32_t *offsets, int nmb) {
-    __shared__ uint32_t warp_sums[32];
-    __shared__ uint32_t carry;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) carry = 0;
-    __syncthreads();
-    for (int base = 0; base < nmb; base += 1024) {
-        const int mb = base + tid;
-        const uint32_t c = mb < nmb ? (uint32_t)__popc(compact_mask(nzmask[mb])) : 0u;
-        uint32_t v = c;
-        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
-        if (lane == 31) warp_sums[warp] = v;
-        __syncthreads();
-        if (warp == 0) {
-            uint32_t w = warp_sums[lane];
-            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, w, d); if (lane >= d) w += t; }
-            warp_sums[lane] = w;
-        }
-        __syncthreads();
-        const uint32_t before = carry + (warp ? warp_sums[warp - 1] : 0u) + v - c;
-        if (mb < nmb) offsets[mb] = before;
-        __syncthreads();
-        if (tid == 1023) carry = before + c;
-        __syncthreads();
-    }
-}
-
-__global__ void __launch_bounds__(32 * kMbWarps) compact_scatter_kernel(const __grid_constant__ CompactArgs a) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int mb = blockIdx.x * kMbWarps + warp;
-    if (mb < a.nmb) compact_mb_lane(lane, a, mb);
+    __syncwarp();
+    enc_mb_p4(lane, a, mx, my, sm);
 }
 
 // One warp per macroblock row; rows advance as a wavefront (see enc_kernels.cuh K7).
@@ -150,6 +118,8 @@ __global__ void __launch_bounds__(32) intra_frame_kernel(const __grid_constant__
         intra_p3(lane, a, mx, my, sm);
         __syncwarp();
         intra_p4(lane, a, mx, my, sm);
+        __syncwarp();
+        intra_p5(lane, a, mx, my, sm);
         __threadfence();
         __syncwarp();
         if (lane == 0) prog[my] = mx + 1;
@@ -213,14 +183,6 @@ int launch_me_refine(const MeRefArgs &a, cudaStream_t st) {
 }
 int launch_encode_inter(const EncMbArgs &a, cudaStream_t st) {
     encode_inter_kernel<<<(a.mbw * a.mbh + kMbWarps - 1) / kMbWarps, 32 * kMbWarps, 0, st>>>(a);
-    GVC_CUDA(cudaGetLastError());
-    return GVC_OK;
-}
-
-int launch_compact(const CompactArgs &a, uint32_t *offsets_scratch, cudaStream_t st) {
-    compact_scan_kernel<<<1, 1024, 0, st>>>(a.nzmask, offsets_scratch, a.nmb);
-    GVC_CUDA(cudaGetLastError());
-    compact_scatter_kernel<<<(a.nmb + kMbWarps - 1) / kMbWarps, 32 * kMbWarps, 0, st>>>(a);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
@@ -313,6 +275,7 @@ int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
     a.rec_y = rec_y; a.rec_u = rec_u; a.rec_v = rec_v; a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, false);
     a.motion = reinterpret_cast<const MbMotion *>(motion); a.coefs = coefs; a.nzmask = nzmask;
+    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
     return launch_encode_inter(a, static_cast<cudaStream_t>(stream));
 }
 
@@ -333,6 +296,7 @@ int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
     a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, true);
     a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.progress = row_progress;
+    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
     return launch_encode_intra(a, static_cast<cudaStream_t>(stream));
 }
 

@@ -27,7 +27,7 @@ using namespace gvc;
 namespace {
 
 // Optional per-stage timing with CUDA events on the launching stream (bench.py's roofline figures).
-enum Stage { kStResize = 0, kStBorder, kStLowres, kStHpel, kStMeLowres, kStMeRefine, kStEncInter, kStEncIntra, kStCompact, kStCount };
+enum Stage { kStResize = 0, kStBorder, kStLowres, kStHpel, kStMeLowres, kStMeRefine, kStEncInter, kStEncIntra, kStCount };
 struct StageTimer {
     bool on = false;
     struct Rec { int stage; cudaEvent_t a, b; };
@@ -66,7 +66,7 @@ struct CudaOps {
     void  release(void *p) { cudaFree(p); }
     void *alloc_host(size_t n) { void *p = nullptr; return cudaHostAlloc(&p, n + 64, cudaHostAllocMapped) == cudaSuccess ? p : nullptr; }
     void *device_alias(void *h) { void *d = nullptr; return cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess ? d : nullptr; }
-    int compact(const CompactArgs &a, uint32_t *offsets) { return timed(kStCompact, [&] { return launch_compact(a, offsets, st); }); }
+    int clear(void *dev, size_t n) { GVC_CUDA(cudaMemsetAsync(dev, 0, n, st)); return 0; }
     void  release_host(void *p) { cudaFreeHost(p); }
     int upload(void *dst, const void *src, size_t n) { GVC_CUDA(cudaMemcpy(dst, src, n, cudaMemcpyHostToDevice)); return 0; }
     int extend_border3(const BorderBatchArgs &a) { return timed(kStBorder, [&] { return launch_extend_border_batch(a, st); }); }

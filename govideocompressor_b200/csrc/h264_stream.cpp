@@ -398,14 +398,11 @@ void write_slice(BitWriter &bw, const PictureData &pic, SliceStats *stats) {
 
     // slice_data()
     int skip_run = 0;
-    const int16_t *packed = pic.coefs;      // compact layout: advances by the number of present blocks of each macroblock
     for (int my = 0; my < pic.mbh; ++my)
         for (int mx = 0; mx < pic.mbw; ++mx) {
             const int       mb = my * pic.mbw + mx;
             const uint32_t  nz = pic.nzmask[mb];
-            const int16_t  *co = pic.compact ? packed : pic.coefs + size_t(mb) * kMbCoefs;
-            if (pic.compact)
-                packed += 16 * __builtin_popcount((nz & 0x00ffffffu) | ((nz & 0x03000000u) ? (1u << 24) : 0u) | (((nz >> 26) & 1u) << 25));
+            const int16_t  *co = pic.compact ? pic.coefs + size_t(16) * pic.block_offsets[mb] : pic.coefs + size_t(mb) * kMbCoefs;
             if (pic.idr) {
                 const int cbp = mb_cbp(nz, true);
                 bw.ue(uint32_t(1 + pic.modes[mb] + 4 * (cbp >> 4) + ((cbp & 15) ? 12 : 0)));   // mb_type I_16x16_<mode>_<cbpc>_<cbpl>

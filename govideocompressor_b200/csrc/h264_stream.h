@@ -72,6 +72,7 @@ struct PictureData {
     const int16_t  *coefs = nullptr;    // kMbCoefs per MB (layout: enc_kernels.cuh), or, with compact = true, only the blocks
                                         // whose compact_mask bit is set, 16 coefficients each, packed MB after MB
     bool            compact = false;
+    const uint32_t *block_offsets = nullptr;   // compact: per MB, index (in blocks) of its first packed block
     const uint32_t *nzmask = nullptr;   // per MB
     const MbMotion *motion = nullptr;   // P pictures
     const uint8_t  *modes = nullptr;    // IDR pictures: Intra16x16 prediction mode

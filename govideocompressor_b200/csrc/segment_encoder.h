@@ -56,7 +56,7 @@ struct SegmentOutput {
 // Ops concept (all calls asynchronous and in order; sync() waits for everything issued so far):
 //   void *alloc(size_t bytes);  void release(void *p);   void *alloc_host(size_t bytes);  void release_host(void *p);   // pinned
 //   int upload(void *dev_dst, const void *host_src, size_t bytes);   void *device_alias(void *pinned_host);   // mapped address
-//   int compact(const CompactArgs &a, uint32_t *offsets_scratch);
+//   int clear(void *dev, size_t bytes);
 //   int extend_border3(const BorderBatchArgs &a);   int lowres_batch(const LowresBatchArgs &a);
 //   int hpel(const HpelArgs &a);  int me_lowres(const MeLowArgs &a);  int me_refine(const MeRefArgs &a);
 //   int encode_inter(const EncMbArgs &a);  int encode_intra(const IntraArgs &a);
@@ -97,13 +97,15 @@ public:
         d_prog_   = static_cast<int *>(ops_.alloc(sizeof(int) * g_.mbh));
         d_one_    = static_cast<int *>(ops_.alloc(sizeof(int)));
         h_blocks_ = static_cast<int16_t *>(ops_.alloc_host(sizeof(int16_t) * kMbCoefs * nmb * n_frames));   // worst case: every block nonzero
-        d_offsets_ = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb));
+        d_offsets_ = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb * n_frames));
+        d_counters_ = static_cast<unsigned *>(ops_.alloc(sizeof(unsigned) * n_frames));
+        h_offsets_ = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * nmb * n_frames));
         h_nz_     = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * nmb * n_frames));
         h_motion_ = static_cast<MbMotion *>(ops_.alloc_host(sizeof(MbMotion) * nmb * n_frames));
         h_modes_  = static_cast<uint8_t *>(ops_.alloc_host(nmb));
         h_done_   = static_cast<int *>(ops_.alloc_host(sizeof(int) * n_frames));
         bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_coefs_ && d_nz_ && d_motion_ && d_modes_ && d_lowmv_ && d_prog_ && d_one_ &&
-                  h_blocks_ && d_offsets_ && h_nz_ && h_motion_ && h_modes_ && h_done_;
+                  h_blocks_ && d_offsets_ && d_counters_ && h_offsets_ && h_nz_ && h_motion_ && h_modes_ && h_done_;
         for (int i = 0; i < 2; ++i) {
             for (int k = 0; k < 4; ++k) ok = ok && rec_y_[i][k];
             ok = ok && rec_u_[i] && rec_v_[i] && rec_low_[i];
@@ -138,6 +140,8 @@ public:
             if ((rc = ops_.lowres_batch(l))) return rc;
         }
         const size_t nmb = size_t(g_.mbw) * g_.mbh;
+        if ((rc = ops_.clear(d_counters_, sizeof(unsigned) * n))) return rc;
+        int16_t *blocks_dev = static_cast<int16_t *>(ops_.device_alias(h_blocks_));
         if (cfg_.keep_recon) recon_store_.assign(size_t(g_.w16) * g_.h16 * 3 / 2 * n, 0);
         for (int f = 0; f < n; ++f) {
             const int r = f & 1, p = r ^ 1;
@@ -149,6 +153,7 @@ public:
                 a.sy = g_.sy; a.sc = g_.sc; a.mbw = g_.mbw; a.mbh = g_.mbh;
                 fill_quant_params(a.q, cfg_.qp_i, true);
                 a.coefs = d_coefs_; a.nzmask = d_nz_; a.modes = d_modes_; a.progress = d_prog_;
+                a.pack.blocks = blocks_dev; a.pack.offsets = d_offsets_; a.pack.counter = d_counters_;
                 if ((rc = ops_.encode_intra(a))) return rc;
             } else {
                 RefPlanes ref;
@@ -168,15 +173,12 @@ public:
                 e.cur_y = cy; e.cur_u = cu; e.cur_v = cv; e.ref = ref; e.rec_y = ry; e.rec_u = ru; e.rec_v = rv;
                 e.sy = g_.sy; e.sc = g_.sc; e.mbw = g_.mbw; e.mbh = g_.mbh; e.q = q;
                 e.motion = d_motion_ + nmb * f; e.coefs = d_coefs_ + size_t(kMbCoefs) * nmb * f; e.nzmask = d_nz_ + nmb * f;
+                e.pack.blocks = blocks_dev + size_t(kMbCoefs) * nmb * f; e.pack.offsets = d_offsets_ + nmb * f; e.pack.counter = d_counters_ + f;
                 if ((rc = ops_.encode_inter(e))) return rc;
             }
-            {   // records of this picture -> host: nonzero blocks packed by a kernel straight into mapped pinned memory, the
+            {   // records of this picture -> host: the encode kernel has packed the nonzero blocks straight into mapped pinned memory, the
                 // small per-macroblock tables by copies, then the arrival flag (stream order: all of it has landed by then)
-                const size_t co = size_t(kMbCoefs) * nmb * f;
-                CompactArgs ca;
-                ca.nzmask = d_nz_ + nmb * f; ca.coefs = d_coefs_ + co; ca.offsets = d_offsets_; ca.nmb = int(nmb);
-                ca.out = static_cast<int16_t *>(ops_.device_alias(h_blocks_)) + co;
-                if ((rc = ops_.compact(ca, d_offsets_))) return rc;
+                if ((rc = ops_.download(h_offsets_ + nmb * f, d_offsets_ + nmb * f, sizeof(uint32_t) * nmb))) return rc;
                 if ((rc = ops_.download(h_nz_ + nmb * f, d_nz_ + nmb * f, sizeof(uint32_t) * nmb))) return rc;
                 if (f == 0) { if ((rc = ops_.download(h_modes_, d_modes_, nmb))) return rc; }
                 else if ((rc = ops_.download(h_motion_ + nmb * f, d_motion_ + nmb * f, sizeof(MbMotion) * nmb))) return rc;
@@ -238,6 +240,7 @@ public:
             pic.qp = f == 0 ? cfg_.qp_i : cfg_.qp_p;
             pic.coefs = h_blocks_ + size_t(kMbCoefs) * nmb * f;
             pic.compact = true;
+            pic.block_offsets = h_offsets_ + nmb * f;
             pic.nzmask = h_nz_ + nmb * f;
             pic.motion = h_motion_ + nmb * f;
             pic.modes = h_modes_;
@@ -301,7 +304,7 @@ private:
         }
         rel(d_coefs_); rel(d_nz_); rel(d_motion_); rel(d_modes_); rel(d_lowmv_); rel(d_prog_); rel(d_one_);
         auto relh = [&](auto *&p) { if (p) ops_.release_host(p); p = nullptr; };
-        rel(d_offsets_);
+        rel(d_offsets_); rel(d_counters_); relh(h_offsets_);
         relh(h_blocks_); relh(h_nz_); relh(h_motion_); relh(h_modes_); relh(h_done_);
         cap_ = 0;
     }
@@ -323,7 +326,8 @@ private:
     int          *d_prog_ = nullptr;
     int          *d_one_ = nullptr;
     int16_t      *h_blocks_ = nullptr;    // pinned + device-mapped: the nonzero blocks of every picture, packed
-    uint32_t     *d_offsets_ = nullptr;
+    uint32_t     *d_offsets_ = nullptr, *h_offsets_ = nullptr;   // per MB: first packed block
+    unsigned     *d_counters_ = nullptr;                          // per picture: blocks handed out
     uint32_t     *h_nz_ = nullptr;
     MbMotion     *h_motion_ = nullptr;
     uint8_t      *h_modes_ = nullptr;

@@ -112,13 +112,13 @@ class Encoder:
         _lib.check(self._lib.gvc_encoder_stats(self._h, ctypes.c_void_p(st.ctypes.data), self.n_last), "gvc_encoder_stats")
         return st
 
-    STAGES = ("resize", "border", "lowres", "hpel", "me_lowres", "me_refine", "encode_inter", "encode_intra", "compact")
+    STAGES = ("resize", "border", "lowres", "hpel", "me_lowres", "me_refine", "encode_inter", "encode_intra")
 
     def set_timing(self, on=True):
         _lib.check(self._lib.gvc_encoder_set_timing(self._h, int(on)), "gvc_encoder_set_timing")
 
     def stage_times(self):
-        ms, n = (ctypes.c_double * 9)(), (ctypes.c_int * 9)()
+        ms, n = (ctypes.c_double * 8)(), (ctypes.c_int * 8)()
         _lib.check(self._lib.gvc_encoder_stage_times(self._h, ms, n), "gvc_encoder_stage_times")
         return {s: (ms[i], n[i]) for i, s in enumerate(self.STAGES)}
 

@@ -199,9 +199,9 @@ int gvc_encoder_recon(gvc_encoder *enc, uint8_t *dst, size_t cap);
 /* per picture: skipped MBs, P16x16 MBs, P8x8 MBs, bytes */
 int gvc_encoder_stats(gvc_encoder *enc, int *stats4_per_picture, int n_pictures);
 /* Per-stage device times (CUDA events on the encoder's stream) for measurement: stages in order resize, border,
- * lowres, hpel, me_lowres, me_refine, encode_inter, encode_intra, compact.  set_timing(on) also clears the totals;
+ * lowres, hpel, me_lowres, me_refine, encode_inter, encode_intra.  set_timing(on) also clears the totals;
  * stage_times synchronises the stream and returns accumulated milliseconds and launch counts (GVC_STAGES entries each). */
-#define GVC_STAGES 9
+#define GVC_STAGES 8
 int gvc_encoder_set_timing(gvc_encoder *enc, int on);
 int gvc_encoder_stage_times(gvc_encoder *enc, double *ms, int *launches);
 /* Muxes the last segment into an MP4 file (temp name + rename). */

@@ -43,6 +43,7 @@ void emu_run_encode_inter(const EncMbArgs &a) {
             for (int l = 0; l < 32; ++l) enc_mb_p1(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) enc_mb_p2(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) enc_mb_p3(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) enc_mb_p4(l, a, mx, my, sm);
         }
 }
 void emu_run_encode_intra(const IntraArgs &a) {
@@ -55,6 +56,7 @@ void emu_run_encode_intra(const IntraArgs &a) {
             for (int l = 0; l < 32; ++l) intra_p2(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) intra_p3(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) intra_p4(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p5(l, a, mx, my, sm);
         }
 }
 
@@ -112,6 +114,7 @@ void emu_encode_inter(const uint8_t *const cur[3], const uint8_t *const ref[7], 
     a.rec_y = rec[0]; a.rec_u = rec[1]; a.rec_v = rec[2]; a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, false);
     a.motion = static_cast<const MbMotion *>(motion); a.coefs = coefs; a.nzmask = nzmask;
+    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
     emu_run_encode_inter(a);
 }
 
@@ -122,6 +125,7 @@ void emu_encode_intra(const uint8_t *const cur[3], uint8_t *const rec[3], int sy
     a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, true);
     a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.progress = nullptr;
+    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
     emu_run_encode_intra(a);
 }
 

@@ -30,13 +30,7 @@ struct EmuOps {
     void  release_host(void *p) { free(p); }
     int upload(void *dst, const void *src, size_t n) { memcpy(dst, src, n); return 0; }
     void *device_alias(void *h) { return h; }
-    int compact(const CompactArgs &a, uint32_t *offsets) {
-        uint32_t run = 0;
-        for (int mb = 0; mb < a.nmb; ++mb) { offsets[mb] = run; run += uint32_t(popcount32(compact_mask(a.nzmask[mb]))); }
-        for (int mb = 0; mb < a.nmb; ++mb)
-            for (int l = 0; l < 32; ++l) compact_mb_lane(l, a, mb);
-        return 0;
-    }
+    int clear(void *p, size_t n) { memset(p, 0, n); return 0; }
     int extend_border3(const BorderBatchArgs &a) {      // same (piece, thread) decomposition as the CUDA kernel
         for (int f = 0; f < a.n_frames; ++f)
             for (int k = 0; k < 3; ++k)
