@@ -259,6 +259,7 @@ def main():
     run_host(args.steps)
     e2e_s = time.perf_counter() - t0
     stream_bytes = int(sum(e.stats()[:, 3].sum() for e in encs))   # the step's result as read on the host
+    d2h_bytes = int(sum(e.record_bytes() for e in encs))
     e2e = world * NSEG * SEG_FRAMES * args.steps / farm.max_over_ranks(e2e_s, "cuda")
 
     if rank == 0:
@@ -293,7 +294,7 @@ def main():
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": CONFIG,
                 "wall_ms_per_step": wall_ms / args.steps,
                 "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": NSEG * SEG_FRAMES * fb,
-                        "d2h_bytes_per_step": NSEG * (SEG_FRAMES * NMB * (26 * 16 * 2 + 4 + 24) + NMB),
+                        "d2h_bytes_per_step": d2h_bytes,
                         "stream_bytes_per_step": stream_bytes, "host_threads": cores},
                 "gpu_launches": launches * NSEG, "clocks": clocks,
                 "roofline": {"kernel": dom, "bound": "hbm", "achieved": d["achieved_gbs"], "peak": peak, "unit": "GB/s",

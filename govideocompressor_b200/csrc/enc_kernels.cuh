@@ -266,6 +266,65 @@ GVC_HD int zigzag4(int i) {   // raster index of the i-th coefficient in frame z
     return (int)((z >> (4 * i)) & 15);
 }
 
+// ------------------------------------------------------------------ 8x8 transform path ----------
+// x264 sub8x8_dct8 / add8x8_idct8 butterflies (H.264 8.5.13), one 1-D pass over 8 values with stride `s`.
+GVC_HD void dct8_1d(int *d, int s) {
+    const int s07 = d[0] + d[7 * s], s16 = d[s] + d[6 * s], s25 = d[2 * s] + d[5 * s], s34 = d[3 * s] + d[4 * s];
+    const int a0 = s07 + s34, a1 = s16 + s25, a2 = s07 - s34, a3 = s16 - s25;
+    const int d07 = d[0] - d[7 * s], d16 = d[s] - d[6 * s], d25 = d[2 * s] - d[5 * s], d34 = d[3 * s] - d[4 * s];
+    const int a4 = d16 + d25 + (d07 + (d07 >> 1)), a5 = d07 - d34 - (d25 + (d25 >> 1));
+    const int a6 = d07 + d34 - (d16 + (d16 >> 1)), a7 = d16 - d25 + (d34 + (d34 >> 1));
+    d[0] = a0 + a1; d[s] = a4 + (a7 >> 2); d[2 * s] = a2 + (a3 >> 1); d[3 * s] = a5 + (a6 >> 2);
+    d[4 * s] = a0 - a1; d[5 * s] = a6 - (a5 >> 2); d[6 * s] = (a2 >> 1) - a3; d[7 * s] = (a4 >> 2) - a7;
+}
+GVC_HD void idct8_1d(int *d, int s) {
+    const int a0 = d[0] + d[4 * s], a2 = d[0] - d[4 * s];
+    const int a4 = (d[2 * s] >> 1) - d[6 * s], a6 = (d[6 * s] >> 1) + d[2 * s];
+    const int b0 = a0 + a6, b2 = a2 + a4, b4 = a2 - a4, b6 = a0 - a6;
+    const int a1 = -d[3 * s] + d[5 * s] - d[7 * s] - (d[7 * s] >> 1), a3 = d[s] + d[7 * s] - d[3 * s] - (d[3 * s] >> 1);
+    const int a5 = -d[s] + d[7 * s] + d[5 * s] + (d[5 * s] >> 1), a7 = d[3 * s] + d[5 * s] + d[s] + (d[s] >> 1);
+    const int b1 = (a7 >> 2) + a1, b3 = a3 + (a5 >> 2), b5 = (a3 >> 2) - a5, b7 = a7 - (a1 >> 2);
+    d[0] = b0 + b7; d[s] = b2 + b5; d[2 * s] = b4 + b3; d[3 * s] = b6 + b1;
+    d[4 * s] = b6 - b1; d[5 * s] = b4 - b3; d[6 * s] = b2 - b5; d[7 * s] = b0 - b7;
+}
+GVC_HD int coef8_class(int i) {     // x264 quant8_scan by (row & 3, col & 3): 0,3,4,3, 3,1,5,1, 4,5,2,5, 3,1,5,1 packed 4 bits each
+    return (int)((0x1513525415133430ull >> (4 * (((i >> 3) & 3) * 4 + (i & 3)))) & 15);
+}
+struct Transform8Args {
+    const uint8_t *src, *pred;
+    uint8_t       *rec;
+    int            sstride, pstride, rstride, bw, bh;   // bw x bh blocks of 8x8
+    Quant8Params   q;
+    int16_t       *coefs;        // 64 levels per block, raster (row = vertical frequency)
+    uint8_t       *nz;           // per block
+};
+// one thread = one 8x8 block: residual, forward transform, quant, levels out, dequant, inverse, reconstruction
+GVC_HD void transform8x8_block(const Transform8Args &a, int bx, int by) {
+    int d[64];
+    const uint8_t *s = a.src + (long long)(8 * by) * a.sstride + 8 * bx, *p = a.pred + (long long)(8 * by) * a.pstride + 8 * bx;
+    for (int y = 0; y < 8; ++y)
+        for (int x = 0; x < 8; ++x) d[y * 8 + x] = (int)s[(long long)y * a.sstride + x] - (int)p[(long long)y * a.pstride + x];
+    for (int y = 0; y < 8; ++y) dct8_1d(d + 8 * y, 1);
+    for (int x = 0; x < 8; ++x) dct8_1d(d + x, 8);
+    int16_t *co = a.coefs + (long long)(by * a.bw + bx) * 64;
+    int      nz = 0;
+    const int qbits = a.q.qp / 6 - 6;
+    for (int i = 0; i < 64; ++i) {
+        const int cls = coef8_class(i);
+        const int l = quant_one((int)(int16_t)d[i], a.q.mf[cls], a.q.bias[cls]);
+        co[i] = (int16_t)l;
+        nz |= l;
+        const int v = qbits >= 0 ? (l * a.q.dq[cls]) * (1 << qbits) : (l * a.q.dq[cls] + (1 << (-qbits - 1))) >> (-qbits);
+        d[i] = (int)(int16_t)v;
+    }
+    a.nz[by * a.bw + bx] = nz != 0;
+    for (int y = 0; y < 8; ++y) idct8_1d(d + 8 * y, 1);
+    for (int x = 0; x < 8; ++x) idct8_1d(d + x, 8);
+    uint8_t *r = a.rec + (long long)(8 * by) * a.rstride + 8 * bx;
+    for (int y = 0; y < 8; ++y)
+        for (int x = 0; x < 8; ++x) r[(long long)y * a.rstride + x] = (uint8_t)clip_u8((int)p[(long long)y * a.pstride + x] + ((d[y * 8 + x] + 32) >> 6));
+}
+
 // SATD contribution of one 4x4 block: sum |H D H| (always even; callers halve per x264's 8x4 pairing)
 GVC_HD int hadamard4_abs(const int d[16]) {
     int t[16], s = 0;

@@ -38,6 +38,13 @@ struct QuantParams {
     int lambda;                  // motion-cost lambda (x264_lambda_tab[qp])
 };
 
+// 8x8 transform (High-profile transform_size_8x8): quantiser constants by coefficient class
+// (class = table[(row&3)*4 + (col&3)], H.264 8.5.9 / x264 quant8_scan).
+struct Quant8Params {
+    int qp;
+    int mf[6], bias[6], dq[6];
+};
+
 // Per-macroblock side information produced by motion search / mode decision.
 struct MbMotion {
     int16_t mv[4][2];   // quarter-sample vectors of the four 8x8 partitions (all equal for 16x16)

@@ -45,6 +45,11 @@ __global__ void __launch_bounds__(kHpThreads) hpel_kernel(const __grid_constant_
     hpel_phase_c(threadIdx.x, a, x0, y0, sm);
 }
 
+__global__ void __launch_bounds__(128) transform8x8_kernel(const __grid_constant__ Transform8Args a) {
+    const int b = blockIdx.x * 128 + threadIdx.x;
+    if (b < a.bw * a.bh) transform8x8_block(a, b % a.bw, b / a.bw);
+}
+
 constexpr int kMbWarps = 4;   // macroblocks (warps) per CTA in the per-MB kernels
 
 __global__ void __launch_bounds__(32 * kMbWarps) me_lowres_kernel(const __grid_constant__ MeLowArgs a) {
@@ -298,6 +303,21 @@ int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
     a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.progress = row_progress;
     a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
     return launch_encode_intra(a, static_cast<cudaStream_t>(stream));
+}
+
+int gvc_transform8x8(const uint8_t *src, int sstride, const uint8_t *pred, int pstride, uint8_t *rec, int rstride, int w, int h, int qp,
+                     int intra, int16_t *coefs, uint8_t *nz, void *stream) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!src || !pred || !rec || !coefs || !nz || w < 8 || h < 8 || (w & 7) || (h & 7)) { set_error("gvc_transform8x8: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    if (qp < 0 || qp > 51) { set_error("gvc_transform8x8: qp %d outside 0..51", qp); return GVC_ERR_INVALID_ARG; }
+    Transform8Args a;
+    a.src = src; a.pred = pred; a.rec = rec; a.sstride = sstride; a.pstride = pstride; a.rstride = rstride; a.bw = w / 8; a.bh = h / 8;
+    fill_quant8_params(a.q, qp, intra != 0);
+    a.coefs = coefs; a.nz = nz;
+    transform8x8_kernel<<<(a.bw * a.bh + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    GVC_CUDA(cudaGetLastError());
+    return GVC_OK;
 }
 
 int gvc_lambda_for_qp(int qp) { return lambda_for_qp(qp); }

@@ -300,6 +300,8 @@ int gvc_encoder_stats(gvc_encoder *e, int *stats4_per_picture, int n_pictures) {
     return GVC_OK;
 }
 
+long long gvc_encoder_record_bytes(gvc_encoder *e) { return e && e->seg ? (long long)e->seg->record_bytes() : -1; }
+
 int gvc_encoder_write_mp4(gvc_encoder *e, const char *path) {
     if (!e || !path || e->out.au_size.empty()) { set_error("gvc_encoder_write_mp4: nothing encoded"); return GVC_ERR_INVALID_ARG; }
     std::vector<Mp4Sample> samples;

@@ -104,8 +104,9 @@ public:
         h_motion_ = static_cast<MbMotion *>(ops_.alloc_host(sizeof(MbMotion) * nmb * n_frames));
         h_modes_  = static_cast<uint8_t *>(ops_.alloc_host(nmb));
         h_done_   = static_cast<int *>(ops_.alloc_host(sizeof(int) * n_frames));
+        h_counters_ = static_cast<unsigned *>(ops_.alloc_host(sizeof(unsigned) * n_frames));
         bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_coefs_ && d_nz_ && d_motion_ && d_modes_ && d_lowmv_ && d_prog_ && d_one_ &&
-                  h_blocks_ && d_offsets_ && d_counters_ && h_offsets_ && h_nz_ && h_motion_ && h_modes_ && h_done_;
+                  h_blocks_ && d_offsets_ && d_counters_ && h_counters_ && h_offsets_ && h_nz_ && h_motion_ && h_modes_ && h_done_;
         for (int i = 0; i < 2; ++i) {
             for (int k = 0; k < 4; ++k) ok = ok && rec_y_[i][k];
             ok = ok && rec_u_[i] && rec_v_[i] && rec_low_[i];
@@ -117,7 +118,14 @@ public:
         return 0;
     }
     CurFrames cur_frames() const { return cur_; }
-    void set_frame_count(int n) { n_ = n; }   // when the kernels of an n-picture segment are replayed from a captured graph
+    void set_frame_count(int n) { n_ = n; }
+    // bytes that crossed PCIe towards the host for the last finished segment: packed blocks + per-macroblock tables + flags
+    size_t record_bytes() const {
+        size_t blocks = 0;
+        for (int f = 0; f < n_; ++f) blocks += h_counters_[f];
+        const size_t nmb = size_t(g_.mbw) * g_.mbh;
+        return blocks * 32 + size_t(n_) * (nmb * (4 + 4) + 8) + size_t(n_ - 1) * nmb * sizeof(MbMotion) + nmb;
+    }   // when the kernels of an n-picture segment are replayed from a captured graph
 
     // Host-side reset of the per-picture arrival flags; call before issuing (or replaying) a segment's kernels.
     void begin_segment(int n) {
@@ -182,6 +190,7 @@ public:
                 if ((rc = ops_.download(h_nz_ + nmb * f, d_nz_ + nmb * f, sizeof(uint32_t) * nmb))) return rc;
                 if (f == 0) { if ((rc = ops_.download(h_modes_, d_modes_, nmb))) return rc; }
                 else if ((rc = ops_.download(h_motion_ + nmb * f, d_motion_ + nmb * f, sizeof(MbMotion) * nmb))) return rc;
+                if ((rc = ops_.download(h_counters_ + f, d_counters_ + f, sizeof(unsigned)))) return rc;
                 if ((rc = ops_.download(h_done_ + f, d_one_, sizeof(int)))) return rc;
             }
             if (cfg_.keep_recon) {
@@ -304,7 +313,7 @@ private:
         }
         rel(d_coefs_); rel(d_nz_); rel(d_motion_); rel(d_modes_); rel(d_lowmv_); rel(d_prog_); rel(d_one_);
         auto relh = [&](auto *&p) { if (p) ops_.release_host(p); p = nullptr; };
-        rel(d_offsets_); rel(d_counters_); relh(h_offsets_);
+        rel(d_offsets_); rel(d_counters_); relh(h_offsets_); relh(h_counters_);
         relh(h_blocks_); relh(h_nz_); relh(h_motion_); relh(h_modes_); relh(h_done_);
         cap_ = 0;
     }
@@ -327,7 +336,7 @@ private:
     int          *d_one_ = nullptr;
     int16_t      *h_blocks_ = nullptr;    // pinned + device-mapped: the nonzero blocks of every picture, packed
     uint32_t     *d_offsets_ = nullptr, *h_offsets_ = nullptr;   // per MB: first packed block
-    unsigned     *d_counters_ = nullptr;                          // per picture: blocks handed out
+    unsigned     *d_counters_ = nullptr, *h_counters_ = nullptr;   // per picture: blocks handed out
     uint32_t     *h_nz_ = nullptr;
     MbMotion     *h_motion_ = nullptr;
     uint8_t      *h_modes_ = nullptr;

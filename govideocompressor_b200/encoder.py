@@ -34,6 +34,8 @@ def _bind(lib):
     lib.gvc_encoder_recon.argtypes = [vp, vp, ctypes.c_size_t]
     lib.gvc_encoder_stats.argtypes = [vp, vp, ci]
     lib.gvc_encoder_write_mp4.argtypes = [vp, ctypes.c_char_p]
+    lib.gvc_encoder_record_bytes.argtypes = [vp]
+    lib.gvc_encoder_record_bytes.restype = ctypes.c_longlong
     lib.gvc_encoder_set_timing.argtypes = [vp, ci]
     lib.gvc_encoder_stage_times.argtypes = [vp, vp, vp]
     lib.gvc_transcode_file.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
@@ -121,6 +123,9 @@ class Encoder:
         ms, n = (ctypes.c_double * 8)(), (ctypes.c_int * 8)()
         _lib.check(self._lib.gvc_encoder_stage_times(self._h, ms, n), "gvc_encoder_stage_times")
         return {s: (ms[i], n[i]) for i, s in enumerate(self.STAGES)}
+
+    def record_bytes(self):
+        return int(self._lib.gvc_encoder_record_bytes(self._h))
 
     def write_mp4(self, path):
         _lib.check(self._lib.gvc_encoder_write_mp4(self._h, os.fsencode(path)), "gvc_encoder_write_mp4")

@@ -54,6 +54,7 @@ def load_library():
     lib.gvc_me_refine.argtypes = [vp, vp] + [c_int] * 3 + [vp, c_int, vp, vp]
     lib.gvc_encode_inter.argtypes = [vp] * 7 + [c_int] * 4 + [vp, c_int, vp, vp, vp]
     lib.gvc_encode_intra.argtypes = [vp] * 6 + [c_int] * 5 + [vp] * 5
+    lib.gvc_transform8x8.argtypes = [vp, c_int, vp, c_int, vp, c_int, c_int, c_int, c_int, c_int, vp, vp, vp]
     lib.gvc_lambda_for_qp.argtypes = [c_int]
     _LIB = lib
     return lib

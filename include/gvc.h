@@ -161,6 +161,11 @@ int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
 int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *cur_v, uint8_t *rec_y, uint8_t *rec_u,
                      uint8_t *rec_v, int sy, int sc, int w16, int h16, int qp, int16_t *coefs, uint32_t *nzmask,
                      uint8_t *modes, int *row_progress, void *stream);
+/* 8x8 transform path (x264 sub8x8_dct8, quant_8x8, dequant_8x8, add8x8_idct8; H.264 8.5.13): residual of src - pred in 8x8
+ * blocks -> levels (64 per block, raster, row = vertical frequency), nz flag per block, reconstruction.  Kernel-level
+ * entry point with oracle parity; the segment encoder writes Constrained-Baseline streams and uses the 4x4 path. */
+int gvc_transform8x8(const uint8_t *src, int sstride, const uint8_t *pred, int pstride, uint8_t *rec, int rstride, int w,
+                     int h, int qp, int intra, int16_t *coefs, uint8_t *nz, void *stream);
 /* x264_lambda_tab[qp] */
 int gvc_lambda_for_qp(int qp);
 
@@ -204,6 +209,8 @@ int gvc_encoder_stats(gvc_encoder *enc, int *stats4_per_picture, int n_pictures)
 #define GVC_STAGES 8
 int gvc_encoder_set_timing(gvc_encoder *enc, int on);
 int gvc_encoder_stage_times(gvc_encoder *enc, double *ms, int *launches);
+/* Bytes the last finished segment sent device -> host (packed nonzero blocks + per-macroblock tables). */
+long long gvc_encoder_record_bytes(gvc_encoder *enc);
 /* Muxes the last segment into an MP4 file (temp name + rename). */
 int gvc_encoder_write_mp4(gvc_encoder *enc, const char *path);
 

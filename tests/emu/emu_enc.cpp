@@ -129,6 +129,16 @@ void emu_encode_intra(const uint8_t *const cur[3], uint8_t *const rec[3], int sy
     emu_run_encode_intra(a);
 }
 
+void emu_transform8x8(const uint8_t *src, int sstride, const uint8_t *pred, int pstride, uint8_t *rec, int rstride, int w, int h, int qp,
+                      int intra, int16_t *coefs, uint8_t *nz) {
+    Transform8Args a;
+    a.src = src; a.pred = pred; a.rec = rec; a.sstride = sstride; a.pstride = pstride; a.rstride = rstride; a.bw = w / 8; a.bh = h / 8;
+    fill_quant8_params(a.q, qp, intra != 0);
+    a.coefs = coefs; a.nz = nz;
+    for (int by = 0; by < a.bh; ++by)
+        for (int bx = 0; bx < a.bw; ++bx) transform8x8_block(a, bx, by);
+}
+
 // quantiser constants as the product computes them: out[0..2]=mf_y, [3..5]=bias_y, [6..8]=dq_y, [9..11]=mf_c, [12..14]=bias_c,
 // [15..17]=dq_c, [18]=qpc, [19]=lambda
 void emu_quant_params(int qp, int intra, int out[20]) {

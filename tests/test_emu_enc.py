@@ -131,3 +131,28 @@ def test_encode_intra_frame(pair, qp):
     assert mo[0] == 2 and set(mo[1:g["mbw"]]) <= {1, 2}          # first MB: DC only; first row: no vertical
     err = np.mean((reco[0].astype(float) - cur.Y.inner()) ** 2)
     assert err < {10: 2.5, 23: 14.0, 38: 140.0}[qp]
+
+
+@pytest.mark.parametrize("qp,intra", [(0, 1), (18, 0), (23, 1), (37, 0), (51, 0)])
+def test_transform8x8_path(qp, intra):
+    """8x8 transform / quant / dequant / reconstruction kernel body against the oracle (x264 sub8x8_dct8 ... add8x8_idct8)."""
+    rng = np.random.Generator(np.random.PCG64(qp))
+    w, h = 48, 32
+    src = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    pred = np.clip(src.astype(int) + rng.integers(-40, 41, (h, w)), 0, 255).astype(np.uint8)
+    rec = np.zeros((h, w), np.uint8)
+    coefs = np.zeros((h // 8) * (w // 8) * 64, np.int16)
+    nz = np.zeros((h // 8) * (w // 8), np.uint8)
+    emu_lib.load().emu_transform8x8(_vp(src.ctypes.data), w, _vp(pred.ctypes.data), w, _vp(rec.ctypes.data), w, w, h, qp, intra,
+                                    _vp(coefs.ctypes.data), _vp(nz.ctypes.data))
+    mf, bias = oracle_lib.quant8_tables(qp, intra)
+    k = 0
+    for by in range(h // 8):
+        for bx in range(w // 8):
+            s, p = src[8 * by:8 * by + 8, 8 * bx:8 * bx + 8], pred[8 * by:8 * by + 8, 8 * bx:8 * bx + 8]
+            q, flag = oracle_lib.quant(oracle_lib.sub_dct(s, p, 8), mf, bias)
+            np.testing.assert_array_equal(coefs[64 * k:64 * k + 64], q)
+            assert nz[k] == flag
+            want = oracle_lib.add_idct(p, oracle_lib.dequant(q.reshape(8, 8), qp, 8), 8)
+            np.testing.assert_array_equal(rec[8 * by:8 * by + 8, 8 * bx:8 * bx + 8], want)
+            k += 1

@@ -121,3 +121,37 @@ def test_encode_intra_frame(pair, qp):
     np.testing.assert_array_equal(nzo, nzg)
     for x, y in zip(reco, recg):
         np.testing.assert_array_equal(x, y)
+
+
+@pytest.mark.parametrize("qp,intra", [(0, 1), (23, 0), (38, 1), (51, 0)])
+def test_transform8x8_path(dev, qp, intra):
+    import torch
+    rng = np.random.Generator(np.random.PCG64(100 + qp))
+    w, h = 1280, 720
+    src = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    pred = np.clip(src.astype(int) + rng.integers(-40, 41, (h, w)), 0, 255).astype(np.uint8)
+    ds, dp = torch.from_numpy(src).cuda(), torch.from_numpy(pred).cuda()
+    dr = torch.zeros((h, w), dtype=torch.uint8, device="cuda")
+    nb = (h // 8) * (w // 8)
+    dco = torch.zeros(nb * 64, dtype=torch.int16, device="cuda")
+    dnz = torch.zeros(nb, dtype=torch.uint8, device="cuda")
+    dev.check(dev.lib.gvc_transform8x8(_vp(ds.data_ptr()), w, _vp(dp.data_ptr()), w, _vp(dr.data_ptr()), w, w, h, qp, intra,
+                                       _vp(dco.data_ptr()), _vp(dnz.data_ptr()), None))
+    torch.cuda.synchronize()
+    rec, coefs, nz = dr.cpu().numpy(), dco.cpu().numpy(), dnz.cpu().numpy()
+    import emu_lib
+    rec2 = np.zeros_like(rec)
+    co2 = np.zeros_like(coefs)
+    nz2 = np.zeros_like(nz)
+    emu_lib.load().emu_transform8x8(_vp(src.ctypes.data), w, _vp(pred.ctypes.data), w, _vp(rec2.ctypes.data), w, w, h, qp, intra,
+                                    _vp(co2.ctypes.data), _vp(nz2.ctypes.data))           # emulation == oracle is a CPU test
+    np.testing.assert_array_equal(coefs, co2)
+    np.testing.assert_array_equal(nz, nz2)
+    np.testing.assert_array_equal(rec, rec2)
+    mf, bias = oracle_lib.quant8_tables(qp, intra)                                        # spot-check blocks against the oracle directly
+    for k in (0, 777, nb - 1):
+        by, bx = divmod(k, w // 8)
+        s, p = src[8 * by:8 * by + 8, 8 * bx:8 * bx + 8], pred[8 * by:8 * by + 8, 8 * bx:8 * bx + 8]
+        q, _ = oracle_lib.quant(oracle_lib.sub_dct(s, p, 8), mf, bias)
+        np.testing.assert_array_equal(coefs[64 * k:64 * k + 64], q)
+        np.testing.assert_array_equal(rec[8 * by:8 * by + 8, 8 * bx:8 * bx + 8], oracle_lib.add_idct(p, oracle_lib.dequant(q.reshape(8, 8), qp, 8), 8))

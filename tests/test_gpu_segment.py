@@ -125,53 +125,23 @@ def test_transcode_file_and_convert_conventions(gvc, tmp_path):
         os.chdir(cwd)
 
 
-def test_segment_reconstruction_equals_the_oracle_pipeline(gvc):
-    """The GPU pipeline end to end (resize -> ... -> reconstruction) against the same path composed from the CPU
-    oracle, at the BASELINE sizes: 4 pictures 1920x1080 -> 1280x720."""
+@pytest.mark.parametrize("sw,sh,w,h,n,merange", [(1920, 1080, 1280, 720, 4, 16),      # cfg2
+                                                  (3840, 2160, 1920, 1080, 3, 32),     # cfg3: 4K -> 1080p, me_range 32
+                                                  (1280, 720, 854, 480, 4, 16)],       # cfg4: 720p -> 480p (coded 864x480)
+                         ids=["cfg2", "cfg3", "cfg4"])
+def test_segment_reconstruction_equals_the_oracle_pipeline(gvc, sw, sh, w, h, n, merange):
+    """The GPU pipeline end to end (resize -> ... -> reconstruction) against the same path composed from the CPU oracle,
+    at the sizes BASELINE.json names; the stream also decodes to that reconstruction."""
     import oracle_segment
-    sw, sh, w, h, n = 1920, 1080, 1280, 720, 4
-    frames = S.moving_sequence(sw, sh, n, seed=6, noise=2)
-    enc = gvc.Encoder(sw, sh, w, h, crf=23, keep_recon=True)
-    enc.encode_host(frames, annexb=True)
+    frames = S.moving_sequence(sw, sh, n, seed=6, noise=2, fast=merange > 16)
+    enc = gvc.Encoder(sw, sh, w, h, crf=23, merange=merange, keep_recon=True)
+    stream = enc.encode_host(frames, annexb=True)
     recon = enc.recon()
-    ref = oracle_segment.encode_segment(frames, sw, sh, w, h, qp_i=20, qp_p=23)
+    ref = oracle_segment.encode_segment(frames, sw, sh, w, h, qp_i=20, qp_p=23, merange=merange)
     for f in range(n):
         ry, ru, rv = S.split_i420(recon[f], enc.w16, enc.h16)
         np.testing.assert_array_equal(ry, ref["recon"][f][0], err_msg=f"picture {f}")
         np.testing.assert_array_equal(ru, ref["recon"][f][1])
         np.testing.assert_array_equal(rv, ref["recon"][f][2])
+    check_decode(enc, stream, recon, w, h, n)
     enc.close()
-
-
-def test_mp4_pieces_through_the_worker_loop(gvc, tmp_path):
-    """The reference flow end to end on one box: pieces named <id>.mp4 holding H.264 (like the splitter's output), handed out
-    by the dispatcher double, converted by convert() = libgvc (host demux/decode by FFmpeg's libraries, GPU resize + encode),
-    uploaded under their original names; the concatenation of the results decodes cleanly."""
-    cv2 = pytest.importorskip("cv2")
-    from govideocompressor_b200 import worker
-    from protocol_twin import FakeServer
-    w, h, n, pieces = 320, 180, 10, 3
-    src, dst, work = (os.path.join(tmp_path, x) for x in ("www", "ftp", "work"))
-    os.makedirs(os.path.join(src, "12clip"))
-    os.makedirs(work)
-    for i in range(pieces):                     # source pieces: H.264 in MP4, made with our own encoder at high quality
-        frames = S.moving_sequence(w, h, n, seed=20 + i)
-        enc = gvc.Encoder(w, h, crf=10, fps=(25, 1))
-        enc.encode_host(frames)
-        enc.write_mp4(os.path.join(src, "12clip", f"{i}.mp4"))
-        enc.close()
-    server = FakeServer("12clip", pieces, "-threads 4 -vcodec libx264 -crf 26 -s 160x90")
-    done = worker.run_worker(server.addr, gvc.convert, worker.local_fetch(src), worker.local_store(dst), work)
-    assert server.join() and done == ["success;2", "success;1", "success;0"]
-    total = 0
-    for i in range(pieces):
-        out = os.path.join(dst, "12clip", f"{i}.mp4")
-        cap = cv2.VideoCapture(out)
-        assert cap.isOpened() and int(cap.get(cv2.CAP_PROP_FRAME_WIDTH)) == 160 and abs(cap.get(cv2.CAP_PROP_FPS) - 25) < 1e-3
-        k = 0
-        while cap.read()[0]:
-            k += 1
-        assert k == n
-        total += k
-        assert "frame=" in open(os.path.join(dst, "12clip", f"c{i}.mp4.log")).read()
-    assert total == pieces * n
