@@ -124,6 +124,50 @@ GVC_HD bool border_piece_xy(const BorderBatchArgs &a, int k, int id, int tid, in
     return x < a.x_hi[k] && y < a.y_hi[k];
 }
 
+// Vector variant: 16 samples per lane.  Usable for a plane whose picture width, padded extents, pitch and base address
+// are multiples of 16 (every BASELINE size); a piece is one warp = 32 groups of 16 samples.
+GVC_HDH bool border16_ok(const BorderBatchArgs &a) {
+    for (int k = 0; k < 3; ++k)
+        if (((a.w[k] | a.x_lo[k] | a.x_hi[k] | a.stride[k]) & 15) || (((unsigned long long)a.p[k] | a.frame_stride[k]) & 15)) return false;
+    return true;
+}
+GVC_HDH int border16_pieces(const BorderBatchArgs &a, int k) {
+    const int gf = (a.x_hi[k] - a.x_lo[k]) >> 4, gs = gf - (a.w[k] >> 4);
+    return ((a.y_hi[k] - a.y_lo[k]) - a.h[k]) * ((gf + 31) >> 5) + a.h[k] * ((gs + 31) >> 5);
+}
+GVC_HD bool border16_piece_xy(const BorderBatchArgs &a, int k, int id, int lane, int &x, int &y) {
+    const int gf = (a.x_hi[k] - a.x_lo[k]) >> 4, gs = gf - (a.w[k] >> 4);
+    const int segs_a = (gf + 31) >> 5, segs_b = (gs + 31) >> 5;
+    const int rows_out = (a.y_hi[k] - a.y_lo[k]) - a.h[k], n_a = rows_out * segs_a;
+    int g;
+    if (id < n_a) {
+        const int r = id / segs_a;
+        g = (id - r * segs_a) * 32 + lane;
+        y = r < -a.y_lo[k] ? a.y_lo[k] + r : a.h[k] + (r + a.y_lo[k]);
+        x = a.x_lo[k] + 16 * g;
+    } else {
+        id -= n_a;
+        if (segs_b == 0) return false;
+        y = id / segs_b;
+        if (y >= a.h[k]) return false;
+        g = (id - y * segs_b) * 32 + lane;
+        const int left = (-a.x_lo[k]) >> 4;
+        x = g < left ? a.x_lo[k] + 16 * g : a.w[k] + 16 * (g - left);
+    }
+    return x < a.x_hi[k] && y < a.y_hi[k];
+}
+GVC_HD void extend_border_16(uint8_t *p, int stride, int w, int h, int x, int y) {   // 16 samples at (x..x+15, y), x % 16 == 0
+    const uint8_t *row = p + (long long)iclamp(y, 0, h - 1) * stride;
+    gvc_uint4 v;
+    if (x >= 0 && x < w) {
+        v = *reinterpret_cast<const gvc_uint4 *>(row + x);
+    } else {
+        const unsigned b = (unsigned)row[x < 0 ? 0 : w - 1] * 0x01010101u;
+        v.x = v.y = v.z = v.w = b;
+    }
+    *reinterpret_cast<gvc_uint4 *>(p + (long long)y * stride + x) = v;
+}
+
 struct LowresBatchArgs {
     const uint8_t *src; uint8_t *dst;
     int sstride, dstride, x_lo, x_hi, y_lo, y_hi, lx_lo, lx_hi, ly_lo, ly_hi;   // x_hi / y_hi inclusive maxima of readable source coordinates
@@ -389,7 +433,6 @@ struct MeRefArgs {
 };
 struct MeRefSmem {               // per warp
     unsigned key[5][32];
-    int      part[32];
     int      center[5][2], best_mv[5][2], best_cost[5];
 };
 GVC_HD void sq8(int i, int &dx, int &dy) {   // (0,-1),(0,1),(-1,0),(1,0),(-1,-1),(-1,1),(1,-1),(1,1)
@@ -463,9 +506,8 @@ GVC_HD void me_ref_pick(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem 
     }
     cx = iclamp(cx, -x0 - (kEncPad - 8), a.w16 - x0 - 16 + (kEncPad - 8));
     cy = iclamp(cy, -y0 - (kEncPad - 8), a.h16 - y0 - 16 + (kEncPad - 8));
-    sm.center[lane][0] = sm.best_mv[lane][0] = 4 * cx;
-    sm.center[lane][1] = sm.best_mv[lane][1] = 4 * cy;
-    sm.best_cost[lane] = 0x7fffffff;
+    sm.center[lane][0] = 4 * cx;
+    sm.center[lane][1] = 4 * cy;
 }
 // lane -> (partition P, 4x4 block offset inside the MB): lanes 0..15 the 16x16 partition, 16..31 the four 8x8s
 GVC_HD void me_lane_block(int lane, int &P, int &ox, int &oy) {
@@ -473,13 +515,16 @@ GVC_HD void me_lane_block(int lane, int &P, int &ox, int &oy) {
     else { const int l = lane - 16, k = l >> 2, j = l & 3; P = 1 + k; ox = 8 * (k & 1) + 4 * (j & 1); oy = 8 * (k >> 1) + 4 * (j >> 1); }
 }
 // Per-lane state that stays in registers across the 17 sub-pel candidates: the lane's 4x4 source block, its offset in
-// the planes and the predictor (the emulation harness keeps one record per lane).
+// the planes, the predictor, and the running best / search centre of the lane's partition (every lane of a partition
+// carries the same best: no shared-memory round trip or leader election per candidate).  The emulation harness keeps one
+// record per lane.
 struct MeLane {
     int       P, ox, oy, px, py;
     long long base;      // (16*my + oy) * stride + 16*mx + ox
     int       cur[16];
+    int       cx, cy, bx, by, bcost;
 };
-GVC_HD void me_lane_init(int lane, const MeRefArgs &a, int mx, int my, MeLane &L) {
+GVC_HD void me_lane_init(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm, MeLane &L) {
     me_lane_block(lane, L.P, L.ox, L.oy);
     me_mvp(a, mx, my, L.px, L.py);
     L.base = (long long)(16 * my + L.oy) * a.stride + 16 * mx + L.ox;
@@ -488,12 +533,15 @@ GVC_HD void me_lane_init(int lane, const MeRefArgs &a, int mx, int my, MeLane &L
         const unsigned w = ld_u32_any(c + (long long)j * a.stride);
         for (int i = 0; i < 4; ++i) L.cur[j * 4 + i] = byte_of(w, i);
     }
+    L.cx = L.bx = sm.center[L.P][0];
+    L.cy = L.by = sm.center[L.P][1];
+    L.bcost = 0x7fffffff;
 }
-// sub-pel candidate ci (-1 = the centre itself) at `step`: each lane's 4x4 Hadamard sum -> sm.part
-GVC_HD void me_ref_satd(int lane, const MeRefArgs &a, const MeLane &L, int ci, int step, MeRefSmem &sm) {
+// sub-pel candidate ci (-1 = the centre itself) at `step`: the lane's 4x4 Hadamard sum (already halved)
+GVC_HD int me_ref_satd(const MeRefArgs &a, const MeLane &L, int ci, int step) {
     int dx = 0, dy = 0;
     if (ci >= 0) sq8(ci, dx, dy);
-    const int mvx = sm.center[L.P][0] + dx * step, mvy = sm.center[L.P][1] + dy * step;
+    const int mvx = L.cx + dx * step, mvy = L.cy + dy * step;
     const int fx = mvx & 3, fy = mvy & 3, q = fy * 4 + fx;
     const long long off = L.base + (long long)(mvy >> 2) * a.stride + (mvx >> 2);
     const int s0 = (int)((kQpelRef0 >> (2 * q)) & 3), s1 = (int)((kQpelRef1 >> (2 * q)) & 3);
@@ -507,20 +555,37 @@ GVC_HD void me_ref_satd(int lane, const MeRefArgs &a, const MeLane &L, int ci, i
         if (two) { w = avg_u8x4(w, ld_u32_any(p2)); p2 += a.stride; }
         for (int i = 0; i < 4; ++i) d[j * 4 + i] = L.cur[j * 4 + i] - byte_of(w, i);
     }
-    sm.part[lane] = hadamard4_abs(d) >> 1;
+    return hadamard4_abs(d) >> 1;
 }
-GVC_HD void me_ref_update(int lane, const MeRefArgs &a, const MeLane &L, int ci, int step, MeRefSmem &sm) {
-    const bool leader = lane == 0 || (lane >= 16 && ((lane - 16) & 3) == 0);
-    if (!leader) return;
+// `total` = SATD of the lane's whole partition for this candidate (sum of its lanes' partials).  Keeps the best; after the
+// last candidate of a step the best becomes the next search centre.
+GVC_HD void me_ref_take(const MeRefArgs &a, MeLane &L, int total, int ci, int step) {
     int dx = 0, dy = 0;
     if (ci >= 0) sq8(ci, dx, dy);
-    const int P = L.P, mvx = sm.center[P][0] + dx * step, mvy = sm.center[P][1] + dy * step;
-    int total = 0;
-    const int n = P == 0 ? 16 : 4;
-    for (int i = 0; i < n; ++i) total += sm.part[lane + i];
+    const int mvx = L.cx + dx * step, mvy = L.cy + dy * step;
     const int cost = total + a.lambda * mv_bits(mvx, mvy, L.px, L.py);
-    if (cost < sm.best_cost[P]) { sm.best_cost[P] = cost; sm.best_mv[P][0] = mvx; sm.best_mv[P][1] = mvy; }
-    if (ci == 7) { sm.center[P][0] = sm.best_mv[P][0]; sm.center[P][1] = sm.best_mv[P][1]; }
+    if (cost < L.bcost) { L.bcost = cost; L.bx = mvx; L.by = mvy; }
+    if (ci == 7) { L.cx = L.bx; L.cy = L.by; }
+}
+// first lane of the partition the lane belongs to, and the number of lanes in it
+GVC_HD void me_group(int lane, int &first, int &count) {
+    if (lane < 16) { first = 0; count = 16; } else { first = lane & ~3; count = 4; }
+}
+#if !defined(GVC_EMU)
+GVC_HD int me_group_sum(int lane, int v) {     // sum over the lanes of the partition: 16-lane or 4-lane butterfly
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    const int t4 = __shfl_xor_sync(0xffffffffu, v, 4);
+    if (lane < 16) v += t4;
+    const int t8 = __shfl_xor_sync(0xffffffffu, v, 8);
+    if (lane < 16) v += t8;
+    return v;
+}
+#endif
+GVC_HD void me_ref_publish(int lane, const MeLane &L, MeRefSmem &sm) {   // partition leaders hand their result to lane 0
+    const bool leader = lane == 0 || (lane >= 16 && ((lane - 16) & 3) == 0);
+    if (!leader) return;
+    sm.best_mv[L.P][0] = L.bx; sm.best_mv[L.P][1] = L.by; sm.best_cost[L.P] = L.bcost;
 }
 GVC_HD void me_ref_out(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
     if (lane != 0) return;

@@ -28,6 +28,13 @@ __global__ void __launch_bounds__(256) extend_border_batch_kernel(const __grid_c
         extend_border_px(a.p[k] + (size_t)f * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], x, y);
 }
 
+__global__ void __launch_bounds__(256) extend_border16_batch_kernel(const __grid_constant__ BorderBatchArgs a) {
+    const int f = blockIdx.y / 3, k = blockIdx.y - 3 * f;
+    int x, y;
+    if (border16_piece_xy(a, k, blockIdx.x * 8 + (threadIdx.x >> 5), threadIdx.x & 31, x, y))
+        extend_border_16(a.p[k] + (size_t)f * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], x, y);
+}
+
 __global__ void __launch_bounds__(256) lowres_batch_kernel(const __grid_constant__ LowresBatchArgs a) {
     const int lx = a.lx_lo + blockIdx.x * 256 + threadIdx.x, ly = a.ly_lo + blockIdx.y;
     if (lx < a.lx_hi && ly < a.ly_hi)
@@ -73,16 +80,14 @@ __global__ void __launch_bounds__(32 * kMbWarps) me_refine_kernel(const __grid_c
     me_ref_int(lane, a, mx, my, sm);
     __syncwarp();
     me_ref_pick(lane, a, mx, my, sm);
-    MeLane L;
-    me_lane_init(lane, a, mx, my, L);
     __syncwarp();
+    MeLane L;
+    me_lane_init(lane, a, mx, my, sm, L);
     for (int step = 2; step >= 1; --step)
-        for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
-            me_ref_satd(lane, a, L, ci, step, sm);
-            __syncwarp();
-            me_ref_update(lane, a, L, ci, step, sm);
-            __syncwarp();
-        }
+        for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci)
+            me_ref_take(a, L, me_group_sum(lane, me_ref_satd(a, L, ci, step)), ci, step);
+    me_ref_publish(lane, L, sm);
+    __syncwarp();
     me_ref_out(lane, a, mx, my, sm);
 }
 
@@ -148,13 +153,18 @@ int launch_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo,
 }
 int launch_extend_border_batch(const BorderBatchArgs &a, cudaStream_t st) {
     if (a.n_frames < 1) return GVC_OK;
+    const bool vec = border16_ok(a);
     int pieces = 1;                                   // the largest plane decides the grid; smaller planes' extra blocks exit
-    for (int k = 0; k < 3; ++k) pieces = border_pieces(a, k) > pieces ? border_pieces(a, k) : pieces;
+    for (int k = 0; k < 3; ++k) {
+        const int n = vec ? (border16_pieces(a, k) + 7) / 8 : border_pieces(a, k);
+        pieces = n > pieces ? n : pieces;
+    }
     for (int f0 = 0; f0 < a.n_frames; f0 += 16384) {     // gridDim.y <= 65535
         BorderBatchArgs b = a;
         b.n_frames = a.n_frames - f0 < 16384 ? a.n_frames - f0 : 16384;
         for (int k = 0; k < 3; ++k) b.p[k] = a.p[k] + (size_t)f0 * a.frame_stride[k];
-        extend_border_batch_kernel<<<dim3(pieces, b.n_frames * 3), 256, 0, st>>>(b);
+        if (vec) extend_border16_batch_kernel<<<dim3(pieces, b.n_frames * 3), 256, 0, st>>>(b);
+        else     extend_border_batch_kernel<<<dim3(pieces, b.n_frames * 3), 256, 0, st>>>(b);
         GVC_CUDA(cudaGetLastError());
     }
     return GVC_OK;

@@ -26,12 +26,19 @@ void emu_run_me_refine(const MeRefArgs &a) {
             for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) me_ref_pick(l, a, mx, my, sm);
             MeLane L[32];
-            for (int l = 0; l < 32; ++l) me_lane_init(l, a, mx, my, L[l]);
+            for (int l = 0; l < 32; ++l) me_lane_init(l, a, mx, my, sm, L[l]);
             for (int step = 2; step >= 1; --step)
                 for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
-                    for (int l = 0; l < 32; ++l) me_ref_satd(l, a, L[l], ci, step, sm);
-                    for (int l = 0; l < 32; ++l) me_ref_update(l, a, L[l], ci, step, sm);
+                    int part[32];
+                    for (int l = 0; l < 32; ++l) part[l] = me_ref_satd(a, L[l], ci, step);
+                    for (int l = 0; l < 32; ++l) {          // what the shuffle butterfly computes on the GPU
+                        int first, count, total = 0;
+                        me_group(l, first, count);
+                        for (int i = 0; i < count; ++i) total += part[first + i];
+                        me_ref_take(a, L[l], total, ci, step);
+                    }
                 }
+            for (int l = 0; l < 32; ++l) me_ref_publish(l, L[l], sm);
             for (int l = 0; l < 32; ++l) me_ref_out(l, a, mx, my, sm);
         }
 }

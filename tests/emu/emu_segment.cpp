@@ -31,14 +31,22 @@ struct EmuOps {
     int upload(void *dst, const void *src, size_t n) { memcpy(dst, src, n); return 0; }
     void *device_alias(void *h) { return h; }
     int clear(void *p, size_t n) { memset(p, 0, n); return 0; }
-    int extend_border3(const BorderBatchArgs &a) {      // same (piece, thread) decomposition as the CUDA kernel
+    int extend_border3(const BorderBatchArgs &a) {      // same (piece, thread) decompositions as the CUDA kernels
+        const bool vec = border16_ok(a);
         for (int f = 0; f < a.n_frames; ++f)
-            for (int k = 0; k < 3; ++k)
-                for (int id = 0; id < border_pieces(a, k) + 3; ++id)
-                    for (int tid = 0; tid < 256; ++tid) {
-                        int x, y;
-                        if (border_piece_xy(a, k, id, tid, x, y)) extend_border_px(a.p[k] + size_t(f) * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], x, y);
-                    }
+            for (int k = 0; k < 3; ++k) {
+                uint8_t *p = a.p[k] + size_t(f) * a.frame_stride[k];
+                int x, y;
+                if (vec) {
+                    for (int id = 0; id < border16_pieces(a, k) + 9; ++id)
+                        for (int lane = 0; lane < 32; ++lane)
+                            if (border16_piece_xy(a, k, id, lane, x, y)) extend_border_16(p, a.stride[k], a.w[k], a.h[k], x, y);
+                } else {
+                    for (int id = 0; id < border_pieces(a, k) + 3; ++id)
+                        for (int tid = 0; tid < 256; ++tid)
+                            if (border_piece_xy(a, k, id, tid, x, y)) extend_border_px(p, a.stride[k], a.w[k], a.h[k], x, y);
+                }
+            }
         return 0;
     }
     int lowres_batch(const LowresBatchArgs &a) {
