@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <new>
 #include <string>
 #include <thread>
@@ -104,6 +105,8 @@ struct gvc_encoder {
 };
 
 namespace {
+
+std::mutex g_upload_turn;
 
 size_t i420_bytes(int w, int h) { return size_t(w) * h + 2 * size_t((w + 1) / 2) * ((h + 1) / 2); }
 
@@ -278,7 +281,12 @@ int gvc_encoder_encode_host(gvc_encoder *e, const uint8_t *frames_i420, int n_fr
         GVC_CUDA(cudaMalloc((void **)&e->d_src, bytes + 64));
         e->d_src_cap = bytes;
     }
-    GVC_CUDA(cudaMemcpyAsync(e->d_src, frames_i420, bytes, cudaMemcpyHostToDevice, e->ops.st));
+    {   // One upload at a time per process: eight encoders copying at once would each crawl at 1/8 of the PCIe rate and no
+        // GPU work could start until all of them finish; taking turns lets the first segment compute while the next uploads.
+        std::lock_guard<std::mutex> turn(g_upload_turn);
+        GVC_CUDA(cudaMemcpyAsync(e->d_src, frames_i420, bytes, cudaMemcpyHostToDevice, e->ops.st));
+        GVC_CUDA(cudaStreamSynchronize(e->ops.st));
+    }
     if ((rc = issue_segment(e, e->d_src, n_frames))) return rc;
     return gvc_encoder_finish(e, annexb, out, out_len);
 }
