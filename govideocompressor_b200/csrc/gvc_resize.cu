@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(kThreads) resize_fused_kernel(const __grid_con
     const TileGeom       g   = tile_geom(pc, tx, ty);
     const uint8_t       *src = pj.src + (size_t)blockIdx.y * pj.sframe;
     uint8_t             *dst = pj.dst + (size_t)blockIdx.y * pj.dframe;
-    uint4               *S   = smem;
+    unsigned            *S   = reinterpret_cast<unsigned *>(smem);
     int4                *T   = reinterpret_cast<int4 *>(smem + kTileRows * s_chunks_max);
 
     resize_phase0(threadIdx.x, pc, pj, src, g, S);

@@ -76,27 +76,30 @@ GVC_HD TileGeom tile_geom(const PlaneClassDev &pc, int tx, int ty) {
 }
 
 // ---------------------------------------------------------------- phase 0: source tile -> smem --
-// S layout: kTileRows rows x s_chunks chunks of 16 bytes; bytes outside the plane are zero.
+// S layout (word-transposed): S[word * kTileRows + row], word = 4-byte group counted from the tile's first 16-byte
+// chunk.  Lanes <-> source rows both when the tile is written here and when the horizontal pass reads it, so every
+// shared-memory access of a warp touches 32 consecutive words (no bank conflicts, no register shuffling to select the
+// word a tap group starts in).  Bytes outside the plane are zero.
 GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, const uint8_t *src,
-                          const TileGeom &g, gvc_uint4 *S) {
+                          const TileGeom &g, unsigned *S) {
     const int  chunks  = pc.s_chunks;
-    const int  total   = kTileRows * chunks;
     const bool aligned = pj.spix == 1 && ((((unsigned long long)src) | (unsigned)pj.sstride) & 15) == 0;
-    for (int i = tid; i < total; i += kThreads) {
-#if defined(GVC_EMU)
-        const int r = (int)(((unsigned long long)(unsigned)i * (unsigned)pc.s_chunks_magic) >> 32);
-#else
-        const int r = (int)__umulhi((unsigned)i, (unsigned)pc.s_chunks_magic);   // i / chunks without a divide
-#endif
-        const int c = i - r * chunks;
-        const int row = g.r0 + r;
+    const int  warp = tid >> 5, lane = tid & 31;
+    const int  r = (warp & (kRowGroups - 1)) * 32 + lane;            // this lane's source row inside the tile
+    const int  row = g.r0 + r;
+    const bool row_ok = r < g.rows && row < pc.sh;
+    const uint8_t *p = src + (long long)(row_ok ? row : 0) * pj.sstride;
+    for (int c = warp / kRowGroups; c < chunks; c += kWarps / kRowGroups) {
         const int col = (g.qa0 << 2) + (c << 4);       // first source sample of this chunk
         gvc_uint4 v;
         v.x = v.y = v.z = v.w = 0u;
-        if (r < g.rows && row < pc.sh && c < g.nchunks + 1 && col < pc.sw) {
-            const uint8_t *p = src + (long long)row * pj.sstride;
+        if (row_ok && c < g.nchunks + 1 && col < pc.sw) {
             if (aligned && col + 16 <= pc.sw) {
+#if defined(GVC_EMU)
                 v = *reinterpret_cast<const gvc_uint4 *>(p + col);
+#else
+                v = __ldg(reinterpret_cast<const gvc_uint4 *>(p + col));
+#endif
             } else {
                 unsigned w[4] = {0u, 0u, 0u, 0u};
                 for (int b = 0; b < 16; ++b) {
@@ -106,24 +109,22 @@ GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
                 v.x = w[0]; v.y = w[1]; v.z = w[2]; v.w = w[3];
             }
         }
-        S[i] = v;
+        unsigned *d = S + (4 * c) * kTileRows + r;
+        d[0] = v.x; d[kTileRows] = v.y; d[2 * kTileRows] = v.z; d[3 * kTileRows] = v.w;
     }
 }
 
 // ---------------------------------------------------------------- phase 1: horizontal ----------
 // T layout: [quad (4 output columns)][kTPad source rows][4] int32.
 template <int NG>
-GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, const gvc_uint4 *S, gvc_int4 *T) {
+GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, const unsigned *S, gvc_int4 *T) {
 #if defined(GVC_EMU)
     const int warp = tid >> 5;
 #else
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // broadcast: lets the compiler treat x / table entries as warp-uniform
 #endif
     const int lane = tid & 31;
-    const int chunks = pc.s_chunks;
     const gvc_int4 *htab = reinterpret_cast<const gvc_int4 *>(pc.htab);
-    gvc_uint4 c0[kRowGroups], c1[kRowGroups];
-    int       kcur = -2;
     constexpr int kColsPerWarp = kTileW / kWarps;       // 16 output columns = 4 quads per warp
     const int xw = warp * kColsPerWarp;                 // tile-relative first column of this warp
     if (xw >= g.ncols) return;                          // warp-uniform
@@ -142,38 +143,26 @@ GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, c
     for (int xi = 0; xi < kColsPerWarp; ++xi) {
         const gvc_int4 e0 = n0, e1 = n1;
         if (xi + 1 < kColsPerWarp) entry(xi + 1, n0, n1);   // table entry of the next column: off the critical path
-        const int qrel = e0.x - g.qa0;
-        const int kc = qrel >> 2, o = qrel & 3, r8 = e0.y;
-        if (kc != kcur) {                                  // warp-uniform: slide the two-chunk window
-#pragma unroll
-            for (int rg = 0; rg < kRowGroups; ++rg) {
-                const gvc_uint4 *row = S + (rg * 32 + lane) * chunks;
-                c0[rg] = (kc == kcur + 1) ? c1[rg] : row[kc];
-                c1[rg] = row[kc + 1];
-            }
-            kcur = kc;
-        }
+        const int r8 = e0.y;
+        const unsigned *wp = S + (e0.x - g.qa0) * kTileRows + lane;   // word holding the first tap, this lane's row
 #pragma unroll
         for (int rg = 0; rg < kRowGroups; ++rg) {
-            unsigned w0, w1, w2, w3;
-            switch (o) {                                   // warp-uniform
-                case 0:  w0 = c0[rg].x; w1 = c0[rg].y; w2 = c0[rg].z; w3 = c0[rg].w; break;
-                case 1:  w0 = c0[rg].y; w1 = c0[rg].z; w2 = c0[rg].w; w3 = c1[rg].x; break;
-                case 2:  w0 = c0[rg].z; w1 = c0[rg].w; w2 = c1[rg].x; w3 = c1[rg].y; break;
-                default: w0 = c0[rg].w; w1 = c1[rg].x; w2 = c1[rg].y; w3 = c1[rg].z; break;
-            }
+            const unsigned *w = wp + rg * 32;
+            const unsigned w0 = w[0], w1 = w[kTileRows];
             const unsigned u0 = funnel_r(w0, w1, r8);
             int a = dp2a_lo_su(e0.z, u0, 0);
             a     = dp2a_hi_su(e0.w, u0, a);
             if (NG >= 2) {
+                const unsigned w2 = w[2 * kTileRows];
                 const unsigned u1 = funnel_r(w1, w2, r8);
                 a = dp2a_lo_su(e1.x, u1, a);
                 a = dp2a_hi_su(e1.y, u1, a);
-            }
-            if (NG >= 3) {
-                const unsigned u2 = funnel_r(w2, w3, r8);
-                a = dp2a_lo_su(e1.z, u2, a);
-                a = dp2a_hi_su(e1.w, u2, a);
+                if (NG >= 3) {
+                    const unsigned w3 = w[3 * kTileRows];
+                    const unsigned u2 = funnel_r(w2, w3, r8);
+                    a = dp2a_lo_su(e1.z, u2, a);
+                    a = dp2a_hi_su(e1.w, u2, a);
+                }
             }
             acc[rg][xi & 3] = imin(a >> 7, 32767);
         }
