@@ -219,8 +219,18 @@ def main():
     def run_device(steps):
         list(pool.map(lambda k: [encs[k].encode_device(dev_src[k].data_ptr(), SEG_FRAMES) for _ in range(steps)], range(NSEG)))
 
+    def slot_host(k, steps):
+        # upload of the slot's next segment overlaps the encode of its current one (two staging buffers per encoder)
+        e, src = encs[k], host_src[k].data_ptr()
+        e.upload_host(src, SEG_FRAMES)
+        for i in range(steps):
+            e.encode_uploaded()
+            if i + 1 < steps:
+                e.upload_host(src, SEG_FRAMES)
+            e.finish_discard()
+
     def run_host(steps):
-        list(pool.map(lambda k: [encs[k].encode_host_discard(host_src[k].data_ptr(), SEG_FRAMES) for _ in range(steps)], range(NSEG)))
+        list(pool.map(lambda k: slot_host(k, steps), range(NSEG)))
 
     # ---- device-resident timing: every GPU stage of the path, 8 segments in flight ---------------
     run_device(args.warmup)

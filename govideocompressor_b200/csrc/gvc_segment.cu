@@ -92,8 +92,14 @@ struct gvc_encoder {
     CudaOps            ops;
     SegmentEncoder<CudaOps> *seg = nullptr;
     gvc_resize_plan   *plan = nullptr;
-    uint8_t           *d_src = nullptr;     // staging for host-supplied source pictures
-    size_t             d_src_cap = 0;
+    // staging for host-supplied source pictures: two buffers so the next segment can upload (on its own copy stream)
+    // while the current one is being encoded
+    uint8_t           *d_src[2] = {nullptr, nullptr};
+    size_t             d_src_cap[2] = {0, 0};
+    int                d_src_frames[2] = {0, 0};
+    cudaStream_t       copy_stream = nullptr;
+    cudaEvent_t        uploaded[2] = {nullptr, nullptr};
+    int                up_next = 0, up_pending = 0;     // next buffer to fill, number of uploaded-but-not-encoded segments
     SegmentOutput      out;
     int                n_last = 0;
     bool               pending = false;
@@ -105,8 +111,6 @@ struct gvc_encoder {
 };
 
 namespace {
-
-std::mutex g_upload_turn;
 
 size_t i420_bytes(int w, int h) { return size_t(w) * h + 2 * size_t((w + 1) / 2) * ((h + 1) / 2); }
 
@@ -216,7 +220,8 @@ void gvc_encoder_destroy(gvc_encoder *e) {
     if (e->graph) cudaGraphDestroy(e->graph);
     delete e->seg;
     if (e->plan) gvc_resize_plan_destroy(e->plan);
-    if (e->d_src) cudaFree(e->d_src);
+    for (int b = 0; b < 2; ++b) { if (e->d_src[b]) cudaFree(e->d_src[b]); if (e->uploaded[b]) cudaEventDestroy(e->uploaded[b]); }
+    if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     if (e->ops.st) cudaStreamDestroy(e->ops.st);
     delete e;
 }
@@ -270,24 +275,44 @@ int gvc_encoder_finish(gvc_encoder *e, int annexb, uint8_t **out, size_t *out_le
     return GVC_OK;
 }
 
-int gvc_encoder_encode_host(gvc_encoder *e, const uint8_t *frames_i420, int n_frames, int annexb, uint8_t **out, size_t *out_len) {
+int gvc_encoder_upload_host(gvc_encoder *e, const uint8_t *frames_i420, int n_frames) {
     int rc = enter();
     if (rc) return rc;
-    if (!e || !frames_i420 || n_frames < 1) { set_error("gvc_encoder_encode_host: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    if (!e || !frames_i420 || n_frames < 1) { set_error("gvc_encoder_upload_host: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    if (e->up_pending >= 2) { set_error("gvc_encoder_upload_host: two segments are already waiting to be encoded"); return GVC_ERR_INVALID_ARG; }
+    if (!e->copy_stream) GVC_CUDA(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+    const int    b = e->up_next;
     const size_t bytes = i420_bytes(e->cfg.src_w, e->cfg.src_h) * n_frames;
-    if (e->d_src_cap < bytes) {
-        if (e->d_src) cudaFree(e->d_src);
-        e->d_src = nullptr; e->d_src_cap = 0;
-        GVC_CUDA(cudaMalloc((void **)&e->d_src, bytes + 64));
-        e->d_src_cap = bytes;
+    if (!e->uploaded[b]) GVC_CUDA(cudaEventCreateWithFlags(&e->uploaded[b], cudaEventDisableTiming));
+    if (e->d_src_cap[b] < bytes) {
+        if (e->d_src[b]) cudaFree(e->d_src[b]);
+        e->d_src[b] = nullptr; e->d_src_cap[b] = 0;
+        GVC_CUDA(cudaMalloc((void **)&e->d_src[b], bytes + 64));
+        e->d_src_cap[b] = bytes;
     }
-    {   // One upload at a time per process: eight encoders copying at once would each crawl at 1/8 of the PCIe rate and no
-        // GPU work could start until all of them finish; taking turns lets the first segment compute while the next uploads.
-        std::lock_guard<std::mutex> turn(g_upload_turn);
-        GVC_CUDA(cudaMemcpyAsync(e->d_src, frames_i420, bytes, cudaMemcpyHostToDevice, e->ops.st));
-        GVC_CUDA(cudaStreamSynchronize(e->ops.st));
-    }
-    if ((rc = issue_segment(e, e->d_src, n_frames))) return rc;
+    GVC_CUDA(cudaMemcpyAsync(e->d_src[b], frames_i420, bytes, cudaMemcpyHostToDevice, e->copy_stream));
+    GVC_CUDA(cudaEventRecord(e->uploaded[b], e->copy_stream));
+    e->d_src_frames[b] = n_frames;
+    e->up_next ^= 1;
+    ++e->up_pending;
+    return GVC_OK;
+}
+
+int gvc_encoder_encode_uploaded(gvc_encoder *e) {
+    int rc = enter();
+    if (rc) return rc;
+    if (!e || e->up_pending < 1) { set_error("gvc_encoder_encode_uploaded: nothing uploaded"); return GVC_ERR_INVALID_ARG; }
+    if (e->pending) { set_error("gvc_encoder_encode_uploaded: finish the previous segment first"); return GVC_ERR_INVALID_ARG; }
+    const int b = e->up_pending == 2 ? e->up_next : e->up_next ^ 1;     // oldest uploaded buffer
+    GVC_CUDA(cudaStreamWaitEvent(e->ops.st, e->uploaded[b], 0));
+    --e->up_pending;
+    return issue_segment(e, e->d_src[b], e->d_src_frames[b]);
+}
+
+int gvc_encoder_encode_host(gvc_encoder *e, const uint8_t *frames_i420, int n_frames, int annexb, uint8_t **out, size_t *out_len) {
+    int rc = gvc_encoder_upload_host(e, frames_i420, n_frames);
+    if (rc) return rc;
+    if ((rc = gvc_encoder_encode_uploaded(e))) return rc;
     return gvc_encoder_finish(e, annexb, out, out_len);
 }
 

@@ -27,6 +27,8 @@ def _bind(lib):
     lib.gvc_encoder_destroy.restype = None
     lib.gvc_encoder_encode_host.argtypes = [vp, vp, ci, ci, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
     lib.gvc_encoder_encode_device.argtypes = [vp, vp, ci]
+    lib.gvc_encoder_upload_host.argtypes = [vp, vp, ci]
+    lib.gvc_encoder_encode_uploaded.argtypes = [vp]
     lib.gvc_encoder_sync.argtypes = [vp]
     lib.gvc_encoder_stream.argtypes = [vp]
     lib.gvc_encoder_stream.restype = vp
@@ -88,6 +90,18 @@ class Encoder:
         """Same work, stream kept inside the encoder (bench: no Python-side copy)."""
         _lib.check(self._lib.gvc_encoder_encode_host(self._h, ctypes.c_void_p(ptr), n, 0, None, None), "gvc_encoder_encode_host")
         self.n_last = n
+
+    def upload_host(self, ptr, n):
+        """Start the asynchronous upload of a segment (pinned host memory); up to two may be pending."""
+        _lib.check(self._lib.gvc_encoder_upload_host(self._h, ctypes.c_void_p(ptr), n), "gvc_encoder_upload_host")
+        self._n_uploaded = getattr(self, "_n_uploaded", []) + [n]
+
+    def encode_uploaded(self):
+        _lib.check(self._lib.gvc_encoder_encode_uploaded(self._h), "gvc_encoder_encode_uploaded")
+        self.n_last = self._n_uploaded.pop(0)
+
+    def finish_discard(self):
+        _lib.check(self._lib.gvc_encoder_finish(self._h, 0, None, None), "gvc_encoder_finish")
 
     def encode_device(self, dev_ptr, n):
         _lib.check(self._lib.gvc_encoder_encode_device(self._h, ctypes.c_void_p(dev_ptr), n), "gvc_encoder_encode_device")

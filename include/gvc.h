@@ -193,6 +193,12 @@ void gvc_encoder_destroy(gvc_encoder *enc);
  * records back, entropy-codes them.  If out != NULL it receives a malloc'ed stream (gvc_free): Annex B when annexb != 0,
  * else 4-byte length-prefixed NAL units (the MP4 sample format). */
 int gvc_encoder_encode_host(gvc_encoder *enc, const uint8_t *frames_i420, int n_frames, int annexb, uint8_t **out, size_t *out_len);
+/* The three steps of gvc_encoder_encode_host, separately, so a caller can upload segment n+1 while segment n is being
+ * encoded: upload_host starts an asynchronous copy (pinned host memory) into one of two staging buffers on the encoder's
+ * copy stream; encode_uploaded issues resize + encode kernels for the oldest uploaded segment (after gvc_encoder_finish
+ * of the previous one); gvc_encoder_finish collects the stream. */
+int gvc_encoder_upload_host(gvc_encoder *enc, const uint8_t *frames_i420, int n_frames);
+int gvc_encoder_encode_uploaded(gvc_encoder *enc);
 /* Same, pictures already in DEVICE memory; only issues the kernels (asynchronous on gvc_encoder_stream()). */
 int gvc_encoder_encode_device(gvc_encoder *enc, const uint8_t *d_frames_i420, int n_frames);
 int gvc_encoder_sync(gvc_encoder *enc);
