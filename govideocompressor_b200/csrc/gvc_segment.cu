@@ -302,7 +302,6 @@ int gvc_encoder_encode_uploaded(gvc_encoder *e) {
     int rc = enter();
     if (rc) return rc;
     if (!e || e->up_pending < 1) { set_error("gvc_encoder_encode_uploaded: nothing uploaded"); return GVC_ERR_INVALID_ARG; }
-    if (e->pending) { set_error("gvc_encoder_encode_uploaded: finish the previous segment first"); return GVC_ERR_INVALID_ARG; }
     const int b = e->up_pending == 2 ? e->up_next : e->up_next ^ 1;     // oldest uploaded buffer
     GVC_CUDA(cudaStreamWaitEvent(e->ops.st, e->uploaded[b], 0));
     --e->up_pending;

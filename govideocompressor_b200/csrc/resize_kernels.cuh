@@ -89,7 +89,8 @@ GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
     const int  row = g.r0 + r;
     const bool row_ok = r < g.rows && row < pc.sh;
     const uint8_t *p = src + (long long)(row_ok ? row : 0) * pj.sstride;
-    for (int c = warp / kRowGroups; c < chunks; c += kWarps / kRowGroups) {
+    // a lane fetches chunk PAIRS (one 32-byte sector) so no sector is pulled from L2 twice by different warps
+    auto fetch = [&](int c) {
         const int col = (g.qa0 << 2) + (c << 4);       // first source sample of this chunk
         gvc_uint4 v;
         v.x = v.y = v.z = v.w = 0u;
@@ -109,8 +110,29 @@ GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
                 v.x = w[0]; v.y = w[1]; v.z = w[2]; v.w = w[3];
             }
         }
-        unsigned *d = S + (4 * c) * kTileRows + r;
-        d[0] = v.x; d[kTileRows] = v.y; d[2 * kTileRows] = v.z; d[3 * kTileRows] = v.w;
+        return v;
+    };
+    // chunk index of the first pair member is chosen so that pairs share a 32-byte sector of the source row when the
+    // row is 32-byte aligned relative to the tile origin (qa0 is a multiple of 4 words = 16 bytes: pair (2j, 2j+1) or
+    // (2j-1, 2j) depending on the parity of qa0/4)
+    const int odd = (g.qa0 >> 2) & 1;
+    constexpr int kPairWarps = kWarps / kRowGroups;    // 4 warps share the chunk pairs of a row group
+#pragma unroll 2
+    for (int j = warp / kRowGroups; 2 * j - odd < chunks; j += kPairWarps) {
+        const int c0 = 2 * j - odd, c1 = c0 + 1;
+        gvc_uint4 v0, v1;
+        v0.x = v0.y = v0.z = v0.w = 0u;
+        v1 = v0;
+        if (c0 >= 0) v0 = fetch(c0);
+        if (c1 < chunks) v1 = fetch(c1);
+        if (c0 >= 0) {
+            unsigned *d = S + (4 * c0) * kTileRows + r;
+            d[0] = v0.x; d[kTileRows] = v0.y; d[2 * kTileRows] = v0.z; d[3 * kTileRows] = v0.w;
+        }
+        if (c1 < chunks) {
+            unsigned *d = S + (4 * c1) * kTileRows + r;
+            d[0] = v1.x; d[kTileRows] = v1.y; d[2 * kTileRows] = v1.z; d[3 * kTileRows] = v1.w;
+        }
     }
 }
 
