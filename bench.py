@@ -195,7 +195,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     gvc.init(local)
     cores = os.cpu_count() or 1
-    encs = [gvc.Encoder(SW, SH, DW, DH, fps=(30, 1), crf=CRF, merange=16, host_threads=max(1, cores // NSEG),
+    encs = [gvc.Encoder(SW, SH, DW, DH, fps=(30, 1), crf=CRF, merange=16, host_threads=int(os.environ.get("GVC_BENCH_HOST_THREADS", max(1, cores // NSEG))),
                         disable_graph=args.no_graph) for _ in range(NSEG)]
     fb = encs[0].frame_bytes()
 

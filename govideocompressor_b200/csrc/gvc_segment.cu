@@ -112,6 +112,12 @@ struct gvc_encoder {
 
 namespace {
 
+double now_ms() {
+    static const auto t0 = std::chrono::steady_clock::now();
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+bool tracing() { static const bool on = getenv("GVC_TRACE") != nullptr; return on; }
+
 size_t i420_bytes(int w, int h) { return size_t(w) * h + 2 * size_t((w + 1) / 2) * ((h + 1) / 2); }
 
 // issue resize (source I420 on the device -> padded current pictures) and every encoder kernel
@@ -265,7 +271,9 @@ int gvc_encoder_finish(gvc_encoder *e, int annexb, uint8_t **out, size_t *out_le
     if (rc) return rc;
     if (!e || !e->pending) { set_error("gvc_encoder_finish: no segment in flight"); return GVC_ERR_INVALID_ARG; }
     const auto t0 = std::chrono::steady_clock::now();
+    if (tracing()) fprintf(stderr, "[gvc %p] %.2f finish begin\n", (void *)e, now_ms());
     if ((rc = e->seg->finish(e->out))) return rc;
+    if (tracing()) fprintf(stderr, "[gvc %p] %.2f finish end\n", (void *)e, now_ms());
     e->ms_entropy = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     e->pending = false;
     if (out && out_len) {
@@ -290,6 +298,7 @@ int gvc_encoder_upload_host(gvc_encoder *e, const uint8_t *frames_i420, int n_fr
         GVC_CUDA(cudaMalloc((void **)&e->d_src[b], bytes + 64));
         e->d_src_cap[b] = bytes;
     }
+    if (tracing()) fprintf(stderr, "[gvc %p] %.2f upload issue buf %d\n", (void *)e, now_ms(), b);
     GVC_CUDA(cudaMemcpyAsync(e->d_src[b], frames_i420, bytes, cudaMemcpyHostToDevice, e->copy_stream));
     GVC_CUDA(cudaEventRecord(e->uploaded[b], e->copy_stream));
     e->d_src_frames[b] = n_frames;
@@ -305,7 +314,10 @@ int gvc_encoder_encode_uploaded(gvc_encoder *e) {
     const int b = e->up_pending == 2 ? e->up_next : e->up_next ^ 1;     // oldest uploaded buffer
     GVC_CUDA(cudaStreamWaitEvent(e->ops.st, e->uploaded[b], 0));
     --e->up_pending;
-    return issue_segment(e, e->d_src[b], e->d_src_frames[b]);
+    const double t0 = now_ms();
+    rc = issue_segment(e, e->d_src[b], e->d_src_frames[b]);
+    if (tracing()) fprintf(stderr, "[gvc %p] %.2f encode issued (%.2f ms on the host)\n", (void *)e, now_ms(), now_ms() - t0);
+    return rc;
 }
 
 int gvc_encoder_encode_host(gvc_encoder *e, const uint8_t *frames_i420, int n_frames, int annexb, uint8_t **out, size_t *out_len) {

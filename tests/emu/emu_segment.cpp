@@ -2,6 +2,8 @@
 // emulation of the kernel bodies, so the CPU suite can check the orchestration, the bitstream writer and the MP4
 // muxer against a real H.264 decoder without a GPU.  Not part of libgvc.so.
 #define GVC_EMU 1
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -99,6 +101,13 @@ int emu_encode_segment(const uint8_t *frames, int n, int w, int h, int fps, int 
     if (rc) return rc;
     SegmentOutput out;
     if ((rc = enc.finish(out))) return rc;
+    if (const char *reps = getenv("GVC_EMU_TIME_STREAM")) {      // developer aid: time the host bitstream writer alone
+        const int n_rep = atoi(reps);
+        const auto t0 = std::chrono::steady_clock::now();
+        for (int i = 0; i < n_rep; ++i) { SegmentOutput tmp; enc.write_stream(tmp); }
+        const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        fprintf(stderr, "write_stream: %.3f ms per picture (%d pictures x %d reps)\n", ms / (double(n) * n_rep), n, n_rep);
+    }
     if (recon) memcpy(recon, out.recon.data(), out.recon.size());
     if (stats)
         for (int f = 0; f < n; ++f) {
