@@ -36,6 +36,17 @@ GVC_HD void ld_u64_any(const uint8_t *p, unsigned &lo, unsigned &hi) {   // 8 by
     lo = __funnelshift_r(w0, w1, s); hi = __funnelshift_r(w1, w2, s);
 #endif
 }
+GVC_HD void ld_u128_any(const uint8_t *p, unsigned w[4]) {   // 16 bytes at any address
+#if defined(GVC_EMU)
+    for (int i = 0; i < 4; ++i) w[i] = ld_u32_any(p + 4 * i);
+#else
+    const unsigned long long a = (unsigned long long)p;
+    const unsigned *q = reinterpret_cast<const unsigned *>(a & ~3ull);
+    const unsigned  s = (unsigned)(a & 3) * 8, w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2), w3 = __ldg(q + 3), w4 = __ldg(q + 4);
+    w[0] = __funnelshift_r(w0, w1, s); w[1] = __funnelshift_r(w1, w2, s);
+    w[2] = __funnelshift_r(w2, w3, s); w[3] = __funnelshift_r(w3, w4, s);
+#endif
+}
 GVC_HD unsigned sad_u8x4(unsigned a, unsigned b, unsigned acc) {   // acc + sum |a.b[i] - b.b[i]|
 #if defined(GVC_EMU)
     for (int i = 0; i < 4; ++i) { const int d = (int)((a >> (8 * i)) & 255) - (int)((b >> (8 * i)) & 255); acc += d < 0 ? -d : d; }
@@ -71,14 +82,47 @@ GVC_HD int byte_of(unsigned w, int i) {
 #endif
 }
 
+// Two samples per 32-bit register, value = lo + (hi << 16) modulo 2^32 with both halves signed ("lo" may borrow from
+// "hi"; sums and differences of such registers stay consistent, as in x264's sum2_t).  |lo|, |hi| < 2^15 throughout.
+GVC_HD unsigned pack_even(unsigned w) {   // samples 0 and 2 of a 4-sample word
+#if defined(GVC_EMU)
+    return w & 0x00ff00ffu;
+#else
+    return __byte_perm(w, 0, 0x4240);
+#endif
+}
+GVC_HD unsigned pack_odd(unsigned w) {    // samples 1 and 3
+#if defined(GVC_EMU)
+    return (w >> 8) & 0x00ff00ffu;
+#else
+    return __byte_perm(w, 0, 0x4341);
+#endif
+}
+GVC_HD unsigned abs_pair(unsigned v) {    // |lo| + (|hi| << 16), halves now clean
+#if defined(GVC_EMU)
+    const unsigned s = ((v >> 15) & 0x10001u) * 0xffffu;
+#else
+    unsigned s;                                       // sign of each half replicated over the half; __byte_perm would
+    asm("prmt.b32 %0, %1, %1, 0xbb99;" : "=r"(s) : "r"(v));   // drop the selector's replicate-sign bits
+#endif
+    return (v + s) ^ s;
+}
+GVC_HD unsigned max_pair(unsigned v) {    // low half: max(lo, hi) of clean unsigned halves; high half: hi
+#if defined(GVC_EMU)
+    const unsigned lo = v & 0xffffu, hi = v >> 16;
+    return (hi << 16) | (lo > hi ? lo : hi);
+#else
+    return __vmaxu2(v, v >> 16);
+#endif
+}
+
 // ------------------------------------------------------------------ se(v) bit count ------------
-GVC_HD int se_bits(int v) {
-    const unsigned code = (v > 0 ? 2u * (unsigned)v - 1u : 2u * (unsigned)(-v)) + 1u;
+GVC_HD int se_bits(int v) {   // 2 * floor(log2(codeNum + 1)) + 1 with codeNum = 2|v| - (v > 0): floor(log2) = bit length of |v|
 #if defined(GVC_EMU)
     int n = 0;
-    for (unsigned c = code; c > 1; c >>= 1) ++n;
+    for (unsigned c = (unsigned)(v < 0 ? -v : v); c; c >>= 1) ++n;
 #else
-    const int n = 31 - __clz(code);
+    const int n = 32 - __clz(v < 0 ? -v : v);
 #endif
     return 2 * n + 1;
 }
@@ -192,41 +236,153 @@ GVC_HD void lowres_px(const uint8_t *src, int sstride, int x_lo, int x_hi, int y
 }
 
 // ------------------------------------------------------------------ K2 half-sample planes -------
-constexpr int kHpTileW = 64, kHpTileH = 32, kHpThreads = 256, kHpPitch = 72;
+// One CTA per 64x32 tile; four samples per work item.  Phase A stages the source tile (with a 4-sample apron, replicated
+// at the region edge) in shared memory as words.  Phase B runs the vertical 6-tap on two samples per register (sum2
+// form, see pack_even), keeps the unrounded sums as int16 for phase C and writes the V plane.  Phase C runs the horizontal
+// 6-tap over source bytes (dp4a, H plane) and over the int16 sums (dp2a, C plane).  Planes, pitch and region bounds that
+// are multiples of four move whole words to and from HBM (`al`); anything else goes byte by byte through the same
+// arithmetic.
+constexpr int kHpTileW = 64, kHpTileH = 32, kHpThreads = 256, kHpWords = kHpTileW / 4 + 2;
 struct HpelSmem {
-    uint8_t src[kHpTileH + 5][kHpPitch];   // tile rows y0-2 .. y0+TH+2, cols x0-2 .. x0+TW+2
-    int16_t v[kHpTileH][kHpPitch];         // unrounded vertical 6-tap sums, cols x0-2 .. x0+TW+2
+    unsigned src[kHpTileH + 5][kHpWords];      // rows y0-2 .. y0+TH+2, samples x0-4 .. x0+TW+3
+    unsigned v[kHpTileH][2 * kHpWords];        // unrounded vertical sums as int16 pairs, same samples
 };
 GVC_HD int tap6(int a, int b, int c, int d, int e, int f) { return a + f - 5 * (b + e) + 20 * (c + d); }
+
+GVC_HD unsigned funnel_r(unsigned lo, unsigned hi, int bits) {     // (hi:lo) >> bits, 0 <= bits < 32
+#if defined(GVC_EMU)
+    return (unsigned)((((unsigned long long)hi << 32) | lo) >> bits);
+#else
+    return __funnelshift_r(lo, hi, (unsigned)bits);
+#endif
+}
+GVC_HD unsigned byte_sel(unsigned a, unsigned b, unsigned sel) {   // prmt.b32 without the replicate-sign modes
+#if defined(GVC_EMU)
+    const unsigned long long ab = ((unsigned long long)b << 32) | a;
+    unsigned r = 0;
+    for (int i = 0; i < 4; ++i) r |= (unsigned)((ab >> (8 * ((sel >> (4 * i)) & 7))) & 255) << (8 * i);
+    return r;
+#else
+    return __byte_perm(a, b, sel);
+#endif
+}
+GVC_HD int dp4a_us(unsigned pix, int coef, int acc) {    // acc + sum of pix.b[i] (unsigned) * coef.b[i] (signed)
+#if defined(GVC_EMU)
+    for (int i = 0; i < 4; ++i) acc += (int)((pix >> (8 * i)) & 255) * (int)(int8_t)((unsigned)coef >> (8 * i));
+    return acc;
+#else
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pix), "r"(coef), "r"(acc));
+    return d;
+#endif
+}
+GVC_HD int dp2a_ss(unsigned pair, int coef, int acc, bool hi) {   // acc + pair.lo16 * coef.b[2hi] + pair.hi16 * coef.b[2hi+1], all signed
+#if defined(GVC_EMU)
+    const int sh = hi ? 16 : 0;
+    return acc + (int)(int16_t)(pair & 0xffff) * (int)(int8_t)((unsigned)coef >> sh) + (int)(int16_t)(pair >> 16) * (int)(int8_t)((unsigned)coef >> (sh + 8));
+#else
+    int d;
+    if (hi) asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(coef), "r"(acc));
+    else    asm("dp2a.lo.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(coef), "r"(acc));
+    return d;
+#endif
+}
+// (v + bias) clamped to [0, top] on both int16 halves of a clean pair (no borrow between the halves)
+GVC_HD unsigned bias_clamp_s16x2(unsigned v, unsigned bias2, unsigned top2) {
+#if defined(GVC_EMU)
+    unsigned r = 0;
+    for (int i = 0; i < 2; ++i) {
+        int h = (int)(int16_t)(v >> (16 * i)) + (int)(int16_t)(bias2 >> (16 * i));
+        const int t = (int)(int16_t)(top2 >> (16 * i));
+        h = h < 0 ? 0 : (h > t ? t : h);
+        r |= (unsigned)(h & 0xffff) << (16 * i);
+    }
+    return r;
+#else
+    return __vmins2(__vmaxs2(__vadd2(v, bias2), 0u), top2);
+#endif
+}
+constexpr int kTapA = 0x1414fb01;    // bytes  1, -5, 20, 20
+constexpr int kTapB = 0x000001fb;    // bytes -5,  1,  0,  0
 
 struct HpelArgs {
     const uint8_t *src; uint8_t *dh, *dv, *dc;   // all at sample (0,0), same stride
     int stride, x_lo, x_hi, y_lo, y_hi;          // region to fill = readable region: [x_lo,x_hi) x [y_lo,y_hi)
 };
-GVC_HD void hpel_phase_a(int tid, const HpelArgs &a, int x0, int y0, HpelSmem &sm) {
-    for (int i = tid; i < (kHpTileH + 5) * (kHpTileW + 5); i += kHpThreads) {
-        const int r = i / (kHpTileW + 5), c = i - r * (kHpTileW + 5);
-        sm.src[r][c] = a.src[(long long)iclamp(y0 - 2 + r, a.y_lo, a.y_hi - 1) * a.stride + iclamp(x0 - 2 + c, a.x_lo, a.x_hi - 1)];
+GVC_HDH bool hpel_aligned(const HpelArgs &a) {
+    return (((unsigned long long)a.src | (unsigned long long)a.dh | (unsigned long long)a.dv | (unsigned long long)a.dc |
+             (unsigned long long)(unsigned)a.stride | (unsigned long long)(unsigned)a.x_lo | (unsigned long long)(unsigned)a.x_hi) & 3) == 0;
+}
+GVC_HD void hpel_store4(uint8_t *plane, const HpelArgs &a, bool al, int x, int y, unsigned w) {   // samples x..x+3 of row y
+    if (y >= a.y_hi || x >= a.x_hi) return;
+    uint8_t *p = plane + (long long)y * a.stride + x;
+    if (al) { *reinterpret_cast<unsigned *>(p) = w; return; }
+    for (int i = 0; i < 4; ++i)
+        if (x + i < a.x_hi) p[i] = (uint8_t)(w >> (8 * i));
+}
+GVC_HD void hpel_phase_a(int tid, const HpelArgs &a, bool al, int x0, int y0, HpelSmem &sm) {
+    for (int i = tid; i < (kHpTileH + 5) * kHpWords; i += kHpThreads) {
+        const int r = i / kHpWords, c = i - r * kHpWords;
+        const int x = x0 - 4 + 4 * c;
+        const uint8_t *row = a.src + (long long)iclamp(y0 - 2 + r, a.y_lo, a.y_hi - 1) * a.stride;
+        unsigned w;
+        if (al && x >= a.x_lo && x < a.x_hi) {
+            w = *reinterpret_cast<const unsigned *>(row + x);
+        } else if (al) {
+            w = 0x01010101u * row[x < a.x_lo ? a.x_lo : a.x_hi - 1];
+        } else {
+            w = 0;
+            for (int k = 0; k < 4; ++k) w |= (unsigned)row[iclamp(x + k, a.x_lo, a.x_hi - 1)] << (8 * k);
+        }
+        sm.src[r][c] = w;
     }
 }
-GVC_HD void hpel_phase_b(int tid, const HpelArgs &a, int x0, int y0, HpelSmem &sm) {
-    for (int i = tid; i < kHpTileH * (kHpTileW + 5); i += kHpThreads) {
-        const int r = i / (kHpTileW + 5), c = i - r * (kHpTileW + 5);
-        const int v = tap6(sm.src[r][c], sm.src[r + 1][c], sm.src[r + 2][c], sm.src[r + 3][c], sm.src[r + 4][c], sm.src[r + 5][c]);
-        sm.v[r][c] = (int16_t)v;
-        const int x = x0 + c - 2, y = y0 + r;
-        if (c >= 2 && c < kHpTileW + 2 && x < a.x_hi && y < a.y_hi) a.dv[(long long)y * a.stride + x] = (uint8_t)clip_u8((v + 16) >> 5);
+GVC_HD void hpel_phase_b(int tid, const HpelArgs &a, bool al, int x0, int y0, HpelSmem &sm) {
+    for (int i = tid; i < kHpTileH * kHpWords; i += kHpThreads) {
+        const int r = i / kHpWords, c = i - r * kHpWords;
+        unsigned e[6], o[6];
+        for (int k = 0; k < 6; ++k) { const unsigned w = sm.src[r + k][c]; e[k] = pack_even(w); o[k] = pack_odd(w); }
+        // sums stay within int16 (-2550 .. 10710); a negative low half has borrowed one from the high half: give it back
+        unsigned ve = (e[0] + e[5]) + 20u * (e[2] + e[3]) - 5u * (e[1] + e[4]);
+        unsigned vo = (o[0] + o[5]) + 20u * (o[2] + o[3]) - 5u * (o[1] + o[4]);
+        ve += (ve & 0x8000u) << 1;
+        vo += (vo & 0x8000u) << 1;
+        sm.v[r][2 * c]     = byte_sel(ve, vo, 0x5410);      // samples 0, 1
+        sm.v[r][2 * c + 1] = byte_sel(ve, vo, 0x7632);      // samples 2, 3
+        if (c >= 1 && c <= kHpTileW / 4) {
+            const unsigned be = (bias_clamp_s16x2(ve, 0x00100010u, 0x1fff1fffu) >> 5) & 0x00ff00ffu;
+            const unsigned bo = (bias_clamp_s16x2(vo, 0x00100010u, 0x1fff1fffu) >> 5) & 0x00ff00ffu;
+            hpel_store4(a.dv, a, al, x0 - 4 + 4 * c, y0 + r, byte_sel(be, bo, 0x6240));
+        }
     }
 }
-GVC_HD void hpel_phase_c(int tid, const HpelArgs &a, int x0, int y0, HpelSmem &sm) {
-    for (int i = tid; i < kHpTileH * kHpTileW; i += kHpThreads) {
-        const int r = i / kHpTileW, c = i - r * kHpTileW;
-        const int x = x0 + c, y = y0 + r;
+GVC_HD void hpel_phase_c(int tid, const HpelArgs &a, bool al, int x0, int y0, HpelSmem &sm) {
+    for (int i = tid; i < kHpTileH * (kHpTileW / 4); i += kHpThreads) {
+        const int r = i / (kHpTileW / 4), c = i - r * (kHpTileW / 4);
+        const int x = x0 + 4 * c, y = y0 + r;
         if (x >= a.x_hi || y >= a.y_hi) continue;
-        const uint8_t *s = &sm.src[r + 2][c];
-        const int16_t *v = &sm.v[r][c];
-        a.dh[(long long)y * a.stride + x] = (uint8_t)clip_u8((tap6(s[0], s[1], s[2], s[3], s[4], s[5]) + 16) >> 5);
-        a.dc[(long long)y * a.stride + x] = (uint8_t)clip_u8((tap6(v[0], v[1], v[2], v[3], v[4], v[5]) + 512) >> 10);
+        // H plane: samples x-2 .. x+6 sit in source words c, c+1, c+2 (word c+1 starts at x)
+        const unsigned w0 = sm.src[r + 2][c], w1 = sm.src[r + 2][c + 1], w2 = sm.src[r + 2][c + 2];
+        int h[4];
+        h[0] = dp4a_us(funnel_r(w1, w2, 16), kTapB, dp4a_us(funnel_r(w0, w1, 16), kTapA, 16));
+        h[1] = dp4a_us(funnel_r(w1, w2, 24), kTapB, dp4a_us(funnel_r(w0, w1, 24), kTapA, 16));
+        h[2] = dp4a_us(w2, kTapB, dp4a_us(w1, kTapA, 16));
+        h[3] = dp4a_us(w2 >> 8, kTapB, dp4a_us(funnel_r(w1, w2, 8), kTapA, 16));
+        unsigned out = 0;
+        for (int k = 0; k < 4; ++k) out |= (unsigned)clip_u8(h[k] >> 5) << (8 * k);
+        hpel_store4(a.dh, a, al, x, y, out);
+        // C plane: the same taps over the vertical sums of samples x-2 .. x+6: int16 pairs 2c+1 .. 2c+5 of the row
+        const unsigned *vr = &sm.v[r][2 * c + 1];
+        const unsigned v0 = vr[0], v1 = vr[1], v2 = vr[2], v3 = vr[3], v4 = vr[4];
+        const unsigned s0 = funnel_r(v0, v1, 16), s1 = funnel_r(v1, v2, 16), s2 = funnel_r(v2, v3, 16), s3 = funnel_r(v3, v4, 16);
+        int q[4];
+        q[0] = dp2a_ss(v2, kTapB, dp2a_ss(v1, kTapA, dp2a_ss(v0, kTapA, 512, false), true), false);
+        q[1] = dp2a_ss(s2, kTapB, dp2a_ss(s1, kTapA, dp2a_ss(s0, kTapA, 512, false), true), false);
+        q[2] = dp2a_ss(v3, kTapB, dp2a_ss(v2, kTapA, dp2a_ss(v1, kTapA, 512, false), true), false);
+        q[3] = dp2a_ss(s3, kTapB, dp2a_ss(s2, kTapA, dp2a_ss(s1, kTapA, 512, false), true), false);
+        out = 0;
+        for (int k = 0; k < 4; ++k) out |= (unsigned)clip_u8(q[k] >> 10) << (8 * k);
+        hpel_store4(a.dc, a, al, x, y, out);
     }
 }
 
@@ -386,44 +542,72 @@ GVC_HD int hadamard4_abs(const int d[16]) {
 }
 
 // ------------------------------------------------------------------ K4a lowres search ----------
-// One warp per macroblock.  lanes stride over the (2r+1)^2 candidates; key = cost<<11 | index.
+// One warp per macroblock (an 8x8 block of the half-resolution plane), exhaustive over (2r+1)^2 displacements.  The warp
+// first stages the (8+2r)^2 search window in shared memory.  A work item is one column dx and kLowChunk consecutive dy:
+// the lane shifts each window row to dx once and feeds it to every candidate of the chunk that uses that row, so a
+// candidate costs its 16 four-byte SADs and a sixth of the row fetches.  key = cost<<11 | index; the warp minimum wins.
+constexpr int kLowMaxR = 22, kLowRows = 8 + 2 * kLowMaxR, kLowPitch = kLowMaxR / 2 + 4, kLowChunk = 6;
 struct MeLowArgs {
     const uint8_t *cur, *ref;   // lowres planes at (0,0)
     int stride, mbw, mbh, r, lambda;
     int16_t *out_mv;            // (dx,dy) per MB
 };
-GVC_HD void me_lowres_lane(int lane, const MeLowArgs &a, int mx, int my, unsigned *keys /* [32] per warp */) {
-    const int n = 2 * a.r + 1;
-    unsigned  c[8][2];
-    const uint8_t *cp = a.cur + (long long)(8 * my) * a.stride + 8 * mx;   // 8-byte aligned (pitch, origin multiples of 8)
-    for (int j = 0; j < 8; ++j) ld_u64_any(cp + (long long)j * a.stride, c[j][0], c[j][1]);
-    unsigned best = 0xffffffffu;
-    for (int idx = lane; idx < n * n; idx += 32) {
-        const int dy = idx / n - a.r, dx = idx - (idx / n) * n - a.r;
-        const uint8_t *p = a.ref + (long long)(8 * my + dy) * a.stride + 8 * mx + dx;
-        unsigned sad = 0;
-        for (int j = 0; j < 8; ++j) {
-            unsigned lo, hi;
-            ld_u64_any(p + (long long)j * a.stride, lo, hi);
-            sad = sad_u8x4(c[j][0], lo, sad);
-            sad = sad_u8x4(c[j][1], hi, sad);
-        }
-        const unsigned cost = sad + (unsigned)(a.lambda * (se_bits(4 * dx) + se_bits(4 * dy)));
-        const unsigned key  = (cost << 11) | (unsigned)idx;
-        best = key < best ? key : best;
-    }
-    keys[lane] = best;
+struct MeLowSmem { unsigned win[kLowRows + kLowChunk][kLowPitch]; };   // per warp: window rows, byte 0 = column 8*mx - r; the
+                                                                       // spare rows are read for dy past the range, never filled
+GVC_HD void me_lowres_load(int lane, const MeLowArgs &a, int mx, int my, MeLowSmem &sm) {
+    const int rows = 8 + 2 * a.r, words = (8 + 2 * a.r + 3) >> 2;
+    const uint8_t *org = a.ref + ((8 * my - a.r) * a.stride + 8 * mx - a.r);
+    const int cs = words <= 8 ? 3 : 4, c = lane & ((1 << cs) - 1);     // 8 or 16 lanes across a row
+    if (c < words)
+        for (int y = lane >> cs; y < rows; y += 32 >> cs) sm.win[y][c] = ld_u32_any(org + (y * a.stride + 4 * c));
 }
-GVC_HD void me_lowres_pick(int lane, const MeLowArgs &a, int mx, int my, const unsigned *keys) {
+GVC_HD unsigned me_lowres_lane(int lane, const MeLowArgs &a, int mx, int my, const MeLowSmem &sm) {
+    const int n = 2 * a.r + 1, items = n * ((n + kLowChunk - 1) / kLowChunk);
+    unsigned  c[8][2];
+    const uint8_t *cp = a.cur + (8 * my * a.stride + 8 * mx);
+    for (int j = 0; j < 8; ++j) ld_u64_any(cp + j * a.stride, c[j][0], c[j][1]);
+    unsigned best = 0xffffffffu;
+    for (int it = lane; it < items; it += 32) {
+        const int ch = it / n, o = it - ch * n, y0 = ch * kLowChunk;    // o = dx + r, y0 = first dy + r of the chunk
+        const int wi = o >> 2, sh = (o & 3) * 8;
+        unsigned acc[kLowChunk];
+        for (int k = 0; k < kLowChunk; ++k) acc[k] = 0;
+#if !defined(GVC_EMU)
+#pragma unroll
+#endif
+        for (int y = 0; y < kLowChunk + 7; ++y) {
+            const unsigned *row = sm.win[y0 + y];                        // rows past the window only feed discarded dy
+            const unsigned w1 = row[wi + 1], lo = funnel_r(row[wi], w1, sh), hi = funnel_r(w1, row[wi + 2], sh);
+#if !defined(GVC_EMU)
+#pragma unroll
+#endif
+            for (int k = 0; k < kLowChunk; ++k) {
+                const int j = y - k;
+                if (j >= 0 && j < 8) acc[k] = sad_u8x4(c[j][1], hi, sad_u8x4(c[j][0], lo, acc[k]));
+            }
+        }
+        const int bx = se_bits(4 * (o - a.r));
+        for (int k = 0; k < kLowChunk; ++k) {
+            const int q = y0 + k;                                        // dy + r
+            if (q >= n) break;
+            const unsigned cost = acc[k] + (unsigned)(a.lambda * (bx + se_bits(4 * (q - a.r))));
+            const unsigned key  = (cost << 11) | (unsigned)(q * n + o);
+            best = key < best ? key : best;
+        }
+    }
+    return best;
+}
+GVC_HD void me_lowres_out(int lane, const MeLowArgs &a, int mx, int my, unsigned best) {
     if (lane != 0) return;
-    unsigned best = keys[0];
-    for (int i = 1; i < 32; ++i) best = keys[i] < best ? keys[i] : best;
     const int n = 2 * a.r + 1, idx = (int)(best & 2047);
     a.out_mv[2 * (my * a.mbw + mx)]     = (int16_t)(idx - (idx / n) * n - a.r);
     a.out_mv[2 * (my * a.mbw + mx) + 1] = (int16_t)(idx / n - a.r);
 }
 
 // ------------------------------------------------------------------ K4b refinement -------------
+// One warp per macroblock.  Phases: load (source rows, predictor and plane table into the warp's shared record) ->
+// 27 integer candidates, one per lane -> pick per partition -> 9 half-sample + 8 quarter-sample SATD candidates with
+// lanes 0..15 on the 16x16 partition and 16..31 on the four 8x8 partitions -> mode decision.
 struct MeRefArgs {
     const uint8_t *cur;          // source luma (0,0)
     RefPlanes      ref;
@@ -432,8 +616,11 @@ struct MeRefArgs {
     MbMotion      *out;
 };
 struct MeRefSmem {               // per warp
-    unsigned key[5][32];
-    int      center[5][2], best_mv[5][2], best_cost[5];
+    gvc_uint4      cur[16];      // the macroblock's 16 source rows
+    const uint8_t *plane[4];     // full, H, V, C sample planes (mc_luma_src order)
+    unsigned       key[5][32];
+    int            center[5][2], best_mv[5][2], best_cost[5];
+    int            mvp[2], low[2];
 };
 GVC_HD void sq8(int i, int &dx, int &dy) {   // (0,-1),(0,1),(-1,0),(1,0),(-1,-1),(-1,1),(1,-1),(1,1)
     dx = i < 2 ? 0 : ((i == 2 || i == 4 || i == 5) ? -1 : 1);
@@ -451,38 +638,48 @@ GVC_HD void me_mvp(const MeRefArgs &a, int mx, int my, int &px, int &py) {
     px = median3(v[0][0], v[1][0], v[2][0]);
     py = median3(v[0][1], v[1][1], v[2][1]);
 }
+GVC_HD void me_ref_load(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
+    if (lane < 16) {
+        unsigned w[4];
+        ld_u128_any(a.cur + (long long)(16 * my + lane) * a.stride + 16 * mx, w);
+        gvc_uint4 r; r.x = w[0]; r.y = w[1]; r.z = w[2]; r.w = w[3];
+        sm.cur[lane] = r;
+    } else if (lane == 16) {
+        int px, py;
+        me_mvp(a, mx, my, px, py);
+        sm.mvp[0] = px; sm.mvp[1] = py;
+    } else if (lane == 17) {
+        sm.low[0] = a.lowres_mv[2 * (my * a.mbw + mx)];
+        sm.low[1] = a.lowres_mv[2 * (my * a.mbw + mx) + 1];
+    } else if (lane == 18) {
+        sm.plane[0] = a.ref.y; sm.plane[1] = a.ref.hh; sm.plane[2] = a.ref.hv; sm.plane[3] = a.ref.hc;
+    }
+}
+// integer candidate i of the macroblock: 5x5 around twice the lowres vector, the rounded predictor, zero
+GVC_HD void me_int_cand(const MeRefArgs &a, const MeRefSmem &sm, int mx, int my, int i, int &cx, int &cy) {
+    if (i < 25)       { cx = 2 * sm.low[0] + (i % 5) - 2; cy = 2 * sm.low[1] + (i / 5) - 2; }
+    else if (i == 25) { cx = (sm.mvp[0] + 2) >> 2; cy = (sm.mvp[1] + 2) >> 2; }
+    else              { cx = 0; cy = 0; }
+    cx = iclamp(cx, -16 * mx - (kEncPad - 8), a.w16 - 16 * mx - 16 + (kEncPad - 8));
+    cy = iclamp(cy, -16 * my - (kEncPad - 8), a.h16 - 16 * my - 16 + (kEncPad - 8));
+}
 // integer candidates: lane i < 27 evaluates candidate i (four 8x8 SADs)
 GVC_HD void me_ref_int(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
     for (int k = 0; k < 5; ++k) sm.key[k][lane] = 0xffffffffu;
     if (lane >= 27) return;
-    int px, py;
-    me_mvp(a, mx, my, px, py);
-    const int x0 = 16 * mx, y0 = 16 * my;
     int cx, cy;
-    if (lane < 25) {
-        cx = 2 * a.lowres_mv[2 * (my * a.mbw + mx)] + (lane % 5) - 2;
-        cy = 2 * a.lowres_mv[2 * (my * a.mbw + mx) + 1] + (lane / 5) - 2;
-    } else if (lane == 25) {
-        cx = (px + 2) >> 2; cy = (py + 2) >> 2;
-    } else {
-        cx = 0; cy = 0;
-    }
-    cx = iclamp(cx, -x0 - (kEncPad - 8), a.w16 - x0 - 16 + (kEncPad - 8));
-    cy = iclamp(cy, -y0 - (kEncPad - 8), a.h16 - y0 - 16 + (kEncPad - 8));
-    const uint8_t *c = a.cur + (long long)y0 * a.stride + x0;
-    const uint8_t *p = a.ref.y + (long long)(y0 + cy) * a.stride + x0 + cx;
+    me_int_cand(a, sm, mx, my, lane, cx, cy);
+    const uint8_t *p = a.ref.y + ((16 * my + cy) * a.stride + 16 * mx + cx);
     unsigned s[4] = {0, 0, 0, 0};
-    for (int j = 0; j < 16; ++j) {
-        unsigned c0, c1, c2, c3, r0, r1, r2, r3;
-        ld_u64_any(c + (long long)j * a.stride, c0, c1);
-        ld_u64_any(c + (long long)j * a.stride + 8, c2, c3);
-        ld_u64_any(p + (long long)j * a.stride, r0, r1);
-        ld_u64_any(p + (long long)j * a.stride + 8, r2, r3);
+    for (int j = 0; j < 16; ++j, p += a.stride) {
+        unsigned r[4];
+        ld_u128_any(p, r);
+        const gvc_uint4 c = sm.cur[j];
         const int k = (j >> 3) * 2;
-        s[k]     = sad_u8x4(c1, r1, sad_u8x4(c0, r0, s[k]));
-        s[k + 1] = sad_u8x4(c3, r3, sad_u8x4(c2, r2, s[k + 1]));
+        s[k]     = sad_u8x4(c.y, r[1], sad_u8x4(c.x, r[0], s[k]));
+        s[k + 1] = sad_u8x4(c.w, r[3], sad_u8x4(c.z, r[2], s[k + 1]));
     }
-    const unsigned bits = (unsigned)(a.lambda * mv_bits(4 * cx, 4 * cy, px, py));
+    const unsigned bits = (unsigned)(a.lambda * mv_bits(4 * cx, 4 * cy, sm.mvp[0], sm.mvp[1]));
     sm.key[0][lane] = ((s[0] + s[1] + s[2] + s[3] + bits) << 5) | (unsigned)lane;
     for (int k = 0; k < 4; ++k) sm.key[1 + k][lane] = ((s[k] + bits) << 5) | (unsigned)lane;
     // candidate coordinates are recomputed by the picker from the winning lane id
@@ -491,21 +688,8 @@ GVC_HD void me_ref_pick(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem 
     if (lane >= 5) return;
     unsigned best = sm.key[lane][0];
     for (int i = 1; i < 27; ++i) best = sm.key[lane][i] < best ? sm.key[lane][i] : best;
-    const int i = (int)(best & 31);
-    int px, py;
-    me_mvp(a, mx, my, px, py);
-    const int x0 = 16 * mx, y0 = 16 * my;
     int cx, cy;
-    if (i < 25) {
-        cx = 2 * a.lowres_mv[2 * (my * a.mbw + mx)] + (i % 5) - 2;
-        cy = 2 * a.lowres_mv[2 * (my * a.mbw + mx) + 1] + (i / 5) - 2;
-    } else if (i == 25) {
-        cx = (px + 2) >> 2; cy = (py + 2) >> 2;
-    } else {
-        cx = 0; cy = 0;
-    }
-    cx = iclamp(cx, -x0 - (kEncPad - 8), a.w16 - x0 - 16 + (kEncPad - 8));
-    cy = iclamp(cy, -y0 - (kEncPad - 8), a.h16 - y0 - 16 + (kEncPad - 8));
+    me_int_cand(a, sm, mx, my, (int)(best & 31), cx, cy);
     sm.center[lane][0] = 4 * cx;
     sm.center[lane][1] = 4 * cy;
 }
@@ -514,48 +698,65 @@ GVC_HD void me_lane_block(int lane, int &P, int &ox, int &oy) {
     if (lane < 16) { P = 0; ox = 4 * (lane & 3); oy = 4 * (lane >> 2); }
     else { const int l = lane - 16, k = l >> 2, j = l & 3; P = 1 + k; ox = 8 * (k & 1) + 4 * (j & 1); oy = 8 * (k >> 1) + 4 * (j >> 1); }
 }
+// Half the 4x4 Hadamard magnitude sum of (source - w): ca/cb hold the source rows' samples (0,2) / (1,3).  Vertical
+// butterflies run on both halves at once, the horizontal pair (0,2)+-(1,3) between registers, and the last stage
+// through |p + q| + |p - q| = 2 max(|p|, |q|).
+GVC_HD int satd4x4_rows(const unsigned ca[4], const unsigned cb[4], const unsigned w[4]) {
+    unsigned A[4], B[4];
+    for (int j = 0; j < 4; ++j) { A[j] = ca[j] - pack_even(w[j]); B[j] = cb[j] - pack_odd(w[j]); }
+    {
+        const unsigned t0 = A[0] + A[1], t1 = A[0] - A[1], t2 = A[2] + A[3], t3 = A[2] - A[3];
+        A[0] = t0 + t2; A[1] = t1 + t3; A[2] = t0 - t2; A[3] = t1 - t3;
+        const unsigned u0 = B[0] + B[1], u1 = B[0] - B[1], u2 = B[2] + B[3], u3 = B[2] - B[3];
+        B[0] = u0 + u2; B[1] = u1 + u3; B[2] = u0 - u2; B[3] = u1 - u3;
+    }
+    unsigned acc = 0;
+    for (int j = 0; j < 4; ++j) acc += max_pair(abs_pair(A[j] + B[j])) + max_pair(abs_pair(A[j] - B[j]));
+    return (int)(acc & 0xffffu);
+}
 // Per-lane state that stays in registers across the 17 sub-pel candidates: the lane's 4x4 source block, its offset in
 // the planes, the predictor, and the running best / search centre of the lane's partition (every lane of a partition
 // carries the same best: no shared-memory round trip or leader election per candidate).  The emulation harness keeps one
 // record per lane.
 struct MeLane {
-    int       P, ox, oy, px, py;
-    long long base;      // (16*my + oy) * stride + 16*mx + ox
-    int       cur[16];
+    int       P, px, py;
+    int       base;      // (16*my + oy) * stride + 16*mx + ox
+    unsigned  ca[4], cb[4];
     int       cx, cy, bx, by, bcost;
 };
 GVC_HD void me_lane_init(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm, MeLane &L) {
-    me_lane_block(lane, L.P, L.ox, L.oy);
-    me_mvp(a, mx, my, L.px, L.py);
-    L.base = (long long)(16 * my + L.oy) * a.stride + 16 * mx + L.ox;
-    const uint8_t *c = a.cur + L.base;
+    int ox, oy;
+    me_lane_block(lane, L.P, ox, oy);
+    L.px = sm.mvp[0]; L.py = sm.mvp[1];
+    L.base = (16 * my + oy) * a.stride + 16 * mx + ox;
     for (int j = 0; j < 4; ++j) {
-        const unsigned w = ld_u32_any(c + (long long)j * a.stride);
-        for (int i = 0; i < 4; ++i) L.cur[j * 4 + i] = byte_of(w, i);
+        const gvc_uint4 r = sm.cur[oy + j];
+        const unsigned w = ox == 0 ? r.x : ox == 4 ? r.y : ox == 8 ? r.z : r.w;
+        L.ca[j] = pack_even(w); L.cb[j] = pack_odd(w);
     }
     L.cx = L.bx = sm.center[L.P][0];
     L.cy = L.by = sm.center[L.P][1];
     L.bcost = 0x7fffffff;
 }
-// sub-pel candidate ci (-1 = the centre itself) at `step`: the lane's 4x4 Hadamard sum (already halved)
-GVC_HD int me_ref_satd(const MeRefArgs &a, const MeLane &L, int ci, int step) {
+// sub-pel candidate ci (-1 = the centre itself) at `step`: the lane's 4x4 Hadamard sum (already halved).  step 2 starts
+// from a full-sample centre, so its candidates read one plane chosen by ci alone; every step 1 candidate has an odd
+// component and averages two planes (mc_luma_src).
+GVC_HD int me_ref_satd(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L, int ci, int step) {
     int dx = 0, dy = 0;
     if (ci >= 0) sq8(ci, dx, dy);
     const int mvx = L.cx + dx * step, mvy = L.cy + dy * step;
-    const int fx = mvx & 3, fy = mvy & 3, q = fy * 4 + fx;
-    const long long off = L.base + (long long)(mvy >> 2) * a.stride + (mvx >> 2);
-    const int s0 = (int)((kQpelRef0 >> (2 * q)) & 3), s1 = (int)((kQpelRef1 >> (2 * q)) & 3);
-    const uint8_t *p1 = (s0 == 0 ? a.ref.y : s0 == 1 ? a.ref.hh : s0 == 2 ? a.ref.hv : a.ref.hc) + off + (fy == 3 ? a.stride : 0);
-    const uint8_t *p2 = (s1 == 0 ? a.ref.y : s1 == 1 ? a.ref.hh : s1 == 2 ? a.ref.hv : a.ref.hc) + off + (fx == 3 ? 1 : 0);
-    const bool two = (q & 5) != 0;
-    int d[16];
-    for (int j = 0; j < 4; ++j) {
-        unsigned w = ld_u32_any(p1);
-        p1 += a.stride;
-        if (two) { w = avg_u8x4(w, ld_u32_any(p2)); p2 += a.stride; }
-        for (int i = 0; i < 4; ++i) d[j * 4 + i] = L.cur[j * 4 + i] - byte_of(w, i);
+    const int off = L.base + (mvy >> 2) * a.stride + (mvx >> 2);
+    unsigned w[4];
+    if (step == 2) {
+        const uint8_t *p = (dx ? (dy ? a.ref.hc : a.ref.hh) : (dy ? a.ref.hv : a.ref.y)) + off;
+        for (int j = 0; j < 4; ++j, p += a.stride) w[j] = ld_u32_any(p);
+    } else {
+        const int fx = mvx & 3, fy = mvy & 3, q = fy * 4 + fx;
+        const uint8_t *p1 = sm.plane[(kQpelRef0 >> (2 * q)) & 3] + (off + (fy == 3 ? a.stride : 0));
+        const uint8_t *p2 = sm.plane[(kQpelRef1 >> (2 * q)) & 3] + (off + (fx == 3 ? 1 : 0));
+        for (int j = 0; j < 4; ++j, p1 += a.stride, p2 += a.stride) w[j] = avg_u8x4(ld_u32_any(p1), ld_u32_any(p2));
     }
-    return hadamard4_abs(d) >> 1;
+    return satd4x4_rows(L.ca, L.cb, w);
 }
 // `total` = SATD of the lane's whole partition for this candidate (sum of its lanes' partials).  Keeps the best; after the
 // last candidate of a step the best becomes the next search centre.

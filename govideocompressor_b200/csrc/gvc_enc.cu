@@ -45,11 +45,12 @@ __global__ void __launch_bounds__(256) lowres_batch_kernel(const __grid_constant
 __global__ void __launch_bounds__(kHpThreads) hpel_kernel(const __grid_constant__ HpelArgs a) {
     __shared__ HpelSmem sm;
     const int x0 = a.x_lo + blockIdx.x * kHpTileW, y0 = a.y_lo + blockIdx.y * kHpTileH;
-    hpel_phase_a(threadIdx.x, a, x0, y0, sm);
+    const bool al = hpel_aligned(a);
+    hpel_phase_a(threadIdx.x, a, al, x0, y0, sm);
     __syncthreads();
-    hpel_phase_b(threadIdx.x, a, x0, y0, sm);
+    hpel_phase_b(threadIdx.x, a, al, x0, y0, sm);
     __syncthreads();
-    hpel_phase_c(threadIdx.x, a, x0, y0, sm);
+    hpel_phase_c(threadIdx.x, a, al, x0, y0, sm);
 }
 
 __global__ void __launch_bounds__(128) transform8x8_kernel(const __grid_constant__ Transform8Args a) {
@@ -60,14 +61,15 @@ __global__ void __launch_bounds__(128) transform8x8_kernel(const __grid_constant
 constexpr int kMbWarps = 4;   // macroblocks (warps) per CTA in the per-MB kernels
 
 __global__ void __launch_bounds__(32 * kMbWarps) me_lowres_kernel(const __grid_constant__ MeLowArgs a) {
-    __shared__ unsigned keys[kMbWarps][32];
+    __shared__ MeLowSmem sms[kMbWarps];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int mb = blockIdx.x * kMbWarps + warp;
     if (mb >= a.mbw * a.mbh) return;
     const int my = mb / a.mbw, mx = mb - my * a.mbw;
-    me_lowres_lane(lane, a, mx, my, keys[warp]);
+    me_lowres_load(lane, a, mx, my, sms[warp]);
     __syncwarp();
-    me_lowres_pick(lane, a, mx, my, keys[warp]);
+    const unsigned best = __reduce_min_sync(0xffffffffu, me_lowres_lane(lane, a, mx, my, sms[warp]));
+    me_lowres_out(lane, a, mx, my, best);
 }
 
 __global__ void __launch_bounds__(32 * kMbWarps) me_refine_kernel(const __grid_constant__ MeRefArgs a) {
@@ -77,15 +79,18 @@ __global__ void __launch_bounds__(32 * kMbWarps) me_refine_kernel(const __grid_c
     if (mb >= a.mbw * a.mbh) return;
     const int my = mb / a.mbw, mx = mb - my * a.mbw;
     MeRefSmem &sm = sms[warp];
+    me_ref_load(lane, a, mx, my, sm);
+    __syncwarp();
     me_ref_int(lane, a, mx, my, sm);
     __syncwarp();
     me_ref_pick(lane, a, mx, my, sm);
     __syncwarp();
     MeLane L;
     me_lane_init(lane, a, mx, my, sm, L);
-    for (int step = 2; step >= 1; --step)
-        for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci)
-            me_ref_take(a, L, me_group_sum(lane, me_ref_satd(a, L, ci, step)), ci, step);
+#pragma unroll
+    for (int ci = -1; ci < 8; ++ci) me_ref_take(a, L, me_group_sum(lane, me_ref_satd(a, sm, L, ci, 2)), ci, 2);
+#pragma unroll
+    for (int ci = 0; ci < 8; ++ci) me_ref_take(a, L, me_group_sum(lane, me_ref_satd(a, sm, L, ci, 1)), ci, 1);
     me_ref_publish(lane, L, sm);
     __syncwarp();
     me_ref_out(lane, a, mx, my, sm);

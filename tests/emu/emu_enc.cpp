@@ -13,9 +13,12 @@ using namespace gvc;
 void emu_run_me_lowres(const MeLowArgs &a) {
     for (int my = 0; my < a.mbh; ++my)
         for (int mx = 0; mx < a.mbw; ++mx) {
-            unsigned keys[32];
-            for (int l = 0; l < 32; ++l) me_lowres_lane(l, a, mx, my, keys);
-            for (int l = 0; l < 32; ++l) me_lowres_pick(l, a, mx, my, keys);
+            MeLowSmem sm;
+            memset(&sm, 0xAB, sizeof(sm));
+            for (int l = 0; l < 32; ++l) me_lowres_load(l, a, mx, my, sm);
+            unsigned best = 0xffffffffu;
+            for (int l = 0; l < 32; ++l) { const unsigned k = me_lowres_lane(l, a, mx, my, sm); best = k < best ? k : best; }
+            for (int l = 0; l < 32; ++l) me_lowres_out(l, a, mx, my, best);
         }
 }
 void emu_run_me_refine(const MeRefArgs &a) {
@@ -23,6 +26,7 @@ void emu_run_me_refine(const MeRefArgs &a) {
         for (int mx = 0; mx < a.mbw; ++mx) {
             MeRefSmem sm;
             memset(&sm, 0xAB, sizeof(sm));
+            for (int l = 0; l < 32; ++l) me_ref_load(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) me_ref_pick(l, a, mx, my, sm);
             MeLane L[32];
@@ -30,7 +34,7 @@ void emu_run_me_refine(const MeRefArgs &a) {
             for (int step = 2; step >= 1; --step)
                 for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
                     int part[32];
-                    for (int l = 0; l < 32; ++l) part[l] = me_ref_satd(a, L[l], ci, step);
+                    for (int l = 0; l < 32; ++l) part[l] = me_ref_satd(a, sm, L[l], ci, step);
                     for (int l = 0; l < 32; ++l) {          // what the shuffle butterfly computes on the GPU
                         int first, count, total = 0;
                         me_group(l, first, count);
@@ -87,9 +91,10 @@ void emu_hpel(const uint8_t *src, uint8_t *dh, uint8_t *dv, uint8_t *dc, int str
         for (int x0 = x_lo; x0 < x_hi; x0 += kHpTileW) {
             HpelSmem sm;
             memset(&sm, 0xAB, sizeof(sm));
-            for (int t = 0; t < kHpThreads; ++t) hpel_phase_a(t, a, x0, y0, sm);
-            for (int t = 0; t < kHpThreads; ++t) hpel_phase_b(t, a, x0, y0, sm);
-            for (int t = 0; t < kHpThreads; ++t) hpel_phase_c(t, a, x0, y0, sm);
+            const bool al = hpel_aligned(a);
+            for (int t = 0; t < kHpThreads; ++t) hpel_phase_a(t, a, al, x0, y0, sm);
+            for (int t = 0; t < kHpThreads; ++t) hpel_phase_b(t, a, al, x0, y0, sm);
+            for (int t = 0; t < kHpThreads; ++t) hpel_phase_c(t, a, al, x0, y0, sm);
         }
 }
 

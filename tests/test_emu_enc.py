@@ -69,6 +69,18 @@ def test_hpel_planes(pair):
         np.testing.assert_array_equal(o.full(), wnt.full())
 
 
+@pytest.mark.parametrize("w,h", [(131, 77), (132, 70), (64, 32), (5, 3), (200, 33)])
+def test_hpel_any_size_and_alignment(w, h):
+    """Odd widths / pitches take the byte-wise load and store path, multiples of four the word path; partial tiles in both."""
+    rng = np.random.Generator(np.random.PCG64(w * 1000 + h))
+    src = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    src[: h // 2, : w // 2] = np.where(rng.integers(0, 2, (h // 2, w // 2)) > 0, 255, 0)     # saturating edges
+    outs = [np.full((h, w), 0xEE, np.uint8) for _ in range(3)]
+    emu_lib.load().emu_hpel(_vp(src.ctypes.data), *[_vp(o.ctypes.data) for o in outs], w, 0, w, 0, h)
+    for o, wnt in zip(outs, E.oracle_hpel_full(src)):
+        np.testing.assert_array_equal(o, wnt)
+
+
 @pytest.mark.parametrize("r,qp", [(8, 23), (16, 36), (3, 0)])
 def test_me_lowres(pair, r, qp):
     g, ref, cur = pair

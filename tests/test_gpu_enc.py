@@ -66,6 +66,21 @@ def test_border_lowres_hpel(pair, dev):
         np.testing.assert_array_equal(_down(dd, o).full(), wnt.full())
 
 
+@pytest.mark.parametrize("w,h", [(131, 77), (132, 70), (64, 32), (5, 3), (200, 33), (1408, 848)])
+def test_hpel_any_size_and_alignment(dev, w, h):
+    """Odd widths / pitches take the byte-wise load and store path, multiples of four the word path; partial tiles in both."""
+    import torch
+    rng = np.random.Generator(np.random.PCG64(w * 1000 + h))
+    src = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    src[: h // 2, : w // 2] = np.where(rng.integers(0, 2, (h // 2, w // 2)) > 0, 255, 0)     # saturating edges
+    dsrc = torch.from_numpy(src).cuda()
+    douts = [torch.full((h, w), 0xEE, dtype=torch.uint8, device="cuda") for _ in range(3)]
+    dev.check(dev.lib.gvc_hpel_filter(_vp(dsrc.data_ptr()), *[_vp(o.data_ptr()) for o in douts], w, 0, w, 0, h, None))
+    torch.cuda.synchronize()
+    for o, wnt in zip(douts, E.oracle_hpel_full(src)):
+        np.testing.assert_array_equal(o.cpu().numpy(), wnt)
+
+
 @pytest.mark.parametrize("r,qp", [(8, 23), (16, 36)])
 def test_me_lowres(pair, r, qp):
     g, ref, cur = pair
