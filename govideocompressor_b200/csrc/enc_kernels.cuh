@@ -866,48 +866,142 @@ struct EncMbArgs {
     PackOut        pack;
 };
 struct EncMbSmem {               // per warp
-    int16_t  cblk[8][16];        // chroma blocks after the forward transform
-    uint8_t  cpred[8][16];
-    int      flags[32];
+    int      cdc[8];             // DC of the eight chroma blocks after the forward transform
+    int      dclev[8];           // quantised chroma DC levels, Cb[0..3] Cr[4..7]
+    unsigned mask;               // nzmask under construction
+    int      flags[32];          // [30], [31]: compact mask and first packed block (pack_reserve)
 };
-GVC_HD void enc_mb_p1(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
-    sm.flags[lane] = 0;
+struct EncLane {                 // what a lane carries in registers across the phases
+    int      d[16];              // residual -> coefficients (raster)
+    unsigned pred[4];            // prediction rows, four samples each
+    unsigned lev[8];             // quantised levels in zig-zag order, two int16 per word
+};
+GVC_HDH bool enc_mb_aligned(const EncMbArgs &a) {   // planes and pitches allow word loads / stores of 4-sample rows
+    return (((unsigned long long)a.cur_y | (unsigned long long)a.cur_u | (unsigned long long)a.cur_v | (unsigned long long)a.rec_y |
+             (unsigned long long)a.rec_u | (unsigned long long)a.rec_v | (unsigned long long)(unsigned)a.sy |
+             (unsigned long long)(unsigned)a.sc) & 3) == 0 && ((unsigned long long)a.coefs & 15) == 0;
+}
+GVC_HD void smem_or(unsigned *p, unsigned v) {
+#if defined(GVC_EMU)
+    *p |= v;
+#else
+    atomicOr(p, v);
+#endif
+}
+// lane -> its 4x4 block: lanes 0..15 luma (raster), 16..19 Cb, 20..23 Cr.  Position in the block's plane, partition index.
+GVC_HD void enc_lane_block(int lane, int mx, int my, int &x, int &y, int &k) {
+    if (lane < 16) { const int bx = 4 * (lane & 3), by = 4 * (lane >> 2); x = 16 * mx + bx; y = 16 * my + by; k = (by >> 3) * 2 + (bx >> 3); }
+    else           { const int b = (lane - 16) & 3; x = 8 * mx + 4 * (b & 1); y = 8 * my + 4 * (b >> 1); k = b; }   // chroma block b lies under partition b
+}
+// Phase 1: prediction, residual, forward 4x4 transform of every block; chroma DCs go to the shared record.
+GVC_HD void enc_mb_p1(int lane, const EncMbArgs &a, bool al, int mx, int my, EncMbSmem &sm, EncLane &L) {
+    if (lane == 0) sm.mask = 0;
     if (lane >= 24) return;
     const MbMotion &mo = a.motion[my * a.mbw + mx];
-    int16_t *co = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs + lane * 16;
-    int pred[16], d[16];
+    int x, y, k;
+    enc_lane_block(lane, mx, my, x, y, k);
+    const int mvx = mo.mv[k][0], mvy = mo.mv[k][1];
     if (lane < 16) {
-        const int bx = 4 * (lane & 3), by = 4 * (lane >> 2), k = (by >> 3) * 2 + (bx >> 3);
-        const int x = 16 * mx + bx, y = 16 * my + by;
-        mc_luma_4x4(a.ref, a.sy, x, y, mo.mv[k][0], mo.mv[k][1], pred);
+        const LumaSrc s = mc_luma_src(a.ref, a.sy, x, y, mvx, mvy);
         for (int j = 0; j < 4; ++j) {
-            const unsigned c = ld_u32_any(a.cur_y + (long long)(y + j) * a.sy + x);
-            for (int i = 0; i < 4; ++i) d[j * 4 + i] = (int)((c >> (8 * i)) & 255) - pred[j * 4 + i];
+            L.pred[j] = ld_u32_any(s.s1 + j * a.sy);
+            if (s.s2) L.pred[j] = avg_u8x4(L.pred[j], ld_u32_any(s.s2 + j * a.sy));
         }
-        dct4x4(d);
-        int nz = 0;
-        for (int i = 0; i < 16; ++i) {
-            const int cls = coef_class(i);
-            d[i] = quant_one(d[i], a.q.mf_y[cls], a.q.bias_y[cls]);
-            nz |= d[i];
-        }
-        for (int i = 0; i < 16; ++i) co[i] = (int16_t)d[zigzag4(i)];
-        sm.flags[lane] = nz != 0;
-        for (int i = 0; i < 16; ++i) d[i] = dequant_one(d[i], a.q.dq_y[coef_class(i)], a.q.qp);
-        idct4x4(d);
-        for (int j = 0; j < 4; ++j)
-            for (int i = 0; i < 4; ++i) a.rec_y[(long long)(y + j) * a.sy + x + i] = (uint8_t)clip_u8(pred[j * 4 + i] + d[j * 4 + i]);
     } else {
-        const int l = lane - 16, p = l >> 2, b = l & 3;
-        const int bx = 4 * (b & 1), by = 4 * (b >> 1), k = b;   // chroma block b lies under luma partition b
-        const int x = 8 * mx + bx, y = 8 * my + by;
-        const uint8_t *src = p ? a.cur_v : a.cur_u;
-        mc_chroma_4x4(p ? a.ref.v : a.ref.u, a.sc, x, y, mo.mv[k][0], mo.mv[k][1], pred);
-        for (int j = 0; j < 4; ++j)
-            for (int i = 0; i < 4; ++i) d[j * 4 + i] = (int)src[(long long)(y + j) * a.sc + x + i] - pred[j * 4 + i];
-        dct4x4(d);
-        for (int i = 0; i < 16; ++i) { sm.cblk[l][i] = (int16_t)d[i]; sm.cpred[l][i] = (uint8_t)pred[i]; }
+        int pr[16];
+        mc_chroma_4x4(lane < 20 ? a.ref.u : a.ref.v, a.sc, x, y, mvx, mvy, pr);
+        for (int j = 0; j < 4; ++j) L.pred[j] = (unsigned)pr[4 * j] | ((unsigned)pr[4 * j + 1] << 8) | ((unsigned)pr[4 * j + 2] << 16) | ((unsigned)pr[4 * j + 3] << 24);
     }
+    const int st = lane < 16 ? a.sy : a.sc;
+    const uint8_t *src = (lane < 16 ? a.cur_y : lane < 20 ? a.cur_u : a.cur_v) + (y * st + x);
+    for (int j = 0; j < 4; ++j) {
+        const unsigned c = al ? *reinterpret_cast<const unsigned *>(src + j * st) : ld_u32_any(src + j * st);
+        for (int i = 0; i < 4; ++i) L.d[j * 4 + i] = byte_of(c, i) - byte_of(L.pred[j], i);
+    }
+    dct4x4(L.d);
+    if (lane >= 16) sm.cdc[lane - 16] = L.d[0];
+}
+// Phase 2: chroma DC path (2x2 transform of the plane's four DCs; every lane of the plane recomputes it and keeps element
+// b), quantisation, levels, dequantisation, inverse transform, reconstruction.
+GVC_HD void enc_mb_p2(int lane, const EncMbArgs &a, bool al, int mx, int my, EncMbSmem &sm, EncLane &L) {
+    if (lane >= 24) return;
+    const QuantParams &q = a.q;
+    const bool luma = lane < 16;
+    int16_t *mbco = a.coefs ? a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs : nullptr;
+    int mydc = 0;
+    if (!luma) {
+        const int l = lane - 16, p = l >> 2, b = l & 3;
+        const int d0 = sm.cdc[4 * p], d1 = sm.cdc[4 * p + 1], d2 = sm.cdc[4 * p + 2], d3 = sm.cdc[4 * p + 3];
+        int dc[4] = {d0 + d1 + d2 + d3, d0 - d1 + d2 - d3, d0 + d1 - d2 - d3, d0 - d1 - d2 + d3};
+        int nzdc = 0;
+        for (int i = 0; i < 4; ++i) { dc[i] = quant_one(dc[i], q.mf_c[0] >> 1, q.bias_c[0] << 1); nzdc |= dc[i]; }
+        if (b == 0) {
+            for (int i = 0; i < 4; ++i) sm.dclev[4 * p + i] = dc[i];
+            if (mbco) for (int i = 0; i < 4; ++i) mbco[24 * 16 + 4 * p + i] = (int16_t)dc[i];
+            if (nzdc) smem_or(&sm.mask, 1u << (24 + p));
+        }
+        const int f = b == 0 ? dc[0] + dc[1] + dc[2] + dc[3] : b == 1 ? dc[0] - dc[1] + dc[2] - dc[3] : b == 2 ? dc[0] + dc[1] - dc[2] - dc[3] : dc[0] - dc[1] - dc[2] + dc[3];
+        mydc = (int)(int16_t)((f * (q.dq_c[0] << (q.qpc / 6))) >> 5);
+        L.d[0] = 0;
+    }
+    int mf[3], bias[3], dq[3];
+    for (int c = 0; c < 3; ++c) { mf[c] = luma ? q.mf_y[c] : q.mf_c[c]; bias[c] = luma ? q.bias_y[c] : q.bias_c[c]; dq[c] = luma ? q.dq_y[c] : q.dq_c[c]; }
+    const int qp = luma ? q.qp : q.qpc;
+    int nz = 0;
+    for (int i = 0; i < 16; ++i) { L.d[i] = quant_one(L.d[i], mf[coef_class(i)], bias[coef_class(i)]); nz |= L.d[i]; }
+    for (int i = 0; i < 8; ++i) L.lev[i] = ((unsigned)L.d[zigzag4(2 * i)] & 0xffffu) | ((unsigned)L.d[zigzag4(2 * i + 1)] << 16);
+    if (nz) smem_or(&sm.mask, 1u << lane);
+    if (mbco) {
+        if (al) {
+            gvc_uint4 *co = reinterpret_cast<gvc_uint4 *>(mbco + lane * 16);
+            gvc_uint4 v0, v1;
+            v0.x = L.lev[0]; v0.y = L.lev[1]; v0.z = L.lev[2]; v0.w = L.lev[3]; v1.x = L.lev[4]; v1.y = L.lev[5]; v1.z = L.lev[6]; v1.w = L.lev[7];
+            co[0] = v0; co[1] = v1;
+        } else {
+            for (int i = 0; i < 16; ++i) mbco[lane * 16 + i] = (int16_t)(L.lev[i >> 1] >> (16 * (i & 1)));
+        }
+    }
+    for (int i = 0; i < 16; ++i) L.d[i] = dequant_one(L.d[i], dq[coef_class(i)], qp);
+    if (!luma) L.d[0] = mydc;
+    idct4x4(L.d);
+    int x, y, k;
+    enc_lane_block(lane, mx, my, x, y, k);
+    const int st = luma ? a.sy : a.sc;
+    uint8_t *rec = (luma ? a.rec_y : lane < 20 ? a.rec_u : a.rec_v) + (y * st + x);
+    for (int j = 0; j < 4; ++j) {
+        unsigned w = 0;
+        for (int i = 0; i < 4; ++i) w |= (unsigned)clip_u8(byte_of(L.pred[j], i) + L.d[j * 4 + i]) << (8 * i);
+        if (al) *reinterpret_cast<unsigned *>(rec + j * st) = w;
+        else for (int i = 0; i < 4; ++i) rec[j * st + i] = (uint8_t)(w >> (8 * i));
+    }
+}
+// Phase 3: lane 0 publishes the mask and reserves room for the packed blocks; lanes 24..26 clear the unused tail of the record.
+GVC_HD void enc_mb_p3(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
+    const int mb = my * a.mbw + mx;
+    if (lane == 0) {
+        a.nzmask[mb] = sm.mask;
+        pack_reserve(lane, a.pack, mb, sm.mask, sm.flags);
+    } else if (lane >= 24 && lane < 27 && a.coefs) {
+        int16_t *z = a.coefs + (long long)mb * kMbCoefs + 24 * 16 + 8 * (lane - 23);   // 8 int16 each: [24][8..15], [25][0..7], [25][8..15]
+        for (int i = 0; i < 8; ++i) z[i] = 0;
+    }
+}
+// Phase 4: present blocks go straight from the lanes' registers to their packed place in host-mapped memory.
+GVC_HD void enc_mb_p4(int lane, const EncMbArgs &a, int mx, int my, const EncMbSmem &sm, const EncLane &L) {
+    if (lane >= 25 || !a.pack.blocks) return;
+    const unsigned cm = (unsigned)sm.flags[30];
+    if (!((cm >> lane) & 1u)) return;
+    const int rank = popcount32(cm & ((1u << lane) - 1u));
+    gvc_uint4 *dst = reinterpret_cast<gvc_uint4 *>(a.pack.blocks + ((long long)(unsigned)sm.flags[31] + rank) * 16);
+    gvc_uint4 v0, v1;
+    if (lane < 24) {
+        v0.x = L.lev[0]; v0.y = L.lev[1]; v0.z = L.lev[2]; v0.w = L.lev[3]; v1.x = L.lev[4]; v1.y = L.lev[5]; v1.z = L.lev[6]; v1.w = L.lev[7];
+    } else {
+        v0.x = ((unsigned)sm.dclev[0] & 0xffffu) | ((unsigned)sm.dclev[1] << 16); v0.y = ((unsigned)sm.dclev[2] & 0xffffu) | ((unsigned)sm.dclev[3] << 16);
+        v0.z = ((unsigned)sm.dclev[4] & 0xffffu) | ((unsigned)sm.dclev[5] << 16); v0.w = ((unsigned)sm.dclev[6] & 0xffffu) | ((unsigned)sm.dclev[7] << 16);
+        v1.x = v1.y = v1.z = v1.w = 0;
+    }
+    dst[0] = v0; dst[1] = v1;
 }
 // Second half of the chroma path, shared by the inter and intra kernels: 2x2 DC transform of the plane's four DCs
 // (every lane of the plane recomputes it and keeps element b), DC + AC quantisation, levels out, reconstruction.
@@ -942,23 +1036,6 @@ GVC_HD void chroma_finish(int lane, const QuantParams &q, int16_t *mbco, uint8_t
     const int x = 8 * mx + 4 * (b & 1), y = 8 * my + 4 * (b >> 1);
     for (int j = 0; j < 4; ++j)
         for (int i = 0; i < 4; ++i) rec[(long long)(y + j) * sc + x + i] = (uint8_t)clip_u8(cpred[l][j * 4 + i] + d[j * 4 + i]);
-}
-GVC_HD void enc_mb_p2(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
-    if (lane < 16 || lane >= 24) return;
-    chroma_finish(lane, a.q, a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs, a.rec_u, a.rec_v, a.sc, mx, my, sm.cblk, sm.cpred, sm.flags);
-}
-GVC_HD void enc_mb_p3(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
-    if (lane != 0) return;
-    uint32_t m = 0;
-    for (int i = 0; i < 26; ++i) m |= (uint32_t)(sm.flags[i] != 0) << i;
-    a.nzmask[my * a.mbw + mx] = m;
-    int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
-    for (int i = 8; i < 16; ++i) mbco[24 * 16 + i] = 0;
-    for (int i = 0; i < 16; ++i) mbco[25 * 16 + i] = 0;
-    pack_reserve(lane, a.pack, my * a.mbw + mx, m, sm.flags);
-}
-GVC_HD void enc_mb_p4(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
-    pack_copy(lane, a.pack, a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs, sm.flags);
 }
 
 // ------------------------------------------------------------------ K7 all-Intra16x16 frame (IDR) -

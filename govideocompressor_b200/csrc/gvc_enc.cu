@@ -103,13 +103,15 @@ __global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __gri
     if (mb >= a.mbw * a.mbh) return;
     const int my = mb / a.mbw, mx = mb - my * a.mbw;
     EncMbSmem &sm = sms[warp];
-    enc_mb_p1(lane, a, mx, my, sm);
+    const bool al = enc_mb_aligned(a);
+    EncLane L;
+    enc_mb_p1(lane, a, al, mx, my, sm, L);
     __syncwarp();
-    enc_mb_p2(lane, a, mx, my, sm);
+    enc_mb_p2(lane, a, al, mx, my, sm, L);
     __syncwarp();
     enc_mb_p3(lane, a, mx, my, sm);
     __syncwarp();
-    enc_mb_p4(lane, a, mx, my, sm);
+    enc_mb_p4(lane, a, mx, my, sm, L);
 }
 
 // One warp per macroblock row; rows advance as a wavefront (see enc_kernels.cuh K7).

@@ -89,7 +89,7 @@ public:
             rec_v_[i] = static_cast<uint8_t *>(ops_.alloc(ps_.c));
             rec_low_[i] = static_cast<uint8_t *>(ops_.alloc(ps_.l));
         }
-        d_coefs_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * kMbCoefs * nmb * n_frames));
+        d_coefs_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * kMbCoefs * nmb));   // staging of the IDR picture's record only
         d_nz_     = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb * n_frames));
         d_motion_ = static_cast<MbMotion *>(ops_.alloc(sizeof(MbMotion) * nmb * n_frames));
         d_modes_  = static_cast<uint8_t *>(ops_.alloc(nmb));
@@ -180,7 +180,7 @@ public:
                 EncMbArgs e;
                 e.cur_y = cy; e.cur_u = cu; e.cur_v = cv; e.ref = ref; e.rec_y = ry; e.rec_u = ru; e.rec_v = rv;
                 e.sy = g_.sy; e.sc = g_.sc; e.mbw = g_.mbw; e.mbh = g_.mbh; e.q = q;
-                e.motion = d_motion_ + nmb * f; e.coefs = d_coefs_ + size_t(kMbCoefs) * nmb * f; e.nzmask = d_nz_ + nmb * f;
+                e.motion = d_motion_ + nmb * f; e.coefs = nullptr; e.nzmask = d_nz_ + nmb * f;   // levels go straight to the packed blocks
                 e.pack.blocks = blocks_dev + size_t(kMbCoefs) * nmb * f; e.pack.offsets = d_offsets_ + nmb * f; e.pack.counter = d_counters_ + f;
                 if ((rc = ops_.encode_inter(e))) return rc;
             }

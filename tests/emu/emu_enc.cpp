@@ -51,10 +51,13 @@ void emu_run_encode_inter(const EncMbArgs &a) {
         for (int mx = 0; mx < a.mbw; ++mx) {
             EncMbSmem sm;
             memset(&sm, 0xAB, sizeof(sm));
-            for (int l = 0; l < 32; ++l) enc_mb_p1(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) enc_mb_p2(l, a, mx, my, sm);
+            const bool al = enc_mb_aligned(a);
+            EncLane L[32];
+            memset(L, 0xAB, sizeof(L));
+            for (int l = 0; l < 32; ++l) enc_mb_p1(l, a, al, mx, my, sm, L[l]);
+            for (int l = 0; l < 32; ++l) enc_mb_p2(l, a, al, mx, my, sm, L[l]);
             for (int l = 0; l < 32; ++l) enc_mb_p3(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) enc_mb_p4(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) enc_mb_p4(l, a, mx, my, sm, L[l]);
         }
 }
 void emu_run_encode_intra(const IntraArgs &a) {
