@@ -614,6 +614,7 @@ struct MeRefArgs {
     int            stride, w16, h16, mbw, mbh, lambda;
     const int16_t *lowres_mv;
     MbMotion      *out;
+    MbMotion      *out_host;     // optional second copy of the result (host-mapped memory), or null
 };
 struct MeRefSmem {               // per warp
     gvc_uint4      cur[16];      // the macroblock's 16 source rows
@@ -801,6 +802,7 @@ GVC_HD void me_ref_out(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &
     }
     m.pad[0] = m.pad[1] = m.pad[2] = 0;
     a.out[my * a.mbw + mx] = m;
+    if (a.out_host) a.out_host[my * a.mbw + mx] = m;
 }
 
 // ------------------------------------------------------------------ record compaction ------------

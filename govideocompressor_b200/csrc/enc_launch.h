@@ -13,6 +13,7 @@ int launch_lowres_batch(const LowresBatchArgs &a, cudaStream_t st);
 int launch_hpel(const HpelArgs &a, cudaStream_t st);
 int launch_me_lowres(const MeLowArgs &a, cudaStream_t st);
 int launch_me_refine(const MeRefArgs &a, cudaStream_t st);
+int launch_signal_picture(int *done, unsigned *count_out, const unsigned *count_in, cudaStream_t st);
 int launch_encode_inter(const EncMbArgs &a, cudaStream_t st);
 int launch_encode_intra(const IntraArgs &a, cudaStream_t st);
 }  // namespace gvc

@@ -198,6 +198,16 @@ int launch_me_lowres(const MeLowArgs &a, cudaStream_t st) {
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
+__global__ void signal_picture_kernel(int *done, unsigned *count_out, const unsigned *count_in) {
+    *count_out = *count_in;
+    __threadfence_system();
+    *reinterpret_cast<volatile int *>(done) = 1;
+}
+int launch_signal_picture(int *done, unsigned *count_out, const unsigned *count_in, cudaStream_t st) {
+    signal_picture_kernel<<<1, 1, 0, st>>>(done, count_out, count_in);
+    GVC_CUDA(cudaGetLastError());
+    return GVC_OK;
+}
 int launch_me_refine(const MeRefArgs &a, cudaStream_t st) {
     me_refine_kernel<<<(a.mbw * a.mbh + kMbWarps - 1) / kMbWarps, 32 * kMbWarps, 0, st>>>(a);
     GVC_CUDA(cudaGetLastError());
@@ -278,7 +288,7 @@ int gvc_me_refine(const uint8_t *cur_y, const gvc_ref_planes *ref, int stride, i
     }
     MeRefArgs a;
     a.cur = cur_y; a.ref = to_ref(ref); a.stride = stride; a.w16 = w16; a.h16 = h16; a.mbw = w16 / 16; a.mbh = h16 / 16;
-    a.lambda = lambda; a.lowres_mv = lowres_mv; a.out = reinterpret_cast<MbMotion *>(out);
+    a.lambda = lambda; a.lowres_mv = lowres_mv; a.out = reinterpret_cast<MbMotion *>(out); a.out_host = nullptr;
     return launch_me_refine(a, static_cast<cudaStream_t>(stream));
 }
 

@@ -77,7 +77,7 @@ struct CudaOps {
     int me_refine(const MeRefArgs &a) { return timed(kStMeRefine, [&] { return launch_me_refine(a, st); }); }
     int encode_inter(const EncMbArgs &a) { return timed(kStEncInter, [&] { return launch_encode_inter(a, st); }); }
     int encode_intra(const IntraArgs &a) { return timed(kStEncIntra, [&] { return launch_encode_intra(a, st); }); }
-    int download(void *dst, const void *src, size_t n) { GVC_CUDA(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, st)); return 0; }
+    int signal_picture(int *done, unsigned *count_out, const unsigned *count_in) { return launch_signal_picture(done, count_out, count_in, st); }
     int copy_plane(uint8_t *dst, int dpitch, const uint8_t *src, int spitch, int w, int h) {
         GVC_CUDA(cudaMemcpy2DAsync(dst, dpitch, src, spitch, w, h, cudaMemcpyDeviceToHost, st));
         return 0;

@@ -9,6 +9,7 @@
 // (gvc_segment.cu); the CPU test-suite instantiates it with the host emulation of the same kernel bodies
 // (tests/emu) to check the orchestration and the bitstream against a real decoder without a GPU.
 #pragma once
+#include <cstdlib>
 #include <cstdint>
 #include <cstring>
 #include <algorithm>
@@ -60,7 +61,7 @@ struct SegmentOutput {
 //   int extend_border3(const BorderBatchArgs &a);   int lowres_batch(const LowresBatchArgs &a);
 //   int hpel(const HpelArgs &a);  int me_lowres(const MeLowArgs &a);  int me_refine(const MeRefArgs &a);
 //   int encode_inter(const EncMbArgs &a);  int encode_intra(const IntraArgs &a);
-//   int download(void *host_dst, const void *dev_src, size_t bytes);
+//   int signal_picture(int *done, unsigned *count_out, const unsigned *count_in);   // *count_out = *count_in; fence; *done = 1
 //   int copy_plane(uint8_t *host_or_dev_dst, int dpitch, const uint8_t *dev_src, int spitch, int w, int h);   // device -> recon store
 //   int sync();
 template <class Ops>
@@ -90,14 +91,10 @@ public:
             rec_low_[i] = static_cast<uint8_t *>(ops_.alloc(ps_.l));
         }
         d_coefs_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * kMbCoefs * nmb));   // staging of the IDR picture's record only
-        d_nz_     = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb * n_frames));
         d_motion_ = static_cast<MbMotion *>(ops_.alloc(sizeof(MbMotion) * nmb * n_frames));
-        d_modes_  = static_cast<uint8_t *>(ops_.alloc(nmb));
         d_lowmv_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * 2 * nmb));
         d_prog_   = static_cast<int *>(ops_.alloc(sizeof(int) * g_.mbh));
-        d_one_    = static_cast<int *>(ops_.alloc(sizeof(int)));
         h_blocks_ = static_cast<int16_t *>(ops_.alloc_host(sizeof(int16_t) * kMbCoefs * nmb * n_frames));   // worst case: every block nonzero
-        d_offsets_ = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb * n_frames));
         d_counters_ = static_cast<unsigned *>(ops_.alloc(sizeof(unsigned) * n_frames));
         h_offsets_ = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * nmb * n_frames));
         h_nz_     = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * nmb * n_frames));
@@ -105,15 +102,13 @@ public:
         h_modes_  = static_cast<uint8_t *>(ops_.alloc_host(nmb));
         h_done_   = static_cast<int *>(ops_.alloc_host(sizeof(int) * n_frames));
         h_counters_ = static_cast<unsigned *>(ops_.alloc_host(sizeof(unsigned) * n_frames));
-        bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_coefs_ && d_nz_ && d_motion_ && d_modes_ && d_lowmv_ && d_prog_ && d_one_ &&
-                  h_blocks_ && d_offsets_ && d_counters_ && h_counters_ && h_offsets_ && h_nz_ && h_motion_ && h_modes_ && h_done_;
+        bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_coefs_ && d_motion_ && d_lowmv_ && d_prog_ &&
+                  h_blocks_ && d_counters_ && h_counters_ && h_offsets_ && h_nz_ && h_motion_ && h_modes_ && h_done_;
         for (int i = 0; i < 2; ++i) {
             for (int k = 0; k < 4; ++k) ok = ok && rec_y_[i][k];
             ok = ok && rec_u_[i] && rec_v_[i] && rec_low_[i];
         }
         if (!ok) { free_all(); return GVC_ERR_NOMEM; }
-        const int one = 1;
-        if (ops_.upload(d_one_, &one, sizeof(int))) { free_all(); return GVC_ERR_CUDA; }
         cap_ = n_frames;
         return 0;
     }
@@ -149,7 +144,12 @@ public:
         }
         const size_t nmb = size_t(g_.mbw) * g_.mbh;
         if ((rc = ops_.clear(d_counters_, sizeof(unsigned) * n))) return rc;
-        int16_t *blocks_dev = static_cast<int16_t *>(ops_.device_alias(h_blocks_));
+        int16_t  *blocks_dev  = static_cast<int16_t *>(ops_.device_alias(h_blocks_));
+        uint32_t *offsets_dev = static_cast<uint32_t *>(ops_.device_alias(h_offsets_)), *nz_dev = static_cast<uint32_t *>(ops_.device_alias(h_nz_));
+        MbMotion *motion_dev  = static_cast<MbMotion *>(ops_.device_alias(h_motion_));
+        uint8_t  *modes_dev   = static_cast<uint8_t *>(ops_.device_alias(h_modes_));
+        int      *done_dev    = static_cast<int *>(ops_.device_alias(h_done_));
+        unsigned *counters_dev = static_cast<unsigned *>(ops_.device_alias(h_counters_));
         if (cfg_.keep_recon) recon_store_.assign(size_t(g_.w16) * g_.h16 * 3 / 2 * n, 0);
         for (int f = 0; f < n; ++f) {
             const int r = f & 1, p = r ^ 1;
@@ -160,8 +160,8 @@ public:
                 a.cur_y = cy; a.cur_u = cu; a.cur_v = cv; a.rec_y = ry; a.rec_u = ru; a.rec_v = rv;
                 a.sy = g_.sy; a.sc = g_.sc; a.mbw = g_.mbw; a.mbh = g_.mbh;
                 fill_quant_params(a.q, cfg_.qp_i, true);
-                a.coefs = d_coefs_; a.nzmask = d_nz_; a.modes = d_modes_; a.progress = d_prog_;
-                a.pack.blocks = blocks_dev; a.pack.offsets = d_offsets_; a.pack.counter = d_counters_;
+                a.coefs = d_coefs_; a.nzmask = nz_dev; a.modes = modes_dev; a.progress = d_prog_;
+                a.pack.blocks = blocks_dev; a.pack.offsets = offsets_dev; a.pack.counter = d_counters_;
                 if ((rc = ops_.encode_intra(a))) return rc;
             } else {
                 RefPlanes ref;
@@ -175,24 +175,18 @@ public:
                 if ((rc = ops_.me_lowres(ml))) return rc;
                 MeRefArgs mr;
                 mr.cur = cy; mr.ref = ref; mr.stride = g_.sy; mr.w16 = g_.w16; mr.h16 = g_.h16; mr.mbw = g_.mbw; mr.mbh = g_.mbh;
-                mr.lambda = q.lambda; mr.lowres_mv = d_lowmv_; mr.out = d_motion_ + nmb * f;
+                mr.lambda = q.lambda; mr.lowres_mv = d_lowmv_; mr.out = d_motion_ + nmb * f; mr.out_host = motion_dev + nmb * f;
                 if ((rc = ops_.me_refine(mr))) return rc;
                 EncMbArgs e;
                 e.cur_y = cy; e.cur_u = cu; e.cur_v = cv; e.ref = ref; e.rec_y = ry; e.rec_u = ru; e.rec_v = rv;
                 e.sy = g_.sy; e.sc = g_.sc; e.mbw = g_.mbw; e.mbh = g_.mbh; e.q = q;
-                e.motion = d_motion_ + nmb * f; e.coefs = nullptr; e.nzmask = d_nz_ + nmb * f;   // levels go straight to the packed blocks
-                e.pack.blocks = blocks_dev + size_t(kMbCoefs) * nmb * f; e.pack.offsets = d_offsets_ + nmb * f; e.pack.counter = d_counters_ + f;
+                e.motion = d_motion_ + nmb * f; e.coefs = nullptr; e.nzmask = nz_dev + nmb * f;   // levels go straight to the packed blocks
+                e.pack.blocks = blocks_dev + size_t(kMbCoefs) * nmb * f; e.pack.offsets = offsets_dev + nmb * f; e.pack.counter = d_counters_ + f;
                 if ((rc = ops_.encode_inter(e))) return rc;
             }
-            {   // records of this picture -> host: the encode kernel has packed the nonzero blocks straight into mapped pinned memory, the
-                // small per-macroblock tables by copies, then the arrival flag (stream order: all of it has landed by then)
-                if ((rc = ops_.download(h_offsets_ + nmb * f, d_offsets_ + nmb * f, sizeof(uint32_t) * nmb))) return rc;
-                if ((rc = ops_.download(h_nz_ + nmb * f, d_nz_ + nmb * f, sizeof(uint32_t) * nmb))) return rc;
-                if (f == 0) { if ((rc = ops_.download(h_modes_, d_modes_, nmb))) return rc; }
-                else if ((rc = ops_.download(h_motion_ + nmb * f, d_motion_ + nmb * f, sizeof(MbMotion) * nmb))) return rc;
-                if ((rc = ops_.download(h_counters_ + f, d_counters_ + f, sizeof(unsigned)))) return rc;
-                if ((rc = ops_.download(h_done_ + f, d_one_, sizeof(int)))) return rc;
-            }
+            // the picture's records were stored into host memory by the kernels above; a last small kernel copies the block
+            // count and raises the arrival flag (stream order + a system-wide fence: everything has landed by then)
+            if ((rc = ops_.signal_picture(done_dev + f, counters_dev + f, d_counters_ + f))) return rc;
             if (cfg_.keep_recon) {
                 uint8_t *dst = recon_store_.data() + size_t(g_.w16) * g_.h16 * 3 / 2 * f;
                 if ((rc = ops_.copy_plane(dst, g_.w16, ry, g_.sy, g_.w16, g_.h16))) return rc;
@@ -254,7 +248,9 @@ public:
             pic.motion = h_motion_ + nmb * f;
             pic.modes = h_modes_;
             BitWriter bw;
-            write_slice(bw, pic, &out.stats[f]);
+            static const bool skip_entropy = getenv("GVC_SKIP_ENTROPY") != nullptr;   // measurement aid: stream is not decodable
+            if (!skip_entropy) write_slice(bw, pic, &out.stats[f]);
+            else bw.rbsp_trailing();
             if (f == 0) {   // parameter sets travel in-band with the IDR too (Annex B extraction stays decodable)
                 BitWriter s, p;
                 write_sps(s, sp);
@@ -311,9 +307,9 @@ private:
             for (int k = 0; k < 4; ++k) rel(rec_y_[i][k]);
             rel(rec_u_[i]); rel(rec_v_[i]); rel(rec_low_[i]);
         }
-        rel(d_coefs_); rel(d_nz_); rel(d_motion_); rel(d_modes_); rel(d_lowmv_); rel(d_prog_); rel(d_one_);
+        rel(d_coefs_); rel(d_motion_); rel(d_lowmv_); rel(d_prog_);
         auto relh = [&](auto *&p) { if (p) ops_.release_host(p); p = nullptr; };
-        rel(d_offsets_); rel(d_counters_); relh(h_offsets_); relh(h_counters_);
+        rel(d_counters_); relh(h_offsets_); relh(h_counters_);
         relh(h_blocks_); relh(h_nz_); relh(h_motion_); relh(h_modes_); relh(h_done_);
         cap_ = 0;
     }
@@ -328,19 +324,18 @@ private:
     uint8_t      *rec_y_[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
     uint8_t      *rec_u_[2] = {nullptr, nullptr}, *rec_v_[2] = {nullptr, nullptr}, *rec_low_[2] = {nullptr, nullptr};
     int16_t      *d_coefs_ = nullptr;
-    uint32_t     *d_nz_ = nullptr;
     MbMotion     *d_motion_ = nullptr;
-    uint8_t      *d_modes_ = nullptr;
     int16_t      *d_lowmv_ = nullptr;
     int          *d_prog_ = nullptr;
-    int          *d_one_ = nullptr;
-    int16_t      *h_blocks_ = nullptr;    // pinned + device-mapped: the nonzero blocks of every picture, packed
-    uint32_t     *d_offsets_ = nullptr, *h_offsets_ = nullptr;   // per MB: first packed block
+    // Records for the host entropy coder live in pinned memory mapped into the device address space; the kernels store
+    // into it directly (no copy engine on the pictures' critical path).
+    int16_t      *h_blocks_ = nullptr;    // the nonzero blocks of every picture, packed
+    uint32_t     *h_offsets_ = nullptr;   // per MB: first packed block
     unsigned     *d_counters_ = nullptr, *h_counters_ = nullptr;   // per picture: blocks handed out
     uint32_t     *h_nz_ = nullptr;
     MbMotion     *h_motion_ = nullptr;
     uint8_t      *h_modes_ = nullptr;
-    int          *h_done_ = nullptr;      // per picture: set to 1 by the last copy of that picture
+    int          *h_done_ = nullptr;      // per picture: set to 1 by the kernel that closes the picture
     std::vector<uint8_t> recon_store_;
 };
 

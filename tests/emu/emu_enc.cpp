@@ -118,7 +118,7 @@ void emu_me_refine(const uint8_t *cur, const uint8_t *const ref[7], int stride, 
                    int lambda, void *out) {
     MeRefArgs a;
     a.cur = cur; a.ref = mkref(ref); a.stride = stride; a.w16 = w16; a.h16 = h16; a.mbw = w16 / 16; a.mbh = h16 / 16;
-    a.lambda = lambda; a.lowres_mv = lowres_mv; a.out = static_cast<MbMotion *>(out);
+    a.lambda = lambda; a.lowres_mv = lowres_mv; a.out = static_cast<MbMotion *>(out); a.out_host = nullptr;
     emu_run_me_refine(a);
 }
 
