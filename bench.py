@@ -306,7 +306,8 @@ def main():
                 "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": NSEG * SEG_FRAMES * fb,
                         "d2h_bytes_per_step": d2h_bytes,
                         "stream_bytes_per_step": stream_bytes, "host_threads": cores},
-                "gpu_launches": launches * NSEG, "clocks": clocks,
+                # stage pass counts + the one-thread kernel that raises each picture's arrival flag (not a timed stage)
+                "gpu_launches": (launches + SEG_FRAMES * args.steps) * NSEG, "clocks": clocks,
                 "roofline": {"kernel": dom, "bound": "hbm", "achieved": d["achieved_gbs"], "peak": peak, "unit": "GB/s",
                              "frac": (d["achieved_gbs"] / peak) if d["achieved_gbs"] else None, "traffic": traffic,
                              "peak_source": peak_src, "algorithmic_bytes_per_launch": d["algorithmic_bytes_per_launch"],

@@ -827,7 +827,7 @@ struct PackOut {
     unsigned *counter;    // blocks handed out so far in this picture (zeroed before the launch)
 };
 // lane 0 reserves room for the macroblock's present blocks (order between macroblocks is whatever the hardware
-// schedules; the offset table makes it irrelevant), every lane then copies its block if present.
+// schedules; the offset table makes it irrelevant), every lane then stores its block there if present.
 GVC_HD void pack_reserve(int lane, const PackOut &po, int mb, uint32_t nz, int *flags) {
     if (lane != 0 || !po.blocks) return;
     const unsigned cm = compact_mask(nz);
@@ -840,16 +840,6 @@ GVC_HD void pack_reserve(int lane, const PackOut &po, int mb, uint32_t nz, int *
     po.offsets[mb] = base;
     flags[30] = (int)cm;
     flags[31] = (int)base;
-}
-GVC_HD void pack_copy(int lane, const PackOut &po, const int16_t *mbco, const int *flags) {
-    if (lane >= 26 || !po.blocks) return;
-    const unsigned cm = (unsigned)flags[30];
-    if (!((cm >> lane) & 1u)) return;
-    const int rank = popcount32(cm & ((1u << lane) - 1u));
-    const gvc_int4 *src = reinterpret_cast<const gvc_int4 *>(mbco + lane * 16);
-    gvc_int4       *dst = reinterpret_cast<gvc_int4 *>(po.blocks + ((long long)(unsigned)flags[31] + rank) * 16);
-    dst[0] = src[0];
-    dst[1] = src[1];
 }
 
 // ------------------------------------------------------------------ K5+K6 inter MB encode -------
@@ -1005,41 +995,6 @@ GVC_HD void enc_mb_p4(int lane, const EncMbArgs &a, int mx, int my, const EncMbS
     }
     dst[0] = v0; dst[1] = v1;
 }
-// Second half of the chroma path, shared by the inter and intra kernels: 2x2 DC transform of the plane's four DCs
-// (every lane of the plane recomputes it and keeps element b), DC + AC quantisation, levels out, reconstruction.
-GVC_HD void chroma_finish(int lane, const QuantParams &q, int16_t *mbco, uint8_t *rec_u, uint8_t *rec_v, int sc, int mx, int my,
-                          const int16_t cblk[8][16], const uint8_t cpred[8][16], int *flags) {
-    const int l = lane - 16, p = l >> 2, b = l & 3;
-    const int d0 = cblk[4 * p][0], d1 = cblk[4 * p + 1][0], d2 = cblk[4 * p + 2][0], d3 = cblk[4 * p + 3][0];
-    int dc[4] = {d0 + d1 + d2 + d3, d0 - d1 + d2 - d3, d0 + d1 - d2 - d3, d0 - d1 - d2 + d3};
-    int nzdc = 0;
-    for (int i = 0; i < 4; ++i) { dc[i] = quant_one(dc[i], q.mf_c[0] >> 1, q.bias_c[0] << 1); nzdc |= dc[i]; }
-    if (b == 0) {
-        for (int i = 0; i < 4; ++i) mbco[24 * 16 + 4 * p + i] = (int16_t)dc[i];
-        flags[24 + p] = nzdc != 0;
-    }
-    const int f[4] = {dc[0] + dc[1] + dc[2] + dc[3], dc[0] - dc[1] + dc[2] - dc[3], dc[0] + dc[1] - dc[2] - dc[3], dc[0] - dc[1] - dc[2] + dc[3]};
-    const int mydc = (int)(int16_t)((f[b] * (q.dq_c[0] << (q.qpc / 6))) >> 5);
-    int d[16], nz = 0;
-    for (int i = 0; i < 16; ++i) d[i] = cblk[l][i];
-    d[0] = 0;
-    for (int i = 0; i < 16; ++i) {
-        const int cls = coef_class(i);
-        d[i] = quant_one(d[i], q.mf_c[cls], q.bias_c[cls]);
-        nz |= d[i];
-    }
-    int16_t *co = mbco + lane * 16;
-    for (int i = 0; i < 16; ++i) co[i] = (int16_t)d[zigzag4(i)];
-    flags[lane] = nz != 0;
-    for (int i = 0; i < 16; ++i) d[i] = dequant_one(d[i], q.dq_c[coef_class(i)], q.qpc);
-    d[0] = mydc;
-    idct4x4(d);
-    uint8_t *rec = p ? rec_v : rec_u;
-    const int x = 8 * mx + 4 * (b & 1), y = 8 * my + 4 * (b >> 1);
-    for (int j = 0; j < 4; ++j)
-        for (int i = 0; i < 4; ++i) rec[(long long)(y + j) * sc + x + i] = (uint8_t)clip_u8(cpred[l][j * 4 + i] + d[j * 4 + i]);
-}
-
 // ------------------------------------------------------------------ K7 all-Intra16x16 frame (IDR) -
 // Specification: oracle/h264_mb.c gvc_oracle_encode_intra_frame (H.264 8.3.3, 8.3.4, 8.5.2, 8.5.10).  One warp
 // per macroblock ROW walks its row left to right; a row may start macroblock mx once the row above has
@@ -1057,160 +1012,224 @@ struct IntraArgs {
     PackOut        pack;
 };
 struct IntraSmem {
-    int      top[16], left[16];       // reconstructed neighbours of the luma MB
-    int      ctop[2][8], cleft[2][8];
-    int      sadp[3][16];
-    int16_t  lblk[16][16];            // dequantised luma AC (entry 0 unused)
-    int16_t  ldc[16];
-    int16_t  cblk[8][16];
-    uint8_t  cpred[8][16];
-    int      flags[32];
+    unsigned topw[4], leftw[4];        // reconstructed neighbours of the luma MB: the row above, the column to the left (4 samples per word)
+    unsigned ctopw[2][2], cleftw[2][2];
+    int      sad[3];                   // SAD of the three candidate modes
+    int      ldc[16], t1[16], dcl[16], t2[16];   // luma DC path: DCs, half-transformed, levels, half-inverse
+    int      cdc[8], dclev[8];         // chroma DCs / their levels (Cb[0..3], Cr[4..7])
+    unsigned mask;
+    int      flags[32];                // [30], [31]: compact mask and first packed block (pack_reserve)
 };
-// phase 0: fetch neighbours
-GVC_HD void intra_p0(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
-    const bool has_top = my > 0, has_left = mx > 0;
-    sm.flags[lane] = 0;
-    if (lane < 16) {
-        sm.top[lane]  = has_top ? ld_u8_cg(a.rec_y + (long long)(16 * my - 1) * a.sy + 16 * mx + lane) : 0;
-        sm.left[lane] = has_left ? ld_u8_cg(a.rec_y + (long long)(16 * my + lane) * a.sy + 16 * mx - 1) : 0;
-    } else {
-        const int l = lane - 16, p = l >> 3, i = l & 7;
-        const uint8_t *r = p ? a.rec_v : a.rec_u;
-        sm.ctop[p][i]  = has_top ? ld_u8_cg(r + (long long)(8 * my - 1) * a.sc + 8 * mx + i) : 0;
-        sm.cleft[p][i] = has_left ? ld_u8_cg(r + (long long)(8 * my + i) * a.sc + 8 * mx - 1) : 0;
+struct IntraLane {                     // per-lane registers carried across the phases
+    unsigned cur[4], pred[4];          // source / prediction rows of the lane's 4x4 block
+    int      d[16];
+    unsigned lev[8];
+};
+GVC_HDH bool intra_aligned(const IntraArgs &a) {
+    return (((unsigned long long)a.cur_y | (unsigned long long)a.cur_u | (unsigned long long)a.cur_v | (unsigned long long)a.rec_y |
+             (unsigned long long)a.rec_u | (unsigned long long)a.rec_v | (unsigned long long)(unsigned)a.sy |
+             (unsigned long long)(unsigned)a.sc) & 3) == 0 && ((unsigned long long)a.coefs & 15) == 0;
+}
+GVC_HD void smem_add(int *p, int v) {
+#if defined(GVC_EMU)
+    *p += v;
+#else
+    atomicAdd(p, v);
+#endif
+}
+GVC_HD unsigned ld_u32_cg(const uint8_t *p, bool al) {   // four samples another CTA of this launch may have written
+#if !defined(GVC_EMU)
+    if (al) return __ldcg(reinterpret_cast<const unsigned *>(p));
+#endif
+    return (unsigned)ld_u8_cg(p) | ((unsigned)ld_u8_cg(p + 1) << 8) | ((unsigned)ld_u8_cg(p + 2) << 16) | ((unsigned)ld_u8_cg(p + 3) << 24);
+}
+GVC_HD int sum_u8x4(unsigned w) { return dp4a_us(w, 0x01010101, 0); }
+GVC_HD unsigned rep_u8(int v) { return (unsigned)v * 0x01010101u; }
+// phase 0: the row above (from the reconstruction in global memory; the column to the left is still in shared memory
+// from the previous macroblock of this row) and the lane's source rows
+GVC_HD void intra_p0(int lane, const IntraArgs &a, bool al, int mx, int my, IntraSmem &sm, IntraLane &L) {
+    if (lane == 0) { sm.sad[0] = sm.sad[1] = sm.sad[2] = 0; sm.mask = 0; }
+    if (my > 0 && lane < 8) {
+        if (lane < 4) sm.topw[lane] = ld_u32_cg(a.rec_y + ((16 * my - 1) * a.sy + 16 * mx + 4 * lane), al);
+        else { const int p = (lane - 4) >> 1, k = lane & 1; sm.ctopw[p][k] = ld_u32_cg((p ? a.rec_v : a.rec_u) + ((8 * my - 1) * a.sc + 8 * mx + 4 * k), al); }
     }
+    if (lane >= 24) return;
+    int x, y, k;
+    enc_lane_block(lane, mx, my, x, y, k);
+    const int st = lane < 16 ? a.sy : a.sc;
+    const uint8_t *src = (lane < 16 ? a.cur_y : lane < 20 ? a.cur_u : a.cur_v) + (y * st + x);
+    for (int j = 0; j < 4; ++j) L.cur[j] = al ? *reinterpret_cast<const unsigned *>(src + j * st) : ld_u32_any(src + j * st);
 }
 GVC_HD int intra_dc_value(const IntraSmem &sm, bool has_top, bool has_left) {
     int sum = 0;
-    for (int i = 0; i < 16; ++i) sum += (has_top ? sm.top[i] : 0) + (has_left ? sm.left[i] : 0);
+    for (int i = 0; i < 4; ++i) sum += (has_top ? sum_u8x4(sm.topw[i]) : 0) + (has_left ? sum_u8x4(sm.leftw[i]) : 0);
     return has_top && has_left ? (sum + 16) >> 5 : (has_top || has_left) ? (sum + 8) >> 4 : 128;
 }
-GVC_HD int intra_pred_px(const IntraSmem &sm, int mode, int dcv, int x, int y) { return mode == 0 ? sm.top[x] : mode == 1 ? sm.left[y] : dcv; }
-// phase 1: per-block SAD of the three candidate modes
-GVC_HD void intra_p1(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+// prediction rows of luma block (bx, by) for a mode: 0 vertical, 1 horizontal, 2 DC
+GVC_HD void intra_pred_rows(const IntraSmem &sm, int mode, int dcv, int bx, int by, unsigned pr[4]) {
+    const unsigned lw = sm.leftw[by >> 2];
+    for (int j = 0; j < 4; ++j) pr[j] = mode == 0 ? sm.topw[bx >> 2] : mode == 1 ? rep_u8(byte_of(lw, j)) : rep_u8(dcv);
+}
+// phase 1: SAD of the three candidate modes over the lane's block, summed per mode in the shared record
+GVC_HD void intra_p1(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm, const IntraLane &L) {
     if (lane >= 16) return;
     const bool has_top = my > 0, has_left = mx > 0;
     const int  dcv = intra_dc_value(sm, has_top, has_left);
     const int  bx = 4 * (lane & 3), by = 4 * (lane >> 2);
-    int s[3] = {0, 0, 0};
-    for (int j = 0; j < 4; ++j) {
-        const unsigned c = ld_u32_any(a.cur_y + (long long)(16 * my + by + j) * a.sy + 16 * mx + bx);
-        for (int i = 0; i < 4; ++i) {
-            const int v = (int)((c >> (8 * i)) & 255);
-            for (int m = 0; m < 3; ++m) s[m] += iabs(v - intra_pred_px(sm, m, dcv, bx + i, by + j));
-        }
+    for (int m = 0; m < 3; ++m) {
+        if ((m == 0 && !has_top) || (m == 1 && !has_left)) continue;
+        unsigned pr[4], s = 0;
+        intra_pred_rows(sm, m, dcv, bx, by, pr);
+        for (int j = 0; j < 4; ++j) s = sad_u8x4(L.cur[j], pr[j], s);
+        smem_add(&sm.sad[m], (int)s);
     }
-    for (int m = 0; m < 3; ++m) sm.sadp[m][lane] = s[m];
 }
 GVC_HD int intra_pick_mode(const IntraSmem &sm, bool has_top, bool has_left) {
     int best = -1, mode = 2;
     for (int m = 0; m < 3; ++m) {
         if ((m == 0 && !has_top) || (m == 1 && !has_left)) continue;
-        int s = 0;
-        for (int i = 0; i < 16; ++i) s += sm.sadp[m][i];
-        if (best < 0 || s < best) { best = s; mode = m; }
+        if (best < 0 || sm.sad[m] < best) { best = sm.sad[m]; mode = m; }
     }
     return mode;
 }
-// phase 2: luma forward transform + AC quant; chroma prediction + forward transform
-GVC_HD void intra_p2(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+// phase 2: prediction, residual, forward transform of every block; DCs to the shared record
+GVC_HD void intra_p2(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm, IntraLane &L) {
     if (lane >= 24) return;
     const bool has_top = my > 0, has_left = mx > 0;
-    int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
-    int d[16];
     if (lane < 16) {
         const int mode = intra_pick_mode(sm, has_top, has_left), dcv = intra_dc_value(sm, has_top, has_left);
-        const int bx = 4 * (lane & 3), by = 4 * (lane >> 2);
-        for (int j = 0; j < 4; ++j) {
-            const unsigned c = ld_u32_any(a.cur_y + (long long)(16 * my + by + j) * a.sy + 16 * mx + bx);
-            for (int i = 0; i < 4; ++i) d[j * 4 + i] = (int)((c >> (8 * i)) & 255) - intra_pred_px(sm, mode, dcv, bx + i, by + j);
-        }
-        dct4x4(d);
-        sm.ldc[lane] = (int16_t)d[0];
-        d[0] = 0;
-        int nz = 0;
-        for (int i = 0; i < 16; ++i) {
-            const int cls = coef_class(i);
-            d[i] = quant_one(d[i], a.q.mf_y[cls], a.q.bias_y[cls]);
-            nz |= d[i];
-        }
-        for (int i = 0; i < 16; ++i) mbco[lane * 16 + i] = (int16_t)d[zigzag4(i)];
-        sm.flags[lane] = nz != 0;
-        for (int i = 0; i < 16; ++i) sm.lblk[lane][i] = (int16_t)dequant_one(d[i], a.q.dq_y[coef_class(i)], a.q.qp);
+        intra_pred_rows(sm, mode, dcv, 4 * (lane & 3), 4 * (lane >> 2), L.pred);
         if (lane == 0) a.modes[my * a.mbw + mx] = (uint8_t)mode;
     } else {
         const int l = lane - 16, p = l >> 2, b = l & 3, bx = b & 1, by = b >> 1;
-        int st[2] = {0, 0}, sl[2] = {0, 0};
-        for (int i = 0; i < 8; ++i) { st[i >> 2] += sm.ctop[p][i]; sl[i >> 2] += sm.cleft[p][i]; }
+        const int st[2] = {sum_u8x4(sm.ctopw[p][0]), sum_u8x4(sm.ctopw[p][1])}, sl[2] = {sum_u8x4(sm.cleftw[p][0]), sum_u8x4(sm.cleftw[p][1])};
         int v;
         if (bx == by)     v = has_top && has_left ? (st[bx] + sl[by] + 4) >> 3 : has_top ? (st[bx] + 2) >> 2 : has_left ? (sl[by] + 2) >> 2 : 128;
         else if (bx == 1) v = has_top ? (st[1] + 2) >> 2 : has_left ? (sl[0] + 2) >> 2 : 128;
         else              v = has_left ? (sl[1] + 2) >> 2 : has_top ? (st[0] + 2) >> 2 : 128;
-        const uint8_t *src = p ? a.cur_v : a.cur_u;
-        const int x = 8 * mx + 4 * bx, y = 8 * my + 4 * by;
-        for (int j = 0; j < 4; ++j)
-            for (int i = 0; i < 4; ++i) d[j * 4 + i] = (int)src[(long long)(y + j) * a.sc + x + i] - v;
-        dct4x4(d);
-        for (int i = 0; i < 16; ++i) { sm.cblk[l][i] = (int16_t)d[i]; sm.cpred[l][i] = (uint8_t)v; }
+        for (int j = 0; j < 4; ++j) L.pred[j] = rep_u8(v);
     }
+    for (int j = 0; j < 4; ++j)
+        for (int i = 0; i < 4; ++i) L.d[j * 4 + i] = byte_of(L.cur[j], i) - byte_of(L.pred[j], i);
+    dct4x4(L.d);
+    if (lane < 16) { sm.ldc[lane] = L.d[0]; L.d[0] = 0; }
+    else           { sm.cdc[lane - 16] = L.d[0]; }
 }
-// phase 3: luma DC path + reconstruction; chroma finish
-GVC_HD void intra_p3(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+// 4-point butterfly of (u0..u3), output k: the 1-D pass of the luma DC Hadamard (x264 dct4x4dc ordering)
+GVC_HD int had4_out(int u0, int u1, int u2, int u3, int k) {
+    const int s01 = u0 + u1, d01 = u0 - u1, s23 = u2 + u3, d23 = u2 - u3;
+    return k == 0 ? s01 + s23 : k == 1 ? s01 - s23 : k == 2 ? d01 - d23 : d01 + d23;
+}
+// phases 3a-3c: the 4x4 Hadamard of the sixteen luma DCs, one element per lane and one dimension per phase
+GVC_HD void intra_p3a(int lane, IntraSmem &sm) {
+    if (lane >= 16) return;
+    const int r = lane >> 2, c = lane & 3;
+    sm.t1[lane] = had4_out(sm.ldc[4 * r], sm.ldc[4 * r + 1], sm.ldc[4 * r + 2], sm.ldc[4 * r + 3], c);
+}
+GVC_HD void intra_p3b(int lane, const IntraArgs &a, IntraSmem &sm) {
+    if (lane >= 16) return;
+    const int r = lane >> 2, c = lane & 3;
+    const int o = (had4_out(sm.t1[c], sm.t1[4 + c], sm.t1[8 + c], sm.t1[12 + c], r) + 1) >> 1;
+    const int lev = quant_one((int)(int16_t)o, a.q.mf_y[0] >> 1, a.q.bias_y[0] << 1);
+    sm.dcl[lane] = lev;
+    if (lev) smem_or(&sm.mask, 1u << 26);
+}
+GVC_HD void intra_p3c(int lane, IntraSmem &sm) {
+    if (lane >= 16) return;
+    const int r = lane >> 2, c = lane & 3;
+    sm.t2[lane] = had4_out(sm.dcl[4 * r], sm.dcl[4 * r + 1], sm.dcl[4 * r + 2], sm.dcl[4 * r + 3], c);
+}
+// phase 3d: DC values back, quantisation, levels, dequantisation, inverse transform, reconstruction; the right-hand
+// column of the macroblock stays in shared memory for the next macroblock of the row
+GVC_HD void intra_p3d(int lane, const IntraArgs &a, bool al, int mx, int my, IntraSmem &sm, IntraLane &L) {
     if (lane >= 24) return;
-    int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
-    if (lane >= 16) { chroma_finish(lane, a.q, mbco, a.rec_u, a.rec_v, a.sc, mx, my, sm.cblk, sm.cpred, sm.flags); return; }
-    const bool has_top = my > 0, has_left = mx > 0;
-    // 4x4 Hadamard of the 16 DCs (every luma lane recomputes it and keeps its own element)
-    int t[16], o[16];
-    for (int i = 0; i < 4; ++i) {
-        const int s01 = sm.ldc[i * 4] + sm.ldc[i * 4 + 1], d01 = sm.ldc[i * 4] - sm.ldc[i * 4 + 1];
-        const int s23 = sm.ldc[i * 4 + 2] + sm.ldc[i * 4 + 3], d23 = sm.ldc[i * 4 + 2] - sm.ldc[i * 4 + 3];
-        t[i * 4] = s01 + s23; t[i * 4 + 1] = s01 - s23; t[i * 4 + 2] = d01 - d23; t[i * 4 + 3] = d01 + d23;
+    const QuantParams &q = a.q;
+    const bool luma = lane < 16;
+    int16_t *mbco = a.coefs ? a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs : nullptr;
+    int mydc;
+    if (luma) {
+        const int r = lane >> 2, c = lane & 3;
+        const int mine = (int)(int16_t)had4_out(sm.t2[c], sm.t2[4 + c], sm.t2[8 + c], sm.t2[12 + c], r);
+        const int qbits = q.qp / 6 - 6;
+        mydc = (int)(int16_t)(qbits >= 0 ? mine * (q.dq_y[0] << qbits) : (mine * q.dq_y[0] + (1 << (-qbits - 1))) >> (-qbits));
+        if (lane == 0 && mbco)
+            for (int i = 0; i < 16; ++i) mbco[25 * 16 + i] = (int16_t)sm.dcl[zigzag4(i)];
+    } else {
+        const int l = lane - 16, p = l >> 2, b = l & 3;
+        const int d0 = sm.cdc[4 * p], d1 = sm.cdc[4 * p + 1], d2 = sm.cdc[4 * p + 2], d3 = sm.cdc[4 * p + 3];
+        int dc[4] = {d0 + d1 + d2 + d3, d0 - d1 + d2 - d3, d0 + d1 - d2 - d3, d0 - d1 - d2 + d3};
+        int nzdc = 0;
+        for (int i = 0; i < 4; ++i) { dc[i] = quant_one(dc[i], q.mf_c[0] >> 1, q.bias_c[0] << 1); nzdc |= dc[i]; }
+        if (b == 0) {
+            for (int i = 0; i < 4; ++i) sm.dclev[4 * p + i] = dc[i];
+            if (mbco) for (int i = 0; i < 4; ++i) mbco[24 * 16 + 4 * p + i] = (int16_t)dc[i];
+            if (nzdc) smem_or(&sm.mask, 1u << (24 + p));
+        }
+        const int f = b == 0 ? dc[0] + dc[1] + dc[2] + dc[3] : b == 1 ? dc[0] - dc[1] + dc[2] - dc[3] : b == 2 ? dc[0] + dc[1] - dc[2] - dc[3] : dc[0] - dc[1] - dc[2] + dc[3];
+        mydc = (int)(int16_t)((f * (q.dq_c[0] << (q.qpc / 6))) >> 5);
+        L.d[0] = 0;
     }
-    int nzdc = 0;
+    int mf[3], bias[3], dq[3];
+    for (int c = 0; c < 3; ++c) { mf[c] = luma ? q.mf_y[c] : q.mf_c[c]; bias[c] = luma ? q.bias_y[c] : q.bias_c[c]; dq[c] = luma ? q.dq_y[c] : q.dq_c[c]; }
+    const int qp = luma ? q.qp : q.qpc;
+    int nz = 0;
+    for (int i = 0; i < 16; ++i) { L.d[i] = quant_one(L.d[i], mf[coef_class(i)], bias[coef_class(i)]); nz |= L.d[i]; }
+    for (int i = 0; i < 8; ++i) L.lev[i] = ((unsigned)L.d[zigzag4(2 * i)] & 0xffffu) | ((unsigned)L.d[zigzag4(2 * i + 1)] << 16);
+    if (nz) smem_or(&sm.mask, 1u << lane);
+    if (mbco) {
+        if (al) {
+            gvc_uint4 *co = reinterpret_cast<gvc_uint4 *>(mbco + lane * 16);
+            gvc_uint4 v0, v1;
+            v0.x = L.lev[0]; v0.y = L.lev[1]; v0.z = L.lev[2]; v0.w = L.lev[3]; v1.x = L.lev[4]; v1.y = L.lev[5]; v1.z = L.lev[6]; v1.w = L.lev[7];
+            co[0] = v0; co[1] = v1;
+        } else {
+            for (int i = 0; i < 16; ++i) mbco[lane * 16 + i] = (int16_t)(L.lev[i >> 1] >> (16 * (i & 1)));
+        }
+        if (lane == 16) for (int i = 8; i < 16; ++i) mbco[24 * 16 + i] = 0;
+    }
+    for (int i = 0; i < 16; ++i) L.d[i] = dequant_one(L.d[i], dq[coef_class(i)], qp);
+    L.d[0] = mydc;
+    idct4x4(L.d);
+    int x, y, k;
+    enc_lane_block(lane, mx, my, x, y, k);
+    const int st = luma ? a.sy : a.sc;
+    uint8_t *rec = (luma ? a.rec_y : lane < 20 ? a.rec_u : a.rec_v) + (y * st + x);
+    unsigned right = 0;
     for (int j = 0; j < 4; ++j) {
-        const int s01 = t[j] + t[4 + j], d01 = t[j] - t[4 + j], s23 = t[8 + j] + t[12 + j], d23 = t[8 + j] - t[12 + j];
-        o[j] = (s01 + s23 + 1) >> 1; o[4 + j] = (s01 - s23 + 1) >> 1; o[8 + j] = (d01 - d23 + 1) >> 1; o[12 + j] = (d01 + d23 + 1) >> 1;
+        unsigned w = 0;
+        for (int i = 0; i < 4; ++i) w |= (unsigned)clip_u8(byte_of(L.pred[j], i) + L.d[j * 4 + i]) << (8 * i);
+        if (al) *reinterpret_cast<unsigned *>(rec + j * st) = w;
+        else for (int i = 0; i < 4; ++i) rec[j * st + i] = (uint8_t)(w >> (8 * i));
+        right |= (w >> 24) << (8 * j);
     }
-    for (int i = 0; i < 16; ++i) { o[i] = quant_one((int)(int16_t)o[i], a.q.mf_y[0] >> 1, a.q.bias_y[0] << 1); nzdc |= o[i]; }
-    if (lane == 0) {
-        for (int i = 0; i < 16; ++i) mbco[25 * 16 + i] = (int16_t)o[zigzag4(i)];
-        sm.flags[26] = nzdc != 0;
-    }
-    for (int i = 0; i < 4; ++i) {
-        const int s01 = o[i * 4] + o[i * 4 + 1], d01 = o[i * 4] - o[i * 4 + 1], s23 = o[i * 4 + 2] + o[i * 4 + 3], d23 = o[i * 4 + 2] - o[i * 4 + 3];
-        t[i * 4] = s01 + s23; t[i * 4 + 1] = s01 - s23; t[i * 4 + 2] = d01 - d23; t[i * 4 + 3] = d01 + d23;
-    }
-    const int j = lane & 3, r = lane >> 2;   // element (r, j) of the inverse transform = column butterfly of column j
-    int mine;
-    {
-        const int s01 = t[j] + t[4 + j], d01 = t[j] - t[4 + j], s23 = t[8 + j] + t[12 + j], d23 = t[8 + j] - t[12 + j];
-        mine = r == 0 ? s01 + s23 : r == 1 ? s01 - s23 : r == 2 ? d01 - d23 : d01 + d23;
-    }
-    mine = (int)(int16_t)mine;
-    const int qbits = a.q.qp / 6 - 6;
-    const int dcq = (int)(int16_t)(qbits >= 0 ? mine * (a.q.dq_y[0] << qbits) : (mine * a.q.dq_y[0] + (1 << (-qbits - 1))) >> (-qbits));
-    int d[16];
-    for (int i = 0; i < 16; ++i) d[i] = sm.lblk[lane][i];
-    d[0] = dcq;
-    idct4x4(d);
-    const int mode = intra_pick_mode(sm, has_top, has_left), dcv = intra_dc_value(sm, has_top, has_left);
-    const int bx = 4 * (lane & 3), by = 4 * (lane >> 2);
-    for (int jj = 0; jj < 4; ++jj)
-        for (int i = 0; i < 4; ++i)
-            a.rec_y[(long long)(16 * my + by + jj) * a.sy + 16 * mx + bx + i] = (uint8_t)clip_u8(intra_pred_px(sm, mode, dcv, bx + i, by + jj) + d[jj * 4 + i]);
+    if (luma) { if ((lane & 3) == 3) sm.leftw[lane >> 2] = right; }
+    else      { const int l = lane - 16, p = l >> 2, b = l & 3; if (b & 1) sm.cleftw[p][b >> 1] = right; }
 }
+// phase 4 (after the row's progress has been published): mask out, room for the packed blocks
 GVC_HD void intra_p4(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
     if (lane != 0) return;
-    uint32_t m = 0;
-    for (int i = 0; i < 27; ++i) m |= (uint32_t)(sm.flags[i] != 0) << i;
-    a.nzmask[my * a.mbw + mx] = m;
-    int16_t *mbco = a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs;
-    for (int i = 8; i < 16; ++i) mbco[24 * 16 + i] = 0;
-    pack_reserve(lane, a.pack, my * a.mbw + mx, m, sm.flags);
+    a.nzmask[my * a.mbw + mx] = sm.mask;
+    pack_reserve(lane, a.pack, my * a.mbw + mx, sm.mask, sm.flags);
 }
-GVC_HD void intra_p5(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
-    pack_copy(lane, a.pack, a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs, sm.flags);
+// phase 5: present blocks from registers / the shared record to their packed place
+GVC_HD void intra_p5(int lane, const IntraArgs &a, int mx, int my, const IntraSmem &sm, const IntraLane &L) {
+    if (lane >= 26 || !a.pack.blocks) return;
+    const unsigned cm = (unsigned)sm.flags[30];
+    if (!((cm >> lane) & 1u)) return;
+    const int rank = popcount32(cm & ((1u << lane) - 1u));
+    gvc_uint4 *dst = reinterpret_cast<gvc_uint4 *>(a.pack.blocks + ((long long)(unsigned)sm.flags[31] + rank) * 16);
+    unsigned w[8];
+    if (lane < 24) {
+        for (int i = 0; i < 8; ++i) w[i] = L.lev[i];
+    } else if (lane == 24) {
+        for (int i = 0; i < 4; ++i) w[i] = ((unsigned)sm.dclev[2 * i] & 0xffffu) | ((unsigned)sm.dclev[2 * i + 1] << 16);
+        for (int i = 4; i < 8; ++i) w[i] = 0;
+    } else {
+        for (int i = 0; i < 8; ++i) w[i] = ((unsigned)sm.dcl[zigzag4(2 * i)] & 0xffffu) | ((unsigned)sm.dcl[zigzag4(2 * i + 1)] << 16);
+    }
+    gvc_uint4 v0, v1;
+    v0.x = w[0]; v0.y = w[1]; v0.z = w[2]; v0.w = w[3]; v1.x = w[4]; v1.y = w[5]; v1.z = w[6]; v1.w = w[7];
+    dst[0] = v0; dst[1] = v1;
 }
 
 }  // namespace gvc

@@ -118,7 +118,9 @@ __global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __gri
 __global__ void __launch_bounds__(32) intra_frame_kernel(const __grid_constant__ IntraArgs a) {
     __shared__ IntraSmem sm;
     const int my = blockIdx.x, lane = threadIdx.x;
+    const bool al = intra_aligned(a);
     volatile int *prog = a.progress;
+    IntraLane L;
     for (int mx = 0; mx < a.mbw; ++mx) {
         if (my > 0) {
             if (lane == 0)
@@ -126,20 +128,26 @@ __global__ void __launch_bounds__(32) intra_frame_kernel(const __grid_constant__
             __syncwarp();
             __threadfence();
         }
-        intra_p0(lane, a, mx, my, sm);
+        intra_p0(lane, a, al, mx, my, sm, L);
         __syncwarp();
-        intra_p1(lane, a, mx, my, sm);
+        intra_p1(lane, a, mx, my, sm, L);
         __syncwarp();
-        intra_p2(lane, a, mx, my, sm);
+        intra_p2(lane, a, mx, my, sm, L);
         __syncwarp();
-        intra_p3(lane, a, mx, my, sm);
+        intra_p3a(lane, sm);
         __syncwarp();
-        intra_p4(lane, a, mx, my, sm);
+        intra_p3b(lane, a, sm);
         __syncwarp();
-        intra_p5(lane, a, mx, my, sm);
+        intra_p3c(lane, sm);
+        __syncwarp();
+        intra_p3d(lane, a, al, mx, my, sm, L);
         __threadfence();
         __syncwarp();
-        if (lane == 0) prog[my] = mx + 1;
+        if (lane == 0) prog[my] = mx + 1;      // the row below may go on; packing is off its critical path
+        intra_p4(lane, a, mx, my, sm);
+        __syncwarp();
+        intra_p5(lane, a, mx, my, sm, L);
+        __syncwarp();
     }
 }
 

@@ -61,17 +61,24 @@ void emu_run_encode_inter(const EncMbArgs &a) {
         }
 }
 void emu_run_encode_intra(const IntraArgs &a) {
-    for (int my = 0; my < a.mbh; ++my)          // rows in order: every wavefront dependency is already satisfied
+    const bool al = intra_aligned(a);
+    for (int my = 0; my < a.mbh; ++my) {        // rows in order: every wavefront dependency is already satisfied
+        IntraSmem sm;                           // lives for the whole row: carries the left neighbours
+        memset(&sm, 0xAB, sizeof(sm));
         for (int mx = 0; mx < a.mbw; ++mx) {
-            IntraSmem sm;
-            memset(&sm, 0xAB, sizeof(sm));
-            for (int l = 0; l < 32; ++l) intra_p0(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) intra_p1(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) intra_p2(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) intra_p3(l, a, mx, my, sm);
+            IntraLane L[32];
+            memset(L, 0xAB, sizeof(L));
+            for (int l = 0; l < 32; ++l) intra_p0(l, a, al, mx, my, sm, L[l]);
+            for (int l = 0; l < 32; ++l) intra_p1(l, a, mx, my, sm, L[l]);
+            for (int l = 0; l < 32; ++l) intra_p2(l, a, mx, my, sm, L[l]);
+            for (int l = 0; l < 32; ++l) intra_p3a(l, sm);
+            for (int l = 0; l < 32; ++l) intra_p3b(l, a, sm);
+            for (int l = 0; l < 32; ++l) intra_p3c(l, sm);
+            for (int l = 0; l < 32; ++l) intra_p3d(l, a, al, mx, my, sm, L[l]);
             for (int l = 0; l < 32; ++l) intra_p4(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) intra_p5(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p5(l, a, mx, my, sm, L[l]);
         }
+    }
 }
 
 extern "C" {
