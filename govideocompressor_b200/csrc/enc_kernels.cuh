@@ -998,8 +998,11 @@ GVC_HD void enc_mb_p4(int lane, const EncMbArgs &a, int mx, int my, const EncMbS
 // ------------------------------------------------------------------ K7 all-Intra16x16 frame (IDR) -
 // Specification: oracle/h264_mb.c gvc_oracle_encode_intra_frame (H.264 8.3.3, 8.3.4, 8.5.2, 8.5.10).  One warp
 // per macroblock ROW walks its row left to right; a row may start macroblock mx once the row above has
-// finished macroblock mx (vertical / DC prediction read its bottom samples).  Progress counters live in global
-// memory (one int per row, zeroed before the launch); all rows are co-resident (<= 148 CTAs of one warp).
+// finished macroblock mx (vertical / DC prediction read its bottom samples).  The hand-over is a mailbox per macroblock
+// in global memory (zeroed before the launch): eight 64-bit words, each carrying four bottom-row samples and a nonzero
+// tag, stored by the lanes that own those samples.  A 64-bit store is single-copy atomic, so a consumer lane that
+// sees the tag has the samples in the same load: no fence on either side and one L2 round trip per dependent step.  All
+// rows are co-resident (<= 148 CTAs of one warp, dispatched in row order).
 struct IntraArgs {
     const uint8_t *cur_y, *cur_u, *cur_v;
     uint8_t       *rec_y, *rec_u, *rec_v;
@@ -1008,7 +1011,7 @@ struct IntraArgs {
     int16_t       *coefs;
     uint32_t      *nzmask;
     uint8_t       *modes;
-    int           *progress;   // [mbh]
+    unsigned long long *mail;  // [mbh*mbw][8] bottom-row mailboxes (zeroed before the launch), see intra_p0
     PackOut        pack;
 };
 struct IntraSmem {
@@ -1037,28 +1040,42 @@ GVC_HD void smem_add(int *p, int v) {
     atomicAdd(p, v);
 #endif
 }
-GVC_HD unsigned ld_u32_cg(const uint8_t *p, bool al) {   // four samples another CTA of this launch may have written
-#if !defined(GVC_EMU)
-    if (al) return __ldcg(reinterpret_cast<const unsigned *>(p));
-#endif
-    return (unsigned)ld_u8_cg(p) | ((unsigned)ld_u8_cg(p + 1) << 8) | ((unsigned)ld_u8_cg(p + 2) << 16) | ((unsigned)ld_u8_cg(p + 3) << 24);
-}
 GVC_HD int sum_u8x4(unsigned w) { return dp4a_us(w, 0x01010101, 0); }
 GVC_HD unsigned rep_u8(int v) { return (unsigned)v * 0x01010101u; }
-// phase 0: the row above (from the reconstruction in global memory; the column to the left is still in shared memory
-// from the previous macroblock of this row) and the lane's source rows
-GVC_HD void intra_p0(int lane, const IntraArgs &a, bool al, int mx, int my, IntraSmem &sm, IntraLane &L) {
-    if (lane == 0) { sm.sad[0] = sm.sad[1] = sm.sad[2] = 0; sm.mask = 0; }
-    if (my > 0 && lane < 8) {
-        if (lane < 4) sm.topw[lane] = ld_u32_cg(a.rec_y + ((16 * my - 1) * a.sy + 16 * mx + 4 * lane), al);
-        else { const int p = (lane - 4) >> 1, k = lane & 1; sm.ctopw[p][k] = ld_u32_cg((p ? a.rec_v : a.rec_u) + ((8 * my - 1) * a.sc + 8 * mx + 4 * k), al); }
-    }
+GVC_HD unsigned mail_wait(const unsigned long long *slot) {      // spins until the producer's tagged word has arrived
+#if defined(GVC_EMU)
+    return (unsigned)*slot;
+#else
+    unsigned long long v;
+    do { v = *reinterpret_cast<const volatile unsigned long long *>(slot); } while ((v >> 32) == 0);
+    return (unsigned)v;
+#endif
+}
+GVC_HD void mail_post(unsigned long long *slot, unsigned data) {
+#if defined(GVC_EMU)
+    *slot = (1ull << 32) | data;
+#else
+    *reinterpret_cast<volatile unsigned long long *>(slot) = (1ull << 32) | data;
+#endif
+}
+// the lane's four source rows of macroblock (mx, my)
+GVC_HD void intra_load_cur(int lane, const IntraArgs &a, bool al, int mx, int my, unsigned out[4]) {
     if (lane >= 24) return;
     int x, y, k;
     enc_lane_block(lane, mx, my, x, y, k);
     const int st = lane < 16 ? a.sy : a.sc;
     const uint8_t *src = (lane < 16 ? a.cur_y : lane < 20 ? a.cur_u : a.cur_v) + (y * st + x);
-    for (int j = 0; j < 4; ++j) L.cur[j] = al ? *reinterpret_cast<const unsigned *>(src + j * st) : ld_u32_any(src + j * st);
+    for (int j = 0; j < 4; ++j) out[j] = al ? *reinterpret_cast<const unsigned *>(src + j * st) : ld_u32_any(src + j * st);
+}
+// phase 0: the row above arrives through the mailbox of the macroblock above (the column to the left is still in shared
+// memory from the previous macroblock of this row)
+GVC_HD void intra_p0(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+    if (lane == 0) { sm.sad[0] = sm.sad[1] = sm.sad[2] = 0; sm.mask = 0; }
+    if (my > 0 && lane < 8) {
+        const unsigned w = mail_wait(a.mail + ((long long)((my - 1) * a.mbw + mx) * 8 + lane));
+        if (lane < 4) sm.topw[lane] = w;
+        else          sm.ctopw[(lane - 4) >> 1][lane & 1] = w;
+    }
 }
 GVC_HD int intra_dc_value(const IntraSmem &sm, bool has_top, bool has_left) {
     int sum = 0;
@@ -1194,22 +1211,43 @@ GVC_HD void intra_p3d(int lane, const IntraArgs &a, bool al, int mx, int my, Int
     enc_lane_block(lane, mx, my, x, y, k);
     const int st = luma ? a.sy : a.sc;
     uint8_t *rec = (luma ? a.rec_y : lane < 20 ? a.rec_u : a.rec_v) + (y * st + x);
-    unsigned right = 0;
+    unsigned right = 0, bottom = 0;
     for (int j = 0; j < 4; ++j) {
         unsigned w = 0;
         for (int i = 0; i < 4; ++i) w |= (unsigned)clip_u8(byte_of(L.pred[j], i) + L.d[j * 4 + i]) << (8 * i);
         if (al) *reinterpret_cast<unsigned *>(rec + j * st) = w;
         else for (int i = 0; i < 4; ++i) rec[j * st + i] = (uint8_t)(w >> (8 * i));
         right |= (w >> 24) << (8 * j);
+        bottom = w;
     }
     if (luma) { if ((lane & 3) == 3) sm.leftw[lane >> 2] = right; }
     else      { const int l = lane - 16, p = l >> 2, b = l & 3; if (b & 1) sm.cleftw[p][b >> 1] = right; }
+    if (my + 1 < a.mbh) {       // the macroblock below waits for these
+        unsigned long long *mail = a.mail + (long long)(my * a.mbw + mx) * 8;
+        if (luma) { if (lane >= 12) mail_post(mail + (lane & 3), bottom); }
+        else      { const int l = lane - 16, p = l >> 2, b = l & 3; if (b >= 2) mail_post(mail + 4 + 2 * p + (b & 1), bottom); }
+    }
 }
-// phase 4 (after the row's progress has been published): mask out, room for the packed blocks
-GVC_HD void intra_p4(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm) {
+// phase 4: mask out; room for the packed blocks comes from the row's own region of the picture's block area (row my starts
+// at block my * mbw * 26), so the wavefront needs no atomic: lane 0 keeps the row's running count
+GVC_HD void intra_p4(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm, int &row_count) {
     if (lane != 0) return;
-    a.nzmask[my * a.mbw + mx] = sm.mask;
-    pack_reserve(lane, a.pack, my * a.mbw + mx, sm.mask, sm.flags);
+    const int mb = my * a.mbw + mx;
+    a.nzmask[mb] = sm.mask;
+    if (!a.pack.blocks) return;
+    const unsigned cm = compact_mask(sm.mask), base = (unsigned)(my * a.mbw * 26 + row_count);
+    row_count += popcount32(cm);
+    a.pack.offsets[mb] = base;
+    sm.flags[30] = (int)cm;
+    sm.flags[31] = (int)base;
+}
+GVC_HD void intra_row_done(int lane, const IntraArgs &a, int row_count) {   // the picture's block count, once per row
+    if (lane != 0 || !a.pack.blocks) return;
+#if defined(GVC_EMU)
+    *a.pack.counter += (unsigned)row_count;
+#else
+    atomicAdd(a.pack.counter, (unsigned)row_count);
+#endif
 }
 // phase 5: present blocks from registers / the shared record to their packed place
 GVC_HD void intra_p5(int lane, const IntraArgs &a, int mx, int my, const IntraSmem &sm, const IntraLane &L) {

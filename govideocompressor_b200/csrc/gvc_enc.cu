@@ -119,16 +119,14 @@ __global__ void __launch_bounds__(32) intra_frame_kernel(const __grid_constant__
     __shared__ IntraSmem sm;
     const int my = blockIdx.x, lane = threadIdx.x;
     const bool al = intra_aligned(a);
-    volatile int *prog = a.progress;
     IntraLane L;
+    unsigned  next[4] = {0, 0, 0, 0};
+    int       row_count = 0;
+    intra_load_cur(lane, a, al, 0, my, next);
     for (int mx = 0; mx < a.mbw; ++mx) {
-        if (my > 0) {
-            if (lane == 0)
-                while (prog[my - 1] < mx + 1) { }
-            __syncwarp();
-            __threadfence();
-        }
-        intra_p0(lane, a, al, mx, my, sm, L);
+        for (int j = 0; j < 4; ++j) L.cur[j] = next[j];
+        if (mx + 1 < a.mbw) intra_load_cur(lane, a, al, mx + 1, my, next);   // in flight while this macroblock is coded
+        intra_p0(lane, a, mx, my, sm);
         __syncwarp();
         intra_p1(lane, a, mx, my, sm, L);
         __syncwarp();
@@ -141,14 +139,13 @@ __global__ void __launch_bounds__(32) intra_frame_kernel(const __grid_constant__
         intra_p3c(lane, sm);
         __syncwarp();
         intra_p3d(lane, a, al, mx, my, sm, L);
-        __threadfence();
         __syncwarp();
-        if (lane == 0) prog[my] = mx + 1;      // the row below may go on; packing is off its critical path
-        intra_p4(lane, a, mx, my, sm);
+        intra_p4(lane, a, mx, my, sm, row_count);
         __syncwarp();
         intra_p5(lane, a, mx, my, sm, L);
         __syncwarp();
     }
+    intra_row_done(lane, a, row_count);
 }
 
 // ---- launchers shared with the segment encoder -------------------------------------------------
@@ -228,7 +225,7 @@ int launch_encode_inter(const EncMbArgs &a, cudaStream_t st) {
 }
 
 int launch_encode_intra(const IntraArgs &a, cudaStream_t st) {
-    GVC_CUDA(cudaMemsetAsync(a.progress, 0, sizeof(int) * a.mbh, st));
+    GVC_CUDA(cudaMemsetAsync(a.mail, 0, sizeof(unsigned long long) * 8 * a.mbw * a.mbh, st));
     intra_frame_kernel<<<a.mbh, 32, 0, st>>>(a);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
@@ -320,11 +317,11 @@ int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
 }
 
 int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *cur_v, uint8_t *rec_y, uint8_t *rec_u, uint8_t *rec_v,
-                     int sy, int sc, int w16, int h16, int qp, int16_t *coefs, uint32_t *nzmask, uint8_t *modes, int *row_progress,
+                     int sy, int sc, int w16, int h16, int qp, int16_t *coefs, uint32_t *nzmask, uint8_t *modes, void *scratch,
                      void *stream) {
     int rc = enter();
     if (rc) return rc;
-    if (!cur_y || !cur_u || !cur_v || !rec_y || !rec_u || !rec_v || !coefs || !nzmask || !modes || !row_progress || (w16 & 15) || (h16 & 15) ||
+    if (!cur_y || !cur_u || !cur_v || !rec_y || !rec_u || !rec_v || !coefs || !nzmask || !modes || !scratch || (w16 & 15) || (h16 & 15) ||
         w16 < 16 || h16 < 16) {
         set_error("gvc_encode_intra: bad arguments");
         return GVC_ERR_INVALID_ARG;
@@ -335,7 +332,7 @@ int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
     a.cur_y = cur_y; a.cur_u = cur_u; a.cur_v = cur_v; a.rec_y = rec_y; a.rec_u = rec_u; a.rec_v = rec_v;
     a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, true);
-    a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.progress = row_progress;
+    a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.mail = static_cast<unsigned long long *>(scratch);
     a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
     return launch_encode_intra(a, static_cast<cudaStream_t>(stream));
 }

@@ -69,7 +69,6 @@ struct CudaOps {
     void *device_alias(void *h) { void *d = nullptr; return cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess ? d : nullptr; }
     int clear(void *dev, size_t n) { GVC_CUDA(cudaMemsetAsync(dev, 0, n, st)); return 0; }
     void  release_host(void *p) { cudaFreeHost(p); }
-    int upload(void *dst, const void *src, size_t n) { GVC_CUDA(cudaMemcpy(dst, src, n, cudaMemcpyHostToDevice)); return 0; }
     int extend_border3(const BorderBatchArgs &a) { return timed(kStBorder, [&] { return launch_extend_border_batch(a, st); }); }
     int lowres_batch(const LowresBatchArgs &a) { return timed(kStLowres, [&] { return launch_lowres_batch(a, st); }); }
     int hpel(const HpelArgs &a) { return timed(kStHpel, [&] { return launch_hpel(a, st); }); }

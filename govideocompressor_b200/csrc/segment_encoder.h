@@ -56,7 +56,7 @@ struct SegmentOutput {
 
 // Ops concept (all calls asynchronous and in order; sync() waits for everything issued so far):
 //   void *alloc(size_t bytes);  void release(void *p);   void *alloc_host(size_t bytes);  void release_host(void *p);   // pinned
-//   int upload(void *dev_dst, const void *host_src, size_t bytes);   void *device_alias(void *pinned_host);   // mapped address
+//   void *device_alias(void *pinned_host);   // the device address of mapped pinned memory
 //   int clear(void *dev, size_t bytes);
 //   int extend_border3(const BorderBatchArgs &a);   int lowres_batch(const LowresBatchArgs &a);
 //   int hpel(const HpelArgs &a);  int me_lowres(const MeLowArgs &a);  int me_refine(const MeRefArgs &a);
@@ -92,7 +92,7 @@ public:
         }
         d_motion_ = static_cast<MbMotion *>(ops_.alloc(sizeof(MbMotion) * nmb * n_frames));
         d_lowmv_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * 2 * nmb));
-        d_prog_   = static_cast<int *>(ops_.alloc(sizeof(int) * g_.mbh));
+        d_mail_   = static_cast<unsigned long long *>(ops_.alloc(sizeof(unsigned long long) * 8 * nmb));
         h_blocks_ = static_cast<int16_t *>(ops_.alloc_host(sizeof(int16_t) * kMbCoefs * nmb * n_frames));   // worst case: every block nonzero
         d_counters_ = static_cast<unsigned *>(ops_.alloc(sizeof(unsigned) * n_frames));
         h_offsets_ = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * nmb * n_frames));
@@ -101,7 +101,7 @@ public:
         h_modes_  = static_cast<uint8_t *>(ops_.alloc_host(nmb));
         h_done_   = static_cast<int *>(ops_.alloc_host(sizeof(int) * n_frames));
         h_counters_ = static_cast<unsigned *>(ops_.alloc_host(sizeof(unsigned) * n_frames));
-        bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_motion_ && d_lowmv_ && d_prog_ &&
+        bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_motion_ && d_lowmv_ && d_mail_ &&
                   h_blocks_ && d_counters_ && h_counters_ && h_offsets_ && h_nz_ && h_motion_ && h_modes_ && h_done_;
         for (int i = 0; i < 2; ++i) {
             for (int k = 0; k < 4; ++k) ok = ok && rec_y_[i][k];
@@ -159,7 +159,7 @@ public:
                 a.cur_y = cy; a.cur_u = cu; a.cur_v = cv; a.rec_y = ry; a.rec_u = ru; a.rec_v = rv;
                 a.sy = g_.sy; a.sc = g_.sc; a.mbw = g_.mbw; a.mbh = g_.mbh;
                 fill_quant_params(a.q, cfg_.qp_i, true);
-                a.coefs = nullptr; a.nzmask = nz_dev; a.modes = modes_dev; a.progress = d_prog_;
+                a.coefs = nullptr; a.nzmask = nz_dev; a.modes = modes_dev; a.mail = d_mail_;
                 a.pack.blocks = blocks_dev; a.pack.offsets = offsets_dev; a.pack.counter = d_counters_;
                 if ((rc = ops_.encode_intra(a))) return rc;
             } else {
@@ -306,7 +306,7 @@ private:
             for (int k = 0; k < 4; ++k) rel(rec_y_[i][k]);
             rel(rec_u_[i]); rel(rec_v_[i]); rel(rec_low_[i]);
         }
-        rel(d_motion_); rel(d_lowmv_); rel(d_prog_);
+        rel(d_motion_); rel(d_lowmv_); rel(d_mail_);
         auto relh = [&](auto *&p) { if (p) ops_.release_host(p); p = nullptr; };
         rel(d_counters_); relh(h_offsets_); relh(h_counters_);
         relh(h_blocks_); relh(h_nz_); relh(h_motion_); relh(h_modes_); relh(h_done_);
@@ -324,7 +324,7 @@ private:
     uint8_t      *rec_u_[2] = {nullptr, nullptr}, *rec_v_[2] = {nullptr, nullptr}, *rec_low_[2] = {nullptr, nullptr};
     MbMotion     *d_motion_ = nullptr;
     int16_t      *d_lowmv_ = nullptr;
-    int          *d_prog_ = nullptr;
+    unsigned long long *d_mail_ = nullptr;   // intra wavefront mailboxes
     // Records for the host entropy coder live in pinned memory mapped into the device address space; the kernels store
     // into it directly (no copy engine on the pictures' critical path).
     int16_t      *h_blocks_ = nullptr;    // the nonzero blocks of every picture, packed

@@ -156,11 +156,13 @@ int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
                      const gvc_mb_motion *motion, int qp, int16_t *coefs, uint32_t *nzmask, void *stream);
 /* K7: an all-Intra16x16 frame (the IDR that opens every segment): prediction from reconstructed neighbours
  * (H.264 8.3.3 vertical / horizontal / DC by SAD, chroma DC), transform with the luma DC Hadamard path, quant,
- * reconstruction.  Macroblock rows run as a wavefront inside one launch; row_progress is device scratch of
- * h16/16 ints (cleared by the call).  modes: chosen Intra16x16 prediction mode per MB. */
+ * reconstruction.  Macroblock rows run as a wavefront inside one launch; scratch is 8-byte aligned device memory of
+ * GVC_INTRA_SCRATCH_BYTES(w16, h16) bytes (cleared by the call: one 64-byte mailbox per macroblock hands the bottom row
+ * of samples to the macroblock below).  modes: chosen Intra16x16 prediction mode per MB. */
+#define GVC_INTRA_SCRATCH_BYTES(w16, h16) ((size_t)((w16) / 16) * ((h16) / 16) * 64)
 int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *cur_v, uint8_t *rec_y, uint8_t *rec_u,
                      uint8_t *rec_v, int sy, int sc, int w16, int h16, int qp, int16_t *coefs, uint32_t *nzmask,
-                     uint8_t *modes, int *row_progress, void *stream);
+                     uint8_t *modes, void *scratch, void *stream);
 /* 8x8 transform path (x264 sub8x8_dct8, quant_8x8, dequant_8x8, add8x8_idct8; H.264 8.5.13): residual of src - pred in 8x8
  * blocks -> levels (64 per block, raster, row = vertical frequency), nz flag per block, reconstruction.  Kernel-level
  * entry point with oracle parity; the segment encoder writes Constrained-Baseline streams and uses the 4x4 path. */

@@ -64,20 +64,23 @@ void emu_run_encode_intra(const IntraArgs &a) {
     const bool al = intra_aligned(a);
     for (int my = 0; my < a.mbh; ++my) {        // rows in order: every wavefront dependency is already satisfied
         IntraSmem sm;                           // lives for the whole row: carries the left neighbours
+        int row_count = 0;
         memset(&sm, 0xAB, sizeof(sm));
         for (int mx = 0; mx < a.mbw; ++mx) {
             IntraLane L[32];
             memset(L, 0xAB, sizeof(L));
-            for (int l = 0; l < 32; ++l) intra_p0(l, a, al, mx, my, sm, L[l]);
+            for (int l = 0; l < 32; ++l) intra_load_cur(l, a, al, mx, my, L[l].cur);
+            for (int l = 0; l < 32; ++l) intra_p0(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) intra_p1(l, a, mx, my, sm, L[l]);
             for (int l = 0; l < 32; ++l) intra_p2(l, a, mx, my, sm, L[l]);
             for (int l = 0; l < 32; ++l) intra_p3a(l, sm);
             for (int l = 0; l < 32; ++l) intra_p3b(l, a, sm);
             for (int l = 0; l < 32; ++l) intra_p3c(l, sm);
             for (int l = 0; l < 32; ++l) intra_p3d(l, a, al, mx, my, sm, L[l]);
-            for (int l = 0; l < 32; ++l) intra_p4(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) intra_p4(l, a, mx, my, sm, row_count);
             for (int l = 0; l < 32; ++l) intra_p5(l, a, mx, my, sm, L[l]);
         }
+        intra_row_done(0, a, row_count);
     }
 }
 
@@ -146,7 +149,9 @@ void emu_encode_intra(const uint8_t *const cur[3], uint8_t *const rec[3], int sy
     a.cur_y = cur[0]; a.cur_u = cur[1]; a.cur_v = cur[2]; a.rec_y = rec[0]; a.rec_u = rec[1]; a.rec_v = rec[2];
     a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, true);
-    a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.progress = nullptr;
+    a.coefs = coefs; a.nzmask = nzmask; a.modes = modes;
+    std::vector<unsigned long long> mail(size_t(8) * a.mbw * a.mbh, 0);
+    a.mail = mail.data();
     a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
     emu_run_encode_intra(a);
 }

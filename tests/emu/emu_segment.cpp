@@ -30,7 +30,6 @@ struct EmuOps {
     void  release(void *p) { free(p); }
     void *alloc_host(size_t n) { return calloc(1, n + 64); }
     void  release_host(void *p) { free(p); }
-    int upload(void *dst, const void *src, size_t n) { memcpy(dst, src, n); return 0; }
     void *device_alias(void *h) { return h; }
     int clear(void *p, size_t n) { memset(p, 0, n); return 0; }
     int extend_border3(const BorderBatchArgs &a) {      // same (piece, thread) decompositions as the CUDA kernels

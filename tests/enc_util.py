@@ -257,7 +257,7 @@ def encode_intra(backend, cur, qp):
         dco = torch.zeros(coefs.size, dtype=torch.int16, device="cuda")
         dnz = torch.zeros(n, dtype=torch.int32, device="cuda")
         dmo = torch.zeros(n, dtype=torch.uint8, device="cuda")
-        prog = torch.full((g["mbh"],), 77, dtype=torch.int32, device="cuda")
+        prog = torch.full((n * 16,), 77, dtype=torch.int32, device="cuda")     # GVC_INTRA_SCRATCH_BYTES, dirty on purpose
         d.check(d.lib.gvc_encode_intra(_vp(cy.ptr), _vp(cu.ptr), _vp(cv.ptr), _vp(ry.ptr), _vp(ru.ptr), _vp(rv.ptr), g["sy"], g["sc"],
                                        g["w16"], g["h16"], qp, _vp(dco.data_ptr()), _vp(dnz.data_ptr()), _vp(dmo.data_ptr()),
                                        _vp(prog.data_ptr()), None))
