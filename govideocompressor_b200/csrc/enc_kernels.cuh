@@ -856,6 +856,7 @@ struct EncMbArgs {
     int16_t       *coefs;
     uint32_t      *nzmask;
     PackOut        pack;
+    uint8_t       *nnz_y, *nnz_u, *nnz_v;   // optional: nonzero levels per 4x4 block, [4*mbh][4*mbw] / [2*mbh][2*mbw] (for the entropy kernels)
 };
 struct EncMbSmem {               // per warp
     int      cdc[8];             // DC of the eight chroma blocks after the forward transform
@@ -884,6 +885,14 @@ GVC_HD void smem_or(unsigned *p, unsigned v) {
 GVC_HD void enc_lane_block(int lane, int mx, int my, int &x, int &y, int &k) {
     if (lane < 16) { const int bx = 4 * (lane & 3), by = 4 * (lane >> 2); x = 16 * mx + bx; y = 16 * my + by; k = (by >> 3) * 2 + (bx >> 3); }
     else           { const int b = (lane - 16) & 3; x = 8 * mx + 4 * (b & 1); y = 8 * my + 4 * (b >> 1); k = b; }   // chroma block b lies under partition b
+}
+// number of nonzero levels of the lane's block -> the maps the entropy kernels derive nC from (H.264 9.2.1)
+GVC_HD void store_block_nnz(int lane, int mx, int my, int mbw, uint8_t *nnz_y, uint8_t *nnz_u, uint8_t *nnz_v, const int d[16]) {
+    if (!nnz_y) return;
+    int cnt = 0;
+    for (int i = 0; i < 16; ++i) cnt += d[i] != 0;
+    if (lane < 16) nnz_y[(4 * my + (lane >> 2)) * (4 * mbw) + 4 * mx + (lane & 3)] = (uint8_t)cnt;
+    else { const int b = (lane - 16) & 3; (lane < 20 ? nnz_u : nnz_v)[(2 * my + (b >> 1)) * (2 * mbw) + 2 * mx + (b & 1)] = (uint8_t)cnt; }
 }
 // Phase 1: prediction, residual, forward 4x4 transform of every block; chroma DCs go to the shared record.
 GVC_HD void enc_mb_p1(int lane, const EncMbArgs &a, bool al, int mx, int my, EncMbSmem &sm, EncLane &L) {
@@ -943,6 +952,7 @@ GVC_HD void enc_mb_p2(int lane, const EncMbArgs &a, bool al, int mx, int my, Enc
     for (int i = 0; i < 16; ++i) { L.d[i] = quant_one(L.d[i], mf[coef_class(i)], bias[coef_class(i)]); nz |= L.d[i]; }
     for (int i = 0; i < 8; ++i) L.lev[i] = ((unsigned)L.d[zigzag4(2 * i)] & 0xffffu) | ((unsigned)L.d[zigzag4(2 * i + 1)] << 16);
     if (nz) smem_or(&sm.mask, 1u << lane);
+    store_block_nnz(lane, mx, my, a.mbw, a.nnz_y, a.nnz_u, a.nnz_v, L.d);
     if (mbco) {
         if (al) {
             gvc_uint4 *co = reinterpret_cast<gvc_uint4 *>(mbco + lane * 16);
@@ -1013,6 +1023,7 @@ struct IntraArgs {
     uint8_t       *modes;
     unsigned long long *mail;  // [mbh*mbw][8] bottom-row mailboxes (zeroed before the launch), see intra_p0
     PackOut        pack;
+    uint8_t       *nnz_y, *nnz_u, *nnz_v;   // optional, as in EncMbArgs (AC levels only)
 };
 struct IntraSmem {
     unsigned topw[4], leftw[4];        // reconstructed neighbours of the luma MB: the row above, the column to the left (4 samples per word)
@@ -1193,6 +1204,7 @@ GVC_HD void intra_p3d(int lane, const IntraArgs &a, bool al, int mx, int my, Int
     for (int i = 0; i < 16; ++i) { L.d[i] = quant_one(L.d[i], mf[coef_class(i)], bias[coef_class(i)]); nz |= L.d[i]; }
     for (int i = 0; i < 8; ++i) L.lev[i] = ((unsigned)L.d[zigzag4(2 * i)] & 0xffffu) | ((unsigned)L.d[zigzag4(2 * i + 1)] << 16);
     if (nz) smem_or(&sm.mask, 1u << lane);
+    store_block_nnz(lane, mx, my, a.mbw, a.nnz_y, a.nnz_u, a.nnz_v, L.d);
     if (mbco) {
         if (al) {
             gvc_uint4 *co = reinterpret_cast<gvc_uint4 *>(mbco + lane * 16);

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include "enc_kernels.cuh"
+#include "entropy_kernels.cuh"
 
 namespace gvc {
 int launch_extend_border(uint8_t *p, int stride, int w, int h, int x_lo, int x_hi, int y_lo, int y_hi, cudaStream_t st);
@@ -16,4 +17,5 @@ int launch_me_refine(const MeRefArgs &a, cudaStream_t st);
 int launch_signal_picture(int *done, unsigned *count_out, const unsigned *count_in, cudaStream_t st);
 int launch_encode_inter(const EncMbArgs &a, cudaStream_t st);
 int launch_encode_intra(const IntraArgs &a, cudaStream_t st);
+int launch_entropy_picture(const EntropyPicture &p, cudaStream_t st);
 }  // namespace gvc

@@ -312,7 +312,7 @@ int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
     a.rec_y = rec_y; a.rec_u = rec_u; a.rec_v = rec_v; a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, false);
     a.motion = reinterpret_cast<const MbMotion *>(motion); a.coefs = coefs; a.nzmask = nzmask;
-    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
+    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr; a.nnz_y = a.nnz_u = a.nnz_v = nullptr;
     return launch_encode_inter(a, static_cast<cudaStream_t>(stream));
 }
 
@@ -333,7 +333,7 @@ int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
     a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, true);
     a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.mail = static_cast<unsigned long long *>(scratch);
-    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
+    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr; a.nnz_y = a.nnz_u = a.nnz_v = nullptr;
     return launch_encode_intra(a, static_cast<cudaStream_t>(stream));
 }
 

@@ -28,7 +28,8 @@ using namespace gvc;
 namespace {
 
 // Optional per-stage timing with CUDA events on the launching stream (bench.py's roofline figures).
-enum Stage { kStResize = 0, kStBorder, kStLowres, kStHpel, kStMeLowres, kStMeRefine, kStEncInter, kStEncIntra, kStCount };
+static_assert(GVC_STAGES == 9, "Stage below must list GVC_STAGES entries");
+enum Stage { kStResize = 0, kStBorder, kStLowres, kStHpel, kStMeLowres, kStMeRefine, kStEncInter, kStEncIntra, kStEntropy, kStCount };
 struct StageTimer {
     bool on = false;
     struct Rec { int stage; cudaEvent_t a, b; };
@@ -77,6 +78,7 @@ struct CudaOps {
     int encode_inter(const EncMbArgs &a) { return timed(kStEncInter, [&] { return launch_encode_inter(a, st); }); }
     int encode_intra(const IntraArgs &a) { return timed(kStEncIntra, [&] { return launch_encode_intra(a, st); }); }
     int signal_picture(int *done, unsigned *count_out, const unsigned *count_in) { return launch_signal_picture(done, count_out, count_in, st); }
+    int entropy_picture(const EntropyPicture &p) { return timed(kStEntropy, [&] { return launch_entropy_picture(p, st); }); }
     int copy_plane(uint8_t *dst, int dpitch, const uint8_t *src, int spitch, int w, int h) {
         GVC_CUDA(cudaMemcpy2DAsync(dst, dpitch, src, spitch, w, h, cudaMemcpyDeviceToHost, st));
         return 0;
@@ -210,6 +212,7 @@ int gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg) {
     sc.w = c.dst_w; sc.h = c.dst_h; sc.fps_num = c.fps_num; sc.fps_den = c.fps_den;
     sc.qp_p = c.crf; sc.qp_i = c.crf >= 3 ? c.crf - 3 : 0;     // x264's default ip_factor 1.4 is about 3 QP
     sc.merange = c.merange; sc.keep_recon = c.keep_recon != 0;
+    sc.device_entropy = c.entropy != GVC_ENTROPY_HOST;
     sc.host_threads = c.host_threads > 0 ? c.host_threads : int(std::max(1u, std::thread::hardware_concurrency()));
     e->seg = new (std::nothrow) SegmentEncoder<CudaOps>(e->ops, sc);
     if (!e->seg) { gvc_encoder_destroy(e); return GVC_ERR_NOMEM; }

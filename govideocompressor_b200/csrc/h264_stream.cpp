@@ -117,54 +117,9 @@ void write_pps(BitWriter &bw) {
 // ------------------------------------------------------------------------------- CAVLC tables --
 namespace {
 
-// Table 9-5, [table][4*total_coeff + trailing_ones]
-const uint8_t kCoeffTokenLen[4][68] = {
-    {1, 0, 0, 0, 6, 2, 0, 0, 8, 6, 3, 0, 9, 8, 7, 5, 10, 9, 8, 6, 11, 10, 9, 7, 13, 11, 10, 8, 13, 13, 11, 9, 13, 13, 13, 10,
-     14, 14, 13, 11, 14, 14, 14, 13, 15, 15, 14, 14, 15, 15, 15, 14, 16, 15, 15, 15, 16, 16, 16, 15, 16, 16, 16, 16, 16, 16, 16, 16},
-    {2, 0, 0, 0, 6, 2, 0, 0, 6, 5, 3, 0, 7, 6, 6, 4, 8, 6, 6, 4, 8, 7, 7, 5, 9, 8, 8, 6, 11, 9, 9, 6, 11, 11, 11, 7,
-     12, 11, 11, 9, 12, 12, 12, 11, 12, 12, 12, 11, 13, 13, 13, 12, 13, 13, 13, 13, 13, 14, 13, 13, 14, 14, 14, 13, 14, 14, 14, 14},
-    {4, 0, 0, 0, 6, 4, 0, 0, 6, 5, 4, 0, 6, 5, 5, 4, 7, 5, 5, 4, 7, 5, 5, 4, 7, 6, 6, 4, 7, 6, 6, 4, 8, 7, 7, 5,
-     8, 8, 7, 6, 9, 8, 8, 7, 9, 9, 8, 8, 9, 9, 9, 8, 10, 9, 9, 9, 10, 10, 10, 10, 10, 10, 10, 10, 10, 10, 10, 10},
-    {6, 0, 0, 0, 6, 6, 0, 0, 6, 6, 6, 0, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6,
-     6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 6}};
-const uint8_t kCoeffTokenBits[4][68] = {
-    {1, 0, 0, 0, 5, 1, 0, 0, 7, 4, 1, 0, 7, 6, 5, 3, 7, 6, 5, 3, 7, 6, 5, 4, 15, 6, 5, 4, 11, 14, 5, 4, 8, 10, 13, 4,
-     15, 14, 9, 4, 11, 10, 13, 12, 15, 14, 9, 12, 11, 10, 13, 8, 15, 1, 9, 12, 11, 14, 13, 8, 7, 10, 9, 12, 4, 6, 5, 8},
-    {3, 0, 0, 0, 11, 2, 0, 0, 7, 7, 3, 0, 7, 10, 9, 5, 7, 6, 5, 4, 4, 6, 5, 6, 7, 6, 5, 8, 15, 6, 5, 4, 11, 14, 13, 4,
-     15, 10, 9, 4, 11, 14, 13, 12, 8, 10, 9, 8, 15, 14, 13, 12, 11, 10, 9, 12, 7, 11, 6, 8, 9, 8, 10, 1, 7, 6, 5, 4},
-    {15, 0, 0, 0, 15, 14, 0, 0, 11, 15, 13, 0, 8, 12, 14, 12, 15, 10, 11, 11, 11, 8, 9, 10, 9, 14, 13, 9, 8, 10, 9, 8, 15, 14, 13, 13,
-     11, 14, 10, 12, 15, 10, 13, 12, 11, 14, 9, 12, 8, 10, 13, 8, 13, 7, 9, 12, 9, 12, 11, 10, 5, 8, 7, 6, 1, 4, 3, 2},
-    {3, 0, 0, 0, 0, 1, 0, 0, 4, 5, 6, 0, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22, 23, 24, 25, 26, 27, 28, 29, 30, 31,
-     32, 33, 34, 35, 36, 37, 38, 39, 40, 41, 42, 43, 44, 45, 46, 47, 48, 49, 50, 51, 52, 53, 54, 55, 56, 57, 58, 59, 60, 61, 62, 63}};
-// chroma DC (nC = -1), [4*total_coeff + trailing_ones]
-const uint8_t kChromaDcTokenLen[20]  = {2, 0, 0, 0, 6, 1, 0, 0, 6, 6, 3, 0, 6, 7, 7, 6, 6, 8, 8, 7};
-const uint8_t kChromaDcTokenBits[20] = {1, 0, 0, 0, 7, 1, 0, 0, 4, 6, 1, 0, 3, 3, 2, 5, 2, 3, 2, 0};
-// Tables 9-7 / 9-8: total_zeros for 4x4 blocks, [total_coeff-1][total_zeros]
-const uint8_t kTotalZerosLen[15][16] = {
-    {1, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 9}, {3, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 6, 6, 6, 6}, {4, 3, 3, 3, 4, 4, 3, 3, 4, 5, 5, 6, 5, 6},
-    {5, 3, 4, 4, 3, 3, 3, 4, 3, 4, 5, 5, 5},          {4, 4, 4, 3, 3, 3, 3, 3, 4, 5, 4, 5},          {6, 5, 3, 3, 3, 3, 3, 3, 4, 3, 6},
-    {6, 5, 3, 3, 3, 2, 3, 4, 3, 6},                   {6, 4, 5, 3, 2, 2, 3, 3, 6},                   {6, 6, 4, 2, 2, 3, 2, 5},
-    {5, 5, 3, 2, 2, 2, 4},                            {4, 4, 3, 3, 1, 3},                            {4, 4, 2, 1, 3},
-    {3, 3, 1, 2},                                     {2, 2, 1},                                     {1, 1}};
-const uint8_t kTotalZerosBits[15][16] = {
-    {1, 3, 2, 3, 2, 3, 2, 3, 2, 3, 2, 3, 2, 3, 2, 1}, {7, 6, 5, 4, 3, 5, 4, 3, 2, 3, 2, 3, 2, 1, 0}, {5, 7, 6, 5, 4, 3, 4, 3, 2, 3, 2, 1, 1, 0},
-    {3, 7, 5, 4, 6, 5, 4, 3, 3, 2, 2, 1, 0},          {5, 4, 3, 7, 6, 5, 4, 3, 2, 1, 1, 0},          {1, 1, 7, 6, 5, 4, 3, 2, 1, 1, 0},
-    {1, 1, 5, 4, 3, 3, 2, 1, 1, 0},                   {1, 1, 1, 3, 3, 2, 2, 1, 0},                   {1, 0, 1, 3, 2, 1, 1, 1},
-    {1, 0, 1, 3, 2, 1, 1},                            {0, 1, 1, 2, 1, 3},                            {0, 1, 1, 1, 1},
-    {0, 1, 1, 1},                                     {0, 1, 1},                                     {0, 1}};
-// Table 9-9 (a): total_zeros for chroma DC 2x2, [total_coeff-1][total_zeros]
-const uint8_t kChromaDcTotalZerosLen[3][4]  = {{1, 2, 3, 3}, {1, 2, 2, 0}, {1, 1, 0, 0}};
-const uint8_t kChromaDcTotalZerosBits[3][4] = {{1, 1, 1, 0}, {1, 1, 0, 0}, {1, 0, 0, 0}};
-// Table 9-10: run_before, [min(zeros_left,7)-1][run_before]
-const uint8_t kRunLen[7][16]  = {{1, 1}, {1, 2, 2}, {2, 2, 2, 2}, {2, 2, 2, 3, 3}, {2, 2, 3, 3, 3, 3}, {2, 3, 3, 3, 3, 3, 3},
-                                 {3, 3, 3, 3, 3, 3, 3, 4, 5, 6, 7, 8, 9, 10, 11}};
-const uint8_t kRunBits[7][16] = {{1, 0}, {1, 1, 0}, {3, 2, 1, 0}, {3, 2, 1, 1, 0}, {3, 2, 3, 2, 1, 0}, {3, 0, 1, 3, 2, 5, 4},
-                                 {7, 6, 5, 4, 3, 2, 1, 1, 1, 1, 1, 1, 1, 1, 1}};
-// Table 9-4 (ChromaArrayType 1): codeNum -> coded_block_pattern
-const uint8_t kCbpIntraFromCode[48] = {47, 31, 15, 0, 23, 27, 29, 30, 7, 11, 13, 14, 39, 43, 45, 46, 16, 3, 5, 10, 12, 19, 21, 26,
-                                       28, 35, 37, 42, 44, 1, 2, 4, 8, 17, 18, 20, 24, 6, 9, 22, 25, 32, 33, 34, 36, 40, 38, 41};
-const uint8_t kCbpInterFromCode[48] = {0, 16, 1, 2, 4, 8, 32, 3, 5, 10, 12, 15, 47, 7, 11, 13, 14, 6, 9, 31, 35, 37, 42, 44,
-                                       33, 34, 36, 40, 39, 43, 45, 46, 17, 18, 20, 24, 19, 21, 26, 28, 23, 27, 29, 30, 22, 25, 38, 41};
+#define GVC_TAB const
+#include "cavlc_tables.h"
+#undef GVC_TAB
 
 struct CbpCode {
     uint8_t inter[48], intra[48];
@@ -369,17 +324,7 @@ void clear_mb_nnz(PicState &s, int mx, int my) {
 }  // namespace
 
 // ------------------------------------------------------------------------------- slice ---------
-void write_slice(BitWriter &bw, const PictureData &pic, SliceStats *stats) {
-    PicState s;
-    s.mbw = pic.mbw; s.mbh = pic.mbh; s.w4 = 4 * pic.mbw; s.h4 = 4 * pic.mbh;
-    s.nnz_y.assign(size_t(s.w4) * s.h4, 0);
-    s.nnz_c[0].assign(size_t(4) * pic.mbw * pic.mbh, 0);
-    s.nnz_c[1].assign(size_t(4) * pic.mbw * pic.mbh, 0);
-    s.mv.assign(size_t(2) * s.w4 * s.h4, 0);
-    s.done.assign(size_t(s.w4) * s.h4, 0);
-    SliceStats st;
-
-    // slice_header()
+void write_slice_header(BitWriter &bw, const PictureData &pic) {
     bw.ue(0);                              // first_mb_in_slice
     bw.ue(pic.idr ? 7 : 5);                // slice_type: all slices of the picture are I / P
     bw.ue(0);                              // pic_parameter_set_id
@@ -395,6 +340,29 @@ void write_slice(BitWriter &bw, const PictureData &pic, SliceStats *stats) {
     }
     bw.se(pic.qp - 26);                    // slice_qp_delta
     bw.ue(1);                              // disable_deblocking_filter_idc = 1: no in-loop filter
+}
+size_t slice_header_bits(const PictureData &pic) {
+    BitWriter bw;
+    write_slice_header(bw, pic);
+    return bw.bit_count();
+}
+std::vector<uint8_t> slice_header_bytes(const PictureData &pic) {
+    BitWriter bw;
+    write_slice_header(bw, pic);
+    return bw.peek();
+}
+
+void write_slice(BitWriter &bw, const PictureData &pic, SliceStats *stats) {
+    PicState s;
+    s.mbw = pic.mbw; s.mbh = pic.mbh; s.w4 = 4 * pic.mbw; s.h4 = 4 * pic.mbh;
+    s.nnz_y.assign(size_t(s.w4) * s.h4, 0);
+    s.nnz_c[0].assign(size_t(4) * pic.mbw * pic.mbh, 0);
+    s.nnz_c[1].assign(size_t(4) * pic.mbw * pic.mbh, 0);
+    s.mv.assign(size_t(2) * s.w4 * s.h4, 0);
+    s.done.assign(size_t(s.w4) * s.h4, 0);
+    SliceStats st;
+
+    write_slice_header(bw, pic);
 
     // slice_data()
     int skip_run = 0;

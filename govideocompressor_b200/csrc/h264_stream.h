@@ -41,6 +41,11 @@ public:
     void se(int32_t v) { ue(v > 0 ? uint32_t(2 * v - 1) : uint32_t(-2 * int64_t(v))); }
     void rbsp_trailing();                        // stop bit + zero alignment; finalises bytes()
     size_t bit_count() const { return len_ * 8 + n_; }
+    std::vector<uint8_t> peek() const {           // the bits written so far, the last byte padded with zeros
+        std::vector<uint8_t> v(buf_.begin(), buf_.begin() + len_);
+        for (int left = n_; left > 0; left -= 8) v.push_back(uint8_t(left >= 8 ? acc_ >> (left - 8) : acc_ << (8 - left)));
+        return v;
+    }
     const std::vector<uint8_t> &bytes() const { return out_; }   // valid after rbsp_trailing()
 private:
     std::vector<uint8_t> buf_, out_;
@@ -82,5 +87,10 @@ struct SliceStats { int skipped = 0, p16 = 0, p8 = 0, intra = 0; size_t bits = 0
 
 // Writes slice_layer_without_partitioning_rbsp() for the whole picture.
 void write_slice(BitWriter &bw, const PictureData &pic, SliceStats *stats);
+// slice_header() alone (uses idr, frame_num, idr_pic_id, qp): its length in bits, and its bits as bytes (zero padded) --
+// for slices whose slice_data() was written by the GPU behind room for the header.
+void write_slice_header(BitWriter &bw, const PictureData &pic);
+size_t slice_header_bits(const PictureData &pic);
+std::vector<uint8_t> slice_header_bytes(const PictureData &pic);
 
 }  // namespace gvc

@@ -20,6 +20,7 @@
 #include "../../include/gvc.h"
 #include "enc_host.h"
 #include "enc_kernels.cuh"
+#include "entropy_kernels.cuh"
 #include "h264_stream.h"
 
 namespace gvc {
@@ -31,6 +32,7 @@ struct SegmentConfig {
     int  merange = 16;                  // full-resolution search range; the lowres window is merange/2
     bool keep_recon = false;            // keep every reconstructed picture (tests compare them with a decoder)
     int  host_threads = 1;              // worker threads for entropy coding (pictures are independent)
+    bool device_entropy = false;        // CAVLC on the GPU (entropy_kernels.cuh): finished slices cross PCIe instead of records
 };
 
 struct PlaneSizes { size_t y, c, l; int oy, oc, ol; };   // bytes per plane and offset of sample (0,0)
@@ -62,6 +64,7 @@ struct SegmentOutput {
 //   int hpel(const HpelArgs &a);  int me_lowres(const MeLowArgs &a);  int me_refine(const MeRefArgs &a);
 //   int encode_inter(const EncMbArgs &a);  int encode_intra(const IntraArgs &a);
 //   int signal_picture(int *done, unsigned *count_out, const unsigned *count_in);   // *count_out = *count_in; fence; *done = 1
+//   int entropy_picture(const EntropyPicture &p);                                    // device_entropy: the picture's slice -> host buffer
 //   int copy_plane(uint8_t *host_or_dev_dst, int dpitch, const uint8_t *dev_src, int spitch, int w, int h);   // device -> recon store
 //   int sync();
 template <class Ops>
@@ -93,16 +96,36 @@ public:
         d_motion_ = static_cast<MbMotion *>(ops_.alloc(sizeof(MbMotion) * nmb * n_frames));
         d_lowmv_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * 2 * nmb));
         d_mail_   = static_cast<unsigned long long *>(ops_.alloc(sizeof(unsigned long long) * 8 * nmb));
-        h_blocks_ = static_cast<int16_t *>(ops_.alloc_host(sizeof(int16_t) * kMbCoefs * nmb * n_frames));   // worst case: every block nonzero
         d_counters_ = static_cast<unsigned *>(ops_.alloc(sizeof(unsigned) * n_frames));
-        h_offsets_ = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * nmb * n_frames));
-        h_nz_     = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * nmb * n_frames));
-        h_motion_ = static_cast<MbMotion *>(ops_.alloc_host(sizeof(MbMotion) * nmb * n_frames));
-        h_modes_  = static_cast<uint8_t *>(ops_.alloc_host(nmb));
         h_done_   = static_cast<int *>(ops_.alloc_host(sizeof(int) * n_frames));
         h_counters_ = static_cast<unsigned *>(ops_.alloc_host(sizeof(unsigned) * n_frames));
-        bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_motion_ && d_lowmv_ && d_mail_ &&
-                  h_blocks_ && d_counters_ && h_counters_ && h_offsets_ && h_nz_ && h_motion_ && h_modes_ && h_done_;
+        bool ok = cur_.y && cur_.u && cur_.v && cur_low_ && d_motion_ && d_lowmv_ && d_mail_ && d_counters_ && h_counters_ && h_done_;
+        if (!cfg_.device_entropy) {     // records for the host entropy coder
+            h_blocks_ = static_cast<int16_t *>(ops_.alloc_host(sizeof(int16_t) * kMbCoefs * nmb * n_frames));   // worst case: every block nonzero
+            h_offsets_ = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * nmb * n_frames));
+            h_nz_     = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * nmb * n_frames));
+            h_motion_ = static_cast<MbMotion *>(ops_.alloc_host(sizeof(MbMotion) * nmb * n_frames));
+            h_modes_  = static_cast<uint8_t *>(ops_.alloc_host(nmb));
+            ok = ok && h_blocks_ && h_offsets_ && h_nz_ && h_motion_ && h_modes_;
+        } else {                        // one picture's records stay on the device; finished slices go to the host
+            e_blocks_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * kMbCoefs * nmb));
+            e_offsets_ = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb));
+            e_nz_      = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb));
+            e_modes_   = static_cast<uint8_t *>(ops_.alloc(nmb));
+            e_nnz_     = static_cast<uint8_t *>(ops_.alloc(24 * nmb));
+            e_mb_buf_  = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * kMbBufWords * nmb));
+            e_mb_bits_ = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb * 3));      // bits, offsets, runs
+            e_mb_kind_ = static_cast<uint8_t *>(ops_.alloc(nmb));
+            slice_words_ = int(std::min<size_t>(size_t(kMbBufWords) * nmb + 64, size_t(1) << 28));
+            e_slice_   = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * slice_words_));
+            e_info_    = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * 8));
+            e_used_    = static_cast<unsigned *>(ops_.alloc(sizeof(unsigned) * (n_frames + 1)));
+            slices_cap_ = size_t(g_.w16) * g_.h16 * 3 * n_frames + 65536;   // twice the raw pictures (noise at QP 0 reaches 1.8x)
+            h_slices_  = static_cast<uint8_t *>(ops_.alloc_host(slices_cap_));
+            h_pos_     = static_cast<uint32_t *>(ops_.alloc_host(sizeof(uint32_t) * 8 * n_frames));
+            ok = ok && e_blocks_ && e_offsets_ && e_nz_ && e_modes_ && e_nnz_ && e_mb_buf_ && e_mb_bits_ && e_mb_kind_ && e_slice_ && e_info_ &&
+                 e_used_ && h_slices_ && h_pos_;
+        }
         for (int i = 0; i < 2; ++i) {
             for (int k = 0; k < 4; ++k) ok = ok && rec_y_[i][k];
             ok = ok && rec_u_[i] && rec_v_[i] && rec_low_[i];
@@ -115,6 +138,11 @@ public:
     void set_frame_count(int n) { n_ = n; }
     // bytes that crossed PCIe towards the host for the last finished segment: packed blocks + per-macroblock tables + flags
     size_t record_bytes() const {
+        if (cfg_.device_entropy) {
+            size_t bytes = 0;
+            for (int f = 0; f < n_; ++f) bytes += ((h_pos_[8 * f + 1] + 15u) & ~15u) + 32 + 8;
+            return bytes;
+        }
         size_t blocks = 0;
         for (int f = 0; f < n_; ++f) blocks += h_counters_[f];
         const size_t nmb = size_t(g_.mbw) * g_.mbh;
@@ -143,10 +171,17 @@ public:
         }
         const size_t nmb = size_t(g_.mbw) * g_.mbh;
         if ((rc = ops_.clear(d_counters_, sizeof(unsigned) * n))) return rc;
-        int16_t  *blocks_dev  = static_cast<int16_t *>(ops_.device_alias(h_blocks_));
-        uint32_t *offsets_dev = static_cast<uint32_t *>(ops_.device_alias(h_offsets_)), *nz_dev = static_cast<uint32_t *>(ops_.device_alias(h_nz_));
-        MbMotion *motion_dev  = static_cast<MbMotion *>(ops_.device_alias(h_motion_));
-        uint8_t  *modes_dev   = static_cast<uint8_t *>(ops_.device_alias(h_modes_));
+        const bool de = cfg_.device_entropy;
+        // where the kernels put a picture's records: mapped host memory for the host entropy coder (one area per picture),
+        // or one device-resident set that the entropy kernels consume before the next picture overwrites it
+        int16_t  *blocks_dev  = de ? e_blocks_ : static_cast<int16_t *>(ops_.device_alias(h_blocks_));
+        uint32_t *offsets_dev = de ? e_offsets_ : static_cast<uint32_t *>(ops_.device_alias(h_offsets_));
+        uint32_t *nz_dev      = de ? e_nz_ : static_cast<uint32_t *>(ops_.device_alias(h_nz_));
+        MbMotion *motion_dev  = de ? nullptr : static_cast<MbMotion *>(ops_.device_alias(h_motion_));
+        uint8_t  *modes_dev   = de ? e_modes_ : static_cast<uint8_t *>(ops_.device_alias(h_modes_));
+        const size_t per_pic  = de ? 0 : 1;      // records of picture f start at f * per_pic * (size of one picture's records)
+        uint8_t *nnz_y = de ? e_nnz_ : nullptr, *nnz_u = de ? e_nnz_ + 16 * nmb : nullptr, *nnz_v = de ? e_nnz_ + 20 * nmb : nullptr;
+        if (de && (rc = ops_.clear(e_used_, sizeof(unsigned)))) return rc;
         int      *done_dev    = static_cast<int *>(ops_.device_alias(h_done_));
         unsigned *counters_dev = static_cast<unsigned *>(ops_.device_alias(h_counters_));
         if (cfg_.keep_recon) recon_store_.assign(size_t(g_.w16) * g_.h16 * 3 / 2 * n, 0);
@@ -161,6 +196,7 @@ public:
                 fill_quant_params(a.q, cfg_.qp_i, true);
                 a.coefs = nullptr; a.nzmask = nz_dev; a.modes = modes_dev; a.mail = d_mail_;
                 a.pack.blocks = blocks_dev; a.pack.offsets = offsets_dev; a.pack.counter = d_counters_;
+                a.nnz_y = nnz_y; a.nnz_u = nnz_u; a.nnz_v = nnz_v;
                 if ((rc = ops_.encode_intra(a))) return rc;
             } else {
                 RefPlanes ref;
@@ -174,17 +210,34 @@ public:
                 if ((rc = ops_.me_lowres(ml))) return rc;
                 MeRefArgs mr;
                 mr.cur = cy; mr.ref = ref; mr.stride = g_.sy; mr.w16 = g_.w16; mr.h16 = g_.h16; mr.mbw = g_.mbw; mr.mbh = g_.mbh;
-                mr.lambda = q.lambda; mr.lowres_mv = d_lowmv_; mr.out = d_motion_ + nmb * f; mr.out_host = motion_dev + nmb * f;
+                mr.lambda = q.lambda; mr.lowres_mv = d_lowmv_; mr.out = d_motion_ + nmb * f; mr.out_host = de ? nullptr : motion_dev + nmb * f;
                 if ((rc = ops_.me_refine(mr))) return rc;
                 EncMbArgs e;
                 e.cur_y = cy; e.cur_u = cu; e.cur_v = cv; e.ref = ref; e.rec_y = ry; e.rec_u = ru; e.rec_v = rv;
                 e.sy = g_.sy; e.sc = g_.sc; e.mbw = g_.mbw; e.mbh = g_.mbh; e.q = q;
-                e.motion = d_motion_ + nmb * f; e.coefs = nullptr; e.nzmask = nz_dev + nmb * f;   // levels go straight to the packed blocks
-                e.pack.blocks = blocks_dev + size_t(kMbCoefs) * nmb * f; e.pack.offsets = offsets_dev + nmb * f; e.pack.counter = d_counters_ + f;
+                e.motion = d_motion_ + nmb * f; e.coefs = nullptr; e.nzmask = nz_dev + nmb * f * per_pic;   // levels go straight to the packed blocks
+                e.pack.blocks = blocks_dev + size_t(kMbCoefs) * nmb * f * per_pic; e.pack.offsets = offsets_dev + nmb * f * per_pic; e.pack.counter = d_counters_ + f;
+                e.nnz_y = nnz_y; e.nnz_u = nnz_u; e.nnz_v = nnz_v;
                 if ((rc = ops_.encode_inter(e))) return rc;
             }
             // the picture's records were stored into host memory by the kernels above; a last small kernel copies the block
             // count and raises the arrival flag (stream order + a system-wide fence: everything has landed by then)
+            if (de) {     // the picture's slice data: macroblock bits, scan, placement, copy to the host buffer
+                EntropyPicture ep;
+                ep.ent.mbw = g_.mbw; ep.ent.mbh = g_.mbh; ep.ent.idr = f == 0;
+                ep.ent.nzmask = e_nz_; ep.ent.motion = d_motion_ + nmb * f; ep.ent.modes = e_modes_;
+                ep.ent.blocks = e_blocks_; ep.ent.offsets = e_offsets_;
+                ep.ent.nnz_y = nnz_y; ep.ent.nnz_c[0] = nnz_u; ep.ent.nnz_c[1] = nnz_v;
+                ep.ent.mb_buf = e_mb_buf_; ep.ent.mb_bits = e_mb_bits_; ep.ent.mb_kind = e_mb_kind_;
+                ep.slice.nmb = int(nmb); ep.slice.mb_buf = e_mb_buf_; ep.slice.mb_bits = e_mb_bits_; ep.slice.mb_kind = e_mb_kind_;
+                ep.slice.mb_off = e_mb_bits_ + nmb; ep.slice.mb_run = e_mb_bits_ + 2 * nmb;
+                ep.slice.slice = e_slice_; ep.slice.slice_words = slice_words_;
+                ep.slice.header_bits = int(slice_header_bits(picture_header(f)));
+                ep.slice.p_slice = f != 0; ep.slice.info = e_info_;
+                ep.host_buf = static_cast<uint8_t *>(ops_.device_alias(h_slices_)); ep.host_cap = unsigned(std::min<size_t>(slices_cap_, 0xfffffff0u));
+                ep.used = e_used_ + f; ep.pos = static_cast<uint32_t *>(ops_.device_alias(h_pos_)) + 8 * f;
+                if ((rc = ops_.entropy_picture(ep))) return rc;
+            }
             if ((rc = ops_.signal_picture(done_dev + f, counters_dev + f, d_counters_ + f))) return rc;
             if (cfg_.keep_recon) {
                 uint8_t *dst = recon_store_.data() + size_t(g_.w16) * g_.h16 * 3 / 2 * f;
@@ -208,9 +261,11 @@ public:
     // Entropy-codes the pictures as their records arrive (worker threads wait on the arrival flags while the GPU is still
     // working on later pictures), then waits for the stream.
     int finish(SegmentOutput &out) {
+        failed_ = false;
         write_stream(out);
         const int rc = ops_.sync();
         if (rc) return rc;
+        if (failed_) return GVC_ERR_TOO_LARGE;     // the slices outgrew the buffers sized from the raw pictures
         if (cfg_.keep_recon) out.recon.swap(recon_store_);
         return 0;
     }
@@ -237,9 +292,26 @@ public:
         out.stats.assign(n_, SliceStats());
         auto code_picture = [&](int f) {
             while (__atomic_load_n(&h_done_[f], __ATOMIC_ACQUIRE) == 0) std::this_thread::yield();
-            PictureData pic;
-            pic.mbw = g_.mbw; pic.mbh = g_.mbh; pic.idr = f == 0; pic.frame_num = f; pic.idr_pic_id = idr_pic_id_;
-            pic.qp = f == 0 ? cfg_.qp_i : cfg_.qp_p;
+            PictureData pic = picture_header(f);
+            if (cfg_.device_entropy) {      // the GPU wrote slice_data() behind room for the header: fill the header in, wrap the NAL
+                const uint32_t *pos = h_pos_ + 8 * f;
+                if (pos[7]) { failed_ = true; return; }
+                std::vector<uint8_t> rbsp(h_slices_ + pos[0], h_slices_ + pos[0] + pos[1]);
+                const std::vector<uint8_t> hdr = slice_header_bytes(pic);
+                for (size_t i = 0; i < hdr.size() && i < rbsp.size(); ++i) rbsp[i] |= hdr[i];
+                SliceStats st;
+                st.skipped = int(pos[3]); st.p16 = int(pos[4]); st.p8 = int(pos[5]); st.intra = int(pos[6]); st.bits = size_t(pos[1]) * 8;
+                out.stats[f] = st;
+                if (f == 0) {
+                    BitWriter s, p;
+                    write_sps(s, sp);
+                    write_pps(p);
+                    append_nal(au[f], 3, 7, s.bytes(), false);
+                    append_nal(au[f], 3, 8, p.bytes(), false);
+                }
+                append_nal(au[f], f == 0 ? 3 : 2, f == 0 ? 5 : 1, rbsp, false);
+                return;
+            }
             pic.coefs = h_blocks_ + size_t(kMbCoefs) * nmb * f;
             pic.compact = true;
             pic.block_offsets = h_offsets_ + nmb * f;
@@ -273,10 +345,19 @@ public:
             out.au_size.push_back(au[f].size());
             out.payload.insert(out.payload.end(), au[f].begin(), au[f].end());
         }
-        idr_pic_id_ = (idr_pic_id_ + 1) & 0xffff;
+        ++idr_count_;
     }
+    bool failed() const { return failed_; }
 
 private:
+    // the fields of picture f's slice header.  idr_pic_id runs through 255..510: consecutive segments differ and ue(v) always
+    // takes 17 bits, so the header length is a constant of the picture type (the GPU entropy pass is replayed from a graph).
+    PictureData picture_header(int f) const {
+        PictureData pic;
+        pic.mbw = g_.mbw; pic.mbh = g_.mbh; pic.idr = f == 0; pic.frame_num = f; pic.idr_pic_id = 255 + (idr_count_ & 255);
+        pic.qp = f == 0 ? cfg_.qp_i : cfg_.qp_p;
+        return pic;
+    }
     // Y/U/V planes at sample (0,0) of one picture whose valid area is w x h luma samples
     BorderBatchArgs border_args(uint8_t *y, uint8_t *u, uint8_t *v, int w, int h) const {
         const int P = kEncPad, Pc = kEncPad / 2, lw = g_.w16 / 2, lh = g_.h16 / 2;
@@ -310,6 +391,8 @@ private:
         auto relh = [&](auto *&p) { if (p) ops_.release_host(p); p = nullptr; };
         rel(d_counters_); relh(h_offsets_); relh(h_counters_);
         relh(h_blocks_); relh(h_nz_); relh(h_motion_); relh(h_modes_); relh(h_done_);
+        rel(e_blocks_); rel(e_offsets_); rel(e_nz_); rel(e_modes_); rel(e_nnz_); rel(e_mb_buf_); rel(e_mb_bits_); rel(e_mb_kind_);
+        rel(e_slice_); rel(e_info_); rel(e_used_); relh(h_slices_); relh(h_pos_);
         cap_ = 0;
     }
 
@@ -317,7 +400,8 @@ private:
     SegmentConfig cfg_;
     EncGeom       g_;
     PlaneSizes    ps_;
-    int           cap_ = 0, n_ = 0, idr_pic_id_ = 0;
+    int           cap_ = 0, n_ = 0, idr_count_ = 0;
+    bool          failed_ = false;
     CurFrames     cur_{nullptr, nullptr, nullptr};
     uint8_t      *cur_low_ = nullptr;
     uint8_t      *rec_y_[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
@@ -334,6 +418,15 @@ private:
     MbMotion     *h_motion_ = nullptr;
     uint8_t      *h_modes_ = nullptr;
     int          *h_done_ = nullptr;      // per picture: set to 1 by the kernel that closes the picture
+    // device_entropy: one picture's records and the entropy pass's scratch on the device, finished slices on the host
+    int16_t      *e_blocks_ = nullptr;
+    uint32_t     *e_offsets_ = nullptr, *e_nz_ = nullptr, *e_mb_buf_ = nullptr, *e_mb_bits_ = nullptr, *e_slice_ = nullptr, *e_info_ = nullptr;
+    uint8_t      *e_modes_ = nullptr, *e_nnz_ = nullptr, *e_mb_kind_ = nullptr;
+    unsigned     *e_used_ = nullptr;
+    int           slice_words_ = 0;
+    size_t        slices_cap_ = 0;
+    uint8_t      *h_slices_ = nullptr;    // the segment's slices, back to back (each padded to 16 bytes)
+    uint32_t     *h_pos_ = nullptr;       // per picture: base, bytes, bits, skipped, p16, p8, intra, error
     std::vector<uint8_t> recon_store_;
 };
 

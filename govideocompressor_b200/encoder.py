@@ -15,7 +15,7 @@ from . import lib as _lib
 class EncoderConfig(ctypes.Structure):
     """struct gvc_encoder_config"""
     _fields_ = [(n, ctypes.c_int) for n in ("src_w", "src_h", "dst_w", "dst_h", "fps_num", "fps_den", "crf", "merange",
-                                            "scale_algo", "keep_recon", "host_threads", "disable_graph")]
+                                            "scale_algo", "keep_recon", "host_threads", "disable_graph", "entropy")]
 
 
 def _bind(lib):
@@ -46,10 +46,10 @@ def _bind(lib):
 
 class Encoder:
     def __init__(self, src_w, src_h, dst_w=0, dst_h=0, fps=(30, 1), crf=23, merange=16, scale_algo=4, keep_recon=False, host_threads=0,
-                 disable_graph=False):
+                 disable_graph=False, entropy=0):
         self._lib = _lib.load_library()
         _bind(self._lib)
-        self.cfg = EncoderConfig(src_w, src_h, dst_w, dst_h, fps[0], fps[1], crf, merange, scale_algo, int(keep_recon), host_threads, int(disable_graph))
+        self.cfg = EncoderConfig(src_w, src_h, dst_w, dst_h, fps[0], fps[1], crf, merange, scale_algo, int(keep_recon), host_threads, int(disable_graph), int(entropy))
         self.src_w, self.src_h = src_w, src_h
         self.dst_w, self.dst_h = dst_w or src_w, dst_h or src_h
         self.w16, self.h16 = (self.dst_w + 15) // 16 * 16, (self.dst_h + 15) // 16 * 16
@@ -128,13 +128,13 @@ class Encoder:
         _lib.check(self._lib.gvc_encoder_stats(self._h, ctypes.c_void_p(st.ctypes.data), self.n_last), "gvc_encoder_stats")
         return st
 
-    STAGES = ("resize", "border", "lowres", "hpel", "me_lowres", "me_refine", "encode_inter", "encode_intra")
+    STAGES = ("resize", "border", "lowres", "hpel", "me_lowres", "me_refine", "encode_inter", "encode_intra", "entropy")
 
     def set_timing(self, on=True):
         _lib.check(self._lib.gvc_encoder_set_timing(self._h, int(on)), "gvc_encoder_set_timing")
 
     def stage_times(self):
-        ms, n = (ctypes.c_double * 8)(), (ctypes.c_int * 8)()
+        ms, n = (ctypes.c_double * 9)(), (ctypes.c_int * 9)()
         _lib.check(self._lib.gvc_encoder_stage_times(self._h, ms, n), "gvc_encoder_stage_times")
         return {s: (ms[i], n[i]) for i, s in enumerate(self.STAGES)}
 

@@ -187,7 +187,11 @@ typedef struct gvc_encoder_config {
     int keep_recon;            /* keep the reconstruction of every picture (tests compare it with a decoder) */
     int host_threads;          /* entropy-coding threads, 0 = all host cores */
     int disable_graph;         /* 1 = launch every kernel individually instead of replaying a captured CUDA graph */
+    int entropy;               /* GVC_ENTROPY_*: where the CAVLC slice data is written; the streams are bit-identical */
 } gvc_encoder_config;
+#define GVC_ENTROPY_DEFAULT 0  /* = GVC_ENTROPY_DEVICE */
+#define GVC_ENTROPY_HOST    1  /* host threads code the kernels' per-macroblock records (h264_stream.cpp) */
+#define GVC_ENTROPY_DEVICE  2  /* entropy kernels: the finished slices cross PCIe, not the records */
 
 int  gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg);
 void gvc_encoder_destroy(gvc_encoder *enc);
@@ -212,9 +216,10 @@ int gvc_encoder_recon(gvc_encoder *enc, uint8_t *dst, size_t cap);
 /* per picture: skipped MBs, P16x16 MBs, P8x8 MBs, bytes */
 int gvc_encoder_stats(gvc_encoder *enc, int *stats4_per_picture, int n_pictures);
 /* Per-stage device times (CUDA events on the encoder's stream) for measurement: stages in order resize, border,
- * lowres, hpel, me_lowres, me_refine, encode_inter, encode_intra.  set_timing(on) also clears the totals;
+ * lowres, hpel, me_lowres, me_refine, encode_inter, encode_intra, entropy (the four entropy kernels of a picture timed as
+ * one entry).  set_timing(on) also clears the totals;
  * stage_times synchronises the stream and returns accumulated milliseconds and launch counts (GVC_STAGES entries each). */
-#define GVC_STAGES 8
+#define GVC_STAGES 9
 int gvc_encoder_set_timing(gvc_encoder *enc, int on);
 int gvc_encoder_stage_times(gvc_encoder *enc, double *ms, int *launches);
 /* Bytes the last finished segment sent device -> host (packed nonzero blocks + per-macroblock tables). */

@@ -139,7 +139,7 @@ void emu_encode_inter(const uint8_t *const cur[3], const uint8_t *const ref[7], 
     a.rec_y = rec[0]; a.rec_u = rec[1]; a.rec_v = rec[2]; a.sy = sy; a.sc = sc; a.mbw = w16 / 16; a.mbh = h16 / 16;
     fill_quant_params(a.q, qp, false);
     a.motion = static_cast<const MbMotion *>(motion); a.coefs = coefs; a.nzmask = nzmask;
-    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
+    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr; a.nnz_y = a.nnz_u = a.nnz_v = nullptr;
     emu_run_encode_inter(a);
 }
 
@@ -152,7 +152,7 @@ void emu_encode_intra(const uint8_t *const cur[3], uint8_t *const rec[3], int sy
     a.coefs = coefs; a.nzmask = nzmask; a.modes = modes;
     std::vector<unsigned long long> mail(size_t(8) * a.mbw * a.mbh, 0);
     a.mail = mail.data();
-    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr;
+    a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr; a.nnz_y = a.nnz_u = a.nnz_v = nullptr;
     emu_run_encode_intra(a);
 }
 

@@ -2,6 +2,7 @@
 // emulation of the kernel bodies, so the CPU suite can check the orchestration, the bitstream writer and the MP4
 // muxer against a real H.264 decoder without a GPU.  Not part of libgvc.so.
 #define GVC_EMU 1
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -62,6 +63,42 @@ struct EmuOps {
     int encode_inter(const EncMbArgs &a) { emu_run_encode_inter(a); return 0; }
     int encode_intra(const IntraArgs &a) { emu_run_encode_intra(a); return 0; }
     int signal_picture(int *done, unsigned *count_out, const unsigned *count_in) { *count_out = *count_in; *done = 1; return 0; }
+    int entropy_picture(const EntropyPicture &p) {      // the entropy kernels' per-thread bodies, serially; the scan as a plain loop
+        const int nmb = p.ent.mbw * p.ent.mbh;
+        for (int mb = 0; mb < nmb; ++mb) ent_mb(p.ent, mb);
+        const SliceArgs &a = p.slice;
+        int prev = -1;
+        unsigned long long bits = 0;
+        unsigned counts[4] = {0, 0, 0, 0};
+        bool ovf = false;
+        for (int i = 0; i < nmb; ++i) {
+            const int k = a.mb_kind[i];
+            ++counts[k & 3];
+            ovf = ovf || (k & 128);
+            if (!(k & 127)) continue;
+            const unsigned run = unsigned(i - 1 - prev);
+            a.mb_run[i] = run;
+            a.mb_off[i] = uint32_t(a.header_bits + bits);
+            bits += (a.p_slice ? ue_len(run) : 0) + a.mb_bits[i];
+            prev = i;
+        }
+        const long long need = std::min<long long>(a.slice_words, ((long long)a.header_bits + (long long)bits + 64 + 1 + 31) / 32 + 4);
+        memset(a.slice, 0, size_t(need) * 4);
+        ent_finish_slice(a, bits, unsigned(nmb - 1 - prev), counts, ovf);
+        for (int mb = 0; mb < nmb; ++mb) ent_place(a, mb);
+        const unsigned bytes = a.info[1], base = p.used[0], padded = (bytes + 15u) & ~15u;
+        const bool fits = a.info[6] == 0 && base + padded <= p.host_cap;
+        if (fits)
+            for (unsigned j = 0; j < padded / 4; ++j) {
+                const uint32_t w = a.slice[j];
+                uint8_t *d = p.host_buf + base + 4 * size_t(j);
+                d[0] = uint8_t(w >> 24); d[1] = uint8_t(w >> 16); d[2] = uint8_t(w >> 8); d[3] = uint8_t(w);
+            }
+        p.used[1] = fits ? base + padded : base;
+        p.pos[0] = base; p.pos[1] = bytes; p.pos[2] = a.info[0]; p.pos[3] = a.info[2]; p.pos[4] = a.info[3]; p.pos[5] = a.info[4];
+        p.pos[6] = a.info[5]; p.pos[7] = fits ? 0u : 1u;
+        return 0;
+    }
     int copy_plane(uint8_t *dst, int dpitch, const uint8_t *src, int spitch, int w, int h) {
         for (int y = 0; y < h; ++y) memcpy(dst + size_t(y) * dpitch, src + size_t(y) * spitch, w);
         return 0;
@@ -76,11 +113,12 @@ extern "C" {
 // annexb (caller buffer of annexb_cap bytes; *annexb_len receives the size), the encoder's reconstruction to recon
 // (n * w16*h16*3/2 bytes, or NULL) and per-picture stats (4 ints each: skipped, p16, p8, bytes).  Returns 0 or <0.
 int emu_encode_segment(const uint8_t *frames, int n, int w, int h, int fps, int qp_i, int qp_p, int merange, const char *mp4_path,
-                       uint8_t *annexb, size_t annexb_cap, size_t *annexb_len, uint8_t *recon, int *stats) {
+                       uint8_t *annexb, size_t annexb_cap, size_t *annexb_len, uint8_t *recon, int *stats, int device_entropy) {
     EmuOps        ops;
     SegmentConfig cfg;
     cfg.w = w; cfg.h = h; cfg.fps_num = fps; cfg.fps_den = 1; cfg.qp_i = qp_i; cfg.qp_p = qp_p; cfg.merange = merange;
     cfg.keep_recon = recon != nullptr;
+    cfg.device_entropy = device_entropy != 0;
     SegmentEncoder<EmuOps> enc(ops, cfg);
     if (enc.reserve(n)) return -4;
     const EncGeom   &g  = enc.geom();

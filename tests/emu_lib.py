@@ -61,7 +61,7 @@ def plan_info(sw, sh, dw, dh, algo):
                 h_taps=out[6], v_taps=out[7])
 
 
-def encode_segment(frames, w, h, fps=30, qp_i=20, qp_p=23, merange=16, mp4_path=None):
+def encode_segment(frames, w, h, fps=30, qp_i=20, qp_p=23, merange=16, mp4_path=None, device_entropy=False):
     """frames: (n, w*h*3/2) uint8 I420.  Runs the product's SegmentEncoder over the emulated kernels.
     Returns dict(annexb=bytes, recon=(n, w16*h16*3/2) uint8, stats=(n,4) int32 [skipped, p16, p8, au_bytes])."""
     lib = load()
@@ -73,9 +73,9 @@ def encode_segment(frames, w, h, fps=30, qp_i=20, qp_p=23, merange=16, mp4_path=
     recon = np.zeros((n, w16 * h16 * 3 // 2), np.uint8)
     stats = np.zeros((n, 4), np.int32)
     lib.emu_encode_segment.argtypes = [ctypes.c_void_p] + [ctypes.c_int] * 7 + [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_size_t,
-                                                                                 ctypes.POINTER(ctypes.c_size_t), ctypes.c_void_p, ctypes.c_void_p]
+                                                                                 ctypes.POINTER(ctypes.c_size_t), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     rc = lib.emu_encode_segment(frames.ctypes.data, n, w, h, fps, qp_i, qp_p, merange, mp4_path.encode() if mp4_path else None,
-                                annexb.ctypes.data, annexb.size, ctypes.byref(alen), recon.ctypes.data, stats.ctypes.data)
+                                annexb.ctypes.data, annexb.size, ctypes.byref(alen), recon.ctypes.data, stats.ctypes.data, int(device_entropy))
     assert rc == 0, f"emu_encode_segment failed: {rc}"
     return dict(annexb=annexb[: alen.value].tobytes(), recon=recon, stats=stats, w16=w16, h16=h16)
 

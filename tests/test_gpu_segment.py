@@ -34,10 +34,11 @@ def check_decode(gvc_enc, annexb, recon, w, h, n):
 
 @pytest.mark.parametrize("w,h,n,crf,kw", [(96, 64, 5, 23, {}), (150, 100, 6, 26, dict(static_left=True, noise=1)),
                                            (128, 96, 5, 28, dict(fast=True, noise=2)), (64, 48, 3, 4, dict(noise=40))])
-def test_stream_identical_to_cpu_emulation_and_decodable(gvc, w, h, n, crf, kw):
+@pytest.mark.parametrize("entropy", [1, 2], ids=["host-cavlc", "gpu-cavlc"])
+def test_stream_identical_to_cpu_emulation_and_decodable(gvc, w, h, n, crf, kw, entropy):
     frames = S.moving_sequence(w, h, n, seed=w + n, **kw)
     merange = 32 if kw.get("fast") else 16
-    enc = gvc.Encoder(w, h, crf=crf, merange=merange, keep_recon=True, host_threads=3)
+    enc = gvc.Encoder(w, h, crf=crf, merange=merange, keep_recon=True, host_threads=3, entropy=entropy)
     stream = enc.encode_host(frames, annexb=True)
     ref = emu_lib.encode_segment(frames, w, h, qp_i=max(crf - 3, 0), qp_p=crf, merange=merange)
     assert stream == ref["annexb"], "GPU stream differs from the CPU emulation of the same kernels"
@@ -70,6 +71,21 @@ def test_baseline_size_with_resize_decodes_to_the_reconstruction(gvc):
             np.testing.assert_array_equal(a, b)
     assert stream2 != stream[: len(stream2)]                 # idr_pic_id differs: consecutive IDRs must not share it
     enc.close()
+
+
+def test_gpu_and_host_entropy_agree_at_baseline_size_with_graph_replay(gvc):
+    """cfg2 shape, CUDA-graph path (no keep_recon), two segments in a row on each encoder: the entropy kernels and the
+    host writer must give the same bytes, and the second segment (graph replay, next idr_pic_id) must still decode."""
+    sw, sh, w, h, n = 1920, 1080, 1280, 720, 6
+    frames = S.moving_sequence(sw, sh, n, seed=5, noise=2)
+    out = {}
+    for entropy in (1, 2):
+        enc = gvc.Encoder(sw, sh, w, h, crf=23, entropy=entropy)
+        out[entropy] = [enc.encode_host(frames, annexb=True), enc.encode_host(frames[::-1].copy(), annexb=True)]
+        np.testing.assert_array_equal(enc.stats().shape, (n, 4))
+        enc.close()
+    assert out[1][0] == out[2][0] and out[1][1] == out[2][1]
+    assert len(h264_decode.decode(out[2][1])) == n
 
 
 def test_1080p_coded_height_1088_and_4k(gvc):
