@@ -8,7 +8,7 @@
 //
 // A macroblock's bits depend on its neighbours only through data that is final before entropy coding starts (their
 // motion vectors and per-block coefficient counts), never on bit positions, so:
-//   ent_mb     one thread per macroblock: its bits (without mb_skip_run) into a private buffer, its length and kind;
+//   ent_mb     one warp per macroblock, one lane per residual block: its bits (without mb_skip_run), its length and kind;
 //   ent_scan   one CTA: skip runs and bit offsets of all macroblocks by two block-wide scans, slice header, trailing bits;
 //   ent_place  one thread per coded macroblock: ue(mb_skip_run) + its bits OR-ed into the slice at its offset;
 //   ent_copy   slice bytes to mapped host memory (byte order fixed on the way), appended to the segment's buffer.
@@ -31,8 +31,8 @@ namespace etab {
 }  // namespace etab
 
 // Upper bound of one macroblock's bits: 27 residual blocks x (coeff_token 16 + 16 levels x 36 + total_zeros 9 + runs 45)
-// + header < 18,000 bits.  The writer still checks and flags an overflow instead of writing past the end.
-constexpr int kMbBufWords = 576;
+// + header < 18,944 bits.  The writers still check and flag an overflow instead of writing past the end.
+constexpr int kMbBufWords = 592;
 
 struct EntropyArgs {
     int mbw, mbh, idr;
@@ -178,38 +178,6 @@ GVC_HD int ent_cbp(uint32_t nz, bool i16) {
     const int chroma = (nz & 0x00ff0000u) ? 2 : (nz & 0x03000000u) ? 1 : 0;
     return luma | (chroma << 4);
 }
-// residual( ) of one macroblock
-GVC_HD void ent_mb_residual(BitOut &bw, const EntropyArgs &a, const int16_t *mbco, int mx, int my, int cbp, bool i16, uint32_t nz) {
-    const unsigned cm = compact_mask(nz);
-    const int w4 = 4 * a.mbw, w2 = 2 * a.mbw;
-    if (i16) {
-        const int nC = ent_nc(a.nnz_y, w4, 4 * mx, 4 * my);
-        if (nz & (1u << 26)) ent_residual(bw, mbco + 16 * popcount32(cm & ((1u << 25) - 1u)), 16, nC);
-        else ent_empty_block(bw, nC);
-    }
-    for (int blk = 0; blk < 16; ++blk) {
-        if (!(cbp & (1 << (blk >> 2)))) continue;
-        const int r = ((blk & 8) | ((blk & 4) >> 1) | ((blk & 2) << 1) | (blk & 1));      // blkIdx (8x8-wise Z scan) -> raster 4x4 block
-        const int bx = 4 * mx + (r & 3), by = 4 * my + (r >> 2), nC = ent_nc(a.nnz_y, w4, bx, by);
-        if (!(nz & (1u << r))) { ent_empty_block(bw, nC); continue; }
-        const int16_t *l = mbco + 16 * popcount32(cm & ((1u << r) - 1u));
-        if (i16) ent_residual(bw, l + 1, 15, nC);
-        else     ent_residual(bw, l, 16, nC);
-    }
-    if (cbp & 0x30)
-        for (int p = 0; p < 2; ++p) {
-            if (nz & (1u << (24 + p))) ent_residual(bw, mbco + 16 * popcount32(cm & ((1u << 24) - 1u)) + 4 * p, 4, -1);
-            else ent_empty_block(bw, -1);
-        }
-    if (cbp & 0x20)
-        for (int p = 0; p < 2; ++p)
-            for (int b = 0; b < 4; ++b) {
-                const int bx = 2 * mx + (b & 1), by = 2 * my + (b >> 1), nC = ent_nc(a.nnz_c[p], w2, bx, by), r = 16 + 4 * p + b;
-                if (nz & (1u << r)) ent_residual(bw, mbco + 16 * popcount32(cm & ((1u << r) - 1u)) + 1, 15, nC);
-                else ent_empty_block(bw, nC);
-            }
-}
-
 // ---- motion vector prediction (8.4.1.3), single reference ---------------------------------------------
 struct EntMv { int x, y; };
 // vector of the 4x4 block (x, y) if it precedes partition cur_k of macroblock cur_mb in decoding order
@@ -239,58 +207,98 @@ GVC_HD EntMv ent_predict_mv(const EntropyArgs &a, int cur_mb, int cur_k, int bx,
 }
 
 // ---- one macroblock: macroblock_layer() without the preceding mb_skip_run ------------------------------
-GVC_HD void ent_mb(const EntropyArgs &a, int mb) {
+// One warp per macroblock, one lane per syntax element group: lanes 0..15 the luma blocks (lane = blkIdx, coding order),
+// 16..23 the chroma AC blocks (Cb 0..3, Cr 0..3), 24 / 25 the chroma DC blocks, 26 the Intra16x16 luma DC block, 27 the
+// header (mb_type, sub types, mvds, coded_block_pattern, mb_qp_delta).  Each lane writes its bits into its own small
+// buffer; the warp then lays them end to end in coding order (header, luma DC, luma, chroma DC, chroma AC).
+constexpr int kEntLanes = 28, kEntLaneWords = 21;      // a residual block is at most 16 + 16*36 + 9 + 45 = 646 bits
+struct EntSmem {                                       // per warp
+    uint32_t lane_buf[kEntLanes][kEntLaneWords];
+    uint32_t mb[kMbBufWords];
+    int      kind, overflow;
+};
+GVC_HD int ent_lane_order(int lane) { return lane == 27 ? 0 : lane == 26 ? 1 : lane < 16 ? 2 + lane : lane < 24 ? 4 + lane : lane - 6; }
+GVC_HD int ent_lane_at(int pos) { return pos == 0 ? 27 : pos == 1 ? 26 : pos < 18 ? pos - 2 : pos < 20 ? pos + 6 : pos < 28 ? pos - 4 : pos; }
+
+// the lane's bits into sm.lane_buf[lane]; returns their number.  Lane 27 also decides P_Skip and sets sm.kind.
+GVC_HD int ent_lane_encode(int lane, const EntropyArgs &a, int mb, EntSmem &sm) {
+    if (lane >= kEntLanes) return 0;
     const int      my = mb / a.mbw, mx = mb - my * a.mbw;
     const uint32_t nz = a.nzmask[mb];
     const int16_t *co = a.blocks + (size_t)16 * a.offsets[mb];
+    const bool     i16 = a.idr != 0;
+    const int      cbp = ent_cbp(nz, i16);
+    const unsigned cm = compact_mask(nz);
     BitOut bw;
-    bo_init(bw, a.mb_buf + (size_t)mb * kMbBufWords, kMbBufWords);
-    int kind;
-    if (a.idr) {
-        const int cbp = ent_cbp(nz, true);
-        bo_ue(bw, (unsigned)(1 + a.modes[mb] + 4 * (cbp >> 4) + ((cbp & 15) ? 12 : 0)));   // mb_type I_16x16_<mode>_<cbpc>_<cbpl>
-        bo_ue(bw, 0);                      // intra_chroma_pred_mode: DC
-        bo_se(bw, 0);                      // mb_qp_delta
-        ent_mb_residual(bw, a, co, mx, my, cbp, true, nz);
-        kind = 3;
-    } else {
-        const MbMotion &mo  = a.motion[mb];
-        const int       cbp = ent_cbp(nz, false);
-        if (mo.mode == 0) {
-            bool  A, B;
-            EntMv va, vb;
-            const EntMv mvp = ent_predict_mv(a, mb, 0, 4 * mx, 4 * my, 4, A, B, va, vb);
-            EntMv skip = mvp;
-            if (!A || !B || (va.x == 0 && va.y == 0) || (vb.x == 0 && vb.y == 0)) skip.x = skip.y = 0;
-            if (cbp == 0 && mo.mv[0][0] == skip.x && mo.mv[0][1] == skip.y) {      // P_Skip: no bits of its own
-                a.mb_bits[mb] = 0;
-                a.mb_kind[mb] = 0;
-                return;
-            }
-            bo_ue(bw, 0);                  // mb_type P_L0_16x16
-            bo_se(bw, mo.mv[0][0] - mvp.x);
-            bo_se(bw, mo.mv[0][1] - mvp.y);
-            kind = 1;
+    bo_init(bw, sm.lane_buf[lane], kEntLaneWords);
+    if (lane == 27) {
+        if (i16) {
+            bo_ue(bw, (unsigned)(1 + a.modes[mb] + 4 * (cbp >> 4) + ((cbp & 15) ? 12 : 0)));   // mb_type I_16x16_<mode>_<cbpc>_<cbpl>
+            bo_ue(bw, 0);                  // intra_chroma_pred_mode: DC
+            bo_se(bw, 0);                  // mb_qp_delta
+            sm.kind = 3;
         } else {
-            bo_ue(bw, 3);                  // mb_type P_8x8
-            for (int k = 0; k < 4; ++k) bo_ue(bw, 0);   // sub_mb_type P_L0_8x8
-            for (int k = 0; k < 4; ++k) {
+            const MbMotion &mo = a.motion[mb];
+            if (mo.mode == 0) {
                 bool  A, B;
                 EntMv va, vb;
-                const EntMv mvp = ent_predict_mv(a, mb, k, 4 * mx + 2 * (k & 1), 4 * my + 2 * (k >> 1), 2, A, B, va, vb);
-                bo_se(bw, mo.mv[k][0] - mvp.x);
-                bo_se(bw, mo.mv[k][1] - mvp.y);
+                const EntMv mvp = ent_predict_mv(a, mb, 0, 4 * mx, 4 * my, 4, A, B, va, vb);
+                EntMv skip = mvp;
+                if (!A || !B || (va.x == 0 && va.y == 0) || (vb.x == 0 && vb.y == 0)) skip.x = skip.y = 0;
+                if (cbp == 0 && mo.mv[0][0] == skip.x && mo.mv[0][1] == skip.y) { sm.kind = 0; return 0; }   // P_Skip: no bits of its own
+                bo_ue(bw, 0);              // mb_type P_L0_16x16
+                bo_se(bw, mo.mv[0][0] - mvp.x);
+                bo_se(bw, mo.mv[0][1] - mvp.y);
+                sm.kind = 1;
+            } else {
+                bo_ue(bw, 3);              // mb_type P_8x8
+                for (int k = 0; k < 4; ++k) bo_ue(bw, 0);   // sub_mb_type P_L0_8x8
+                for (int k = 0; k < 4; ++k) {
+                    bool  A, B;
+                    EntMv va, vb;
+                    const EntMv mvp = ent_predict_mv(a, mb, k, 4 * mx + 2 * (k & 1), 4 * my + 2 * (k >> 1), 2, A, B, va, vb);
+                    bo_se(bw, mo.mv[k][0] - mvp.x);
+                    bo_se(bw, mo.mv[k][1] - mvp.y);
+                }
+                sm.kind = 2;
             }
-            kind = 2;
+            bo_ue(bw, etab::kCbpInterCode[cbp]);   // coded_block_pattern me(v)
+            if (cbp) bo_se(bw, 0);                 // mb_qp_delta
         }
-        bo_ue(bw, etab::kCbpInterCode[cbp]);   // coded_block_pattern me(v)
-        if (cbp) {
-            bo_se(bw, 0);                  // mb_qp_delta
-            ent_mb_residual(bw, a, co, mx, my, cbp, false, nz);
+    } else if (lane == 26) {
+        if (i16) {
+            const int nC = ent_nc(a.nnz_y, 4 * a.mbw, 4 * mx, 4 * my);
+            if (nz & (1u << 26)) ent_residual(bw, co + 16 * popcount32(cm & ((1u << 25) - 1u)), 16, nC);
+            else ent_empty_block(bw, nC);
+        }
+    } else if (lane < 16) {
+        if (cbp & (1 << (lane >> 2))) {
+            const int r = ((lane & 8) | ((lane & 4) >> 1) | ((lane & 2) << 1) | (lane & 1));    // blkIdx (8x8-wise Z scan) -> raster 4x4 block
+            const int bx = 4 * mx + (r & 3), by = 4 * my + (r >> 2), nC = ent_nc(a.nnz_y, 4 * a.mbw, bx, by);
+            if (!(nz & (1u << r))) ent_empty_block(bw, nC);
+            else {
+                const int16_t *l = co + 16 * popcount32(cm & ((1u << r) - 1u));
+                if (i16) ent_residual(bw, l + 1, 15, nC);
+                else     ent_residual(bw, l, 16, nC);
+            }
+        }
+    } else if (lane < 24) {
+        if (cbp & 0x20) {
+            const int p = (lane - 16) >> 2, b = (lane - 16) & 3;
+            const int bx = 2 * mx + (b & 1), by = 2 * my + (b >> 1), nC = ent_nc(a.nnz_c[p], 2 * a.mbw, bx, by);
+            if (nz & (1u << lane)) ent_residual(bw, co + 16 * popcount32(cm & ((1u << lane) - 1u)) + 1, 15, nC);
+            else ent_empty_block(bw, nC);
+        }
+    } else {
+        if (cbp & 0x30) {
+            const int p = lane - 24;
+            if (nz & (1u << (24 + p))) ent_residual(bw, co + 16 * popcount32(cm & ((1u << 24) - 1u)) + 4 * p, 4, -1);
+            else ent_empty_block(bw, -1);
         }
     }
-    a.mb_bits[mb] = (uint32_t)bo_finish(bw);
-    a.mb_kind[mb] = (uint8_t)(kind | (bw.overflow ? 128 : 0));
+    const int bits = bo_finish(bw);
+    if (bw.overflow) sm.overflow = 1;
+    return bits;
 }
 
 // ---- slice assembly -------------------------------------------------------------------------------------

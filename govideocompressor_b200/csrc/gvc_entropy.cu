@@ -8,9 +8,36 @@
 namespace gvc {
 namespace {
 
-__global__ void __launch_bounds__(128) ent_mb_kernel(const __grid_constant__ EntropyArgs a) {
-    const int mb = blockIdx.x * 128 + threadIdx.x;
-    if (mb < a.mbw * a.mbh) ent_mb(a, mb);
+constexpr int kEntWarps = 4;
+__global__ void __launch_bounds__(32 * kEntWarps) ent_mb_kernel(const __grid_constant__ EntropyArgs a) {
+    __shared__ EntSmem sms[kEntWarps];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int mb = blockIdx.x * kEntWarps + warp;
+    if (mb >= a.mbw * a.mbh) return;
+    EntSmem &sm = sms[warp];
+    if (lane == 0) { sm.kind = 0; sm.overflow = 0; }
+    __syncwarp();
+    const int bits = ent_lane_encode(lane, a, mb, sm);
+    // bit offsets in coding order: thread p takes the length of the lane that sits at position p, scans, hands it back
+    int v = __shfl_sync(0xffffffffu, bits, ent_lane_at(lane));
+    const int mine = v;
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += o;
+    }
+    const int total = __shfl_sync(0xffffffffu, v, 31);
+    const int off = __shfl_sync(0xffffffffu, v - mine, lane < kEntLanes ? ent_lane_order(lane) : lane);
+    const int words = (total + 31) >> 5;
+    for (int j = lane; j < words; j += 32) sm.mb[j] = 0;
+    __syncwarp();
+    if (lane < kEntLanes && bits) ent_or_bits(sm.mb, kMbBufWords, (unsigned long long)off, sm.lane_buf[lane], bits);
+    __syncwarp();
+    uint32_t *dst = a.mb_buf + (size_t)mb * kMbBufWords;
+    for (int j = lane; j < words; j += 32) dst[j] = sm.mb[j];
+    if (lane == 0) {
+        a.mb_bits[mb] = (uint32_t)total;
+        a.mb_kind[mb] = (uint8_t)(sm.kind | (sm.overflow ? 128 : 0));
+    }
 }
 
 constexpr int kScanThreads = 1024;
@@ -130,7 +157,7 @@ __global__ void __launch_bounds__(256) ent_copy_kernel(const uint32_t *slice, co
 
 int launch_entropy_picture(const EntropyPicture &p, cudaStream_t st) {
     const int nmb = p.ent.mbw * p.ent.mbh;
-    ent_mb_kernel<<<(nmb + 127) / 128, 128, 0, st>>>(p.ent);
+    ent_mb_kernel<<<(nmb + kEntWarps - 1) / kEntWarps, 32 * kEntWarps, 0, st>>>(p.ent);
     GVC_CUDA(cudaGetLastError());
     ent_scan_kernel<<<1, kScanThreads, 0, st>>>(p.slice);
     GVC_CUDA(cudaGetLastError());

@@ -61,9 +61,34 @@ struct StageTimer {
 };
 
 struct CudaOps {
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr;       // the pictures' dependent kernel chain
+    cudaStream_t side = nullptr;     // per-picture work nothing on the chain waits for (entropy pass, arrival flag)
+    cudaEvent_t  ev_fork = nullptr, ev_side[2] = {nullptr, nullptr};
+    bool         on_side = false;
     StageTimer   tm;
-    template <class F> int timed(int stage, F f) { tm.begin(stage, st); const int rc = f(); tm.end(st); return rc; }
+    cudaStream_t cur() const { return on_side ? side : st; }
+    // side_begin: what follows runs on the side stream, after everything issued on the chain so far.  side_end(slot):
+    // back to the chain; wait_side(slot) makes the chain wait for the side work closed with that slot.  While per-stage
+    // timing is on everything stays on the chain (its events bracket single launches).
+    int side_begin() {
+        if (tm.on) return 0;
+        GVC_CUDA(cudaEventRecord(ev_fork, st));
+        GVC_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+        on_side = true;
+        return 0;
+    }
+    int side_end(int slot) {
+        if (!on_side) return 0;
+        GVC_CUDA(cudaEventRecord(ev_side[slot], side));
+        on_side = false;
+        return 0;
+    }
+    int wait_side(int slot) {
+        if (tm.on) return 0;
+        GVC_CUDA(cudaStreamWaitEvent(st, ev_side[slot], 0));
+        return 0;
+    }
+    template <class F> int timed(int stage, F f) { tm.begin(stage, cur()); const int rc = f(); tm.end(cur()); return rc; }
     void *alloc(size_t n) { void *p = nullptr; return cudaMalloc(&p, n + 64) == cudaSuccess ? p : nullptr; }
     void  release(void *p) { cudaFree(p); }
     void *alloc_host(size_t n) { void *p = nullptr; return cudaHostAlloc(&p, n + 64, cudaHostAllocMapped) == cudaSuccess ? p : nullptr; }
@@ -77,8 +102,8 @@ struct CudaOps {
     int me_refine(const MeRefArgs &a) { return timed(kStMeRefine, [&] { return launch_me_refine(a, st); }); }
     int encode_inter(const EncMbArgs &a) { return timed(kStEncInter, [&] { return launch_encode_inter(a, st); }); }
     int encode_intra(const IntraArgs &a) { return timed(kStEncIntra, [&] { return launch_encode_intra(a, st); }); }
-    int signal_picture(int *done, unsigned *count_out, const unsigned *count_in) { return launch_signal_picture(done, count_out, count_in, st); }
-    int entropy_picture(const EntropyPicture &p) { return timed(kStEntropy, [&] { return launch_entropy_picture(p, st); }); }
+    int signal_picture(int *done, unsigned *count_out, const unsigned *count_in) { return launch_signal_picture(done, count_out, count_in, cur()); }
+    int entropy_picture(const EntropyPicture &p) { return timed(kStEntropy, [&] { return launch_entropy_picture(p, cur()); }); }
     int copy_plane(uint8_t *dst, int dpitch, const uint8_t *src, int spitch, int w, int h) {
         GVC_CUDA(cudaMemcpy2DAsync(dst, dpitch, src, spitch, w, h, cudaMemcpyDeviceToHost, st));
         return 0;
@@ -206,7 +231,13 @@ int gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg) {
     gvc_encoder *e = new (std::nothrow) gvc_encoder;
     if (!e) return GVC_ERR_NOMEM;
     e->cfg = c;
-    if (cudaStreamCreateWithFlags(&e->ops.st, cudaStreamNonBlocking) != cudaSuccess) { delete e; set_error("cudaStreamCreate failed"); return GVC_ERR_CUDA; }
+    if (cudaStreamCreateWithFlags(&e->ops.st, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&e->ops.side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ops.ev_fork, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&e->ops.ev_side[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ops.ev_side[1], cudaEventDisableTiming) != cudaSuccess) {
+        gvc_encoder_destroy(e);
+        set_error("cudaStreamCreate / cudaEventCreate failed");
+        return GVC_ERR_CUDA;
+    }
     if ((rc = gvc_resize_plan_create(&e->plan, c.src_w, c.src_h, c.dst_w, c.dst_h, GVC_PIX_YUV420P, c.scale_algo))) { gvc_encoder_destroy(e); return rc; }
     SegmentConfig sc;
     sc.w = c.dst_w; sc.h = c.dst_h; sc.fps_num = c.fps_num; sc.fps_den = c.fps_den;
@@ -230,7 +261,10 @@ void gvc_encoder_destroy(gvc_encoder *e) {
     if (e->plan) gvc_resize_plan_destroy(e->plan);
     for (int b = 0; b < 2; ++b) { if (e->d_src[b]) cudaFree(e->d_src[b]); if (e->uploaded[b]) cudaEventDestroy(e->uploaded[b]); }
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+    if (e->ops.side) cudaStreamDestroy(e->ops.side);
     if (e->ops.st) cudaStreamDestroy(e->ops.st);
+    if (e->ops.ev_fork) cudaEventDestroy(e->ops.ev_fork);
+    for (int b = 0; b < 2; ++b) if (e->ops.ev_side[b]) cudaEventDestroy(e->ops.ev_side[b]);
     delete e;
 }
 

@@ -65,6 +65,7 @@ struct SegmentOutput {
 //   int encode_inter(const EncMbArgs &a);  int encode_intra(const IntraArgs &a);
 //   int signal_picture(int *done, unsigned *count_out, const unsigned *count_in);   // *count_out = *count_in; fence; *done = 1
 //   int entropy_picture(const EntropyPicture &p);                                    // device_entropy: the picture's slice -> host buffer
+//   int side_begin();  int side_end(int slot);  int wait_side(int slot);            // fork / join of work the picture chain does not wait for
 //   int copy_plane(uint8_t *host_or_dev_dst, int dpitch, const uint8_t *dev_src, int spitch, int w, int h);   // device -> recon store
 //   int sync();
 template <class Ops>
@@ -108,11 +109,12 @@ public:
             h_modes_  = static_cast<uint8_t *>(ops_.alloc_host(nmb));
             ok = ok && h_blocks_ && h_offsets_ && h_nz_ && h_motion_ && h_modes_;
         } else {                        // one picture's records stay on the device; finished slices go to the host
-            e_blocks_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * kMbCoefs * nmb));
-            e_offsets_ = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb));
-            e_nz_      = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb));
+            // two sets of records: the entropy pass of picture f runs beside the kernels of picture f + 1
+            e_blocks_  = static_cast<int16_t *>(ops_.alloc(sizeof(int16_t) * kMbCoefs * nmb * 2));
+            e_offsets_ = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb * 2));
+            e_nz_      = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb * 2));
             e_modes_   = static_cast<uint8_t *>(ops_.alloc(nmb));
-            e_nnz_     = static_cast<uint8_t *>(ops_.alloc(24 * nmb));
+            e_nnz_     = static_cast<uint8_t *>(ops_.alloc(24 * nmb * 2));
             e_mb_buf_  = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * kMbBufWords * nmb));
             e_mb_bits_ = static_cast<uint32_t *>(ops_.alloc(sizeof(uint32_t) * nmb * 3));      // bits, offsets, runs
             e_mb_kind_ = static_cast<uint8_t *>(ops_.alloc(nmb));
@@ -179,8 +181,8 @@ public:
         uint32_t *nz_dev      = de ? e_nz_ : static_cast<uint32_t *>(ops_.device_alias(h_nz_));
         MbMotion *motion_dev  = de ? nullptr : static_cast<MbMotion *>(ops_.device_alias(h_motion_));
         uint8_t  *modes_dev   = de ? e_modes_ : static_cast<uint8_t *>(ops_.device_alias(h_modes_));
-        const size_t per_pic  = de ? 0 : 1;      // records of picture f start at f * per_pic * (size of one picture's records)
-        uint8_t *nnz_y = de ? e_nnz_ : nullptr, *nnz_u = de ? e_nnz_ + 16 * nmb : nullptr, *nnz_v = de ? e_nnz_ + 20 * nmb : nullptr;
+        // records of picture f: its own area of the host tables, or device set f & 1
+        auto rset = [&](int f) { return size_t(de ? (f & 1) : f); };
         if (de && (rc = ops_.clear(e_used_, sizeof(unsigned)))) return rc;
         int      *done_dev    = static_cast<int *>(ops_.device_alias(h_done_));
         unsigned *counters_dev = static_cast<unsigned *>(ops_.device_alias(h_counters_));
@@ -189,6 +191,8 @@ public:
             const int r = f & 1, p = r ^ 1;
             uint8_t *cy = cur_.y + ps_.y * f + ps_.oy, *cu = cur_.u + ps_.c * f + ps_.oc, *cv = cur_.v + ps_.c * f + ps_.oc;
             uint8_t *ry = rec_y_[r][0] + ps_.oy, *ru = rec_u_[r] + ps_.oc, *rv = rec_v_[r] + ps_.oc;
+            uint8_t *nnz_y = de ? e_nnz_ + 24 * nmb * rset(f) : nullptr, *nnz_u = de ? nnz_y + 16 * nmb : nullptr, *nnz_v = de ? nnz_y + 20 * nmb : nullptr;
+            if (de && f >= 2 && (rc = ops_.wait_side(f & 1))) return rc;      // the entropy pass of picture f - 2 has read this set
             if (f == 0) {
                 IntraArgs a;
                 a.cur_y = cy; a.cur_u = cu; a.cur_v = cv; a.rec_y = ry; a.rec_u = ru; a.rec_v = rv;
@@ -215,18 +219,20 @@ public:
                 EncMbArgs e;
                 e.cur_y = cy; e.cur_u = cu; e.cur_v = cv; e.ref = ref; e.rec_y = ry; e.rec_u = ru; e.rec_v = rv;
                 e.sy = g_.sy; e.sc = g_.sc; e.mbw = g_.mbw; e.mbh = g_.mbh; e.q = q;
-                e.motion = d_motion_ + nmb * f; e.coefs = nullptr; e.nzmask = nz_dev + nmb * f * per_pic;   // levels go straight to the packed blocks
-                e.pack.blocks = blocks_dev + size_t(kMbCoefs) * nmb * f * per_pic; e.pack.offsets = offsets_dev + nmb * f * per_pic; e.pack.counter = d_counters_ + f;
+                e.motion = d_motion_ + nmb * f; e.coefs = nullptr; e.nzmask = nz_dev + nmb * rset(f);   // levels go straight to the packed blocks
+                e.pack.blocks = blocks_dev + size_t(kMbCoefs) * nmb * rset(f); e.pack.offsets = offsets_dev + nmb * rset(f); e.pack.counter = d_counters_ + f;
                 e.nnz_y = nnz_y; e.nnz_u = nnz_u; e.nnz_v = nnz_v;
                 if ((rc = ops_.encode_inter(e))) return rc;
             }
             // the picture's records were stored into host memory by the kernels above; a last small kernel copies the block
             // count and raises the arrival flag (stream order + a system-wide fence: everything has landed by then)
+            // nothing below is waited for by the next picture's kernels: it runs beside them
+            if ((rc = ops_.side_begin())) return rc;
             if (de) {     // the picture's slice data: macroblock bits, scan, placement, copy to the host buffer
                 EntropyPicture ep;
                 ep.ent.mbw = g_.mbw; ep.ent.mbh = g_.mbh; ep.ent.idr = f == 0;
-                ep.ent.nzmask = e_nz_; ep.ent.motion = d_motion_ + nmb * f; ep.ent.modes = e_modes_;
-                ep.ent.blocks = e_blocks_; ep.ent.offsets = e_offsets_;
+                ep.ent.nzmask = e_nz_ + nmb * rset(f); ep.ent.motion = d_motion_ + nmb * f; ep.ent.modes = e_modes_;
+                ep.ent.blocks = e_blocks_ + size_t(kMbCoefs) * nmb * rset(f); ep.ent.offsets = e_offsets_ + nmb * rset(f);
                 ep.ent.nnz_y = nnz_y; ep.ent.nnz_c[0] = nnz_u; ep.ent.nnz_c[1] = nnz_v;
                 ep.ent.mb_buf = e_mb_buf_; ep.ent.mb_bits = e_mb_bits_; ep.ent.mb_kind = e_mb_kind_;
                 ep.slice.nmb = int(nmb); ep.slice.mb_buf = e_mb_buf_; ep.slice.mb_bits = e_mb_bits_; ep.slice.mb_kind = e_mb_kind_;
@@ -239,6 +245,7 @@ public:
                 if ((rc = ops_.entropy_picture(ep))) return rc;
             }
             if ((rc = ops_.signal_picture(done_dev + f, counters_dev + f, d_counters_ + f))) return rc;
+            if ((rc = ops_.side_end(f & 1))) return rc;
             if (cfg_.keep_recon) {
                 uint8_t *dst = recon_store_.data() + size_t(g_.w16) * g_.h16 * 3 / 2 * f;
                 if ((rc = ops_.copy_plane(dst, g_.w16, ry, g_.sy, g_.w16, g_.h16))) return rc;
@@ -255,6 +262,9 @@ public:
                 if ((rc = ops_.lowres_batch(lowres_args(ry, rec_low_[r] + ps_.ol)))) return rc;
             }
         }
+        // the chain ends where the side work ends (one stream to wait on; a captured graph must rejoin its origin)
+        if ((rc = ops_.wait_side(0))) return rc;
+        if (n >= 2 && (rc = ops_.wait_side(1))) return rc;
         return 0;
     }
 

@@ -65,7 +65,20 @@ struct EmuOps {
     int signal_picture(int *done, unsigned *count_out, const unsigned *count_in) { *count_out = *count_in; *done = 1; return 0; }
     int entropy_picture(const EntropyPicture &p) {      // the entropy kernels' per-thread bodies, serially; the scan as a plain loop
         const int nmb = p.ent.mbw * p.ent.mbh;
-        for (int mb = 0; mb < nmb; ++mb) ent_mb(p.ent, mb);
+        for (int mb = 0; mb < nmb; ++mb) {                  // the warp of ent_mb_kernel, lane by lane
+            static EntSmem sm;
+            sm.kind = 0; sm.overflow = 0;
+            int bits[32] = {0}, off[32] = {0}, total = 0;
+            for (int l = 0; l < 32; ++l) bits[l] = ent_lane_encode(l, p.ent, mb, sm);
+            for (int pos = 0; pos < kEntLanes; ++pos) { off[ent_lane_at(pos)] = total; total += bits[ent_lane_at(pos)]; }
+            const int words = (total + 31) >> 5;
+            for (int j = 0; j < words; ++j) sm.mb[j] = 0;
+            for (int l = 0; l < kEntLanes; ++l)
+                if (bits[l]) ent_or_bits(sm.mb, kMbBufWords, (unsigned long long)off[l], sm.lane_buf[l], bits[l]);
+            memcpy(p.ent.mb_buf + size_t(mb) * kMbBufWords, sm.mb, size_t(words) * 4);
+            p.ent.mb_bits[mb] = uint32_t(total);
+            p.ent.mb_kind[mb] = uint8_t(sm.kind | (sm.overflow ? 128 : 0));
+        }
         const SliceArgs &a = p.slice;
         int prev = -1;
         unsigned long long bits = 0;
@@ -103,6 +116,9 @@ struct EmuOps {
         for (int y = 0; y < h; ++y) memcpy(dst + size_t(y) * dpitch, src + size_t(y) * spitch, w);
         return 0;
     }
+    int side_begin() { return 0; }
+    int side_end(int) { return 0; }
+    int wait_side(int) { return 0; }
     int sync() { return 0; }
 };
 }  // namespace
