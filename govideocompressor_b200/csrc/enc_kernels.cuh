@@ -616,12 +616,17 @@ struct MeRefArgs {
     MbMotion      *out;
     MbMotion      *out_host;     // optional second copy of the result (host-mapped memory), or null
 };
+#ifndef GVC_ME_EARLY_MUL
+#define GVC_ME_EARLY_MUL 32
+#endif
+constexpr int kMeEarlyMul = GVC_ME_EARLY_MUL;   // early termination: zero-vector SAD <= kMeEarlyMul * lambda (oracle/h264_mb.c)
 struct MeRefSmem {               // per warp
     gvc_uint4      cur[16];      // the macroblock's 16 source rows
     const uint8_t *plane[4];     // full, H, V, C sample planes (mc_luma_src order)
     unsigned       key[5][32];
     int            center[5][2], best_mv[5][2], best_cost[5];
     int            mvp[2], low[2];
+    int            zero_sad;     // 16x16 SAD of the zero vector
 };
 GVC_HD void sq8(int i, int &dx, int &dy) {   // (0,-1),(0,1),(-1,0),(1,0),(-1,-1),(-1,1),(1,-1),(1,1)
     dx = i < 2 ? 0 : ((i == 2 || i == 4 || i == 5) ? -1 : 1);
@@ -683,7 +688,20 @@ GVC_HD void me_ref_int(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &
     const unsigned bits = (unsigned)(a.lambda * mv_bits(4 * cx, 4 * cy, sm.mvp[0], sm.mvp[1]));
     sm.key[0][lane] = ((s[0] + s[1] + s[2] + s[3] + bits) << 5) | (unsigned)lane;
     for (int k = 0; k < 4; ++k) sm.key[1 + k][lane] = ((s[k] + bits) << 5) | (unsigned)lane;
+    if (lane == 26) sm.zero_sad = (int)(s[0] + s[1] + s[2] + s[3]);
     // candidate coordinates are recomputed by the picker from the winning lane id
+}
+// early termination: the zero vector predicts the macroblock well enough; one 16x16 partition, no sub-sample search
+GVC_HD bool me_ref_early(const MeRefArgs &a, const MeRefSmem &sm) { return sm.zero_sad <= kMeEarlyMul * a.lambda; }
+GVC_HD void me_ref_early_out(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm) {
+    if (lane != 0) return;
+    MbMotion m;
+    m.mode = 0;
+    m.cost = sm.zero_sad + a.lambda * mv_bits(0, 0, sm.mvp[0], sm.mvp[1]);
+    for (int k = 0; k < 4; ++k) m.mv[k][0] = m.mv[k][1] = 0;
+    m.pad[0] = m.pad[1] = m.pad[2] = 0;
+    a.out[my * a.mbw + mx] = m;
+    if (a.out_host) a.out_host[my * a.mbw + mx] = m;
 }
 GVC_HD void me_ref_pick(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
     if (lane >= 5) return;

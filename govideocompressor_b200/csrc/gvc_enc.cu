@@ -83,6 +83,7 @@ __global__ void __launch_bounds__(32 * kMbWarps) me_refine_kernel(const __grid_c
     __syncwarp();
     me_ref_int(lane, a, mx, my, sm);
     __syncwarp();
+    if (me_ref_early(a, sm)) { me_ref_early_out(lane, a, mx, my, sm); return; }
     me_ref_pick(lane, a, mx, my, sm);
     __syncwarp();
     MeLane L;

@@ -100,6 +100,9 @@ int  gvc_oracle_lambda(int qp);
 int  gvc_oracle_se_bits(int v);
 void gvc_oracle_me_lowres(const uint8_t *cur, const uint8_t *ref, int stride, int mbw, int mbh, int r, int lambda,
                           int16_t *out_mv, int32_t *out_cost);
+#ifndef GVC_ME_EARLY_MUL
+#define GVC_ME_EARLY_MUL 32   /* SAD threshold of the zero-vector early termination, in units of lambda (product: enc_kernels.cuh kMeEarlyMul) */
+#endif
 void gvc_oracle_me_refine(const uint8_t *cur, const uint8_t *const planes[4], int stride, int w16, int h16, int pad,
                           const int16_t *lowres_mv, int lambda, int32_t *out);
 void gvc_oracle_encode_inter_frame(const uint8_t *const cur[3], const uint8_t *const ref_luma[4],

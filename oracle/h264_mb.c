@@ -114,7 +114,7 @@ void gvc_oracle_me_refine(const uint8_t *cur, const uint8_t *const planes[4], in
             const int xmin = -x0 - (pad - 8), xmax = w16 - x0 - 16 + (pad - 8);
             const int ymin = -y0 - (pad - 8), ymax = h16 - y0 - 16 + (pad - 8);
             const int basex = 2 * lowres_mv[2 * (my * mbw + mx)], basey = 2 * lowres_mv[2 * (my * mbw + mx) + 1];
-            long best16 = -1, best8[4] = {-1, -1, -1, -1};
+            long best16 = -1, best8[4] = {-1, -1, -1, -1}, zero_sad = 0;
             int  b16x = 0, b16y = 0, b8x[4] = {0, 0, 0, 0}, b8y[4] = {0, 0, 0, 0};
             for (int i = 0; i < 27; i++) {
                 int cx, cy;
@@ -133,6 +133,15 @@ void gvc_oracle_me_refine(const uint8_t *cur, const uint8_t *const planes[4], in
                     if (best8[k] < 0 || s + bits < best8[k]) { best8[k] = s + bits; b8x[k] = cx; b8y[k] = cy; }
                 }
                 if (best16 < 0 || s16 + bits < best16) { best16 = s16 + bits; b16x = cx; b16y = cy; }
+                if (i == 26) zero_sad = s16;
+            }
+            int32_t *o = out + 10 * (my * mbw + mx);
+            /* early termination (the idea of x264's early-skip probe, analyse.c): a macroblock the zero vector already
+             * predicts to within GVC_ME_EARLY_MUL * lambda of SAD keeps it as one 16x16 partition, no sub-sample search */
+            if (zero_sad <= (long)GVC_ME_EARLY_MUL * lambda) {
+                for (int k = 0; k < 8; k++) o[k] = 0;
+                o[8] = (int32_t)(zero_sad + lambda * mv_bits(0, 0, px, py)); o[9] = 0;
+                continue;
             }
             int m16x = 4 * b16x, m16y = 4 * b16y;
             const int j16 = subpel_refine(&c, x0, y0, 16, &m16x, &m16y, px, py);
@@ -141,7 +150,6 @@ void gvc_oracle_me_refine(const uint8_t *cur, const uint8_t *const planes[4], in
                 m8x[k] = 4 * b8x[k]; m8y[k] = 4 * b8y[k];
                 j8 += subpel_refine(&c, x0 + 8 * (k & 1), y0 + 8 * (k >> 1), 8, &m8x[k], &m8y[k], px, py);
             }
-            int32_t *o = out + 10 * (my * mbw + mx);
             if (j8 < j16) {
                 for (int k = 0; k < 4; k++) { o[2 * k] = m8x[k]; o[2 * k + 1] = m8y[k]; }
                 o[8] = j8; o[9] = 1;

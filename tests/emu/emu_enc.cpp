@@ -2,6 +2,8 @@
 // lane / thread by thread on the host, phase by phase, so the CPU suite can compare their logic with the oracle.
 // Not part of libgvc.so.
 #define GVC_EMU 1
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -28,6 +30,10 @@ void emu_run_me_refine(const MeRefArgs &a) {
             memset(&sm, 0xAB, sizeof(sm));
             for (int l = 0; l < 32; ++l) me_ref_load(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
+            if (me_ref_early(a, sm)) {
+                for (int l = 0; l < 32; ++l) me_ref_early_out(l, a, mx, my, sm);
+                continue;
+            }
             for (int l = 0; l < 32; ++l) me_ref_pick(l, a, mx, my, sm);
             MeLane L[32];
             for (int l = 0; l < 32; ++l) me_lane_init(l, a, mx, my, sm, L[l]);
@@ -43,6 +49,7 @@ void emu_run_me_refine(const MeRefArgs &a) {
                     }
                 }
             for (int l = 0; l < 32; ++l) me_ref_publish(l, L[l], sm);
+
             for (int l = 0; l < 32; ++l) me_ref_out(l, a, mx, my, sm);
         }
 }

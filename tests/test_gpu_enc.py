@@ -106,6 +106,29 @@ def test_me_refine_and_encode_inter(pair, qp):
         np.testing.assert_array_equal(x, y)
 
 
+def test_me_refine_early_termination_on_static_content():
+    """Macroblocks the zero vector predicts to within 32*lambda of SAD stop before the sub-sample search: a frame whose left
+    half repeats the reference exactly (plus a faint flicker on a few macroblocks) exercises both exits side by side."""
+    g = E.geom(160, 96)
+    ref_yuv, cur_yuv = E.make_pair(g["w16"], g["h16"], seed=21)
+    cur_yuv = {k: v.copy() for k, v in cur_yuv.items()}
+    for k, v in cur_yuv.items():
+        v[:, : v.shape[1] // 2] = ref_yuv[k][:, : v.shape[1] // 2]
+    cur_yuv["Y"][5:9, 20:30] ^= 1                      # SAD 40: still below the threshold at lambda 4 (128)
+    cur_yuv["Y"][40:44, 3:60] = 255 - cur_yuv["Y"][40:44, 3:60]      # far above it
+    ref, cur = E.Frame(g, ref_yuv), E.Frame(g, cur_yuv, with_hpel=False)
+    lam = oracle_lib.load().gvc_oracle_lambda(23)
+    low = E.me_lowres("oracle", cur, ref, 8, lam)
+    mo = E.me_refine("oracle", cur, ref, low, lam)
+    mb = E.me_refine("gpu", cur, ref, low, lam)
+    for f in ("mv", "cost", "mode"):
+        np.testing.assert_array_equal(mo[f], mb[f])
+    mv = mo["mv"].reshape(g["mbh"], g["mbw"], 4, 2)
+    assert not mv[0, :4].any() and not mv[5, :4].any()          # static macroblocks keep the zero vector
+    assert mo["cost"].reshape(g["mbh"], g["mbw"])[0, 0] <= 32 * lam + 64
+    assert mv[:, g["mbw"] // 2 + 1:].any()                      # the moving half went through the full search
+
+
 def test_encode_inter_all_fractional_phases(pair):
     g, ref, cur = pair
     n = g["mbw"] * g["mbh"]
