@@ -554,6 +554,17 @@ struct MeLowArgs {
 };
 struct MeLowSmem { unsigned win[kLowRows + kLowChunk][kLowPitch]; };   // per warp: window rows, byte 0 = column 8*mx - r; the
                                                                        // spare rows are read for dy past the range, never filled
+// The zero displacement costs SAD0 + 2 lambda; every other one at least 8 lambda of vector bits alone (se(+-4) takes 7
+// bits).  So SAD0 < 6 lambda decides the exhaustive search before it starts: same result, no window, no candidates.
+GVC_HD unsigned me_lowres_zero_sad(int lane, const MeLowArgs &a, int mx, int my) {   // lanes 0..7: one row each
+    if (lane >= 8) return 0;
+    const int o = (8 * my + lane) * a.stride + 8 * mx;
+    unsigned c0, c1, r0, r1;
+    ld_u64_any(a.cur + o, c0, c1);
+    ld_u64_any(a.ref + o, r0, r1);
+    return sad_u8x4(c1, r1, sad_u8x4(c0, r0, 0));
+}
+GVC_HD bool me_lowres_zero_wins(const MeLowArgs &a, unsigned sad0) { return sad0 < 6u * (unsigned)a.lambda; }
 GVC_HD void me_lowres_load(int lane, const MeLowArgs &a, int mx, int my, MeLowSmem &sm) {
     const int rows = 8 + 2 * a.r, words = (8 + 2 * a.r + 3) >> 2;
     const uint8_t *org = a.ref + ((8 * my - a.r) * a.stride + 8 * mx - a.r);

@@ -66,6 +66,10 @@ __global__ void __launch_bounds__(32 * kMbWarps) me_lowres_kernel(const __grid_c
     const int mb = blockIdx.x * kMbWarps + warp;
     if (mb >= a.mbw * a.mbh) return;
     const int my = mb / a.mbw, mx = mb - my * a.mbw;
+    if (me_lowres_zero_wins(a, __reduce_add_sync(0xffffffffu, me_lowres_zero_sad(lane, a, mx, my)))) {
+        me_lowres_out(lane, a, mx, my, (unsigned)(a.r * (2 * a.r + 1) + a.r));      // index of displacement (0, 0)
+        return;
+    }
     me_lowres_load(lane, a, mx, my, sms[warp]);
     __syncwarp();
     const unsigned best = __reduce_min_sync(0xffffffffu, me_lowres_lane(lane, a, mx, my, sms[warp]));

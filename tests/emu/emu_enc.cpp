@@ -15,6 +15,12 @@ using namespace gvc;
 void emu_run_me_lowres(const MeLowArgs &a) {
     for (int my = 0; my < a.mbh; ++my)
         for (int mx = 0; mx < a.mbw; ++mx) {
+            unsigned sad0 = 0;
+            for (int l = 0; l < 32; ++l) sad0 += me_lowres_zero_sad(l, a, mx, my);
+            if (me_lowres_zero_wins(a, sad0)) {
+                for (int l = 0; l < 32; ++l) me_lowres_out(l, a, mx, my, unsigned(a.r * (2 * a.r + 1) + a.r));
+                continue;
+            }
             MeLowSmem sm;
             memset(&sm, 0xAB, sizeof(sm));
             for (int l = 0; l < 32; ++l) me_lowres_load(l, a, mx, my, sm);

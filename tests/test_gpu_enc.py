@@ -119,6 +119,8 @@ def test_me_refine_early_termination_on_static_content():
     ref, cur = E.Frame(g, ref_yuv), E.Frame(g, cur_yuv, with_hpel=False)
     lam = oracle_lib.load().gvc_oracle_lambda(23)
     low = E.me_lowres("oracle", cur, ref, 8, lam)
+    np.testing.assert_array_equal(low, E.me_lowres("gpu", cur, ref, 8, lam))     # static blocks: decided by the zero displacement alone
+    assert not low.reshape(g["mbh"], g["mbw"], 2)[0, :4].any()
     mo = E.me_refine("oracle", cur, ref, low, lam)
     mb = E.me_refine("gpu", cur, ref, low, lam)
     for f in ("mv", "cost", "mode"):
