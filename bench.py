@@ -192,6 +192,8 @@ def main():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # the version banner goes to stdout: rank 0 prints ONE JSON line and nothing else
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     gvc.init(local)
     cores = os.cpu_count() or 1
