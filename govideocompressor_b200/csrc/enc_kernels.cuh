@@ -546,13 +546,15 @@ GVC_HD int hadamard4_abs(const int d[16]) {
 // first stages the (8+2r)^2 search window in shared memory.  A work item is one column dx and kLowChunk consecutive dy:
 // the lane shifts each window row to dx once and feeds it to every candidate of the chunk that uses that row, so a
 // candidate costs its 16 four-byte SADs and a sixth of the row fetches.  key = cost<<11 | index; the warp minimum wins.
-constexpr int kLowMaxR = 22, kLowRows = 8 + 2 * kLowMaxR, kLowPitch = kLowMaxR / 2 + 4, kLowChunk = 6;
+constexpr int kLowMaxR = 22, kLowRows = 8 + 2 * kLowMaxR, kLowPitch = kLowMaxR / 2 + 4;
+constexpr int kLowChunk = 6, kLowChunkWide = 11;     // dy per work item: 6 fills two rounds of lanes at r = 8, 11 four rounds at r = 16
+GVC_HDH int me_lowres_chunk(int r) { return r <= 10 ? kLowChunk : kLowChunkWide; }
 struct MeLowArgs {
     const uint8_t *cur, *ref;   // lowres planes at (0,0)
     int stride, mbw, mbh, r, lambda;
     int16_t *out_mv;            // (dx,dy) per MB
 };
-struct MeLowSmem { unsigned win[kLowRows + kLowChunk][kLowPitch]; };   // per warp: window rows, byte 0 = column 8*mx - r; the
+struct MeLowSmem { unsigned win[kLowRows + kLowChunkWide][kLowPitch]; };   // per warp: window rows, byte 0 = column 8*mx - r; the
                                                                        // spare rows are read for dy past the range, never filled
 // The zero displacement costs SAD0 + 2 lambda; every other one at least 8 lambda of vector bits alone (se(+-4) takes 7
 // bits).  So SAD0 < 6 lambda decides the exhaustive search before it starts: same result, no window, no candidates.
@@ -572,33 +574,34 @@ GVC_HD void me_lowres_load(int lane, const MeLowArgs &a, int mx, int my, MeLowSm
     if (c < words)
         for (int y = lane >> cs; y < rows; y += 32 >> cs) sm.win[y][c] = ld_u32_any(org + (y * a.stride + 4 * c));
 }
+template <int kChunk>
 GVC_HD unsigned me_lowres_lane(int lane, const MeLowArgs &a, int mx, int my, const MeLowSmem &sm) {
-    const int n = 2 * a.r + 1, items = n * ((n + kLowChunk - 1) / kLowChunk);
+    const int n = 2 * a.r + 1, items = n * ((n + kChunk - 1) / kChunk);
     unsigned  c[8][2];
     const uint8_t *cp = a.cur + (8 * my * a.stride + 8 * mx);
     for (int j = 0; j < 8; ++j) ld_u64_any(cp + j * a.stride, c[j][0], c[j][1]);
     unsigned best = 0xffffffffu;
     for (int it = lane; it < items; it += 32) {
-        const int ch = it / n, o = it - ch * n, y0 = ch * kLowChunk;    // o = dx + r, y0 = first dy + r of the chunk
+        const int ch = it / n, o = it - ch * n, y0 = ch * kChunk;    // o = dx + r, y0 = first dy + r of the chunk
         const int wi = o >> 2, sh = (o & 3) * 8;
-        unsigned acc[kLowChunk];
-        for (int k = 0; k < kLowChunk; ++k) acc[k] = 0;
+        unsigned acc[kChunk];
+        for (int k = 0; k < kChunk; ++k) acc[k] = 0;
 #if !defined(GVC_EMU)
 #pragma unroll
 #endif
-        for (int y = 0; y < kLowChunk + 7; ++y) {
+        for (int y = 0; y < kChunk + 7; ++y) {
             const unsigned *row = sm.win[y0 + y];                        // rows past the window only feed discarded dy
             const unsigned w1 = row[wi + 1], lo = funnel_r(row[wi], w1, sh), hi = funnel_r(w1, row[wi + 2], sh);
 #if !defined(GVC_EMU)
 #pragma unroll
 #endif
-            for (int k = 0; k < kLowChunk; ++k) {
+            for (int k = 0; k < kChunk; ++k) {
                 const int j = y - k;
                 if (j >= 0 && j < 8) acc[k] = sad_u8x4(c[j][1], hi, sad_u8x4(c[j][0], lo, acc[k]));
             }
         }
         const int bx = se_bits(4 * (o - a.r));
-        for (int k = 0; k < kLowChunk; ++k) {
+        for (int k = 0; k < kChunk; ++k) {
             const int q = y0 + k;                                        // dy + r
             if (q >= n) break;
             const unsigned cost = acc[k] + (unsigned)(a.lambda * (bx + se_bits(4 * (q - a.r))));

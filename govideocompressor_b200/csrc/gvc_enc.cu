@@ -72,7 +72,9 @@ __global__ void __launch_bounds__(32 * kMbWarps) me_lowres_kernel(const __grid_c
     }
     me_lowres_load(lane, a, mx, my, sms[warp]);
     __syncwarp();
-    const unsigned best = __reduce_min_sync(0xffffffffu, me_lowres_lane(lane, a, mx, my, sms[warp]));
+    const unsigned mine = me_lowres_chunk(a.r) == kLowChunk ? me_lowres_lane<kLowChunk>(lane, a, mx, my, sms[warp])
+                                                            : me_lowres_lane<kLowChunkWide>(lane, a, mx, my, sms[warp]);
+    const unsigned best = __reduce_min_sync(0xffffffffu, mine);
     me_lowres_out(lane, a, mx, my, best);
 }
 

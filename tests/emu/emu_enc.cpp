@@ -25,7 +25,7 @@ void emu_run_me_lowres(const MeLowArgs &a) {
             memset(&sm, 0xAB, sizeof(sm));
             for (int l = 0; l < 32; ++l) me_lowres_load(l, a, mx, my, sm);
             unsigned best = 0xffffffffu;
-            for (int l = 0; l < 32; ++l) { const unsigned k = me_lowres_lane(l, a, mx, my, sm); best = k < best ? k : best; }
+            for (int l = 0; l < 32; ++l) { const unsigned k = me_lowres_chunk(a.r) == kLowChunk ? me_lowres_lane<kLowChunk>(l, a, mx, my, sm) : me_lowres_lane<kLowChunkWide>(l, a, mx, my, sm); best = k < best ? k : best; }
             for (int l = 0; l < 32; ++l) me_lowres_out(l, a, mx, my, best);
         }
 }
