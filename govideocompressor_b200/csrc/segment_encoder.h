@@ -272,9 +272,14 @@ public:
     // working on later pictures), then waits for the stream.
     int finish(SegmentOutput &out) {
         failed_ = false;
-        write_stream(out);
-        const int rc = ops_.sync();
-        if (rc) return rc;
+        int rc;
+        if (cfg_.device_entropy) {      // the slices arrive finished: wait once (no polling thread), then wrap them
+            if ((rc = ops_.sync())) return rc;
+            write_stream(out);
+        } else {                        // host entropy coding overlaps the GPU: workers start on a picture when its flag is up
+            write_stream(out);
+            if ((rc = ops_.sync())) return rc;
+        }
         if (failed_) return GVC_ERR_TOO_LARGE;     // the slices outgrew the buffers sized from the raw pictures
         if (cfg_.keep_recon) out.recon.swap(recon_store_);
         return 0;
@@ -341,7 +346,7 @@ public:
             }
             append_nal(au[f], f == 0 ? 3 : 2, f == 0 ? 5 : 1, bw.bytes(), false);
         };
-        const int workers = std::max(1, std::min(n_, std::min(cfg_.host_threads, 64)));
+        const int workers = cfg_.device_entropy ? 1 : std::max(1, std::min(n_, std::min(cfg_.host_threads, 64)));
         if (workers == 1) {
             for (int f = 0; f < n_; ++f) code_picture(f);
         } else {
