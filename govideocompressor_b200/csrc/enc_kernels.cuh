@@ -307,11 +307,14 @@ constexpr int kTapB = 0x000001fb;    // bytes -5,  1,  0,  0
 
 struct HpelArgs {
     const uint8_t *src; uint8_t *dh, *dv, *dc;   // all at sample (0,0), same stride
-    int stride, x_lo, x_hi, y_lo, y_hi;          // region to fill = readable region: [x_lo,x_hi) x [y_lo,y_hi)
+    int stride, x_lo, x_hi, y_lo, y_hi;          // region to fill: [x_lo,x_hi) x [y_lo,y_hi)
+    int cx_lo, cx_hi, cy_lo, cy_hi;              // readable part of src (reads clamp to it: edge replication); = the region, or the
+                                                 // picture itself when the border has not been extended yet
 };
 GVC_HDH bool hpel_aligned(const HpelArgs &a) {
     return (((unsigned long long)a.src | (unsigned long long)a.dh | (unsigned long long)a.dv | (unsigned long long)a.dc |
-             (unsigned long long)(unsigned)a.stride | (unsigned long long)(unsigned)a.x_lo | (unsigned long long)(unsigned)a.x_hi) & 3) == 0;
+             (unsigned long long)(unsigned)a.stride | (unsigned long long)(unsigned)a.x_lo | (unsigned long long)(unsigned)a.x_hi |
+             (unsigned long long)(unsigned)a.cx_lo | (unsigned long long)(unsigned)a.cx_hi) & 3) == 0;
 }
 GVC_HD void hpel_store4(uint8_t *plane, const HpelArgs &a, bool al, int x, int y, unsigned w) {   // samples x..x+3 of row y
     if (y >= a.y_hi || x >= a.x_hi) return;
@@ -324,15 +327,15 @@ GVC_HD void hpel_phase_a(int tid, const HpelArgs &a, bool al, int x0, int y0, Hp
     for (int i = tid; i < (kHpTileH + 5) * kHpWords; i += kHpThreads) {
         const int r = i / kHpWords, c = i - r * kHpWords;
         const int x = x0 - 4 + 4 * c;
-        const uint8_t *row = a.src + (long long)iclamp(y0 - 2 + r, a.y_lo, a.y_hi - 1) * a.stride;
+        const uint8_t *row = a.src + (long long)iclamp(y0 - 2 + r, a.cy_lo, a.cy_hi - 1) * a.stride;
         unsigned w;
-        if (al && x >= a.x_lo && x < a.x_hi) {
+        if (al && x >= a.cx_lo && x < a.cx_hi) {
             w = *reinterpret_cast<const unsigned *>(row + x);
         } else if (al) {
-            w = 0x01010101u * row[x < a.x_lo ? a.x_lo : a.x_hi - 1];
+            w = 0x01010101u * row[x < a.cx_lo ? a.cx_lo : a.cx_hi - 1];
         } else {
             w = 0;
-            for (int k = 0; k < 4; ++k) w |= (unsigned)row[iclamp(x + k, a.x_lo, a.x_hi - 1)] << (8 * k);
+            for (int k = 0; k < 4; ++k) w |= (unsigned)row[iclamp(x + k, a.cx_lo, a.cx_hi - 1)] << (8 * k);
         }
         sm.src[r][c] = w;
     }

@@ -270,6 +270,7 @@ int gvc_hpel_filter(const uint8_t *src, uint8_t *dh, uint8_t *dv, uint8_t *dc, i
     HpelArgs a;
     a.src = src; a.dh = dh; a.dv = dv; a.dc = dc; a.stride = stride;
     a.x_lo = x_lo; a.x_hi = x_hi; a.y_lo = y_lo; a.y_hi = y_hi;
+    a.cx_lo = x_lo; a.cx_hi = x_hi; a.cy_lo = y_lo; a.cy_hi = y_hi;      // the C ABI's region is also the readable part of src
     return launch_hpel(a, static_cast<cudaStream_t>(stream));
 }
 

@@ -63,10 +63,33 @@ struct StageTimer {
 struct CudaOps {
     cudaStream_t st = nullptr;       // the pictures' dependent kernel chain
     cudaStream_t side = nullptr;     // per-picture work nothing on the chain waits for (entropy pass, arrival flag)
-    cudaEvent_t  ev_fork = nullptr, ev_side[2] = {nullptr, nullptr};
-    bool         on_side = false;
+    cudaStream_t aux[2] = {nullptr, nullptr};   // branches of the reference plane preparation that run beside the chain
+    cudaEvent_t  ev_fork = nullptr, ev_side[2] = {nullptr, nullptr}, ev_prep = nullptr, ev_aux[2] = {nullptr, nullptr};
+    bool         on_side = false, prep_open = false;
+    int          branch = 0;
     StageTimer   tm;
-    cudaStream_t cur() const { return on_side ? side : st; }
+    cudaStream_t cur() const { return on_side ? side : branch ? aux[branch - 1] : st; }
+    // prep_fork: the two auxiliary branches start after everything issued on the chain so far; prep_on(b) selects where the
+    // next launches go (0 = the chain); prep_join makes the chain wait for both branches.
+    int prep_fork() {
+        if (tm.on) return 0;
+        GVC_CUDA(cudaEventRecord(ev_prep, st));
+        GVC_CUDA(cudaStreamWaitEvent(aux[0], ev_prep, 0));
+        GVC_CUDA(cudaStreamWaitEvent(aux[1], ev_prep, 0));
+        prep_open = true;
+        return 0;
+    }
+    int prep_on(int b) { if (!tm.on) branch = b; return 0; }
+    int prep_join() {
+        branch = 0;
+        if (!prep_open) return 0;
+        for (int b = 0; b < 2; ++b) {
+            GVC_CUDA(cudaEventRecord(ev_aux[b], aux[b]));
+            GVC_CUDA(cudaStreamWaitEvent(st, ev_aux[b], 0));
+        }
+        prep_open = false;
+        return 0;
+    }
     // side_begin: what follows runs on the side stream, after everything issued on the chain so far.  side_end(slot):
     // back to the chain; wait_side(slot) makes the chain wait for the side work closed with that slot.  While per-stage
     // timing is on everything stays on the chain (its events bracket single launches).
@@ -95,10 +118,10 @@ struct CudaOps {
     void *device_alias(void *h) { void *d = nullptr; return cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess ? d : nullptr; }
     int clear(void *dev, size_t n) { GVC_CUDA(cudaMemsetAsync(dev, 0, n, st)); return 0; }
     void  release_host(void *p) { cudaFreeHost(p); }
-    int extend_border3(const BorderBatchArgs &a) { return timed(kStBorder, [&] { return launch_extend_border_batch(a, st); }); }
-    int lowres_batch(const LowresBatchArgs &a) { return timed(kStLowres, [&] { return launch_lowres_batch(a, st); }); }
-    int hpel(const HpelArgs &a) { return timed(kStHpel, [&] { return launch_hpel(a, st); }); }
-    int me_lowres(const MeLowArgs &a) { return timed(kStMeLowres, [&] { return launch_me_lowres(a, st); }); }
+    int extend_border3(const BorderBatchArgs &a) { return timed(kStBorder, [&] { return launch_extend_border_batch(a, cur()); }); }
+    int lowres_batch(const LowresBatchArgs &a) { return timed(kStLowres, [&] { return launch_lowres_batch(a, cur()); }); }
+    int hpel(const HpelArgs &a) { return timed(kStHpel, [&] { return launch_hpel(a, cur()); }); }
+    int me_lowres(const MeLowArgs &a) { return timed(kStMeLowres, [&] { return launch_me_lowres(a, cur()); }); }
     int me_refine(const MeRefArgs &a) { return timed(kStMeRefine, [&] { return launch_me_refine(a, st); }); }
     int encode_inter(const EncMbArgs &a) { return timed(kStEncInter, [&] { return launch_encode_inter(a, st); }); }
     int encode_intra(const IntraArgs &a) { return timed(kStEncIntra, [&] { return launch_encode_intra(a, st); }); }
@@ -233,7 +256,10 @@ int gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg) {
     e->cfg = c;
     if (cudaStreamCreateWithFlags(&e->ops.st, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&e->ops.side, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&e->ops.ev_fork, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&e->ops.ev_side[0], cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&e->ops.ev_side[1], cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&e->ops.ev_side[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&e->ops.aux[0], cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&e->ops.aux[1], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ops.ev_prep, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&e->ops.ev_aux[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ops.ev_aux[1], cudaEventDisableTiming) != cudaSuccess) {
         gvc_encoder_destroy(e);
         set_error("cudaStreamCreate / cudaEventCreate failed");
         return GVC_ERR_CUDA;
@@ -262,6 +288,8 @@ void gvc_encoder_destroy(gvc_encoder *e) {
     for (int b = 0; b < 2; ++b) { if (e->d_src[b]) cudaFree(e->d_src[b]); if (e->uploaded[b]) cudaEventDestroy(e->uploaded[b]); }
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     if (e->ops.side) cudaStreamDestroy(e->ops.side);
+    for (int b = 0; b < 2; ++b) { if (e->ops.aux[b]) cudaStreamDestroy(e->ops.aux[b]); if (e->ops.ev_aux[b]) cudaEventDestroy(e->ops.ev_aux[b]); }
+    if (e->ops.ev_prep) cudaEventDestroy(e->ops.ev_prep);
     if (e->ops.st) cudaStreamDestroy(e->ops.st);
     if (e->ops.ev_fork) cudaEventDestroy(e->ops.ev_fork);
     for (int b = 0; b < 2; ++b) if (e->ops.ev_side[b]) cudaEventDestroy(e->ops.ev_side[b]);

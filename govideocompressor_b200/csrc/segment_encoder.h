@@ -66,6 +66,7 @@ struct SegmentOutput {
 //   int signal_picture(int *done, unsigned *count_out, const unsigned *count_in);   // *count_out = *count_in; fence; *done = 1
 //   int entropy_picture(const EntropyPicture &p);                                    // device_entropy: the picture's slice -> host buffer
 //   int side_begin();  int side_end(int slot);  int wait_side(int slot);            // fork / join of work the picture chain does not wait for
+//   int prep_fork();  int prep_on(int branch);  int prep_join();                     // three concurrent branches (0 = the chain itself) and their join
 //   int copy_plane(uint8_t *host_or_dev_dst, int dpitch, const uint8_t *dev_src, int spitch, int w, int h);   // device -> recon store
 //   int sync();
 template <class Ops>
@@ -208,10 +209,9 @@ public:
                 ref.u = rec_u_[p] + ps_.oc; ref.v = rec_v_[p] + ps_.oc; ref.low = rec_low_[p] + ps_.ol;
                 QuantParams q;
                 fill_quant_params(q, cfg_.qp_p, false);
-                MeLowArgs ml;
-                ml.cur = cur_low_ + ps_.l * f + ps_.ol; ml.ref = ref.low; ml.stride = g_.sl; ml.mbw = g_.mbw; ml.mbh = g_.mbh;
-                ml.r = cfg_.merange / 2; ml.lambda = q.lambda; ml.out_mv = d_lowmv_;
-                if ((rc = ops_.me_lowres(ml))) return rc;
+                // the lowres search of this picture was issued with the reference's plane preparation (below, previous
+                // iteration), beside the half-sample filter and the border extension: wait for all three branches
+                if ((rc = ops_.prep_join())) return rc;
                 MeRefArgs mr;
                 mr.cur = cy; mr.ref = ref; mr.stride = g_.sy; mr.w16 = g_.w16; mr.h16 = g_.h16; mr.mbw = g_.mbw; mr.mbh = g_.mbh;
                 mr.lambda = q.lambda; mr.lowres_mv = d_lowmv_; mr.out = d_motion_ + nmb * f; mr.out_host = de ? nullptr : motion_dev + nmb * f;
@@ -252,14 +252,30 @@ public:
                 if ((rc = ops_.copy_plane(dst + size_t(g_.w16) * g_.h16, lw, ru, g_.sc, lw, lh))) return rc;
                 if ((rc = ops_.copy_plane(dst + size_t(g_.w16) * g_.h16 * 5 / 4, lw, rv, g_.sc, lw, lh))) return rc;
             }
-            if (f + 1 < n) {                // the reconstruction becomes the next picture's reference
-                BorderBatchArgs b = border_args(ry, ru, rv, g_.w16, g_.h16);
-                if ((rc = ops_.extend_border3(b))) return rc;
+            if (f + 1 < n) {
+                // The reconstruction becomes the next picture's reference.  Three independent branches (the half-sample and
+                // lowres kernels replicate the picture edge themselves instead of reading the extended border): border
+                // extension | lowres planes, then the next picture's lowres search | half-sample planes.
+                if ((rc = ops_.prep_fork())) return rc;
+                if ((rc = ops_.prep_on(1))) return rc;
+                LowresBatchArgs la = lowres_args(ry, rec_low_[r] + ps_.ol);
+                la.x_lo = 0; la.x_hi = g_.w16 - 1; la.y_lo = 0; la.y_hi = g_.h16 - 1;
+                if ((rc = ops_.lowres_batch(la))) return rc;
+                QuantParams qn;
+                fill_quant_params(qn, cfg_.qp_p, false);
+                MeLowArgs ml;
+                ml.cur = cur_low_ + ps_.l * (f + 1) + ps_.ol; ml.ref = rec_low_[r] + ps_.ol; ml.stride = g_.sl; ml.mbw = g_.mbw; ml.mbh = g_.mbh;
+                ml.r = cfg_.merange / 2; ml.lambda = qn.lambda; ml.out_mv = d_lowmv_;
+                if ((rc = ops_.me_lowres(ml))) return rc;
+                if ((rc = ops_.prep_on(2))) return rc;
                 HpelArgs ha;
                 ha.src = ry; ha.dh = rec_y_[r][1] + ps_.oy; ha.dv = rec_y_[r][2] + ps_.oy; ha.dc = rec_y_[r][3] + ps_.oy;
                 ha.stride = g_.sy; ha.x_lo = -P; ha.x_hi = g_.w16 + P; ha.y_lo = -P; ha.y_hi = g_.h16 + P;
+                ha.cx_lo = 0; ha.cx_hi = g_.w16; ha.cy_lo = 0; ha.cy_hi = g_.h16;
                 if ((rc = ops_.hpel(ha))) return rc;
-                if ((rc = ops_.lowres_batch(lowres_args(ry, rec_low_[r] + ps_.ol)))) return rc;
+                if ((rc = ops_.prep_on(0))) return rc;
+                BorderBatchArgs b = border_args(ry, ru, rv, g_.w16, g_.h16);
+                if ((rc = ops_.extend_border3(b))) return rc;
             }
         }
         // the chain ends where the side work ends (one stream to wait on; a captured graph must rejoin its origin)

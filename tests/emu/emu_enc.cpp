@@ -12,6 +12,17 @@
 
 using namespace gvc;
 
+void emu_run_hpel(const HpelArgs &a) {
+    for (int y0 = a.y_lo; y0 < a.y_hi; y0 += kHpTileH)
+        for (int x0 = a.x_lo; x0 < a.x_hi; x0 += kHpTileW) {
+            static HpelSmem sm;
+            memset(&sm, 0xAB, sizeof(sm));
+            const bool al = hpel_aligned(a);
+            for (int t = 0; t < kHpThreads; ++t) hpel_phase_a(t, a, al, x0, y0, sm);
+            for (int t = 0; t < kHpThreads; ++t) hpel_phase_b(t, a, al, x0, y0, sm);
+            for (int t = 0; t < kHpThreads; ++t) hpel_phase_c(t, a, al, x0, y0, sm);
+        }
+}
 void emu_run_me_lowres(const MeLowArgs &a) {
     for (int my = 0; my < a.mbh; ++my)
         for (int mx = 0; mx < a.mbw; ++mx) {
@@ -113,15 +124,8 @@ void emu_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, i
 void emu_hpel(const uint8_t *src, uint8_t *dh, uint8_t *dv, uint8_t *dc, int stride, int x_lo, int x_hi, int y_lo, int y_hi) {
     HpelArgs a;
     a.src = src; a.dh = dh; a.dv = dv; a.dc = dc; a.stride = stride; a.x_lo = x_lo; a.x_hi = x_hi; a.y_lo = y_lo; a.y_hi = y_hi;
-    for (int y0 = y_lo; y0 < y_hi; y0 += kHpTileH)
-        for (int x0 = x_lo; x0 < x_hi; x0 += kHpTileW) {
-            HpelSmem sm;
-            memset(&sm, 0xAB, sizeof(sm));
-            const bool al = hpel_aligned(a);
-            for (int t = 0; t < kHpThreads; ++t) hpel_phase_a(t, a, al, x0, y0, sm);
-            for (int t = 0; t < kHpThreads; ++t) hpel_phase_b(t, a, al, x0, y0, sm);
-            for (int t = 0; t < kHpThreads; ++t) hpel_phase_c(t, a, al, x0, y0, sm);
-        }
+    a.cx_lo = x_lo; a.cx_hi = x_hi; a.cy_lo = y_lo; a.cy_hi = y_hi;
+    emu_run_hpel(a);
 }
 
 void emu_me_lowres(const uint8_t *cur, const uint8_t *ref, int stride, int mbw, int mbh, int r, int lambda, int16_t *out_mv) {

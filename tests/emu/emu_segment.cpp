@@ -21,6 +21,7 @@ void emu_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo, i
 void emu_hpel(const uint8_t *src, uint8_t *dh, uint8_t *dv, uint8_t *dc, int stride, int x_lo, int x_hi, int y_lo, int y_hi);
 }
 void emu_run_me_lowres(const MeLowArgs &a);
+void emu_run_hpel(const HpelArgs &a);
 void emu_run_me_refine(const MeRefArgs &a);
 void emu_run_encode_inter(const EncMbArgs &a);
 void emu_run_encode_intra(const IntraArgs &a);
@@ -57,7 +58,7 @@ struct EmuOps {
                        nullptr, a.dstride, a.lx_lo, a.lx_hi, a.ly_lo, a.ly_hi);
         return 0;
     }
-    int hpel(const HpelArgs &a) { emu_hpel(a.src, a.dh, a.dv, a.dc, a.stride, a.x_lo, a.x_hi, a.y_lo, a.y_hi); return 0; }
+    int hpel(const HpelArgs &a) { emu_run_hpel(a); return 0; }
     int me_lowres(const MeLowArgs &a) { emu_run_me_lowres(a); return 0; }
     int me_refine(const MeRefArgs &a) { emu_run_me_refine(a); return 0; }
     int encode_inter(const EncMbArgs &a) { emu_run_encode_inter(a); return 0; }
@@ -116,6 +117,9 @@ struct EmuOps {
         for (int y = 0; y < h; ++y) memcpy(dst + size_t(y) * dpitch, src + size_t(y) * spitch, w);
         return 0;
     }
+    int prep_fork() { return 0; }
+    int prep_on(int) { return 0; }
+    int prep_join() { return 0; }
     int side_begin() { return 0; }
     int side_end(int) { return 0; }
     int wait_side(int) { return 0; }

@@ -16,9 +16,11 @@ def _vp(x):
     return ctypes.c_void_p(x)
 
 
-@pytest.fixture(scope="module")
-def pair():
+@pytest.fixture(scope="module", params=["pitch128", "odd-pitch"])
+def pair(request):
     g = E.geom(96, 64)
+    if request.param == "odd-pitch":      # pitches / addresses that are not multiples of four: the byte-wise load and store paths
+        g = dict(g, sy=g["sy"] + 3, sc=g["sc"] + 1, sl=g["sl"] + 1)
     ref_yuv, cur_yuv = E.make_pair(g["w16"], g["h16"], seed=3)
     return g, E.Frame(g, ref_yuv), E.Frame(g, cur_yuv, with_hpel=False)
 

@@ -15,10 +15,12 @@ def _vp(x):
     return ctypes.c_void_p(x)
 
 
-@pytest.fixture(scope="module", params=[(96, 64, 3), (1280, 720, 11), (200, 120, 5)], ids=["96x64", "720p", "200x120"])
+@pytest.fixture(scope="module", params=[(96, 64, 3, 0), (1280, 720, 11, 0), (200, 120, 5, 0), (96, 64, 3, 1)], ids=["96x64", "720p", "200x120", "96x64-odd-pitch"])
 def pair(request):
-    w, h, seed = request.param
+    w, h, seed, odd = request.param
     g = E.geom(w, h)
+    if odd:                               # pitches / addresses that are not multiples of four: the byte-wise load and store paths
+        g = dict(g, sy=g["sy"] + 3, sc=g["sc"] + 1, sl=g["sl"] + 1)
     ref_yuv, cur_yuv = E.make_pair(g["w16"], g["h16"], seed=seed)
     return g, E.Frame(g, ref_yuv), E.Frame(g, cur_yuv, with_hpel=False)
 

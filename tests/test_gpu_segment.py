@@ -33,7 +33,8 @@ def check_decode(gvc_enc, annexb, recon, w, h, n):
 
 
 @pytest.mark.parametrize("w,h,n,crf,kw", [(96, 64, 5, 23, {}), (150, 100, 6, 26, dict(static_left=True, noise=1)),
-                                           (128, 96, 5, 28, dict(fast=True, noise=2)), (64, 48, 3, 4, dict(noise=40))])
+                                           (128, 96, 5, 28, dict(fast=True, noise=2)), (64, 48, 3, 4, dict(noise=40)),
+                                           (352, 288, 4, 30, dict(noise=3)), (48, 162, 3, 20, dict(noise=2))])
 @pytest.mark.parametrize("entropy", [1, 2], ids=["host-cavlc", "gpu-cavlc"])
 def test_stream_identical_to_cpu_emulation_and_decodable(gvc, w, h, n, crf, kw, entropy):
     frames = S.moving_sequence(w, h, n, seed=w + n, **kw)
