@@ -948,6 +948,7 @@ GVC_HD void enc_mb_p1(int lane, const EncMbArgs &a, bool al, int mx, int my, Enc
         mc_chroma_4x4(lane < 20 ? a.ref.u : a.ref.v, a.sc, x, y, mvx, mvy, pr);
         for (int j = 0; j < 4; ++j) L.pred[j] = (unsigned)pr[4 * j] | ((unsigned)pr[4 * j + 1] << 8) | ((unsigned)pr[4 * j + 2] << 16) | ((unsigned)pr[4 * j + 3] << 24);
     }
+    GVC_RECONVERGE(0x00ffffffu);
     const int st = lane < 16 ? a.sy : a.sc;
     const uint8_t *src = (lane < 16 ? a.cur_y : lane < 20 ? a.cur_u : a.cur_v) + (y * st + x);
     for (int j = 0; j < 4; ++j) {
@@ -980,6 +981,7 @@ GVC_HD void enc_mb_p2(int lane, const EncMbArgs &a, bool al, int mx, int my, Enc
         mydc = (int)(int16_t)((f * (q.dq_c[0] << (q.qpc / 6))) >> 5);
         L.d[0] = 0;
     }
+    GVC_RECONVERGE(0x00ffffffu);
     int mf[3], bias[3], dq[3];
     for (int c = 0; c < 3; ++c) { mf[c] = luma ? q.mf_y[c] : q.mf_c[c]; bias[c] = luma ? q.bias_y[c] : q.bias_c[c]; dq[c] = luma ? q.dq_y[c] : q.dq_c[c]; }
     const int qp = luma ? q.qp : q.qpc;
@@ -998,6 +1000,7 @@ GVC_HD void enc_mb_p2(int lane, const EncMbArgs &a, bool al, int mx, int my, Enc
             for (int i = 0; i < 16; ++i) mbco[lane * 16 + i] = (int16_t)(L.lev[i >> 1] >> (16 * (i & 1)));
         }
     }
+    GVC_RECONVERGE(0x00ffffffu);
     for (int i = 0; i < 16; ++i) L.d[i] = dequant_one(L.d[i], dq[coef_class(i)], qp);
     if (!luma) L.d[0] = mydc;
     idct4x4(L.d);
@@ -1172,6 +1175,7 @@ GVC_HD void intra_p2(int lane, const IntraArgs &a, int mx, int my, IntraSmem &sm
         else              v = has_left ? (sl[1] + 2) >> 2 : has_top ? (st[0] + 2) >> 2 : 128;
         for (int j = 0; j < 4; ++j) L.pred[j] = rep_u8(v);
     }
+    GVC_RECONVERGE(0x00ffffffu);
     for (int j = 0; j < 4; ++j)
         for (int i = 0; i < 4; ++i) L.d[j * 4 + i] = byte_of(L.cur[j], i) - byte_of(L.pred[j], i);
     dct4x4(L.d);
@@ -1232,6 +1236,7 @@ GVC_HD void intra_p3d(int lane, const IntraArgs &a, bool al, int mx, int my, Int
         mydc = (int)(int16_t)((f * (q.dq_c[0] << (q.qpc / 6))) >> 5);
         L.d[0] = 0;
     }
+    GVC_RECONVERGE(0x00ffffffu);
     int mf[3], bias[3], dq[3];
     for (int c = 0; c < 3; ++c) { mf[c] = luma ? q.mf_y[c] : q.mf_c[c]; bias[c] = luma ? q.bias_y[c] : q.bias_c[c]; dq[c] = luma ? q.dq_y[c] : q.dq_c[c]; }
     const int qp = luma ? q.qp : q.qpc;
@@ -1251,6 +1256,7 @@ GVC_HD void intra_p3d(int lane, const IntraArgs &a, bool al, int mx, int my, Int
         }
         if (lane == 16) for (int i = 8; i < 16; ++i) mbco[24 * 16 + i] = 0;
     }
+    GVC_RECONVERGE(0x00ffffffu);
     for (int i = 0; i < 16; ++i) L.d[i] = dequant_one(L.d[i], dq[coef_class(i)], qp);
     L.d[0] = mydc;
     idct4x4(L.d);
