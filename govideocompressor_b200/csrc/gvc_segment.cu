@@ -442,7 +442,8 @@ int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char 
     log += std::string(gvc_version()) + "\n";
     TranscodeOptions opt;
     std::string      err;
-    if ((rc = parse_ffmpeg_args(ffmpeg_args, opt, err))) { set_error("%s", err.c_str()); return finish(rc); }
+    rc = parse_ffmpeg_args(ffmpeg_args, opt, err);
+    if (rc != 0) { set_error("%s", err.c_str()); return finish(rc); }
     std::unique_ptr<FrameSource> srcf = open_frame_source(in_path, err);
     if (!srcf) { set_error("%s: %s", in_path, err.c_str()); return finish(err == "No such file or directory" ? GVC_ERR_IO : GVC_ERR_UNSUPPORTED); }
     int w = srcf->w, h = srcf->h, fn = srcf->fps_num, fd = srcf->fps_den;
