@@ -89,6 +89,20 @@ def test_gpu_and_host_entropy_agree_at_baseline_size_with_graph_replay(gvc):
     assert len(h264_decode.decode(out[2][1])) == n
 
 
+def test_segment_lengths_change_on_the_graph_path(gvc):
+    """Segments of 5, 2, 1 and 5 pictures on the same encoders (CUDA graph re-captured per length; the side-stream joins differ
+    for 1 and 2 pictures): GPU entropy coding and host entropy coding agree and every stream decodes."""
+    w, h = 320, 192
+    frames = S.moving_sequence(w, h, 5, seed=9, noise=2)
+    encs = {e: gvc.Encoder(w, h, crf=24, entropy=e) for e in (1, 2)}
+    for n in (5, 2, 1, 5):
+        out = {e: encs[e].encode_host(frames[:n], annexb=True) for e in (1, 2)}
+        assert out[1] == out[2], f"streams differ for a {n}-picture segment"
+        assert len(h264_decode.decode(out[2])) == n
+    for e in encs.values():
+        e.close()
+
+
 def test_1080p_coded_height_1088_and_4k(gvc):
     for (w, h, n) in ((1920, 1080, 3), (3840, 2160, 2)):
         frames = S.moving_sequence(w, h, n, seed=5, noise=1)
