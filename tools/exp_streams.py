@@ -1,7 +1,8 @@
 #!/usr/bin/env python
-"""Experiment: device-resident throughput of the cfg2 path against the number of segments in flight.
+"""Experiment: device-resident throughput of the path against the number of segments in flight.
 
-    python tools/exp_streams.py 1 2 4 8 12 16
+    python tools/exp_streams.py 1 2 4 8 12 16                       # cfg2 shape: 1080p -> 720p, 38 pictures, me_range 16
+    GVC_SHAPE=3840x2160:1920x1080:14:32 python tools/exp_streams.py 1 4 8    # cfg3 shape (src:dst:pictures:me_range)
 """
 import os
 import sys
@@ -18,7 +19,10 @@ import torch
 import govideocompressor_b200 as gvc
 from util_inputs import make_frame
 
-SW, SH, DW, DH, N = 1920, 1080, 1280, 720, 38
+SW, SH, DW, DH, N, MERANGE = 1920, 1080, 1280, 720, 38, 16
+if os.environ.get("GVC_SHAPE"):
+    a, b, c, d = os.environ["GVC_SHAPE"].split(":")
+    (SW, SH), (DW, DH), N, MERANGE = map(int, a.split("x")), map(int, b.split("x")), int(c), int(d)
 
 
 def main():
@@ -30,7 +34,7 @@ def main():
     src = torch.from_numpy(seg).cuda()
     steps = 6
     for s in counts:
-        encs = [gvc.Encoder(SW, SH, DW, DH, crf=23, host_threads=1) for _ in range(s)]
+        encs = [gvc.Encoder(SW, SH, DW, DH, crf=23, merange=MERANGE, host_threads=1) for _ in range(s)]
         pool = ThreadPoolExecutor(s)
         run = lambda n: list(pool.map(lambda k: [encs[k].encode_device(src.data_ptr(), N) for _ in range(n)], range(s)))
         run(2)
