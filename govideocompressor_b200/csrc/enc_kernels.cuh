@@ -643,7 +643,6 @@ struct MeRefSmem {               // per warp
     unsigned       key[5][32];
     int            center[5][2], best_mv[5][2], best_cost[5];
     int            mvp[2], low[2];
-    int            zero_sad;     // 16x16 SAD of the zero vector
 };
 GVC_HD void sq8(int i, int &dx, int &dy) {   // (0,-1),(0,1),(-1,0),(1,0),(-1,-1),(-1,1),(1,-1),(1,1)
     dx = i < 2 ? 0 : ((i == 2 || i == 4 || i == 5) ? -1 : 1);
@@ -678,6 +677,15 @@ GVC_HD void me_ref_load(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem 
         sm.plane[0] = a.ref.y; sm.plane[1] = a.ref.hh; sm.plane[2] = a.ref.hv; sm.plane[3] = a.ref.hc;
     }
 }
+// the lane's share of the 16x16 SAD at the zero vector (two lanes per row): decides the early termination before any
+// candidate is evaluated
+GVC_HD unsigned me_ref_zero_part(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm) {
+    const int row = lane >> 1, half = lane & 1;
+    unsigned r0, r1;
+    ld_u64_any(a.ref.y + ((16 * my + row) * a.stride + 16 * mx + 8 * half), r0, r1);
+    const gvc_uint4 c = sm.cur[row];
+    return half ? sad_u8x4(c.w, r1, sad_u8x4(c.z, r0, 0)) : sad_u8x4(c.y, r1, sad_u8x4(c.x, r0, 0));
+}
 // integer candidate i of the macroblock: 5x5 around twice the lowres vector, the rounded predictor, zero
 GVC_HD void me_int_cand(const MeRefArgs &a, const MeRefSmem &sm, int mx, int my, int i, int &cx, int &cy) {
     if (i < 25)       { cx = 2 * sm.low[0] + (i % 5) - 2; cy = 2 * sm.low[1] + (i / 5) - 2; }
@@ -705,16 +713,16 @@ GVC_HD void me_ref_int(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &
     const unsigned bits = (unsigned)(a.lambda * mv_bits(4 * cx, 4 * cy, sm.mvp[0], sm.mvp[1]));
     sm.key[0][lane] = ((s[0] + s[1] + s[2] + s[3] + bits) << 5) | (unsigned)lane;
     for (int k = 0; k < 4; ++k) sm.key[1 + k][lane] = ((s[k] + bits) << 5) | (unsigned)lane;
-    if (lane == 26) sm.zero_sad = (int)(s[0] + s[1] + s[2] + s[3]);
+
     // candidate coordinates are recomputed by the picker from the winning lane id
 }
 // early termination: the zero vector predicts the macroblock well enough; one 16x16 partition, no sub-sample search
-GVC_HD bool me_ref_early(const MeRefArgs &a, const MeRefSmem &sm) { return sm.zero_sad <= kMeEarlyMul * a.lambda; }
-GVC_HD void me_ref_early_out(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm) {
+GVC_HD bool me_ref_early(const MeRefArgs &a, int zero_sad) { return zero_sad <= kMeEarlyMul * a.lambda; }
+GVC_HD void me_ref_early_out(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm, int zero_sad) {
     if (lane != 0) return;
     MbMotion m;
     m.mode = 0;
-    m.cost = sm.zero_sad + a.lambda * mv_bits(0, 0, sm.mvp[0], sm.mvp[1]);
+    m.cost = zero_sad + a.lambda * mv_bits(0, 0, sm.mvp[0], sm.mvp[1]);
     for (int k = 0; k < 4; ++k) m.mv[k][0] = m.mv[k][1] = 0;
     m.pad[0] = m.pad[1] = m.pad[2] = 0;
     a.out[my * a.mbw + mx] = m;

@@ -87,9 +87,10 @@ __global__ void __launch_bounds__(32 * kMbWarps) me_refine_kernel(const __grid_c
     MeRefSmem &sm = sms[warp];
     me_ref_load(lane, a, mx, my, sm);
     __syncwarp();
+    const int zero_sad = (int)__reduce_add_sync(0xffffffffu, me_ref_zero_part(lane, a, mx, my, sm));
+    if (me_ref_early(a, zero_sad)) { me_ref_early_out(lane, a, mx, my, sm, zero_sad); return; }
     me_ref_int(lane, a, mx, my, sm);
     __syncwarp();
-    if (me_ref_early(a, sm)) { me_ref_early_out(lane, a, mx, my, sm); return; }
     me_ref_pick(lane, a, mx, my, sm);
     __syncwarp();
     MeLane L;

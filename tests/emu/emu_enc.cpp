@@ -46,11 +46,13 @@ void emu_run_me_refine(const MeRefArgs &a) {
             MeRefSmem sm;
             memset(&sm, 0xAB, sizeof(sm));
             for (int l = 0; l < 32; ++l) me_ref_load(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
-            if (me_ref_early(a, sm)) {
-                for (int l = 0; l < 32; ++l) me_ref_early_out(l, a, mx, my, sm);
+            int zero_sad = 0;
+            for (int l = 0; l < 32; ++l) zero_sad += int(me_ref_zero_part(l, a, mx, my, sm));
+            if (me_ref_early(a, zero_sad)) {
+                for (int l = 0; l < 32; ++l) me_ref_early_out(l, a, mx, my, sm, zero_sad);
                 continue;
             }
+            for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) me_ref_pick(l, a, mx, my, sm);
             MeLane L[32];
             for (int l = 0; l < 32; ++l) me_lane_init(l, a, mx, my, sm, L[l]);
