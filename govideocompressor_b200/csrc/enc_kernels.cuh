@@ -98,23 +98,6 @@ GVC_HD unsigned pack_odd(unsigned w) {    // samples 1 and 3
     return __byte_perm(w, 0, 0x4341);
 #endif
 }
-GVC_HD unsigned abs_pair(unsigned v) {    // |lo| + (|hi| << 16), halves now clean
-#if defined(GVC_EMU)
-    const unsigned s = ((v >> 15) & 0x10001u) * 0xffffu;
-#else
-    unsigned s;                                       // sign of each half replicated over the half; __byte_perm would
-    asm("prmt.b32 %0, %1, %1, 0xbb99;" : "=r"(s) : "r"(v));   // drop the selector's replicate-sign bits
-#endif
-    return (v + s) ^ s;
-}
-GVC_HD unsigned max_pair(unsigned v) {    // low half: max(lo, hi) of clean unsigned halves; high half: hi
-#if defined(GVC_EMU)
-    const unsigned lo = v & 0xffffu, hi = v >> 16;
-    return (hi << 16) | (lo > hi ? lo : hi);
-#else
-    return __vmaxu2(v, v >> 16);
-#endif
-}
 
 // ------------------------------------------------------------------ se(v) bit count ------------
 GVC_HD int se_bits(int v) {   // 2 * floor(log2(codeNum + 1)) + 1 with codeNum = 2|v| - (v > 0): floor(log2) = bit length of |v|
@@ -742,21 +725,28 @@ GVC_HD void me_lane_block(int lane, int &P, int &ox, int &oy) {
     if (lane < 16) { P = 0; ox = 4 * (lane & 3); oy = 4 * (lane >> 2); }
     else { const int l = lane - 16, k = l >> 2, j = l & 3; P = 1 + k; ox = 8 * (k & 1) + 4 * (j & 1); oy = 8 * (k >> 1) + 4 * (j >> 1); }
 }
-// Half the 4x4 Hadamard magnitude sum of (source - w): ca/cb hold the source rows' samples (0,2) / (1,3).  Vertical
-// butterflies run on both halves at once, the horizontal pair (0,2)+-(1,3) between registers, and the last stage
-// through |p + q| + |p - q| = 2 max(|p|, |q|).
-GVC_HD int satd4x4_rows(const unsigned ca[4], const unsigned cb[4], const unsigned w[4]) {
-    unsigned A[4], B[4];
-    for (int j = 0; j < 4; ++j) { A[j] = ca[j] - pack_even(w[j]); B[j] = cb[j] - pack_odd(w[j]); }
-    {
-        const unsigned t0 = A[0] + A[1], t1 = A[0] - A[1], t2 = A[2] + A[3], t3 = A[2] - A[3];
-        A[0] = t0 + t2; A[1] = t1 + t3; A[2] = t0 - t2; A[3] = t1 - t3;
-        const unsigned u0 = B[0] + B[1], u1 = B[0] - B[1], u2 = B[2] + B[3], u3 = B[2] - B[3];
-        B[0] = u0 + u2; B[1] = u1 + u3; B[2] = u0 - u2; B[3] = u1 - u3;
+// Half the 4x4 Hadamard magnitude sum of (w - source).  The horizontal transform of a row of four samples is four dp4a
+// with +-1 patterns (FMA pipe: the integer ALU pipe is the busy one in these kernels), started from the negated transform
+// of the source row (hc, computed once per macroblock), so the subtraction is free.  Vertical: one butterfly stage, the last
+// one through |p + q| + |p - q| = 2 max(|p|, |q|).
+constexpr int kHad0 = 0x01010101, kHad1 = (int)0xffff0101, kHad2 = 0x01ffff01, kHad3 = (int)0xff01ff01;   // (1,1,1,1) (1,1,-1,-1) (1,-1,-1,1) (1,-1,1,-1)
+GVC_HD void had_row_neg(unsigned w, int out[4]) {     // minus the horizontal Hadamard transform of four samples
+    out[0] = -dp4a_us(w, kHad0, 0); out[1] = -dp4a_us(w, kHad1, 0); out[2] = -dp4a_us(w, kHad2, 0); out[3] = -dp4a_us(w, kHad3, 0);
+}
+GVC_HD int satd4x4_rows(const int hc[16], const unsigned w[4]) {
+    int t[16];
+    for (int j = 0; j < 4; ++j) {
+        t[4 * j]     = dp4a_us(w[j], kHad0, hc[4 * j]);
+        t[4 * j + 1] = dp4a_us(w[j], kHad1, hc[4 * j + 1]);
+        t[4 * j + 2] = dp4a_us(w[j], kHad2, hc[4 * j + 2]);
+        t[4 * j + 3] = dp4a_us(w[j], kHad3, hc[4 * j + 3]);
     }
-    unsigned acc = 0;
-    for (int j = 0; j < 4; ++j) acc += max_pair(abs_pair(A[j] + B[j])) + max_pair(abs_pair(A[j] - B[j]));
-    return (int)(acc & 0xffffu);
+    int acc = 0;
+    for (int k = 0; k < 4; ++k) {
+        const int s0 = t[k] + t[4 + k], s1 = t[k] - t[4 + k], s2 = t[8 + k] + t[12 + k], s3 = t[8 + k] - t[12 + k];
+        acc += imax(iabs(s0), iabs(s2)) + imax(iabs(s1), iabs(s3));
+    }
+    return acc;
 }
 // Per-lane state that stays in registers across the 17 sub-pel candidates: the lane's 4x4 source block, its offset in
 // the planes, the predictor, and the running best / search centre of the lane's partition (every lane of a partition
@@ -765,7 +755,7 @@ GVC_HD int satd4x4_rows(const unsigned ca[4], const unsigned cb[4], const unsign
 struct MeLane {
     int       P, px, py;
     int       base;      // (16*my + oy) * stride + 16*mx + ox
-    unsigned  ca[4], cb[4];
+    int       hc[16];    // minus the horizontal Hadamard transform of the lane's four source rows
     int       cx, cy, bx, by, bcost;
 };
 GVC_HD void me_lane_init(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm, MeLane &L) {
@@ -776,7 +766,7 @@ GVC_HD void me_lane_init(int lane, const MeRefArgs &a, int mx, int my, const MeR
     for (int j = 0; j < 4; ++j) {
         const gvc_uint4 r = sm.cur[oy + j];
         const unsigned w = ox == 0 ? r.x : ox == 4 ? r.y : ox == 8 ? r.z : r.w;
-        L.ca[j] = pack_even(w); L.cb[j] = pack_odd(w);
+        had_row_neg(w, L.hc + 4 * j);
     }
     L.cx = L.bx = sm.center[L.P][0];
     L.cy = L.by = sm.center[L.P][1];
@@ -800,7 +790,7 @@ GVC_HD int me_ref_satd(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L,
         const uint8_t *p2 = sm.plane[(kQpelRef1 >> (2 * q)) & 3] + (off + (fx == 3 ? 1 : 0));
         for (int j = 0; j < 4; ++j, p1 += a.stride, p2 += a.stride) w[j] = avg_u8x4(ld_u32_any(p1), ld_u32_any(p2));
     }
-    return satd4x4_rows(L.ca, L.cb, w);
+    return satd4x4_rows(L.hc, w);
 }
 // `total` = SATD of the lane's whole partition for this candidate (sum of its lanes' partials).  Keeps the best; after the
 // last candidate of a step the best becomes the next search centre.
