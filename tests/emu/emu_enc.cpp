@@ -55,6 +55,32 @@ void emu_run_me_refine(const MeRefArgs &a) {
             for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) me_ref_pick(l, a, mx, my, sm);
             MeLane L[32];
+            if (me_ref_one_partition(sm)) {                 // the warp's one-partition path, shuffles spelled out
+                for (int l = 0; l < 32; ++l) me_fast_init(l, a, mx, my, sm, L[l]);
+                unsigned key[32];
+                int kx[32], ky[32];
+                for (int l = 0; l < 32; ++l) { key[l] = 0xffffffffu; kx[l] = L[l].cx; ky[l] = L[l].cy; }
+                for (int step = 2; step >= 1; --step) {
+                    for (int r = 0; r < (step == 2 ? 5 : 4); ++r) {
+                        int part[32];
+                        for (int l = 0; l < 32; ++l) { const int ci = me_fast_cand(l, r, step); part[l] = ci < 8 ? me_ref_satd(a, sm, L[l], ci, step) : 0; }
+                        for (int l = 0; l < 32; ++l) {
+                            int total = 0;
+                            for (int i = 0; i < 16; ++i) total += part[(l & 16) + i];
+                            const int ci = me_fast_cand(l, r, step);
+                            if (ci < 8) me_fast_take(a, L[l], total, ci, step, key[l], kx[l], ky[l]);
+                        }
+                    }
+                    for (int l = 0; l < 16; ++l) {
+                        const int w = key[l + 16] < key[l] ? l + 16 : l;
+                        const unsigned k = key[w] & ~15u;
+                        const int x = kx[w], y = ky[w];
+                        for (int h = 0; h < 2; ++h) { key[l + 16 * h] = k; kx[l + 16 * h] = x; ky[l + 16 * h] = y; L[l + 16 * h].cx = x; L[l + 16 * h].cy = y; }
+                    }
+                }
+                for (int l = 0; l < 32; ++l) me_fast_out(l, a, mx, my, key[l], kx[l], ky[l]);
+                continue;
+            }
             for (int l = 0; l < 32; ++l) me_lane_init(l, a, mx, my, sm, L[l]);
             for (int step = 2; step >= 1; --step)
                 for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
