@@ -195,8 +195,8 @@ typedef struct gvc_encoder_config {
 
 int  gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg);
 void gvc_encoder_destroy(gvc_encoder *enc);
-/* One segment from HOST memory: n_frames I420 pictures.  Copies in, runs every kernel, copies the per-macroblock
- * records back, entropy-codes them.  If out != NULL it receives a malloc'ed stream (gvc_free): Annex B when annexb != 0,
+/* One segment from HOST memory: n_frames I420 pictures.  Copies in, runs every kernel (entropy coding included unless
+ * cfg.entropy = GVC_ENTROPY_HOST, in which case host threads code the records the kernels send back).  If out != NULL it receives a malloc'ed stream (gvc_free): Annex B when annexb != 0,
  * else 4-byte length-prefixed NAL units (the MP4 sample format). */
 int gvc_encoder_encode_host(gvc_encoder *enc, const uint8_t *frames_i420, int n_frames, int annexb, uint8_t **out, size_t *out_len);
 /* The three steps of gvc_encoder_encode_host, separately, so a caller can upload segment n+1 while segment n is being
@@ -209,7 +209,8 @@ int gvc_encoder_encode_uploaded(gvc_encoder *enc);
 int gvc_encoder_encode_device(gvc_encoder *enc, const uint8_t *d_frames_i420, int n_frames);
 int gvc_encoder_sync(gvc_encoder *enc);
 void *gvc_encoder_stream(gvc_encoder *enc);      /* the cudaStream_t the encoder launches on */
-/* Completes a segment started with gvc_encoder_encode_device: D2H of the records + entropy coding. */
+/* Completes a segment started with gvc_encoder_encode_device / _encode_uploaded: waits for the slices (or entropy-codes the
+ * records on host threads), wraps them into NAL units.  GVC_ERR_TOO_LARGE if the slices outgrew twice the raw pictures. */
 int gvc_encoder_finish(gvc_encoder *enc, int annexb, uint8_t **out, size_t *out_len);
 /* keep_recon: the coded-size (multiples of 16) I420 reconstruction of every picture of the last segment. */
 int gvc_encoder_recon(gvc_encoder *enc, uint8_t *dst, size_t cap);
@@ -222,7 +223,7 @@ int gvc_encoder_stats(gvc_encoder *enc, int *stats4_per_picture, int n_pictures)
 #define GVC_STAGES 9
 int gvc_encoder_set_timing(gvc_encoder *enc, int on);
 int gvc_encoder_stage_times(gvc_encoder *enc, double *ms, int *launches);
-/* Bytes the last finished segment sent device -> host (packed nonzero blocks + per-macroblock tables). */
+/* Bytes the last finished segment sent device -> host (finished slices, or packed nonzero blocks + per-macroblock tables). */
 long long gvc_encoder_record_bytes(gvc_encoder *enc);
 /* Muxes the last segment into an MP4 file (temp name + rename). */
 int gvc_encoder_write_mp4(gvc_encoder *enc, const char *path);
@@ -230,7 +231,8 @@ int gvc_encoder_write_mp4(gvc_encoder *enc, const char *path);
 /* THE drop-in for client.go:115 `exec.Command("ffmpeg", "-i", in_path, args..., out_path)`: ffmpeg_args is the
  * third field of the job string (server.go:179) verbatim.  On success out_path exists; on ANY failure it does not
  * (the reference detects failure by the missing file, client.go:163-167).  *log_out (gvc_free) is the text the
- * reference writes to c<id>.mp4.log (client.go:120-123).  Input container in this build: YUV4MPEG2. */
+ * reference writes to c<id>.mp4.log (client.go:120-123).  Input containers: YUV4MPEG2 natively, anything libavformat reads
+ * (MP4 / H.264 pieces as the reference's splitter makes them) when FFmpeg's libraries can be dlopen'ed (GVC_FFMPEG_LIBDIR). */
 int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char *out_path, char **log_out, size_t *log_len);
 
 #ifdef __cplusplus
