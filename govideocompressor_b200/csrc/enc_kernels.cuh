@@ -74,6 +74,16 @@ GVC_HD unsigned avg_u8x4(unsigned a, unsigned b) {   // per byte (a + b + 1) >> 
     return __vavgu4(a, b);
 #endif
 }
+GVC_HD unsigned byte_sel(unsigned a, unsigned b, unsigned sel) {   // prmt.b32 without the replicate-sign modes
+#if defined(GVC_EMU)
+    const unsigned long long ab = ((unsigned long long)b << 32) | a;
+    unsigned r = 0;
+    for (int i = 0; i < 4; ++i) r |= (unsigned)((ab >> (8 * ((sel >> (4 * i)) & 7))) & 255) << (8 * i);
+    return r;
+#else
+    return __byte_perm(a, b, sel);
+#endif
+}
 GVC_HD int byte_of(unsigned w, int i) {
 #if defined(GVC_EMU)
     return (int)((w >> (8 * i)) & 255);
@@ -218,6 +228,29 @@ GVC_HD void lowres_px(const uint8_t *src, int sstride, int x_lo, int x_hi, int y
     if (dc) dc[o] = (uint8_t)avg4(v[1][1], v[2][1], v[1][2], v[2][2]);
 }
 
+// Four phase-0 lowres samples lx .. lx+3 of row ly in one go.  avg4 is two nested rounding averages, so on packed bytes it
+// is vavg(vavg(top, bottom) of the even columns, vavg(top, bottom) of the odd columns): 4 word loads, 4 byte selects, 3
+// averages, 1 word store.  Word path when planes / pitches are multiples of four and the eight source columns need no
+// clamping; otherwise sample by sample through lowres_px (same results).
+GVC_HDH bool lowres_aligned(const LowresBatchArgs &a) {
+    return (((unsigned long long)a.src | (unsigned long long)a.dst | (unsigned long long)(unsigned)a.sstride | (unsigned long long)(unsigned)a.dstride |
+             a.sframe | a.dframe | (unsigned long long)(unsigned)a.lx_lo) & 3) == 0;
+}
+GVC_HD void lowres_quad(const LowresBatchArgs &a, bool al, const uint8_t *src, uint8_t *dst, int lx, int ly) {
+    if (al && lx + 4 <= a.lx_hi && 2 * lx >= a.x_lo && 2 * lx + 7 <= a.x_hi) {
+        const uint8_t *r0 = src + (iclamp(2 * ly, a.y_lo, a.y_hi) * a.sstride + 2 * lx);
+        const uint8_t *r1 = src + (iclamp(2 * ly + 1, a.y_lo, a.y_hi) * a.sstride + 2 * lx);
+        const unsigned t0 = *reinterpret_cast<const unsigned *>(r0), t1 = *reinterpret_cast<const unsigned *>(r0 + 4);
+        const unsigned b0 = *reinterpret_cast<const unsigned *>(r1), b1 = *reinterpret_cast<const unsigned *>(r1 + 4);
+        const unsigned even = avg_u8x4(byte_sel(t0, t1, 0x6420), byte_sel(b0, b1, 0x6420));
+        const unsigned odd  = avg_u8x4(byte_sel(t0, t1, 0x7531), byte_sel(b0, b1, 0x7531));
+        *reinterpret_cast<unsigned *>(dst + (ly * a.dstride + lx)) = avg_u8x4(even, odd);
+        return;
+    }
+    for (int i = 0; i < 4; ++i)
+        if (lx + i < a.lx_hi) lowres_px(src, a.sstride, a.x_lo, a.x_hi, a.y_lo, a.y_hi, dst, nullptr, nullptr, nullptr, a.dstride, lx + i, ly);
+}
+
 // ------------------------------------------------------------------ K2 half-sample planes -------
 // One CTA per 64x32 tile; four samples per work item.  Phase A stages the source tile (with a 4-sample apron, replicated
 // at the region edge) in shared memory as words.  Phase B runs the vertical 6-tap on two samples per register (sum2
@@ -237,16 +270,6 @@ GVC_HD unsigned funnel_r(unsigned lo, unsigned hi, int bits) {     // (hi:lo) >>
     return (unsigned)((((unsigned long long)hi << 32) | lo) >> bits);
 #else
     return __funnelshift_r(lo, hi, (unsigned)bits);
-#endif
-}
-GVC_HD unsigned byte_sel(unsigned a, unsigned b, unsigned sel) {   // prmt.b32 without the replicate-sign modes
-#if defined(GVC_EMU)
-    const unsigned long long ab = ((unsigned long long)b << 32) | a;
-    unsigned r = 0;
-    for (int i = 0; i < 4; ++i) r |= (unsigned)((ab >> (8 * ((sel >> (4 * i)) & 7))) & 255) << (8 * i);
-    return r;
-#else
-    return __byte_perm(a, b, sel);
 #endif
 }
 GVC_HD int dp4a_us(unsigned pix, int coef, int acc) {    // acc + sum of pix.b[i] (unsigned) * coef.b[i] (signed)

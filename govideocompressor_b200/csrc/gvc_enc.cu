@@ -36,10 +36,9 @@ __global__ void __launch_bounds__(256) extend_border16_batch_kernel(const __grid
 }
 
 __global__ void __launch_bounds__(256) lowres_batch_kernel(const __grid_constant__ LowresBatchArgs a) {
-    const int lx = a.lx_lo + blockIdx.x * 256 + threadIdx.x, ly = a.ly_lo + blockIdx.y;
+    const int lx = a.lx_lo + 4 * (blockIdx.x * 256 + threadIdx.x), ly = a.ly_lo + blockIdx.y;      // four samples per thread
     if (lx < a.lx_hi && ly < a.ly_hi)
-        lowres_px(a.src + (size_t)blockIdx.z * a.sframe, a.sstride, a.x_lo, a.x_hi, a.y_lo, a.y_hi, a.dst + (size_t)blockIdx.z * a.dframe,
-                  nullptr, nullptr, nullptr, a.dstride, lx, ly);
+        lowres_quad(a, lowres_aligned(a), a.src + (size_t)blockIdx.z * a.sframe, a.dst + (size_t)blockIdx.z * a.dframe, lx, ly);
 }
 
 __global__ void __launch_bounds__(kHpThreads) hpel_kernel(const __grid_constant__ HpelArgs a) {
@@ -225,7 +224,7 @@ int launch_lowres_batch(const LowresBatchArgs &a, cudaStream_t st) {
         LowresBatchArgs b = a;
         b.n_frames = a.n_frames - f0 < 32768 ? a.n_frames - f0 : 32768;
         b.src = a.src + (size_t)f0 * a.sframe; b.dst = a.dst + (size_t)f0 * a.dframe;
-        lowres_batch_kernel<<<dim3((a.lx_hi - a.lx_lo + 255) / 256, a.ly_hi - a.ly_lo, b.n_frames), 256, 0, st>>>(b);
+        lowres_batch_kernel<<<dim3((a.lx_hi - a.lx_lo + 1023) / 1024, a.ly_hi - a.ly_lo, b.n_frames), 256, 0, st>>>(b);
         GVC_CUDA(cudaGetLastError());
     }
     return GVC_OK;

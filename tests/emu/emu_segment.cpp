@@ -52,10 +52,12 @@ struct EmuOps {
             }
         return 0;
     }
-    int lowres_batch(const LowresBatchArgs &a) {
+    int lowres_batch(const LowresBatchArgs &a) {        // the kernel's thread decomposition: four samples per thread
+        const bool al = lowres_aligned(a);
         for (int f = 0; f < a.n_frames; ++f)
-            emu_lowres(a.src + size_t(f) * a.sframe, a.sstride, a.x_lo, a.x_hi + 1, a.y_lo, a.y_hi + 1, a.dst + size_t(f) * a.dframe, nullptr, nullptr,
-                       nullptr, a.dstride, a.lx_lo, a.lx_hi, a.ly_lo, a.ly_hi);
+            for (int ly = a.ly_lo; ly < a.ly_hi; ++ly)
+                for (int lx = a.lx_lo; lx < a.lx_hi; lx += 4)
+                    lowres_quad(a, al, a.src + size_t(f) * a.sframe, a.dst + size_t(f) * a.dframe, lx, ly);
         return 0;
     }
     int hpel(const HpelArgs &a) { emu_run_hpel(a); return 0; }
