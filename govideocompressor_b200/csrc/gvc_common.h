@@ -17,6 +17,10 @@ bool initialised();
 // SURVEY.md 8b) and returns GVC_OK or an error status.
 int enter();
 
+// gvc_resize.cu: resolves the device address of the built-in scratch array of gvc_resize_frames_device_static() on
+// device `dev` (which must be current).  gvc_init() calls it so the module load and the reservation happen at start-up.
+int resize_static_prepare(int dev);
+
 #define GVC_CUDA(call)                                                                              \
     do {                                                                                            \
         cudaError_t e__ = (call);                                                                   \

@@ -56,6 +56,9 @@ int gvc_init(int device_ordinal) {
         return GVC_ERR_UNSUPPORTED;
     }
     GVC_CUDA(cudaFree(0));
+    // start-up is the time to reserve fixed device memory: the built-in scratch of gvc_resize_frames_device_static()
+    int rc = resize_static_prepare(device_ordinal);
+    if (rc) return rc;
     g_device = device_ordinal;
     return GVC_OK;
 }

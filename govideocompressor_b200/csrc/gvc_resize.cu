@@ -407,10 +407,13 @@ int gvc_resize_frames_host(gvc_resize_plan *p, const gvc_frames *src, const gvc_
 // performs no allocation of any kind: no cudaMalloc/cudaFree, no allocating library call.
 //
 // The price is a fixed ceiling.  The array below occupies kStaticScratchBytes of device memory on
-// every GPU that loads libgvc.so, from load until the process exits, whether or not this entry
-// point is ever called.  A frame needs 2 * (src_h * dst_w + 2 * ceil(src_h/2) * ceil(dst_w/2))
-// bytes of it (4.1 MB for 1080p->720p, 12.4 MB for 2160p->1080p); frames are processed in groups
-// that fit, and a plan whose single frame does not fit is rejected with GVC_ERR_TOO_LARGE.
+// the GPU gvc_init() selects, from gvc_init() until the process exits, whether or not this entry
+// point is ever called.  (CUDA loads a module's device image lazily, at the first use of anything
+// in it; gvc_init() asks for the array's address so that this happens -- and the 16 MiB are
+// reserved, or found to be unavailable -- during start-up and not inside the first steady-state
+// call.)  A frame needs 2 * (src_h * dst_w + 2 * ceil(src_h/2) * ceil(dst_w/2)) bytes of it (4.1 MB
+// for 1080p->720p, 12.4 MB for 2160p->1080p); frames are processed in groups that fit, and a plan
+// whose single frame does not fit is rejected with GVC_ERR_TOO_LARGE.
 namespace {
 
 constexpr size_t kStaticScratchBytes = size_t(16) << 20;   // 16 MiB, the stated maximum
@@ -422,20 +425,28 @@ constexpr int kMaxDevices = 64;
 int16_t   *g_static_scratch_addr[kMaxDevices] = {};
 std::mutex g_static_scratch_mutex;
 
-int static_scratch_address(int16_t **out) {
-    const int dev = gvc::current_device();
+int static_scratch_address(int dev, int16_t **out) {     // `dev` must be the current device
     if (dev < 0 || dev >= kMaxDevices) { set_error("device ordinal %d outside the supported range 0..%d", dev, kMaxDevices - 1); return GVC_ERR_INVALID_ARG; }
     std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
     if (!g_static_scratch_addr[dev]) {
         void *p = nullptr;
-        GVC_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));   // enter() made `dev` current
+        GVC_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        // the two kernels the entry point launches are loaded now as well (lazy loading would otherwise do it, with
+        // whatever bookkeeping memory that takes, inside the first call)
+        cudaFuncAttributes fa;
+        GVC_CUDA(cudaFuncGetAttributes(&fa, gvc::resize_hpass_kernel));
+        GVC_CUDA(cudaFuncGetAttributes(&fa, gvc::resize_vpass_kernel));
         g_static_scratch_addr[dev] = static_cast<int16_t *>(p);
     }
-    *out = g_static_scratch_addr[dev];
+    if (out) *out = g_static_scratch_addr[dev];
     return GVC_OK;
 }
 
 }  // namespace
+
+// Called by gvc_init() with the selected device current: loads this file's device image (which reserves the array)
+// and remembers the array's address, so gvc_resize_frames_device_static() itself never triggers either.
+int gvc::resize_static_prepare(int dev) { return static_scratch_address(dev, nullptr); }
 
 extern "C" int gvc_resize_frames_device_static(const gvc_resize_plan *p, const gvc_frames *src, const gvc_frames *dst,
                                                int n_frames, void *stream) {
@@ -472,8 +483,8 @@ extern "C" int gvc_resize_frames_device_static(const gvc_resize_plan *p, const g
         return GVC_ERR_TOO_LARGE;
     }
     if (n_frames == 0) return GVC_OK;
-    int16_t *scratch = nullptr;
-    if ((rc = static_scratch_address(&scratch))) return rc;
+    int16_t *scratch = nullptr;      // resolved by gvc_init(); the lookup below only reads the remembered address
+    if ((rc = static_scratch_address(gvc::current_device(), &scratch))) return rc;
 
     // Nothing in the scratch has to start at zero: the horizontal pass writes every element the
     // vertical pass reads (all src_h x dst_w samples of each plane), so whatever an earlier call left

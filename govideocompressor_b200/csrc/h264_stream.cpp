@@ -1,7 +1,8 @@
 // h264_stream.cpp -- see h264_stream.h.  Tables are those of ITU-T H.264 (Table 9-4 coded_block_pattern
 // mapping, Table 9-5 coeff_token, Tables 9-7/9-8/9-9 total_zeros, Table 9-10 run_before), stored as
-// (length, bits) pairs; tests/test_h264_stream.py checks each one is a prefix-free code and that a real
-// decoder (FFmpeg's h264) reproduces the kernels' reconstruction from the streams written here.
+// (length, bits) pairs; tests/test_emu_entropy.py checks that the GPU writer's phases give the same bytes, and
+// tests/test_tier3_decode.py that a real decoder (FFmpeg's h264) reproduces the kernels' reconstruction from the
+// streams written here (noise at QP 0..30 exercises every table).
 #include "h264_stream.h"
 
 #include <algorithm>

@@ -97,10 +97,10 @@ int gvc_resize_frames_host(gvc_resize_plan *plan, const gvc_frames *src, const g
  * neighbouring segments) and for GPUs whose memory is fully budgeted at start-up (a late allocation could
  * fail after the job was accepted; server.go:276-283 never re-queues a failed piece).
  *   - Limit: one frame needs 2*(src_h*dst_w + 2*ceil(src_h/2)*ceil(dst_w/2)) bytes of the array (4.1 MB for
- *     1080p->720p, 12.4 MB for 2160p->1080p); larger plans return GVC_ERR_TOO_LARGE.  The 16 MiB are held on
- *     every GPU that loads libgvc.so until the process exits.
- *   - The first call on a device looks up the array's device address (one cudaGetSymbolAddress); make that
- *     first call before starting any stream capture.
+ *     1080p->720p, 12.4 MB for 2160p->1080p); larger plans return GVC_ERR_TOO_LARGE.
+ *   - The 16 MiB are reserved by gvc_init() on the GPU it selects (it looks the array's device address up, which
+ *     also makes CUDA load the code that holds it) and stay reserved until the process exits; if they cannot be
+ *     had, gvc_init() fails.  The entry point itself does no set-up on its first call.
  *   - All calls share the one array: calls whose kernels can overlap on the GPU (different streams, or
  *     several host threads) race on it.  Serialise them on one stream.  Nothing in the array needs clearing
  *     between calls; every element read has been written earlier in the same call. */
@@ -174,7 +174,8 @@ int gvc_lambda_for_qp(int qp);
 /* ---------------------------------------------------------------- segment encoder ------------- */
 /* Replaces: what one spawned `ffmpeg -i <id>.mp4 <args> c<id>.mp4` does for one piece (client.go:101-130):
  * resize, H.264 encode (IDR + P pictures, closed GOP per call), container.  Kernels run on the library's own
- * stream for the encoder; entropy coding (CAVLC) and muxing run on host threads (north_star keeps them on the host). */
+ * streams for the encoder; the CAVLC slice data is written by the entropy kernels by default or by
+ * host threads with cfg.entropy = GVC_ENTROPY_HOST (north_star's first wording); NAL wrapping and muxing run on the host. */
 typedef struct gvc_encoder gvc_encoder;
 
 typedef struct gvc_encoder_config {

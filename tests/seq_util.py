@@ -44,3 +44,27 @@ def split_i420(frame, w, h):
 def psnr(a, b):
     mse = np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2)
     return 99.0 if mse == 0 else 10 * np.log10(255.0 ** 2 / mse)
+
+
+def parameter_sets(annexb):
+    """(SPS bytes, PPS bytes) of an Annex B stream: the first NAL units of type 7 and 8, start codes stripped."""
+    b, found = bytes(annexb), {}
+    i = b.find(b"\x00\x00\x01")
+    while i >= 0:
+        j = b.find(b"\x00\x00\x01", i + 3)
+        nal = b[i + 3: (j - 1 if j > 0 and b[j - 1] == 0 else j) if j >= 0 else len(b)]
+        if nal and (nal[0] & 31) in (7, 8):
+            found.setdefault(nal[0] & 31, nal)
+        i = j
+    return found.get(7), found.get(8)
+
+
+def write_concat_list(directory, names):
+    """filelist.txt as server.go:325-347 writes it (`file 'N.mp4'` lines).  The operator's concat.sh (server.go:357) names the
+    demuxer with `-f concat`; a library caller gets the same demuxer by probing, which needs the format's header line."""
+    path = directory + "/filelist.txt"
+    with open(path, "w") as f:
+        f.write("ffconcat version 1.0\n")
+        for n in names:
+            f.write("file '%s'\n" % n)
+    return path

@@ -94,3 +94,28 @@ def test_mp4_container_opens_and_counts_frames(tmp_path):
         np.testing.assert_array_equal(fr.reshape(h, w), ry[:h, :w])     # raw luma straight from the container path
         k += 1
     assert k == n
+
+
+@pytest.mark.skipif(emu_lib.ffmpeg_libdir() is None, reason="no FFmpeg shared libraries in this image")
+def test_concatenated_segments_decode_to_every_reconstruction(tmp_path):
+    """What the operator's concat.sh does with the workers' results (server.go:357 `ffmpeg -f concat -i filelist.txt -c copy`):
+    three independently encoded segments carry byte-identical SPS / PPS, and FFmpeg's concat demuxer + h264 decoder return
+    every picture of every segment equal to that segment's reconstruction."""
+    w, h, n, pieces = 150, 100, 5, 3
+    res = []
+    for i in range(pieces):
+        frames = S.moving_sequence(w, h, n + i, seed=30 + i, noise=1)
+        res.append(emu_lib.encode_segment(frames, w, h, fps=25, qp_i=22, qp_p=25, mp4_path=os.path.join(tmp_path, f"{i}.mp4")))
+    sets = [S.parameter_sets(r["annexb"]) for r in res]
+    assert sets[0][0] and sets[0][1] and all(s == sets[0] for s in sets), "segments differ in SPS / PPS: stream copy concat would break"
+    info, got = emu_lib.read_media(S.write_concat_list(str(tmp_path), [f"{i}.mp4" for i in range(pieces)]))
+    assert info["frames"] == sum(n + i for i in range(pieces)) and (info["w"], info["h"]) == (w, h)
+    k = 0
+    for i in range(pieces):
+        for f in range(n + i):
+            ry, ru, rv = S.split_i420(res[i]["recon"][f], res[i]["w16"], res[i]["h16"])
+            y, u, v = S.split_i420(got[k], w, h)
+            np.testing.assert_array_equal(y, ry[:h, :w], err_msg=f"segment {i} picture {f}")
+            np.testing.assert_array_equal(u, ru[: h // 2, : w // 2])
+            np.testing.assert_array_equal(v, rv[: h // 2, : w // 2])
+            k += 1

@@ -7,7 +7,12 @@ drops failed pieces for good, server.go:276-283).  For them the library offers a
 plane lives in a fixed 16 MiB array inside the library.  This test calls it through the C ABI and requires
 the very same bytes as the regular entry point gives (our resize tests are bit-exact, so the tolerance is
 zero), twice in a row with different pictures and different plans, because the array is shared by all calls
-and keeps whatever the previous call left in it.  It also checks the documented size limit.
+and keeps whatever the previous call left in it.  The same outputs are also compared with the CPU oracle of
+libswscale (oracle/sws_resize.c, itself pinned to the real library by tests/golden), so the variant is not
+only checked against our own other kernel.  The property the entry point exists for is asserted directly:
+the amount of free device memory (cudaMemGetInfo) is the same before and after each call, the first one
+included -- gvc_init() has already reserved the array and loaded the kernels.  It also checks the documented
+size limit.
 
 The file name makes pytest collect it last; it must pass both on its own and after the other GPU tests.
 """
@@ -46,6 +51,17 @@ def _run_static(plan, src, dst, n):
     return plan._lib.gvc_resize_frames_device_static(plan._h, ctypes.byref(s), ctypes.byref(d), n, ctypes.c_void_p(st))
 
 
+def _oracle_frames(src, sw, sh, dw, dh):
+    """The CPU oracle's resize of every frame of a packed I420 device batch, packed the same way."""
+    import oracle_lib
+    import seq_util as S
+    out = []
+    for fr in src.cpu().numpy():
+        planes = oracle_lib.sws_scale(list(S.split_i420(fr, sw, sh)), sw, sh, dw, dh, "yuv420p", 4)
+        out.append(np.concatenate([p.reshape(-1) for p in planes]))
+    return np.stack(out)
+
+
 def test_static_scratch_variant_matches_regular_entry_point_twice(gvc):
     import torch
     # call 1: 8 frames 640x360 -> 426x240; call 2: a different plan and picture, 3 frames 1920x1080 -> 1280x720
@@ -56,9 +72,14 @@ def test_static_scratch_variant_matches_regular_entry_point_twice(gvc):
         want = torch.zeros((n, plan.frame_bytes(dw, dh)), dtype=torch.uint8, device="cuda")
         got = torch.full_like(want, 0x77)
         plan.resize_device(src, want, n)                  # the existing entry point (fused kernel here)
+        torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info()[0]        # cudaMemGetInfo
         assert _run_static(plan, src, got, n) == 0, plan._lib.gvc_last_error()
         torch.cuda.synchronize()
+        assert torch.cuda.mem_get_info()[0] == free_before, "the allocation-free entry point changed the free device memory"
         assert torch.equal(got, want), "allocation-free variant differs from gvc_resize_frames_device"
+        np.testing.assert_array_equal(got.cpu().numpy(), _oracle_frames(src, sw, sh, dw, dh),
+                                      err_msg="allocation-free variant differs from the libswscale oracle")
         plan.close()
 
 
