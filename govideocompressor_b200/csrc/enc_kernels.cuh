@@ -627,272 +627,9 @@ GVC_HD void me_lowres_out(int lane, const MeLowArgs &a, int mx, int my, unsigned
     a.out_mv[2 * (my * a.mbw + mx) + 1] = (int16_t)(idx / n - a.r);
 }
 
-// ------------------------------------------------------------------ K4b refinement -------------
-// One warp per macroblock.  Phases: load (source rows, predictor and plane table into the warp's shared record) ->
-// 27 integer candidates, one per lane -> pick per partition -> 9 half-sample + 8 quarter-sample SATD candidates with
-// lanes 0..15 on the 16x16 partition and 16..31 on the four 8x8 partitions -> mode decision.
-struct MeRefArgs {
-    const uint8_t *cur;          // source luma (0,0)
-    RefPlanes      ref;
-    int            stride, w16, h16, mbw, mbh, lambda;
-    const int16_t *lowres_mv;
-    MbMotion      *out;
-    MbMotion      *out_host;     // optional second copy of the result (host-mapped memory), or null
-};
-#ifndef GVC_ME_EARLY_MUL
-#define GVC_ME_EARLY_MUL 32
-#endif
-constexpr int kMeEarlyMul = GVC_ME_EARLY_MUL;   // early termination: zero-vector SAD <= kMeEarlyMul * lambda (oracle/h264_mb.c)
-struct MeRefSmem {               // per warp
-    gvc_uint4      cur[16];      // the macroblock's 16 source rows
-    const uint8_t *plane[4];     // full, H, V, C sample planes (mc_luma_src order)
-    unsigned       key[5][32];
-    int            center[5][2], best_mv[5][2], best_cost[5];
-    int            mvp[2], low[2];
-};
-GVC_HD void sq8(int i, int &dx, int &dy) {   // (0,-1),(0,1),(-1,0),(1,0),(-1,-1),(-1,1),(1,-1),(1,1)
-    dx = i < 2 ? 0 : ((i == 2 || i == 4 || i == 5) ? -1 : 1);
-    dy = i == 0 ? -1 : i == 1 ? 1 : (i < 4 ? 0 : ((i & 1) ? 1 : -1));
-}
-GVC_HD void me_mvp(const MeRefArgs &a, int mx, int my, int &px, int &py) {
-    int v[3][2];
-    int nx[3] = {mx - 1, mx, mx + 1}, ny[3] = {my, my - 1, my - 1};
-    if (!(nx[2] < a.mbw && ny[2] >= 0)) { nx[2] = mx - 1; ny[2] = my - 1; }
-    for (int k = 0; k < 3; ++k) {
-        const bool ok = nx[k] >= 0 && nx[k] < a.mbw && ny[k] >= 0 && ny[k] < a.mbh;
-        v[k][0] = ok ? 8 * a.lowres_mv[2 * (ny[k] * a.mbw + nx[k])] : 0;
-        v[k][1] = ok ? 8 * a.lowres_mv[2 * (ny[k] * a.mbw + nx[k]) + 1] : 0;
-    }
-    px = median3(v[0][0], v[1][0], v[2][0]);
-    py = median3(v[0][1], v[1][1], v[2][1]);
-}
-GVC_HD void me_ref_load(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
-    if (lane < 16) {
-        unsigned w[4];
-        ld_u128_any(a.cur + (long long)(16 * my + lane) * a.stride + 16 * mx, w);
-        gvc_uint4 r; r.x = w[0]; r.y = w[1]; r.z = w[2]; r.w = w[3];
-        sm.cur[lane] = r;
-    } else if (lane == 16) {
-        int px, py;
-        me_mvp(a, mx, my, px, py);
-        sm.mvp[0] = px; sm.mvp[1] = py;
-    } else if (lane == 17) {
-        sm.low[0] = a.lowres_mv[2 * (my * a.mbw + mx)];
-        sm.low[1] = a.lowres_mv[2 * (my * a.mbw + mx) + 1];
-    } else if (lane == 18) {
-        sm.plane[0] = a.ref.y; sm.plane[1] = a.ref.hh; sm.plane[2] = a.ref.hv; sm.plane[3] = a.ref.hc;
-    }
-}
-// the lane's share of the 16x16 SAD at the zero vector (two lanes per row): decides the early termination before any
-// candidate is evaluated
-GVC_HD unsigned me_ref_zero_part(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm) {
-    const int row = lane >> 1, half = lane & 1;
-    unsigned r0, r1;
-    ld_u64_any(a.ref.y + ((16 * my + row) * a.stride + 16 * mx + 8 * half), r0, r1);
-    const gvc_uint4 c = sm.cur[row];
-    return half ? sad_u8x4(c.w, r1, sad_u8x4(c.z, r0, 0)) : sad_u8x4(c.y, r1, sad_u8x4(c.x, r0, 0));
-}
-// integer candidate i of the macroblock: 5x5 around twice the lowres vector, the rounded predictor, zero
-GVC_HD void me_int_cand(const MeRefArgs &a, const MeRefSmem &sm, int mx, int my, int i, int &cx, int &cy) {
-    if (i < 25)       { cx = 2 * sm.low[0] + (i % 5) - 2; cy = 2 * sm.low[1] + (i / 5) - 2; }
-    else if (i == 25) { cx = (sm.mvp[0] + 2) >> 2; cy = (sm.mvp[1] + 2) >> 2; }
-    else              { cx = 0; cy = 0; }
-    cx = iclamp(cx, -16 * mx - (kEncPad - 8), a.w16 - 16 * mx - 16 + (kEncPad - 8));
-    cy = iclamp(cy, -16 * my - (kEncPad - 8), a.h16 - 16 * my - 16 + (kEncPad - 8));
-}
-// integer candidates: lane i < 27 evaluates candidate i (four 8x8 SADs)
-GVC_HD void me_ref_int(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
-    for (int k = 0; k < 5; ++k) sm.key[k][lane] = 0xffffffffu;
-    if (lane >= 27) return;
-    int cx, cy;
-    me_int_cand(a, sm, mx, my, lane, cx, cy);
-    const uint8_t *p = a.ref.y + ((16 * my + cy) * a.stride + 16 * mx + cx);
-    unsigned s[4] = {0, 0, 0, 0};
-    for (int j = 0; j < 16; ++j, p += a.stride) {
-        unsigned r[4];
-        ld_u128_any(p, r);
-        const gvc_uint4 c = sm.cur[j];
-        const int k = (j >> 3) * 2;
-        s[k]     = sad_u8x4(c.y, r[1], sad_u8x4(c.x, r[0], s[k]));
-        s[k + 1] = sad_u8x4(c.w, r[3], sad_u8x4(c.z, r[2], s[k + 1]));
-    }
-    const unsigned bits = (unsigned)(a.lambda * mv_bits(4 * cx, 4 * cy, sm.mvp[0], sm.mvp[1]));
-    sm.key[0][lane] = ((s[0] + s[1] + s[2] + s[3] + bits) << 5) | (unsigned)lane;
-    for (int k = 0; k < 4; ++k) sm.key[1 + k][lane] = ((s[k] + bits) << 5) | (unsigned)lane;
-
-    // candidate coordinates are recomputed by the picker from the winning lane id
-}
-// early termination: the zero vector predicts the macroblock well enough; one 16x16 partition, no sub-sample search
-GVC_HD bool me_ref_early(const MeRefArgs &a, int zero_sad) { return zero_sad <= kMeEarlyMul * a.lambda; }
-GVC_HD void me_ref_early_out(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm, int zero_sad) {
-    if (lane != 0) return;
-    MbMotion m;
-    m.mode = 0;
-    m.cost = zero_sad + a.lambda * mv_bits(0, 0, sm.mvp[0], sm.mvp[1]);
-    for (int k = 0; k < 4; ++k) m.mv[k][0] = m.mv[k][1] = 0;
-    m.pad[0] = m.pad[1] = m.pad[2] = 0;
-    a.out[my * a.mbw + mx] = m;
-    if (a.out_host) a.out_host[my * a.mbw + mx] = m;
-}
-GVC_HD void me_ref_pick(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
-    if (lane >= 5) return;
-    unsigned best = sm.key[lane][0];
-    for (int i = 1; i < 27; ++i) best = sm.key[lane][i] < best ? sm.key[lane][i] : best;
-    int cx, cy;
-    me_int_cand(a, sm, mx, my, (int)(best & 31), cx, cy);
-    sm.center[lane][0] = 4 * cx;
-    sm.center[lane][1] = 4 * cy;
-}
-// lane -> (partition P, 4x4 block offset inside the MB): lanes 0..15 the 16x16 partition, 16..31 the four 8x8s
-GVC_HD void me_lane_block(int lane, int &P, int &ox, int &oy) {
-    if (lane < 16) { P = 0; ox = 4 * (lane & 3); oy = 4 * (lane >> 2); }
-    else { const int l = lane - 16, k = l >> 2, j = l & 3; P = 1 + k; ox = 8 * (k & 1) + 4 * (j & 1); oy = 8 * (k >> 1) + 4 * (j >> 1); }
-}
-// Half the 4x4 Hadamard magnitude sum of (w - source).  The horizontal transform of a row of four samples is four dp4a
-// with +-1 patterns (FMA pipe: the integer ALU pipe is the busy one in these kernels), started from the negated transform
-// of the source row (hc, computed once per macroblock), so the subtraction is free.  Vertical: one butterfly stage, the last
-// one through |p + q| + |p - q| = 2 max(|p|, |q|).
-constexpr int kHad0 = 0x01010101, kHad1 = (int)0xffff0101, kHad2 = 0x01ffff01, kHad3 = (int)0xff01ff01;   // (1,1,1,1) (1,1,-1,-1) (1,-1,-1,1) (1,-1,1,-1)
-GVC_HD void had_row_neg(unsigned w, int out[4]) {     // minus the horizontal Hadamard transform of four samples
-    out[0] = -dp4a_us(w, kHad0, 0); out[1] = -dp4a_us(w, kHad1, 0); out[2] = -dp4a_us(w, kHad2, 0); out[3] = -dp4a_us(w, kHad3, 0);
-}
-GVC_HD int satd4x4_rows(const int hc[16], const unsigned w[4]) {
-    int t[16];
-    for (int j = 0; j < 4; ++j) {
-        t[4 * j]     = dp4a_us(w[j], kHad0, hc[4 * j]);
-        t[4 * j + 1] = dp4a_us(w[j], kHad1, hc[4 * j + 1]);
-        t[4 * j + 2] = dp4a_us(w[j], kHad2, hc[4 * j + 2]);
-        t[4 * j + 3] = dp4a_us(w[j], kHad3, hc[4 * j + 3]);
-    }
-    int acc = 0;
-    for (int k = 0; k < 4; ++k) {
-        const int s0 = t[k] + t[4 + k], s1 = t[k] - t[4 + k], s2 = t[8 + k] + t[12 + k], s3 = t[8 + k] - t[12 + k];
-        acc += imax(iabs(s0), iabs(s2)) + imax(iabs(s1), iabs(s3));
-    }
-    return acc;
-}
-// Per-lane state that stays in registers across the 17 sub-pel candidates: the lane's 4x4 source block, its offset in
-// the planes, the predictor, and the running best / search centre of the lane's partition (every lane of a partition
-// carries the same best: no shared-memory round trip or leader election per candidate).  The emulation harness keeps one
-// record per lane.
-struct MeLane {
-    int       P, px, py;
-    int       base;      // (16*my + oy) * stride + 16*mx + ox
-    int       hc[16];    // minus the horizontal Hadamard transform of the lane's four source rows
-    int       cx, cy, bx, by, bcost;
-};
-GVC_HD void me_lane_init(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm, MeLane &L) {
-    int ox, oy;
-    me_lane_block(lane, L.P, ox, oy);
-    L.px = sm.mvp[0]; L.py = sm.mvp[1];
-    L.base = (16 * my + oy) * a.stride + 16 * mx + ox;
-    for (int j = 0; j < 4; ++j) {
-        const gvc_uint4 r = sm.cur[oy + j];
-        const unsigned w = ox == 0 ? r.x : ox == 4 ? r.y : ox == 8 ? r.z : r.w;
-        had_row_neg(w, L.hc + 4 * j);
-    }
-    L.cx = L.bx = sm.center[L.P][0];
-    L.cy = L.by = sm.center[L.P][1];
-    L.bcost = 0x7fffffff;
-}
-// sub-pel candidate ci (-1 = the centre itself) at `step`: the lane's 4x4 Hadamard sum (already halved).  step 2 starts
-// from a full-sample centre, so its candidates read one plane chosen by ci alone; every step 1 candidate has an odd
-// component and averages two planes (mc_luma_src).
-GVC_HD int me_ref_satd(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L, int ci, int step) {
-    int dx = 0, dy = 0;
-    if (ci >= 0) sq8(ci, dx, dy);
-    const int mvx = L.cx + dx * step, mvy = L.cy + dy * step;
-    const int off = L.base + (mvy >> 2) * a.stride + (mvx >> 2);
-    unsigned w[4];
-    if (step == 2) {
-        const uint8_t *p = (dx ? (dy ? a.ref.hc : a.ref.hh) : (dy ? a.ref.hv : a.ref.y)) + off;
-        for (int j = 0; j < 4; ++j, p += a.stride) w[j] = ld_u32_any(p);
-    } else {
-        const int fx = mvx & 3, fy = mvy & 3, q = fy * 4 + fx;
-        const uint8_t *p1 = sm.plane[(kQpelRef0 >> (2 * q)) & 3] + (off + (fy == 3 ? a.stride : 0));
-        const uint8_t *p2 = sm.plane[(kQpelRef1 >> (2 * q)) & 3] + (off + (fx == 3 ? 1 : 0));
-        for (int j = 0; j < 4; ++j, p1 += a.stride, p2 += a.stride) w[j] = avg_u8x4(ld_u32_any(p1), ld_u32_any(p2));
-    }
-    return satd4x4_rows(L.hc, w);
-}
-// `total` = SATD of the lane's whole partition for this candidate (sum of its lanes' partials).  Keeps the best; after the
-// last candidate of a step the best becomes the next search centre.
-GVC_HD void me_ref_take(const MeRefArgs &a, MeLane &L, int total, int ci, int step) {
-    int dx = 0, dy = 0;
-    if (ci >= 0) sq8(ci, dx, dy);
-    const int mvx = L.cx + dx * step, mvy = L.cy + dy * step;
-    const int cost = total + a.lambda * mv_bits(mvx, mvy, L.px, L.py);
-    if (cost < L.bcost) { L.bcost = cost; L.bx = mvx; L.by = mvy; }
-    if (ci == 7) { L.cx = L.bx; L.cy = L.by; }
-}
-// first lane of the partition the lane belongs to, and the number of lanes in it
-GVC_HD void me_group(int lane, int &first, int &count) {
-    if (lane < 16) { first = 0; count = 16; } else { first = lane & ~3; count = 4; }
-}
-#if !defined(GVC_EMU)
-GVC_HD int me_group_sum(int lane, int v) {     // sum over the lanes of the partition: 16-lane or 4-lane butterfly
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    const int t4 = __shfl_xor_sync(0xffffffffu, v, 4);
-    if (lane < 16) v += t4;
-    const int t8 = __shfl_xor_sync(0xffffffffu, v, 8);
-    if (lane < 16) v += t8;
-    return v;
-}
-#endif
-// ---- one-partition path --------------------------------------------------------------------------------
-// Part of the search specification (oracle/h264_mb.c): when the four 8x8 partitions pick the same integer vector as the
-// 16x16 partition, the macroblock is coded as one 16x16 partition and the 8x8 refinements are not run (on the test
-// clips: bytes within 0.01 %, PSNR unchanged).  The warp then puts both half-warps on the 16x16 partition, two sub-sample
-// candidates per round: 5 + 4 rounds instead of 9 + 8.
-GVC_HD bool me_ref_one_partition(const MeRefSmem &sm) {
-    bool same = true;
-    for (int k = 1; k < 5; ++k) same = same && sm.center[k][0] == sm.center[0][0] && sm.center[k][1] == sm.center[0][1];
-    return same;
-}
-GVC_HD void me_fast_init(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm, MeLane &L) {
-    me_lane_init(lane & 15, a, mx, my, sm, L);      // both half-warps take the 16 blocks of the 16x16 partition
-}
-// candidate of the lane's half-warp in round r of `step` (step 2: -1, 0 | 1, 2 | ... | 7, none; step 1: 0, 1 | ... | 6, 7); 8 = none
-GVC_HD int me_fast_cand(int lane, int r, int step) { return step == 2 ? 2 * r - 1 + (lane >> 4) : 2 * r + (lane >> 4); }
-// best so far as key = cost << 4 | order (order: position in the sequential candidate list, 0 = carried over), with its vector
-GVC_HD void me_fast_take(const MeRefArgs &a, const MeLane &L, int total, int ci, int step, unsigned &key, int &kx, int &ky) {
-    int dx = 0, dy = 0;
-    if (ci >= 0) sq8(ci, dx, dy);
-    const int mvx = L.cx + dx * step, mvy = L.cy + dy * step;
-    const unsigned k = ((unsigned)(total + a.lambda * mv_bits(mvx, mvy, L.px, L.py)) << 4) | (unsigned)(ci + 1);
-    if (k < key) { key = k; kx = mvx; ky = mvy; }
-}
-GVC_HD void me_fast_out(int lane, const MeRefArgs &a, int mx, int my, unsigned key, int kx, int ky) {
-    if (lane != 0) return;
-    MbMotion m;
-    m.mode = 0;
-    m.cost = (int)(key >> 4);
-    for (int k = 0; k < 4; ++k) { m.mv[k][0] = (int16_t)kx; m.mv[k][1] = (int16_t)ky; }
-    m.pad[0] = m.pad[1] = m.pad[2] = 0;
-    a.out[my * a.mbw + mx] = m;
-    if (a.out_host) a.out_host[my * a.mbw + mx] = m;
-}
-GVC_HD void me_ref_publish(int lane, const MeLane &L, MeRefSmem &sm) {   // partition leaders hand their result to lane 0
-    const bool leader = lane == 0 || (lane >= 16 && ((lane - 16) & 3) == 0);
-    if (!leader) return;
-    sm.best_mv[L.P][0] = L.bx; sm.best_mv[L.P][1] = L.by; sm.best_cost[L.P] = L.bcost;
-}
-GVC_HD void me_ref_out(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
-    if (lane != 0) return;
-    const int j16 = sm.best_cost[0];
-    const int j8  = sm.best_cost[1] + sm.best_cost[2] + sm.best_cost[3] + sm.best_cost[4] + 8 * a.lambda;
-    MbMotion m;
-    m.mode = j8 < j16 ? 1 : 0;
-    m.cost = j8 < j16 ? j8 : j16;
-    for (int k = 0; k < 4; ++k) {
-        m.mv[k][0] = (int16_t)(m.mode ? sm.best_mv[1 + k][0] : sm.best_mv[0][0]);
-        m.mv[k][1] = (int16_t)(m.mode ? sm.best_mv[1 + k][1] : sm.best_mv[0][1]);
-    }
-    m.pad[0] = m.pad[1] = m.pad[2] = 0;
-    a.out[my * a.mbw + mx] = m;
-    if (a.out_host) a.out_host[my * a.mbw + mx] = m;
-}
+}  // namespace gvc
+#include "me_refine.cuh"
+namespace gvc {
 
 // ------------------------------------------------------------------ record compaction ------------
 // Most 4x4 blocks quantise to nothing; the host entropy coder only needs the ones that did not.  Per macroblock the
