@@ -194,3 +194,201 @@ GVC_HD void me_ref_early_out(int lane, const MeRefArgs &a, int mx, int my, const
     a.out[my * a.mbw + mx] = m;
     if (a.out_host) a.out_host[my * a.mbw + mx] = m;
 }
+
+// ------------------------------------------------------------------ sub-sample refinement ------
+// lane -> (partition P, 4x4 block offset inside the MB): lanes 0..15 the 16x16 partition, 16..31 the four 8x8s
+GVC_HD void me_lane_block(int lane, int &P, int &ox, int &oy) {
+    if (lane < 16) { P = 0; ox = 4 * (lane & 3); oy = 4 * (lane >> 2); }
+    else { const int l = lane - 16, k = l >> 2, j = l & 3; P = 1 + k; ox = 8 * (k & 1) + 4 * (j & 1); oy = 8 * (k >> 1) + 4 * (j >> 1); }
+}
+// Half the 4x4 Hadamard magnitude sum of (w - source).  The horizontal transform of a row of four samples is four dp4a
+// with +-1 patterns (FMA pipe: the integer ALU pipe is the busy one in these kernels), started from the negated transform
+// of the source row (hc, computed once per macroblock), so the subtraction is free.  Vertical: one butterfly stage, the last
+// one through |p + q| + |p - q| = 2 max(|p|, |q|).
+constexpr int kHad0 = 0x01010101, kHad1 = (int)0xffff0101, kHad2 = 0x01ffff01, kHad3 = (int)0xff01ff01;   // (1,1,1,1) (1,1,-1,-1) (1,-1,-1,1) (1,-1,1,-1)
+GVC_HD void had_row_neg(unsigned w, int out[4]) {     // minus the horizontal Hadamard transform of four samples
+    out[0] = -dp4a_us(w, kHad0, 0); out[1] = -dp4a_us(w, kHad1, 0); out[2] = -dp4a_us(w, kHad2, 0); out[3] = -dp4a_us(w, kHad3, 0);
+}
+GVC_HD int satd4x4_rows(const int hc[16], unsigned w0, unsigned w1, unsigned w2, unsigned w3) {
+    const unsigned w[4] = {w0, w1, w2, w3};
+    int t[16];
+    for (int j = 0; j < 4; ++j) {
+        t[4 * j]     = dp4a_us(w[j], kHad0, hc[4 * j]);
+        t[4 * j + 1] = dp4a_us(w[j], kHad1, hc[4 * j + 1]);
+        t[4 * j + 2] = dp4a_us(w[j], kHad2, hc[4 * j + 2]);
+        t[4 * j + 3] = dp4a_us(w[j], kHad3, hc[4 * j + 3]);
+    }
+    int acc = 0;
+    for (int k = 0; k < 4; ++k) {
+        const int s0 = t[k] + t[4 + k], s1 = t[k] - t[4 + k], s2 = t[8 + k] + t[12 + k], s3 = t[8 + k] - t[12 + k];
+        acc += imax(iabs(s0), iabs(s2)) + imax(iabs(s1), iabs(s3));
+    }
+    return acc;
+}
+// Per-lane state that stays in registers across the 17 sub-sample candidates: the lane's 4x4 source block (as the negated
+// horizontal transform of its rows), where the block sits in the windows / planes, the predictor, and the search centre of
+// the lane's partition (every lane of a partition carries the same centre and best: no shared-memory round trip or leader
+// election per candidate).  The emulation harness keeps one record per lane.
+struct MeLane {
+    int  P, px, py;
+    int  wx, wy;      // window column / row of the block's sample displaced by (X, Y) full samples: (X + wx, Y + wy)
+    int  base;        // the same for the planes themselves: offset (16*my + oy) * stride + 16*mx + ox
+    int  hc[16];      // minus the horizontal Hadamard transform of the lane's four source rows
+    int  cx, cy;      // search centre, quarter samples
+    bool far;         // the partition's integer vector lies outside the windows: read the planes
+};
+GVC_HD void me_lane_init(int lane, const MeRefArgs &a, int mx, int my, const MeRefSmem &sm, const MeGeom &g, int ccx, int ccy, MeLane &L) {
+    int ox, oy;
+    me_lane_block(lane, L.P, ox, oy);
+    L.px = sm.mvp[0]; L.py = sm.mvp[1];
+    L.wx = ox + g.ax + kMeWinX - g.wbx; L.wy = oy + kMeWinY - g.wby;
+    L.base = (16 * my + oy) * a.stride + 16 * mx + ox;
+    for (int j = 0; j < 4; ++j) {
+        const gvc_uint4 r = sm.cur[oy + j];
+        const unsigned w = ox == 0 ? r.x : ox == 4 ? r.y : ox == 8 ? r.z : r.w;
+        had_row_neg(w, L.hc + 4 * j);
+    }
+    L.cx = 4 * ccx; L.cy = 4 * ccy;
+    L.far = !me_in_window(g, ccx, ccy);
+}
+GVC_HD unsigned me_win4(const unsigned *win, int col, int row) {     // four samples at window (col .. col+3, row), any col
+    const unsigned *r = win + row * kMeWinPitchW + (col >> 2);
+    return funnel_r(r[0], r[1], (col & 3) * 8);
+}
+GVC_HD const uint8_t *me_plane(const MeRefArgs &a, int p) { return p == 0 ? a.ref.y : p == 1 ? a.ref.hh : p == 2 ? a.ref.hv : a.ref.hc; }
+// SATD share of the lane's 4x4 block for the vector (mvx, mvy), any quarter-sample position (mc_luma_src's rule: one
+// plane, or the average of two), from the windows or -- far partitions -- from the planes.  Already halved.
+GVC_HD int me_satd_at(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L, int mvx, int mvy) {
+    const int fx = mvx & 3, fy = mvy & 3, q = fy * 4 + fx;
+    const int p1 = (kQpelRef0 >> (2 * q)) & 3, p2 = (kQpelRef1 >> (2 * q)) & 3;
+    const bool two = (q & 5) != 0;
+    unsigned w[4];
+    if (!L.far) {
+        const int col = (mvx >> 2) + L.wx, row = (mvy >> 2) + L.wy;
+        for (int j = 0; j < 4; ++j) w[j] = me_win4(sm.win[p1], col, row + (fy == 3 ? 1 : 0) + j);
+        if (two) for (int j = 0; j < 4; ++j) w[j] = avg_u8x4(w[j], me_win4(sm.win[p2], col + (fx == 3 ? 1 : 0), row + j));
+    } else {
+        const int off = L.base + (mvy >> 2) * a.stride + (mvx >> 2);
+        const uint8_t *s1 = me_plane(a, p1) + (off + (fy == 3 ? a.stride : 0)), *s2 = me_plane(a, p2) + (off + (fx == 3 ? 1 : 0));
+        for (int j = 0; j < 4; ++j) w[j] = ld_u32_any(s1 + j * a.stride);
+        if (two) for (int j = 0; j < 4; ++j) w[j] = avg_u8x4(w[j], ld_u32_any(s2 + j * a.stride));
+    }
+    return satd4x4_rows(L.hc, w[0], w[1], w[2], w[3]);
+}
+// The nine half-sample candidates around a FULL-sample centre, v[ci + 1] for ci = -1 (the centre) .. 7 (sq8 order), with the
+// window rows shared between the candidates that read the same plane: full plane 4 rows; V plane 5 rows for (0,-1),(0,+1);
+// H plane 4 rows, two shifts, for (-1,0),(+1,0); C plane 5 rows, two shifts, for the four diagonal ones.
+GVC_HD void me_half_all(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L, int v[9]) {
+    if (L.far) {
+        for (int ci = -1; ci < 8; ++ci) {
+            int dx = 0, dy = 0;
+            if (ci >= 0) sq8(ci, dx, dy);
+            v[ci + 1] = me_satd_at(a, sm, L, L.cx + 2 * dx, L.cy + 2 * dy);
+        }
+        return;
+    }
+    constexpr int W = kMeWinPitchW;
+    const int col = (L.cx >> 2) + L.wx, row = (L.cy >> 2) + L.wy;
+    {
+        const unsigned *r = sm.win[0] + row * W + (col >> 2);
+        const int sh = (col & 3) * 8;
+        v[0] = satd4x4_rows(L.hc, funnel_r(r[0], r[1], sh), funnel_r(r[W], r[W + 1], sh), funnel_r(r[2 * W], r[2 * W + 1], sh), funnel_r(r[3 * W], r[3 * W + 1], sh));
+    }
+    {
+        const unsigned *r = sm.win[2] + (row - 1) * W + (col >> 2);
+        const int sh = (col & 3) * 8;
+        unsigned w[5];
+        for (int j = 0; j < 5; ++j) w[j] = funnel_r(r[W * j], r[W * j + 1], sh);
+        v[1] = satd4x4_rows(L.hc, w[0], w[1], w[2], w[3]);      // (0,-1)
+        v[2] = satd4x4_rows(L.hc, w[1], w[2], w[3], w[4]);      // (0,+1)
+    }
+    const int cm = col - 1, shm = (cm & 3) * 8;                 // five samples from column col-1 sit in two words
+    {
+        const unsigned *r = sm.win[1] + row * W + (cm >> 2);
+        unsigned m[4], p[4];
+        for (int j = 0; j < 4; ++j) { const unsigned lo = r[W * j], hi = r[W * j + 1]; m[j] = funnel_r(lo, hi, shm); p[j] = funnel_rc(lo, hi, shm + 8); }
+        v[3] = satd4x4_rows(L.hc, m[0], m[1], m[2], m[3]);      // (-1,0)
+        v[4] = satd4x4_rows(L.hc, p[0], p[1], p[2], p[3]);      // (+1,0)
+    }
+    {
+        const unsigned *r = sm.win[3] + (row - 1) * W + (cm >> 2);
+        unsigned m[5], p[5];
+        for (int j = 0; j < 5; ++j) { const unsigned lo = r[W * j], hi = r[W * j + 1]; m[j] = funnel_r(lo, hi, shm); p[j] = funnel_rc(lo, hi, shm + 8); }
+        v[5] = satd4x4_rows(L.hc, m[0], m[1], m[2], m[3]);      // (-1,-1)
+        v[6] = satd4x4_rows(L.hc, m[1], m[2], m[3], m[4]);      // (-1,+1)
+        v[7] = satd4x4_rows(L.hc, p[0], p[1], p[2], p[3]);      // (+1,-1)
+        v[8] = satd4x4_rows(L.hc, p[1], p[2], p[3], p[4]);      // (+1,+1)
+    }
+}
+// the eight quarter-sample candidates around the centre (sq8 order)
+GVC_HD void me_quarter_all(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L, int v[8]) {
+    for (int ci = 0; ci < 8; ++ci) {
+        int dx, dy;
+        sq8(ci, dx, dy);
+        v[ci] = me_satd_at(a, sm, L, L.cx + dx, L.cy + dy);
+    }
+}
+// Best candidate so far of a partition as key = cost << 4 | order (order = position in the sequential candidate list, 0 = the
+// one carried over from the previous step: the sequential search replaces its best only by a strictly lower cost).
+struct MeBest { unsigned key; int x, y; };
+GVC_HD void me_take(const MeRefArgs &a, const MeLane &L, int total, int ci, int step, MeBest &b) {
+    int dx = 0, dy = 0;
+    if (ci >= 0) sq8(ci, dx, dy);
+    const int mvx = L.cx + dx * step, mvy = L.cy + dy * step;
+    const unsigned k = ((unsigned)(total + a.lambda * mv_bits(mvx, mvy, L.px, L.py)) << 4) | (unsigned)(ci + 1);
+    if (k < b.key) { b.key = k; b.x = mvx; b.y = mvy; }
+}
+GVC_HD void me_next_step(MeLane &L, MeBest &b) { b.key &= ~15u; L.cx = b.x; L.cy = b.y; }   // the best becomes the centre, order 0
+// first lane of the partition the lane belongs to, and the number of lanes in it
+GVC_HD void me_group(int lane, int &first, int &count) {
+    if (lane < 16) { first = 0; count = 16; } else { first = lane & ~3; count = 4; }
+}
+#if !defined(GVC_EMU)
+GVC_HD int me_group_sum(int lane, int v) {     // sum over the lanes of the partition: 16-lane or 4-lane butterfly
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    const int t4 = __shfl_xor_sync(0xffffffffu, v, 4);
+    if (lane < 16) v += t4;
+    const int t8 = __shfl_xor_sync(0xffffffffu, v, 8);
+    if (lane < 16) v += t8;
+    return v;
+}
+#endif
+// ---- one-partition path --------------------------------------------------------------------------------
+// Part of the search specification (oracle/h264_mb.c): when the four 8x8 partitions pick the same integer vector as the
+// 16x16 partition, the macroblock is coded as one 16x16 partition and the 8x8 refinements are not run (on the test
+// clips: bytes within 0.01 %, PSNR unchanged).  The warp then puts both half-warps on the 16x16 partition, two sub-sample
+// candidates per round: 5 + 4 rounds instead of 9 + 8.
+// candidate of the lane's half-warp in round r of `step` (step 2: -1, 0 | 1, 2 | ... | 7, none; step 1: 0, 1 | ... | 6, 7); 8 = none
+GVC_HD int me_fast_cand(int lane, int r, int step) { return step == 2 ? 2 * r - 1 + (lane >> 4) : 2 * r + (lane >> 4); }
+GVC_HD int me_fast_satd(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L, int ci, int step) {
+    int dx = 0, dy = 0;
+    if (ci >= 0) sq8(ci, dx, dy);
+    return me_satd_at(a, sm, L, L.cx + dx * step, L.cy + dy * step);
+}
+GVC_HD void me_write_out(const MeRefArgs &a, int mx, int my, int mode, int cost, const int mvx[4], const int mvy[4]) {
+    MbMotion m;
+    m.mode = (uint8_t)mode;
+    m.cost = cost;
+    for (int k = 0; k < 4; ++k) { m.mv[k][0] = (int16_t)mvx[k]; m.mv[k][1] = (int16_t)mvy[k]; }
+    m.pad[0] = m.pad[1] = m.pad[2] = 0;
+    a.out[my * a.mbw + mx] = m;
+    if (a.out_host) a.out_host[my * a.mbw + mx] = m;
+}
+GVC_HD void me_fast_out(int lane, const MeRefArgs &a, int mx, int my, const MeBest &b) {
+    if (lane != 0) return;
+    const int x[4] = {b.x, b.x, b.x, b.x}, y[4] = {b.y, b.y, b.y, b.y};
+    me_write_out(a, mx, my, 0, (int)(b.key >> 4), x, y);
+}
+// lane 0 with the bests of the five partitions (its own = the 16x16's, and those of lanes 16, 20, 24, 28)
+GVC_HD void me_ref_out(int lane, const MeRefArgs &a, int mx, int my, const MeBest b[5]) {
+    if (lane != 0) return;
+    const int j16 = (int)(b[0].key >> 4);
+    const int j8  = (int)(b[1].key >> 4) + (int)(b[2].key >> 4) + (int)(b[3].key >> 4) + (int)(b[4].key >> 4) + 8 * a.lambda;
+    const int mode = j8 < j16 ? 1 : 0;
+    int x[4], y[4];
+    for (int k = 0; k < 4; ++k) { x[k] = mode ? b[1 + k].x : b[0].x; y[k] = mode ? b[1 + k].y : b[0].y; }
+    me_write_out(a, mx, my, mode, mode ? j8 : j16, x, y);
+}
+
+}  // namespace gvc
