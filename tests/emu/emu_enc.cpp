@@ -46,56 +46,73 @@ void emu_run_me_refine(const MeRefArgs &a) {
             MeRefSmem sm;
             memset(&sm, 0xAB, sizeof(sm));
             for (int l = 0; l < 32; ++l) me_ref_load(l, a, mx, my, sm);
-            int zero_sad = 0;
-            for (int l = 0; l < 32; ++l) zero_sad += int(me_ref_zero_part(l, a, mx, my, sm));
+            unsigned zq[4] = {0, 0, 0, 0};
+            for (int l = 0; l < 32; ++l) zq[me_zero_quadrant(l)] += me_ref_zero_part(l, a, mx, my, sm);
+            const int zero_sad = int(zq[0] + zq[1] + zq[2] + zq[3]);
             if (me_ref_early(a, zero_sad)) {
                 for (int l = 0; l < 32; ++l) me_ref_early_out(l, a, mx, my, sm, zero_sad);
                 continue;
             }
-            for (int l = 0; l < 32; ++l) me_ref_int(l, a, mx, my, sm);
-            for (int l = 0; l < 32; ++l) me_ref_pick(l, a, mx, my, sm);
+            const MeGeom g = me_geom(a, sm, mx, my);
+            for (int l = 0; l < 32; ++l) me_stage_plain(l, a, g, sm);
+            // integer candidates: the warp minimum of each partition's keys, the vector of the winning lane
+            unsigned best[5] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+            for (int l = 0; l < 32; ++l) {
+                unsigned key[5];
+                me_ref_int(l, a, sm, g, zq, key);
+                for (int k = 0; k < 5; ++k) best[k] = key[k] < best[k] ? key[k] : best[k];
+            }
+            int ccx[5], ccy[5];
+            for (int k = 0; k < 5; ++k) me_int_cand(sm, g, int(best[k] & 31u), ccx[k], ccy[k]);
+            bool one = true;
+            for (int k = 1; k < 5; ++k) one = one && ccx[k] == ccx[0] && ccy[k] == ccy[0];
             MeLane L[32];
-            if (me_ref_one_partition(sm)) {                 // the warp's one-partition path, shuffles spelled out
-                for (int l = 0; l < 32; ++l) me_fast_init(l, a, mx, my, sm, L[l]);
-                unsigned key[32];
-                int kx[32], ky[32];
-                for (int l = 0; l < 32; ++l) { key[l] = 0xffffffffu; kx[l] = L[l].cx; ky[l] = L[l].cy; }
+            MeBest b[32];
+            if (one) {                 // the warp's one-partition path, shuffles spelled out
+                for (int l = 0; l < 32; ++l) { me_lane_init(l & 15, a, mx, my, sm, g, ccx[0], ccy[0], L[l]); b[l].key = 0xffffffffu; b[l].x = L[l].cx; b[l].y = L[l].cy; }
                 for (int step = 2; step >= 1; --step) {
                     for (int r = 0; r < (step == 2 ? 5 : 4); ++r) {
                         int part[32];
-                        for (int l = 0; l < 32; ++l) { const int ci = me_fast_cand(l, r, step); part[l] = ci < 8 ? me_ref_satd(a, sm, L[l], ci, step) : 0; }
+                        for (int l = 0; l < 32; ++l) { const int ci = me_fast_cand(l, r, step); part[l] = ci < 8 ? me_fast_satd(a, sm, L[l], ci, step) : 0; }
                         for (int l = 0; l < 32; ++l) {
                             int total = 0;
                             for (int i = 0; i < 16; ++i) total += part[(l & 16) + i];
                             const int ci = me_fast_cand(l, r, step);
-                            if (ci < 8) me_fast_take(a, L[l], total, ci, step, key[l], kx[l], ky[l]);
+                            if (ci < 8) me_take(a, L[l], total, ci, step, b[l]);
                         }
                     }
                     for (int l = 0; l < 16; ++l) {
-                        const int w = key[l + 16] < key[l] ? l + 16 : l;
-                        const unsigned k = key[w] & ~15u;
-                        const int x = kx[w], y = ky[w];
-                        for (int h = 0; h < 2; ++h) { key[l + 16 * h] = k; kx[l + 16 * h] = x; ky[l + 16 * h] = y; L[l + 16 * h].cx = x; L[l + 16 * h].cy = y; }
+                        const MeBest w = b[l + 16].key < b[l].key ? b[l + 16] : b[l];
+                        b[l] = b[l + 16] = w;
                     }
+                    for (int l = 0; l < 32; ++l) me_next_step(L[l], b[l]);
                 }
-                for (int l = 0; l < 32; ++l) me_fast_out(l, a, mx, my, key[l], kx[l], ky[l]);
+                for (int l = 0; l < 32; ++l) me_fast_out(l, a, mx, my, b[l]);
                 continue;
             }
-            for (int l = 0; l < 32; ++l) me_lane_init(l, a, mx, my, sm, L[l]);
-            for (int step = 2; step >= 1; --step)
-                for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci) {
-                    int part[32];
-                    for (int l = 0; l < 32; ++l) part[l] = me_ref_satd(a, sm, L[l], ci, step);
+            for (int l = 0; l < 32; ++l) {
+                int P, ox, oy;
+                me_lane_block(l, P, ox, oy);
+                me_lane_init(l, a, mx, my, sm, g, ccx[P], ccy[P], L[l]);
+                b[l].key = 0xffffffffu; b[l].x = L[l].cx; b[l].y = L[l].cy;
+            }
+            for (int step = 2; step >= 1; --step) {
+                int v[32][9];
+                for (int l = 0; l < 32; ++l) {
+                    if (step == 2) me_half_all(a, sm, L[l], v[l]);
+                    else           me_quarter_all(a, sm, L[l], v[l] + 1);
+                }
+                for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci)
                     for (int l = 0; l < 32; ++l) {          // what the shuffle butterfly computes on the GPU
                         int first, count, total = 0;
                         me_group(l, first, count);
-                        for (int i = 0; i < count; ++i) total += part[first + i];
-                        me_ref_take(a, L[l], total, ci, step);
+                        for (int i = 0; i < count; ++i) total += v[first + i][ci + 1];
+                        me_take(a, L[l], total, ci, step, b[l]);
                     }
-                }
-            for (int l = 0; l < 32; ++l) me_ref_publish(l, L[l], sm);
-
-            for (int l = 0; l < 32; ++l) me_ref_out(l, a, mx, my, sm);
+                if (step == 2) for (int l = 0; l < 32; ++l) me_next_step(L[l], b[l]);
+            }
+            const MeBest all[5] = {b[0], b[16], b[20], b[24], b[28]};
+            for (int l = 0; l < 32; ++l) me_ref_out(l, a, mx, my, all);
         }
 }
 void emu_run_encode_inter(const EncMbArgs &a) {
