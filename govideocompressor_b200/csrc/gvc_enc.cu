@@ -1,5 +1,7 @@
 // gvc_enc.cu -- launchers and C ABI of the encoder-side kernels (include/gvc.h "encoder stages").
 // Kernel bodies: enc_kernels.cuh.  These entry points take DEVICE pointers and are asynchronous on `stream`.
+#include <cuda.h>
+
 #include <cstring>
 
 #include "enc_host.h"
@@ -77,57 +79,153 @@ __global__ void __launch_bounds__(32 * kMbWarps) me_lowres_kernel(const __grid_c
     me_lowres_out(lane, a, mx, my, best);
 }
 
-// 9 CTAs per SM (56 registers, a few spilled words): resident warps, not issue slots, bound the kernel mix (+1.5 % measured)
-__global__ void __launch_bounds__(32 * kMbWarps, 9) me_refine_kernel(const __grid_constant__ MeRefArgs a) {
-    __shared__ MeRefSmem sms[kMbWarps];
+// ---- TMA plumbing of me_refine (see me_refine.cuh): four tensor maps, one per sample plane of the reference picture, each
+// describing the whole padded plane as a 2-D byte tensor (row pitch = the plane's stride); a window is one box of it.
+struct MeRefTma {
+    CUtensorMap map[4];          // each one travels as its own __grid_constant__ kernel parameter: TMA takes the descriptor's address,
+    int on;                      // which must stay in parameter space (never a local copy).  on = 0: planes not addressable by TMA
+};                               // (alignment); the windows are then staged with plain loads
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// one box of the tensor map into shared memory; x must be a multiple of 16 (bytes of the innermost dimension)
+__device__ __forceinline__ void tma_box_2d(void *dst, const CUtensorMap *map, int x, int y, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<unsigned long long>(map)), "r"(smem_u32(bar)), "r"(x), "r"(y) : "memory");
+}
+
+constexpr int kMeWarps = 4;   // macroblocks (warps) per CTA of me_refine: 24.6 KB of windows per CTA
+__global__ void __launch_bounds__(32 * kMeWarps, 8)
+me_refine_kernel(const __grid_constant__ MeRefArgs a, const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_h,
+                 const __grid_constant__ CUtensorMap map_v, const __grid_constant__ CUtensorMap map_c, const int tma_on) {
+    __shared__ MeRefSmem sms[kMeWarps];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int mb = blockIdx.x * kMbWarps + warp;
+    const int mb = blockIdx.x * kMeWarps + warp;
     if (mb >= a.mbw * a.mbh) return;
     const int my = mb / a.mbw, mx = mb - my * a.mbw;
     MeRefSmem &sm = sms[warp];
     me_ref_load(lane, a, mx, my, sm);
     __syncwarp();
-    const int zero_sad = (int)__reduce_add_sync(0xffffffffu, me_ref_zero_part(lane, a, mx, my, sm));
+    // zero-vector SAD: per 8x8 quadrant (lanes of one quadrant: same bit 4, same bit 0), then the whole macroblock
+    unsigned zq[4];
+    {
+        unsigned v = me_ref_zero_part(lane, a, mx, my, sm);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) zq[q] = __shfl_sync(0xffffffffu, v, ((q >> 1) << 4) | (q & 1));
+    }
+    const int zero_sad = (int)(zq[0] + zq[1] + zq[2] + zq[3]);
     if (me_ref_early(a, zero_sad)) { me_ref_early_out(lane, a, mx, my, sm, zero_sad); return; }
-    me_ref_int(lane, a, mx, my, sm);
-    __syncwarp();
-    me_ref_pick(lane, a, mx, my, sm);
-    __syncwarp();
+    const MeGeom g = me_geom(a, sm, mx, my);
+    if (tma_on) {
+        if (lane == 0) {
+            mbar_init(&sm.bar[0], 1);
+            mbar_init(&sm.bar[1], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");      // the barriers exist before the copy engine signals them
+            constexpr unsigned kBox = kMeWinPitch * kMeWinRows;
+            mbar_expect_tx(&sm.bar[0], 2 * kBox);                                    // tensor coordinates: the plane's padding is part of the tensor
+            tma_box_2d(sm.win[0], &map_y, g.wox + kEncPad, g.woy + kEncPad, &sm.bar[0]);
+            tma_box_2d(sm.pred, &map_y, g.pox + kEncPad, g.poy + kEncPad, &sm.bar[0]);
+            mbar_expect_tx(&sm.bar[1], 3 * kBox);
+            tma_box_2d(sm.win[1], &map_h, g.wox + kEncPad, g.woy + kEncPad, &sm.bar[1]);
+            tma_box_2d(sm.win[2], &map_v, g.wox + kEncPad, g.woy + kEncPad, &sm.bar[1]);
+            tma_box_2d(sm.win[3], &map_c, g.wox + kEncPad, g.woy + kEncPad, &sm.bar[1]);
+        }
+        __syncwarp();
+        mbar_wait(&sm.bar[0], 0);
+    } else {
+        me_stage_plain(lane, a, g, sm);
+        __syncwarp();
+    }
+    // integer candidates, one per lane; the best per partition by a key-packed warp minimum, its vector from the winning lane
+    int ccx[5], ccy[5];
+    {
+        unsigned key[5];
+        me_ref_int(lane, a, sm, g, zq, key);
+        int cx, cy;
+        me_int_cand(sm, g, lane < 27 ? lane : 26, cx, cy);
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const int w = (int)(__reduce_min_sync(0xffffffffu, key[k]) & 31u);
+            ccx[k] = __shfl_sync(0xffffffffu, cx, w);
+            ccy[k] = __shfl_sync(0xffffffffu, cy, w);
+        }
+    }
+    if (tma_on) mbar_wait(&sm.bar[1], 0);
     MeLane L;
-    if (me_ref_one_partition(sm)) {      // warp-uniform: both half-warps on the 16x16 partition, two candidates per round
-        me_fast_init(lane, a, mx, my, sm, L);
-        unsigned key = 0xffffffffu;
-        int      kx = L.cx, ky = L.cy;
+    const bool one = ccx[1] == ccx[0] && ccx[2] == ccx[0] && ccx[3] == ccx[0] && ccx[4] == ccx[0] &&
+                     ccy[1] == ccy[0] && ccy[2] == ccy[0] && ccy[3] == ccy[0] && ccy[4] == ccy[0];
+    if (one) {      // warp-uniform: both half-warps on the 16x16 partition, two candidates per round
+        me_lane_init(lane & 15, a, mx, my, sm, g, ccx[0], ccy[0], L);
+        MeBest b;
+        b.key = 0xffffffffu; b.x = L.cx; b.y = L.cy;
         for (int step = 2; step >= 1; --step) {
 #pragma unroll
             for (int r = 0; r < 5; ++r) {
                 if (step == 1 && r == 4) break;
                 const int ci = me_fast_cand(lane, r, step);
-                int v = ci < 8 ? me_ref_satd(a, sm, L, ci, step) : 0;
+                int v = ci < 8 ? me_fast_satd(a, sm, L, ci, step) : 0;
                 v += __shfl_xor_sync(0xffffffffu, v, 1);
                 v += __shfl_xor_sync(0xffffffffu, v, 2);
                 v += __shfl_xor_sync(0xffffffffu, v, 4);
                 v += __shfl_xor_sync(0xffffffffu, v, 8);
-                if (ci < 8) me_fast_take(a, L, v, ci, step, key, kx, ky);
+                if (ci < 8) me_take(a, L, v, ci, step, b);
             }
             // the better half-warp wins (order bits break ties as the sequential search would); it is the next centre
-            const unsigned ok = __shfl_xor_sync(0xffffffffu, key, 16);
-            const int      ox = __shfl_xor_sync(0xffffffffu, kx, 16), oy = __shfl_xor_sync(0xffffffffu, ky, 16);
-            if (ok < key) { key = ok; kx = ox; ky = oy; }
-            key &= ~15u;
-            L.cx = kx; L.cy = ky;
+            const unsigned ok = __shfl_xor_sync(0xffffffffu, b.key, 16);
+            const int      ox = __shfl_xor_sync(0xffffffffu, b.x, 16), oy = __shfl_xor_sync(0xffffffffu, b.y, 16);
+            if (ok < b.key) { b.key = ok; b.x = ox; b.y = oy; }
+            me_next_step(L, b);
         }
-        me_fast_out(lane, a, mx, my, key, kx, ky);
+        me_fast_out(lane, a, mx, my, b);
         return;
     }
-    me_lane_init(lane, a, mx, my, sm, L);
+    int P, ox, oy;
+    me_lane_block(lane, P, ox, oy);
+    const int pcx = P == 0 ? ccx[0] : P == 1 ? ccx[1] : P == 2 ? ccx[2] : P == 3 ? ccx[3] : ccx[4];
+    const int pcy = P == 0 ? ccy[0] : P == 1 ? ccy[1] : P == 2 ? ccy[2] : P == 3 ? ccy[3] : ccy[4];
+    me_lane_init(lane, a, mx, my, sm, g, pcx, pcy, L);
+    MeBest b;
+    b.key = 0xffffffffu; b.x = L.cx; b.y = L.cy;
+    {
+        int v[9];
+        me_half_all(a, sm, L, v);
 #pragma unroll
-    for (int ci = -1; ci < 8; ++ci) me_ref_take(a, L, me_group_sum(lane, me_ref_satd(a, sm, L, ci, 2)), ci, 2);
+        for (int ci = -1; ci < 8; ++ci) me_take(a, L, me_group_sum(lane, v[ci + 1]), ci, 2, b);
+        me_next_step(L, b);
+    }
+    {
+        int v[8];
+        me_quarter_all(a, sm, L, v);
 #pragma unroll
-    for (int ci = 0; ci < 8; ++ci) me_ref_take(a, L, me_group_sum(lane, me_ref_satd(a, sm, L, ci, 1)), ci, 1);
-    me_ref_publish(lane, L, sm);
-    __syncwarp();
-    me_ref_out(lane, a, mx, my, sm);
+        for (int ci = 0; ci < 8; ++ci) me_take(a, L, me_group_sum(lane, v[ci]), ci, 1, b);
+    }
+    MeBest all[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const int src = k == 0 ? 0 : 12 + 4 * k;
+        all[k].key = __shfl_sync(0xffffffffu, b.key, src);
+        all[k].x = __shfl_sync(0xffffffffu, b.x, src);
+        all[k].y = __shfl_sync(0xffffffffu, b.y, src);
+    }
+    me_ref_out(lane, a, mx, my, all);
 }
 
 __global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __grid_constant__ EncMbArgs a) {
@@ -250,8 +348,43 @@ int launch_signal_picture(int *done, unsigned *count_out, const unsigned *count_
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
+// cuTensorMapEncodeTiled through the runtime's driver entry point table (libgvc.so does not link libcuda directly)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+// Describes the padded planes of a.ref to TMA; tma.on = 0 when they cannot be (base or pitch not a multiple of 16 bytes).
+static void me_refine_tma(const MeRefArgs &a, MeRefTma &tma) {
+    memset(&tma, 0, sizeof(tma));
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc || (a.stride & 15) || a.stride < a.w16 + 2 * kEncPad) return;
+    const uint8_t *pl[4] = {a.ref.y, a.ref.hh, a.ref.hv, a.ref.hc};
+    for (int p = 0; p < 4; ++p) {
+        const uint8_t *base = pl[p] - ((size_t)kEncPad * a.stride + kEncPad);        // first byte of the padded plane
+        if (reinterpret_cast<uintptr_t>(base) & 15) return;
+        const cuuint64_t dims[2] = {(cuuint64_t)a.stride, (cuuint64_t)(a.h16 + 2 * kEncPad)};
+        const cuuint64_t strides[1] = {(cuuint64_t)a.stride};
+        const cuuint32_t box[2] = {(cuuint32_t)kMeWinPitch, (cuuint32_t)kMeWinRows}, es[2] = {1, 1};
+        if (enc(&tma.map[p], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t *>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return;
+    }
+    tma.on = 1;
+}
 int launch_me_refine(const MeRefArgs &a, cudaStream_t st) {
-    me_refine_kernel<<<(a.mbw * a.mbh + kMbWarps - 1) / kMbWarps, 32 * kMbWarps, 0, st>>>(a);
+    MeRefTma tma;
+    me_refine_tma(a, tma);
+    static const bool carve = [] { return cudaFuncSetAttribute(me_refine_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100) == cudaSuccess; }();
+    (void)carve;
+    me_refine_kernel<<<(a.mbw * a.mbh + kMeWarps - 1) / kMeWarps, 32 * kMeWarps, 0, st>>>(a, tma.map[0], tma.map[1], tma.map[2], tma.map[3], tma.on);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
