@@ -115,11 +115,12 @@ me_refine_kernel(const __grid_constant__ MeRefArgs a, const __grid_constant__ CU
                  const __grid_constant__ CUtensorMap map_v, const __grid_constant__ CUtensorMap map_c, const int tma_on) {
     __shared__ MeRefSmem sms[kMeWarps];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int mb = blockIdx.x * kMeWarps + warp;
-    if (mb >= a.mbw * a.mbh) return;
-    const int my = mb / a.mbw, mx = mb - my * a.mbw;
+    const int mx = blockIdx.x * kMeWarps + warp, my = blockIdx.y;      // a CTA takes kMeWarps neighbouring macroblocks of one row
+    if (mx >= a.mbw) return;
     MeRefSmem &sm = sms[warp];
     me_ref_load(lane, a, mx, my, sm);
+    __syncwarp();
+    me_mvp(sm, lane);
     __syncwarp();
     // zero-vector SAD: per 8x8 quadrant (lanes of one quadrant: same bit 4, same bit 0), then the whole macroblock
     unsigned zq[4];
@@ -177,6 +178,7 @@ me_refine_kernel(const __grid_constant__ MeRefArgs a, const __grid_constant__ CU
         MeBest b;
         b.key = 0xffffffffu; b.x = L.cx; b.y = L.cy;
         for (int step = 2; step >= 1; --step) {
+            const MeStepCost sc = me_step_cost(a, L, step);
 #pragma unroll
             for (int r = 0; r < 5; ++r) {
                 if (step == 1 && r == 4) break;
@@ -186,7 +188,7 @@ me_refine_kernel(const __grid_constant__ MeRefArgs a, const __grid_constant__ CU
                 v += __shfl_xor_sync(0xffffffffu, v, 2);
                 v += __shfl_xor_sync(0xffffffffu, v, 4);
                 v += __shfl_xor_sync(0xffffffffu, v, 8);
-                if (ci < 8) me_take(a, L, v, ci, step, b);
+                if (ci < 8) me_take(L, sc, v, ci, step, b);
             }
             // the better half-warp wins (order bits break ties as the sequential search would); it is the next centre
             const unsigned ok = __shfl_xor_sync(0xffffffffu, b.key, 16);
@@ -207,15 +209,17 @@ me_refine_kernel(const __grid_constant__ MeRefArgs a, const __grid_constant__ CU
     {
         int v[9];
         me_half_all(a, sm, L, v);
+        const MeStepCost sc = me_step_cost(a, L, 2);
 #pragma unroll
-        for (int ci = -1; ci < 8; ++ci) me_take(a, L, me_group_sum(lane, v[ci + 1]), ci, 2, b);
+        for (int ci = -1; ci < 8; ++ci) me_take(L, sc, me_group_sum(lane, v[ci + 1]), ci, 2, b);
         me_next_step(L, b);
     }
     {
         int v[8];
         me_quarter_all(a, sm, L, v);
+        const MeStepCost sc = me_step_cost(a, L, 1);
 #pragma unroll
-        for (int ci = 0; ci < 8; ++ci) me_take(a, L, me_group_sum(lane, v[ci]), ci, 1, b);
+        for (int ci = 0; ci < 8; ++ci) me_take(L, sc, me_group_sum(lane, v[ci]), ci, 1, b);
     }
     MeBest all[5];
 #pragma unroll
@@ -384,7 +388,7 @@ int launch_me_refine(const MeRefArgs &a, cudaStream_t st) {
     me_refine_tma(a, tma);
     static const bool carve = [] { return cudaFuncSetAttribute(me_refine_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100) == cudaSuccess; }();
     (void)carve;
-    me_refine_kernel<<<(a.mbw * a.mbh + kMeWarps - 1) / kMeWarps, 32 * kMeWarps, 0, st>>>(a, tma.map[0], tma.map[1], tma.map[2], tma.map[3], tma.on);
+    me_refine_kernel<<<dim3((a.mbw + kMeWarps - 1) / kMeWarps, a.mbh), 32 * kMeWarps, 0, st>>>(a, tma.map[0], tma.map[1], tma.map[2], tma.map[3], tma.on);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }

@@ -49,24 +49,19 @@ struct
     unsigned           pred[kMeWinWords];     // full plane at the predictor candidate
     gvc_uint4          cur[16];               // the macroblock's 16 source rows
     unsigned long long bar[2];                // mbarriers: [0] full + predictor windows, [1] H, V, C windows
-    int                mvp[2], low[2];
+    int                mvp[2], low[2], nb[6];
 };
 
-GVC_HD void sq8(int i, int &dx, int &dy) {   // (0,-1),(0,1),(-1,0),(1,0),(-1,-1),(-1,1),(1,-1),(1,1)
-    dx = i < 2 ? 0 : ((i == 2 || i == 4 || i == 5) ? -1 : 1);
-    dy = i == 0 ? -1 : i == 1 ? 1 : (i < 4 ? 0 : ((i & 1) ? 1 : -1));
+GVC_HD void sq8(int i, int &dx, int &dy) {   // (0,-1),(0,1),(-1,0),(1,0),(-1,-1),(-1,1),(1,-1),(1,1): d + 1 in two bits per entry
+    dx = (int)((0xA085u >> (2 * i)) & 3u) - 1;
+    dy = (int)((0x8858u >> (2 * i)) & 3u) - 1;
 }
-GVC_HD void me_mvp(const MeRefArgs &a, int mx, int my, int &px, int &py) {
-    int v[3][2];
-    int nx[3] = {mx - 1, mx, mx + 1}, ny[3] = {my, my - 1, my - 1};
-    if (!(nx[2] < a.mbw && ny[2] >= 0)) { nx[2] = mx - 1; ny[2] = my - 1; }
-    for (int k = 0; k < 3; ++k) {
-        const bool ok = nx[k] >= 0 && nx[k] < a.mbw && ny[k] >= 0 && ny[k] < a.mbh;
-        v[k][0] = ok ? 8 * a.lowres_mv[2 * (ny[k] * a.mbw + nx[k])] : 0;
-        v[k][1] = ok ? 8 * a.lowres_mv[2 * (ny[k] * a.mbw + nx[k]) + 1] : 0;
-    }
-    px = median3(v[0][0], v[1][0], v[2][0]);
-    py = median3(v[0][1], v[1][1], v[2][1]);
+// component c of neighbour k's lowres vector in quarter samples (k: left, above, above right -- or above left when there is none), 0 outside
+GVC_HD int me_neighbour(const MeRefArgs &a, int mx, int my, int k, int c) {
+    int nx = k == 0 ? mx - 1 : k == 1 ? mx : mx + 1, ny = k == 0 ? my : my - 1;
+    if (k == 2 && !(nx < a.mbw && ny >= 0)) nx = mx - 1;
+    const bool ok = nx >= 0 && nx < a.mbw && ny >= 0 && ny < a.mbh;
+    return ok ? 8 * a.lowres_mv[2 * (ny * a.mbw + nx) + c] : 0;
 }
 GVC_HDH bool me_cur_aligned(const MeRefArgs &a) { return ((((unsigned long long)a.cur) | (unsigned)a.stride) & 15) == 0; }
 GVC_HD void me_ref_load(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem &sm) {
@@ -81,14 +76,16 @@ GVC_HD void me_ref_load(int lane, const MeRefArgs &a, int mx, int my, MeRefSmem 
             r.x = w[0]; r.y = w[1]; r.z = w[2]; r.w = w[3];
         }
         sm.cur[lane] = r;
-    } else if (lane == 16) {
-        int px, py;
-        me_mvp(a, mx, my, px, py);
-        sm.mvp[0] = px; sm.mvp[1] = py;
-    } else if (lane == 17) {
-        sm.low[0] = a.lowres_mv[2 * (my * a.mbw + mx)];
-        sm.low[1] = a.lowres_mv[2 * (my * a.mbw + mx) + 1];
+    } else if (lane < 22) {          // six lanes fetch the neighbours' vectors; every lane takes the medians itself (me_mvp)
+        const int i = lane - 16;
+        sm.nb[i] = me_neighbour(a, mx, my, i >> 1, i & 1);
+    } else if (lane < 24) {
+        sm.low[lane - 22] = a.lowres_mv[2 * (my * a.mbw + mx) + (lane - 22)];
     }
+}
+GVC_HD void me_mvp(MeRefSmem &sm, int lane) {      // after me_ref_load: the median predictor into the shared record (same value from every lane)
+    const int px = median3(sm.nb[0], sm.nb[2], sm.nb[4]), py = median3(sm.nb[1], sm.nb[3], sm.nb[5]);
+    if (lane == 0) { sm.mvp[0] = px; sm.mvp[1] = py; }
 }
 // the lane's share of the 16x16 SAD at the zero vector (two lanes per row: lane = 2 * row + half).  The sum over all
 // lanes decides the early termination; the sums per 8x8 quadrant (rows 0..7 / 8..15 x halves) are candidate 26's SADs.
@@ -205,6 +202,13 @@ GVC_HD void me_lane_block(int lane, int &P, int &ox, int &oy) {
 // with +-1 patterns (FMA pipe: the integer ALU pipe is the busy one in these kernels), started from the negated transform
 // of the source row (hc, computed once per macroblock), so the subtraction is free.  Vertical: one butterfly stage, the last
 // one through |p + q| + |p - q| = 2 max(|p|, |q|).
+GVC_HD int absdiff(int a, int b) {
+#if defined(GVC_EMU)
+    return a > b ? a - b : b - a;
+#else
+    return (int)__sad(a, b, 0u);
+#endif
+}
 constexpr int kHad0 = 0x01010101, kHad1 = (int)0xffff0101, kHad2 = 0x01ffff01, kHad3 = (int)0xff01ff01;   // (1,1,1,1) (1,1,-1,-1) (1,-1,-1,1) (1,-1,1,-1)
 GVC_HD void had_row_neg(unsigned w, int out[4]) {     // minus the horizontal Hadamard transform of four samples
     out[0] = -dp4a_us(w, kHad0, 0); out[1] = -dp4a_us(w, kHad1, 0); out[2] = -dp4a_us(w, kHad2, 0); out[3] = -dp4a_us(w, kHad3, 0);
@@ -218,10 +222,12 @@ GVC_HD int satd4x4_rows(const int hc[16], unsigned w0, unsigned w1, unsigned w2,
         t[4 * j + 2] = dp4a_us(w[j], kHad2, hc[4 * j + 2]);
         t[4 * j + 3] = dp4a_us(w[j], kHad3, hc[4 * j + 3]);
     }
+    // vertical: |t0 + t1| = |t0 - (-t1)| and |t0 - t1| are one absolute-difference instruction each (the negation is a multiply-add
+    // pipe move), then |p + q| + |p - q| = 2 max(|p|, |q|) replaces the second butterfly stage
     int acc = 0;
     for (int k = 0; k < 4; ++k) {
-        const int s0 = t[k] + t[4 + k], s1 = t[k] - t[4 + k], s2 = t[8 + k] + t[12 + k], s3 = t[8 + k] - t[12 + k];
-        acc += imax(iabs(s0), iabs(s2)) + imax(iabs(s1), iabs(s3));
+        const int n1 = -t[4 + k], n3 = -t[12 + k];
+        acc += imax(absdiff(t[k], n1), absdiff(t[8 + k], n3)) + imax(absdiff(t[k], t[4 + k]), absdiff(t[8 + k], t[12 + k]));
     }
     return acc;
 }
@@ -331,12 +337,22 @@ GVC_HD void me_quarter_all(const MeRefArgs &a, const MeRefSmem &sm, const MeLane
 // Best candidate so far of a partition as key = cost << 4 | order (order = position in the sequential candidate list, 0 = the
 // one carried over from the previous step: the sequential search replaces its best only by a strictly lower cost).
 struct MeBest { unsigned key; int x, y; };
-GVC_HD void me_take(const MeRefArgs &a, const MeLane &L, int total, int ci, int step, MeBest &b) {
+// lambda * se(v) bits of the three x and three y components a step's candidates use: [0] centre - step, [1] centre, [2] centre + step
+struct MeStepCost { int x[3], y[3]; };
+GVC_HD MeStepCost me_step_cost(const MeRefArgs &a, const MeLane &L, int step) {
+    MeStepCost c;
+    for (int i = 0; i < 3; ++i) {
+        c.x[i] = a.lambda * se_bits(L.cx + (i - 1) * step - L.px);
+        c.y[i] = a.lambda * se_bits(L.cy + (i - 1) * step - L.py);
+    }
+    return c;
+}
+GVC_HD void me_take(const MeLane &L, const MeStepCost &c, int total, int ci, int step, MeBest &b) {
     int dx = 0, dy = 0;
     if (ci >= 0) sq8(ci, dx, dy);
-    const int mvx = L.cx + dx * step, mvy = L.cy + dy * step;
-    const unsigned k = ((unsigned)(total + a.lambda * mv_bits(mvx, mvy, L.px, L.py)) << 4) | (unsigned)(ci + 1);
-    if (k < b.key) { b.key = k; b.x = mvx; b.y = mvy; }
+    const int bits = (dx < 0 ? c.x[0] : dx > 0 ? c.x[2] : c.x[1]) + (dy < 0 ? c.y[0] : dy > 0 ? c.y[2] : c.y[1]);
+    const unsigned k = ((unsigned)(total + bits) << 4) | (unsigned)(ci + 1);
+    if (k < b.key) { b.key = k; b.x = L.cx + dx * step; b.y = L.cy + dy * step; }
 }
 GVC_HD void me_next_step(MeLane &L, MeBest &b) { b.key &= ~15u; L.cx = b.x; L.cy = b.y; }   // the best becomes the centre, order 0
 // first lane of the partition the lane belongs to, and the number of lanes in it

@@ -46,6 +46,7 @@ void emu_run_me_refine(const MeRefArgs &a) {
             MeRefSmem sm;
             memset(&sm, 0xAB, sizeof(sm));
             for (int l = 0; l < 32; ++l) me_ref_load(l, a, mx, my, sm);
+            for (int l = 0; l < 32; ++l) me_mvp(sm, l);
             unsigned zq[4] = {0, 0, 0, 0};
             for (int l = 0; l < 32; ++l) zq[me_zero_quadrant(l)] += me_ref_zero_part(l, a, mx, my, sm);
             const int zero_sad = int(zq[0] + zq[1] + zq[2] + zq[3]);
@@ -71,6 +72,8 @@ void emu_run_me_refine(const MeRefArgs &a) {
             if (one) {                 // the warp's one-partition path, shuffles spelled out
                 for (int l = 0; l < 32; ++l) { me_lane_init(l & 15, a, mx, my, sm, g, ccx[0], ccy[0], L[l]); b[l].key = 0xffffffffu; b[l].x = L[l].cx; b[l].y = L[l].cy; }
                 for (int step = 2; step >= 1; --step) {
+                    MeStepCost sc[32];
+                    for (int l = 0; l < 32; ++l) sc[l] = me_step_cost(a, L[l], step);
                     for (int r = 0; r < (step == 2 ? 5 : 4); ++r) {
                         int part[32];
                         for (int l = 0; l < 32; ++l) { const int ci = me_fast_cand(l, r, step); part[l] = ci < 8 ? me_fast_satd(a, sm, L[l], ci, step) : 0; }
@@ -78,7 +81,7 @@ void emu_run_me_refine(const MeRefArgs &a) {
                             int total = 0;
                             for (int i = 0; i < 16; ++i) total += part[(l & 16) + i];
                             const int ci = me_fast_cand(l, r, step);
-                            if (ci < 8) me_take(a, L[l], total, ci, step, b[l]);
+                            if (ci < 8) me_take(L[l], sc[l], total, ci, step, b[l]);
                         }
                     }
                     for (int l = 0; l < 16; ++l) {
@@ -102,12 +105,14 @@ void emu_run_me_refine(const MeRefArgs &a) {
                     if (step == 2) me_half_all(a, sm, L[l], v[l]);
                     else           me_quarter_all(a, sm, L[l], v[l] + 1);
                 }
+                MeStepCost sc[32];
+                for (int l = 0; l < 32; ++l) sc[l] = me_step_cost(a, L[l], step);
                 for (int ci = (step == 2 ? -1 : 0); ci < 8; ++ci)
                     for (int l = 0; l < 32; ++l) {          // what the shuffle butterfly computes on the GPU
                         int first, count, total = 0;
                         me_group(l, first, count);
                         for (int i = 0; i < count; ++i) total += v[first + i][ci + 1];
-                        me_take(a, L[l], total, ci, step, b[l]);
+                        me_take(L[l], sc[l], total, ci, step, b[l]);
                     }
                 if (step == 2) for (int l = 0; l < 32; ++l) me_next_step(L[l], b[l]);
             }
