@@ -668,6 +668,9 @@ GVC_HD void pack_reserve(int lane, const PackOut &po, int mb, uint32_t nz, int *
     flags[31] = (int)base;
 }
 
+// the small kernel that closes a picture: *count_out = *count_in; system-wide fence; *done = 1
+struct SignalArgs { int *done; unsigned *count_out; const unsigned *count_in; };
+
 // ------------------------------------------------------------------ K5+K6 inter MB encode -------
 // coef layout per MB (int16[26][16]): blocks 0..15 luma 4x4 (raster block order, zig-zag coefficient order),
 // 16..19 Cb AC, 20..23 Cr AC (entry 0 = 0), 24: chroma DC levels Cb[0..3] Cr[4..7], 25: luma DC (Intra16x16 only).

@@ -53,6 +53,13 @@ struct MbMotion {
     uint8_t pad[3];
 };
 
-constexpr int kMbCoefs = 26 * 16;   // int16 per macroblock: see mb_coef_layout in enc_kernels.cuh
+constexpr int kMbCoefs = 26 * 16;
+
+// Segments are independent (server.go:176-190 hands out whole pieces), so up to kMaxBatch of them advance picture by picture
+// together: every stage is ONE launch whose grid carries the segment index, and the kernel picks that segment's argument
+// record out of a Batch<> kernel parameter (parameter space: up to 32 KB on sm_70+ with CUDA >= 12.1).
+constexpr int kMaxBatch = 16;
+template <class A> struct Batch { A a[kMaxBatch]; };
+   // int16 per macroblock: see mb_coef_layout in enc_kernels.cuh
 
 }  // namespace gvc

@@ -23,28 +23,34 @@ __global__ void __launch_bounds__(256) lowres_kernel(const uint8_t *src, int sst
     if (lx < lx_hi && ly < ly_hi) lowres_px(src, sstride, x_lo, x_hi, y_lo, y_hi, d0, dh, dv, dc, dstride, lx, ly);
 }
 
-__global__ void __launch_bounds__(256) extend_border_batch_kernel(const __grid_constant__ BorderBatchArgs a) {
+__global__ void __launch_bounds__(256) extend_border_batch_kernel(const __grid_constant__ Batch<BorderBatchArgs> B) {
+    const BorderBatchArgs &a = B.a[blockIdx.z];
     const int f = blockIdx.y / 3, k = blockIdx.y - 3 * f;
     int x, y;
-    if (border_piece_xy(a, k, blockIdx.x, threadIdx.x, x, y))
+    if (f < a.n_frames && border_piece_xy(a, k, blockIdx.x, threadIdx.x, x, y))
         extend_border_px(a.p[k] + (size_t)f * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], x, y);
 }
 
-__global__ void __launch_bounds__(256) extend_border16_batch_kernel(const __grid_constant__ BorderBatchArgs a) {
+__global__ void __launch_bounds__(256) extend_border16_batch_kernel(const __grid_constant__ Batch<BorderBatchArgs> B) {
+    const BorderBatchArgs &a = B.a[blockIdx.z];
     const int f = blockIdx.y / 3, k = blockIdx.y - 3 * f;
     int x, y;
-    if (border16_piece_xy(a, k, blockIdx.x * 8 + (threadIdx.x >> 5), threadIdx.x & 31, x, y))
+    if (f < a.n_frames && border16_piece_xy(a, k, blockIdx.x * 8 + (threadIdx.x >> 5), threadIdx.x & 31, x, y))
         extend_border_16(a.p[k] + (size_t)f * a.frame_stride[k], a.stride[k], a.w[k], a.h[k], x, y);
 }
 
-__global__ void __launch_bounds__(256) lowres_batch_kernel(const __grid_constant__ LowresBatchArgs a) {
+// grid.z = segment * frames_max + picture
+__global__ void __launch_bounds__(256) lowres_batch_kernel(const __grid_constant__ Batch<LowresBatchArgs> B, int frames_max) {
+    const int seg = blockIdx.z / frames_max, f = blockIdx.z - seg * frames_max;
+    const LowresBatchArgs &a = B.a[seg];
     const int lx = a.lx_lo + 4 * (blockIdx.x * 256 + threadIdx.x), ly = a.ly_lo + blockIdx.y;      // four samples per thread
-    if (lx < a.lx_hi && ly < a.ly_hi)
-        lowres_quad(a, lowres_aligned(a), a.src + (size_t)blockIdx.z * a.sframe, a.dst + (size_t)blockIdx.z * a.dframe, lx, ly);
+    if (f < a.n_frames && lx < a.lx_hi && ly < a.ly_hi)
+        lowres_quad(a, lowres_aligned(a), a.src + (size_t)f * a.sframe, a.dst + (size_t)f * a.dframe, lx, ly);
 }
 
-__global__ void __launch_bounds__(kHpThreads) hpel_kernel(const __grid_constant__ HpelArgs a) {
+__global__ void __launch_bounds__(kHpThreads) hpel_kernel(const __grid_constant__ Batch<HpelArgs> B) {
     __shared__ HpelSmem sm;
+    const HpelArgs &a = B.a[blockIdx.z];
     const int x0 = a.x_lo + blockIdx.x * kHpTileW, y0 = a.y_lo + blockIdx.y * kHpTileH;
     const bool al = hpel_aligned(a);
     hpel_phase_a(threadIdx.x, a, al, x0, y0, sm);
@@ -61,12 +67,13 @@ __global__ void __launch_bounds__(128) transform8x8_kernel(const __grid_constant
 
 constexpr int kMbWarps = 4;   // macroblocks (warps) per CTA in the per-MB kernels
 
-__global__ void __launch_bounds__(32 * kMbWarps) me_lowres_kernel(const __grid_constant__ MeLowArgs a) {
+// per-macroblock kernels: a CTA takes kMbWarps neighbouring macroblocks of one row (grid.x), grid.y = macroblock row, grid.z = segment
+__global__ void __launch_bounds__(32 * kMbWarps) me_lowres_kernel(const __grid_constant__ Batch<MeLowArgs> B) {
     __shared__ MeLowSmem sms[kMbWarps];
+    const MeLowArgs &a = B.a[blockIdx.z];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int mb = blockIdx.x * kMbWarps + warp;
-    if (mb >= a.mbw * a.mbh) return;
-    const int my = mb / a.mbw, mx = mb - my * a.mbw;
+    const int mx = blockIdx.x * kMbWarps + warp, my = blockIdx.y;
+    if (mx >= a.mbw) return;
     if (me_lowres_zero_wins(a, __reduce_add_sync(0xffffffffu, me_lowres_zero_sad(lane, a, mx, my)))) {
         me_lowres_out(lane, a, mx, my, (unsigned)(a.r * (2 * a.r + 1) + a.r));      // index of displacement (0, 0)
         return;
@@ -82,9 +89,9 @@ __global__ void __launch_bounds__(32 * kMbWarps) me_lowres_kernel(const __grid_c
 // ---- TMA plumbing of me_refine (see me_refine.cuh): four tensor maps, one per sample plane of the reference picture, each
 // describing the whole padded plane as a 2-D byte tensor (row pitch = the plane's stride); a window is one box of it.
 struct MeRefTma {
-    CUtensorMap map[4];          // each one travels as its own __grid_constant__ kernel parameter: TMA takes the descriptor's address,
-    int on;                      // which must stay in parameter space (never a local copy).  on = 0: planes not addressable by TMA
-};                               // (alignment); the windows are then staged with plain loads
+    CUtensorMap map[4];          // TMA takes the descriptor's ADDRESS, which must stay in parameter space (never a local copy): the
+    int on;                      // kernel only forms &T.a[segment].map[p] of its __grid_constant__ parameter.  on = 0: planes not
+};                               // addressable by TMA (alignment); the windows are then staged with plain loads
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -111,9 +118,11 @@ __device__ __forceinline__ void tma_box_2d(void *dst, const CUtensorMap *map, in
 
 constexpr int kMeWarps = 4;   // macroblocks (warps) per CTA of me_refine: 24.6 KB of windows per CTA
 __global__ void __launch_bounds__(32 * kMeWarps, 8)
-me_refine_kernel(const __grid_constant__ MeRefArgs a, const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_h,
-                 const __grid_constant__ CUtensorMap map_v, const __grid_constant__ CUtensorMap map_c, const int tma_on) {
+me_refine_kernel(const __grid_constant__ Batch<MeRefArgs> B, const __grid_constant__ Batch<MeRefTma> T) {
     __shared__ MeRefSmem sms[kMeWarps];
+    const MeRefArgs &a = B.a[blockIdx.z];
+    const CUtensorMap *maps = T.a[blockIdx.z].map;
+    const int tma_on = T.a[blockIdx.z].on;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int mx = blockIdx.x * kMeWarps + warp, my = blockIdx.y;      // a CTA takes kMeWarps neighbouring macroblocks of one row
     if (mx >= a.mbw) return;
@@ -142,12 +151,12 @@ me_refine_kernel(const __grid_constant__ MeRefArgs a, const __grid_constant__ CU
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");      // the barriers exist before the copy engine signals them
             constexpr unsigned kBox = kMeWinPitch * kMeWinRows;
             mbar_expect_tx(&sm.bar[0], 2 * kBox);                                    // tensor coordinates: the plane's padding is part of the tensor
-            tma_box_2d(sm.win[0], &map_y, g.wox + kEncPad, g.woy + kEncPad, &sm.bar[0]);
-            tma_box_2d(sm.pred, &map_y, g.pox + kEncPad, g.poy + kEncPad, &sm.bar[0]);
+            tma_box_2d(sm.win[0], &maps[0], g.wox + kEncPad, g.woy + kEncPad, &sm.bar[0]);
+            tma_box_2d(sm.pred, &maps[0], g.pox + kEncPad, g.poy + kEncPad, &sm.bar[0]);
             mbar_expect_tx(&sm.bar[1], 3 * kBox);
-            tma_box_2d(sm.win[1], &map_h, g.wox + kEncPad, g.woy + kEncPad, &sm.bar[1]);
-            tma_box_2d(sm.win[2], &map_v, g.wox + kEncPad, g.woy + kEncPad, &sm.bar[1]);
-            tma_box_2d(sm.win[3], &map_c, g.wox + kEncPad, g.woy + kEncPad, &sm.bar[1]);
+            tma_box_2d(sm.win[1], &maps[1], g.wox + kEncPad, g.woy + kEncPad, &sm.bar[1]);
+            tma_box_2d(sm.win[2], &maps[2], g.wox + kEncPad, g.woy + kEncPad, &sm.bar[1]);
+            tma_box_2d(sm.win[3], &maps[3], g.wox + kEncPad, g.woy + kEncPad, &sm.bar[1]);
         }
         __syncwarp();
         mbar_wait(&sm.bar[0], 0);
@@ -232,12 +241,12 @@ me_refine_kernel(const __grid_constant__ MeRefArgs a, const __grid_constant__ CU
     me_ref_out(lane, a, mx, my, all);
 }
 
-__global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __grid_constant__ EncMbArgs a) {
+__global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __grid_constant__ Batch<EncMbArgs> B) {
     __shared__ EncMbSmem sms[kMbWarps];
+    const EncMbArgs &a = B.a[blockIdx.z];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int mb = blockIdx.x * kMbWarps + warp;
-    if (mb >= a.mbw * a.mbh) return;
-    const int my = mb / a.mbw, mx = mb - my * a.mbw;
+    const int mx = blockIdx.x * kMbWarps + warp, my = blockIdx.y;
+    if (mx >= a.mbw) return;
     EncMbSmem &sm = sms[warp];
     const bool al = enc_mb_aligned(a);
     EncLane L;
@@ -251,9 +260,11 @@ __global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __gri
 }
 
 // One warp per macroblock row; rows advance as a wavefront (see enc_kernels.cuh K7).
-__global__ void __launch_bounds__(32) intra_frame_kernel(const __grid_constant__ IntraArgs a) {
+__global__ void __launch_bounds__(32) intra_frame_kernel(const __grid_constant__ Batch<IntraArgs> B) {
     __shared__ IntraSmem sm;
+    const IntraArgs &a = B.a[blockIdx.y];
     const int my = blockIdx.x, lane = threadIdx.x;
+    if (my >= a.mbh) return;
     const bool al = intra_aligned(a);
     // The CTA is one warp.  __syncthreads() (bar.sync.aligned) instead of __syncwarp() between the phases: an aligned barrier
     // requires the warp to be converged, a warp-level sync does not bring the lanes back together -- with __syncwarp() the
@@ -302,53 +313,91 @@ int launch_lowres(const uint8_t *src, int sstride, int x_lo, int x_hi, int y_lo,
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
-int launch_extend_border_batch(const BorderBatchArgs &a, cudaStream_t st) {
-    if (a.n_frames < 1) return GVC_OK;
-    const bool vec = border16_ok(a);
+// ---- batched launchers: `count` (<= kMaxBatch) argument records of equal geometry, one per segment; one launch covers them all
+template <class A> static void fill_batch(Batch<A> &B, const A *a, int count) {
+    for (int i = 0; i < count; ++i) B.a[i] = a[i];
+    for (int i = count; i < kMaxBatch; ++i) B.a[i] = a[0];      // never indexed by the grid; keeps the parameter block defined
+}
+#define GVC_CHECK_BATCH(count) do { if ((count) < 1 || (count) > kMaxBatch) { set_error("batch of %d segments outside 1..%d", (count), kMaxBatch); return GVC_ERR_INVALID_ARG; } } while (0)
+
+int launch_extend_border_batch(const BorderBatchArgs *a, int count, cudaStream_t st) {
+    GVC_CHECK_BATCH(count);
+    int frames = 0;
+    bool vec = true;
+    for (int i = 0; i < count; ++i) { frames = a[i].n_frames > frames ? a[i].n_frames : frames; vec = vec && border16_ok(a[i]); }
+    if (frames < 1) return GVC_OK;
     int pieces = 1;                                   // the largest plane decides the grid; smaller planes' extra blocks exit
     for (int k = 0; k < 3; ++k) {
-        const int n = vec ? (border16_pieces(a, k) + 7) / 8 : border_pieces(a, k);
+        const int n = vec ? (border16_pieces(a[0], k) + 7) / 8 : border_pieces(a[0], k);
         pieces = n > pieces ? n : pieces;
     }
-    for (int f0 = 0; f0 < a.n_frames; f0 += 16384) {     // gridDim.y <= 65535
-        BorderBatchArgs b = a;
-        b.n_frames = a.n_frames - f0 < 16384 ? a.n_frames - f0 : 16384;
-        for (int k = 0; k < 3; ++k) b.p[k] = a.p[k] + (size_t)f0 * a.frame_stride[k];
-        if (vec) extend_border16_batch_kernel<<<dim3(pieces, b.n_frames * 3), 256, 0, st>>>(b);
-        else     extend_border_batch_kernel<<<dim3(pieces, b.n_frames * 3), 256, 0, st>>>(b);
+    for (int f0 = 0; f0 < frames; f0 += 16384) {     // gridDim.y <= 65535
+        Batch<BorderBatchArgs> B;
+        fill_batch(B, a, count);
+        int nf = 0;
+        for (int i = 0; i < kMaxBatch; ++i) {
+            BorderBatchArgs &b = B.a[i];
+            const int left = b.n_frames - f0;
+            b.n_frames = left < 0 ? 0 : left < 16384 ? left : 16384;
+            for (int k = 0; k < 3; ++k) b.p[k] += (size_t)f0 * b.frame_stride[k];
+            if (i < count) nf = b.n_frames > nf ? b.n_frames : nf;
+        }
+        if (vec) extend_border16_batch_kernel<<<dim3(pieces, nf * 3, count), 256, 0, st>>>(B);
+        else     extend_border_batch_kernel<<<dim3(pieces, nf * 3, count), 256, 0, st>>>(B);
         GVC_CUDA(cudaGetLastError());
     }
     return GVC_OK;
 }
-int launch_lowres_batch(const LowresBatchArgs &a, cudaStream_t st) {
-    if (a.n_frames < 1 || a.lx_hi <= a.lx_lo || a.ly_hi <= a.ly_lo) return GVC_OK;
-    for (int f0 = 0; f0 < a.n_frames; f0 += 32768) {
-        LowresBatchArgs b = a;
-        b.n_frames = a.n_frames - f0 < 32768 ? a.n_frames - f0 : 32768;
-        b.src = a.src + (size_t)f0 * a.sframe; b.dst = a.dst + (size_t)f0 * a.dframe;
-        lowres_batch_kernel<<<dim3((a.lx_hi - a.lx_lo + 1023) / 1024, a.ly_hi - a.ly_lo, b.n_frames), 256, 0, st>>>(b);
+int launch_lowres_batch(const LowresBatchArgs *a, int count, cudaStream_t st) {
+    GVC_CHECK_BATCH(count);
+    int frames = 0;
+    for (int i = 0; i < count; ++i) frames = a[i].n_frames > frames ? a[i].n_frames : frames;
+    if (frames < 1 || a[0].lx_hi <= a[0].lx_lo || a[0].ly_hi <= a[0].ly_lo) return GVC_OK;
+    const int per = 65535 / count;                   // gridDim.z <= 65535
+    for (int f0 = 0; f0 < frames; f0 += per) {
+        Batch<LowresBatchArgs> B;
+        fill_batch(B, a, count);
+        int nf = 0;
+        for (int i = 0; i < kMaxBatch; ++i) {
+            LowresBatchArgs &b = B.a[i];
+            const int left = b.n_frames - f0;
+            b.n_frames = left < 0 ? 0 : left < per ? left : per;
+            b.src += (size_t)f0 * b.sframe; b.dst += (size_t)f0 * b.dframe;
+            if (i < count) nf = b.n_frames > nf ? b.n_frames : nf;
+        }
+        lowres_batch_kernel<<<dim3((a[0].lx_hi - a[0].lx_lo + 1023) / 1024, a[0].ly_hi - a[0].ly_lo, nf * count), 256, 0, st>>>(B, nf);
         GVC_CUDA(cudaGetLastError());
     }
     return GVC_OK;
 }
-int launch_hpel(const HpelArgs &a, cudaStream_t st) {
-    if (a.x_hi <= a.x_lo || a.y_hi <= a.y_lo) return GVC_OK;
-    hpel_kernel<<<dim3((a.x_hi - a.x_lo + kHpTileW - 1) / kHpTileW, (a.y_hi - a.y_lo + kHpTileH - 1) / kHpTileH), kHpThreads, 0, st>>>(a);
+int launch_hpel(const HpelArgs *a, int count, cudaStream_t st) {
+    GVC_CHECK_BATCH(count);
+    if (a[0].x_hi <= a[0].x_lo || a[0].y_hi <= a[0].y_lo) return GVC_OK;
+    Batch<HpelArgs> B;
+    fill_batch(B, a, count);
+    hpel_kernel<<<dim3((a[0].x_hi - a[0].x_lo + kHpTileW - 1) / kHpTileW, (a[0].y_hi - a[0].y_lo + kHpTileH - 1) / kHpTileH, count), kHpThreads, 0, st>>>(B);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
-int launch_me_lowres(const MeLowArgs &a, cudaStream_t st) {
-    me_lowres_kernel<<<(a.mbw * a.mbh + kMbWarps - 1) / kMbWarps, 32 * kMbWarps, 0, st>>>(a);
+int launch_me_lowres(const MeLowArgs *a, int count, cudaStream_t st) {
+    GVC_CHECK_BATCH(count);
+    Batch<MeLowArgs> B;
+    fill_batch(B, a, count);
+    me_lowres_kernel<<<dim3((a[0].mbw + kMbWarps - 1) / kMbWarps, a[0].mbh, count), 32 * kMbWarps, 0, st>>>(B);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
-__global__ void signal_picture_kernel(int *done, unsigned *count_out, const unsigned *count_in) {
-    *count_out = *count_in;
+__global__ void signal_picture_kernel(const __grid_constant__ Batch<SignalArgs> B) {
+    const SignalArgs &a = B.a[threadIdx.x];
+    *a.count_out = *a.count_in;
     __threadfence_system();
-    *reinterpret_cast<volatile int *>(done) = 1;
+    *reinterpret_cast<volatile int *>(a.done) = 1;
 }
-int launch_signal_picture(int *done, unsigned *count_out, const unsigned *count_in, cudaStream_t st) {
-    signal_picture_kernel<<<1, 1, 0, st>>>(done, count_out, count_in);
+int launch_signal_picture(const SignalArgs *a, int count, cudaStream_t st) {
+    GVC_CHECK_BATCH(count);
+    Batch<SignalArgs> B;
+    fill_batch(B, a, count);
+    signal_picture_kernel<<<1, count, 0, st>>>(B);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
@@ -383,24 +432,33 @@ static void me_refine_tma(const MeRefArgs &a, MeRefTma &tma) {
     }
     tma.on = 1;
 }
-int launch_me_refine(const MeRefArgs &a, cudaStream_t st) {
-    MeRefTma tma;
-    me_refine_tma(a, tma);
+int launch_me_refine(const MeRefArgs *a, int count, cudaStream_t st) {
+    GVC_CHECK_BATCH(count);
+    Batch<MeRefArgs> B;
+    Batch<MeRefTma>  T;
+    fill_batch(B, a, count);
+    for (int i = 0; i < kMaxBatch; ++i) me_refine_tma(B.a[i], T.a[i]);
     static const bool carve = [] { return cudaFuncSetAttribute(me_refine_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100) == cudaSuccess; }();
     (void)carve;
-    me_refine_kernel<<<dim3((a.mbw + kMeWarps - 1) / kMeWarps, a.mbh), 32 * kMeWarps, 0, st>>>(a, tma.map[0], tma.map[1], tma.map[2], tma.map[3], tma.on);
+    me_refine_kernel<<<dim3((a[0].mbw + kMeWarps - 1) / kMeWarps, a[0].mbh, count), 32 * kMeWarps, 0, st>>>(B, T);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
-int launch_encode_inter(const EncMbArgs &a, cudaStream_t st) {
-    encode_inter_kernel<<<(a.mbw * a.mbh + kMbWarps - 1) / kMbWarps, 32 * kMbWarps, 0, st>>>(a);
+int launch_encode_inter(const EncMbArgs *a, int count, cudaStream_t st) {
+    GVC_CHECK_BATCH(count);
+    Batch<EncMbArgs> B;
+    fill_batch(B, a, count);
+    encode_inter_kernel<<<dim3((a[0].mbw + kMbWarps - 1) / kMbWarps, a[0].mbh, count), 32 * kMbWarps, 0, st>>>(B);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
 
-int launch_encode_intra(const IntraArgs &a, cudaStream_t st) {
-    GVC_CUDA(cudaMemsetAsync(a.mail, 0, sizeof(unsigned long long) * 8 * a.mbw * a.mbh, st));
-    intra_frame_kernel<<<a.mbh, 32, 0, st>>>(a);
+int launch_encode_intra(const IntraArgs *a, int count, cudaStream_t st) {
+    GVC_CHECK_BATCH(count);
+    for (int i = 0; i < count; ++i) GVC_CUDA(cudaMemsetAsync(a[i].mail, 0, sizeof(unsigned long long) * 8 * a[i].mbw * a[i].mbh, st));
+    Batch<IntraArgs> B;
+    fill_batch(B, a, count);
+    intra_frame_kernel<<<dim3(a[0].mbh, count), 32, 0, st>>>(B);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
@@ -438,7 +496,7 @@ int gvc_hpel_filter(const uint8_t *src, uint8_t *dh, uint8_t *dv, uint8_t *dc, i
     a.src = src; a.dh = dh; a.dv = dv; a.dc = dc; a.stride = stride;
     a.x_lo = x_lo; a.x_hi = x_hi; a.y_lo = y_lo; a.y_hi = y_hi;
     a.cx_lo = x_lo; a.cx_hi = x_hi; a.cy_lo = y_lo; a.cy_hi = y_hi;      // the C ABI's region is also the readable part of src
-    return launch_hpel(a, static_cast<cudaStream_t>(stream));
+    return launch_hpel(&a, 1, static_cast<cudaStream_t>(stream));
 }
 
 int gvc_me_lowres(const uint8_t *cur_low, const uint8_t *ref_low, int stride, int mbw, int mbh, int range, int lambda,
@@ -449,7 +507,7 @@ int gvc_me_lowres(const uint8_t *cur_low, const uint8_t *ref_low, int stride, in
     if (range < 0 || range > 22) { set_error("gvc_me_lowres: lowres range %d outside 0..22", range); return GVC_ERR_INVALID_ARG; }
     MeLowArgs a;
     a.cur = cur_low; a.ref = ref_low; a.stride = stride; a.mbw = mbw; a.mbh = mbh; a.r = range; a.lambda = lambda; a.out_mv = out_mv;
-    return launch_me_lowres(a, static_cast<cudaStream_t>(stream));
+    return launch_me_lowres(&a, 1, static_cast<cudaStream_t>(stream));
 }
 
 static RefPlanes to_ref(const gvc_ref_planes *r) {
@@ -469,7 +527,7 @@ int gvc_me_refine(const uint8_t *cur_y, const gvc_ref_planes *ref, int stride, i
     MeRefArgs a;
     a.cur = cur_y; a.ref = to_ref(ref); a.stride = stride; a.w16 = w16; a.h16 = h16; a.mbw = w16 / 16; a.mbh = h16 / 16;
     a.lambda = lambda; a.lowres_mv = lowres_mv; a.out = reinterpret_cast<MbMotion *>(out); a.out_host = nullptr;
-    return launch_me_refine(a, static_cast<cudaStream_t>(stream));
+    return launch_me_refine(&a, 1, static_cast<cudaStream_t>(stream));
 }
 
 int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *cur_v, const gvc_ref_planes *ref, uint8_t *rec_y,
@@ -488,7 +546,7 @@ int gvc_encode_inter(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
     fill_quant_params(a.q, qp, false);
     a.motion = reinterpret_cast<const MbMotion *>(motion); a.coefs = coefs; a.nzmask = nzmask;
     a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr; a.nnz_y = a.nnz_u = a.nnz_v = nullptr;
-    return launch_encode_inter(a, static_cast<cudaStream_t>(stream));
+    return launch_encode_inter(&a, 1, static_cast<cudaStream_t>(stream));
 }
 
 int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *cur_v, uint8_t *rec_y, uint8_t *rec_u, uint8_t *rec_v,
@@ -509,7 +567,7 @@ int gvc_encode_intra(const uint8_t *cur_y, const uint8_t *cur_u, const uint8_t *
     fill_quant_params(a.q, qp, true);
     a.coefs = coefs; a.nzmask = nzmask; a.modes = modes; a.mail = static_cast<unsigned long long *>(scratch);
     a.pack.blocks = nullptr; a.pack.offsets = nullptr; a.pack.counter = nullptr; a.nnz_y = a.nnz_u = a.nnz_v = nullptr;
-    return launch_encode_intra(a, static_cast<cudaStream_t>(stream));
+    return launch_encode_intra(&a, 1, static_cast<cudaStream_t>(stream));
 }
 
 int gvc_transform8x8(const uint8_t *src, int sstride, const uint8_t *pred, int pstride, uint8_t *rec, int rstride, int w, int h, int qp,

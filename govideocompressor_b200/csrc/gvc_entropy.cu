@@ -9,8 +9,10 @@ namespace gvc {
 namespace {
 
 constexpr int kEntWarps = 4;
-__global__ void __launch_bounds__(32 * kEntWarps) ent_mb_kernel(const __grid_constant__ EntropyArgs a) {
+// every kernel of the pass: grid.y = segment of the batch (its EntropyPicture record)
+__global__ void __launch_bounds__(32 * kEntWarps) ent_mb_kernel(const __grid_constant__ Batch<EntropyPicture> B) {
     __shared__ EntSmem sms[kEntWarps];
+    const EntropyArgs &a = B.a[blockIdx.y].ent;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int mb = blockIdx.x * kEntWarps + warp;
     if (mb >= a.mbw * a.mbh) return;
@@ -66,7 +68,8 @@ template <int OP> __device__ __forceinline__ int block_scan(int v, int *warp_par
     return v;
 }
 
-__global__ void __launch_bounds__(kScanThreads) ent_scan_kernel(const __grid_constant__ SliceArgs a) {
+__global__ void __launch_bounds__(kScanThreads) ent_scan_kernel(const __grid_constant__ Batch<EntropyPicture> B) {
+    const SliceArgs &a = B.a[blockIdx.x].slice;
     __shared__ int      part[32];
     __shared__ unsigned counts[4];
     __shared__ int      any_overflow;
@@ -127,14 +130,20 @@ __global__ void __launch_bounds__(kScanThreads) ent_scan_kernel(const __grid_con
     }
 }
 
-__global__ void __launch_bounds__(128) ent_place_kernel(const __grid_constant__ SliceArgs a) {
+__global__ void __launch_bounds__(128) ent_place_kernel(const __grid_constant__ Batch<EntropyPicture> B) {
+    const SliceArgs &a = B.a[blockIdx.y].slice;
     const int mb = blockIdx.x * 128 + threadIdx.x;
     if (mb < a.nmb) ent_place(a, mb);
 }
 
 // slice bytes -> the segment's buffer in mapped host memory, appended after the previous pictures
-__global__ void __launch_bounds__(256) ent_copy_kernel(const uint32_t *slice, const uint32_t *info, uint8_t *host_buf, unsigned host_cap,
-                                                       unsigned *used /* [f], [f+1] */, uint32_t *pos /* host: base, bytes, bits, skipped, p16, p8, intra, error */) {
+__global__ void __launch_bounds__(256) ent_copy_kernel(const __grid_constant__ Batch<EntropyPicture> B) {
+    const EntropyPicture &p = B.a[blockIdx.y];
+    const uint32_t *slice = p.slice.slice, *info = p.slice.info;
+    uint8_t *host_buf = p.host_buf;
+    const unsigned host_cap = p.host_cap;
+    unsigned *used = p.used;        // [f], [f+1]
+    uint32_t *pos = p.pos;          // host: base, bytes, bits, skipped, p16, p8, intra, error
     const unsigned bytes = info[1], base = used[0], padded = (bytes + 15u) & ~15u;
     const bool     fits = info[6] == 0 && base + padded <= host_cap;
     if (fits) {
@@ -155,15 +164,18 @@ __global__ void __launch_bounds__(256) ent_copy_kernel(const uint32_t *slice, co
 
 }  // namespace
 
-int launch_entropy_picture(const EntropyPicture &p, cudaStream_t st) {
-    const int nmb = p.ent.mbw * p.ent.mbh;
-    ent_mb_kernel<<<(nmb + kEntWarps - 1) / kEntWarps, 32 * kEntWarps, 0, st>>>(p.ent);
+int launch_entropy_picture(const EntropyPicture *p, int count, cudaStream_t st) {
+    if (count < 1 || count > kMaxBatch) { set_error("batch of %d segments outside 1..%d", count, kMaxBatch); return GVC_ERR_INVALID_ARG; }
+    Batch<EntropyPicture> B;
+    for (int i = 0; i < kMaxBatch; ++i) B.a[i] = p[i < count ? i : 0];
+    const int nmb = p[0].ent.mbw * p[0].ent.mbh;
+    ent_mb_kernel<<<dim3((nmb + kEntWarps - 1) / kEntWarps, count), 32 * kEntWarps, 0, st>>>(B);
     GVC_CUDA(cudaGetLastError());
-    ent_scan_kernel<<<1, kScanThreads, 0, st>>>(p.slice);
+    ent_scan_kernel<<<count, kScanThreads, 0, st>>>(B);
     GVC_CUDA(cudaGetLastError());
-    ent_place_kernel<<<(nmb + 127) / 128, 128, 0, st>>>(p.slice);
+    ent_place_kernel<<<dim3((nmb + 127) / 128, count), 128, 0, st>>>(B);
     GVC_CUDA(cudaGetLastError());
-    ent_copy_kernel<<<16, 256, 0, st>>>(p.slice.slice, p.slice.info, p.host_buf, p.host_cap, p.used, p.pos);
+    ent_copy_kernel<<<dim3(16, count), 256, 0, st>>>(B);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
