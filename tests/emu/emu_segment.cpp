@@ -34,7 +34,10 @@ struct EmuOps {
     void  release_host(void *p) { free(p); }
     void *device_alias(void *h) { return h; }
     int clear(void *p, size_t n) { memset(p, 0, n); return 0; }
-    int extend_border3(const BorderBatchArgs &a) {      // same (piece, thread) decompositions as the CUDA kernels
+    // the batched stage launchers: one argument record per segment, run one after the other
+    int extend_border3(const BorderBatchArgs *b, int count) { for (int i = 0; i < count; ++i) extend_border3_one(b[i]); return 0; }
+    int lowres_batch(const LowresBatchArgs *b, int count) { for (int i = 0; i < count; ++i) lowres_batch_one(b[i]); return 0; }
+    int extend_border3_one(const BorderBatchArgs &a) {      // same (piece, thread) decompositions as the CUDA kernels
         const bool vec = border16_ok(a);
         for (int f = 0; f < a.n_frames; ++f)
             for (int k = 0; k < 3; ++k) {
@@ -52,7 +55,7 @@ struct EmuOps {
             }
         return 0;
     }
-    int lowres_batch(const LowresBatchArgs &a) {        // the kernel's thread decomposition: four samples per thread
+    int lowres_batch_one(const LowresBatchArgs &a) {        // the kernel's thread decomposition: four samples per thread
         const bool al = lowres_aligned(a);
         for (int f = 0; f < a.n_frames; ++f)
             for (int ly = a.ly_lo; ly < a.ly_hi; ++ly)
@@ -60,13 +63,14 @@ struct EmuOps {
                     lowres_quad(a, al, a.src + size_t(f) * a.sframe, a.dst + size_t(f) * a.dframe, lx, ly);
         return 0;
     }
-    int hpel(const HpelArgs &a) { emu_run_hpel(a); return 0; }
-    int me_lowres(const MeLowArgs &a) { emu_run_me_lowres(a); return 0; }
-    int me_refine(const MeRefArgs &a) { emu_run_me_refine(a); return 0; }
-    int encode_inter(const EncMbArgs &a) { emu_run_encode_inter(a); return 0; }
-    int encode_intra(const IntraArgs &a) { emu_run_encode_intra(a); return 0; }
-    int signal_picture(int *done, unsigned *count_out, const unsigned *count_in) { *count_out = *count_in; *done = 1; return 0; }
-    int entropy_picture(const EntropyPicture &p) {      // the entropy kernels' per-thread bodies, serially; the scan as a plain loop
+    int hpel(const HpelArgs *a, int count) { for (int i = 0; i < count; ++i) emu_run_hpel(a[i]); return 0; }
+    int me_lowres(const MeLowArgs *a, int count) { for (int i = 0; i < count; ++i) emu_run_me_lowres(a[i]); return 0; }
+    int me_refine(const MeRefArgs *a, int count) { for (int i = 0; i < count; ++i) emu_run_me_refine(a[i]); return 0; }
+    int encode_inter(const EncMbArgs *a, int count) { for (int i = 0; i < count; ++i) emu_run_encode_inter(a[i]); return 0; }
+    int encode_intra(const IntraArgs *a, int count) { for (int i = 0; i < count; ++i) emu_run_encode_intra(a[i]); return 0; }
+    int signal_picture(const SignalArgs *a, int count) { for (int i = 0; i < count; ++i) { *a[i].count_out = *a[i].count_in; *a[i].done = 1; } return 0; }
+    int entropy_picture(const EntropyPicture *p, int count) { for (int i = 0; i < count; ++i) entropy_picture_one(p[i]); return 0; }
+    int entropy_picture_one(const EntropyPicture &p) {      // the entropy kernels' per-thread bodies, serially; the scan as a plain loop
         const int nmb = p.ent.mbw * p.ent.mbh;
         for (int mb = 0; mb < nmb; ++mb) {                  // the warp of ent_mb_kernel, lane by lane
             static EntSmem sm;
@@ -192,6 +196,54 @@ int emu_encode_segment(const uint8_t *frames, int n, int w, int h, int fps, int 
     }
     return 0;
 }
+}
+
+// A batch of `count` segments of one shape through ONE SegmentEncoder (they advance together, one emulated launch per stage):
+// frames = all segments' pictures back to back, n[s] pictures each.  annexb receives the streams back to back, annexb_len[s] bytes each.
+extern "C" int emu_encode_batch(const uint8_t *frames, const int *n, int count, int w, int h, int fps, int qp_i, int qp_p, int merange,
+                                uint8_t *annexb, size_t annexb_cap, size_t *annexb_len, int device_entropy) {
+    EmuOps        ops;
+    SegmentConfig cfg;
+    cfg.w = w; cfg.h = h; cfg.fps_num = fps; cfg.fps_den = 1; cfg.qp_i = qp_i; cfg.qp_p = qp_p; cfg.merange = merange;
+    cfg.device_entropy = device_entropy != 0;
+    cfg.max_batch = count;
+    SegmentEncoder<EmuOps> enc(ops, cfg);
+    int nmax = 0;
+    for (int s = 0; s < count; ++s) nmax = std::max(nmax, n[s]);
+    if (enc.reserve(count, nmax)) return -4;
+    const EncGeom   &g  = enc.geom();
+    const PlaneSizes ps = enc.planes();
+    const int cw = (w + 1) / 2, ch = (h + 1) / 2;
+    const uint8_t *src = frames;
+    for (int s = 0; s < count; ++s) {
+        auto cur = enc.cur_frames(s);
+        for (int f = 0; f < n[s]; ++f, src += size_t(w) * h * 3 / 2) {
+            for (int y = 0; y < h; ++y) memcpy(cur.y + ps.y * f + ps.oy + size_t(y) * g.sy, src + size_t(y) * w, w);
+            for (int y = 0; y < ch; ++y) {
+                memcpy(cur.u + ps.c * f + ps.oc + size_t(y) * g.sc, src + size_t(w) * h + size_t(y) * cw, cw);
+                memcpy(cur.v + ps.c * f + ps.oc + size_t(y) * g.sc, src + size_t(w) * h + size_t(cw) * ch + size_t(y) * cw, cw);
+            }
+        }
+    }
+    enc.begin_segment(n, count);
+    int rc = enc.encode_device(n, count);
+    if (rc) return rc;
+    std::vector<SegmentOutput> outs{size_t(count)};
+    if ((rc = enc.finish(outs.data()))) return rc;
+    size_t o = 0;
+    for (int s = 0; s < count; ++s) {
+        const std::vector<uint8_t> &pl = outs[size_t(s)].payload;
+        size_t i = 0, o0 = o;
+        while (i + 4 <= pl.size()) {
+            const size_t len = (size_t(pl[i]) << 24) | (size_t(pl[i + 1]) << 16) | (size_t(pl[i + 2]) << 8) | pl[i + 3];
+            if (o + 4 + len > annexb_cap) return -8;
+            annexb[o] = 0; annexb[o + 1] = 0; annexb[o + 2] = 0; annexb[o + 3] = 1;
+            memcpy(annexb + o + 4, pl.data() + i + 4, len);
+            o += 4 + len; i += 4 + len;
+        }
+        annexb_len[s] = o - o0;
+    }
+    return 0;
 }
 
 // ---- media input (product code media_input.cpp) exercised on the host -------------------------------------

@@ -80,6 +80,24 @@ def encode_segment(frames, w, h, fps=30, qp_i=20, qp_p=23, merange=16, mp4_path=
     return dict(annexb=annexb[: alen.value].tobytes(), recon=recon, stats=stats, w16=w16, h16=h16)
 
 
+def encode_batch(segments, w, h, fps=30, qp_i=20, qp_p=23, merange=16, device_entropy=False):
+    """segments: list of (n_s, w*h*3/2) uint8 arrays encoded TOGETHER by one SegmentEncoder (one emulated launch per stage for
+    the whole batch).  Returns the list of Annex B streams."""
+    lib = load()
+    frames = np.ascontiguousarray(np.concatenate(segments, axis=0), np.uint8)
+    n = (ctypes.c_int * len(segments))(*[s.shape[0] for s in segments])
+    annexb = np.zeros(max(1 << 20, frames.size * 2), np.uint8)
+    lens = (ctypes.c_size_t * len(segments))()
+    lib.emu_encode_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_int] * 6 + [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int]
+    rc = lib.emu_encode_batch(frames.ctypes.data, n, len(segments), w, h, fps, qp_i, qp_p, merange, annexb.ctypes.data, annexb.size, lens, int(device_entropy))
+    assert rc == 0, f"emu_encode_batch failed: {rc}"
+    out, o = [], 0
+    for k in range(len(segments)):
+        out.append(annexb[o:o + lens[k]].tobytes())
+        o += lens[k]
+    return out
+
+
 def ffmpeg_libdir():
     """Directory of the FFmpeg shared libraries bundled in the opencv wheel (for GVC_FFMPEG_LIBDIR), or None."""
     try:
