@@ -111,8 +111,12 @@ struct CudaOps {
         GVC_CUDA(cudaStreamWaitEvent(st, ev_side[slot], 0));
         return 0;
     }
+#if defined(GVC_MEASURE)
     // GVC_DUP_STAGE=<stage index>: measurement aid, issues that stage's launches twice (what does the stage cost in the mix?)
     static int dup_stage() { static const int s = getenv("GVC_DUP_STAGE") ? atoi(getenv("GVC_DUP_STAGE")) : -1; return s; }
+#else
+    static int dup_stage() { return -1; }
+#endif
     template <class F> int timed(int stage, F f) {
         tm.begin(stage, cur());
         int rc = f();
@@ -126,15 +130,15 @@ struct CudaOps {
     void *device_alias(void *h) { void *d = nullptr; return cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess ? d : nullptr; }
     int clear(void *dev, size_t n) { GVC_CUDA(cudaMemsetAsync(dev, 0, n, st)); return 0; }
     void  release_host(void *p) { cudaFreeHost(p); }
-    int extend_border3(const BorderBatchArgs &a) { return timed(kStBorder, [&] { return launch_extend_border_batch(a, cur()); }); }
-    int lowres_batch(const LowresBatchArgs &a) { return timed(kStLowres, [&] { return launch_lowres_batch(a, cur()); }); }
-    int hpel(const HpelArgs &a) { return timed(kStHpel, [&] { return launch_hpel(a, cur()); }); }
-    int me_lowres(const MeLowArgs &a) { return timed(kStMeLowres, [&] { return launch_me_lowres(a, cur()); }); }
-    int me_refine(const MeRefArgs &a) { return timed(kStMeRefine, [&] { return launch_me_refine(a, st); }); }
-    int encode_inter(const EncMbArgs &a) { return timed(kStEncInter, [&] { return launch_encode_inter(a, st); }); }
-    int encode_intra(const IntraArgs &a) { return timed(kStEncIntra, [&] { return launch_encode_intra(a, st); }); }
-    int signal_picture(int *done, unsigned *count_out, const unsigned *count_in) { return launch_signal_picture(done, count_out, count_in, cur()); }
-    int entropy_picture(const EntropyPicture &p) { return timed(kStEntropy, [&] { return launch_entropy_picture(p, cur()); }); }
+    int extend_border3(const BorderBatchArgs *a, int n) { return timed(kStBorder, [&] { return launch_extend_border_batch(a, n, cur()); }); }
+    int lowres_batch(const LowresBatchArgs *a, int n) { return timed(kStLowres, [&] { return launch_lowres_batch(a, n, cur()); }); }
+    int hpel(const HpelArgs *a, int n) { return timed(kStHpel, [&] { return launch_hpel(a, n, cur()); }); }
+    int me_lowres(const MeLowArgs *a, int n) { return timed(kStMeLowres, [&] { return launch_me_lowres(a, n, cur()); }); }
+    int me_refine(const MeRefArgs *a, int n) { return timed(kStMeRefine, [&] { return launch_me_refine(a, n, st); }); }
+    int encode_inter(const EncMbArgs *a, int n) { return timed(kStEncInter, [&] { return launch_encode_inter(a, n, st); }); }
+    int encode_intra(const IntraArgs *a, int n) { return timed(kStEncIntra, [&] { return launch_encode_intra(a, n, st); }); }
+    int signal_picture(const SignalArgs *a, int n) { return launch_signal_picture(a, n, cur()); }
+    int entropy_picture(const EntropyPicture *p, int n) { return timed(kStEntropy, [&] { return launch_entropy_picture(p, n, cur()); }); }
     int copy_plane(uint8_t *dst, int dpitch, const uint8_t *src, int spitch, int w, int h) {
         GVC_CUDA(cudaMemcpy2DAsync(dst, dpitch, src, spitch, w, h, cudaMemcpyDeviceToHost, st));
         return 0;
@@ -149,22 +153,26 @@ struct gvc_encoder {
     CudaOps            ops;
     SegmentEncoder<CudaOps> *seg = nullptr;
     gvc_resize_plan   *plan = nullptr;
-    // staging for host-supplied source pictures: two buffers so the next segment can upload (on its own copy stream)
-    // while the current one is being encoded
+    int                max_batch = 1;
+    // staging for host-supplied source pictures: two buffers (each holds a whole batch) so the next batch can upload (on its
+    // own copy stream) while the current one is being encoded
     uint8_t           *d_src[2] = {nullptr, nullptr};
     size_t             d_src_cap[2] = {0, 0};
-    int                d_src_frames[2] = {0, 0};
+    std::vector<size_t> d_src_off[2];          // per segment of the batch: where its pictures start in the buffer
+    std::vector<int>   d_src_frames[2];
     cudaStream_t       copy_stream = nullptr;
     cudaEvent_t        uploaded[2] = {nullptr, nullptr};
-    int                up_next = 0, up_pending = 0;     // next buffer to fill, number of uploaded-but-not-encoded segments
-    SegmentOutput      out;
-    int                n_last = 0;
+    cudaEvent_t        consumed[2] = {nullptr, nullptr};     // the resize that read staging buffer b has run: b may be overwritten
+    bool               consumed_valid[2] = {false, false};
+    int                up_next = 0, up_pending = 0;     // next buffer to fill, number of uploaded-but-not-encoded batches
+    std::vector<SegmentOutput> outs;           // one per segment of the last finished batch
+    int                lanes_last = 0, selected = 0;    // segments in the last batch; the one stats / recon / write_mp4 refer to
     bool               pending = false;
     double             ms_kernels = 0, ms_entropy = 0;
-    // the per-picture kernel chain of a segment (everything after the resize) captured once and replayed
+    // the per-picture kernel chain of a batch (everything after the resize) captured once per batch shape and replayed
     cudaGraph_t        graph = nullptr;
     cudaGraphExec_t    graph_exec = nullptr;
-    int                graph_n = 0;
+    std::vector<int>   graph_n;
 };
 
 namespace {
@@ -173,49 +181,72 @@ double now_ms() {
     static const auto t0 = std::chrono::steady_clock::now();
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
-bool tracing() { static const bool on = getenv("GVC_TRACE") != nullptr; return on; }
+#if defined(GVC_MEASURE)
+bool tracing() { static const bool on = getenv("GVC_TRACE") != nullptr; return on; }     // timeline of issue / finish on stderr
+#else
+constexpr bool tracing() { return false; }
+#endif
 
 size_t i420_bytes(int w, int h) { return size_t(w) * h + 2 * size_t((w + 1) / 2) * ((h + 1) / 2); }
 
-// issue resize (source I420 on the device -> padded current pictures) and every encoder kernel
-int issue_segment(gvc_encoder *e, const uint8_t *d_frames, int n) {
-    int rc = e->seg->reserve(n);
-    if (rc) { set_error("out of device memory reserving %d pictures", n); return rc; }
+// issue resize (source I420 on the device -> padded current pictures) and every encoder kernel for a batch of segments;
+// staging >= 0: the pictures sit in that staging buffer, which may be refilled once the resizes have read it
+int issue_batch(gvc_encoder *e, const uint8_t *const *d_frames, const int *n, int count, int staging) {
+    if (count < 1 || count > e->max_batch) { set_error("batch of %d segments outside 1..%d (gvc_encoder_config.max_batch)", count, e->max_batch); return GVC_ERR_INVALID_ARG; }
+    int nmax = 0;
+    for (int s = 0; s < count; ++s) {
+        if (!d_frames[s] || n[s] < 1) { set_error("segment %d of the batch: null pictures or no pictures", s); return GVC_ERR_INVALID_ARG; }
+        nmax = std::max(nmax, n[s]);
+    }
+    int rc = e->seg->reserve(count, nmax);
+    if (rc) { set_error("out of device memory reserving %d segments of %d pictures", count, nmax); return rc; }
     const EncGeom   &g  = e->seg->geom();
     const PlaneSizes ps = e->seg->planes();
-    auto cur = e->seg->cur_frames();
     const int sw = e->cfg.src_w, sh = e->cfg.src_h, scw = (sw + 1) / 2, sch = (sh + 1) / 2;
-    gvc_frames src, dst;
-    src.plane[0] = const_cast<uint8_t *>(d_frames);
-    src.plane[1] = src.plane[0] + size_t(sw) * sh;
-    src.plane[2] = src.plane[1] + size_t(scw) * sch;
-    src.stride[0] = sw; src.stride[1] = src.stride[2] = scw;
-    src.frame_stride[0] = src.frame_stride[1] = src.frame_stride[2] = i420_bytes(sw, sh);
-    dst.plane[0] = cur.y + ps.oy; dst.plane[1] = cur.u + ps.oc; dst.plane[2] = cur.v + ps.oc;
-    dst.stride[0] = g.sy; dst.stride[1] = dst.stride[2] = g.sc;
-    dst.frame_stride[0] = ps.y; dst.frame_stride[1] = dst.frame_stride[2] = ps.c;
-    if ((rc = e->ops.timed(kStResize, [&] { return gvc_resize_frames_device(e->plan, &src, &dst, n, e->ops.st); }))) return rc;
-    e->seg->begin_segment(n);
+    rc = e->ops.timed(kStResize, [&] {
+        for (int s = 0; s < count; ++s) {
+            auto cur = e->seg->cur_frames(s);
+            gvc_frames src, dst;
+            src.plane[0] = const_cast<uint8_t *>(d_frames[s]);
+            src.plane[1] = src.plane[0] + size_t(sw) * sh;
+            src.plane[2] = src.plane[1] + size_t(scw) * sch;
+            src.stride[0] = sw; src.stride[1] = src.stride[2] = scw;
+            src.frame_stride[0] = src.frame_stride[1] = src.frame_stride[2] = i420_bytes(sw, sh);
+            dst.plane[0] = cur.y + ps.oy; dst.plane[1] = cur.u + ps.oc; dst.plane[2] = cur.v + ps.oc;
+            dst.stride[0] = g.sy; dst.stride[1] = dst.stride[2] = g.sc;
+            dst.frame_stride[0] = ps.y; dst.frame_stride[1] = dst.frame_stride[2] = ps.c;
+            const int r = gvc_resize_frames_device(e->plan, &src, &dst, n[s], e->ops.st);
+            if (r) return r;
+        }
+        return 0;
+    });
+    if (rc) return rc;
+    if (staging >= 0) {
+        GVC_CUDA(cudaEventRecord(e->consumed[staging], e->ops.st));
+        e->consumed_valid[staging] = true;
+    }
+    e->seg->begin_segment(n, count);
     const bool use_graph = !e->cfg.disable_graph && !e->cfg.keep_recon && !e->ops.tm.on;
     if (!use_graph) {
-        if ((rc = e->seg->encode_device(n))) return rc;
+        if ((rc = e->seg->encode_device(n, count))) return rc;
     } else {
-        if (!e->graph_exec || e->graph_n != n) {       // ~12 launches per picture: capture once per segment length
+        const std::vector<int> shape(n, n + count);
+        if (!e->graph_exec || e->graph_n != shape) {       // ~11 launches per picture: capture once per batch shape
             if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
             if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
             GVC_CUDA(cudaStreamBeginCapture(e->ops.st, cudaStreamCaptureModeThreadLocal));
-            rc = e->seg->encode_device(n);
+            rc = e->seg->encode_device(n, count);
             cudaError_t ce = cudaStreamEndCapture(e->ops.st, &e->graph);
             if (rc) return rc;
             if (ce != cudaSuccess) { set_error("stream capture failed: %s", cudaGetErrorString(ce)); return GVC_ERR_CUDA; }
             GVC_CUDA(cudaGraphInstantiate(&e->graph_exec, e->graph, 0));
-            e->graph_n = n;
+            e->graph_n = shape;
         } else {
-            e->seg->set_frame_count(n);
+            e->seg->set_frame_counts(n, count);
         }
         GVC_CUDA(cudaGraphLaunch(e->graph_exec, e->ops.st));
     }
-    e->n_last = n;
+    e->lanes_last = count;
     e->pending = true;
     return GVC_OK;
 }
@@ -259,9 +290,12 @@ int gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg) {
     if ((c.src_w | c.src_h | c.dst_w | c.dst_h) & 1) { set_error("odd picture sizes are not supported by the 4:2:0 encoder"); return GVC_ERR_UNSUPPORTED; }
     if (c.crf < 0 || c.crf > 51) { set_error("crf %d outside 0..51", c.crf); return GVC_ERR_INVALID_ARG; }
     if (c.merange < 4 || c.merange > 44) { set_error("merange %d outside 4..44", c.merange); return GVC_ERR_INVALID_ARG; }
+    if (c.max_batch <= 0) c.max_batch = 1;
+    if (c.max_batch > kMaxBatch) { set_error("max_batch %d above the limit of %d segments per batch", c.max_batch, kMaxBatch); return GVC_ERR_INVALID_ARG; }
     gvc_encoder *e = new (std::nothrow) gvc_encoder;
     if (!e) return GVC_ERR_NOMEM;
     e->cfg = c;
+    e->max_batch = c.max_batch;
     if (cudaStreamCreateWithFlags(&e->ops.st, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&e->ops.side, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&e->ops.ev_fork, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&e->ops.ev_side[0], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&e->ops.ev_side[1], cudaEventDisableTiming) != cudaSuccess ||
@@ -278,6 +312,7 @@ int gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg) {
     sc.qp_p = c.crf; sc.qp_i = c.crf >= 3 ? c.crf - 3 : 0;     // x264's default ip_factor 1.4 is about 3 QP
     sc.merange = c.merange; sc.keep_recon = c.keep_recon != 0;
     sc.device_entropy = c.entropy != GVC_ENTROPY_HOST;
+    sc.max_batch = c.max_batch;
     sc.host_threads = c.host_threads > 0 ? c.host_threads : int(std::max(1u, std::thread::hardware_concurrency()));
     e->seg = new (std::nothrow) SegmentEncoder<CudaOps>(e->ops, sc);
     if (!e->seg) { gvc_encoder_destroy(e); return GVC_ERR_NOMEM; }
@@ -293,7 +328,7 @@ void gvc_encoder_destroy(gvc_encoder *e) {
     if (e->graph) cudaGraphDestroy(e->graph);
     delete e->seg;
     if (e->plan) gvc_resize_plan_destroy(e->plan);
-    for (int b = 0; b < 2; ++b) { if (e->d_src[b]) cudaFree(e->d_src[b]); if (e->uploaded[b]) cudaEventDestroy(e->uploaded[b]); }
+    for (int b = 0; b < 2; ++b) { if (e->d_src[b]) cudaFree(e->d_src[b]); if (e->uploaded[b]) cudaEventDestroy(e->uploaded[b]); if (e->consumed[b]) cudaEventDestroy(e->consumed[b]); }
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     if (e->ops.side) cudaStreamDestroy(e->ops.side);
     for (int b = 0; b < 2; ++b) { if (e->ops.aux[b]) cudaStreamDestroy(e->ops.aux[b]); if (e->ops.ev_aux[b]) cudaEventDestroy(e->ops.ev_aux[b]); }
@@ -304,11 +339,14 @@ void gvc_encoder_destroy(gvc_encoder *e) {
     delete e;
 }
 
-int gvc_encoder_encode_device(gvc_encoder *e, const uint8_t *d_frames_i420, int n_frames) {
+int gvc_encoder_encode_device_batch(gvc_encoder *e, const uint8_t *const *d_frames_i420, const int *n_frames, int count) {
     int rc = enter();
     if (rc) return rc;
-    if (!e || !d_frames_i420 || n_frames < 1) { set_error("gvc_encoder_encode_device: bad arguments"); return GVC_ERR_INVALID_ARG; }
-    return issue_segment(e, d_frames_i420, n_frames);
+    if (!e || !d_frames_i420 || !n_frames) { set_error("gvc_encoder_encode_device_batch: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    return issue_batch(e, d_frames_i420, n_frames, count, -1);
+}
+int gvc_encoder_encode_device(gvc_encoder *e, const uint8_t *d_frames_i420, int n_frames) {
+    return gvc_encoder_encode_device_batch(e, &d_frames_i420, &n_frames, 1);
 }
 
 int gvc_encoder_sync(gvc_encoder *e) {
@@ -338,32 +376,59 @@ int gvc_encoder_stage_times(gvc_encoder *e, double *ms8, int *launches8) {   // 
 
 void *gvc_encoder_stream(gvc_encoder *e) { return e ? static_cast<void *>(e->ops.st) : nullptr; }
 
-int gvc_encoder_finish(gvc_encoder *e, int annexb, uint8_t **out, size_t *out_len) {
+int gvc_encoder_finish_batch(gvc_encoder *e, int annexb, uint8_t **out, size_t *out_len) {
     int rc = enter();
     if (rc) return rc;
     if (!e || !e->pending) { set_error("gvc_encoder_finish: no segment in flight"); return GVC_ERR_INVALID_ARG; }
     const auto t0 = std::chrono::steady_clock::now();
     if (tracing()) fprintf(stderr, "[gvc %p] %.2f finish begin\n", (void *)e, now_ms());
-    if ((rc = e->seg->finish(e->out))) return rc;
+    if (e->outs.size() < size_t(e->lanes_last)) e->outs.resize(size_t(e->lanes_last));
+    if ((rc = e->seg->finish(e->outs.data()))) { set_error("the coded pictures outgrew the slice buffers (twice the raw pictures)"); return rc; }
     if (tracing()) fprintf(stderr, "[gvc %p] %.2f finish end\n", (void *)e, now_ms());
     e->ms_entropy = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     e->pending = false;
-    if (out && out_len) {
-        *out = to_stream(e->out, annexb, out_len);
-        if (!*out) return GVC_ERR_NOMEM;
-    }
+    e->selected = 0;
+    if (out && out_len)
+        for (int s = 0; s < e->lanes_last; ++s) {
+            out[s] = to_stream(e->outs[size_t(s)], annexb, &out_len[s]);
+            if (!out[s]) { for (int k = 0; k < s; ++k) { free(out[k]); out[k] = nullptr; } return GVC_ERR_NOMEM; }
+        }
+    return GVC_OK;
+}
+int gvc_encoder_finish(gvc_encoder *e, int annexb, uint8_t **out, size_t *out_len) {
+    if (e && e->pending && e->lanes_last != 1 && out) { set_error("gvc_encoder_finish: %d segments in flight, use gvc_encoder_finish_batch", e->lanes_last); return GVC_ERR_INVALID_ARG; }
+    return gvc_encoder_finish_batch(e, annexb, out, out_len);
+}
+
+int gvc_encoder_select(gvc_encoder *e, int segment) {
+    if (!e || segment < 0 || segment >= e->lanes_last) { set_error("gvc_encoder_select: segment %d outside the last batch", segment); return GVC_ERR_INVALID_ARG; }
+    e->selected = segment;
     return GVC_OK;
 }
 
-int gvc_encoder_upload_host(gvc_encoder *e, const uint8_t *frames_i420, int n_frames) {
+int gvc_encoder_upload_host_batch(gvc_encoder *e, const uint8_t *const *frames_i420, const int *n_frames, int count) {
     int rc = enter();
     if (rc) return rc;
-    if (!e || !frames_i420 || n_frames < 1) { set_error("gvc_encoder_upload_host: bad arguments"); return GVC_ERR_INVALID_ARG; }
-    if (e->up_pending >= 2) { set_error("gvc_encoder_upload_host: two segments are already waiting to be encoded"); return GVC_ERR_INVALID_ARG; }
+    if (!e || !frames_i420 || !n_frames || count < 1 || count > e->max_batch) { set_error("gvc_encoder_upload_host: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    if (e->up_pending >= 2) { set_error("gvc_encoder_upload_host: two batches are already waiting to be encoded"); return GVC_ERR_INVALID_ARG; }
     if (!e->copy_stream) GVC_CUDA(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
     const int    b = e->up_next;
-    const size_t bytes = i420_bytes(e->cfg.src_w, e->cfg.src_h) * n_frames;
+    const size_t fb = i420_bytes(e->cfg.src_w, e->cfg.src_h);
+    size_t bytes = 0;
+    e->d_src_off[b].assign(size_t(count), 0);
+    e->d_src_frames[b].assign(n_frames, n_frames + count);
+    for (int s = 0; s < count; ++s) {
+        if (!frames_i420[s] || n_frames[s] < 1) { set_error("gvc_encoder_upload_host: segment %d has no pictures", s); return GVC_ERR_INVALID_ARG; }
+        e->d_src_off[b][size_t(s)] = bytes;
+        bytes += (fb * size_t(n_frames[s]) + 255) & ~size_t(255);
+    }
     if (!e->uploaded[b]) GVC_CUDA(cudaEventCreateWithFlags(&e->uploaded[b], cudaEventDisableTiming));
+    if (!e->consumed[b]) GVC_CUDA(cudaEventCreateWithFlags(&e->consumed[b], cudaEventDisableTiming));
+    // the resize kernels of the batch that last used this buffer must have read it before it is overwritten (or freed)
+    if (e->consumed_valid[b]) {
+        if (e->d_src_cap[b] < bytes) GVC_CUDA(cudaEventSynchronize(e->consumed[b]));
+        else GVC_CUDA(cudaStreamWaitEvent(e->copy_stream, e->consumed[b], 0));
+    }
     if (e->d_src_cap[b] < bytes) {
         if (e->d_src[b]) cudaFree(e->d_src[b]);
         e->d_src[b] = nullptr; e->d_src_cap[b] = 0;
@@ -371,12 +436,15 @@ int gvc_encoder_upload_host(gvc_encoder *e, const uint8_t *frames_i420, int n_fr
         e->d_src_cap[b] = bytes;
     }
     if (tracing()) fprintf(stderr, "[gvc %p] %.2f upload issue buf %d\n", (void *)e, now_ms(), b);
-    GVC_CUDA(cudaMemcpyAsync(e->d_src[b], frames_i420, bytes, cudaMemcpyHostToDevice, e->copy_stream));
+    for (int s = 0; s < count; ++s)
+        GVC_CUDA(cudaMemcpyAsync(e->d_src[b] + e->d_src_off[b][size_t(s)], frames_i420[s], fb * size_t(n_frames[s]), cudaMemcpyHostToDevice, e->copy_stream));
     GVC_CUDA(cudaEventRecord(e->uploaded[b], e->copy_stream));
-    e->d_src_frames[b] = n_frames;
     e->up_next ^= 1;
     ++e->up_pending;
     return GVC_OK;
+}
+int gvc_encoder_upload_host(gvc_encoder *e, const uint8_t *frames_i420, int n_frames) {
+    return gvc_encoder_upload_host_batch(e, &frames_i420, &n_frames, 1);
 }
 
 int gvc_encoder_encode_uploaded(gvc_encoder *e) {
@@ -387,7 +455,10 @@ int gvc_encoder_encode_uploaded(gvc_encoder *e) {
     GVC_CUDA(cudaStreamWaitEvent(e->ops.st, e->uploaded[b], 0));
     --e->up_pending;
     const double t0 = now_ms();
-    rc = issue_segment(e, e->d_src[b], e->d_src_frames[b]);
+    const int count = int(e->d_src_frames[b].size());
+    const uint8_t *ptr[kMaxBatch];
+    for (int s = 0; s < count; ++s) ptr[s] = e->d_src[b] + e->d_src_off[b][size_t(s)];
+    rc = issue_batch(e, ptr, e->d_src_frames[b].data(), count, b);
     if (tracing()) fprintf(stderr, "[gvc %p] %.2f encode issued (%.2f ms on the host)\n", (void *)e, now_ms(), now_ms() - t0);
     return rc;
 }
@@ -399,31 +470,38 @@ int gvc_encoder_encode_host(gvc_encoder *e, const uint8_t *frames_i420, int n_fr
     return gvc_encoder_finish(e, annexb, out, out_len);
 }
 
+static const SegmentOutput *selected_output(gvc_encoder *e) {
+    return e && size_t(e->selected) < e->outs.size() ? &e->outs[size_t(e->selected)] : nullptr;
+}
+
 int gvc_encoder_recon(gvc_encoder *e, uint8_t *dst, size_t cap) {
-    if (!e || !dst) { set_error("gvc_encoder_recon: bad arguments"); return GVC_ERR_INVALID_ARG; }
-    if (e->out.recon.empty()) { set_error("the encoder was created without keep_recon"); return GVC_ERR_INVALID_ARG; }
-    if (cap < e->out.recon.size()) { set_error("recon buffer too small: need %zu bytes", e->out.recon.size()); return GVC_ERR_TOO_LARGE; }
-    memcpy(dst, e->out.recon.data(), e->out.recon.size());
+    const SegmentOutput *o = selected_output(e);
+    if (!o || !dst) { set_error("gvc_encoder_recon: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    if (o->recon.empty()) { set_error("the encoder was created without keep_recon"); return GVC_ERR_INVALID_ARG; }
+    if (cap < o->recon.size()) { set_error("recon buffer too small: need %zu bytes", o->recon.size()); return GVC_ERR_TOO_LARGE; }
+    memcpy(dst, o->recon.data(), o->recon.size());
     return GVC_OK;
 }
 
 int gvc_encoder_stats(gvc_encoder *e, int *stats4_per_picture, int n_pictures) {
-    if (!e || !stats4_per_picture) { set_error("gvc_encoder_stats: bad arguments"); return GVC_ERR_INVALID_ARG; }
-    for (int f = 0; f < n_pictures && f < (int)e->out.stats.size(); ++f) {
-        stats4_per_picture[4 * f] = e->out.stats[f].skipped; stats4_per_picture[4 * f + 1] = e->out.stats[f].p16;
-        stats4_per_picture[4 * f + 2] = e->out.stats[f].p8; stats4_per_picture[4 * f + 3] = int(e->out.au_size[f]);
+    const SegmentOutput *o = selected_output(e);
+    if (!o || !stats4_per_picture) { set_error("gvc_encoder_stats: bad arguments"); return GVC_ERR_INVALID_ARG; }
+    for (int f = 0; f < n_pictures && f < (int)o->stats.size(); ++f) {
+        stats4_per_picture[4 * f] = o->stats[f].skipped; stats4_per_picture[4 * f + 1] = o->stats[f].p16;
+        stats4_per_picture[4 * f + 2] = o->stats[f].p8; stats4_per_picture[4 * f + 3] = int(o->au_size[f]);
     }
     return GVC_OK;
 }
 
-long long gvc_encoder_record_bytes(gvc_encoder *e) { return e && e->seg ? (long long)e->seg->record_bytes() : -1; }
+long long gvc_encoder_record_bytes(gvc_encoder *e) { return e && e->seg && e->selected < e->lanes_last ? (long long)e->seg->record_bytes(e->selected) : -1; }
 
 int gvc_encoder_write_mp4(gvc_encoder *e, const char *path) {
-    if (!e || !path || e->out.au_size.empty()) { set_error("gvc_encoder_write_mp4: nothing encoded"); return GVC_ERR_INVALID_ARG; }
+    const SegmentOutput *o = selected_output(e);
+    if (!o || !path || o->au_size.empty()) { set_error("gvc_encoder_write_mp4: nothing encoded"); return GVC_ERR_INVALID_ARG; }
     std::vector<Mp4Sample> samples;
-    for (size_t f = 0; f < e->out.au_size.size(); ++f) samples.push_back(Mp4Sample{e->out.au_offset[f], e->out.au_size[f], f == 0});
+    for (size_t f = 0; f < o->au_size.size(); ++f) samples.push_back(Mp4Sample{o->au_offset[f], o->au_size[f], f == 0});
     std::string err, tmp = std::string(path) + ".gvc.tmp";
-    if (!write_mp4(tmp, e->cfg.dst_w, e->cfg.dst_h, e->cfg.fps_num, e->cfg.fps_den, e->out.sps_nal, e->out.pps_nal, e->out.payload, samples, err)) {
+    if (!write_mp4(tmp, e->cfg.dst_w, e->cfg.dst_h, e->cfg.fps_num, e->cfg.fps_den, o->sps_nal, o->pps_nal, o->payload, samples, err)) {
         set_error("%s", err.c_str());
         return GVC_ERR_IO;
     }
@@ -485,12 +563,13 @@ int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char 
         if (n < gop) eof = true;
         if (rc || n == 0) break;
         if ((rc = gvc_encoder_encode_host(e, host, n, 0, nullptr, nullptr))) break;
-        if (sps.empty()) { sps = e->out.sps_nal; pps = e->out.pps_nal; }
+        const SegmentOutput &so = e->outs[0];
+        if (sps.empty()) { sps = so.sps_nal; pps = so.pps_nal; }
         for (int i = 0; i < n; ++i) {
-            samples.push_back(Mp4Sample{payload.size() + e->out.au_offset[i], e->out.au_size[i], i == 0});
-            n_skip += e->out.stats[i].skipped; n_p16 += e->out.stats[i].p16; n_p8 += e->out.stats[i].p8; n_intra += e->out.stats[i].intra;
+            samples.push_back(Mp4Sample{payload.size() + so.au_offset[i], so.au_size[i], i == 0});
+            n_skip += so.stats[i].skipped; n_p16 += so.stats[i].p16; n_p8 += so.stats[i].p8; n_intra += so.stats[i].intra;
         }
-        payload.insert(payload.end(), e->out.payload.begin(), e->out.payload.end());
+        payload.insert(payload.end(), so.payload.begin(), so.payload.end());
         total += n;
     }
     cudaFreeHost(host);

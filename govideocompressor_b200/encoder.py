@@ -15,7 +15,7 @@ from . import lib as _lib
 class EncoderConfig(ctypes.Structure):
     """struct gvc_encoder_config"""
     _fields_ = [(n, ctypes.c_int) for n in ("src_w", "src_h", "dst_w", "dst_h", "fps_num", "fps_den", "crf", "merange",
-                                            "scale_algo", "keep_recon", "host_threads", "disable_graph", "entropy")]
+                                            "scale_algo", "keep_recon", "host_threads", "disable_graph", "entropy", "max_batch")]
 
 
 def _bind(lib):
@@ -33,6 +33,10 @@ def _bind(lib):
     lib.gvc_encoder_stream.argtypes = [vp]
     lib.gvc_encoder_stream.restype = vp
     lib.gvc_encoder_finish.argtypes = [vp, ci, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
+    lib.gvc_encoder_upload_host_batch.argtypes = [vp, vp, vp, ci]
+    lib.gvc_encoder_encode_device_batch.argtypes = [vp, vp, vp, ci]
+    lib.gvc_encoder_finish_batch.argtypes = [vp, ci, vp, vp]
+    lib.gvc_encoder_select.argtypes = [vp, ci]
     lib.gvc_encoder_recon.argtypes = [vp, vp, ctypes.c_size_t]
     lib.gvc_encoder_stats.argtypes = [vp, vp, ci]
     lib.gvc_encoder_write_mp4.argtypes = [vp, ctypes.c_char_p]
@@ -46,10 +50,10 @@ def _bind(lib):
 
 class Encoder:
     def __init__(self, src_w, src_h, dst_w=0, dst_h=0, fps=(30, 1), crf=23, merange=16, scale_algo=4, keep_recon=False, host_threads=0,
-                 disable_graph=False, entropy=0):
+                 disable_graph=False, entropy=0, max_batch=1):
         self._lib = _lib.load_library()
         _bind(self._lib)
-        self.cfg = EncoderConfig(src_w, src_h, dst_w, dst_h, fps[0], fps[1], crf, merange, scale_algo, int(keep_recon), host_threads, int(disable_graph), int(entropy))
+        self.cfg = EncoderConfig(src_w, src_h, dst_w, dst_h, fps[0], fps[1], crf, merange, scale_algo, int(keep_recon), host_threads, int(disable_graph), int(entropy), int(max_batch))
         self.src_w, self.src_h = src_w, src_h
         self.dst_w, self.dst_h = dst_w or src_w, dst_h or src_h
         self.w16, self.h16 = (self.dst_w + 15) // 16 * 16, (self.dst_h + 15) // 16 * 16
@@ -83,29 +87,73 @@ class Encoder:
         out, ln = ctypes.c_void_p(), ctypes.c_size_t()
         _lib.check(self._lib.gvc_encoder_encode_host(self._h, ctypes.c_void_p(ptr), n, int(annexb), ctypes.byref(out), ctypes.byref(ln)),
                    "gvc_encoder_encode_host")
+        self._counts = [n]
         self.n_last = n
         return self._take(out, ln)
 
     def encode_host_discard(self, ptr, n):
         """Same work, stream kept inside the encoder (bench: no Python-side copy)."""
         _lib.check(self._lib.gvc_encoder_encode_host(self._h, ctypes.c_void_p(ptr), n, 0, None, None), "gvc_encoder_encode_host")
+        self._counts = [n]
         self.n_last = n
 
     def upload_host(self, ptr, n):
         """Start the asynchronous upload of a segment (pinned host memory); up to two may be pending."""
         _lib.check(self._lib.gvc_encoder_upload_host(self._h, ctypes.c_void_p(ptr), n), "gvc_encoder_upload_host")
-        self._n_uploaded = getattr(self, "_n_uploaded", []) + [n]
+        self._n_uploaded = getattr(self, "_n_uploaded", []) + [[n]]
 
     def encode_uploaded(self):
         _lib.check(self._lib.gvc_encoder_encode_uploaded(self._h), "gvc_encoder_encode_uploaded")
-        self.n_last = self._n_uploaded.pop(0)
+        self._counts = self._n_uploaded.pop(0)
+        self.n_last = self._counts[0]
 
     def finish_discard(self):
         _lib.check(self._lib.gvc_encoder_finish(self._h, 0, None, None), "gvc_encoder_finish")
 
     def encode_device(self, dev_ptr, n):
         _lib.check(self._lib.gvc_encoder_encode_device(self._h, ctypes.c_void_p(dev_ptr), n), "gvc_encoder_encode_device")
+        self._counts = [n]
         self.n_last = n
+
+    # ---- batches: several segments of the encoder's shape encoded together, one launch per stage for all of them
+    @staticmethod
+    def _batch_args(ptrs, counts):
+        k = len(ptrs)
+        return (ctypes.c_void_p * k)(*[int(p) for p in ptrs]), (ctypes.c_int * k)(*[int(c) for c in counts]), k
+
+    def encode_device_batch(self, dev_ptrs, counts):
+        """dev_ptrs[s]: device address of segment s's I420 pictures, counts[s] of them.  Issues the kernels only."""
+        P, N, k = self._batch_args(dev_ptrs, counts)
+        _lib.check(self._lib.gvc_encoder_encode_device_batch(self._h, P, N, k), "gvc_encoder_encode_device_batch")
+        self._counts = list(counts)
+        self.n_last = counts[0]
+
+    def upload_host_batch(self, host_ptrs, counts):
+        P, N, k = self._batch_args(host_ptrs, counts)
+        _lib.check(self._lib.gvc_encoder_upload_host_batch(self._h, P, N, k), "gvc_encoder_upload_host_batch")
+        self._n_uploaded = getattr(self, "_n_uploaded", []) + [list(counts)]
+
+    def finish_batch(self, annexb=True, keep=True):
+        """Completes the batch in flight; returns the list of streams (or None with keep=False: they stay in the encoder)."""
+        k = len(self._counts)
+        if not keep:
+            _lib.check(self._lib.gvc_encoder_finish_batch(self._h, int(annexb), None, None), "gvc_encoder_finish_batch")
+            return None
+        outs, lens = (ctypes.c_void_p * k)(), (ctypes.c_size_t * k)()
+        _lib.check(self._lib.gvc_encoder_finish_batch(self._h, int(annexb), outs, lens), "gvc_encoder_finish_batch")
+        return [self._take(ctypes.c_void_p(outs[i]), ctypes.c_size_t(lens[i])) for i in range(k)]
+
+    def encode_host_batch(self, segments, annexb=True):
+        """segments: list of uint8 arrays (n_s, frame_bytes).  Returns the list of streams."""
+        segs = [np.ascontiguousarray(s, np.uint8) for s in segments]
+        self.upload_host_batch([s.ctypes.data for s in segs], [s.shape[0] for s in segs])
+        self.encode_uploaded()
+        return self.finish_batch(annexb)
+
+    def select(self, segment):
+        """Which segment of the last finished batch recon() / stats() / record_bytes() / write_mp4() refer to."""
+        _lib.check(self._lib.gvc_encoder_select(self._h, segment), "gvc_encoder_select")
+        self.n_last = self._counts[segment]
 
     def sync(self):
         _lib.check(self._lib.gvc_encoder_sync(self._h), "gvc_encoder_sync")

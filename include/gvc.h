@@ -189,7 +189,9 @@ typedef struct gvc_encoder_config {
     int host_threads;          /* entropy-coding threads, 0 = all host cores */
     int disable_graph;         /* 1 = launch every kernel individually instead of replaying a captured CUDA graph */
     int entropy;               /* GVC_ENTROPY_*: where the CAVLC slice data is written; the streams are bit-identical */
+    int max_batch;             /* segments one call may encode together (gvc_encoder_*_batch), 0/1 = one; <= GVC_MAX_BATCH */
 } gvc_encoder_config;
+#define GVC_MAX_BATCH 16
 #define GVC_ENTROPY_DEFAULT 0  /* = GVC_ENTROPY_DEVICE */
 #define GVC_ENTROPY_HOST    1  /* host threads code the kernels' per-macroblock records (h264_stream.cpp) */
 #define GVC_ENTROPY_DEVICE  2  /* entropy kernels: the finished slices cross PCIe, not the records */
@@ -206,6 +208,17 @@ int gvc_encoder_encode_host(gvc_encoder *enc, const uint8_t *frames_i420, int n_
  * of the previous one); gvc_encoder_finish collects the stream. */
 int gvc_encoder_upload_host(gvc_encoder *enc, const uint8_t *frames_i420, int n_frames);
 int gvc_encoder_encode_uploaded(gvc_encoder *enc);
+/* Batches.  Segments share nothing (server.go:176-190 hands whole pieces to workers), so up to cfg.max_batch segments of the
+ * encoder's shape are encoded TOGETHER: they advance picture by picture in lockstep and every stage is one kernel launch for
+ * all of them (lengths may differ; a shorter segment drops out of the later launches).  The streams are byte-identical to the
+ * ones the segments give when encoded one at a time.  frames[s] / n_frames[s] describe segment s; finish_batch fills out[s] /
+ * out_len[s] (each gvc_free'd by the caller; both arrays may be NULL).  The single-segment calls above are batches of one.
+ * gvc_encoder_select() chooses which segment of the last finished batch gvc_encoder_recon / _stats / _record_bytes /
+ * _write_mp4 refer to (0 after every finish). */
+int gvc_encoder_upload_host_batch(gvc_encoder *enc, const uint8_t *const *frames_i420, const int *n_frames, int count);
+int gvc_encoder_encode_device_batch(gvc_encoder *enc, const uint8_t *const *d_frames_i420, const int *n_frames, int count);
+int gvc_encoder_finish_batch(gvc_encoder *enc, int annexb, uint8_t **out, size_t *out_len);
+int gvc_encoder_select(gvc_encoder *enc, int segment);
 /* Same, pictures already in DEVICE memory; only issues the kernels (asynchronous on gvc_encoder_stream()). */
 int gvc_encoder_encode_device(gvc_encoder *enc, const uint8_t *d_frames_i420, int n_frames);
 int gvc_encoder_sync(gvc_encoder *enc);
