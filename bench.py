@@ -221,81 +221,85 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     gvc.init(local)
     cores = os.cpu_count() or 1
-    encs = [gvc.Encoder(SW, SH, DW, DH, fps=(30, 1), crf=CRF, merange=16, host_threads=int(os.environ.get("GVC_BENCH_HOST_THREADS", max(1, cores // NSEG))),
-                        disable_graph=args.no_graph) for _ in range(NSEG)]
-    fb = encs[0].frame_bytes()
+    # ONE encoder object: the clip's NSEG segments form a batch that advances picture by picture together, one kernel launch
+    # per stage for all of them (CUDA graph replayed per step).  Two more encoders only for the e2e pipeline below.
+    def make_encoder():
+        return gvc.Encoder(SW, SH, DW, DH, fps=(30, 1), crf=CRF, merange=16, host_threads=cores, disable_graph=args.no_graph, max_batch=NSEG)
+    enc = make_encoder()
+    fb = enc.frame_bytes()
 
     seg0 = synth_segment(rank)
     host_src = [torch.from_numpy(seg0 if b == 0 else np.roll(seg0, 5 * b, axis=0)).pin_memory() for b in range(NSEG)]
     dev_src = [h.cuda() for h in host_src]
-    from concurrent.futures import ThreadPoolExecutor
-    pool = ThreadPoolExecutor(NSEG)                  # one issuing thread per segment (ctypes releases the GIL)
+    dev_ptrs, host_ptrs, counts = [d.data_ptr() for d in dev_src], [h.data_ptr() for h in host_src], [SEG_FRAMES] * NSEG
 
     def barrier():
         torch.cuda.synchronize()
-        for e in encs:
-            e.sync()
+        enc.sync()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # each segment slot is driven by its own host thread, like 8 worker processes sharing the box: a slot starts its next
-    # segment as soon as its previous one is issued / finished, so copies, kernels and host entropy coding of different
-    # segments overlap (no barrier between steps)
     def run_device(steps):
-        list(pool.map(lambda k: [encs[k].encode_device(dev_src[k].data_ptr(), SEG_FRAMES) for _ in range(steps)], range(NSEG)))
+        for _ in range(steps):
+            enc.encode_device_batch(dev_ptrs, counts)
 
-    def slot_host(k, steps):
-        # upload of the slot's next segment overlaps the encode of its current one (two staging buffers per encoder)
-        e, src = encs[k], host_src[k].data_ptr()
-        e.upload_host(src, SEG_FRAMES)
-        for i in range(steps):
-            e.encode_uploaded()
-            if i + 1 < steps:
-                e.upload_host(src, SEG_FRAMES)
-            e.finish_discard()
-
+    # end to end: the upload of step k + 1 (copy stream, second staging buffer) overlaps the kernels of step k; finish() of step k
+    # waits for its slices and wraps them into NAL units on the host
     def run_host(steps):
-        list(pool.map(lambda k: slot_host(k, steps), range(NSEG)))
+        enc.upload_host_batch(host_ptrs, counts)
+        for i in range(steps):
+            enc.encode_uploaded()
+            if i + 1 < steps:
+                enc.upload_host_batch(host_ptrs, counts)
+            enc.finish_batch(keep=False)
 
-    # ---- device-resident timing: every GPU stage of the path, 8 segments in flight ---------------
+    # ---- device-resident timing: every GPU stage of the path, the batch of 8 segments per step -------
     run_device(args.warmup)
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(NSEG)]
-    exts = [torch.cuda.ExternalStream(e.stream_handle()) for e in encs]
+    ext = torch.cuda.ExternalStream(enc.stream_handle())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
-    for k in range(NSEG):
-        ev[k][0].record(exts[k])
+    e0.record(ext)
     run_device(args.steps)
-    for k in range(NSEG):
-        ev[k][1].record(exts[k])
+    e1.record(ext)
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop()
-    # device time of the step = the slowest stream's span (all streams start together); wall clock is reported beside it
-    ms_total = max(ev[k][0].elapsed_time(ev[k][1]) for k in range(NSEG))
+    ms_total = e0.elapsed_time(e1)
     from govideocompressor_b200 import farm
     ms_total = farm.max_over_ranks(ms_total, "cuda")
     value = world * NSEG * SEG_FRAMES * args.steps / (ms_total * 1e-3)
 
-    # ---- stage pass: one segment alone on the GPU, per-kernel CUDA events (roofline figures) -------
-    enc = encs[0]
+    # ---- stage pass: the same batched launches with a CUDA-event pair around every one (roofline figures) -------
     enc.set_timing(True)
     for i in range(args.steps):
-        enc.encode_device(dev_src[i % NSEG].data_ptr(), SEG_FRAMES)
+        enc.encode_device_batch(dev_ptrs, counts)
     stages = enc.stage_times()
     enc.set_timing(False)
+    # one segment alone on the GPU (the reference's one-piece-per-worker model)
+    enc.encode_device(dev_ptrs[0], SEG_FRAMES)
+    enc.sync()
+    e0.record(ext)
+    for i in range(args.steps):
+        enc.encode_device(dev_ptrs[i % NSEG], SEG_FRAMES)
+    e1.record(ext)
+    enc.sync()
+    one_segment_ms = e0.elapsed_time(e1) / args.steps
 
-    # ---- end to end through the C ABI: host pictures in, H.264 streams out, 8 segments in flight ---
+    # ---- end to end through the C ABI: host pictures in, H.264 streams out ---
     run_host(1)
     barrier()
     t0 = time.perf_counter()
     run_host(args.steps)
     e2e_s = time.perf_counter() - t0
-    stream_bytes = int(sum(e.stats()[:, 3].sum() for e in encs))   # the step's result as read on the host
-    d2h_bytes = int(sum(e.record_bytes() for e in encs))
+    stream_bytes, d2h_bytes = 0, 0
+    for k in range(NSEG):
+        enc.select(k)
+        stream_bytes += int(enc.stats()[:, 3].sum())       # the step's result as read on the host
+        d2h_bytes += enc.record_bytes()
     e2e = world * NSEG * SEG_FRAMES * args.steps / farm.max_over_ranks(e2e_s, "cuda")
 
     if rank == 0:
@@ -306,21 +310,25 @@ def main():
             peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
         table, launches = {}, 0
         for name, (ms, n) in stages.items():
-            launches += n * (4 if name == "entropy" else 1)      # the entropy entry times its four kernels together
+            launches += n * (4 if name == "entropy" else NSEG if name == "resize" else 1)   # entropy: four kernels per entry; resize: one launch per segment
             if n == 0:
                 continue
             avg = ms / n
             b = ALGO_BYTES.get(name)
-            table[name] = {"launches_per_segment": n / args.steps, "ms_per_segment": ms / args.steps, "avg_launch_ms": avg,
+            if name == "resize":
+                b, avg = b * NSEG, avg              # the entry brackets the batch's NSEG resize launches
+            elif b:
+                b = b * NSEG                        # one launch covers the batch's NSEG pictures
+            table[name] = {"launches_per_step": n / args.steps, "ms_per_step": ms / args.steps, "avg_launch_ms": avg,
                            "share_of_kernel_time": None, "algorithmic_bytes_per_launch": b,
                            "achieved_gbs": (b / (avg * 1e-3) / 1e9) if b else None}
-        ktotal = sum(s["ms_per_segment"] for s in table.values())
+        ktotal = sum(s["ms_per_step"] for s in table.values())
         for s in table.values():
-            s["share_of_kernel_time"] = s["ms_per_segment"] / ktotal
+            s["share_of_kernel_time"] = s["ms_per_step"] / ktotal
             if s["achieved_gbs"] is not None:
                 s["frac_of_peak"] = s["achieved_gbs"] / peak
         # dominant single kernel ("entropy" is four small kernels timed as one entry, "border" has no byte model)
-        dom = max((k for k in table if table[k]["algorithmic_bytes_per_launch"]), key=lambda k: table[k]["ms_per_segment"])
+        dom = max((k for k in table if table[k]["algorithmic_bytes_per_launch"]), key=lambda k: table[k]["ms_per_step"])
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
@@ -334,21 +342,20 @@ def main():
                         "d2h_bytes_per_step": d2h_bytes,
                         "stream_bytes_per_step": stream_bytes, "host_threads": cores},
                 # stage pass counts + the one-thread kernel that raises each picture's arrival flag (not a timed stage)
-                "gpu_launches": (launches + SEG_FRAMES * args.steps) * NSEG, "clocks": clocks,
+                "gpu_launches": launches + SEG_FRAMES * args.steps, "clocks": clocks, "one_segment_alone_ms": one_segment_ms,
                 "roofline": {"kernel": dom, "bound": "hbm", "achieved": d["achieved_gbs"], "peak": peak, "unit": "GB/s",
                              "frac": (d["achieved_gbs"] / peak) if d["achieved_gbs"] else None, "traffic": traffic,
                              "peak_source": peak_src, "algorithmic_bytes_per_launch": d["algorithmic_bytes_per_launch"],
                              "launch_ms_avg": d["avg_launch_ms"], "share_of_step": d["share_of_kernel_time"],
-                             "note": "dominant single kernel by accumulated CUDA-event time in the stage pass (one segment alone on the "
-                                     "GPU, individual launches); the timed region replays the same kernels from CUDA graphs, 8 streams. "
-                                     "The kernel is instruction-issue bound, not HBM bound (ncu: issue slots ~51 % busy with one wave of "
-                                     "24 warps per SM, DRAM traffic = algorithmic bytes): see profiles/r1t_kernels_summary.md"},
+                             "note": "dominant single kernel by accumulated CUDA-event time in the stage pass: the same batched launches as the timed "
+                                     "region (one launch per stage for the 8 segments), each bracketed by its own CUDA-event pair; the timed "
+                                     "region replays them from one CUDA graph.  The kernel is instruction-issue bound, not HBM bound: see "
+                                     "profiles/ and DESIGN.md"},
                 "stages": table}
         if cpu:
             line["cpu_baseline"] = cpu
         print(json.dumps(line))
-    for e in encs:
-        e.close()
+    enc.close()
     if world > 1:
         dist.destroy_process_group()
 
