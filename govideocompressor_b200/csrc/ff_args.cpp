@@ -85,12 +85,22 @@ int parse_ffmpeg_args(const std::string &args, TranscodeOptions &opt, std::strin
             if (!parse_size(v, '/', a, b)) { a = atoi(v.c_str()); b = 1; }
             if (a < 1) { err = "bad -r"; return GVC_ERR_INVALID_ARG; }
             opt.fps_num = a; opt.fps_den = b;
-        } else if (k == "-an" || k == "-y") {
-        } else if (k == "-acodec" || k == "-c:a") {
-            if (!need(v)) return GVC_ERR_INVALID_ARG;      // audio is not carried by this path yet
+        } else if (k == "-an") {
+            opt.drop_audio = true;
+        } else if (k == "-y") {
+        } else if (k == "-acodec" || k == "-c:a" || k == "-codec:a") {
+            if (!need(v)) return GVC_ERR_INVALID_ARG;
+            // the audio stream is always stream-copied (what the reference's own splitter does, server.go:199-200); a request to
+            // re-encode it cannot be honoured on this path
+            if (v != "copy" && v != "aac") { err = "audio codec '" + v + "' is not available on this path (audio is stream-copied)"; return GVC_ERR_UNSUPPORTED; }
         } else if (k == "-b:v" || k == "-b") {
-            err = "bitrate mode (" + k + ") is not implemented; use -crf";
-            return GVC_ERR_UNSUPPORTED;
+            if (!need(v)) return GVC_ERR_INVALID_ARG;
+            char *end = nullptr;
+            double b = strtod(v.c_str(), &end);
+            if (end && (*end == 'k' || *end == 'K')) { b *= 1e3; ++end; }
+            else if (end && (*end == 'M' || *end == 'm')) { b *= 1e6; ++end; }
+            if (end == v.c_str() || (end && *end) || b < 1000 || b > 2e9) { err = "bad " + k + " value '" + v + "'"; return GVC_ERR_INVALID_ARG; }
+            opt.bitrate = long(b);
         } else {
             err = "unrecognised option '" + k + "'";
             return GVC_ERR_INVALID_ARG;

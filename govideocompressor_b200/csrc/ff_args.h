@@ -16,7 +16,8 @@ struct TranscodeOptions {
     int  merange = 16;                // -me_range
     int  fps_num = 0, fps_den = 0;    // -r (0 = input rate)
     std::string preset = "medium";
-    bool drop_audio = true;
+    bool drop_audio = false;          // -an
+    long bitrate = 0;                 // -b:v in bits per second (0 = constant quality from -crf)
 };
 
 // Returns 0 or a negative gvc_status; err describes the offending token.

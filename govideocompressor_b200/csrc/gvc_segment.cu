@@ -6,6 +6,7 @@
 // (client.go:120-123).  On any failure it leaves NO output file, because the reference detects failure only by the
 // missing file (client.go:163-167).
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -309,7 +310,7 @@ int gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg) {
     if ((rc = gvc_resize_plan_create(&e->plan, c.src_w, c.src_h, c.dst_w, c.dst_h, GVC_PIX_YUV420P, c.scale_algo))) { gvc_encoder_destroy(e); return rc; }
     SegmentConfig sc;
     sc.w = c.dst_w; sc.h = c.dst_h; sc.fps_num = c.fps_num; sc.fps_den = c.fps_den;
-    sc.qp_p = c.crf; sc.qp_i = c.crf >= 3 ? c.crf - 3 : 0;     // x264's default ip_factor 1.4 is about 3 QP
+    sc.qp_p = c.crf; sc.qp_i = c.crf >= 3 ? c.crf - 3 : 0;     // x264's default ip_factor 1.4 is about 3 QP (also gvc_encoder_set_crf)
     sc.merange = c.merange; sc.keep_recon = c.keep_recon != 0;
     sc.device_entropy = c.entropy != GVC_ENTROPY_HOST;
     sc.max_batch = c.max_batch;
@@ -509,7 +510,85 @@ int gvc_encoder_write_mp4(gvc_encoder *e, const char *path) {
     return GVC_OK;
 }
 
+int gvc_encoder_set_crf(gvc_encoder *e, int crf) {
+    if (!e || crf < 0 || crf > 51) { set_error("gvc_encoder_set_crf: crf %d outside 0..51", crf); return GVC_ERR_INVALID_ARG; }
+    if (e->pending) { set_error("gvc_encoder_set_crf: a segment is in flight"); return GVC_ERR_INVALID_ARG; }
+    if (crf == e->cfg.crf) return GVC_OK;
+    e->cfg.crf = crf;
+    e->seg->set_qp(crf >= 3 ? crf - 3 : 0, crf);
+    e->graph_n.clear();          // quantiser constants are kernel arguments: the captured graph is for the old ones
+    return GVC_OK;
+}
+
+}  // extern "C"
+
 // ---------------------------------------------------------------------------------------------- transcode
+namespace {
+
+// `-r`: ffmpeg's output frame rate drops or repeats pictures so that the duration stays; output picture j shows the input
+// picture that is on screen at time j / out_fps.
+class RateAdapter : public FrameSource {
+public:
+    RateAdapter(std::unique_ptr<FrameSource> src, int out_num, int out_den) : src_(std::move(src)) {
+        w = src_->w; h = src_->h; format_name = src_->format_name;
+        in_num_ = src_->fps_num; in_den_ = src_->fps_den;
+        fps_num = out_num; fps_den = out_den;
+        has_audio = src_->has_audio; audio_copyable = src_->audio_copyable; audio_codec_id = src_->audio_codec_id;
+        last_.resize(size_t(w) * h + 2 * size_t((w + 1) / 2) * ((h + 1) / 2));
+    }
+    int read(uint8_t *dst, int max_frames, std::string &err) override {
+        int n = 0;
+        while (n < max_frames && !eof_) {
+            // input index shown at output picture out_idx_: floor(out_idx * in_fps / out_fps)
+            const long long want = (long long)out_idx_ * in_num_ * fps_den / ((long long)in_den_ * fps_num);
+            while (in_idx_ < want && !eof_) {
+                const int r = src_->read(last_.data(), 1, err);
+                if (r < 0) return -1;
+                if (r == 0) eof_ = true; else ++in_idx_;
+            }
+            if (eof_ && in_idx_ < want) break;
+            if (in_idx_ < 0) break;
+            memcpy(dst + last_.size() * size_t(n), last_.data(), last_.size());
+            ++n; ++out_idx_;
+        }
+        if (eof_) audio = src_->audio;
+        return n;
+    }
+private:
+    std::unique_ptr<FrameSource> src_;
+    std::vector<uint8_t> last_;
+    long long in_idx_ = -1;
+    long      out_idx_ = 0;
+    int       in_num_ = 30, in_den_ = 1;
+    bool      eof_ = false;
+};
+
+// The worker process converts piece after piece (client.go:37 loops forever): the encoder, its device buffers and the pinned
+// staging memory of the previous piece are kept and reused when the next piece has the same shape.
+struct TranscodeCache {
+    std::mutex   mu;
+    gvc_encoder *enc = nullptr;
+    int          key[8] = {0, 0, 0, 0, 0, 0, 0, 0};      // src w, h, dst w, h, fps num, den, merange, scaler
+    uint8_t     *pinned[2] = {nullptr, nullptr};
+    size_t       pinned_bytes = 0;
+    int          device = -1;
+    long         allocations = 0;                        // encoder creations + pinned allocations so far (gvc_transcode_allocations)
+    void drop() {
+        if (enc) { gvc_encoder_destroy(enc); enc = nullptr; }
+        for (int i = 0; i < 2; ++i) { if (pinned[i]) cudaFreeHost(pinned[i]); pinned[i] = nullptr; }
+        pinned_bytes = 0;
+    }
+};
+TranscodeCache &transcode_cache() { static TranscodeCache c; return c; }
+
+constexpr size_t kChunkBytes = size_t(512) << 20;        // raw pictures of one GOP held in pinned memory (two such buffers)
+
+}  // namespace
+
+extern "C" long gvc_transcode_allocations(void) { return transcode_cache().allocations; }
+
+extern "C" {
+
 int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char *out_path, char **log_out, size_t *log_len) {
     std::string log;
     auto finish = [&](int rc) {
@@ -532,57 +611,132 @@ int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char 
     if (rc != 0) { set_error("%s", err.c_str()); return finish(rc); }
     std::unique_ptr<FrameSource> srcf = open_frame_source(in_path, err);
     if (!srcf) { set_error("%s: %s", in_path, err.c_str()); return finish(err == "No such file or directory" ? GVC_ERR_IO : GVC_ERR_UNSUPPORTED); }
-    int w = srcf->w, h = srcf->h, fn = srcf->fps_num, fd = srcf->fps_den;
+    const int w = srcf->w, h = srcf->h;
     if ((w | h) & 1) { set_error("%s: odd picture size %dx%d is not supported", in_path, w, h); return finish(GVC_ERR_UNSUPPORTED); }
-    if (opt.fps_num > 0) { fn = opt.fps_num; fd = opt.fps_den; }
-    gvc_encoder_config c;
-    memset(&c, 0, sizeof(c));
-    c.src_w = w; c.src_h = h; c.dst_w = opt.dst_w ? opt.dst_w : w; c.dst_h = opt.dst_h ? opt.dst_h : h;
-    c.fps_num = fn; c.fps_den = fd; c.crf = opt.crf; c.merange = opt.merange; c.scale_algo = opt.scale_algo;
-    gvc_encoder *e = nullptr;
-    if ((rc = gvc_encoder_create(&e, &c))) return finish(rc);
-    char buf[512];
-    snprintf(buf, sizeof(buf), "Input #0, %s, from '%s': %dx%d, %d/%d fps\nOutput #0, mp4, to '%s': h264 (gvc sm_100a), yuv420p, %dx%d, crf %d\n",
-             srcf->format_name.c_str(), in_path, w, h, fn, fd, out_path, c.dst_w, c.dst_h, c.crf);
+    // audio: an AAC stream is carried over unchanged; anything else cannot be, and silently dropping it would hand the operator's
+    // concat step (server.go:357) a file without sound -- so it is an error unless the job says -an
+    const bool want_audio = srcf->has_audio && !opt.drop_audio;
+    if (want_audio && !srcf->audio_copyable) {
+        set_error("%s: the audio stream (codec id 0x%x) cannot be carried over (only AAC is stream-copied); add -an to drop it", in_path, srcf->audio_codec_id);
+        return finish(GVC_ERR_UNSUPPORTED);
+    }
+    const int in_fn = srcf->fps_num, in_fd = srcf->fps_den;
+    if (opt.fps_num > 0 && (long long)opt.fps_num * in_fd != (long long)in_fn * opt.fps_den)
+        srcf.reset(new RateAdapter(std::move(srcf), opt.fps_num, opt.fps_den));
+    const int fn = srcf->fps_num, fd = srcf->fps_den;
+    const int dw = opt.dst_w ? opt.dst_w : w, dh = opt.dst_h ? opt.dst_h : h;
+
+    TranscodeCache &C = transcode_cache();
+    std::lock_guard<std::mutex> lock(C.mu);
+    const size_t fb = i420_bytes(w, h);
+    const int    gop = int(std::max<size_t>(1, std::min<size_t>(size_t(std::min(opt.gop, 250)), std::max<size_t>(16, kChunkBytes / fb))));
+    const int    key[8] = {w, h, dw, dh, fn, fd, opt.merange, opt.scale_algo};
+    if (C.enc && (memcmp(key, C.key, sizeof(key)) != 0 || C.device != gvc::current_device())) C.drop();
+    const int    start_crf = opt.bitrate > 0 ? (C.enc ? C.enc->cfg.crf : 26) : opt.crf;     // bitrate mode starts from the last piece's QP
+    if (!C.enc) {
+        gvc_encoder_config c;
+        memset(&c, 0, sizeof(c));
+        c.src_w = w; c.src_h = h; c.dst_w = dw; c.dst_h = dh; c.fps_num = fn; c.fps_den = fd; c.crf = start_crf; c.merange = opt.merange; c.scale_algo = opt.scale_algo;
+        if ((rc = gvc_encoder_create(&C.enc, &c))) return finish(rc);
+        memcpy(C.key, key, sizeof(key));
+        C.device = gvc::current_device();
+        ++C.allocations;
+    }
+    if (C.pinned_bytes < fb * size_t(gop)) {
+        for (int i = 0; i < 2; ++i) { if (C.pinned[i]) cudaFreeHost(C.pinned[i]); C.pinned[i] = nullptr; }
+        C.pinned_bytes = 0;
+        for (int i = 0; i < 2; ++i)
+            if (cudaHostAlloc((void **)&C.pinned[i], fb * size_t(gop), cudaHostAllocDefault) != cudaSuccess) { C.drop(); set_error("cannot allocate pinned staging"); return finish(GVC_ERR_NOMEM); }
+        C.pinned_bytes = fb * size_t(gop);
+        ++C.allocations;
+    }
+    gvc_encoder *e = C.enc;
+    if ((rc = gvc_encoder_set_crf(e, start_crf))) return finish(rc);
+    char buf[640];
+    snprintf(buf, sizeof(buf), "Input #0, %s, from '%s': %dx%d, %d/%d fps%s\nOutput #0, mp4, to '%s': h264 (gvc sm_100a), yuv420p, %dx%d, %d/%d fps, ",
+             srcf->format_name.c_str(), in_path, w, h, in_fn, in_fd, srcf->has_audio ? (want_audio ? ", audio: aac (copy)" : ", audio dropped (-an)") : "", out_path, dw, dh, fn, fd);
+    log += buf;
+    if (opt.bitrate > 0) snprintf(buf, sizeof(buf), "bitrate %ld kb/s (constant QP per GOP, chosen by re-encoding)\n", opt.bitrate / 1000);
+    else snprintf(buf, sizeof(buf), "crf %d\n", opt.crf);
     log += buf;
 
-    const size_t fb = i420_bytes(w, h);
-    const int    gop = std::max(1, std::min(opt.gop, 250));
-    uint8_t     *host = nullptr;
-    if (cudaHostAlloc((void **)&host, fb * gop, cudaHostAllocDefault) != cudaSuccess) { gvc_encoder_destroy(e); set_error("cannot allocate pinned staging"); return finish(GVC_ERR_NOMEM); }
     std::vector<uint8_t>   payload;
     std::vector<Mp4Sample> samples;
     std::vector<uint8_t>   sps, pps;
-    int       total = 0;
+    int       total = 0, gops = 0, passes = 0;
     long      n_skip = 0, n_p16 = 0, n_p8 = 0, n_intra = 0;
+    double    budget_carry = 0;                  // bits the earlier GOPs left over (+) or overspent (-)
     const auto t0 = std::chrono::steady_clock::now();
-    bool eof = false;
-    while (!eof && rc == 0) {
-        const int n = srcf->read(host, gop, err);
-        if (n < 0) { set_error("%s: %s (picture %d)", in_path, err.c_str(), total); rc = GVC_ERR_IO; }
-        if (n < gop) eof = true;
-        if (rc || n == 0) break;
-        if ((rc = gvc_encoder_encode_host(e, host, n, 0, nullptr, nullptr))) break;
+    auto encode_gop = [&](const uint8_t *host, int n) -> int {      // upload + kernels, asynchronous
+        int r = gvc_encoder_upload_host(e, host, n);
+        return r ? r : gvc_encoder_encode_uploaded(e);
+    };
+    auto gop_bits = [&]() { double b = 0; for (size_t sz : e->outs[0].au_size) b += 8.0 * double(sz); return b; };
+    int cur = 0;
+    int n_cur = srcf->read(C.pinned[0], gop, err);
+    if (n_cur < 0) { set_error("%s: %s (picture %d)", in_path, err.c_str(), total); rc = GVC_ERR_IO; }
+    while (rc == 0 && n_cur > 0) {
+        if ((rc = encode_gop(C.pinned[cur], n_cur))) break;
+        // the host decodes the next GOP while the GPU encodes this one
+        int n_next = n_cur == gop ? srcf->read(C.pinned[cur ^ 1], gop, err) : 0;
+        if (n_next < 0) { set_error("%s: %s (picture %d)", in_path, err.c_str(), total + n_cur); rc = GVC_ERR_IO; }
+        int frc = gvc_encoder_finish(e, 0, nullptr, nullptr);
+        if (rc == 0) rc = frc;
+        if (rc) break;
+        ++passes;
+        if (opt.bitrate > 0) {
+            // one constant QP per GOP, found by re-encoding it (milliseconds each): bits fall by about 2^(-1/6) per QP step
+            const double target = std::max(1000.0, double(opt.bitrate) * n_cur * fd / fn + budget_carry);
+            int    qp = e->cfg.crf, best_qp = qp;
+            double bits = gop_bits(), best_err = fabs(bits - target);
+            int    lo = -1, hi = 52;                 // QPs known to give too many / too few bits
+            for (int pass = 0; pass < 6 && fabs(bits - target) > 0.05 * target; ++pass) {
+                if (bits > target) lo = std::max(lo, qp); else hi = std::min(hi, qp);
+                int next = qp + int(lround(6.0 * log2(bits / target)));
+                next = std::max(lo + 1, std::min(hi - 1, std::max(0, std::min(51, next))));
+                if (next <= lo || next >= hi || next == qp) break;
+                qp = next;
+                if ((rc = gvc_encoder_set_crf(e, qp)) || (rc = encode_gop(C.pinned[cur], n_cur)) || (rc = gvc_encoder_finish(e, 0, nullptr, nullptr))) break;
+                ++passes;
+                bits = gop_bits();
+                if (fabs(bits - target) < best_err) { best_err = fabs(bits - target); best_qp = qp; }
+            }
+            if (rc) break;
+            if (best_qp != e->cfg.crf) {
+                if ((rc = gvc_encoder_set_crf(e, best_qp)) || (rc = encode_gop(C.pinned[cur], n_cur)) || (rc = gvc_encoder_finish(e, 0, nullptr, nullptr))) break;
+                ++passes;
+                bits = gop_bits();
+            }
+            budget_carry = std::max(-0.5 * target, std::min(0.5 * target, target - bits));
+            snprintf(buf, sizeof(buf), "[gvc] gop %d: %d pictures, qp %d, %.0f bits (target %.0f)\n", gops, n_cur, e->cfg.crf, bits, target);
+            log += buf;
+        }
         const SegmentOutput &so = e->outs[0];
         if (sps.empty()) { sps = so.sps_nal; pps = so.pps_nal; }
-        for (int i = 0; i < n; ++i) {
+        for (int i = 0; i < n_cur; ++i) {
             samples.push_back(Mp4Sample{payload.size() + so.au_offset[i], so.au_size[i], i == 0});
             n_skip += so.stats[i].skipped; n_p16 += so.stats[i].p16; n_p8 += so.stats[i].p8; n_intra += so.stats[i].intra;
         }
         payload.insert(payload.end(), so.payload.begin(), so.payload.end());
-        total += n;
+        total += n_cur;
+        ++gops;
+        cur ^= 1;
+        n_cur = n_next;
     }
-    cudaFreeHost(host);
-    gvc_encoder_destroy(e);
-    if (rc == 0 && total == 0) { set_error("%s: no frames", in_path); rc = GVC_ERR_IO; }
-    if (rc) return finish(rc);
+    if (rc) {                    // leave the cached encoder in a clean state for the next piece
+        if (e->pending) gvc_encoder_finish(e, 0, nullptr, nullptr);
+        while (e->up_pending > 0) { if (gvc_encoder_encode_uploaded(e) || gvc_encoder_finish(e, 0, nullptr, nullptr)) { C.drop(); break; } }
+        return finish(rc);
+    }
+    if (total == 0) { set_error("%s: no frames", in_path); return finish(GVC_ERR_IO); }
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     std::string tmp = std::string(out_path) + ".gvc.tmp";
-    if (!write_mp4(tmp, c.dst_w, c.dst_h, fn, fd, sps, pps, payload, samples, err)) { set_error("%s", err.c_str()); return finish(GVC_ERR_IO); }
+    const Mp4Audio *audio = want_audio && !srcf->audio.packets.empty() ? &srcf->audio : nullptr;
+    if (!write_mp4(tmp, dw, dh, fn, fd, sps, pps, payload, samples, err, audio)) { set_error("%s", err.c_str()); return finish(GVC_ERR_IO); }
     if (rename(tmp.c_str(), out_path) != 0) { remove(tmp.c_str()); set_error("cannot rename %s to %s", tmp.c_str(), out_path); return finish(GVC_ERR_IO); }
     const double dur = double(total) * fd / fn, kbps = dur > 0 ? payload.size() * 8.0 / 1000.0 / dur : 0;
-    snprintf(buf, sizeof(buf), "frame=%5d fps=%.0f size=%8zukB time=%.2fs bitrate=%.1fkbits/s\n[gvc] mb I:%ld P16:%ld P8:%ld skip:%ld\n",
-             total, secs > 0 ? total / secs : 0.0, payload.size() / 1024, dur, kbps, n_intra, n_p16, n_p8, n_skip);
+    snprintf(buf, sizeof(buf), "frame=%5d fps=%.0f size=%8zukB time=%.2fs bitrate=%.1fkbits/s\n[gvc] mb I:%ld P16:%ld P8:%ld skip:%ld gops:%d passes:%d audio:%zu packets\n",
+             total, secs > 0 ? total / secs : 0.0, payload.size() / 1024, dur, kbps, n_intra, n_p16, n_p8, n_skip, gops, passes, audio ? audio->packets.size() : size_t(0));
     log += buf;
     return finish(GVC_OK);
 }

@@ -150,6 +150,24 @@ public:
         if (*reinterpret_cast<int *>(static_cast<char *>(st) + 8) != stream_ || !codecpar) { err = "unexpected AVStream layout"; return false; }
         cctx_ = a.avcodec_alloc_context3(dec);
         if (!cctx_ || a.avcodec_parameters_to_context(cctx_, codecpar) < 0 || a.avcodec_open2(cctx_, dec, nullptr) < 0) { err = "cannot open the video decoder"; return false; }
+        // audio: AVCodecParameters starts with codec_type, codec_id, codec_tag, extradata, extradata_size in every libavcodec
+        // this reader accepts; AV_CODEC_ID_AAC = 0x15002
+        astream_ = a.av_find_best_stream(fmt_, /*AVMEDIA_TYPE_AUDIO*/ 1, -1, -1, nullptr, 0);
+        if (astream_ >= 0 && unsigned(astream_) < nb) {
+            const char *ap = *reinterpret_cast<char **>(static_cast<char *>(streams[astream_]) + 16);
+            has_audio = true;
+            if (ap) {
+                audio_codec_id = *reinterpret_cast<const int *>(ap + 4);
+                const uint8_t *xd = *reinterpret_cast<uint8_t *const *>(ap + 16);
+                const int xn = *reinterpret_cast<const int *>(ap + 24);
+                if (audio_codec_id == 0x15002 && xd && xn >= 2 && xn <= 64) {
+                    audio.asc.assign(xd, xd + xn);
+                    audio_copyable = parse_aac_config(audio);
+                }
+            }
+        } else {
+            astream_ = -1;
+        }
         const AvRational r = a.av_guess_frame_rate(fmt_, st, nullptr);
         if (r.num > 0 && r.den > 0) { fps_num = r.num; fps_den = r.den; }
         pkt_ = a.av_packet_alloc();
@@ -190,9 +208,11 @@ private:
             }
             if (flushed_) return true;                        // drained
             int rr;
-            for (;;) {                                         // next packet of our stream
+            for (;;) {                                         // next packet of our stream; audio packets are kept on the way
                 rr = a.av_read_frame(fmt_, pkt_);
-                if (rr < 0 || static_cast<AvPacketHead *>(pkt_)->stream_index == stream_) break;
+                const AvPacketHead *ph = static_cast<AvPacketHead *>(pkt_);
+                if (rr < 0 || ph->stream_index == stream_) break;
+                if (audio_copyable && ph->stream_index == astream_ && ph->data && ph->size > 0) audio.packets.emplace_back(ph->data, ph->data + ph->size);
                 a.av_packet_unref(pkt_);
             }
             if (rr < 0) { a.avcodec_send_packet(cctx_, nullptr); flushed_ = true; continue; }
@@ -210,7 +230,7 @@ private:
         }
     }
     void *fmt_ = nullptr, *cctx_ = nullptr, *pkt_ = nullptr, *frame_ = nullptr;
-    int   stream_ = -1;
+    int   stream_ = -1, astream_ = -1;
     bool  have_ = false, flushed_ = false;
 };
 

@@ -12,6 +12,8 @@
 #include <memory>
 #include <string>
 
+#include "mp4_mux.h"
+
 namespace gvc {
 
 class FrameSource {
@@ -19,6 +21,11 @@ public:
     virtual ~FrameSource() {}
     int w = 0, h = 0, fps_num = 30, fps_den = 1;
     std::string format_name;
+    // The piece's audio stream (the splitter maps one: server.go:199-200).  AAC is carried into the output unchanged: its
+    // packets are collected while the pictures are read (complete once read() has returned 0); any other codec is only flagged.
+    bool     has_audio = false, audio_copyable = false;
+    int      audio_codec_id = 0;
+    Mp4Audio audio;
     // Reads up to max_frames pictures as tight I420 into dst (w*h*3/2 bytes each).  Returns the number read
     // (0 at end of stream) or a negative value on a damaged input (err explains).
     virtual int read(uint8_t *dst, int max_frames, std::string &err) = 0;

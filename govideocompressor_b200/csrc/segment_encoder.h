@@ -87,6 +87,7 @@ public:
     const EncGeom &geom() const { return g_; }
     const PlaneSizes &planes() const { return ps_; }
     int max_batch() const { return cfg_.max_batch; }
+    void set_qp(int qp_i, int qp_p) { cfg_.qp_i = qp_i; cfg_.qp_p = qp_p; }      // takes effect with the next encode_device
 
     // Source pictures in the padded layout (interiors filled, borders not yet extended): device arrays holding
     // n planes each, ps_.y / ps_.c bytes apart.  The resize stage writes straight into these.

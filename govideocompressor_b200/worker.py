@@ -73,7 +73,10 @@ def serve_one_job(server_addr, convert, fetch, store, workdir, timeout=10.0):
     except OSError:
         return None
     try:
-        data = conn.recv(100)                                      # client.go:43-45
+        try:
+            data = conn.recv(100)                                  # client.go:43-45
+        except OSError:
+            return None                                            # client.go:46-50: a failed read ends this round of the loop
         if not data:
             return None
         parts = data.decode(errors="replace").split(";")

@@ -221,6 +221,8 @@ int gvc_encoder_finish_batch(gvc_encoder *enc, int annexb, uint8_t **out, size_t
 int gvc_encoder_select(gvc_encoder *enc, int segment);
 /* Same, pictures already in DEVICE memory; only issues the kernels (asynchronous on gvc_encoder_stream()). */
 int gvc_encoder_encode_device(gvc_encoder *enc, const uint8_t *d_frames_i420, int n_frames);
+/* Changes `-crf` between segments (quantiser constants are kernel arguments: the next call captures a new graph). */
+int gvc_encoder_set_crf(gvc_encoder *enc, int crf);
 int gvc_encoder_sync(gvc_encoder *enc);
 void *gvc_encoder_stream(gvc_encoder *enc);      /* the cudaStream_t the encoder launches on */
 /* Completes a segment started with gvc_encoder_encode_device / _encode_uploaded: waits for the slices (or entropy-codes the
@@ -248,6 +250,9 @@ int gvc_encoder_write_mp4(gvc_encoder *enc, const char *path);
  * reference writes to c<id>.mp4.log (client.go:120-123).  Input containers: YUV4MPEG2 natively, anything libavformat reads
  * (MP4 / H.264 pieces as the reference's splitter makes them) when FFmpeg's libraries can be dlopen'ed (GVC_FFMPEG_LIBDIR). */
 int gvc_transcode_file(const char *in_path, const char *ffmpeg_args, const char *out_path, char **log_out, size_t *log_len);
+/* Diagnostic: how many times gvc_transcode_file had to create its encoder or allocate its pinned staging memory.  The worker
+ * converts piece after piece (client.go:37); pieces of one shape reuse both, so the count stays put from the second piece on. */
+long gvc_transcode_allocations(void);
 
 #ifdef __cplusplus
 }

@@ -133,6 +133,31 @@ struct EmuOps {
 };
 }  // namespace
 
+// Test input with sound: emu_set_audio(n, seed) makes the next MP4 files written by emu_encode_segment carry an AAC track of n
+// pseudo-random packets (AudioSpecificConfig 0x12 0x10: AAC-LC, 44.1 kHz, stereo).  The payload is never decoded by anything here.
+static Mp4Audio g_emu_audio;
+extern "C" void emu_set_audio(int n_packets, unsigned seed) {
+    g_emu_audio = Mp4Audio();
+    if (n_packets <= 0) return;
+    g_emu_audio.asc = {0x12, 0x10};
+    parse_aac_config(g_emu_audio);
+    unsigned x = seed * 2654435761u + 12345u;
+    for (int i = 0; i < n_packets; ++i) {
+        x = x * 1664525u + 1013904223u;
+        std::vector<uint8_t> p(size_t(40 + (x >> 24) % 200));
+        for (uint8_t &b : p) { x = x * 1664525u + 1013904223u; b = uint8_t(x >> 24); }
+        g_emu_audio.packets.push_back(p);
+    }
+}
+static unsigned long long fnv(unsigned long long h, const uint8_t *p, size_t n) { for (size_t i = 0; i < n; ++i) { h ^= p[i]; h *= 1099511628211ull; } return h; }
+static unsigned long long audio_hash(const Mp4Audio &a) {
+    unsigned long long h = 1469598103934665603ull;
+    h = fnv(h, a.asc.data(), a.asc.size());
+    for (const auto &p : a.packets) { const unsigned n = unsigned(p.size()); h = fnv(h, reinterpret_cast<const uint8_t *>(&n), 4); h = fnv(h, p.data(), p.size()); }
+    return h;
+}
+extern "C" unsigned long long emu_audio_hash(void) { return audio_hash(g_emu_audio); }
+
 extern "C" {
 
 // frames: n pictures, I420 tight (w*h*3/2 each).  Writes an MP4 to mp4_path (if not NULL), the Annex B stream to
@@ -192,7 +217,7 @@ int emu_encode_segment(const uint8_t *frames, int n, int w, int h, int fps, int 
         std::vector<Mp4Sample> samples;
         for (int f = 0; f < n; ++f) samples.push_back(Mp4Sample{out.au_offset[f], out.au_size[f], f == 0});
         std::string err;
-        if (!write_mp4(mp4_path, w, h, fps, 1, out.sps_nal, out.pps_nal, out.payload, samples, err)) return -6;
+        if (!write_mp4(mp4_path, w, h, fps, 1, out.sps_nal, out.pps_nal, out.payload, samples, err, g_emu_audio.packets.empty() ? nullptr : &g_emu_audio)) return -6;
     }
     return 0;
 }
@@ -248,7 +273,7 @@ extern "C" int emu_encode_batch(const uint8_t *frames, const int *n, int count, 
 
 // ---- media input (product code media_input.cpp) exercised on the host -------------------------------------
 #include "../../govideocompressor_b200/csrc/media_input.h"
-extern "C" int emu_read_media(const char *path, uint8_t *dst, size_t cap, int *info /* w, h, fps_num, fps_den, frames */, char *err, int err_cap) {
+extern "C" int emu_read_media(const char *path, uint8_t *dst, size_t cap, int *info /* w, h, fps_num, fps_den, frames, has_audio, copyable, packets, rate, channels, hash lo, hash hi */, char *err, int err_cap) {
     std::string e;
     auto src = open_frame_source(path, e);
     if (!src) { snprintf(err, err_cap, "%s", e.c_str()); return -1; }
@@ -264,5 +289,19 @@ extern "C" int emu_read_media(const char *path, uint8_t *dst, size_t cap, int *i
         total += n;
     }
     info[4] = total;
+    info[5] = src->has_audio; info[6] = src->audio_copyable; info[7] = int(src->audio.packets.size()); info[8] = src->audio.sample_rate; info[9] = src->audio.channels;
+    *reinterpret_cast<unsigned long long *>(info + 10) = audio_hash(src->audio);
     return 0;
+}
+
+// ---- the job's argument string (product code ff_args.cpp) parsed on the host ---------------------------------------------------
+#include "../../govideocompressor_b200/csrc/ff_args.h"
+extern "C" int emu_parse_args(const char *args, int *out /* dst_w, dst_h, crf, scale_algo, gop, merange, fps_num, fps_den, drop_audio, bitrate */, char *err, int err_cap) {
+    TranscodeOptions o;
+    std::string e;
+    const int rc = parse_ffmpeg_args(args, o, e);
+    snprintf(err, err_cap, "%s", e.c_str());
+    out[0] = o.dst_w; out[1] = o.dst_h; out[2] = o.crf; out[3] = o.scale_algo; out[4] = o.gop; out[5] = o.merange; out[6] = o.fps_num; out[7] = o.fps_den;
+    out[8] = o.drop_audio; out[9] = int(o.bitrate);
+    return rc;
 }

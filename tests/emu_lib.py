@@ -115,11 +115,35 @@ def read_media(path, max_frames=64, max_w=1920, max_h=1088):
         os.environ["GVC_FFMPEG_LIBDIR"] = d
     lib = load()
     buf = np.zeros(max_frames * max_w * max_h * 3 // 2, np.uint8)
-    info = (ctypes.c_int * 5)()
+    info = (ctypes.c_int * 12)()
     err = ctypes.create_string_buffer(256)
     rc = lib.emu_read_media(os.fsencode(path), ctypes.c_void_p(buf.ctypes.data), ctypes.c_size_t(buf.size), info, err, 256)
     if rc != 0:
         raise RuntimeError(err.value.decode())
     w, h, n = info[0], info[1], info[4]
     fb = w * h * 3 // 2
+    global last_audio
+    last_audio = dict(has_audio=bool(info[5]), copyable=bool(info[6]), packets=info[7], sample_rate=info[8], channels=info[9],
+                      hash=(info[10] & 0xffffffff) | ((info[11] & 0xffffffff) << 32))
     return dict(w=w, h=h, fps=(info[2], info[3]), frames=n), buf[: n * fb].reshape(n, fb).copy()
+
+
+last_audio = None
+
+
+def set_audio(n_packets, seed=1):
+    """MP4 files written by encode_segment from now on carry an AAC track of n_packets pseudo-random packets (0 = none).
+    Returns the hash read_media reports for that track (last_audio["hash"])."""
+    lib = load()
+    lib.emu_set_audio(int(n_packets), int(seed))
+    lib.emu_audio_hash.restype = ctypes.c_ulonglong
+    return int(lib.emu_audio_hash())
+
+
+def parse_args(args):
+    """The product's parser of the job's ffmpeg-style argument string (csrc/ff_args.cpp).  Returns (status, options dict, error text)."""
+    out = (ctypes.c_int * 10)()
+    err = ctypes.create_string_buffer(256)
+    rc = load().emu_parse_args(args.encode(), out, err, 256)
+    keys = ("dst_w", "dst_h", "crf", "scale_algo", "gop", "merange", "fps_num", "fps_den", "drop_audio", "bitrate")
+    return rc, dict(zip(keys, list(out))), err.value.decode()

@@ -287,3 +287,78 @@ def test_batch_reconstruction_matches_the_cpu_emulation(gvc):
         enc.select(k)
         check_decode(enc, streams[k], enc.recon(), w, h, seg.shape[0])
     enc.close()
+
+
+def _mp4_piece(path, w, h, n, seed, fps=25, audio_packets=0, noise=2):
+    """An input piece as the splitter makes them (server.go:199-200): H.264 in MP4, optionally with an AAC track."""
+    frames = S.moving_sequence(w, h, n, seed=seed, noise=noise)
+    want = emu_lib.set_audio(audio_packets, seed=seed) if audio_packets else 0
+    try:
+        emu_lib.encode_segment(frames, w, h, fps=fps, qp_i=14, qp_p=16, mp4_path=path)
+    finally:
+        emu_lib.set_audio(0)
+    return want
+
+
+def test_transcode_carries_the_aac_track_and_an_drops_it(gvc, tmp_path):
+    """The piece's audio stream (server.go:199-200 maps one into every piece) comes out of gvc_transcode_file unchanged: same
+    AudioSpecificConfig, same packets; `-an` drops it; the video next to it still decodes."""
+    w, h, n = 192, 112, 9
+    src = os.path.join(tmp_path, "3.mp4")
+    want = _mp4_piece(src, w, h, n, seed=11, audio_packets=17)
+    out = os.path.join(tmp_path, "c3.mp4")
+    rc, log = gvc.transcode_file(src, "-threads 4 -vcodec libx264 -s 96x56", out)
+    assert rc == 0, log
+    assert "audio: aac (copy)" in log and "audio:17 packets" in log
+    info, _ = emu_lib.read_media(out)
+    a = emu_lib.last_audio
+    assert info["frames"] == n and (info["w"], info["h"]) == (96, 56)
+    assert a["has_audio"] and a["packets"] == 17 and a["hash"] == want and a["sample_rate"] == 44100
+    rc, log = gvc.transcode_file(src, "-vcodec libx264 -an", out)
+    assert rc == 0 and "audio dropped" in log
+    emu_lib.read_media(out)
+    assert not emu_lib.last_audio["has_audio"]
+
+
+def test_transcode_bitrate_mode_lands_on_the_requested_rate(gvc, tmp_path):
+    """`-b:v`: the option surface of north_star keeps "CRF/bitrate".  Two targets on the same piece, several GOPs (-g 12): the
+    file's video bitrate is within 10 % of each target and the log shows the QP search."""
+    w, h, n, fps = 320, 192, 48, 24
+    src = os.path.join(tmp_path, "8.mp4")
+    _mp4_piece(src, w, h, n, seed=13, fps=fps, noise=6)
+    out = os.path.join(tmp_path, "c8.mp4")
+    sizes = {}
+    for target in (900_000, 300_000):
+        rc, log = gvc.transcode_file(src, "-vcodec libx264 -g 12 -b:v %dk" % (target // 1000), out)
+        assert rc == 0, log
+        assert "gop 3:" in log and "bitrate %d kb/s" % (target // 1000) in log
+        kbps = float(log.split("bitrate=")[1].split("kbits/s")[0])
+        sizes[target] = kbps
+        assert abs(kbps * 1000 - target) <= 0.10 * target, f"asked for {target} b/s, got {kbps} kb/s\n{log}"
+        info, _ = emu_lib.read_media(out)
+        assert info["frames"] == n
+    assert sizes[900_000] > 2 * sizes[300_000]
+
+
+def test_transcode_output_rate_drops_or_repeats_pictures_and_state_is_reused(gvc, tmp_path):
+    """`-r`: half the rate keeps every second picture, double repeats each one (the duration stays, as with ffmpeg's output -r).
+    Pieces of one shape reuse the encoder and the pinned staging memory of the previous call (the worker loops forever,
+    client.go:37): the allocation counter stands still from the second piece on."""
+    import ctypes
+    w, h, n = 160, 96, 10
+    src = os.path.join(tmp_path, "2.mp4")
+    _mp4_piece(src, w, h, n, seed=17, fps=30)
+    out = os.path.join(tmp_path, "c2.mp4")
+    lib = gvc.load_library()
+    lib.gvc_transcode_allocations.restype = ctypes.c_long
+    for args, frames, rate in (("-vcodec libx264", n, 30), ("-vcodec libx264 -r 15", n // 2, 15), ("-vcodec libx264 -r 60", 2 * n, 60)):
+        rc, log = gvc.transcode_file(src, args, out)
+        assert rc == 0, log
+        info, _ = emu_lib.read_media(out)
+        assert info["frames"] == frames and info["fps"] == (rate, 1), (args, info)
+    rc, _ = gvc.transcode_file(src, "-vcodec libx264 -crf 30", out)
+    before = lib.gvc_transcode_allocations()
+    for crf in (20, 30):
+        rc, log = gvc.transcode_file(src, "-vcodec libx264 -crf %d" % crf, out)
+        assert rc == 0
+    assert lib.gvc_transcode_allocations() == before, "a second piece of the same shape allocated again"

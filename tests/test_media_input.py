@@ -53,3 +53,26 @@ def test_mp4_h264_segment_is_demuxed_and_decoded(tmp_path):
     open(junk, "wb").write(b"this is not a video" * 10)
     with pytest.raises(RuntimeError):
         emu_lib.read_media(junk)
+
+
+@pytest.mark.skipif(emu_lib.ffmpeg_libdir() is None, reason="no FFmpeg shared libraries in this image")
+def test_aac_track_is_found_and_its_packets_come_back_unchanged(tmp_path):
+    """The reference's pieces carry an audio stream (server.go:199-200).  The MP4 writer's AAC track is seen by libavformat, and
+    the product's reader hands back exactly the packets that went in (they are stream-copied into the output, never decoded)."""
+    w, h, n = 96, 64, 6
+    frames = S.moving_sequence(w, h, n, seed=3)
+    p = os.path.join(tmp_path, "5.mp4")
+    want = emu_lib.set_audio(23, seed=9)
+    try:
+        emu_lib.encode_segment(frames, w, h, fps=25, mp4_path=p)
+    finally:
+        emu_lib.set_audio(0)
+    info, got = emu_lib.read_media(p)
+    assert info["frames"] == n
+    a = emu_lib.last_audio
+    assert a["has_audio"] and a["copyable"] and a["packets"] == 23 and a["sample_rate"] == 44100 and a["channels"] == 2
+    assert a["hash"] == want
+    q = os.path.join(tmp_path, "6.mp4")                       # a piece without sound
+    emu_lib.encode_segment(frames, w, h, fps=25, mp4_path=q)
+    emu_lib.read_media(q)
+    assert not emu_lib.last_audio["has_audio"] and emu_lib.last_audio["packets"] == 0

@@ -89,3 +89,37 @@ def test_job_string_longer_than_100_bytes_is_truncated_like_the_reference():
     c.sendall(b"fail;0;truncated")
     c.close()
     server.join(5)
+
+
+def test_the_documented_argument_grammar_is_the_parsers_grammar():
+    """INTEGRATION.md's option table is the contract a maintainer of the Go side reads (the job string of server.go:179 is free
+    form).  Every example in it must parse (together with the mandatory codec option), every listed option name too, and
+    options the table does not list must be refused."""
+    import os
+    import re
+    import emu_lib
+    doc = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "INTEGRATION.md")).read()
+    rows = re.findall(r"^\| (`-[^|]*) \| `([^`]*)` \|", doc, flags=re.M)
+    assert len(rows) >= 15, "option table not found in INTEGRATION.md"
+    listed = set()
+    for names, example in rows:
+        opts = re.findall(r"`(-[^`]+)`", names)
+        listed.update(opts)
+        args = example if example.split()[0] in ("-vcodec", "-c:v", "-codec:v") else "-vcodec libx264 " + example
+        rc, opt, err = emu_lib.parse_args(args)
+        assert rc == 0, f"documented example {example!r} is refused: {err}"
+        for o in opts:                                     # every spelling of the option, with the example's value
+            alt = " ".join([o] + example.split()[1:])
+            alt = alt if o in ("-vcodec", "-c:v", "-codec:v") else "-vcodec libx264 " + alt
+            assert emu_lib.parse_args(alt)[0] == 0, f"documented option {o!r} is refused"
+    assert emu_lib.parse_args("-vcodec libx264 -b:v 2M")[1]["bitrate"] == 2000000
+    assert emu_lib.parse_args("-vcodec libx264 -b:v 800k")[1]["bitrate"] == 800000
+    assert emu_lib.parse_args("-vcodec libx264 -an")[1]["drop_audio"] == 1
+    assert emu_lib.parse_args("-threads 4 -vcodec libx264")[0] == 0                    # server.go:69-70, the "264" shorthand
+    assert emu_lib.parse_args("-threads 4 -vcodec libx265 -crf 26")[0] == -5           # server.go:67-68, the "265" shorthand: unsupported
+    for bad in ("-bogus 1", "-bf 2", "-vcodec libx264 -acodec mp3", "-vcodec libx264 -b:v fast", "-vcodec libx264 -vf hflip", "-crf 23"):
+        assert emu_lib.parse_args(bad)[0] != 0, f"{bad!r} should be refused"
+    # the parser knows no option the table does not list
+    src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "govideocompressor_b200", "csrc", "ff_args.cpp")).read()
+    known = set(re.findall(r'k == "(-[^"]+)"', src))
+    assert known == listed, f"parser and document disagree: {sorted(known ^ listed)}"
