@@ -5,6 +5,6 @@ The product is libgvc.so (hand-written CUDA behind the C ABI in include/gvc.h). 
 thin Python host mirror used by tests and bench.py; it binds the C ABI with ctypes and has no CPU
 fallback: importing works anywhere, but every compute call needs the built library and a B200.
 """
-from .lib import GvcError, load_library, library_path, init, version  # noqa: F401
+from .lib import GvcError, load_library, library_path, init, version, psnr_ssim  # noqa: F401
 from .resize import ResizePlan, BICUBIC, BILINEAR, YUV420P, NV12  # noqa: F401
 from .encoder import Encoder, transcode_file, convert  # noqa: F401

@@ -56,6 +56,7 @@ def load_library():
     lib.gvc_encode_intra.argtypes = [vp] * 6 + [c_int] * 5 + [vp] * 5
     lib.gvc_transform8x8.argtypes = [vp, c_int, vp, c_int, vp, c_int, c_int, c_int, c_int, c_int, vp, vp, vp]
     lib.gvc_lambda_for_qp.argtypes = [c_int]
+    lib.gvc_psnr_ssim.argtypes = [vp, c_int, vp, c_int, c_int, c_int, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_double), vp]
     _LIB = lib
     return lib
 
@@ -77,3 +78,14 @@ def init(device=-1):
 
 def version():
     return load_library().gvc_version().decode()
+
+
+def psnr_ssim(a_ptr, stride_a, b_ptr, stride_b, w, h, stream=None):
+    """gvc_psnr_ssim on two DEVICE planes: returns (ssd, mean SSIM, PSNR in dB)."""
+    import math
+    lib = load_library()
+    ssd, ssim = ctypes.c_ulonglong(0), ctypes.c_double(0)
+    check(lib.gvc_psnr_ssim(ctypes.c_void_p(a_ptr), stride_a, ctypes.c_void_p(b_ptr), stride_b, w, h, ctypes.byref(ssd), ctypes.byref(ssim),
+                            ctypes.c_void_p(stream) if stream else None), "gvc_psnr_ssim")
+    psnr = 100.0 if ssd.value == 0 else 10.0 * math.log10(255.0 * 255.0 * w * h / ssd.value)
+    return ssd.value, ssim.value, psnr

@@ -171,6 +171,14 @@ int gvc_transform8x8(const uint8_t *src, int sstride, const uint8_t *pred, int p
 /* x264_lambda_tab[qp] */
 int gvc_lambda_for_qp(int qp);
 
+/* ---------------------------------------------------------------- quality (K9) --------------- */
+/* Measures a coded plane against its source the way north_star's tier 2 states the tolerance (PSNR, SSIM): x264's
+ * pixel_ssd_wxh and pixel_ssim_wxh (common/pixel.c; what `ffmpeg -psnr -ssim` with libx264 reports for the spawned process of
+ * client.go:115).  a, b: DEVICE pointers to two w x h planes.  *ssd = sum of squared differences (PSNR = 10 log10(255^2 w h /
+ * ssd)); *ssim = mean SSIM over the 8x8 windows stepping by 4 samples.  Synchronous on `stream`. */
+int gvc_psnr_ssim(const uint8_t *a, int stride_a, const uint8_t *b, int stride_b, int w, int h, unsigned long long *ssd,
+                  double *ssim, void *stream);
+
 /* ---------------------------------------------------------------- segment encoder ------------- */
 /* Replaces: what one spawned `ffmpeg -i <id>.mp4 <args> c<id>.mp4` does for one piece (client.go:101-130):
  * resize, H.264 encode (IDR + P pictures, closed GOP per call), container.  Kernels run on the library's own

@@ -97,6 +97,8 @@ void gvc_oracle_mc_chroma(uint8_t *dst, int dstride, const uint8_t *src, int str
 
 /* ---------------------------------------------------------------- frame-level composition (h264_mb.c) ------ */
 int  gvc_oracle_lambda(int qp);
+/* quality.c: x264 pixel_ssd_wxh / pixel_ssim_wxh (mean SSIM over the 8x8 windows, accumulated in double) of two w x h planes */
+void gvc_oracle_psnr_ssim(const uint8_t *a, int sa, const uint8_t *b, int sb, int w, int h, uint64_t *ssd, double *ssim);
 int  gvc_oracle_se_bits(int v);
 void gvc_oracle_me_lowres(const uint8_t *cur, const uint8_t *ref, int stride, int mbw, int mbh, int r, int lambda,
                           int16_t *out_mv, int32_t *out_cost);

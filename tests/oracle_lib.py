@@ -161,3 +161,11 @@ def mc_chroma(plane_padded, pad, bx, by, mvx, mvy, w, h):
     load().gvc_oracle_mc_chroma(_p(dst), w, ctypes.c_void_p(plane_padded.ctypes.data + pad * stride + pad), stride,
                                 bx, by, mvx, mvy, w, h)
     return dst
+
+
+def psnr_ssim(a, b):
+    """x264 pixel_ssd_wxh / pixel_ssim_wxh of two equally sized uint8 planes: (ssd, mean ssim)."""
+    a, b = np.ascontiguousarray(a, np.uint8), np.ascontiguousarray(b, np.uint8)
+    ssd, ssim = ctypes.c_uint64(0), ctypes.c_double(0)
+    load().gvc_oracle_psnr_ssim(_p(a), a.strides[0], _p(b), b.strides[0], a.shape[1], a.shape[0], ctypes.byref(ssd), ctypes.byref(ssim))
+    return ssd.value, ssim.value
