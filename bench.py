@@ -1,20 +1,26 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the segment compress hot path (BASELINE.json: 1080p->720p H.264 frames/sec).
 
-A "step" is one pass of the hot path over the cfg2 workload on one GPU: the 10 s 1080p30 clip split into 8 segments of 38
-pictures (1920x1080 I420), all 8 in flight on the GPU at once (one encoder object and CUDA stream per segment, the way 8
-reference workers would share a box): resize to 1280x720 (bicubic), then the H.264 encode kernels (IDR + 37 P pictures
-per segment: lowres, motion search, motion compensation + transform/quant/reconstruction, border extension, half-sample
-planes).  One process per GPU; with N GPUs every rank encodes its own clip (segments share nothing: weak scaling, no
-collective on the data path).
+A "step" is one pass of the hot path over one GPU's share of the configured workload (default cfg2: the 10 s 1080p30 clip
+split into 8 segments of 38 pictures, 1920x1080 I420): resize (bicubic) and H.264 encode (IDR + P pictures per segment:
+lowres, motion search, motion compensation + transform/quant/reconstruction, border extension, half-sample planes, CAVLC).
+The segments of a step are encoded as batches: within a batch they advance picture by picture together, ONE kernel launch
+per stage for all of them.  One process per GPU; with N GPUs every rank encodes its own clip (segments share nothing: weak
+scaling, no collective on the data path).
 
-  value   pictures/s over all ranks, source pictures resident in HBM, every GPU stage, CUDA events on the encoder's stream
-  e2e     the same metric through the C ABI with pinned HOST pictures in and the H.264 stream out
-          (gvc_encoder_encode_host: H2D + kernels + D2H of the macroblock records + CAVLC on host threads)
+  value     pictures/s over all ranks, source pictures resident in HBM, every GPU stage, CUDA events on the encoders' streams
+  e2e       the same metric through the C ABI with pinned HOST pictures in and the H.264 streams out
+  e2e_file  the call the Go worker makes (gvc_transcode_file) on the workload's pieces as .mp4 files: host demux + H.264
+            decode by FFmpeg's libraries, H2D, kernels, MP4 out (cfg2 only; one piece at a time, like one worker)
+  quality   PSNR / SSIM (x264's pixel_ssd / pixel_ssim, on the device) of the reconstruction against the resized source,
+            and the bitrate, for the benchmarked clip
   roofline / stages / cpu_baseline / clocks: see DESIGN.md "Measurement"
 
+--config cfg1|cfg2|cfg3|cfg4 selects BASELINE.json's configurations (the metric is quoted on cfg2, the default);
+--clip testsrc|pan the content (SURVEY 8(d) testsrc-style clip, or a globally translating texture where no macroblock
+leaves the motion search early).
 `--impl reference` times the CPU implementation of the same path on the host cores: FFmpeg's libswscale (the image's
-bundled build) for the resize and the oracle port (oracle/*.c) for the x264-semantics stages, one short segment per core.
+bundled build) for the resize and the oracle port (oracle/*.c) for the x264-semantics stages, one whole segment per core.
 """
 import argparse
 import json
@@ -28,31 +34,58 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 
-SW, SH, DW, DH = 1920, 1080, 1280, 720
-SEG_FRAMES = 38                      # ceil(300 pictures / 8 segments)
-NSEG = 8                             # segments of the clip, all in flight on one GPU
 CRF = 23
-NMB = (DW // 16) * (DH // 16)
 METRIC = "1080p->720p H.264 frames/sec"
-CONFIG = {"workload": "cfg2: 10 s 1080p30 synthetic testsrc-style clip (SURVEY.md 8d) in 8 segments of 38 pictures, the whole clip per GPU per step (8 segments "
-                      "in flight), 1920x1080 -> 1280x720 bicubic + H.264 (IDR+P, crf 23, me_range 16)",
-          "segment_frames": SEG_FRAMES, "segments_per_step": NSEG, "crf": CRF,
-          "l2": "inputs larger than L2: 8 source segments = 945 MB per step, each read once",
-          "parallelism": "clip-per-GPU (8 independent segments each), no collective"}
-# ALGORITHMIC bytes per launch (SURVEY.md 8(d) formulas at the coded size 1280x720; DESIGN.md "Measurement")
-WH = DW * DH
-ALGO_BYTES = {"resize": int(1.5 * (SW * SH + WH)) * SEG_FRAMES,     # one launch covers the segment
-              "hpel": 4 * WH, "lowres": WH + WH // 4, "me_lowres": WH // 2 + 4 * NMB, "me_refine": 5 * WH + 24 * NMB,
-              "encode_inter": int(7.5 * WH), "encode_intra": 6 * WH, "border": None, "entropy": None}
+# BASELINE.json configs made concrete; per GPU and step: `nseg` segments of `seg` pictures
+CONFIGS = {
+    "cfg1": dict(sw=1920, sh=1080, dw=1920, dh=1080, seg=300, nseg=1, merange=16,
+                 what="cfg1: 10 s 1080p30 synthetic clip as ONE segment of 300 pictures, no resize, H.264 (IDR+P, crf 23, me_range 16)"),
+    "cfg2": dict(sw=1920, sh=1080, dw=1280, dh=720, seg=38, nseg=8, merange=16,
+                 what="cfg2: 10 s 1080p30 synthetic clip (SURVEY.md 8d) in 8 segments of 38 pictures, the whole clip per GPU per step, "
+                      "1920x1080 -> 1280x720 bicubic + H.264 (IDR+P, crf 23, me_range 16)"),
+    "cfg3": dict(sw=3840, sh=2160, dw=1920, dh=1080, seg=56, nseg=8, merange=32,
+                 what="cfg3: 60 s 4K60 synthetic clip in 64 segments of 56 pictures, 8 segments per GPU per step, 3840x2160 -> 1920x1080 "
+                      "bicubic + H.264 (IDR+P, crf 23, me_range 32)"),
+    "cfg4": dict(sw=1280, sh=720, dw=854, dh=480, seg=60, nseg=32, merange=16,
+                 what="cfg4: 256 clips of 2 s 720p30 (60 pictures), 32 clips per GPU per step, 1280x720 -> 854x480 bicubic + H.264 "
+                      "(IDR+P, crf 23, me_range 16)"),
+}
 
 
-def synth_segment(seed, n=SEG_FRAMES):
-    """SURVEY.md 8(d) synthetic testsrc-style clip (colour bars, translating gradient, orbiting box, LCG-noise patch), I420."""
+def workload(name, clip):
+    c = dict(CONFIGS[name])
+    c["name"], c["clip"] = name, clip
+    c["w16"], c["h16"] = (c["dw"] + 15) // 16 * 16, (c["dh"] + 15) // 16 * 16
+    c["nmb"] = (c["w16"] // 16) * (c["h16"] // 16)
+    c["frame_bytes"] = c["sw"] * c["sh"] * 3 // 2
+    return c
+
+
+def config_json(c, batches=None):
+    src_mb = c["nseg"] * c["seg"] * c["frame_bytes"] / 1e6
+    out = {"workload": c["what"], "config": c["name"], "clip": c["clip"], "segment_frames": c["seg"], "segments_per_step": c["nseg"], "crf": CRF,
+           "l2": "inputs larger than L2: %.0f MB of source pictures per step, each read once" % src_mb,
+           "parallelism": "clip-per-GPU (%d independent segments each), no collective" % c["nseg"]}
+    return out
+
+
+def algo_bytes(c):
+    """ALGORITHMIC bytes per picture and stage (SURVEY.md 8(d) formulas at the coded size; DESIGN.md "Measurement")."""
+    wh, nmb = c["w16"] * c["h16"], c["nmb"]
+    resize = int(1.5 * (c["sw"] * c["sh"] + c["dw"] * c["dh"])) if (c["sw"], c["sh"]) != (c["dw"], c["dh"]) else None
+    return {"resize": resize, "hpel": 4 * wh, "lowres": wh + wh // 4, "me_lowres": wh // 2 + 4 * nmb, "me_refine": 5 * wh + 24 * nmb,
+            "encode_inter": int(7.5 * wh), "encode_intra": 6 * wh, "border": None, "entropy": None}
+
+
+def synth_segment(c, seed, n=None):
+    """One segment of the configured clip, I420: SURVEY.md 8(d) testsrc-style content (colour bars, translating gradient,
+    orbiting box, LCG-noise patch) or the translating texture."""
     import numpy as np
     from util_inputs import make_frame
-    seg = np.empty((n, SW * SH * 3 // 2), np.uint8)
+    n = n or c["seg"]
+    seg = np.empty((n, c["frame_bytes"]), np.uint8)
     for f in range(n):
-        seg[f] = np.concatenate([p.reshape(-1) for p in make_frame(SW, SH, "yuv420p", "testsrc", seed, t=f)])
+        seg[f] = np.concatenate([p.reshape(-1) for p in make_frame(c["sw"], c["sh"], "yuv420p", c["clip"], seed, t=f)])
     return seg
 
 
@@ -110,14 +143,15 @@ _CPU_SEG = {}
 def _cpu_worker(args):
     """One whole segment of the workload through the CPU path (runs in a worker process; the segment's source pictures are
     made once per process and kept, so that only the path itself is timed)."""
-    seed, n = args
+    name, clip, seed, n = args
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
     import oracle_segment
-    if (seed, n) not in _CPU_SEG:
+    c = workload(name, clip)
+    if args not in _CPU_SEG:
         _CPU_SEG.clear()
-        _CPU_SEG[(seed, n)] = synth_segment(seed, n)
-    frames = _CPU_SEG[(seed, n)]
+        _CPU_SEG[args] = synth_segment(c, seed, n)
+    frames = _CPU_SEG[args]
     try:
         import sws_ref
         sws_ref.load()
@@ -125,33 +159,35 @@ def _cpu_worker(args):
     except Exception:
         real = False
     t0 = time.perf_counter()
-    oracle_segment.encode_segment(frames, SW, SH, DW, DH, qp_i=CRF - 3, qp_p=CRF, merange=16, use_libswscale=real)
+    oracle_segment.encode_segment(frames, c["sw"], c["sh"], c["dw"], c["dh"], qp_i=CRF - 3, qp_p=CRF, merange=c["merange"], use_libswscale=real)
     return time.perf_counter() - t0, real
 
 
 class CpuArm:
-    """`cores` worker processes, each encoding its own whole segment (SEG_FRAMES pictures: 1 IDR + P) per step, side by side:
-    pictures/s of the whole host.  The pool lives across steps so every step times the path only."""
+    """`cores` worker processes, each encoding its own whole segment of the workload (1 IDR + P pictures) per step, side by
+    side: pictures/s of the whole host.  The pool lives across steps so every step times the path only.  Segments longer than
+    `max_frames` pictures are cut to that many (the rate per picture of a P-picture run does not depend on its length)."""
 
-    def __init__(self, cores, frames_per_segment=SEG_FRAMES):
+    def __init__(self, c, cores, max_frames=38):
         from concurrent.futures import ProcessPoolExecutor
         import multiprocessing as mp
-        self.cores, self.n = cores, frames_per_segment
+        self.c, self.cores, self.n = c, cores, min(c["seg"], max_frames)
         self.ex = ProcessPoolExecutor(cores, mp_context=mp.get_context("spawn"))
         self.real = True
 
     def step(self):
         t0 = time.perf_counter()
-        res = list(self.ex.map(_cpu_worker, [(s, self.n) for s in range(self.cores)], chunksize=1))
+        res = list(self.ex.map(_cpu_worker, [(self.c["name"], self.c["clip"], s, self.n) for s in range(self.cores)], chunksize=1))
         wall = time.perf_counter() - t0
         busy = max(r[0] for r in res)              # workers run side by side; the slowest one bounds the throughput
         self.real = all(r[1] for r in res)
         return self.cores * self.n / busy, busy, wall
 
     def describe(self):
-        return ("%d processes x 1 segment of %d pictures (1 IDR + %d P) of the cfg2 clip per step; resize by %s, all other stages by "
+        return ("%d processes x 1 segment of %d pictures (1 IDR + %d P) of the %s %s clip per step; resize by %s, all other stages by "
                 "the oracle port (oracle/*.c, -O3, no hand-written SIMD); no entropy coding on this arm" %
-                (self.cores, self.n, self.n - 1, "FFmpeg libswscale 9.1.100 (bit-exact flags)" if self.real else "the oracle port"))
+                (self.cores, self.n, self.n - 1, self.c["name"], self.c["clip"],
+                 "FFmpeg libswscale 9.1.100 (bit-exact flags)" if self.real else "the oracle port"))
 
     def close(self):
         self.ex.shutdown()
@@ -160,25 +196,93 @@ class CpuArm:
 def run_reference(args, rank):
     if rank != 0:
         return
+    c = workload(args.config, args.clip)
     cores = os.cpu_count() or 1
-    arm = CpuArm(cores)
+    arm = CpuArm(c, cores)
     arm.step()                                      # builds every worker's source segment; also the first warm-up step
     for _ in range(max(0, args.warmup - 1)):
         arm.step()
-    vals, busy = [], []
+    busy = []
     for _ in range(args.steps):
-        v, b, _ = arm.step()
-        vals.append(v)
-        busy.append(b)
+        busy.append(arm.step()[1])
     desc = arm.describe()
+    n = arm.n
     arm.close()
-    v = cores * SEG_FRAMES * len(busy) / sum(busy)
+    v = cores * n * len(busy) / sum(busy)
     print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus,
                       "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(busy) / len(busy),
                       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                      "config": CONFIG,
+                      "config": config_json(c),
                       "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": desc},
                       "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def measure_quality(gvc, torch, np, c, seg_frames, n_pictures=None):
+    """PSNR-Y/U/V and SSIM-Y (mean over the pictures, as x264 reports them) of one segment's reconstruction against the resized
+    source, and its bitrate at 30 pictures/s -- all pictures of the segment unless n_pictures says fewer."""
+    n = min(n_pictures or seg_frames.shape[0], seg_frames.shape[0])
+    frames = seg_frames[:n]
+    enc = gvc.Encoder(c["sw"], c["sh"], c["dw"], c["dh"], fps=(30, 1), crf=CRF, merange=c["merange"], keep_recon=True)
+    stream = enc.encode_host(frames, annexb=False)
+    recon = torch.from_numpy(enc.recon()).cuda()
+    w, h, w16, h16 = c["dw"], c["dh"], enc.w16, enc.h16
+    src = torch.from_numpy(frames).cuda()
+    if (c["sw"], c["sh"]) != (w, h):
+        plan = gvc.ResizePlan(c["sw"], c["sh"], w, h)
+        ref = torch.zeros((n, plan.frame_bytes(w, h)), dtype=torch.uint8, device="cuda")
+        plan.resize_device(src, ref, n)
+        torch.cuda.synchronize()
+        plan.close()
+    else:
+        ref = src
+    cw, ch = w // 2, h // 2
+    acc = {"psnr_y": [], "psnr_u": [], "psnr_v": [], "ssim_y": []}
+    for f in range(n):
+        a, b = ref[f].data_ptr(), recon[f].data_ptr()
+        _, ssim, py = gvc.psnr_ssim(a, w, b, w16, w, h)
+        _, _, pu = gvc.psnr_ssim(a + w * h, cw, b + w16 * h16, w16 // 2, cw, ch)
+        _, _, pv = gvc.psnr_ssim(a + w * h + cw * ch, cw, b + w16 * h16 * 5 // 4, w16 // 2, cw, ch)
+        acc["psnr_y"].append(py); acc["psnr_u"].append(pu); acc["psnr_v"].append(pv); acc["ssim_y"].append(ssim)
+    enc.close()
+    out = {k: float(np.mean(v)) for k, v in acc.items()}
+    out["kbit_per_s"] = len(stream) * 8 / 1000.0 / (n / 30.0)
+    out["pictures"] = n
+    out["note"] = ("mean over the pictures of one segment (1 IDR + P), reconstruction vs the resized source, x264's pixel_ssd / pixel_ssim "
+                   "on the device (gvc_psnr_ssim); no libx264 exists on this box to compare with (tier 2 unmeasured)")
+    return out
+
+
+def measure_transcode_file(gvc, c, segments, workdir):
+    """gvc_transcode_file -- the one call the Go worker makes -- on the step's pieces as <id>.mp4 files (H.264, made here with
+    this encoder at crf 12), one piece at a time like one worker: pictures/s including host demux + H.264 decode."""
+    import shutil
+    os.makedirs(workdir, exist_ok=True)
+    try:
+        enc = gvc.Encoder(c["sw"], c["sh"], fps=(30, 1), crf=12)
+        paths = []
+        for i, seg in enumerate(segments):
+            enc.encode_host(seg)
+            p = os.path.join(workdir, "%d.mp4" % i)
+            enc.write_mp4(p)
+            paths.append(p)
+        enc.close()
+        args = "-threads 4 -vcodec libx264 -crf %d" % CRF + (" -s %dx%d" % (c["dw"], c["dh"]) if (c["sw"], c["sh"]) != (c["dw"], c["dh"]) else "")
+        rc, log = gvc.transcode_file(paths[0], args, os.path.join(workdir, "c0.mp4"))      # warm-up: encoder + pinned memory are created here
+        if rc != 0:
+            return {"unavailable": log.strip().splitlines()[-1] if log else "status %d" % rc}
+        t0 = time.perf_counter()
+        n = 0
+        for i, p in enumerate(paths):
+            rc, log = gvc.transcode_file(p, args, os.path.join(workdir, "c%d.mp4" % i))
+            if rc != 0:
+                return {"unavailable": log.strip().splitlines()[-1]}
+            n += segments[i].shape[0]
+        dt = time.perf_counter() - t0
+        return {"value": n / dt, "unit": "frames/s", "pieces": len(paths), "args": args,
+                "note": "gvc_transcode_file on .mp4 pieces, one at a time (one worker process): host demux + H.264 decode (FFmpeg's libavcodec, "
+                        "one thread) + H2D + kernels + MP4 out"}
+    finally:
+        shutil.rmtree(workdir, ignore_errors=True)
 
 
 def main():
@@ -187,7 +291,10 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gvc", choices=["gvc", "reference"])
+    ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS))
+    ap.add_argument("--clip", default="testsrc", choices=["testsrc", "pan"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the quality and e2e_file measurements")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels one by one instead of replaying CUDA graphs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -197,11 +304,22 @@ def main():
         run_reference(args, rank)
         return
     args.warmup = max(args.warmup, 3)
+    c = workload(args.config, args.clip)
+    cores = os.cpu_count() or 1
+    # every rank gets its own share of the host cores BEFORE it allocates pinned memory or starts threads (first-touch placement
+    # of the staging buffers, no migration of the issuing threads between ranks' cores)
+    if world > 1 and hasattr(os, "sched_setaffinity"):
+        try:
+            avail = sorted(os.sched_getaffinity(0))
+            per = max(1, len(avail) // world)
+            os.sched_setaffinity(0, set(avail[local * per:(local + 1) * per]) or set(avail))
+            cores = per
+        except OSError:
+            pass
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:     # before CUDA is initialised in this process
-        cores = os.cpu_count() or 1
-        arm = CpuArm(cores)
+        arm = CpuArm(c, cores)
         arm.step()                                  # makes the source segments (untimed), warms the workers
         v, busy, wall = arm.step()
         cpu = {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": arm.describe() + "; one step, %.1f s" % busy}
@@ -216,23 +334,21 @@ def main():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"      # the version banner goes to stdout: rank 0 prints ONE JSON line and nothing else
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     gvc.init(local)
-    cores = os.cpu_count() or 1
-    # The clip's NSEG segments are encoded as NENC batches of NSEG / NENC segments: within a batch the segments advance picture by
-    # picture together, one kernel launch per stage for all of them (one CUDA graph per batch, replayed per step); the batches run
-    # on their own streams, each issued by its own host thread, so one batch's dependent chain fills the other's gaps.
-    NENC = int(os.environ.get("GVC_BENCH_ENCODERS", "2"))
-    assert NSEG % NENC == 0
+    SW, SH, DW, DH, SEG_FRAMES, NSEG = c["sw"], c["sh"], c["dw"], c["dh"], c["seg"], c["nseg"]
+    # The step's NSEG segments are encoded as NENC batches: within a batch the segments advance picture by picture together, one
+    # kernel launch per stage for all of them (one CUDA graph per batch, replayed per step); the batches run on their own streams,
+    # each issued by its own host thread, so one batch's dependent chain fills the other's gaps.
+    NENC = int(os.environ.get("GVC_BENCH_ENCODERS", "2" if NSEG % 2 == 0 else "1"))
+    assert NSEG % NENC == 0 and NSEG // NENC <= 16
     PER = NSEG // NENC
-    encs = [gvc.Encoder(SW, SH, DW, DH, fps=(30, 1), crf=CRF, merange=16, host_threads=max(1, cores // NENC), disable_graph=args.no_graph, max_batch=PER)
+    encs = [gvc.Encoder(SW, SH, DW, DH, fps=(30, 1), crf=CRF, merange=c["merange"], host_threads=max(1, cores // NENC), disable_graph=args.no_graph, max_batch=PER)
             for _ in range(NENC)]
     enc = encs[0]
     fb = enc.frame_bytes()
 
-    seg0 = synth_segment(rank)
+    seg0 = synth_segment(c, rank)
     host_src = [torch.from_numpy(seg0 if b == 0 else np.roll(seg0, 5 * b, axis=0)).pin_memory() for b in range(NSEG)]
     dev_src = [h.cuda() for h in host_src]
     counts = [SEG_FRAMES] * PER
@@ -266,7 +382,7 @@ def main():
     def run_host(steps):
         list(pool.map(lambda k: slot_host(k, steps), range(NENC)))
 
-    # ---- device-resident timing: every GPU stage of the path, the whole clip per step -------
+    # ---- device-resident timing: every GPU stage of the path, the whole share per step -------
     run_device(args.warmup)
     sampler = ClockSampler(local)
     barrier()
@@ -318,6 +434,15 @@ def main():
             stream_bytes += int(e.stats()[:, 3].sum())     # the step's result as read on the host
             d2h_bytes += e.record_bytes()
     e2e = world * NSEG * SEG_FRAMES * args.steps / farm.max_over_ranks(e2e_s, "cuda")
+    for e in encs:
+        e.close()
+
+    quality = e2e_file = None
+    if rank == 0 and not args.no_extras:
+        quality = measure_quality(gvc, torch, np, c, seg0, 38)
+        if args.config == "cfg2":
+            e2e_file = measure_transcode_file(gvc, c, [seg0 if b == 0 else np.roll(seg0, 5 * b, axis=0) for b in range(NSEG)],
+                                              os.path.join(os.environ.get("TMPDIR", "/tmp"), "gvc_bench_pieces_%d" % os.getpid()))
 
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -325,17 +450,18 @@ def main():
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
         else:
             peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+        AB = algo_bytes(c)
         table, launches = {}, 0
         for name, (ms, n) in stages.items():
             launches += n * (4 if name == "entropy" else PER if name == "resize" else 1)    # entropy: four kernels per entry; resize: one launch per segment
             if n == 0:
                 continue
             avg = ms / n
-            b = ALGO_BYTES.get(name)
-            if name == "resize":
-                b = b * PER                         # the entry brackets the batch's resize launches (one per segment)
-            elif b:
-                b = b * PER                         # one launch covers one picture of every segment of the batch
+            b = AB.get(name)
+            if b:
+                # one launch covers one picture of every segment of the batch; a resize entry brackets the batch's launches (one per
+                # segment, a segment's pictures each)
+                b = b * PER * (SEG_FRAMES if name == "resize" else 1)
             table[name] = {"launches_per_step": n / args.steps, "ms_per_step": ms / args.steps, "avg_launch_ms": avg,
                            "share_of_kernel_time": None, "algorithmic_bytes_per_launch": b,
                            "achieved_gbs": (b / (avg * 1e-3) / 1e9) if b else None}
@@ -348,32 +474,37 @@ def main():
         dom = max((k for k in table if table[k]["algorithmic_bytes_per_launch"]), key=lambda k: table[k]["ms_per_step"])
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath):
-            traffic = json.load(open(tpath)).get(dom)
+        if os.path.exists(tpath) and args.config == "cfg2":
+            t = json.load(open(tpath)).get(dom)
+            traffic = t * PER if isinstance(t, (int, float)) else t       # the file holds bytes per picture; a launch covers PER pictures
         d = table[dom]
+        cfg = config_json(c)
+        cfg.update({"batches": NENC, "segments_per_batch": PER})
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": CONFIG,
+                "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg,
                 "wall_ms_per_step": wall_ms / args.steps,
                 "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": NSEG * SEG_FRAMES * fb,
                         "d2h_bytes_per_step": d2h_bytes,
                         "stream_bytes_per_step": stream_bytes, "host_threads": cores},
-                # stage pass counts + the one-thread kernel that raises each picture's arrival flag (not a timed stage)
-                "gpu_launches": (launches + SEG_FRAMES * args.steps) * NENC, "batches": NENC, "segments_per_batch": PER, "clocks": clocks, "one_segment_alone_ms": one_segment_ms,
+                # stage pass counts + the small kernel that raises each picture's arrival flags (not a timed stage)
+                "gpu_launches": (launches + SEG_FRAMES * args.steps) * NENC, "clocks": clocks, "one_segment_alone_ms": one_segment_ms,
                 "roofline": {"kernel": dom, "bound": "hbm", "achieved": d["achieved_gbs"], "peak": peak, "unit": "GB/s",
                              "frac": (d["achieved_gbs"] / peak) if d["achieved_gbs"] else None, "traffic": traffic,
                              "peak_source": peak_src, "algorithmic_bytes_per_launch": d["algorithmic_bytes_per_launch"],
                              "launch_ms_avg": d["avg_launch_ms"], "share_of_step": d["share_of_kernel_time"],
                              "note": "dominant single kernel by accumulated CUDA-event time in the stage pass: the same batched launches as the timed "
-                                     "region (one launch per stage for the 8 segments), each bracketed by its own CUDA-event pair; the timed "
-                                     "region replays them from one CUDA graph.  The kernel is instruction-issue bound, not HBM bound: see "
-                                     "profiles/ and DESIGN.md"},
+                                     "region (one launch per stage for the batch's segments), each bracketed by its own CUDA-event pair; the timed "
+                                     "region replays them from one CUDA graph per batch.  The kernel is bound by the integer pipes, not by HBM: "
+                                     "see DESIGN.md 5 and profiles/"},
                 "stages": table}
         if cpu:
             line["cpu_baseline"] = cpu
+        if quality:
+            line["quality"] = quality
+        if e2e_file:
+            line["e2e_file"] = e2e_file
         print(json.dumps(line))
-    for e in encs:
-        e.close()
     if world > 1:
         dist.destroy_process_group()
 

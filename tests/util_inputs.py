@@ -50,6 +50,8 @@ def make_frame(w, h, fmt="yuv420p", kind="random", seed=0, t=0):
              ((((cx >> 1) + cy) & 1) * 255).astype(np.uint8)]
     elif kind == "testsrc":
         p = testsrc_planes(w, h, t, seed)
+    elif kind == "pan":
+        p = pan_planes(w, h, t, seed)
     else:
         raise ValueError(kind)
     if fmt == "nv12":
@@ -58,3 +60,32 @@ def make_frame(w, h, fmt="yuv420p", kind="random", seed=0, t=0):
         uv[:, 1::2] = p[2]
         return [p[0], uv]
     return p
+
+
+_PAN_CACHE = {}
+
+
+def pan_planes(w, h, t=0, seed=0):
+    """Second content point for the bench: a band-limited texture (noise blown up 8x and box filtered, plus fine grain) that
+    translates as a whole by (+3, +2) luma samples per picture -- global motion, so no macroblock is predicted by the zero
+    vector and none leaves the motion search early; chroma moves with it."""
+    key = (w, h, seed)
+    if key not in _PAN_CACHE:
+        _PAN_CACHE.clear()
+        rng = np.random.Generator(np.random.PCG64(1000 + seed))
+        m = 512                                    # room for the translation
+
+        def field(hh, ww, scale, grain):
+            small = rng.integers(0, 256, ((hh + m) // scale + 3, (ww + m) // scale + 3)).astype(np.float64)
+            big = np.kron(small, np.ones((scale, scale)))
+            k = scale
+            c = np.cumsum(np.cumsum(np.pad(big, ((k, 0), (k, 0))), 0), 1)
+            box = (c[k:, k:] - c[:-k, k:] - c[k:, :-k] + c[:-k, :-k]) / (k * k)
+            return np.clip(box + rng.integers(-grain, grain + 1, box.shape), 0, 255).astype(np.uint8)
+        cw, ch = _chroma_dims(w, h)
+        _PAN_CACHE[key] = (field(h, w, 8, 10), field(ch, cw, 4, 3), field(ch, cw, 4, 3))
+    Y, U, V = _PAN_CACHE[key]
+    cw, ch = _chroma_dims(w, h)
+    ox, oy = (3 * t) % 500, (2 * t) % 500
+    ox, oy = ox - (ox & 1), oy - (oy & 1)          # even: chroma moves by whole samples too
+    return [Y[oy:oy + h, ox:ox + w].copy(), U[oy // 2:oy // 2 + ch, ox // 2:ox // 2 + cw].copy(), V[oy // 2:oy // 2 + ch, ox // 2:ox // 2 + cw].copy()]

@@ -10,7 +10,7 @@ from concurrent.futures import ThreadPoolExecutor
 
 gvc.init(0)
 N = 8
-seg = bench.synth_segment(0)
+seg = bench.synth_segment(bench.workload("cfg2", "testsrc"), 0)
 host = [torch.from_numpy(seg).pin_memory() for _ in range(N)]
 dev = [torch.empty_like(h, device="cuda") for h in host]
 streams = [torch.cuda.Stream() for _ in range(N)]

@@ -8,7 +8,7 @@ import govideocompressor_b200 as gvc
 import bench
 gvc.init(0)
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 8
-src = torch.from_numpy(bench.synth_segment(0, n)).cuda()
+src = torch.from_numpy(bench.synth_segment(bench.workload("cfg2", "testsrc"), 0, n)).cuda()
 enc = gvc.Encoder(1920, 1080, 1280, 720, crf=23)
 for _ in range(2):
     enc.encode_device(src.data_ptr(), n); enc.sync()

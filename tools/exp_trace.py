@@ -10,7 +10,7 @@ from concurrent.futures import ThreadPoolExecutor
 gvc.init(0)
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 8
 encs = [gvc.Encoder(1920, 1080, 1280, 720, crf=23, host_threads=int(os.environ.get("GVC_HOST_THREADS", "2"))) for _ in range(n)]
-seg = bench.synth_segment(0)
+seg = bench.synth_segment(bench.workload("cfg2", "testsrc"), 0)
 host = [torch.from_numpy(seg).pin_memory() for _ in range(n)]
 pool = ThreadPoolExecutor(n)
 def slot(k, steps):
