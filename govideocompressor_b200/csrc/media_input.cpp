@@ -105,7 +105,11 @@ LavApi &lav() {
     api.h_util = open_lib(dir, "libavutil");
     api.h_codec = open_lib(dir, "libavcodec");
     api.h_format = open_lib(dir, "libavformat");
-    if (!api.h_util || !api.h_codec || !api.h_format) { api.where = "libavformat/libavcodec/libavutil not found (set GVC_FFMPEG_LIBDIR)"; return api; }
+    if (!api.h_util || !api.h_codec || !api.h_format) {
+        const char *why = dlerror();
+        api.where = std::string("libavformat/libavcodec/libavutil could not be loaded (set GVC_FFMPEG_LIBDIR)") + (why ? std::string(": ") + why : std::string());
+        return api;
+    }
     bool ok = true;
 #define LOAD(handle, name) ok = ok && (*(void **)(&api.name) = dlsym(handle, #name)) != nullptr
     LOAD(api.h_format, avformat_open_input); LOAD(api.h_format, avformat_find_stream_info); LOAD(api.h_format, av_find_best_stream);

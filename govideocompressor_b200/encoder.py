@@ -204,6 +204,7 @@ def _find_ffmpeg_libs():
         d = os.path.join(os.path.dirname(os.path.dirname(spec.origin)), "opencv_python_headless.libs")
         if os.path.isdir(d):
             os.environ["GVC_FFMPEG_LIBDIR"] = d
+            import cv2  # noqa: F401  the wheel's FFmpeg build finds its own dependencies (libvpx, libssl ...) only once cv2 has loaded them
     except Exception:
         pass
 
