@@ -334,7 +334,18 @@ def main():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # NCCL prints its version banner (NCCL_DEBUG=VERSION) on the C-level stdout when the communicator comes up; stdout carries
+        # the ONE JSON line, so file descriptor 1 points at stderr while that happens (the environment is left as the driver set it)
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            os.dup2(saved, 1)
+            os.close(saved)
     gvc.init(local)
     SW, SH, DW, DH, SEG_FRAMES, NSEG = c["sw"], c["sh"], c["dw"], c["dh"], c["seg"], c["nseg"]
     # The step's NSEG segments are encoded as NENC batches: within a batch the segments advance picture by picture together, one

@@ -3,6 +3,7 @@ pieces highest index first, one per connection, parses "success;id" / "fail;id[;
 never re-queues a failed piece, stops when every piece has been reported."""
 import socket
 import threading
+import time
 
 
 class FakeServer:
@@ -15,6 +16,7 @@ class FakeServer:
         self.order = list(range(pieces))                         # initMap
         self.remain = {i: str(i) for i in range(pieces)}         # remainMap
         self.sent, self.success, self.failed = [], [], []
+        self.t_sent, self.t_success = [], []                     # wall-clock times of the hand-outs and of the `success` reports
         self.sock = socket.socket()
         self.sock.bind(("127.0.0.1", 0))
         self.sock.listen(16)
@@ -44,6 +46,7 @@ class FakeServer:
                 self._next -= 1
             job = self.dir + ";" + piece + ";" + self.args       # server.go:179
             self.sent.append(job)
+            self.t_sent.append(time.perf_counter())
             c.sendall(job.encode())
             threading.Thread(target=self._reader, args=(c,), daemon=True).start()
         self.sock.close()
@@ -59,6 +62,7 @@ class FakeServer:
             elif data[0:7] == "success":                         # server.go:284-292
                 n = int(data.split(";")[1])
                 self.success.append(n)
+                self.t_success.append(time.perf_counter())
                 self.remain.pop(n, None)
             else:
                 self.failed.append(["lost", ""])

@@ -71,9 +71,12 @@ def main():
     jobs = [p.communicate()[0].split() for p in procs]
     done = sum(len([j for j in js if j.startswith("success")]) for js in jobs)
     outs = [f for f in os.listdir(os.path.join(dst, "12clip"))] if os.path.isdir(os.path.join(dst, "12clip")) else []
+    ts = sorted(server.t_success)
+    k = len(procs)                                  # the first job of every worker pays its start-up (python, CUDA context, library load)
+    steady = (len(ts) - k) * args.frames / (ts[-1] - ts[k - 1]) if len(ts) > k and ts[-1] > ts[k - 1] else None
     print(json.dumps({"farm": "dispatcher twin + %d worker processes on %d GPU(s)" % (len(procs), args.gpus), "config": args.config, "pieces": args.pieces,
                       "frames_per_piece": args.frames, "args": ffargs, "all_done": bool(ok) and done == args.pieces, "wall_s": wall,
-                      "frames_per_s": args.pieces * args.frames / wall, "jobs_per_worker": [len(j) for j in jobs],
+                      "frames_per_s": args.pieces * args.frames / wall, "frames_per_s_after_every_worker_s_first_job": steady, "jobs_per_worker": [len(j) for j in jobs],
                       "outputs": len([f for f in outs if not f.endswith(".log")]),
                       "note": "wall clock includes the workers' start-up (python + CUDA context + library load), host H.264 decode of the pieces and MP4 writing"}))
     import shutil
