@@ -8,6 +8,7 @@
 #include "enc_kernels.cuh"
 #include "enc_launch.h"
 #include "gvc_common.h"
+#include "tma.cuh"
 
 namespace gvc {
 
@@ -92,30 +93,6 @@ struct MeRefTma {
     CUtensorMap map[4];          // TMA takes the descriptor's ADDRESS, which must stay in parameter space (never a local copy): the
     int on;                      // kernel only forms &T.a[segment].map[p] of its __grid_constant__ parameter.  on = 0: planes not
 };                               // addressable by TMA (alignment); the windows are then staged with plain loads
-__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-// one box of the tensor map into shared memory; x must be a multiple of 16 (bytes of the innermost dimension)
-__device__ __forceinline__ void tma_box_2d(void *dst, const CUtensorMap *map, int x, int y, unsigned long long *bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<unsigned long long>(map)), "r"(smem_u32(bar)), "r"(x), "r"(y) : "memory");
-}
-
 constexpr int kMeWarps = 4;   // macroblocks (warps) per CTA of me_refine: 24.6 KB of windows per CTA
 __global__ void __launch_bounds__(32 * kMeWarps, 8)
 me_refine_kernel(const __grid_constant__ Batch<MeRefArgs> B, const __grid_constant__ Batch<MeRefTma> T) {
@@ -400,19 +377,6 @@ int launch_signal_picture(const SignalArgs *a, int count, cudaStream_t st) {
     signal_picture_kernel<<<1, count, 0, st>>>(B);
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
-}
-// cuTensorMapEncodeTiled through the runtime's driver entry point table (libgvc.so does not link libcuda directly)
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
-                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_tiled_fn() {
-    static EncodeTiledFn fn = [] {
-        void *p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
-        return reinterpret_cast<EncodeTiledFn>(p);
-    }();
-    return fn;
 }
 // Describes the padded planes of a.ref to TMA; tma.on = 0 when they cannot be (base or pitch not a multiple of 16 bytes).
 static void me_refine_tma(const MeRefArgs &a, MeRefTma &tma) {

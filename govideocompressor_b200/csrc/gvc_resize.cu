@@ -13,13 +13,19 @@
 #include "gvc_common.h"
 #include "resize_kernels.cuh"
 #include "resize_plan.h"
+#include "tma.cuh"
 
 namespace gvc {
 
 // ------------------------------------------------------------------------------- kernels ------
+// The three planes' tensor maps (3-D: bytes of a row as 16-bit elements, rows, frames) travel as kernel parameters; on = 0 for a
+// plane TMA cannot address (NV12 chroma, unaligned base / pitch): its tiles are then filled with plain loads.
+struct ResizeTma { CUtensorMap map[3]; int on[3]; };
+
 template <int NG, int VT>
-__global__ void __launch_bounds__(kThreads) resize_fused_kernel(const __grid_constant__ ResizeParams P, int s_chunks_max) {
-    extern __shared__ uint4 smem[];
+__global__ void __launch_bounds__(kThreads) resize_fused_kernel(const __grid_constant__ ResizeParams P, const __grid_constant__ ResizeTma M, int s_chunks_max) {
+    extern __shared__ __align__(128) uint4 smem[];
+    __shared__ unsigned long long bar;
     const int            tile = blockIdx.x;
     const int            j    = find_job(P, tile);
     const PlaneJob      &pj   = P.job[j];
@@ -31,10 +37,22 @@ __global__ void __launch_bounds__(kThreads) resize_fused_kernel(const __grid_con
     uint8_t             *dst = pj.dst + (size_t)blockIdx.y * pj.dframe;
     unsigned            *S   = reinterpret_cast<unsigned *>(smem);
     int4                *T   = reinterpret_cast<int4 *>(smem + kTileRows * s_chunks_max);
+    const int            pitch_w = 4 * s_chunks_max;
 
-    resize_phase0(threadIdx.x, pc, pj, src, g, S);
-    __syncthreads();
-    resize_phase1<NG>(threadIdx.x, pc, g, S, T);
+    if (M.on[j]) {      // the whole source tile is one box: 16 * s_chunks_max bytes x kTileRows rows of frame blockIdx.y
+        if (threadIdx.x == 0) {
+            mbar_init(&bar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            mbar_expect_tx(&bar, (unsigned)(16 * s_chunks_max * kTileRows));
+            tma_box_3d(S, &M.map[j], 2 * g.qa0, g.r0, (int)blockIdx.y, &bar);      // x in 16-bit elements: byte 4 * qa0
+        }
+        __syncthreads();
+        mbar_wait(&bar, 0);
+    } else {
+        resize_phase0(threadIdx.x, pc, pj, src, g, S, pitch_w);
+        __syncthreads();
+    }
+    resize_phase1<NG>(threadIdx.x, pc, g, S, pitch_w, T);
     __syncthreads();
     resize_phase2<VT>(threadIdx.x, pc, pj, dst, g, T);
 }
@@ -126,7 +144,7 @@ int upload_tables(gvc_resize_plan *p) {
     return GVC_OK;
 }
 
-typedef void (*fused_fn)(const ResizeParams, int);
+typedef void (*fused_fn)(const ResizeParams, const ResizeTma, int);
 template <int NG, int VT>
 struct PickVt {
     static fused_fn get(int vt) { return vt >= VT ? static_cast<fused_fn>(resize_fused_kernel<NG, VT>) : PickVt<NG, VT - 1>::get(vt); }
@@ -157,6 +175,27 @@ int check_frames(const gvc_resize_plan *p, const gvc_frames *f, int w, int h, co
     return GVC_OK;
 }
 
+// Tensor maps of the source planes of `nf` frames: plane k as a 3-D tensor of 16-bit elements (a row's bytes in pairs, so a
+// box may be up to 512 bytes wide), rows, frames.  A box = one tile's source rows; what lies outside the plane reads as zeros.
+void resize_tma(const ResizeParams &P, int nf, int s_chunks_max, ResizeTma &M) {
+    memset(&M, 0, sizeof(M));
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc || 16 * s_chunks_max > 512) return;
+    for (int k = 0; k < P.njobs; ++k) {
+        const PlaneJob      &j  = P.job[k];
+        const PlaneClassDev &pc = P.cls[j.cls];
+        unsigned long long fstride = j.sframe;
+        if (nf == 1 && (fstride & 15)) fstride = ((unsigned long long)j.sstride * pc.sh + 15) & ~15ull;      // never used as an offset
+        if (j.spix != 1 || (reinterpret_cast<uintptr_t>(j.src) & 15) || (j.sstride & 15) || (fstride & 15) || fstride == 0) continue;
+        const cuuint64_t dims[3] = {(cuuint64_t)((pc.sw + 1) / 2), (cuuint64_t)pc.sh, (cuuint64_t)nf};
+        const cuuint64_t strides[2] = {(cuuint64_t)j.sstride, (cuuint64_t)fstride};
+        const cuuint32_t box[3] = {(cuuint32_t)(8 * s_chunks_max), (cuuint32_t)kTileRows, 1}, es[3] = {1, 1, 1};
+        if (enc(&M.map[k], CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, const_cast<uint8_t *>(j.src), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS)
+            M.on[k] = 1;
+    }
+}
+
 int launch_device(const gvc_resize_plan *p, const gvc_frames *src, const gvc_frames *dst, int n_frames, cudaStream_t st, int sslot) {
     const bool nv12 = p->fmt == GVC_PIX_NV12;
     if (p->t.fused_ok && !p->force_two_pass) {
@@ -184,7 +223,9 @@ int launch_device(const gvc_resize_plan *p, const gvc_frames *src, const gvc_fra
             const int nf = std::min(32768, n_frames - f0);
             ResizeParams Q = P;
             for (int k = 0; k < 3; ++k) { Q.job[k].src += (size_t)f0 * Q.job[k].sframe; Q.job[k].dst += (size_t)f0 * Q.job[k].dframe; }
-            fn<<<dim3(P.tiles_per_frame, nf), kThreads, p->t.smem_bytes, st>>>(Q, p->t.s_chunks_max);
+            ResizeTma M;
+            resize_tma(Q, nf, p->t.s_chunks_max, M);
+            fn<<<dim3(P.tiles_per_frame, nf), kThreads, p->t.smem_bytes, st>>>(Q, M, p->t.s_chunks_max);
             GVC_CUDA(cudaGetLastError());
         }
         return GVC_OK;

@@ -7,9 +7,10 @@
 //
 // Two device paths:
 //   * fused (resize_fused_kernel): one CTA = one 128 x TH output tile of one plane of one frame.
-//     phase 0  source tile -> shared memory (128-bit coalesced loads when the plane is 16 B aligned)
-//     phase 1  horizontal pass, lanes <-> source rows, x marches warp-uniformly so taps/positions are
-//              uniform loads; pixels are consumed as packed words through dp2a (2 taps / instruction)
+//     phase 0  source tile -> shared memory: ONE TMA box per tile (cp.async.bulk.tensor.3d, completion on an
+//              mbarrier); plain loads for planes TMA cannot address
+//     phase 1  horizontal pass, lanes <-> output columns, each lane walks down the tile's rows with its taps in
+//              registers; pixels are consumed as packed words through dp2a (2 taps / instruction)
 //     phase 2  vertical pass from the int32 intermediate tile in shared memory, 4 pixels per lane,
 //              32-bit stores.  No intermediate ever touches HBM: traffic = source + destination.
 //   * two-pass (resize_hpass_kernel / resize_vpass_kernel): any tap count / ratio, int16 intermediate
@@ -76,126 +77,71 @@ GVC_HD TileGeom tile_geom(const PlaneClassDev &pc, int tx, int ty) {
 }
 
 // ---------------------------------------------------------------- phase 0: source tile -> smem --
-// S layout (word-transposed): S[word * kTileRows + row], word = 4-byte group counted from the tile's first 16-byte
-// chunk.  Lanes <-> source rows both when the tile is written here and when the horizontal pass reads it, so every
-// shared-memory access of a warp touches 32 consecutive words (no bank conflicts, no register shuffling to select the
-// word a tap group starts in).  Bytes outside the plane are zero.
-GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, const uint8_t *src,
-                          const TileGeom &g, unsigned *S) {
-    const int  chunks  = pc.s_chunks;
-    const bool aligned = pj.spix == 1 && ((((unsigned long long)src) | (unsigned)pj.sstride) & 15) == 0;
-    const int  warp = tid >> 5, lane = tid & 31;
-    const int  r = (warp & (kRowGroups - 1)) * 32 + lane;            // this lane's source row inside the tile
-    const int  row = g.r0 + r;
-    const bool row_ok = r < g.rows && row < pc.sh;
-    const uint8_t *p = src + (long long)(row_ok ? row : 0) * pj.sstride;
-    // a lane fetches chunk PAIRS (one 32-byte sector) so no sector is pulled from L2 twice by different warps
-    auto fetch = [&](int c) {
-        const int col = (g.qa0 << 2) + (c << 4);       // first source sample of this chunk
-        gvc_uint4 v;
-        v.x = v.y = v.z = v.w = 0u;
-        if (row_ok && c < g.nchunks + 1 && col < pc.sw) {
-            if (aligned && col + 16 <= pc.sw) {
-#if defined(GVC_EMU)
-                v = *reinterpret_cast<const gvc_uint4 *>(p + col);
-#else
-                v = __ldg(reinterpret_cast<const gvc_uint4 *>(p + col));
-#endif
+// S layout (row major): source row r of the tile occupies words [r * pitch_w, (r + 1) * pitch_w), byte 0 = sample 4 * qa0 of
+// the plane (a multiple of 16 bytes), all kTileRows rows present.  On the GPU the tile normally arrives as ONE TMA box
+// (gvc_resize.cu; rows / columns outside the plane come back as zeros); this is the same fill with plain loads, for planes
+// TMA cannot address (NV12 chroma, unaligned pointers or pitches) and for the CPU emulation.  Bytes outside the plane are zero.
+GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, const uint8_t *src, const TileGeom &g, unsigned *S, int pitch_w) {
+    const bool aligned = pj.spix == 1 && ((((unsigned long long)src) | (unsigned)pj.sstride) & 3) == 0;
+    for (int i = tid; i < kTileRows * pitch_w; i += kThreads) {
+        const int r = i / pitch_w, c = i - r * pitch_w, row = g.r0 + r, col = 4 * (g.qa0 + c);
+        unsigned w = 0;
+        if (row < pc.sh && col < pc.sw) {
+            const uint8_t *p = src + (long long)row * pj.sstride;
+            if (aligned && col + 4 <= pc.sw) {
+                w = *reinterpret_cast<const unsigned *>(p + col);
             } else {
-                unsigned w[4] = {0u, 0u, 0u, 0u};
-                for (int b = 0; b < 16; ++b) {
-                    const int cc = col + b;
-                    if (cc < pc.sw) w[b >> 2] |= (unsigned)p[(long long)cc * pj.spix] << ((b & 3) * 8);
-                }
-                v.x = w[0]; v.y = w[1]; v.z = w[2]; v.w = w[3];
+                for (int b = 0; b < 4; ++b)
+                    if (col + b < pc.sw) w |= (unsigned)p[(long long)(col + b) * pj.spix] << (8 * b);
             }
         }
-        return v;
-    };
-    // chunk index of the first pair member is chosen so that pairs share a 32-byte sector of the source row when the
-    // row is 32-byte aligned relative to the tile origin (qa0 is a multiple of 4 words = 16 bytes: pair (2j, 2j+1) or
-    // (2j-1, 2j) depending on the parity of qa0/4)
-    const int odd = (g.qa0 >> 2) & 1;
-    constexpr int kPairWarps = kWarps / kRowGroups;    // 4 warps share the chunk pairs of a row group
-#pragma unroll 2
-    for (int j = warp / kRowGroups; 2 * j - odd < chunks; j += kPairWarps) {
-        const int c0 = 2 * j - odd, c1 = c0 + 1;
-        gvc_uint4 v0, v1;
-        v0.x = v0.y = v0.z = v0.w = 0u;
-        v1 = v0;
-        if (c0 >= 0) v0 = fetch(c0);
-        if (c1 < chunks) v1 = fetch(c1);
-        if (c0 >= 0) {
-            unsigned *d = S + (4 * c0) * kTileRows + r;
-            d[0] = v0.x; d[kTileRows] = v0.y; d[2 * kTileRows] = v0.z; d[3 * kTileRows] = v0.w;
-        }
-        if (c1 < chunks) {
-            unsigned *d = S + (4 * c1) * kTileRows + r;
-            d[0] = v1.x; d[kTileRows] = v1.y; d[2 * kTileRows] = v1.z; d[3 * kTileRows] = v1.w;
-        }
+        S[i] = w;
     }
 }
 
 // ---------------------------------------------------------------- phase 1: horizontal ----------
+// Lanes <-> output columns: a lane keeps its column's table entry (first source word, byte offset, packed tap pairs) in
+// registers and walks down the tile's source rows -- per intermediate sample three (NG = 2) shared-memory words of the row,
+// two funnel shifts to the column's byte offset, four dp2a (two taps each), shift, clamp, one store; nothing per sample is
+// recomputed or reloaded.  A warp's 32 columns read at most a dozen neighbouring words of a row (no bank conflicts), and the
+// stores of a warp fall into 32 different banks.  Warp w takes columns 32 * (w & 3) .. + 31 and rows 32 * (w >> 2) .. + 31.
 // T layout: [quad (4 output columns)][kTPad source rows][4] int32.
 template <int NG>
-GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, const unsigned *S, gvc_int4 *T) {
-#if defined(GVC_EMU)
-    const int warp = tid >> 5;
-#else
-    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // broadcast: lets the compiler treat x / table entries as warp-uniform
-#endif
-    const int lane = tid & 31;
+GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, const unsigned *S, int pitch_w, gvc_int4 *T) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const int xl = (warp & 3) * 32 + lane;                 // tile-relative output column
+    if ((warp & 3) * 32 >= g.ncols) return;                // warp-uniform: the tile has no such columns
     const gvc_int4 *htab = reinterpret_cast<const gvc_int4 *>(pc.htab);
-    constexpr int kColsPerWarp = kTileW / kWarps;       // 16 output columns = 4 quads per warp
-    const int xw = warp * kColsPerWarp;                 // tile-relative first column of this warp
-    if (xw >= g.ncols) return;                          // warp-uniform
-    auto entry = [&](int xi, gvc_int4 &e0, gvc_int4 &e1) {
-        const int x = imin(g.x0 + xw + xi, pc.dw - 1);
+    const int x = imin(g.x0 + xl, pc.dw - 1);
 #if defined(GVC_EMU)
-        e0 = htab[(long long)x * 2]; e1 = htab[(long long)x * 2 + 1];
+    const gvc_int4 e0 = htab[(long long)x * 2], e1 = htab[(long long)x * 2 + 1];
 #else
-        e0 = __ldg(htab + (long long)x * 2); e1 = __ldg(htab + (long long)x * 2 + 1);
+    const gvc_int4 e0 = __ldg(htab + (long long)x * 2), e1 = __ldg(htab + (long long)x * 2 + 1);
 #endif
-    };
-    gvc_int4 n0, n1;
-    entry(0, n0, n1);
-    int acc[kRowGroups][4];
+    const int r8 = e0.y, r0 = (warp >> 2) * 32;
+    const unsigned *w = S + r0 * pitch_w + (e0.x - g.qa0);
+    int *t = reinterpret_cast<int *>(T) + ((xl >> 2) * kTPad + r0) * 4 + (xl & 3);
+#if !defined(GVC_EMU)
 #pragma unroll 4
-    for (int xi = 0; xi < kColsPerWarp; ++xi) {
-        const gvc_int4 e0 = n0, e1 = n1;
-        if (xi + 1 < kColsPerWarp) entry(xi + 1, n0, n1);   // table entry of the next column: off the critical path
-        const int r8 = e0.y;
-        const unsigned *wp = S + (e0.x - g.qa0) * kTileRows + lane;   // word holding the first tap, this lane's row
-#pragma unroll
-        for (int rg = 0; rg < kRowGroups; ++rg) {
-            const unsigned *w = wp + rg * 32;
-            const unsigned w0 = w[0], w1 = w[kTileRows];
-            const unsigned u0 = funnel_r(w0, w1, r8);
-            int a = dp2a_lo_su(e0.z, u0, 0);
-            a     = dp2a_hi_su(e0.w, u0, a);
-            if (NG >= 2) {
-                const unsigned w2 = w[2 * kTileRows];
-                const unsigned u1 = funnel_r(w1, w2, r8);
-                a = dp2a_lo_su(e1.x, u1, a);
-                a = dp2a_hi_su(e1.y, u1, a);
-                if (NG >= 3) {
-                    const unsigned w3 = w[3 * kTileRows];
-                    const unsigned u2 = funnel_r(w2, w3, r8);
-                    a = dp2a_lo_su(e1.z, u2, a);
-                    a = dp2a_hi_su(e1.w, u2, a);
-                }
-            }
-            acc[rg][xi & 3] = imin(a >> 7, 32767);
-        }
-        if ((xi & 3) == 3) {
-#pragma unroll
-            for (int rg = 0; rg < kRowGroups; ++rg) {
-                gvc_int4 v;
-                v.x = acc[rg][0]; v.y = acc[rg][1]; v.z = acc[rg][2]; v.w = acc[rg][3];
-                T[(((xw + xi) >> 2) * kTPad) + rg * 32 + lane] = v;
+#endif
+    for (int r = 0; r < 32; ++r, w += pitch_w, t += 4) {
+        const unsigned w0 = w[0], w1 = w[1];
+        const unsigned u0 = funnel_r(w0, w1, r8);
+        int a = dp2a_lo_su(e0.z, u0, 0);
+        a     = dp2a_hi_su(e0.w, u0, a);
+        if (NG >= 2) {
+            const unsigned w2 = w[2];
+            const unsigned u1 = funnel_r(w1, w2, r8);
+            a = dp2a_lo_su(e1.x, u1, a);
+            a = dp2a_hi_su(e1.y, u1, a);
+            if (NG >= 3) {
+                const unsigned w3 = w[3];
+                const unsigned u2 = funnel_r(w2, w3, r8);
+                a = dp2a_lo_su(e1.z, u2, a);
+                a = dp2a_hi_su(e1.w, u2, a);
             }
         }
+        *t = imin(a >> 7, 32767);
     }
 }
 

@@ -26,8 +26,8 @@ void run_tile(const ResizeParams &P, int tile, int frame, int s_chunks_max) {
     memset(T.data(), 0xCD, T.size() * sizeof(gvc_int4));
     const uint8_t *src = pj.src + size_t(frame) * pj.sframe;
     uint8_t       *dst = pj.dst + size_t(frame) * pj.dframe;
-    for (int tid = 0; tid < kThreads; ++tid) resize_phase0(tid, pc, pj, src, g, reinterpret_cast<unsigned *>(S.data()));
-    for (int tid = 0; tid < kThreads; ++tid) resize_phase1<NG>(tid, pc, g, reinterpret_cast<const unsigned *>(S.data()), T.data());
+    for (int tid = 0; tid < kThreads; ++tid) resize_phase0(tid, pc, pj, src, g, reinterpret_cast<unsigned *>(S.data()), 4 * s_chunks_max);
+    for (int tid = 0; tid < kThreads; ++tid) resize_phase1<NG>(tid, pc, g, reinterpret_cast<const unsigned *>(S.data()), 4 * s_chunks_max, T.data());
     for (int tid = 0; tid < kThreads; ++tid) resize_phase2<VT>(tid, pc, pj, dst, g, T.data());
 }
 
