@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(kThreads) resize_fused_kernel(const __grid_con
     const PlaneJob      &pj   = P.job[j];
     const PlaneClassDev &pc   = P.cls[pj.cls];
     const int            t    = tile - pj.tile_base;
-    const int            ty = t / pc.tiles_x, tx = t - ty * pc.tiles_x;
+    const int            ty = pc.tiles_x_magic ? (int)(((unsigned)t * (unsigned)pc.tiles_x_magic) >> 20) : t / pc.tiles_x, tx = t - ty * pc.tiles_x;
     const TileGeom       g   = tile_geom(pc, tx, ty);
     const uint8_t       *src = pj.src + (size_t)blockIdx.y * pj.sframe;
     uint8_t             *dst = pj.dst + (size_t)blockIdx.y * pj.dframe;

@@ -53,6 +53,17 @@ GVC_HD unsigned funnel_r(unsigned lo, unsigned hi, int sh) {    // bytes of hi:l
 #endif
 }
 
+GVC_HD unsigned pack_sat_u8x4(int v0, int v1, int v2, int v3) {   // bytes clip_u8(v0) | clip_u8(v1) << 8 | clip_u8(v2) << 16 | clip_u8(v3) << 24
+#if defined(GVC_EMU)
+    return (unsigned)clip_u8(v0) | ((unsigned)clip_u8(v1) << 8) | ((unsigned)clip_u8(v2) << 16) | ((unsigned)clip_u8(v3) << 24);
+#else
+    unsigned hi, d;                                      // cvt.pack: d = c << 16 | sat(a) << 8 | sat(b)
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(v3), "r"(v2), "r"(0));
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(v1), "r"(v0), "r"(hi));
+    return d;
+#endif
+}
+
 struct TileGeom {
     int x0, ncols;   // first output column, number of output columns (<= kTileW)
     int y0, nrows;   // first output row, number of output rows (<= th)
@@ -162,16 +173,19 @@ GVC_HD void resize_phase2(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
     if (xl >= g.ncols) return;
     const bool store32 = pj.dpix == 1 && ((((unsigned long long)dst) | (unsigned)pj.dstride) & 3) == 0 && xl + 4 <= g.ncols;
     const gvc_int4 *colbase = T + lane * kTPad - g.r0;
-    uint8_t *prow = dst + (long long)(g.x0 + xl) * pj.dpix;
+    // the lane's four pixels of row y, and the table row of y: both advance by kWarps rows per iteration
+    uint8_t        *p  = dst + (long long)(g.x0 + xl) * pj.dpix + (long long)(g.y0 + warp) * pj.dstride;
+    const gvc_int4 *vt = vtab + (long long)(g.y0 + warp) * VQ;
+    const long long pstep = (long long)kWarps * pj.dstride;
 #pragma unroll 1
-    for (int y = g.y0 + warp; y < g.y0 + g.nrows; y += kWarps) {
+    for (int y = g.y0 + warp; y < g.y0 + g.nrows; y += kWarps, p += pstep, vt += kWarps * VQ) {
         int cf[4 * VQ];
 #pragma unroll
         for (int i = 0; i < VQ; ++i) {
 #if defined(GVC_EMU)
-            const gvc_int4 e = vtab[(long long)y * VQ + i];
+            const gvc_int4 e = vt[i];
 #else
-            const gvc_int4 e = __ldg(vtab + (long long)y * VQ + i);
+            const gvc_int4 e = __ldg(vt + i);
 #endif
             cf[4 * i] = e.x; cf[4 * i + 1] = e.y; cf[4 * i + 2] = e.z; cf[4 * i + 3] = e.w;
         }
@@ -183,16 +197,15 @@ GVC_HD void resize_phase2(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
             const int      c = cf[j + 1];
             a0 += t.x * c; a1 += t.y * c; a2 += t.z * c; a3 += t.w * c;
         }
-        const int b0 = clip_u8(a0 >> 19), b1 = clip_u8(a1 >> 19), b2 = clip_u8(a2 >> 19), b3 = clip_u8(a3 >> 19);
-        uint8_t  *p  = prow + (long long)y * pj.dstride;
+        const unsigned out = pack_sat_u8x4(a0 >> 19, a1 >> 19, a2 >> 19, a3 >> 19);      // two saturating pack instructions
         if (store32) {
-            *reinterpret_cast<unsigned *>(p) = (unsigned)b0 | ((unsigned)b1 << 8) | ((unsigned)b2 << 16) | ((unsigned)b3 << 24);
+            *reinterpret_cast<unsigned *>(p) = out;
         } else {
             const int n = g.ncols - xl;
-            p[0] = (uint8_t)b0;
-            if (n > 1) p[pj.dpix] = (uint8_t)b1;
-            if (n > 2) p[2 * pj.dpix] = (uint8_t)b2;
-            if (n > 3) p[3 * pj.dpix] = (uint8_t)b3;
+            p[0] = (uint8_t)out;
+            if (n > 1) p[pj.dpix] = (uint8_t)(out >> 8);
+            if (n > 2) p[2 * pj.dpix] = (uint8_t)(out >> 16);
+            if (n > 3) p[3 * pj.dpix] = (uint8_t)(out >> 24);
         }
     }
 }

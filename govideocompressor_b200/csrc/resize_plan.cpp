@@ -67,6 +67,9 @@ bool build_resize_tables(ResizeTables &t, int sw, int sh, int dw, int dh, int al
         d.hgroups = ng; d.vtaps = vb.taps; d.vq = vq; d.th = th[c];
         d.tiles_x = (d.dw + kTileW - 1) / kTileW;
         d.tiles_y = (d.dh + d.th - 1) / d.th;
+        d.tiles_x_magic = (1 << 20) / d.tiles_x + 1;
+        for (long long i = 0; i < (long long)d.tiles_x * d.tiles_y && d.tiles_x_magic; ++i)
+            if (i * d.tiles_x_magic >= (1ll << 31) || int((i * d.tiles_x_magic) >> 20) != int(i / d.tiles_x)) d.tiles_x_magic = 0;
         d.htab = nullptr; d.vtab = nullptr;
         t.htab[c].assign(size_t(d.dw) * kHEntry, 0);
         t.vtab[c].assign(size_t(d.dh) * 4 * vq, 0);

@@ -23,6 +23,7 @@ struct PlaneClassDev {            // geometry + tables shared by all planes of o
     int vq;                       // int4 per vertical table row (row = vpos, taps..., zero padded)
     int th;                       // output rows per tile
     int tiles_x, tiles_y;
+    int tiles_x_magic;            // t / tiles_x == (t * magic) >> 20 for every tile index of the plane (0: divide)
     int s_chunks;                 // odd; 16-byte chunks per source-tile row in shared memory
     int s_chunks_magic;           // ceil(2^32 / s_chunks): i / s_chunks == umulhi(i, magic) for the small i used
     int vt;                       // vertical taps the kernel is instantiated for (>= vtaps, table zero padded)
