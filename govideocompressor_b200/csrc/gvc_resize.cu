@@ -155,9 +155,9 @@ struct PickVt<NG, 1> {
 };
 fused_fn pick_fused(int ng, int vt) {
     switch (ng) {
-        case 1: return PickVt<1, kMaxVTaps>::get(vt);
-        case 2: return PickVt<2, kMaxVTaps>::get(vt);
-        default: return PickVt<3, kMaxVTaps>::get(vt);
+        case 1: return PickVt<1, kMaxVPairs>::get(vt);
+        case 2: return PickVt<2, kMaxVPairs>::get(vt);
+        default: return PickVt<3, kMaxVPairs>::get(vt);
     }
 }
 

@@ -45,6 +45,20 @@ GVC_HD int dp2a_hi_su(int coef_pair, unsigned pix, int acc) {   // acc + c.lo*pi
     return d;
 #endif
 }
+GVC_HD int dp2a_ss(unsigned pair, unsigned coef, int acc, bool hi) {   // acc + pair.lo16 * coef.b[2hi] + pair.hi16 * coef.b[2hi+1], all signed
+#if defined(GVC_EMU)
+    const int sh = hi ? 16 : 0;
+    return acc + (int)(short)(pair & 0xffff) * (int)(signed char)(coef >> sh) + (int)(short)(pair >> 16) * (int)(signed char)(coef >> (sh + 8));
+#else
+    int d;
+    if (hi) asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(coef), "r"(acc));
+    else    asm("dp2a.lo.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(coef), "r"(acc));
+    return d;
+#endif
+}
+GVC_HD int dp2a_su(unsigned pair, unsigned coef, int acc, bool hi) {   // the same with unsigned coefficient bytes
+    return hi ? dp2a_hi_su((int)pair, coef, acc) : dp2a_lo_su((int)pair, coef, acc);
+}
 GVC_HD unsigned funnel_r(unsigned lo, unsigned hi, int sh) {    // bytes of hi:lo shifted right by sh (0..24) bits
 #if defined(GVC_EMU)
     return sh ? (lo >> sh) | (hi << (32 - sh)) : lo;
@@ -78,9 +92,8 @@ GVC_HD TileGeom tile_geom(const PlaneClassDev &pc, int tx, int ty) {
     g.ncols = imin(kTileW, pc.dw - g.x0);
     g.y0    = ty * pc.th;
     g.nrows = imin(pc.th, pc.dh - g.y0);
-    const int vrow = 4 * pc.vq;
-    g.r0    = pc.vtab[(long long)g.y0 * vrow];
-    g.rows  = pc.vtab[(long long)(g.y0 + g.nrows - 1) * vrow] + pc.vtaps - g.r0;
+    g.r0    = pc.vtab[(long long)g.y0 * kVEntry];                               // even: rows are kept in (even, odd) pairs
+    g.rows  = pc.vtab[(long long)(g.y0 + g.nrows - 1) * kVEntry + 9] - g.r0;
     g.qa0   = pc.htab[(long long)g.x0 * kHEntry] & ~3;
     const int qlast = pc.htab[(long long)(g.x0 + g.ncols - 1) * kHEntry] + pc.hgroups;  // last word touched
     g.nchunks = ((qlast - g.qa0) >> 2) + 1;
@@ -116,7 +129,7 @@ GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
 // two funnel shifts to the column's byte offset, four dp2a (two taps each), shift, clamp, one store; nothing per sample is
 // recomputed or reloaded.  A warp's 32 columns read at most a dozen neighbouring words of a row (no bank conflicts), and the
 // stores of a warp fall into 32 different banks.  Warp w takes columns 32 * (w & 3) .. + 31 and rows 32 * (w >> 2) .. + 31.
-// T layout: [quad (4 output columns)][kTPad source rows][4] int32.
+// T layout: [quad (4 output columns)][kTPad row pairs][4] words, a word = the int16 samples of rows (2p, 2p + 1) of one column.
 template <int NG>
 GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, const unsigned *S, int pitch_w, gvc_int4 *T) {
     const int warp = tid >> 5, lane = tid & 31;
@@ -131,37 +144,44 @@ GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, c
 #endif
     const int r8 = e0.y, r0 = (warp >> 2) * 32;
     const unsigned *w = S + r0 * pitch_w + (e0.x - g.qa0);
-    int *t = reinterpret_cast<int *>(T) + ((xl >> 2) * kTPad + r0) * 4 + (xl & 3);
-#if !defined(GVC_EMU)
-#pragma unroll 4
-#endif
-    for (int r = 0; r < 32; ++r, w += pitch_w, t += 4) {
-        const unsigned w0 = w[0], w1 = w[1];
+    unsigned *t = reinterpret_cast<unsigned *>(T) + ((xl >> 2) * kTPad + (r0 >> 1)) * 4 + (xl & 3);
+    auto sample = [&](const unsigned *row) {
+        const unsigned w0 = row[0], w1 = row[1];
         const unsigned u0 = funnel_r(w0, w1, r8);
         int a = dp2a_lo_su(e0.z, u0, 0);
         a     = dp2a_hi_su(e0.w, u0, a);
         if (NG >= 2) {
-            const unsigned w2 = w[2];
+            const unsigned w2 = row[2];
             const unsigned u1 = funnel_r(w1, w2, r8);
             a = dp2a_lo_su(e1.x, u1, a);
             a = dp2a_hi_su(e1.y, u1, a);
             if (NG >= 3) {
-                const unsigned w3 = w[3];
+                const unsigned w3 = row[3];
                 const unsigned u2 = funnel_r(w2, w3, r8);
                 a = dp2a_lo_su(e1.z, u2, a);
                 a = dp2a_hi_su(e1.w, u2, a);
             }
         }
-        *t = imin(a >> 7, 32767);
+        return imin(a >> 7, 32767);
+    };
+#if !defined(GVC_EMU)
+#pragma unroll 2
+#endif
+    for (int r = 0; r < 32; r += 2, w += 2 * pitch_w, t += 4) {
+        const int t0 = sample(w), t1 = sample(w + pitch_w);
+        *t = ((unsigned)t0 & 0xffffu) | ((unsigned)t1 << 16);      // rows (r, r + 1) as one pair of int16
     }
 }
 
 // ---------------------------------------------------------------- phase 2: vertical ------------
-// VT = vertical taps of the plan (the larger of the luma / chroma banks; the other bank is zero padded).
-template <int VT>
+// NP = row pairs of the plan (every output row's taps lie within NP pairs from its first, even, row).  A vertical coefficient is
+// split into its low byte (unsigned) and high byte (signed), c = 256 hi + lo, so that sum t c = sum t lo + 256 sum t hi and each of
+// the two sums takes TWO rows per dp2a from a (row, row + 1) pair word: per output pixel 2 NP dp2a and a quarter of NP 128-bit
+// shared-memory loads (the int32 tile of the earlier version needed one multiply and twice the bytes per tap).
+template <int NP>
 GVC_HD void resize_phase2(int tid, const PlaneClassDev &pc, const PlaneJob &pj, uint8_t *dst,
                           const TileGeom &g, const gvc_int4 *T) {
-    constexpr int VQ = (VT + 1 + 3) / 4;             // int4 per vertical table row (vpos + taps)
+    constexpr int NE = NP <= 2 ? 1 : NP <= 6 ? 2 : 3;    // int4 of a table entry that carry coefficients of the first NP pairs
 #if defined(GVC_EMU)
     const int warp = tid >> 5;
 #else
@@ -172,31 +192,36 @@ GVC_HD void resize_phase2(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
     const int  xl      = lane * 4;                   // tile-relative column of this lane's 4 pixels
     if (xl >= g.ncols) return;
     const bool store32 = pj.dpix == 1 && ((((unsigned long long)dst) | (unsigned)pj.dstride) & 3) == 0 && xl + 4 <= g.ncols;
-    const gvc_int4 *colbase = T + lane * kTPad - g.r0;
-    // the lane's four pixels of row y, and the table row of y: both advance by kWarps rows per iteration
+    const gvc_int4 *colbase = T + lane * kTPad;
+    // the lane's four pixels of row y, and the table entry of y: both advance by kWarps rows per iteration
     uint8_t        *p  = dst + (long long)(g.x0 + xl) * pj.dpix + (long long)(g.y0 + warp) * pj.dstride;
-    const gvc_int4 *vt = vtab + (long long)(g.y0 + warp) * VQ;
+    const gvc_int4 *vt = vtab + (long long)(g.y0 + warp) * (kVEntry / 4);
     const long long pstep = (long long)kWarps * pj.dstride;
 #pragma unroll 1
-    for (int y = g.y0 + warp; y < g.y0 + g.nrows; y += kWarps, p += pstep, vt += kWarps * VQ) {
-        int cf[4 * VQ];
+    for (int y = g.y0 + warp; y < g.y0 + g.nrows; y += kWarps, p += pstep, vt += kWarps * (kVEntry / 4)) {
+        unsigned cf[4 * NE];
 #pragma unroll
-        for (int i = 0; i < VQ; ++i) {
+        for (int i = 0; i < NE; ++i) {
 #if defined(GVC_EMU)
             const gvc_int4 e = vt[i];
 #else
             const gvc_int4 e = __ldg(vt + i);
 #endif
-            cf[4 * i] = e.x; cf[4 * i + 1] = e.y; cf[4 * i + 2] = e.z; cf[4 * i + 3] = e.w;
+            cf[4 * i] = (unsigned)e.x; cf[4 * i + 1] = (unsigned)e.y; cf[4 * i + 2] = (unsigned)e.z; cf[4 * i + 3] = (unsigned)e.w;
         }
-        const gvc_int4 *col = colbase + cf[0];
-        int a0 = 64 << 12, a1 = 64 << 12, a2 = 64 << 12, a3 = 64 << 12;
+        const gvc_int4 *col = colbase + (((int)cf[0] - g.r0) >> 1);
+        int l0 = 0, l1 = 0, l2 = 0, l3 = 0, h0 = 0, h1 = 0, h2 = 0, h3 = 0;
 #pragma unroll
-        for (int j = 0; j < VT; ++j) {
+        for (int j = 0; j < NP; ++j) {
             const gvc_int4 t = col[j];
-            const int      c = cf[j + 1];
-            a0 += t.x * c; a1 += t.y * c; a2 += t.z * c; a3 += t.w * c;
+            const unsigned lo = cf[1 + 2 * (j >> 1)], hi = cf[2 + 2 * (j >> 1)];      // bytes 0, 1 for even j, bytes 2, 3 for odd j
+            const bool     up = (j & 1) != 0;
+            l0 = dp2a_su((unsigned)t.x, lo, l0, up); h0 = dp2a_ss((unsigned)t.x, hi, h0, up);
+            l1 = dp2a_su((unsigned)t.y, lo, l1, up); h1 = dp2a_ss((unsigned)t.y, hi, h1, up);
+            l2 = dp2a_su((unsigned)t.z, lo, l2, up); h2 = dp2a_ss((unsigned)t.z, hi, h2, up);
+            l3 = dp2a_su((unsigned)t.w, lo, l3, up); h3 = dp2a_ss((unsigned)t.w, hi, h3, up);
         }
+        const int a0 = (64 << 12) + l0 + h0 * 256, a1 = (64 << 12) + l1 + h1 * 256, a2 = (64 << 12) + l2 + h2 * 256, a3 = (64 << 12) + l3 + h3 * 256;
         const unsigned out = pack_sat_u8x4(a0 >> 19, a1 >> 19, a2 >> 19, a3 >> 19);      // two saturating pack instructions
         if (store32) {
             *reinterpret_cast<unsigned *>(p) = out;

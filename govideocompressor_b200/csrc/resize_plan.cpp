@@ -16,7 +16,7 @@ int pick_tile_height(const FilterBank &vb, int dh) {
         bool ok = true;
         for (int y0 = 0; y0 < dh && ok; y0 += th) {
             const int y1 = std::min(y0 + th, dh) - 1;
-            ok = vb.pos[y1] + vb.taps - vb.pos[y0] <= kTileRows;
+            ok = vb.pos[y1] + vb.taps - (vb.pos[y0] & ~1) <= kTileRows;      // a tile starts on an even source row (rows are stored in pairs)
         }
         if (ok) return th;
     }
@@ -53,9 +53,10 @@ bool build_resize_tables(ResizeTables &t, int sw, int sh, int dw, int dh, int al
         th[c] = pick_tile_height(t.vb[c], t.gcls[c].dh);
         ok = ok && th[c] >= std::min(8, t.gcls[c].dh);
     }
-    int vt = std::max(t.vb[0].taps, t.vb[1].taps);
-    ok = ok && ng <= kMaxHGroups && vt <= kMaxVTaps;
-    vq = (vt + 1 + 3) / 4;
+    const int vtaps = std::max(t.vb[0].taps, t.vb[1].taps);
+    ok = ok && ng <= kMaxHGroups && vtaps <= kMaxVTaps;
+    int vt = (vtaps + 2) / 2;          // row pairs: taps + 1 rows when the first row is odd
+    vq = kVEntry / 4;
     t.fused_ok = ok;
     if (!ok) return true;
     t.ng = ng; t.vq = vq; t.vt = vt;
@@ -72,7 +73,7 @@ bool build_resize_tables(ResizeTables &t, int sw, int sh, int dw, int dh, int al
             if (i * d.tiles_x_magic >= (1ll << 31) || int((i * d.tiles_x_magic) >> 20) != int(i / d.tiles_x)) d.tiles_x_magic = 0;
         d.htab = nullptr; d.vtab = nullptr;
         t.htab[c].assign(size_t(d.dw) * kHEntry, 0);
-        t.vtab[c].assign(size_t(d.dh) * 4 * vq, 0);
+        t.vtab[c].assign(size_t(d.dh) * kVEntry, 0);
         for (int x = 0; x < d.dw; ++x) {
             int32_t *e = &t.htab[c][size_t(x) * kHEntry];
             e[0] = hb.pos[x] >> 2;            // aligned source word holding the first tap
@@ -84,9 +85,19 @@ bool build_resize_tables(ResizeTables &t, int sw, int sh, int dw, int dh, int al
             }
         }
         for (int y = 0; y < d.dh; ++y) {
-            int32_t *e = &t.vtab[c][size_t(y) * 4 * vq];
-            e[0] = vb.pos[y];
-            for (int j = 0; j < vb.taps; ++j) e[1 + j] = vb.coef[size_t(y) * vb.taps + j];
+            // coefficient c = 256 * hi + lo (lo = c & 255 unsigned, hi = c >> 8 signed): sum t * c = sum t * lo + 256 * sum t * hi, each
+            // sum two rows per dp2a on (row, row + 1) pairs of 16-bit intermediates
+            int32_t *e = &t.vtab[c][size_t(y) * kVEntry];
+            const int first = vb.pos[y] & ~1;
+            uint32_t lo[4] = {0, 0, 0, 0}, hi[4] = {0, 0, 0, 0};
+            for (int j = 0; j < vb.taps; ++j) {
+                const int cf = vb.coef[size_t(y) * vb.taps + j], slot = vb.pos[y] - first + j;
+                lo[slot >> 2] |= uint32_t(cf & 255) << (8 * (slot & 3));
+                hi[slot >> 2] |= uint32_t((cf >> 8) & 255) << (8 * (slot & 3));
+            }
+            e[0] = first; e[1] = int32_t(lo[0]); e[2] = int32_t(hi[0]); e[3] = int32_t(lo[1]);
+            e[4] = int32_t(hi[1]); e[5] = int32_t(lo[2]); e[6] = int32_t(hi[2]); e[7] = int32_t(lo[3]);
+            e[8] = int32_t(hi[3]); e[9] = vb.pos[y] + vb.taps;
         }
         int chunks = 1;   // widest tile in 16-byte chunks, +1 look-ahead chunk for the sliding window
         for (int x0 = 0; x0 < d.dw; x0 += kTileW) {

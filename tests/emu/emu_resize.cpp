@@ -40,7 +40,7 @@ template <int NG>
 struct PickVt<NG, 1> {
     static tile_fn get(int) { return run_tile<NG, 1>; }
 };
-tile_fn pick(int ng, int vt) { return ng == 1 ? PickVt<1, kMaxVTaps>::get(vt) : ng == 2 ? PickVt<2, kMaxVTaps>::get(vt) : PickVt<3, kMaxVTaps>::get(vt); }
+tile_fn pick(int ng, int vt) { return ng == 1 ? PickVt<1, kMaxVPairs>::get(vt) : ng == 2 ? PickVt<2, kMaxVPairs>::get(vt) : PickVt<3, kMaxVPairs>::get(vt); }
 
 }  // namespace
 

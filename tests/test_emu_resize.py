@@ -70,7 +70,7 @@ def test_emulated_kernels_ragged_and_padded(dims, fmt, mode):
 def test_plan_facts_for_headline_config():
     info = emu_lib.plan_info(1920, 1080, 1280, 720, 4)
     assert info["fused"] and info["h_taps"] == 6 and info["v_taps"] == 6
-    assert info["ng"] == 2 and info["vq"] == 2 and info["th_luma"] >= 32
-    assert info["smem"] <= 64 * 1024
+    assert info["ng"] == 2 and info["vq"] == 3 and info["th_luma"] >= 32        # vq: int4 per vertical table entry (12 words)
+    assert info["smem"] <= 36 * 1024                                              # source tile + int16 row-pair intermediate: 6 CTAs per SM
     # extreme shrink: fused limits exceeded -> two-pass path
     assert not emu_lib.plan_info(1280, 720, 320, 180, 4)["fused"]
