@@ -153,11 +153,14 @@ template <int NG>
 struct PickVt<NG, 1> {
     static fused_fn get(int) { return resize_fused_kernel<NG, 1>; }
 };
-fused_fn pick_fused(int ng, int vt) {
-    switch (ng) {
+fused_fn pick_fused(int nt, int vt) {
+    switch (nt) {
         case 1: return PickVt<1, kMaxVPairs>::get(vt);
         case 2: return PickVt<2, kMaxVPairs>::get(vt);
-        default: return PickVt<3, kMaxVPairs>::get(vt);
+        case 3: return PickVt<3, kMaxVPairs>::get(vt);
+        case 4: return PickVt<4, kMaxVPairs>::get(vt);
+        case 5: return PickVt<5, kMaxVPairs>::get(vt);
+        default: return PickVt<6, kMaxVPairs>::get(vt);
     }
 }
 
@@ -217,7 +220,7 @@ int launch_device(const gvc_resize_plan *p, const gvc_frames *src, const gvc_fra
         const int lt = p->t.cls[0].tiles_x * p->t.cls[0].tiles_y, ct = p->t.cls[1].tiles_x * p->t.cls[1].tiles_y;
         P.job[0].tile_base = 0; P.job[1].tile_base = lt; P.job[2].tile_base = lt + ct;
         P.tiles_per_frame = lt + 2 * ct;
-        fused_fn fn = pick_fused(p->t.ng, p->t.vt);
+        fused_fn fn = pick_fused(p->t.nt, p->t.vt);
         GVC_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->t.smem_bytes));
         for (int f0 = 0; f0 < n_frames; f0 += 32768) {
             const int nf = std::min(32768, n_frames - f0);

@@ -130,7 +130,8 @@ GVC_HD void resize_phase0(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
 // recomputed or reloaded.  A warp's 32 columns read at most a dozen neighbouring words of a row (no bank conflicts), and the
 // stores of a warp fall into 32 different banks.  Warp w takes columns 32 * (w & 3) .. + 31 and rows 32 * (w >> 2) .. + 31.
 // T layout: [quad (4 output columns)][kTPad row pairs][4] words, a word = the int16 samples of rows (2p, 2p + 1) of one column.
-template <int NG>
+// NT = tap PAIRS of the plan (the larger of the luma / chroma banks): one dp2a each.
+template <int NT>
 GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, const unsigned *S, int pitch_w, gvc_int4 *T) {
     const int warp = tid >> 5, lane = tid & 31;
     const int xl = (warp & 3) * 32 + lane;                 // tile-relative output column
@@ -149,17 +150,17 @@ GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, c
         const unsigned w0 = row[0], w1 = row[1];
         const unsigned u0 = funnel_r(w0, w1, r8);
         int a = dp2a_lo_su(e0.z, u0, 0);
-        a     = dp2a_hi_su(e0.w, u0, a);
-        if (NG >= 2) {
+        if (NT >= 2) a = dp2a_hi_su(e0.w, u0, a);
+        if (NT >= 3) {
             const unsigned w2 = row[2];
             const unsigned u1 = funnel_r(w1, w2, r8);
             a = dp2a_lo_su(e1.x, u1, a);
-            a = dp2a_hi_su(e1.y, u1, a);
-            if (NG >= 3) {
+            if (NT >= 4) a = dp2a_hi_su(e1.y, u1, a);
+            if (NT >= 5) {
                 const unsigned w3 = row[3];
                 const unsigned u2 = funnel_r(w2, w3, r8);
                 a = dp2a_lo_su(e1.z, u2, a);
-                a = dp2a_hi_su(e1.w, u2, a);
+                if (NT >= 6) a = dp2a_hi_su(e1.w, u2, a);
             }
         }
         return imin(a >> 7, 32767);
@@ -213,9 +214,11 @@ GVC_HD void resize_phase2(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
         int l0 = 0, l1 = 0, l2 = 0, l3 = 0, h0 = 0, h1 = 0, h2 = 0, h3 = 0;
 #pragma unroll
         for (int j = 0; j < NP; ++j) {
-            const gvc_int4 t = col[j];
             const unsigned lo = cf[1 + 2 * (j >> 1)], hi = cf[2 + 2 * (j >> 1)];      // bytes 0, 1 for even j, bytes 2, 3 for odd j
             const bool     up = (j & 1) != 0;
+            // an output row whose first tap sits on an even source row leaves the last pair empty (warp-uniform: y is)
+            if (j == NP - 1 && NP > 1 && (((lo | hi) >> (up ? 16 : 0)) & 0xffffu) == 0) break;
+            const gvc_int4 t = col[j];
             l0 = dp2a_su((unsigned)t.x, lo, l0, up); h0 = dp2a_ss((unsigned)t.x, hi, h0, up);
             l1 = dp2a_su((unsigned)t.y, lo, l1, up); h1 = dp2a_ss((unsigned)t.y, hi, h1, up);
             l2 = dp2a_su((unsigned)t.z, lo, l2, up); h2 = dp2a_ss((unsigned)t.z, hi, h2, up);

@@ -60,6 +60,7 @@ bool build_resize_tables(ResizeTables &t, int sw, int sh, int dw, int dh, int al
     t.fused_ok = ok;
     if (!ok) return true;
     t.ng = ng; t.vq = vq; t.vt = vt;
+    t.nt = (std::max(t.hb[0].taps, t.hb[1].taps) + 1) / 2;
     int s_chunks_max = 1;
     for (int c = 0; c < 2; ++c) {
         PlaneClassDev    &d  = t.cls[c];

@@ -14,7 +14,7 @@ struct ResizeTables {
     FilterBank hb[2], vb[2];                 // [0] luma, [1] chroma
     GenericClassDev gcls[2];                 // table pointers left null
     bool   fused_ok = false;
-    int    ng = 1, vq = 1, vt = 1, s_chunks_max = 1;
+    int    ng = 1, nt = 1, vq = 1, vt = 1, s_chunks_max = 1;   // ng: groups of 4 horizontal taps (table layout); nt: tap pairs (kernel template)
     size_t smem_bytes = 0;
     PlaneClassDev cls[2];                    // table pointers left null
     std::vector<int32_t> htab[2], vtab[2];   // fused-kernel tables (see resize_types.h)

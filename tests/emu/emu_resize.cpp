@@ -40,7 +40,16 @@ template <int NG>
 struct PickVt<NG, 1> {
     static tile_fn get(int) { return run_tile<NG, 1>; }
 };
-tile_fn pick(int ng, int vt) { return ng == 1 ? PickVt<1, kMaxVPairs>::get(vt) : ng == 2 ? PickVt<2, kMaxVPairs>::get(vt) : PickVt<3, kMaxVPairs>::get(vt); }
+tile_fn pick(int nt, int vt) {
+    switch (nt) {
+        case 1: return PickVt<1, kMaxVPairs>::get(vt);
+        case 2: return PickVt<2, kMaxVPairs>::get(vt);
+        case 3: return PickVt<3, kMaxVPairs>::get(vt);
+        case 4: return PickVt<4, kMaxVPairs>::get(vt);
+        case 5: return PickVt<5, kMaxVPairs>::get(vt);
+        default: return PickVt<6, kMaxVPairs>::get(vt);
+    }
+}
 
 }  // namespace
 
@@ -77,7 +86,7 @@ int emu_resize(const uint8_t *const sp[3], const int sstride[3], const size_t sf
             j.tile_base = k == 0 ? 0 : k == 1 ? lt : lt + ct;
         }
         P.tiles_per_frame = lt + 2 * ct;
-        tile_fn fn = pick(t.ng, t.vt);
+        tile_fn fn = pick(t.nt, t.vt);
         for (int f = 0; f < n_frames; ++f)
             for (int tile = 0; tile < P.tiles_per_frame; ++tile) fn(P, tile, f, t.s_chunks_max);
         return 0;
