@@ -166,11 +166,15 @@ GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, c
         return imin(a >> 7, 32767);
     };
 #if !defined(GVC_EMU)
-#pragma unroll 2
+#pragma unroll 4
 #endif
     for (int r = 0; r < 32; r += 2, w += 2 * pitch_w, t += 4) {
         const int t0 = sample(w), t1 = sample(w + pitch_w);
+#if defined(GVC_EMU)
         *t = ((unsigned)t0 & 0xffffu) | ((unsigned)t1 << 16);      // rows (r, r + 1) as one pair of int16
+#else
+        *t = __byte_perm((unsigned)t0, (unsigned)t1, 0x5410);      // rows (r, r + 1) as one pair of int16
+#endif
     }
 }
 
