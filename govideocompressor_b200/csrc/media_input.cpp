@@ -74,6 +74,7 @@ struct LavApi {
     void (*av_frame_free)(void **) = nullptr;
     void (*av_frame_unref)(void *) = nullptr;
     unsigned (*avformat_version)() = nullptr;
+    int (*av_opt_set_int)(void *, const char *, int64_t, int) = nullptr;      // optional: decoder threads
     bool ok = false;
     std::string where;
 };
@@ -121,6 +122,7 @@ LavApi &lav() {
     LOAD(api.h_util, av_frame_alloc); LOAD(api.h_util, av_frame_free); LOAD(api.h_util, av_frame_unref);
 #undef LOAD
     if (!ok) { api.where = "libav* symbols missing"; return api; }
+    *(void **)(&api.av_opt_set_int) = dlsym(api.h_util, "av_opt_set_int");
     const unsigned major = api.avformat_version() >> 16;
     if (major < 59 || major > 63) { api.where = "libavformat major version " + std::to_string(major) + " is outside the range this reader was written for (59..63)"; return api; }
     api.ok = true;
@@ -153,7 +155,15 @@ public:
         void *codecpar = *reinterpret_cast<void **>(static_cast<char *>(st) + 16);
         if (*reinterpret_cast<int *>(static_cast<char *>(st) + 8) != stream_ || !codecpar) { err = "unexpected AVStream layout"; return false; }
         cctx_ = a.avcodec_alloc_context3(dec);
-        if (!cctx_ || a.avcodec_parameters_to_context(cctx_, codecpar) < 0 || a.avcodec_open2(cctx_, dec, nullptr) < 0) { err = "cannot open the video decoder"; return false; }
+        if (!cctx_ || a.avcodec_parameters_to_context(cctx_, codecpar) < 0) { err = "cannot open the video decoder"; return false; }
+        // host decode is what bounds a worker once the kernels take milliseconds: let libavcodec use the cores the spawned ffmpeg would
+        // (frame threads; GVC_DECODE_THREADS overrides, 1 = the single-threaded decoder)
+        if (a.av_opt_set_int) {
+            const char *env = getenv("GVC_DECODE_THREADS");
+            const long  n = env ? atol(env) : 0;      // 0 = libavcodec picks one per core
+            a.av_opt_set_int(cctx_, "threads", n < 0 ? 0 : n, 0);
+        }
+        if (a.avcodec_open2(cctx_, dec, nullptr) < 0) { err = "cannot open the video decoder"; return false; }
         // audio: AVCodecParameters starts with codec_type, codec_id, codec_tag, extradata, extradata_size in every libavcodec
         // this reader accepts; AV_CODEC_ID_AAC = 0x15002
         astream_ = a.av_find_best_stream(fmt_, /*AVMEDIA_TYPE_AUDIO*/ 1, -1, -1, nullptr, 0);
