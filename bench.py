@@ -280,7 +280,7 @@ def measure_transcode_file(gvc, c, segments, workdir):
         dt = time.perf_counter() - t0
         return {"value": n / dt, "unit": "frames/s", "pieces": len(paths), "args": args,
                 "note": "gvc_transcode_file on .mp4 pieces, one at a time (one worker process): host demux + H.264 decode (FFmpeg's libavcodec, "
-                        "one thread) + H2D + kernels + MP4 out"}
+                        "frame threads) + H2D + kernels + MP4 out"}
     finally:
         shutil.rmtree(workdir, ignore_errors=True)
 

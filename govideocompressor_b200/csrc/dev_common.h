@@ -30,4 +30,15 @@ GVC_HD int imin(int a, int b) { return a < b ? a : b; }
 GVC_HD int imax(int a, int b) { return a > b ? a : b; }
 GVC_HD int iclamp(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 GVC_HD int iabs(int v) { return v < 0 ? -v : v; }
+GVC_HD unsigned pack_sat_u8x4(int v0, int v1, int v2, int v3) {   // bytes clip_u8(v0) | clip_u8(v1) << 8 | clip_u8(v2) << 16 | clip_u8(v3) << 24
+#if defined(GVC_EMU)
+    return (unsigned)clip_u8(v0) | ((unsigned)clip_u8(v1) << 8) | ((unsigned)clip_u8(v2) << 16) | ((unsigned)clip_u8(v3) << 24);
+#else
+    unsigned hi, d;                                      // cvt.pack: d = c << 16 | sat(a) << 8 | sat(b)
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(v3), "r"(v2), "r"(0));
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(v1), "r"(v0), "r"(hi));
+    return d;
+#endif
+}
+
 }  // namespace gvc

@@ -37,6 +37,12 @@ void fill_quant_params(QuantParams &q, int qp, bool intra) {
     one_qp(q.qp, dz, q.mf_y, q.bias_y, q.dq_y);
     one_qp(q.qpc, dz, q.mf_c, q.bias_c, q.dq_c);
     q.lambda = lambda_for_qp(qp);
+    for (int c = 0; c < 3; ++c) {
+        q.thr_y[c] = (65536 + q.mf_y[c] - 1) / q.mf_y[c] - q.bias_y[c];
+        q.thr_c[c] = (65536 + q.mf_c[c] - 1) / q.mf_c[c] - q.bias_c[c];
+    }
+    const int mdc = q.mf_c[0] >> 1;
+    q.thr_cdc = (65536 + mdc - 1) / mdc - (q.bias_c[0] << 1);
 }
 
 void fill_quant8_params(Quant8Params &q, int qp, bool intra) {

@@ -460,8 +460,10 @@ GVC_HD void idct4x4(int c[16]) {  // H.264 8.5.12.2, result includes the (x+32)>
         c[x] = (s02 + s13 + 32) >> 6; c[4 + x] = (d02 + d13 + 32) >> 6; c[8 + x] = (d02 - d13 + 32) >> 6; c[12 + x] = (s02 - s13 + 32) >> 6;
     }
 }
-GVC_HD int quant_one(int c, int mf, int bias) {   // x264 QUANT_ONE
-    return c > 0 ? (int)(((unsigned)(bias + c) * (unsigned)mf) >> 16) : -(int)(((unsigned)(bias - c) * (unsigned)mf) >> 16);
+GVC_HD int quant_one(int c, int mf, int bias) {   // x264 QUANT_ONE: sign(c) * (((bias + |c|) * mf) >> 16)
+    const int s = c >> 31;                                                   // 0 or -1
+    const int q = (int)(((unsigned)(bias + ((c ^ s) - s)) * (unsigned)mf) >> 16);
+    return (q ^ s) - s;
 }
 GVC_HD int dequant_one(int c, int scale, int qp) {   // H.264 8.5.12.1 / x264 dequant_4x4; wraps to int16 like the oracle
     const int qbits = qp / 6 - 4;
@@ -752,6 +754,59 @@ GVC_HD void enc_mb_p1(int lane, const EncMbArgs &a, bool al, int mx, int my, Enc
     dct4x4(L.d);
     if (lane >= 16) sm.cdc[lane - 16] = L.d[0];
 }
+// Between phase 1 and phase 2: can ANY coefficient of the lane's block quantise to a nonzero level?  (bias + |c|) * mf >> 16 >= 1
+// exactly when |c| >= thr of its class (QuantParams::thr_*), so three maxima per block decide it.  Static content leaves most
+// macroblocks of a P picture without a single level: when no lane of the warp answers yes, phase 2 is replaced by
+// enc_mb_p2_zero -- same outputs (all levels zero, reconstruction = prediction) without quantiser, inverse transform or packing.
+GVC_HD bool enc_mb_any_level(int lane, const EncMbArgs &a, const EncMbSmem &sm, const EncLane &L) {
+    if (lane >= 24) return false;
+    const QuantParams &q = a.q;
+    const bool luma = lane < 16;
+    int m[3] = {0, 0, 0};
+    for (int i = luma ? 0 : 1; i < 16; ++i) m[coef_class(i)] = imax(m[coef_class(i)], iabs(L.d[i]));   // a chroma block's DC goes the 2x2 way
+    bool any = false;
+    for (int c = 0; c < 3; ++c) any = any || m[c] >= (luma ? q.thr_y[c] : q.thr_c[c]);
+    if (!luma) {
+        const int p = (lane - 16) >> 2;
+        const int d0 = sm.cdc[4 * p], d1 = sm.cdc[4 * p + 1], d2 = sm.cdc[4 * p + 2], d3 = sm.cdc[4 * p + 3];
+        const int mdc = imax(imax(iabs(d0 + d1 + d2 + d3), iabs(d0 - d1 + d2 - d3)), imax(iabs(d0 + d1 - d2 - d3), iabs(d0 - d1 - d2 + d3)));
+        any = any || mdc >= q.thr_cdc;
+    }
+    return any;
+}
+GVC_HD void enc_mb_p2_zero(int lane, const EncMbArgs &a, bool al, int mx, int my, EncMbSmem &sm, EncLane &L) {
+    if (lane >= 24) return;
+    const bool luma = lane < 16;
+    int16_t *mbco = a.coefs ? a.coefs + (long long)(my * a.mbw + mx) * kMbCoefs : nullptr;
+    for (int i = 0; i < 8; ++i) L.lev[i] = 0;
+    if (!luma && ((lane - 16) & 3) == 0) {
+        const int p = (lane - 16) >> 2;
+        for (int i = 0; i < 4; ++i) sm.dclev[4 * p + i] = 0;
+        if (mbco) for (int i = 0; i < 4; ++i) mbco[24 * 16 + 4 * p + i] = 0;
+    }
+    if (a.nnz_y) {
+        if (luma) a.nnz_y[(4 * my + (lane >> 2)) * (4 * a.mbw) + 4 * mx + (lane & 3)] = 0;
+        else { const int b = (lane - 16) & 3; (lane < 20 ? a.nnz_u : a.nnz_v)[(2 * my + (b >> 1)) * (2 * a.mbw) + 2 * mx + (b & 1)] = 0; }
+    }
+    if (mbco) {
+        if (al) {
+            gvc_uint4 *co = reinterpret_cast<gvc_uint4 *>(mbco + lane * 16);
+            gvc_uint4 z; z.x = z.y = z.z = z.w = 0;
+            co[0] = z; co[1] = z;
+        } else {
+            for (int i = 0; i < 16; ++i) mbco[lane * 16 + i] = 0;
+        }
+    }
+    int x, y, k;
+    enc_lane_block(lane, mx, my, x, y, k);
+    const int st = luma ? a.sy : a.sc;
+    uint8_t *rec = (luma ? a.rec_y : lane < 20 ? a.rec_u : a.rec_v) + (y * st + x);
+    for (int j = 0; j < 4; ++j) {
+        const unsigned w = L.pred[j];
+        if (al) *reinterpret_cast<unsigned *>(rec + j * st) = w;
+        else for (int i = 0; i < 4; ++i) rec[j * st + i] = (uint8_t)(w >> (8 * i));
+    }
+}
 // Phase 2: chroma DC path (2x2 transform of the plane's four DCs; every lane of the plane recomputes it and keeps element
 // b), quantisation, levels, dequantisation, inverse transform, reconstruction.
 GVC_HD void enc_mb_p2(int lane, const EncMbArgs &a, bool al, int mx, int my, EncMbSmem &sm, EncLane &L) {
@@ -803,8 +858,8 @@ GVC_HD void enc_mb_p2(int lane, const EncMbArgs &a, bool al, int mx, int my, Enc
     const int st = luma ? a.sy : a.sc;
     uint8_t *rec = (luma ? a.rec_y : lane < 20 ? a.rec_u : a.rec_v) + (y * st + x);
     for (int j = 0; j < 4; ++j) {
-        unsigned w = 0;
-        for (int i = 0; i < 4; ++i) w |= (unsigned)clip_u8(byte_of(L.pred[j], i) + L.d[j * 4 + i]) << (8 * i);
+        const unsigned w = pack_sat_u8x4(byte_of(L.pred[j], 0) + L.d[j * 4], byte_of(L.pred[j], 1) + L.d[j * 4 + 1],
+                                         byte_of(L.pred[j], 2) + L.d[j * 4 + 2], byte_of(L.pred[j], 3) + L.d[j * 4 + 3]);
         if (al) *reinterpret_cast<unsigned *>(rec + j * st) = w;
         else for (int i = 0; i < 4; ++i) rec[j * st + i] = (uint8_t)(w >> (8 * i));
     }
@@ -1060,8 +1115,8 @@ GVC_HD void intra_p3d(int lane, const IntraArgs &a, bool al, int mx, int my, Int
     uint8_t *rec = (luma ? a.rec_y : lane < 20 ? a.rec_u : a.rec_v) + (y * st + x);
     unsigned right = 0, bottom = 0;
     for (int j = 0; j < 4; ++j) {
-        unsigned w = 0;
-        for (int i = 0; i < 4; ++i) w |= (unsigned)clip_u8(byte_of(L.pred[j], i) + L.d[j * 4 + i]) << (8 * i);
+        const unsigned w = pack_sat_u8x4(byte_of(L.pred[j], 0) + L.d[j * 4], byte_of(L.pred[j], 1) + L.d[j * 4 + 1],
+                                         byte_of(L.pred[j], 2) + L.d[j * 4 + 2], byte_of(L.pred[j], 3) + L.d[j * 4 + 3]);
         if (al) *reinterpret_cast<unsigned *>(rec + j * st) = w;
         else for (int i = 0; i < 4; ++i) rec[j * st + i] = (uint8_t)(w >> (8 * i));
         right |= (w >> 24) << (8 * j);

@@ -36,6 +36,8 @@ struct QuantParams {
     int mf_c[3], bias_c[3];      // chroma
     int dq_y[3], dq_c[3];        // LevelScale (dequant multipliers, 16*normAdjust)
     int lambda;                  // motion-cost lambda (x264_lambda_tab[qp])
+    // smallest |coefficient| that quantises to a nonzero level, per class: (bias + |c|) * mf >= 65536; cdc = chroma DC (mf >> 1, bias << 1)
+    int thr_y[3], thr_c[3], thr_cdc;
 };
 
 // 8x8 transform (High-profile transform_size_8x8): quantiser constants by coefficient class

@@ -229,7 +229,8 @@ __global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __gri
     EncLane L;
     enc_mb_p1(lane, a, al, mx, my, sm, L);
     __syncwarp();
-    enc_mb_p2(lane, a, al, mx, my, sm, L);
+    if (__any_sync(0xffffffffu, enc_mb_any_level(lane, a, sm, L))) enc_mb_p2(lane, a, al, mx, my, sm, L);
+    else enc_mb_p2_zero(lane, a, al, mx, my, sm, L);      // warp-uniform: nothing of this macroblock survives the quantiser
     __syncwarp();
     enc_mb_p3(lane, a, mx, my, sm);
     __syncwarp();

@@ -129,7 +129,9 @@ void emu_run_encode_inter(const EncMbArgs &a) {
             EncLane L[32];
             memset(L, 0xAB, sizeof(L));
             for (int l = 0; l < 32; ++l) enc_mb_p1(l, a, al, mx, my, sm, L[l]);
-            for (int l = 0; l < 32; ++l) enc_mb_p2(l, a, al, mx, my, sm, L[l]);
+            bool any = false;
+            for (int l = 0; l < 32; ++l) any = enc_mb_any_level(l, a, sm, L[l]) || any;
+            for (int l = 0; l < 32; ++l) { if (any) enc_mb_p2(l, a, al, mx, my, sm, L[l]); else enc_mb_p2_zero(l, a, al, mx, my, sm, L[l]); }
             for (int l = 0; l < 32; ++l) enc_mb_p3(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) enc_mb_p4(l, a, mx, my, sm, L[l]);
         }
