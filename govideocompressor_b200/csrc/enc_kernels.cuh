@@ -762,10 +762,14 @@ GVC_HD bool enc_mb_any_level(int lane, const EncMbArgs &a, const EncMbSmem &sm, 
     if (lane >= 24) return false;
     const QuantParams &q = a.q;
     const bool luma = lane < 16;
-    int m[3] = {0, 0, 0};
-    for (int i = luma ? 0 : 1; i < 16; ++i) m[coef_class(i)] = imax(m[coef_class(i)], iabs(L.d[i]));   // a chroma block's DC goes the 2x2 way
-    bool any = false;
-    for (int c = 0; c < 3; ++c) any = any || m[c] >= (luma ? q.thr_y[c] : q.thr_c[c]);
+    // maxima per coefficient class (0: both indices even, 2: both odd, 1: mixed); a chroma block's DC goes the 2x2 way.  Written out so
+    // that every index is a compile-time constant (the block stays in registers).
+    const int dc = luma ? iabs(L.d[0]) : 0;
+    const int m0 = imax(imax(dc, iabs(L.d[2])), imax(iabs(L.d[8]), iabs(L.d[10])));
+    const int m2 = imax(imax(iabs(L.d[5]), iabs(L.d[7])), imax(iabs(L.d[13]), iabs(L.d[15])));
+    const int m1 = imax(imax(imax(iabs(L.d[1]), iabs(L.d[3])), imax(iabs(L.d[4]), iabs(L.d[6]))),
+                        imax(imax(iabs(L.d[9]), iabs(L.d[11])), imax(iabs(L.d[12]), iabs(L.d[14]))));
+    bool any = m0 >= (luma ? q.thr_y[0] : q.thr_c[0]) || m1 >= (luma ? q.thr_y[1] : q.thr_c[1]) || m2 >= (luma ? q.thr_y[2] : q.thr_c[2]);
     if (!luma) {
         const int p = (lane - 16) >> 2;
         const int d0 = sm.cdc[4 * p], d1 = sm.cdc[4 * p + 1], d2 = sm.cdc[4 * p + 2], d3 = sm.cdc[4 * p + 3];
