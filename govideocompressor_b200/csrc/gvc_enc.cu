@@ -174,7 +174,7 @@ me_refine_kernel(const __grid_constant__ Batch<MeRefArgs> B, const __grid_consta
                 v += __shfl_xor_sync(0xffffffffu, v, 2);
                 v += __shfl_xor_sync(0xffffffffu, v, 4);
                 v += __shfl_xor_sync(0xffffffffu, v, 8);
-                if (ci < 8) me_take(L, sc, v, ci, step, b);
+                if (ci < 8) me_take_desc(L, sc, v, me_desc(L.cx, L.cy, ci, step), ci, step, b);
             }
             // the better half-warp wins (order bits break ties as the sequential search would); it is the next centre
             const unsigned ok = __shfl_xor_sync(0xffffffffu, b.key, 16);

@@ -56,6 +56,40 @@ GVC_HD void sq8(int i, int &dx, int &dy) {   // (0,-1),(0,1),(-1,0),(1,0),(-1,-1
     dx = (int)((0xA085u >> (2 * i)) & 3u) - 1;
     dy = (int)((0x8858u >> (2 * i)) & 3u) - 1;
 }
+// ---- candidate descriptors ---------------------------------------------------------------------------------------------
+// Where a sub-sample candidate's samples come from depends only on the fractional part of the search centre (0 or 2 per
+// component) and on the candidate: mc_luma_src's plane pair, the full-sample displacement of each plane's block relative to the
+// centre's, and whether a second plane is averaged in.  All 9 + 4 x 8 cases are worked out at compile time into one word each:
+// bits 0-1 plane 1, 2-3 column + 1, 4-5 row + 1, 6 second plane used, 7-8 plane 2, 9-10 column + 1, 11-12 row + 1, 13-14 dx + 1,
+// 15-16 dy + 1 ((dx, dy) = the candidate's direction, sq8 order; the centre itself is direction (0, 0)).
+constexpr int me_dx8(int i) { return (int)((0xA085u >> (2 * i)) & 3u) - 1; }
+constexpr int me_dy8(int i) { return (int)((0x8858u >> (2 * i)) & 3u) - 1; }
+constexpr unsigned me_desc_make(int fcx, int fcy, int dx, int dy, int step) {
+    const int mvx = fcx + dx * step, mvy = fcy + dy * step;          // relative to the centre's full-sample position
+    const int X = mvx >> 2, Y = mvy >> 2, fx = mvx & 3, fy = mvy & 3, q = fy * 4 + fx;
+    const unsigned p1 = (kQpelRef0 >> (2 * q)) & 3u, p2 = (kQpelRef1 >> (2 * q)) & 3u, two = (q & 5) ? 1u : 0u;
+    return p1 | (unsigned)(X + 1) << 2 | (unsigned)(Y + (fy == 3 ? 1 : 0) + 1) << 4 | two << 6 | p2 << 7 | (unsigned)(X + (fx == 3 ? 1 : 0) + 1) << 9 |
+           (unsigned)(Y + 1) << 11 | (unsigned)(dx + 1) << 13 | (unsigned)(dy + 1) << 15;
+}
+struct MeDescTable { unsigned v[41]; };
+constexpr MeDescTable me_desc_table() {
+    MeDescTable t{};
+    t.v[0] = me_desc_make(0, 0, 0, 0, 2);
+    for (int i = 0; i < 8; ++i) t.v[1 + i] = me_desc_make(0, 0, me_dx8(i), me_dy8(i), 2);
+    for (int c = 0; c < 4; ++c)
+        for (int i = 0; i < 8; ++i) t.v[9 + 8 * c + i] = me_desc_make((c & 1) * 2, (c >> 1) * 2, me_dx8(i), me_dy8(i), 1);
+    return t;
+}
+#if defined(GVC_EMU)
+static const MeDescTable kMeDesc = me_desc_table();
+#else
+__constant__ const MeDescTable kMeDesc = me_desc_table();
+#endif
+// descriptor of candidate ci (-1 = the centre, step 2 only) of a step around centre (cx, cy) in quarter samples
+GVC_HD unsigned me_desc(int cx, int cy, int ci, int step) {
+    return kMeDesc.v[step == 2 ? ci + 1 : 9 + 8 * (((cx >> 1) & 1) | (cy & 2)) + ci];
+}
+
 // component c of neighbour k's lowres vector in quarter samples (k: left, above, above right -- or above left when there is none), 0 outside
 GVC_HD int me_neighbour(const MeRefArgs &a, int mx, int my, int k, int c) {
     int nx = k == 0 ? mx - 1 : k == 1 ? mx : mx + 1, ny = k == 0 ? my : my - 1;
@@ -281,6 +315,24 @@ GVC_HD int me_satd_at(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L, 
     }
     return satd4x4_rows(L.hc, w[0], w[1], w[2], w[3]);
 }
+// The same for the candidate a descriptor names, relative to the lane's search centre: no fraction arithmetic, no plane table.
+GVC_HD int me_satd_desc(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L, unsigned d) {
+    const int p1 = (int)(d & 3u), p2 = (int)((d >> 7) & 3u);
+    const int c1 = (int)((d >> 2) & 3u) - 1, r1 = (int)((d >> 4) & 3u) - 1, c2 = (int)((d >> 9) & 3u) - 1, r2 = (int)((d >> 11) & 3u) - 1;
+    const bool two = (d & 64u) != 0;
+    unsigned w[4];
+    if (!L.far) {
+        const int col = (L.cx >> 2) + L.wx, row = (L.cy >> 2) + L.wy;
+        for (int j = 0; j < 4; ++j) w[j] = me_win4(sm.win[p1], col + c1, row + r1 + j);
+        if (two) for (int j = 0; j < 4; ++j) w[j] = avg_u8x4(w[j], me_win4(sm.win[p2], col + c2, row + r2 + j));
+    } else {
+        const int off = L.base + (L.cy >> 2) * a.stride + (L.cx >> 2);
+        const uint8_t *s1 = me_plane(a, p1) + (off + r1 * a.stride + c1), *s2 = me_plane(a, p2) + (off + r2 * a.stride + c2);
+        for (int j = 0; j < 4; ++j) w[j] = ld_u32_any(s1 + j * a.stride);
+        if (two) for (int j = 0; j < 4; ++j) w[j] = avg_u8x4(w[j], ld_u32_any(s2 + j * a.stride));
+    }
+    return satd4x4_rows(L.hc, w[0], w[1], w[2], w[3]);
+}
 // The nine half-sample candidates around a FULL-sample centre, v[ci + 1] for ci = -1 (the centre) .. 7 (sq8 order), with the
 // window rows shared between the candidates that read the same plane: full plane 4 rows; V plane 5 rows for (0,-1),(0,+1);
 // H plane 4 rows, two shifts, for (-1,0),(+1,0); C plane 5 rows, two shifts, for the four diagonal ones.
@@ -328,11 +380,7 @@ GVC_HD void me_half_all(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L
 }
 // the eight quarter-sample candidates around the centre (sq8 order)
 GVC_HD void me_quarter_all(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L, int v[8]) {
-    for (int ci = 0; ci < 8; ++ci) {
-        int dx, dy;
-        sq8(ci, dx, dy);
-        v[ci] = me_satd_at(a, sm, L, L.cx + dx, L.cy + dy);
-    }
+    for (int ci = 0; ci < 8; ++ci) v[ci] = me_satd_desc(a, sm, L, me_desc(L.cx, L.cy, ci, 1));
 }
 // Best candidate so far of a partition as key = cost << 4 | order (order = position in the sequential candidate list, 0 = the
 // one carried over from the previous step: the sequential search replaces its best only by a strictly lower cost).
@@ -350,6 +398,13 @@ GVC_HD MeStepCost me_step_cost(const MeRefArgs &a, const MeLane &L, int step) {
 GVC_HD void me_take(const MeLane &L, const MeStepCost &c, int total, int ci, int step, MeBest &b) {
     int dx = 0, dy = 0;
     if (ci >= 0) sq8(ci, dx, dy);
+    const int bits = (dx < 0 ? c.x[0] : dx > 0 ? c.x[2] : c.x[1]) + (dy < 0 ? c.y[0] : dy > 0 ? c.y[2] : c.y[1]);
+    const unsigned k = ((unsigned)(total + bits) << 4) | (unsigned)(ci + 1);
+    if (k < b.key) { b.key = k; b.x = L.cx + dx * step; b.y = L.cy + dy * step; }
+}
+// the same with the direction taken from the candidate's descriptor (the one-partition path: the candidate differs per half-warp)
+GVC_HD void me_take_desc(const MeLane &L, const MeStepCost &c, int total, unsigned d, int ci, int step, MeBest &b) {
+    const int dx = (int)((d >> 13) & 3u) - 1, dy = (int)((d >> 15) & 3u) - 1;
     const int bits = (dx < 0 ? c.x[0] : dx > 0 ? c.x[2] : c.x[1]) + (dy < 0 ? c.y[0] : dy > 0 ? c.y[2] : c.y[1]);
     const unsigned k = ((unsigned)(total + bits) << 4) | (unsigned)(ci + 1);
     if (k < b.key) { b.key = k; b.x = L.cx + dx * step; b.y = L.cy + dy * step; }
@@ -378,9 +433,7 @@ GVC_HD int me_group_sum(int lane, int v) {     // sum over the lanes of the part
 // candidate of the lane's half-warp in round r of `step` (step 2: -1, 0 | 1, 2 | ... | 7, none; step 1: 0, 1 | ... | 6, 7); 8 = none
 GVC_HD int me_fast_cand(int lane, int r, int step) { return step == 2 ? 2 * r - 1 + (lane >> 4) : 2 * r + (lane >> 4); }
 GVC_HD int me_fast_satd(const MeRefArgs &a, const MeRefSmem &sm, const MeLane &L, int ci, int step) {
-    int dx = 0, dy = 0;
-    if (ci >= 0) sq8(ci, dx, dy);
-    return me_satd_at(a, sm, L, L.cx + dx * step, L.cy + dy * step);
+    return me_satd_desc(a, sm, L, me_desc(L.cx, L.cy, ci, step));
 }
 GVC_HD void me_write_out(const MeRefArgs &a, int mx, int my, int mode, int cost, const int mvx[4], const int mvy[4]) {
     MbMotion m;

@@ -81,7 +81,7 @@ void emu_run_me_refine(const MeRefArgs &a) {
                             int total = 0;
                             for (int i = 0; i < 16; ++i) total += part[(l & 16) + i];
                             const int ci = me_fast_cand(l, r, step);
-                            if (ci < 8) me_take(L[l], sc[l], total, ci, step, b[l]);
+                            if (ci < 8) me_take_desc(L[l], sc[l], total, me_desc(L[l].cx, L[l].cy, ci, step), ci, step, b[l]);
                         }
                     }
                     for (int l = 0; l < 16; ++l) {
