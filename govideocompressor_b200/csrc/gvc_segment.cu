@@ -188,6 +188,12 @@ bool tracing() { static const bool on = getenv("GVC_TRACE") != nullptr; return o
 constexpr bool tracing() { return false; }
 #endif
 
+// QP of the IDR picture for `-crf`: 3 below the P pictures' (x264's default ip_factor 1.4 is about 3 QP), but not below 4.  The
+// streams declare Constrained Baseline, whose CAVLC has no level_prefix above 15 (H.264 9.2.2.1): a level must stay below 2064.
+// Only the luma DC of an Intra16x16 macroblock can get larger -- up to 16 * 16 * 255 / 2 before the quantiser -- and from QP 4 on
+// (multiplier 8192 / 2) its largest level is 2040 (2331 at QP 3); every other coefficient stays below 820 even at QP 0.
+int idr_qp(int crf) { return std::max(crf - 3, 4); }
+
 size_t i420_bytes(int w, int h) { return size_t(w) * h + 2 * size_t((w + 1) / 2) * ((h + 1) / 2); }
 
 // issue resize (source I420 on the device -> padded current pictures) and every encoder kernel for a batch of segments;
@@ -310,7 +316,7 @@ int gvc_encoder_create(gvc_encoder **enc, const gvc_encoder_config *cfg) {
     if ((rc = gvc_resize_plan_create(&e->plan, c.src_w, c.src_h, c.dst_w, c.dst_h, GVC_PIX_YUV420P, c.scale_algo))) { gvc_encoder_destroy(e); return rc; }
     SegmentConfig sc;
     sc.w = c.dst_w; sc.h = c.dst_h; sc.fps_num = c.fps_num; sc.fps_den = c.fps_den;
-    sc.qp_p = c.crf; sc.qp_i = c.crf >= 3 ? c.crf - 3 : 0;     // x264's default ip_factor 1.4 is about 3 QP (also gvc_encoder_set_crf)
+    sc.qp_p = c.crf; sc.qp_i = idr_qp(c.crf);
     sc.merange = c.merange; sc.keep_recon = c.keep_recon != 0;
     sc.device_entropy = c.entropy != GVC_ENTROPY_HOST;
     sc.max_batch = c.max_batch;
@@ -515,7 +521,7 @@ int gvc_encoder_set_crf(gvc_encoder *e, int crf) {
     if (e->pending) { set_error("gvc_encoder_set_crf: a segment is in flight"); return GVC_ERR_INVALID_ARG; }
     if (crf == e->cfg.crf) return GVC_OK;
     e->cfg.crf = crf;
-    e->seg->set_qp(crf >= 3 ? crf - 3 : 0, crf);
+    e->seg->set_qp(idr_qp(crf), crf);
     e->graph_n.clear();          // quantiser constants are kernel arguments: the captured graph is for the old ones
     return GVC_OK;
 }

@@ -190,7 +190,7 @@ typedef struct gvc_encoder_config {
     int src_w, src_h;          /* incoming pictures: 8-bit I420, planes tight */
     int dst_w, dst_h;          /* encoded size; 0 = same as source (`-s WxH` / `-vf scale=`) */
     int fps_num, fps_den;      /* 0 = 30/1 */
-    int crf;                   /* `-crf`, 0..51; P pictures use QP = crf, the IDR QP = crf - 3 */
+    int crf;                   /* `-crf`, 0..51; P pictures use QP = crf, the IDR QP = max(crf - 3, 4) (levels stay codable in Baseline CAVLC) */
     int merange;               /* `-me_range`, 0 = 16 */
     int scale_algo;            /* GVC_SCALE_*, 0 = bicubic */
     int keep_recon;            /* keep the reconstruction of every picture (tests compare it with a decoder) */

@@ -41,7 +41,7 @@ def test_stream_identical_to_cpu_emulation_and_decodable(gvc, w, h, n, crf, kw, 
     merange = 32 if kw.get("fast") else 16
     enc = gvc.Encoder(w, h, crf=crf, merange=merange, keep_recon=True, host_threads=3, entropy=entropy)
     stream = enc.encode_host(frames, annexb=True)
-    ref = emu_lib.encode_segment(frames, w, h, qp_i=max(crf - 3, 0), qp_p=crf, merange=merange)
+    ref = emu_lib.encode_segment(frames, w, h, qp_i=max(crf - 3, 4), qp_p=crf, merange=merange)     # gvc_segment.cu idr_qp()
     assert stream == ref["annexb"], "GPU stream differs from the CPU emulation of the same kernels"
     np.testing.assert_array_equal(enc.recon(), ref["recon"])
     np.testing.assert_array_equal(enc.stats(), ref["stats"])
