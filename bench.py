@@ -296,6 +296,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the quality and e2e_file measurements")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels one by one instead of replaying CUDA graphs")
+    ap.add_argument("--strong", action="store_true", help="strong scaling: ONE clip per step for the whole job, its segments dealt out to the ranks "
+                                                           "(govideocompressor_b200.farm.segments_for_rank: highest index first, like the dispatcher)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -348,10 +350,17 @@ def main():
             os.close(saved)
     gvc.init(local)
     SW, SH, DW, DH, SEG_FRAMES, NSEG = c["sw"], c["sh"], c["dw"], c["dh"], c["seg"], c["nseg"]
+    from govideocompressor_b200 import farm
+    TOTAL_SEG = world * NSEG                           # segments of a step over all ranks (weak scaling: every rank has its own clip)
+    if args.strong:
+        mine = farm.segments_for_rank(NSEG, rank, world)      # this rank's share of the ONE clip
+        if not mine:
+            raise SystemExit("--strong: more ranks than segments")
+        TOTAL_SEG, NSEG = NSEG, len(mine)
     # The step's NSEG segments are encoded as NENC batches: within a batch the segments advance picture by picture together, one
     # kernel launch per stage for all of them (one CUDA graph per batch, replayed per step); the batches run on their own streams,
     # each issued by its own host thread, so one batch's dependent chain fills the other's gaps.
-    NENC = int(os.environ.get("GVC_BENCH_ENCODERS", "2" if NSEG % 2 == 0 else "1"))
+    NENC = int(os.environ.get("GVC_BENCH_ENCODERS", "2" if NSEG % 2 == 0 and NSEG >= 4 else "1"))
     assert NSEG % NENC == 0 and NSEG // NENC <= 16
     PER = NSEG // NENC
     encs = [gvc.Encoder(SW, SH, DW, DH, fps=(30, 1), crf=CRF, merange=c["merange"], host_threads=max(1, cores // NENC), disable_graph=args.no_graph, max_batch=PER)
@@ -412,9 +421,8 @@ def main():
     clocks = sampler.stop()
     # device time of the step = the slowest stream's span (all streams start together); wall clock is reported beside it
     ms_total = max(ev[k][0].elapsed_time(ev[k][1]) for k in range(NENC))
-    from govideocompressor_b200 import farm
     ms_total = farm.max_over_ranks(ms_total, "cuda")
-    value = world * NSEG * SEG_FRAMES * args.steps / (ms_total * 1e-3)
+    value = TOTAL_SEG * SEG_FRAMES * args.steps / (ms_total * 1e-3)
 
     # ---- stage pass: the same batched launches with a CUDA-event pair around every one (roofline figures) -------
     enc.set_timing(True)
@@ -444,7 +452,7 @@ def main():
             e.select(k)
             stream_bytes += int(e.stats()[:, 3].sum())     # the step's result as read on the host
             d2h_bytes += e.record_bytes()
-    e2e = world * NSEG * SEG_FRAMES * args.steps / farm.max_over_ranks(e2e_s, "cuda")
+    e2e = TOTAL_SEG * SEG_FRAMES * args.steps / farm.max_over_ranks(e2e_s, "cuda")
     for e in encs:
         e.close()
 
@@ -491,8 +499,11 @@ def main():
         d = table[dom]
         cfg = config_json(c)
         cfg.update({"batches": NENC, "segments_per_batch": PER})
+        if args.strong:
+            cfg["parallelism"] = "ONE clip per step, its %d segments dealt out to the %d ranks highest index first (no collective)" % (TOTAL_SEG, world)
+            cfg["segments_per_step"] = TOTAL_SEG
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+                "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong" if args.strong else "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg,
                 "wall_ms_per_step": wall_ms / args.steps,
                 "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": NSEG * SEG_FRAMES * fb,

@@ -67,6 +67,21 @@ def main():
         us = timed(lambda: plan.resize_device(src, dst, n), args.iters)
         add("resize x8", "%dx%d->%dx%d" % (sw, sh, dw, dh), us, int(1.5 * (sw * sh + dw * dh)) * n)
 
+    # ---- K1 resize, one 38-picture segment per launch (the pipeline's launch), and the allocation-free two-pass entry point
+    import govideocompressor_b200.lib as L
+    for (sw, sh, dw, dh) in ((1920, 1080, 1280, 720), (3840, 2160, 1920, 1080)):
+        n = 38
+        plan = gvc.ResizePlan(sw, sh, dw, dh)
+        src = torch.randint(0, 256, (n, plan.frame_bytes(sw, sh)), dtype=torch.uint8, device="cuda")
+        dst = torch.empty((n, plan.frame_bytes(dw, dh)), dtype=torch.uint8, device="cuda")
+        us = timed(lambda: plan.resize_device(src, dst, n), args.iters)
+        add("resize x38", "%dx%d->%dx%d" % (sw, sh, dw, dh), us, int(1.5 * (sw * sh + dw * dh)) * n)
+        s_, d_ = plan._frames_packed(src.data_ptr(), sw, sh), plan._frames_packed(dst.data_ptr(), dw, dh)
+        st = torch.cuda.current_stream().cuda_stream
+        n2 = 8
+        us = timed(lambda: plan._lib.gvc_resize_frames_device_static(plan._h, ctypes.byref(s_), ctypes.byref(d_), n2, ctypes.c_void_p(st)), max(5, args.iters // 5))
+        add("resize static x8", "%dx%d->%dx%d (two-pass, built-in scratch)" % (sw, sh, dw, dh), us, int(1.5 * (sw * sh + dw * dh)) * n2)
+
     # ---- encoder stages per coded size
     P = E.PAD
     for (w, h, r) in ((854, 480, 8), (1280, 720, 8), (1920, 1080, 8), (3840, 2160, 16)):
