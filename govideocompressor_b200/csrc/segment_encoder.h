@@ -81,6 +81,14 @@ public:
     SegmentEncoder(Ops &ops, const SegmentConfig &cfg) : ops_(ops), cfg_(cfg), g_(make_geom(cfg.w, cfg.h)), ps_(plane_sizes(g_)) {
         cfg_.max_batch = std::max(1, std::min(cfg_.max_batch, kMaxBatch));
         lanes_.resize(size_t(cfg_.max_batch));
+        // How much of the planes' padding anything ever reads: a vector reaches merange (twice the lowres window) + 2 (the 5x5 grid)
+        // + 1 (the sample right of / below a quarter position) samples beyond the picture, chroma half of that + 1 (bilinear), the
+        // lowres search its window.  Border extension, half-sample planes and lowres planes are produced only that far (rounded up to
+        // the kernels' vector widths) instead of over the whole kEncPad.
+        const int reach = cfg_.merange + 3;
+        pad_y_ = std::min(kEncPad, (reach + 1 + 15) / 16 * 16);
+        pad_c_ = std::min(kEncPad / 2, (reach / 2 + 2 + 15) / 16 * 16);
+        pad_l_ = std::min(kEncPad / 2, (cfg_.merange / 2 + 4 + 3) / 4 * 4);
     }
     ~SegmentEncoder() { free_all(); }
 
@@ -246,7 +254,7 @@ public:
             nmax = std::max(nmax, n[s]);
         }
         set_frame_counts(n, lanes);
-        const int P = kEncPad;
+        const int P = pad_y_;
         const int lw = g_.w16 / 2, lh = g_.h16 / 2;
         const size_t nmb = size_t(g_.mbw) * g_.mbh;
         const bool de = cfg_.device_entropy;
@@ -257,9 +265,15 @@ public:
             LowresBatchArgs l[kMaxBatch];
             for (int s = 0; s < lanes; ++s) {
                 Lane &L = lanes_[size_t(s)];
+                // source pictures are only read inside the coded picture: fill what lies between the picture and the coded size,
+                // lowres of the coded area only
                 b[s] = border_args(L.cur.y + ps_.oy, L.cur.u + ps_.oc, L.cur.v + ps_.oc, cfg_.w, cfg_.h);
+                b[s].x_lo[0] = b[s].y_lo[0] = 0; b[s].x_hi[0] = g_.w16; b[s].y_hi[0] = g_.h16;
+                for (int k = 1; k < 3; ++k) { b[s].x_lo[k] = b[s].y_lo[k] = 0; b[s].x_hi[k] = lw; b[s].y_hi[k] = lh; }
                 b[s].frame_stride[0] = ps_.y; b[s].frame_stride[1] = b[s].frame_stride[2] = ps_.c; b[s].n_frames = n[s];
                 l[s] = lowres_args(L.cur.y + ps_.oy, L.cur_low + ps_.ol);
+                l[s].x_lo = 0; l[s].x_hi = g_.w16 - 1; l[s].y_lo = 0; l[s].y_hi = g_.h16 - 1;
+                l[s].lx_lo = 0; l[s].lx_hi = lw; l[s].ly_lo = 0; l[s].ly_hi = lh;
                 l[s].sframe = ps_.y; l[s].dframe = ps_.l; l[s].n_frames = n[s];
             }
             if ((rc = ops_.extend_border3(b, lanes))) return rc;
@@ -527,7 +541,7 @@ private:
     }
     // Y/U/V planes at sample (0,0) of one picture whose valid area is w x h luma samples
     BorderBatchArgs border_args(uint8_t *y, uint8_t *u, uint8_t *v, int w, int h) const {
-        const int P = kEncPad, Pc = kEncPad / 2, lw = g_.w16 / 2, lh = g_.h16 / 2;
+        const int P = pad_y_, Pc = pad_c_, lw = g_.w16 / 2, lh = g_.h16 / 2;
         BorderBatchArgs b;
         b.p[0] = y; b.p[1] = u; b.p[2] = v;
         b.stride[0] = g_.sy; b.stride[1] = b.stride[2] = g_.sc;
@@ -539,7 +553,7 @@ private:
         return b;
     }
     LowresBatchArgs lowres_args(const uint8_t *y, uint8_t *low) const {
-        const int P = kEncPad, Pc = kEncPad / 2, lw = g_.w16 / 2, lh = g_.h16 / 2;
+        const int P = pad_y_, Pc = pad_l_, lw = g_.w16 / 2, lh = g_.h16 / 2;
         LowresBatchArgs l;
         l.src = y; l.dst = low; l.sstride = g_.sy; l.dstride = g_.sl;
         l.x_lo = -P; l.x_hi = g_.w16 + P - 1; l.y_lo = -P; l.y_hi = g_.h16 + P - 1;
@@ -553,6 +567,7 @@ private:
     EncGeom       g_;
     PlaneSizes    ps_;
     int           cap_ = 0, active_ = 0;
+    int           pad_y_ = kEncPad, pad_c_ = kEncPad / 2, pad_l_ = kEncPad / 2;   // padding actually produced (luma, chroma, lowres)
     int           slice_words_ = 0;
     size_t        slices_cap_ = 0;
     std::vector<Lane> lanes_;
