@@ -61,6 +61,79 @@ __global__ void __launch_bounds__(kHpThreads) hpel_kernel(const __grid_constant_
     hpel_phase_c(threadIdx.x, a, al, x0, y0, sm);
 }
 
+// The same three planes for word-aligned arguments, without shared memory: a lane owns one 4-sample column and walks down
+// kHpColRows rows with the six source rows of the vertical filter in registers (packed as in hpel_phase_b); the
+// horizontal neighbours' words and vertical sums come from the adjacent lanes by shuffle.  Lanes 0 and 31 only feed their
+// neighbours, so a warp writes 30 words (120 samples) per row.
+constexpr int kHpColRows = 16, kHpColWarps = 4, kHpColSpan = 120;
+__global__ void __launch_bounds__(32 * kHpColWarps) hpel_cols_kernel(const __grid_constant__ Batch<HpelArgs> B) {
+    const HpelArgs &a = B.a[blockIdx.z];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x = a.x_lo - 4 + kHpColSpan * blockIdx.x + 4 * lane;
+    const int y0 = a.y_lo + kHpColRows * (blockIdx.y * kHpColWarps + warp);
+    if (y0 >= a.y_hi) return;
+    // edge replication: a word outside the readable columns is the edge sample four times
+    const int      xc = min(max(x, a.cx_lo), a.cx_hi - 4);
+    const unsigned sel = x < a.cx_lo ? 0x0000u : (x >= a.cx_hi ? 0x3333u : 0x3210u);
+    const bool     ok = lane >= 1 && lane <= 30 && x < a.x_hi;
+    const uint8_t *sp = a.src + xc;
+    const int      stride = a.stride, cy_lo = a.cy_lo, cy_top = a.cy_hi - 1, y_hi = a.y_hi;
+    unsigned e[6], o[6];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const int      yy = min(max(y0 - 2 + k, cy_lo), cy_top);
+        const unsigned w = __byte_perm(__ldg(reinterpret_cast<const unsigned *>(sp + (long long)yy * stride)), 0, sel);
+        e[k] = pack_even(w);
+        o[k] = pack_odd(w);
+    }
+    long long ofs = (long long)y0 * stride + x;
+#pragma unroll
+    for (int r = 0; r < kHpColRows; ++r) {
+        const int y = y0 + r;
+        {
+            const int      yy = min(max(y + 3, cy_lo), cy_top);
+            const unsigned w = __byte_perm(__ldg(reinterpret_cast<const unsigned *>(sp + (long long)yy * stride)), 0, sel);
+            e[(r + 5) % 6] = pack_even(w);
+            o[(r + 5) % 6] = pack_odd(w);
+        }
+        const unsigned e0 = e[r % 6], e1 = e[(r + 1) % 6], e2 = e[(r + 2) % 6], e3 = e[(r + 3) % 6], e4 = e[(r + 4) % 6], e5 = e[(r + 5) % 6];
+        const unsigned o0 = o[r % 6], o1 = o[(r + 1) % 6], o2 = o[(r + 2) % 6], o3 = o[(r + 3) % 6], o4 = o[(r + 4) % 6], o5 = o[(r + 5) % 6];
+        unsigned ve = (e0 + e5) + 20u * (e2 + e3) - 5u * (e1 + e4);
+        unsigned vo = (o0 + o5) + 20u * (o2 + o3) - 5u * (o1 + o4);
+        ve += (ve & 0x8000u) << 1;
+        vo += (vo & 0x8000u) << 1;
+        // V plane
+        const unsigned be = (bias_clamp_s16x2(ve, 0x00100010u, 0x1fff1fffu) >> 5) & 0x00ff00ffu;
+        const unsigned bo = (bias_clamp_s16x2(vo, 0x00100010u, 0x1fff1fffu) >> 5) & 0x00ff00ffu;
+        const unsigned out_v = __byte_perm(be, bo, 0x6240);
+        // H plane: samples x-2 .. x+6 of row y
+        const unsigned w1 = __byte_perm(e2, o2, 0x6240);
+        const unsigned w0 = __shfl_up_sync(0xffffffffu, w1, 1), w2 = __shfl_down_sync(0xffffffffu, w1, 1);
+        const int h0 = dp4a_us(__funnelshift_r(w1, w2, 16), kTapB, dp4a_us(__funnelshift_r(w0, w1, 16), kTapA, 16));
+        const int h1 = dp4a_us(__funnelshift_r(w1, w2, 24), kTapB, dp4a_us(__funnelshift_r(w0, w1, 24), kTapA, 16));
+        const int h2 = dp4a_us(w2, kTapB, dp4a_us(w1, kTapA, 16));
+        const int h3 = dp4a_us(w2 >> 8, kTapB, dp4a_us(__funnelshift_r(w1, w2, 8), kTapA, 16));
+        const unsigned out_h = pack_sat_u8x4(h0 >> 5, h1 >> 5, h2 >> 5, h3 >> 5);
+        // C plane: the taps over the vertical sums of the same samples
+        const unsigned p01 = __byte_perm(ve, vo, 0x5410), p23 = __byte_perm(ve, vo, 0x7632);
+        const unsigned l23 = __shfl_up_sync(0xffffffffu, p23, 1);
+        const unsigned r01 = __shfl_down_sync(0xffffffffu, p01, 1), r23 = __shfl_down_sync(0xffffffffu, p23, 1);
+        const unsigned s0 = __funnelshift_r(l23, p01, 16), s1 = __funnelshift_r(p01, p23, 16), s2 = __funnelshift_r(p23, r01, 16),
+                       s3 = __funnelshift_r(r01, r23, 16);
+        const int q0 = dp2a_ss(p23, kTapB, dp2a_ss(p01, kTapA, dp2a_ss(l23, kTapA, 512, false), true), false);
+        const int q1 = dp2a_ss(s2, kTapB, dp2a_ss(s1, kTapA, dp2a_ss(s0, kTapA, 512, false), true), false);
+        const int q2 = dp2a_ss(r01, kTapB, dp2a_ss(p23, kTapA, dp2a_ss(p01, kTapA, 512, false), true), false);
+        const int q3 = dp2a_ss(s3, kTapB, dp2a_ss(s2, kTapA, dp2a_ss(s1, kTapA, 512, false), true), false);
+        const unsigned out_c = pack_sat_u8x4(q0 >> 10, q1 >> 10, q2 >> 10, q3 >> 10);
+        if (ok && y < y_hi) {
+            *reinterpret_cast<unsigned *>(a.dv + ofs) = out_v;
+            *reinterpret_cast<unsigned *>(a.dh + ofs) = out_h;
+            *reinterpret_cast<unsigned *>(a.dc + ofs) = out_c;
+        }
+        ofs += stride;
+    }
+}
+
 __global__ void __launch_bounds__(128) transform8x8_kernel(const __grid_constant__ Transform8Args a) {
     const int b = blockIdx.x * 128 + threadIdx.x;
     if (b < a.bw * a.bh) transform8x8_block(a, b % a.bw, b / a.bw);
@@ -353,7 +426,15 @@ int launch_hpel(const HpelArgs *a, int count, cudaStream_t st) {
     if (a[0].x_hi <= a[0].x_lo || a[0].y_hi <= a[0].y_lo) return GVC_OK;
     Batch<HpelArgs> B;
     fill_batch(B, a, count);
-    hpel_kernel<<<dim3((a[0].x_hi - a[0].x_lo + kHpTileW - 1) / kHpTileW, (a[0].y_hi - a[0].y_lo + kHpTileH - 1) / kHpTileH, count), kHpThreads, 0, st>>>(B);
+    bool cols = a[0].cx_hi - a[0].cx_lo >= 4;
+    for (int i = 0; i < count; ++i) cols = cols && hpel_aligned(a[i]);
+    if (cols) {
+        const int band = kHpColRows * kHpColWarps;
+        hpel_cols_kernel<<<dim3((a[0].x_hi - a[0].x_lo + kHpColSpan - 1) / kHpColSpan, (a[0].y_hi - a[0].y_lo + band - 1) / band, count),
+                           32 * kHpColWarps, 0, st>>>(B);
+    } else {
+        hpel_kernel<<<dim3((a[0].x_hi - a[0].x_lo + kHpTileW - 1) / kHpTileW, (a[0].y_hi - a[0].y_lo + kHpTileH - 1) / kHpTileH, count), kHpThreads, 0, st>>>(B);
+    }
     GVC_CUDA(cudaGetLastError());
     return GVC_OK;
 }
