@@ -234,17 +234,24 @@ GVC_HD void lowres_px(const uint8_t *src, int sstride, int x_lo, int x_hi, int y
 // clamping; otherwise sample by sample through lowres_px (same results).
 GVC_HDH bool lowres_aligned(const LowresBatchArgs &a) {
     return (((unsigned long long)a.src | (unsigned long long)a.dst | (unsigned long long)(unsigned)a.sstride | (unsigned long long)(unsigned)a.dstride |
-             a.sframe | a.dframe | (unsigned long long)(unsigned)a.lx_lo) & 3) == 0;
+             a.sframe | a.dframe | (unsigned long long)(unsigned)a.lx_lo | (unsigned long long)(unsigned)a.x_lo |
+             (unsigned long long)(unsigned)(a.x_hi + 1)) & 3) == 0;
 }
 GVC_HD void lowres_quad(const LowresBatchArgs &a, bool al, const uint8_t *src, uint8_t *dst, int lx, int ly) {
-    if (al && lx + 4 <= a.lx_hi && 2 * lx >= a.x_lo && 2 * lx + 7 <= a.x_hi) {
-        const uint8_t *r0 = src + (iclamp(2 * ly, a.y_lo, a.y_hi) * a.sstride + 2 * lx);
-        const uint8_t *r1 = src + (iclamp(2 * ly + 1, a.y_lo, a.y_hi) * a.sstride + 2 * lx);
-        const unsigned t0 = *reinterpret_cast<const unsigned *>(r0), t1 = *reinterpret_cast<const unsigned *>(r0 + 4);
-        const unsigned b0 = *reinterpret_cast<const unsigned *>(r1), b1 = *reinterpret_cast<const unsigned *>(r1 + 4);
+    // eight source columns 2lx .. 2lx+7: all readable, or all left of the readable columns (= the first one eight times), or
+    // all right of them (= the last one)
+    const int  sx = 2 * lx;
+    const bool in = sx >= a.x_lo && sx + 7 <= a.x_hi, left = sx + 7 < a.x_lo, right = sx > a.x_hi;
+    if (al && lx + 4 <= a.lx_hi && (in || left || right)) {
+        const int      xa = in ? sx : (left ? a.x_lo : a.x_hi - 3), xb = in ? sx + 4 : xa;
+        const unsigned sel = in ? 0x3210u : (left ? 0x0000u : 0x3333u);
+        const uint8_t *r0 = src + (long long)iclamp(2 * ly, a.y_lo, a.y_hi) * a.sstride;
+        const uint8_t *r1 = src + (long long)iclamp(2 * ly + 1, a.y_lo, a.y_hi) * a.sstride;
+        const unsigned t0 = byte_sel(*reinterpret_cast<const unsigned *>(r0 + xa), 0, sel), t1 = byte_sel(*reinterpret_cast<const unsigned *>(r0 + xb), 0, sel);
+        const unsigned b0 = byte_sel(*reinterpret_cast<const unsigned *>(r1 + xa), 0, sel), b1 = byte_sel(*reinterpret_cast<const unsigned *>(r1 + xb), 0, sel);
         const unsigned even = avg_u8x4(byte_sel(t0, t1, 0x6420), byte_sel(b0, b1, 0x6420));
         const unsigned odd  = avg_u8x4(byte_sel(t0, t1, 0x7531), byte_sel(b0, b1, 0x7531));
-        *reinterpret_cast<unsigned *>(dst + (ly * a.dstride + lx)) = avg_u8x4(even, odd);
+        *reinterpret_cast<unsigned *>(dst + ((long long)ly * a.dstride + lx)) = avg_u8x4(even, odd);
         return;
     }
     for (int i = 0; i < 4; ++i)

@@ -20,6 +20,14 @@ __global__ void __launch_bounds__(32 * kEntWarps) ent_mb_kernel(const __grid_con
     if (lane == 0) { sm.kind = 0; sm.overflow = 0; }
     __syncwarp();
     const int bits = ent_lane_encode(lane, a, mb, sm);
+    if (!__any_sync(0xffffffffu, bits != 0)) {       // P_Skip: nothing to lay out
+        __syncwarp();
+        if (lane == 0) {
+            a.mb_bits[mb] = 0;
+            a.mb_kind[mb] = (uint8_t)(sm.kind | (sm.overflow ? 128 : 0));
+        }
+        return;
+    }
     // bit offsets in coding order: thread p takes the length of the lane that sits at position p, scans, hands it back
     int v = __shfl_sync(0xffffffffu, bits, ent_lane_at(lane));
     const int mine = v;
