@@ -701,6 +701,7 @@ struct EncMbSmem {               // per warp
     int      dclev[8];           // quantised chroma DC levels, Cb[0..3] Cr[4..7]
     unsigned mask;               // nzmask under construction
     int      flags[32];          // [30], [31]: compact mask and first packed block (pack_reserve)
+    unsigned cpred[32];          // chroma prediction, one 4-sample row word per lane: [plane][row 0..7][half]
 };
 struct EncLane {                 // what a lane carries in registers across the phases
     int      d[16];              // residual -> coefficients (raster)
@@ -732,24 +733,40 @@ GVC_HD void store_block_nnz(int lane, int mx, int my, int mbw, uint8_t *nnz_y, u
     if (lane < 16) nnz_y[(4 * my + (lane >> 2)) * (4 * mbw) + 4 * mx + (lane & 3)] = (uint8_t)cnt;
     else { const int b = (lane - 16) & 3; (lane < 20 ? nnz_u : nnz_v)[(2 * my + (b >> 1)) * (2 * mbw) + 2 * mx + (b & 1)] = (uint8_t)cnt; }
 }
+// Phase 0: chroma prediction (H.264 8.4.2.2.2, x264 mc_chroma) with the whole warp: the two 8x8 planes are 32 row words of
+// four samples, one per lane.  Two samples per register: the four weights sum to 64, so a weighted sum stays below 2^16 and
+// the halves never meet.
+GVC_HD void enc_mb_p0(int lane, const EncMbArgs &a, int mx, int my, EncMbSmem &sm) {
+    const int row = (lane >> 1) & 7, half = lane & 1, k = (row >> 2) * 2 + half;      // chroma block k lies under partition k
+    const MbMotion &mo = a.motion[my * a.mbw + mx];
+    const int mvx = mo.mv[k][0], mvy = mo.mv[k][1];
+    const unsigned dx = (unsigned)(mvx & 7), dy = (unsigned)(mvy & 7);
+    const unsigned cA = (8 - dx) * (8 - dy), cB = dx * (8 - dy), cC = (8 - dx) * dy, cD = dx * dy;
+    const uint8_t *s = (lane < 16 ? a.ref.u : a.ref.v) + ((long long)(8 * my + row + (mvy >> 3)) * a.sc + 8 * mx + 4 * half + (mvx >> 3));
+    unsigned t0, t1, b0, b1;
+    ld_u64_any(s, t0, t1);
+    ld_u64_any(s + a.sc, b0, b1);
+    const unsigned tr = funnel_r(t0, t1, 8), br = funnel_r(b0, b1, 8);                 // the samples one to the right
+    const unsigned e = cA * pack_even(t0) + cB * pack_even(tr) + cC * pack_even(b0) + cD * pack_even(br) + 0x00200020u;
+    const unsigned o = cA * pack_odd(t0) + cB * pack_odd(tr) + cC * pack_odd(b0) + cD * pack_odd(br) + 0x00200020u;
+    sm.cpred[lane] = byte_sel((e >> 6) & 0x00ff00ffu, (o >> 6) & 0x00ff00ffu, 0x6240);
+    if (lane == 0) sm.mask = 0;
+}
 // Phase 1: prediction, residual, forward 4x4 transform of every block; chroma DCs go to the shared record.
 GVC_HD void enc_mb_p1(int lane, const EncMbArgs &a, bool al, int mx, int my, EncMbSmem &sm, EncLane &L) {
-    if (lane == 0) sm.mask = 0;
     if (lane >= 24) return;
-    const MbMotion &mo = a.motion[my * a.mbw + mx];
     int x, y, k;
     enc_lane_block(lane, mx, my, x, y, k);
-    const int mvx = mo.mv[k][0], mvy = mo.mv[k][1];
     if (lane < 16) {
-        const LumaSrc s = mc_luma_src(a.ref, a.sy, x, y, mvx, mvy);
+        const MbMotion &mo = a.motion[my * a.mbw + mx];
+        const LumaSrc s = mc_luma_src(a.ref, a.sy, x, y, mo.mv[k][0], mo.mv[k][1]);
         for (int j = 0; j < 4; ++j) {
             L.pred[j] = ld_u32_any(s.s1 + j * a.sy);
             if (s.s2) L.pred[j] = avg_u8x4(L.pred[j], ld_u32_any(s.s2 + j * a.sy));
         }
     } else {
-        int pr[16];
-        mc_chroma_4x4(lane < 20 ? a.ref.u : a.ref.v, a.sc, x, y, mvx, mvy, pr);
-        for (int j = 0; j < 4; ++j) L.pred[j] = (unsigned)pr[4 * j] | ((unsigned)pr[4 * j + 1] << 8) | ((unsigned)pr[4 * j + 2] << 16) | ((unsigned)pr[4 * j + 3] << 24);
+        const int b = (lane - 16) & 3, base = (lane < 20 ? 0 : 16) + 8 * (b >> 1) + (b & 1);   // rows 4(b>>1) .., half b&1 of phase 0's words
+        for (int j = 0; j < 4; ++j) L.pred[j] = sm.cpred[base + 2 * j];
     }
     GVC_RECONVERGE(0x00ffffffu);
     const int st = lane < 16 ? a.sy : a.sc;

@@ -300,6 +300,8 @@ __global__ void __launch_bounds__(32 * kMbWarps) encode_inter_kernel(const __gri
     EncMbSmem &sm = sms[warp];
     const bool al = enc_mb_aligned(a);
     EncLane L;
+    enc_mb_p0(lane, a, mx, my, sm);
+    __syncwarp();
     enc_mb_p1(lane, a, al, mx, my, sm, L);
     __syncwarp();
     if (__any_sync(0xffffffffu, enc_mb_any_level(lane, a, sm, L))) enc_mb_p2(lane, a, al, mx, my, sm, L);

@@ -128,6 +128,7 @@ void emu_run_encode_inter(const EncMbArgs &a) {
             const bool al = enc_mb_aligned(a);
             EncLane L[32];
             memset(L, 0xAB, sizeof(L));
+            for (int l = 0; l < 32; ++l) enc_mb_p0(l, a, mx, my, sm);
             for (int l = 0; l < 32; ++l) enc_mb_p1(l, a, al, mx, my, sm, L[l]);
             bool any = false;
             for (int l = 0; l < 32; ++l) any = enc_mb_any_level(l, a, sm, L[l]) || any;
