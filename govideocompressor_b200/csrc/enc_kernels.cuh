@@ -52,7 +52,9 @@ GVC_HD unsigned sad_u8x4(unsigned a, unsigned b, unsigned acc) {   // acc + sum 
     for (int i = 0; i < 4; ++i) { const int d = (int)((a >> (8 * i)) & 255) - (int)((b >> (8 * i)) & 255); acc += d < 0 ? -d : d; }
     return acc;
 #else
-    return __vsadu4(a, b) + acc;   // VABSDIFF4.U8.ACC
+    unsigned d;                    // VABSDIFF4.U8.ACC with the accumulator as its third operand: written as `__vsadu4(a, b) + acc` the
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(acc));   // compiler sums pairs with an extra IADD3
+    return d;
 #endif
 }
 
