@@ -422,28 +422,6 @@ GVC_HD LumaSrc mc_luma_src(const RefPlanes &r, int stride, int x, int y, int mvx
     o.s2 = (q & 5) ? pl[(kQpelRef1 >> (2 * q)) & 3] + off + (fx == 3 ? 1 : 0) : nullptr;
     return o;
 }
-// 4x4 luma prediction block at (x,y) with vector (mvx,mvy); out[16] raster
-GVC_HD void mc_luma_4x4(const RefPlanes &r, int stride, int x, int y, int mvx, int mvy, int out[16]) {
-    const LumaSrc s = mc_luma_src(r, stride, x, y, mvx, mvy);
-    for (int j = 0; j < 4; ++j) {
-        const unsigned a = ld_u32_any(s.s1 + (long long)j * stride);
-        if (s.s2) {
-            const unsigned b = ld_u32_any(s.s2 + (long long)j * stride);
-            for (int i = 0; i < 4; ++i) out[j * 4 + i] = (int)(((a >> (8 * i)) & 255) + ((b >> (8 * i)) & 255) + 1) >> 1;
-        } else {
-            for (int i = 0; i < 4; ++i) out[j * 4 + i] = (int)((a >> (8 * i)) & 255);
-        }
-    }
-}
-// 4x4 chroma prediction block at chroma position (x,y), luma vector (mvx,mvy) in quarter luma samples
-GVC_HD void mc_chroma_4x4(const uint8_t *src, int stride, int x, int y, int mvx, int mvy, int out[16]) {
-    const int dx = mvx & 7, dy = mvy & 7;
-    const int cA = (8 - dx) * (8 - dy), cB = dx * (8 - dy), cC = (8 - dx) * dy, cD = dx * dy;
-    const uint8_t *s = src + (long long)(y + (mvy >> 3)) * stride + x + (mvx >> 3);
-    for (int j = 0; j < 4; ++j, s += stride)
-        for (int i = 0; i < 4; ++i) out[j * 4 + i] = (cA * s[i] + cB * s[i + 1] + cC * s[stride + i] + cD * s[stride + i + 1] + 32) >> 6;
-}
-
 // ------------------------------------------------------------------ 4x4 transforms --------------
 GVC_HD void dct4x4(int d[16]) {   // x264 sub4x4_dct butterflies, rows then columns, in place
     for (int y = 0; y < 4; ++y) {
