@@ -265,35 +265,36 @@ GVC_HD int ent_lane_encode(int lane, const EntropyArgs &a, int mb, EntSmem &sm) 
             bo_ue(bw, etab::kCbpInterCode[cbp]);   // coded_block_pattern me(v)
             if (cbp) bo_se(bw, 0);                 // mb_qp_delta
         }
-    } else if (lane == 26) {
-        if (i16) {
-            const int nC = ent_nc(a.nnz_y, 4 * a.mbw, 4 * mx, 4 * my);
-            if (nz & (1u << 26)) ent_residual(bw, co + 16 * popcount32(cm & ((1u << 25) - 1u)), 16, nC);
-            else ent_empty_block(bw, nC);
-        }
-    } else if (lane < 16) {
-        if (cbp & (1 << (lane >> 2))) {
-            const int r = ((lane & 8) | ((lane & 4) >> 1) | ((lane & 2) << 1) | (lane & 1));    // blkIdx (8x8-wise Z scan) -> raster 4x4 block
-            const int bx = 4 * mx + (r & 3), by = 4 * my + (r >> 2), nC = ent_nc(a.nnz_y, 4 * a.mbw, bx, by);
-            if (!(nz & (1u << r))) ent_empty_block(bw, nC);
-            else {
-                const int16_t *l = co + 16 * popcount32(cm & ((1u << r) - 1u));
-                if (i16) ent_residual(bw, l + 1, 15, nC);
-                else     ent_residual(bw, l, 16, nC);
-            }
-        }
-    } else if (lane < 24) {
-        if (cbp & 0x20) {
-            const int p = (lane - 16) >> 2, b = (lane - 16) & 3;
-            const int bx = 2 * mx + (b & 1), by = 2 * my + (b >> 1), nC = ent_nc(a.nnz_c[p], 2 * a.mbw, bx, by);
-            if (nz & (1u << lane)) ent_residual(bw, co + 16 * popcount32(cm & ((1u << lane) - 1u)) + 1, 15, nC);
-            else ent_empty_block(bw, nC);
-        }
     } else {
-        if (cbp & 0x30) {
+        // Residual lanes.  Which block, how many coefficients and which nC differ per lane; the coder itself is called from ONE
+        // place, so luma, chroma AC and DC lanes run it together instead of one group after the other.
+        const int16_t *l = co;
+        const uint8_t *map = a.nnz_y;
+        int  n = 16, pitch = 4 * a.mbw, bx = 0, by = 0, bit = 0;
+        bool coded = false, dc = false;
+        if (lane == 26) {                                   // Intra16x16 luma DC
+            coded = i16; bit = 26; bx = 4 * mx; by = 4 * my;
+            l = co + 16 * popcount32(cm & ((1u << 25) - 1u));
+        } else if (lane < 16) {
+            const int r = ((lane & 8) | ((lane & 4) >> 1) | ((lane & 2) << 1) | (lane & 1));    // blkIdx (8x8-wise Z scan) -> raster 4x4 block
+            coded = (cbp & (1 << (lane >> 2))) != 0; bit = r; bx = 4 * mx + (r & 3); by = 4 * my + (r >> 2);
+            l = co + 16 * popcount32(cm & ((1u << r) - 1u)) + (i16 ? 1 : 0);
+            n = i16 ? 15 : 16;
+        } else if (lane < 24) {
+            const int p = (lane - 16) >> 2, k = (lane - 16) & 3;
+            coded = (cbp & 0x20) != 0; bit = lane; map = a.nnz_c[p]; pitch = 2 * a.mbw; bx = 2 * mx + (k & 1); by = 2 * my + (k >> 1);
+            l = co + 16 * popcount32(cm & ((1u << lane) - 1u)) + 1;
+            n = 15;
+        } else {                                            // lanes 24, 25: chroma DC
             const int p = lane - 24;
-            if (nz & (1u << (24 + p))) ent_residual(bw, co + 16 * popcount32(cm & ((1u << 24) - 1u)) + 4 * p, 4, -1);
-            else ent_empty_block(bw, -1);
+            coded = (cbp & 0x30) != 0; bit = 24 + p; dc = true;
+            l = co + 16 * popcount32(cm & ((1u << 24) - 1u)) + 4 * p;
+            n = 4;
+        }
+        if (coded) {
+            const int nC = dc ? -1 : ent_nc(map, pitch, bx, by);
+            if (nz & (1u << bit)) ent_residual(bw, l, n, nC);
+            else ent_empty_block(bw, nC);
         }
     }
     const int bits = bo_finish(bw);
