@@ -66,6 +66,15 @@ def download_and_convert(path, args, convert, fetch, store, workdir):
         os.chdir(cwd)
 
 
+def job_buffer_bytes():
+    """client.go:43 reads the job into 100 bytes, which truncates long argument strings; GVC_JOB_BUF lifts that (opt-in,
+    SURVEY.md 8f.4 — the Go-side change is sketched in INTEGRATION.md)."""
+    try:
+        return max(100, int(os.environ.get("GVC_JOB_BUF", "100")))
+    except ValueError:
+        return 100
+
+
 def serve_one_job(server_addr, convert, fetch, store, workdir, timeout=10.0):
     """One iteration of client.go:37-80.  Returns the status sent, or None when no job was received."""
     try:
@@ -74,7 +83,7 @@ def serve_one_job(server_addr, convert, fetch, store, workdir, timeout=10.0):
         return None
     try:
         try:
-            data = conn.recv(100)                                  # client.go:43-45
+            data = conn.recv(job_buffer_bytes())                   # client.go:43-45
         except OSError:
             return None                                            # client.go:46-50: a failed read ends this round of the loop
         if not data:

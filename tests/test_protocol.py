@@ -91,6 +91,71 @@ def test_job_string_longer_than_100_bytes_is_truncated_like_the_reference():
     server.join(5)
 
 
+def flaky_convert(calls, fail_first=()):
+    """Fails a piece (no output file) the first time it is seen, succeeds afterwards."""
+    seen = set()
+
+    def convert(path, args):
+        calls.append(path)
+        piece = path.split(".")[0]
+        with open("c" + path + ".log", "w") as f:
+            f.write("log")
+        if piece in fail_first and piece not in seen:
+            seen.add(piece)
+            return 0
+        with open(path, "rb") as src, open("c" + path, "wb") as dst:
+            dst.write(b"ENC:" + src.read())
+        return 0
+    return convert
+
+
+def test_opt_in_requeue_hands_a_failed_piece_out_again(tmp_path):
+    """SURVEY 8f.4, behind a flag: the reference drops a failed piece (previous test); with requeue=1 it comes back once."""
+    src, dst, work = (os.path.join(tmp_path, x) for x in ("www", "ftp", "work"))
+    os.makedirs(work)
+    make_pieces(src, "d", 3)
+    server = FakeServer("d", 3, "264", requeue=1)
+    calls = []
+    done = worker.run_worker(server.addr, flaky_convert(calls, fail_first=("1",)), worker.local_fetch(src), worker.local_store(dst), work)
+    assert server.join(5)                                         # nothing remains
+    assert done == ["success;2", "fail;1", "success;0", "success;1"]
+    assert calls == ["2.mp4", "1.mp4", "0.mp4", "1.mp4"] and server.failed == []
+    assert open(os.path.join(dst, "d", "1.mp4"), "rb").read() == b"ENC:piece1"
+
+
+def test_opt_in_requeue_gives_up_after_its_limit_and_covers_lost_reports(tmp_path):
+    src, dst, work = (os.path.join(tmp_path, x) for x in ("www", "ftp", "work"))
+    os.makedirs(work)
+    make_pieces(src, "d", 2)
+    server = FakeServer("d", 2, "264", requeue=2)
+    done = worker.run_worker(server.addr, stub_convert([], fail_ids=("0",)), worker.local_fetch(src), worker.local_store(dst), work)
+    server.join(5)
+    assert done == ["success;1", "fail;0", "fail;0", "fail;0"]      # first hand-out + two more, then it is reported as failed
+    assert server.failed == [["fail", "0"]] and list(server.remain) == [0]
+    # a worker that takes a job and dies without reporting: the piece is handed out again instead of being lost
+    import socket
+    make_pieces(src, "e", 1)
+    server = FakeServer("e", 1, "264", requeue=1)
+    c = socket.create_connection(server.addr)
+    assert c.recv(100).decode() == "e;0;-threads 4 -vcodec libx264"
+    c.close()
+    done = worker.run_worker(server.addr, stub_convert([]), worker.local_fetch(src), worker.local_store(dst), work)
+    assert server.join(5) and done == ["success;0"]
+
+
+def test_opt_in_job_buffer_carries_a_long_argument_string(tmp_path, monkeypatch):
+    src, dst, work = (os.path.join(tmp_path, x) for x in ("www", "ftp", "work"))
+    os.makedirs(work)
+    make_pieces(src, "d", 1)
+    long_args = "-threads 4 -vcodec libx264 " + "-an " * 30
+    monkeypatch.setenv("GVC_JOB_BUF", "4096")
+    server = FakeServer("d", 1, long_args, buf=4096)
+    calls = []
+    done = worker.run_worker(server.addr, stub_convert(calls), worker.local_fetch(src), worker.local_store(dst), work)
+    assert server.join(5) and done == ["success;0"]
+    assert calls == [("0.mp4", long_args)]                        # nothing was cut off (client.go:43 would have kept 100 bytes)
+
+
 def test_the_documented_argument_grammar_is_the_parsers_grammar():
     """INTEGRATION.md's option table is the contract a maintainer of the Go side reads (the job string of server.go:179 is free
     form).  Every example in it must parse (together with the mandatory codec option), every listed option name too, and
