@@ -6,6 +6,8 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#include <thread>
 #include <vector>
 
 namespace gvc {
@@ -156,11 +158,14 @@ public:
         if (*reinterpret_cast<int *>(static_cast<char *>(st) + 8) != stream_ || !codecpar) { err = "unexpected AVStream layout"; return false; }
         cctx_ = a.avcodec_alloc_context3(dec);
         if (!cctx_ || a.avcodec_parameters_to_context(cctx_, codecpar) < 0) { err = "cannot open the video decoder"; return false; }
-        // host decode is what bounds a worker once the kernels take milliseconds: let libavcodec use the cores the spawned ffmpeg would
-        // (frame threads; GVC_DECODE_THREADS overrides, 1 = the single-threaded decoder)
+        // host decode is what bounds a worker once the kernels take milliseconds: frame threads, but not one per core as the
+        // spawned ffmpeg's decoder would take -- a piece is a few dozen pictures, and every frame thread adds a picture of
+        // start-up latency (measured on 38-picture 1080p pieces, 16 cores: 747 / 1,564 / 1,543 / 1,229 pictures/s with 1 / 4 / 8 /
+        // 16 threads, tools/exp_decode_threads.py).  GVC_DECODE_THREADS overrides (1 = single-threaded, 0 = libavcodec's choice).
         if (a.av_opt_set_int) {
             const char *env = getenv("GVC_DECODE_THREADS");
-            const long  n = env ? atol(env) : 0;      // 0 = libavcodec picks one per core
+            const long  cores = long(std::thread::hardware_concurrency());
+            const long  n = env ? atol(env) : std::max(1L, std::min(8L, cores));
             a.av_opt_set_int(cctx_, "threads", n < 0 ? 0 : n, 0);
         }
         if (a.avcodec_open2(cctx_, dec, nullptr) < 0) { err = "cannot open the video decoder"; return false; }
