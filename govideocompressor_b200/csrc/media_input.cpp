@@ -7,6 +7,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <algorithm>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -135,7 +138,15 @@ class LavSource : public FrameSource {
 public:
     ~LavSource() override {
         LavApi &a = lav();
-        if (frame_) a.av_frame_free(&frame_);
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            stop_ = true;
+        }
+        cv_job_.notify_all();
+        for (auto &t : copiers_) t.join();
+        for (void *&f : ring_)
+            if (f) a.av_frame_free(&f);
+        frame_ = nullptr;
         if (pkt_) a.av_packet_free(&pkt_);
         if (cctx_) a.avcodec_free_context(&cctx_);
         if (fmt_) a.avformat_close_input(&fmt_);
@@ -144,7 +155,12 @@ public:
         LavApi &a = lav();
         if (!a.ok) { err = a.where; return false; }
         if (a.avformat_open_input(&fmt_, path.c_str(), nullptr, nullptr) < 0) { fmt_ = nullptr; err = "cannot open / unknown container"; return false; }
-        if (a.avformat_find_stream_info(fmt_, nullptr) < 0) { err = "no stream information"; return false; }
+        // AVFormatContext: av_class, iformat, ...; AVInputFormat: name, ...  An MP4 / MOV header already carries what this reader
+        // needs (stream types, decoder configuration, frame rate); avformat_find_stream_info would decode the first pictures on
+        // one thread just to learn the pixel format, which the real decoder reports anyway -- a quarter of a short piece's time.
+        const char *const *ifmt = *reinterpret_cast<const char *const **>(static_cast<char *>(fmt_) + 8);
+        const bool mov = ifmt && *ifmt && strncmp(*ifmt, "mov,", 4) == 0;
+        if (!mov && a.avformat_find_stream_info(fmt_, nullptr) < 0) { err = "no stream information"; return false; }
         const void *dec = nullptr;
         stream_ = a.av_find_best_stream(fmt_, /*AVMEDIA_TYPE_VIDEO*/ 0, -1, -1, &dec, 0);
         if (stream_ < 0 || !dec) { err = "no decodable video stream"; return false; }
@@ -190,8 +206,9 @@ public:
         const AvRational r = a.av_guess_frame_rate(fmt_, st, nullptr);
         if (r.num > 0 && r.den > 0) { fps_num = r.num; fps_den = r.den; }
         pkt_ = a.av_packet_alloc();
-        frame_ = a.av_frame_alloc();
-        if (!pkt_ || !frame_) { err = "out of memory"; return false; }
+        for (void *&f : ring_) f = a.av_frame_alloc();
+        frame_ = ring_[0];
+        if (!pkt_ || std::find(ring_, ring_ + kRing, nullptr) != ring_ + kRing) { err = "out of memory"; return false; }
         format_name = "lavf";
         // decode the first picture now: the caller needs the size before it reads
         if (!pump(err)) return false;
@@ -204,11 +221,12 @@ public:
         while (n < max_frames) {
             if (!have_ && !pump(err)) return -1;
             if (!have_) break;
-            copy_out(dst + fb * n);
-            lav().av_frame_unref(frame_);
+            hand_to_copier(dst + fb * n);                     // the picture's 3 MB are moved by a helper while the decoder is fed
             have_ = false;
             ++n;
         }
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_done_.wait(lk, [&] { return pending_ == 0; });      // the caller reads dst next
         return n;
     }
 private:
@@ -240,15 +258,58 @@ private:
             if (sr < 0) { err = "the decoder rejected a packet"; return false; }
         }
     }
-    void copy_out(uint8_t *dst) const {
-        const AvFrameHead *fh = static_cast<const AvFrameHead *>(frame_);
+    // Decoded pictures leave through a ring of AVFrames: the reading thread keeps pumping packets into the decoder while
+    // kCopiers helpers move finished pictures into the caller's (pinned) buffer -- at 1080p the row-wise copy of a picture
+    // costs about as much host time as the frame-threaded decoder needs to produce it.
+    static constexpr int kRing = 6, kCopiers = 2;
+    struct CopyJob { int slot; uint8_t *dst; };
+    void hand_to_copier(uint8_t *dst) {
+        std::unique_lock<std::mutex> lk(mu_);
+        if (copiers_.empty())
+            for (int i = 0; i < kCopiers; ++i) copiers_.emplace_back([this] { copier(); });
+        int slot = 0;
+        while (ring_[slot] != frame_) ++slot;
+        busy_[slot] = true;
+        ++pending_;
+        jobs_.push_back(CopyJob{slot, dst});
+        cv_job_.notify_one();
+        // next picture goes into a free frame
+        cv_done_.wait(lk, [&] { return std::find(busy_, busy_ + kRing, false) != busy_ + kRing; });
+        frame_ = ring_[std::find(busy_, busy_ + kRing, false) - busy_];
+    }
+    void copier() {
+        std::unique_lock<std::mutex> lk(mu_);
+        for (;;) {
+            cv_job_.wait(lk, [&] { return stop_ || !jobs_.empty(); });
+            if (jobs_.empty()) return;                         // stop_
+            const CopyJob j = jobs_.front();
+            jobs_.pop_front();
+            lk.unlock();
+            copy_out(ring_[j.slot], j.dst);
+            lav().av_frame_unref(ring_[j.slot]);
+            lk.lock();
+            busy_[j.slot] = false;
+            --pending_;
+            cv_done_.notify_all();
+        }
+    }
+    void copy_out(const void *frame, uint8_t *dst) const {
+        const AvFrameHead *fh = static_cast<const AvFrameHead *>(frame);
         for (int k = 0; k < 3; ++k) {
             const int pw = k ? (w + 1) / 2 : w, ph = k ? (h + 1) / 2 : h;
             for (int y = 0; y < ph; ++y) memcpy(dst + size_t(y) * pw, fh->data[k] + size_t(y) * fh->linesize[k], pw);
             dst += size_t(pw) * ph;
         }
     }
-    void *fmt_ = nullptr, *cctx_ = nullptr, *pkt_ = nullptr, *frame_ = nullptr;
+    void *fmt_ = nullptr, *cctx_ = nullptr, *pkt_ = nullptr, *frame_ = nullptr;      // frame_: the ring entry the decoder fills next
+    void *ring_[kRing] = {};
+    bool  busy_[kRing] = {};
+    std::mutex mu_;
+    std::condition_variable cv_job_, cv_done_;
+    std::deque<CopyJob> jobs_;
+    std::vector<std::thread> copiers_;
+    int   pending_ = 0;
+    bool  stop_ = false;
     int   stream_ = -1, astream_ = -1;
     bool  have_ = false, flushed_ = false;
 };
