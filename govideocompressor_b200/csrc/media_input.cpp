@@ -219,14 +219,13 @@ public:
         const size_t fb = size_t(w) * h + 2 * size_t((w + 1) / 2) * ((h + 1) / 2);
         int n = 0;
         while (n < max_frames) {
-            if (!have_ && !pump(err)) return -1;
+            if (!have_ && !pump(err)) { drain(); return -1; }
             if (!have_) break;
             hand_to_copier(dst + fb * n);                     // the picture's 3 MB are moved by a helper while the decoder is fed
             have_ = false;
             ++n;
         }
-        std::unique_lock<std::mutex> lk(mu_);
-        cv_done_.wait(lk, [&] { return pending_ == 0; });      // the caller reads dst next
+        drain();                                               // the caller reads dst next
         return n;
     }
 private:
@@ -276,6 +275,10 @@ private:
         // next picture goes into a free frame
         cv_done_.wait(lk, [&] { return std::find(busy_, busy_ + kRing, false) != busy_ + kRing; });
         frame_ = ring_[std::find(busy_, busy_ + kRing, false) - busy_];
+    }
+    void drain() {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_done_.wait(lk, [&] { return pending_ == 0; });
     }
     void copier() {
         std::unique_lock<std::mutex> lk(mu_);
