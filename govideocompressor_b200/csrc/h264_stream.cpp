@@ -23,8 +23,21 @@ void append_nal(std::vector<uint8_t> &out, int nal_ref_idc, int nal_unit_type, c
     std::vector<uint8_t> nal;
     nal.reserve(rbsp.size() + rbsp.size() / 64 + 8);
     nal.push_back(uint8_t((nal_ref_idc << 5) | nal_unit_type));
-    int zeros = 0;
-    for (uint8_t b : rbsp) {
+    // emulation prevention (7.4.1): a byte <= 3 after two zero bytes gets a 0x03 in front.  Zero bytes are rare in entropy-coded
+    // data, so the stretches between them are appended whole and only the bytes after a zero go through the state machine.
+    const uint8_t *p = rbsp.data();
+    const size_t   n = rbsp.size();
+    size_t i = 0;
+    int    zeros = 0;
+    while (i < n) {
+        if (zeros == 0) {
+            const void *z = memchr(p + i, 0, n - i);
+            const size_t j = z ? size_t(static_cast<const uint8_t *>(z) - p) : n;
+            nal.insert(nal.end(), p + i, p + j);
+            i = j;
+            if (i == n) break;
+        }
+        const uint8_t b = p[i++];
         if (zeros >= 2 && b <= 3) { nal.push_back(3); zeros = 0; }   // emulation_prevention_three_byte
         nal.push_back(b);
         zeros = b == 0 ? zeros + 1 : 0;

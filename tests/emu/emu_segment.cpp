@@ -305,3 +305,12 @@ extern "C" int emu_parse_args(const char *args, int *out /* dst_w, dst_h, crf, s
     out[8] = o.drop_audio; out[9] = int(o.bitrate);
     return rc;
 }
+
+// the product's NAL wrapper (h264_stream.cpp append_nal) on an arbitrary payload: returns the bytes written (Annex B framing)
+extern "C" long emu_append_nal(const uint8_t *rbsp, long n, int ref_idc, int type, uint8_t *out, long cap) {
+    std::vector<uint8_t> v, in(rbsp, rbsp + n);
+    gvc::append_nal(v, ref_idc, type, in, true);
+    if (long(v.size()) > cap) return -1;
+    memcpy(out, v.data(), v.size());
+    return long(v.size());
+}

@@ -147,3 +147,14 @@ def parse_args(args):
     rc = load().emu_parse_args(args.encode(), out, err, 256)
     keys = ("dst_w", "dst_h", "crf", "scale_algo", "gop", "merange", "fps_num", "fps_den", "drop_audio", "bitrate")
     return rc, dict(zip(keys, list(out))), err.value.decode()
+
+
+def append_nal(rbsp, ref_idc=3, nal_type=5):
+    """The product's NAL wrapper on an arbitrary payload (Annex B start code + header byte + escaped payload)."""
+    lib = load()
+    lib.emu_append_nal.restype = ctypes.c_long
+    lib.emu_append_nal.argtypes = [ctypes.c_char_p, ctypes.c_long, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_long]
+    out = np.zeros(len(rbsp) * 2 + 16, np.uint8)
+    n = lib.emu_append_nal(bytes(rbsp), len(rbsp), ref_idc, nal_type, out.ctypes.data, out.size)
+    assert n >= 0
+    return out[:n].tobytes()

@@ -161,3 +161,31 @@ def test_lowres_and_mc_known_answers():
     np.testing.assert_array_equal(O.mc_chroma(ch, 16, 4, 4, 4, 0, 4, 4), (cb(4, 4) + cb(5, 4) + 1) >> 1)     # half way
     np.testing.assert_array_equal(O.mc_chroma(ch, 16, 4, 4, 2, 6, 4, 4),
                                   (12 * cb(4, 4) + 4 * cb(5, 4) + 36 * cb(4, 5) + 12 * cb(5, 5) + 32) >> 6)
+
+
+def test_nal_wrapper_escapes_exactly_like_the_standard_state_machine():
+    """H.264 7.4.1 / B.1: 0x03 goes in front of any byte <= 3 that follows two zero bytes.  The product's wrapper skips from zero
+    byte to zero byte; compare it with the byte-by-byte state machine on payloads full of zeros and on random ones."""
+    import emu_lib
+    rng = np.random.Generator(np.random.PCG64(7))
+
+    def reference(rbsp, ref_idc, t):
+        out, zeros = bytearray([0, 0, 0, 1, (ref_idc << 5) | t]), 0
+        for b in rbsp:
+            if zeros >= 2 and b <= 3:
+                out.append(3)
+                zeros = 0
+            out.append(b)
+            zeros = zeros + 1 if b == 0 else 0
+        return bytes(out)
+
+    cases = [b"", b"\x00", b"\x00\x00", b"\x00\x00\x00", b"\x00\x00\x01", b"\x00\x00\x03\x00\x00\x03", b"\x00" * 17, b"\x01\x00\x00\x04\x00\x00\x02",
+             bytes(range(256)) * 3]
+    for n, zero_share in ((1, 0.5), (7, 0.9), (300, 0.6), (5000, 0.3), (5000, 0.02), (100000, 0.004)):
+        for _ in range(4):
+            v = rng.integers(0, 256, n, dtype=np.uint8)
+            v[rng.random(n) < zero_share] = 0
+            v[rng.random(n) < zero_share / 4] = rng.integers(1, 4)
+            cases.append(v.tobytes())
+    for c in cases:
+        assert emu_lib.append_nal(c, 2, 1) == reference(c, 2, 1), "payload of %d bytes" % len(c)
