@@ -433,7 +433,13 @@ public:
         for (int s = 0; s < active_; ++s) lanes_[size_t(s)].failed = false;
         if (cfg_.device_entropy) {      // the slices arrive finished: wait once (no polling thread), then wrap them
             if ((rc = ops_.sync())) return rc;
-            for (int s = 0; s < active_; ++s) write_stream(s, outs[s]);
+            if (active_ == 1) {
+                write_stream(0, outs[0]);
+            } else {                    // the segments of a batch share nothing: wrap them side by side
+                std::vector<std::thread> pool;
+                for (int s = 0; s < active_; ++s) pool.emplace_back([this, s, outs] { write_stream(s, outs[s]); });
+                for (std::thread &th : pool) th.join();
+            }
         } else {                        // host entropy coding overlaps the GPU: workers start on a picture when its flag is up
             for (int s = 0; s < active_; ++s) write_stream(s, outs[s]);
             if ((rc = ops_.sync())) return rc;
