@@ -203,7 +203,9 @@ public:
         } else {
             astream_ = -1;
         }
-        const AvRational r = a.av_guess_frame_rate(fmt_, st, nullptr);
+        AvRational r = a.av_guess_frame_rate(fmt_, st, nullptr);
+        if (mov && (r.num <= 0 || r.den <= 0) && a.avformat_find_stream_info(fmt_, nullptr) >= 0)    // a header without a usable rate: probe after all
+            r = a.av_guess_frame_rate(fmt_, st, nullptr);
         if (r.num > 0 && r.den > 0) { fps_num = r.num; fps_den = r.den; }
         pkt_ = a.av_packet_alloc();
         for (void *&f : ring_) f = a.av_frame_alloc();
