@@ -152,17 +152,21 @@ GVC_HD void resize_phase1(int tid, const PlaneClassDev &pc, const TileGeom &g, c
                 if (NT >= 6) a = dp2a_hi_su(e1.w, u2, a);
             }
         }
-        return imin(a >> 7, 32767);
+        return a >> 7;                                          // hScale8To15's upper clamp is part of the pack below
     };
 #if !defined(GVC_EMU)
 #pragma unroll 4
 #endif
     for (int r = 0; r < 32; r += 2, w += 2 * pitch_w, t += 4) {
         const int t0 = sample(w), t1 = sample(w + pitch_w);
+        // rows (r, r + 1) as one pair of int16, saturated: min(v, 32767) is swscale's clamp, the lower bound is never reached
+        // (the negative lobes of a filter sum to far less than 2^15 / 255 * 128)
 #if defined(GVC_EMU)
-        *t = ((unsigned)t0 & 0xffffu) | ((unsigned)t1 << 16);      // rows (r, r + 1) as one pair of int16
+        *t = ((unsigned)imax(imin(t0, 32767), -32768) & 0xffffu) | ((unsigned)imax(imin(t1, 32767), -32768) << 16);
 #else
-        *t = __byte_perm((unsigned)t0, (unsigned)t1, 0x5410);      // rows (r, r + 1) as one pair of int16
+        unsigned pr;
+        asm("cvt.pack.sat.s16.s32 %0, %1, %2;" : "=r"(pr) : "r"(t1), "r"(t0));
+        *t = pr;
 #endif
     }
 }
