@@ -208,7 +208,7 @@ GVC_HD void resize_phase2(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
             cf[4 * i] = (unsigned)e.x; cf[4 * i + 1] = (unsigned)e.y; cf[4 * i + 2] = (unsigned)e.z; cf[4 * i + 3] = (unsigned)e.w;
         }
         const gvc_int4 *col = colbase + (((int)cf[0] - g.r0) >> 1);
-        int l0 = 0, l1 = 0, l2 = 0, l3 = 0, h0 = 0, h1 = 0, h2 = 0, h3 = 0;
+        int l0 = 64 << 12, l1 = 64 << 12, l2 = 64 << 12, l3 = 64 << 12, h0 = 0, h1 = 0, h2 = 0, h3 = 0;      // the rounding term rides in the low sums
 #pragma unroll
         for (int j = 0; j < NP; ++j) {
             const unsigned lo = cf[1 + 2 * (j >> 1)], hi = cf[2 + 2 * (j >> 1)];      // bytes 0, 1 for even j, bytes 2, 3 for odd j
@@ -221,7 +221,7 @@ GVC_HD void resize_phase2(int tid, const PlaneClassDev &pc, const PlaneJob &pj, 
             l2 = dp2a_su((unsigned)t.z, lo, l2, up); h2 = dp2a_ss((unsigned)t.z, hi, h2, up);
             l3 = dp2a_su((unsigned)t.w, lo, l3, up); h3 = dp2a_ss((unsigned)t.w, hi, h3, up);
         }
-        const int a0 = (64 << 12) + l0 + h0 * 256, a1 = (64 << 12) + l1 + h1 * 256, a2 = (64 << 12) + l2 + h2 * 256, a3 = (64 << 12) + l3 + h3 * 256;
+        const int a0 = l0 + h0 * 256, a1 = l1 + h1 * 256, a2 = l2 + h2 * 256, a3 = l3 + h3 * 256;
         const unsigned out = pack_sat_u8x4(a0 >> 19, a1 >> 19, a2 >> 19, a3 >> 19);      // two saturating pack instructions
         if (store32) {
             *reinterpret_cast<unsigned *>(p) = out;
